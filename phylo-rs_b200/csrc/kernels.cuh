@@ -1,0 +1,722 @@
+// kernels.cuh — hand-written sm_100a kernels of the Felsenstein-pruning hot path.
+//
+// Data layout in HBM:
+//   tips   u8  [row][P_pad]                     encoded tip codes, sites (patterns) fastest
+//   P      f64 [node][model_cat][4][4]          transition matrix of edge (parent -> node), row-major
+//   clv    f64 [slot][clv_cat][state][tile_pad] conditional likelihoods of one site tile, sites fastest
+//   scale  i32 [clv_cat][tile_pad]              accumulated power-of-two rescaling exponents (bits)
+// Every CLV load/store is a 16-byte (two-site) access on the site axis; P matrices are block-uniform.
+#pragma once
+#include "cuda_compat.h"
+#include <stdint.h>
+#include <math.h>
+
+namespace phb {
+
+constexpr int MAX_CAT = 32;
+constexpr int CLV_THREADS = 256;          // threads per block in the CLV kernels
+constexpr int SITES_PER_BLOCK = 2 * CLV_THREADS;
+
+// tip code: bits 0..3 = state mask over A,C,G,T; bit 4 = gap ('-': all-ones profile, log-scale 0);
+// 0xFF = byte outside Nucleotide::profile's 17 accepted codes (src/alphabet.rs:44-64).
+constexpr uint8_t CODE_GAP = 0x1F;
+constexpr uint8_t CODE_INVALID = 0xFF;
+
+__host__ __device__ inline uint8_t encode_byte(uint8_t c)
+{
+    switch (c) {
+    case 'A': return 1;
+    case 'C': return 2;
+    case 'G': return 4;
+    case 'T':
+    case 'U': return 8;
+    case 'R': return 1 | 4;
+    case 'Y': return 2 | 8;
+    case 'S': return 2 | 4;
+    case 'W': return 1 | 8;
+    case 'K': return 4 | 8;
+    case 'M': return 1 | 2;
+    case 'B': return 2 | 4 | 8;
+    case 'D': return 1 | 4 | 8;
+    case 'H': return 1 | 2 | 8;
+    case 'V': return 1 | 2 | 4;
+    case 'N': return 15;
+    case '-': return CODE_GAP;
+    default: return CODE_INVALID;
+    }
+}
+
+__host__ __device__ inline uint8_t decode_code(uint8_t code)
+{
+    if (code == CODE_GAP) return '-';
+    if (code > 15) return '?';
+    const char *tab = "?ACMGRSVTWYHKDBN";
+    return (uint8_t)tab[code];
+}
+
+// Model handed to kernels by value (constant bank).  phb_set_model, include/phylo_b200.h.
+struct ModelDev {
+    double lambda[4];
+    double V[16]; // column-major: V[i + 4k]
+    double pi[4];
+    double sqrt_pi[4];
+    double inv_sqrt_pi[4];
+    double rates[MAX_CAT];
+    double weights[MAX_CAT];
+    double ln_weights[MAX_CAT];
+    double ln_tip[5];         // ln(1/popcount) for popcount 0..4: leaf Profile::scale() log-scales
+    int clv_idx[MAX_CAT];     // model category -> CLV category index, -1 = closed-form invariant
+    int cat_of_clv[MAX_CAT];  // CLV category -> model category
+    int n_cat;
+    int n_clv;
+};
+
+// One binary internal-node update of a level.  kind bit0/bit1: child 0/1 is a tip.
+struct NodeOp {
+    int32_t out_slot;
+    int32_t c0, c1; // CLV slot (internal child) or alignment row (tip child)
+    int32_t e0, e1; // dense node id of the child == index of its edge's P matrix
+    int32_t kind;
+};
+
+// Generic-arity update (unifurcations, polytomies: src/tree/likelihood.rs:113 iterates any arity).
+struct GenOp {
+    int32_t out_slot;
+    int32_t child_begin, child_end; // range in the GenChild array
+    int32_t pad;
+};
+struct GenChild {
+    int32_t src;  // slot or row
+    int32_t edge; // dense child id
+    int32_t is_tip;
+    int32_t pad;
+};
+
+// ---------------------------------------------------------------------------------------------
+// K0: alignment packing.  ASCII bytes -> tip codes, transposed to [row][P_pad].
+// Replaces the byte->profile step of src/tree/likelihood.rs:104-108 (Nucleotide::profile).
+// ---------------------------------------------------------------------------------------------
+__global__ void pack_pattern_major_kernel(const uint8_t *__restrict__ in, int n_rows, int64_t n_patterns,
+                                          int64_t p_first, uint8_t *__restrict__ tips, int64_t P_pad,
+                                          int64_t dst_off, int *__restrict__ row_invalid)
+{
+    // 32x32 byte tile transpose through shared memory; in[(p_first + p) * n_rows + r]
+    __shared__ uint8_t tile[32][33];
+    int64_t p0 = (int64_t)blockIdx.x * 32;
+    int r0 = blockIdx.y * 32;
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        int64_t p = p0 + j;
+        int r = r0 + threadIdx.x;
+        uint8_t code = CODE_GAP;
+        if (p < n_patterns && r < n_rows) code = encode_byte(in[(p_first + p) * n_rows + r]);
+        tile[j][threadIdx.x] = code;
+    }
+    __syncthreads();
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        int r = r0 + j;
+        int64_t p = p0 + threadIdx.x;
+        if (r < n_rows && p < n_patterns) {
+            uint8_t code = tile[threadIdx.x][j];
+            tips[(int64_t)r * P_pad + dst_off + p] = code;
+            if (code == CODE_INVALID) row_invalid[r] = 1;
+        }
+    }
+}
+
+__global__ void pack_row_major_kernel(const uint8_t *__restrict__ in, int n_rows, int64_t n_patterns,
+                                      int64_t in_stride, int64_t p_first, uint8_t *__restrict__ tips,
+                                      int64_t P_pad, int64_t dst_off, int *__restrict__ row_invalid)
+{
+    int r = blockIdx.y;
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_patterns;
+         p += (int64_t)gridDim.x * blockDim.x) {
+        uint8_t code = encode_byte(in[(int64_t)r * in_stride + p_first + p]);
+        tips[(int64_t)r * P_pad + dst_off + p] = code;
+        if (code == CODE_INVALID) row_invalid[r] = 1;
+    }
+}
+
+__global__ void fill_pad_kernel(uint8_t *__restrict__ tips, int row0, int64_t P, int64_t P_pad)
+{
+    int r = row0 + blockIdx.y;
+    for (int64_t p = P + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P_pad;
+         p += (int64_t)gridDim.x * blockDim.x)
+        tips[(int64_t)r * P_pad + p] = CODE_GAP;
+}
+
+__global__ void mult_to_double_kernel(const uint64_t *__restrict__ in, int64_t n, int64_t n_pad,
+                                      double *__restrict__ out)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_pad;
+         i += (int64_t)gridDim.x * blockDim.x)
+        out[i] = (i < n) ? (in ? (double)in[i] : 1.0) : 0.0;
+}
+
+__global__ void unpack_kernel(const uint8_t *__restrict__ tips, int n_rows, int row0, int64_t P_pad,
+                              int64_t first, int64_t n, int layout, uint8_t *__restrict__ out)
+{
+    int r = row0 + blockIdx.y;
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n;
+         p += (int64_t)gridDim.x * blockDim.x) {
+        uint8_t ch = decode_code(tips[(int64_t)r * P_pad + first + p]);
+        if (layout == 0) out[p * n_rows + r] = ch;
+        else out[(int64_t)r * n + p] = ch;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1: per-branch transition matrices, one thread per (node, model category).
+// P = diag(1/sqrt(pi)) * (V * diag(exp(lambda * r * t))) * V^T * diag(sqrt(pi));
+// exact identity when r * t == 0.0.  Follows GtrModel::category_transition (src/models/gtr.rs:61-64)
+// and RateMatrix::transition (src/models/rate_matrix.rs:113-135).
+// ---------------------------------------------------------------------------------------------
+__global__ void transition_kernel(const double *__restrict__ blen, int n_nodes, ModelDev M,
+                                  double *__restrict__ P)
+{
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n_nodes * M.n_cat) return;
+    int node = idx / M.n_cat, cat = idx - node * M.n_cat;
+    double t = M.rates[cat] * blen[node];
+    double *out = P + (size_t)idx * 16;
+    if (t == 0.0) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) out[i] = ((i >> 2) == (i & 3)) ? 1.0 : 0.0;
+        return;
+    }
+    double e[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) e[k] = exp(M.lambda[k] * t);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            double acc = (M.V[i + 0] * e[0]) * M.V[j + 0];
+#pragma unroll
+            for (int k = 1; k < 4; ++k) acc += (M.V[i + 4 * k] * e[k]) * M.V[j + 4 * k];
+            out[i * 4 + j] = M.inv_sqrt_pi[i] * acc * M.sqrt_pi[j];
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K7: per-pattern tip constants.  leaf_ls = sum over leaves of the Profile::scale() log-scale of
+// the leaf profile (src/tree/likelihood.rs:108, src/tree/likelihood/profile.rs:20-39: R,Y,.. add
+// ln 1/2, B,D,.. ln 1/3, N ln 1/4, gap 0);  inv_mask = AND of all leaf masks = the rate-0 (+I)
+// category's CLV at the root in closed form (src/models/gtr.rs:94-99).
+// ---------------------------------------------------------------------------------------------
+__global__ void tip_constants_kernel(const uint8_t *__restrict__ tips, int64_t P_pad,
+                                     const int32_t *__restrict__ leaf_rows, int n_leaves, ModelDev M,
+                                     double *__restrict__ leaf_ls, uint8_t *__restrict__ inv_mask)
+{
+    int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; // group of 4 sites
+    if (q * 4 >= P_pad) return;
+    double ls[4] = {0.0, 0.0, 0.0, 0.0};
+    uint32_t inv[4] = {15u, 15u, 15u, 15u};
+    for (int l = 0; l < n_leaves; ++l) {
+        uchar4 c4 = *reinterpret_cast<const uchar4 *>(tips + (int64_t)leaf_rows[l] * P_pad + q * 4);
+        uint32_t c[4] = {c4.x, c4.y, c4.z, c4.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            uint32_t m = c[k] & 15u;
+            inv[k] &= m;
+            if (!(c[k] & 16u)) ls[k] += M.ln_tip[__popc(m)];
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        leaf_ls[q * 4 + k] = ls[k];
+        inv_mask[q * 4 + k] = (uint8_t)inv[k];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2: level-batched CLV update (the HBM-bound hot kernel).
+// One block = one (node, CLV category, 512-site block); one thread = one site PAIR, so every CLV
+// access is a 16-byte load/store on the coalesced site axis.  Implements the internal-node branch
+// of prune_pattern_category (src/tree/likelihood.rs:110-131):
+//     v[i] = prod_children ( sum_j P_child[i][j] * clv_child[j] ),
+// with Profile::scale()'s divide-by-max replaced by an exact power-of-two rescale whenever the
+// site maximum drops below 2^-256; exponents accumulate in `scale` (integer atomics: exact and
+// order-independent).  Tip children read one code byte per site and sum the masked columns of P.
+// ---------------------------------------------------------------------------------------------
+constexpr double RESCALE_THRESHOLD = 8.636168555094445e-78; // 2^-256
+
+__device__ __forceinline__ void rescale_site(double &v0, double &v1, double &v2, double &v3, int *acc)
+{
+    double m = fmax(fmax(v0, v1), fmax(v2, v3));
+    if (m < RESCALE_THRESHOLD && m > 0.0) {
+        int s = -ilogb(m);
+        if (s > 1000) s = 1000;
+        double f = __longlong_as_double((long long)(1023 + s) << 52);
+        v0 *= f; v1 *= f; v2 *= f; v3 *= f;
+        atomicAdd(acc, s);
+    }
+}
+
+__device__ __forceinline__ void load_P(const double *__restrict__ Pm, double (&p)[16])
+{
+    const double2 *q = reinterpret_cast<const double2 *>(Pm);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        double2 t = __ldg(q + i);
+        p[2 * i] = t.x;
+        p[2 * i + 1] = t.y;
+    }
+}
+
+// contribution of an internal child for a site pair: out[i] = sum_j P[i][j] * x[j]
+__device__ __forceinline__ void contrib_internal(const double (&p)[16], const double2 *__restrict__ src,
+                                                 size_t stride2, double2 (&out)[4])
+{
+    double2 x0 = src[0], x1 = src[stride2], x2 = src[2 * stride2], x3 = src[3 * stride2];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        out[i].x = p[4 * i] * x0.x + p[4 * i + 1] * x1.x + p[4 * i + 2] * x2.x + p[4 * i + 3] * x3.x;
+        out[i].y = p[4 * i] * x0.y + p[4 * i + 1] * x1.y + p[4 * i + 2] * x2.y + p[4 * i + 3] * x3.y;
+    }
+}
+
+// contribution of a tip child: sum of the columns of P selected by the tip's state mask
+__device__ __forceinline__ double masked_row(const double (&p)[16], int i, uint32_t m)
+{
+    double a = (m & 1u) ? p[4 * i] : 0.0;
+    a += (m & 2u) ? p[4 * i + 1] : 0.0;
+    a += (m & 4u) ? p[4 * i + 2] : 0.0;
+    a += (m & 8u) ? p[4 * i + 3] : 0.0;
+    return a;
+}
+__device__ __forceinline__ void contrib_tip(const double (&p)[16], const uint8_t *__restrict__ codes,
+                                            double2 (&out)[4])
+{
+    uchar2 c = *reinterpret_cast<const uchar2 *>(codes);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        out[i].x = masked_row(p, i, c.x);
+        out[i].y = masked_row(p, i, c.y);
+    }
+}
+
+template <bool TIP0, bool TIP1>
+__device__ __forceinline__ void clv_update_pair(const NodeOp &op, int cat_clv, int cat_model, int n_cat_model,
+                                                const double *__restrict__ Pmat, double *__restrict__ clv,
+                                                size_t slot_stride, size_t tile_pad,
+                                                const uint8_t *__restrict__ tips, int64_t P_pad,
+                                                int64_t tile_off, int *__restrict__ scale, int64_t site)
+{
+    double p[16];
+    double2 a[4], b[4];
+    const size_t stride2 = tile_pad / 2;
+    const size_t cat_off = (size_t)cat_clv * 4 * tile_pad + (size_t)site;
+    load_P(Pmat + ((size_t)op.e0 * n_cat_model + cat_model) * 16, p);
+    if (TIP0) contrib_tip(p, tips + (int64_t)op.c0 * P_pad + tile_off + site, a);
+    else contrib_internal(p, reinterpret_cast<const double2 *>(clv + (size_t)op.c0 * slot_stride + cat_off), stride2, a);
+    load_P(Pmat + ((size_t)op.e1 * n_cat_model + cat_model) * 16, p);
+    if (TIP1) contrib_tip(p, tips + (int64_t)op.c1 * P_pad + tile_off + site, b);
+    else contrib_internal(p, reinterpret_cast<const double2 *>(clv + (size_t)op.c1 * slot_stride + cat_off), stride2, b);
+    double2 v[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        v[i].x = a[i].x * b[i].x;
+        v[i].y = a[i].y * b[i].y;
+    }
+    int *sc = scale + (size_t)cat_clv * tile_pad + site;
+    rescale_site(v[0].x, v[1].x, v[2].x, v[3].x, sc);
+    rescale_site(v[0].y, v[1].y, v[2].y, v[3].y, sc + 1);
+    double2 *dst = reinterpret_cast<double2 *>(clv + (size_t)op.out_slot * slot_stride + cat_off);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) dst[i * stride2] = v[i];
+}
+
+__global__ void __launch_bounds__(CLV_THREADS)
+clv_update_level_kernel(const NodeOp *__restrict__ ops, int n_ops, ModelDev M,
+                        const double *__restrict__ Pmat, double *__restrict__ clv, size_t slot_stride,
+                        size_t tile_pad, int tile_len, int blocks_per_row,
+                        const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off,
+                        int *__restrict__ scale)
+{
+    int sb = blockIdx.x % blocks_per_row;
+    int rest = blockIdx.x / blocks_per_row;
+    int cat_clv = rest % M.n_clv;
+    int opi = rest / M.n_clv;
+    if (opi >= n_ops) return;
+    int64_t site = ((int64_t)sb * CLV_THREADS + threadIdx.x) * 2;
+    if (site >= tile_len) return;
+    const NodeOp op = ops[opi];
+    const int cat_model = M.cat_of_clv[cat_clv];
+    switch (op.kind & 3) {
+    case 0: clv_update_pair<false, false>(op, cat_clv, cat_model, M.n_cat, Pmat, clv, slot_stride, tile_pad, tips, P_pad, tile_off, scale, site); break;
+    case 1: clv_update_pair<true, false>(op, cat_clv, cat_model, M.n_cat, Pmat, clv, slot_stride, tile_pad, tips, P_pad, tile_off, scale, site); break;
+    case 2: clv_update_pair<false, true>(op, cat_clv, cat_model, M.n_cat, Pmat, clv, slot_stride, tile_pad, tips, P_pad, tile_off, scale, site); break;
+    default: clv_update_pair<true, true>(op, cat_clv, cat_model, M.n_cat, Pmat, clv, slot_stride, tile_pad, tips, P_pad, tile_off, scale, site); break;
+    }
+}
+
+// Generic arity (1 child, or > 2 children): running product, rescaled after every child so a
+// polytomy cannot underflow between rescales.
+__global__ void __launch_bounds__(CLV_THREADS)
+clv_update_generic_kernel(const GenOp *__restrict__ ops, int n_ops, const GenChild *__restrict__ kids,
+                          ModelDev M, const double *__restrict__ Pmat, double *__restrict__ clv,
+                          size_t slot_stride, size_t tile_pad, int tile_len, int blocks_per_row,
+                          const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off,
+                          int *__restrict__ scale)
+{
+    int sb = blockIdx.x % blocks_per_row;
+    int rest = blockIdx.x / blocks_per_row;
+    int cat_clv = rest % M.n_clv;
+    int opi = rest / M.n_clv;
+    if (opi >= n_ops) return;
+    int64_t site = ((int64_t)sb * CLV_THREADS + threadIdx.x) * 2;
+    if (site >= tile_len) return;
+    const GenOp op = ops[opi];
+    const int cat_model = M.cat_of_clv[cat_clv];
+    const size_t stride2 = tile_pad / 2;
+    const size_t cat_off = (size_t)cat_clv * 4 * tile_pad + (size_t)site;
+    int *sc = scale + (size_t)cat_clv * tile_pad + site;
+    double2 v[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = make_double2(1.0, 1.0);
+    for (int k = op.child_begin; k < op.child_end; ++k) {
+        const GenChild ch = kids[k];
+        double p[16];
+        double2 a[4];
+        load_P(Pmat + ((size_t)ch.edge * M.n_cat + cat_model) * 16, p);
+        if (ch.is_tip) contrib_tip(p, tips + (int64_t)ch.src * P_pad + tile_off + site, a);
+        else contrib_internal(p, reinterpret_cast<const double2 *>(clv + (size_t)ch.src * slot_stride + cat_off), stride2, a);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            v[i].x *= a[i].x;
+            v[i].y *= a[i].y;
+        }
+        rescale_site(v[0].x, v[1].x, v[2].x, v[3].x, sc);
+        rescale_site(v[0].y, v[1].y, v[2].y, v[3].y, sc + 1);
+    }
+    double2 *dst = reinterpret_cast<double2 *>(clv + (size_t)op.out_slot * slot_stride + cat_off);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) dst[i * stride2] = v[i];
+}
+
+// A tree that is a single leaf (root without children): its "CLV" is the tip mask itself.
+__global__ void clv_from_tip_kernel(double *__restrict__ clv, size_t slot_stride, int out_slot, int n_clv,
+                                    size_t tile_pad, int tile_len, const uint8_t *__restrict__ tips,
+                                    int64_t P_pad, int64_t tile_off, int row)
+{
+    int64_t site = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (site >= tile_len) return;
+    uint32_t m = tips[(int64_t)row * P_pad + tile_off + site];
+    for (int c = 0; c < n_clv; ++c)
+        for (int i = 0; i < 4; ++i)
+            clv[(size_t)out_slot * slot_stride + ((size_t)c * 4 + i) * tile_pad + site] = ((m >> i) & 1u) ? 1.0 : 0.0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K3: root kernel.  Per pattern: root_mass_c = sum_i pi_i * clv_root[c][i]; cat_ll_c = ln w_c +
+// ln root_mass_c + log_scale_c (src/tree/likelihood.rs:135-140); site_ll = log_sum_exp over
+// categories (:61-68, :205); partial = sum mult * site_ll by warp shuffle + block reduction into
+// one double per block (fixed order => deterministic).  The rate-0 (+I) category is evaluated in
+// closed form from inv_mask unless the context carries it as a CLV category.
+// ---------------------------------------------------------------------------------------------
+constexpr int ROOT_THREADS = 256;
+constexpr double LN2 = 0.6931471805599453;
+
+__device__ __forceinline__ double block_reduce_sum(double v)
+{
+    __shared__ double warp_sums[32];
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    if (lane == 0) warp_sums[warp] = v;
+    __syncthreads();
+    double r = 0.0;
+    if (threadIdx.x == 0) {
+        int nw = (blockDim.x + 31) >> 5;
+        for (int w = 0; w < nw; ++w) r += warp_sums[w];
+    }
+    __syncthreads();
+    return r;
+}
+
+__global__ void __launch_bounds__(ROOT_THREADS)
+root_kernel(const double *__restrict__ root_clv /* slot base */, size_t tile_pad, int tile_len,
+            const int *__restrict__ scale, const double *__restrict__ leaf_ls /* + tile_off */,
+            const uint8_t *__restrict__ inv_mask, const double *__restrict__ mult, ModelDev M,
+            double *__restrict__ per_pattern /* + tile_off */, double *__restrict__ cat_ll_out /* nullable [n_cat][tile_pad] */,
+            double *__restrict__ partials)
+{
+    int64_t site = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    double contrib = 0.0;
+    if (site < tile_len) {
+        double lls[MAX_CAT];
+        const double lls_leaf = leaf_ls[site];
+        double mx = -INFINITY;
+        for (int c = 0; c < M.n_cat; ++c) {
+            double mass = 0.0, ls = lls_leaf;
+            int cc = M.clv_idx[c];
+            if (cc >= 0) {
+                const double *r = root_clv + (size_t)cc * 4 * tile_pad + site;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) mass += M.pi[i] * r[(size_t)i * tile_pad];
+                ls -= (double)scale[(size_t)cc * tile_pad + site] * LN2;
+            } else {
+                uint32_t m = inv_mask[site];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) mass += M.pi[i] * (((m >> i) & 1u) ? 1.0 : 0.0);
+            }
+            double ll = M.ln_weights[c] + log(mass) + ls;
+            lls[c] = ll;
+            if (cat_ll_out) cat_ll_out[(size_t)c * tile_pad + site] = ll;
+            mx = fmax(mx, ll);
+        }
+        double site_ll;
+        if (!isfinite(mx)) site_ll = mx;
+        else {
+            double s = 0.0;
+            for (int c = 0; c < M.n_cat; ++c) s += exp(lls[c] - mx);
+            site_ll = mx + log(s);
+        }
+        per_pattern[site] = site_ll;
+        contrib = mult[site] * site_ll;
+    }
+    double r = block_reduce_sum(contrib);
+    if (threadIdx.x == 0) partials[blockIdx.x] = r;
+}
+
+// K4: final deterministic reduction of the per-block partials to one double per GPU.
+__global__ void final_reduce_kernel(const double *__restrict__ partials, int n, double *__restrict__ out)
+{
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) acc += partials[i];
+    double r = block_reduce_sum(acc);
+    if (threadIdx.x == 0) *out = r;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K5/K6: marginal-ASR pre-order pass (src/tree/likelihood.rs:303-398), level-batched from the root.
+// Posteriors overwrite the up-pass CLVs in place (same buffers, same layout).  One thread = one
+// (parent node, pattern): it reads the parent's per-category posterior once, updates EVERY child
+//     post_v = normalise( up_v (.) (P^T post_parent) )            (:321-342)
+// and folds the category mixture  mixed_v = normalise( sum_c w_c post_v,c ),
+// w_c = exp(cat_ll_c - site_ll) or 1/K when site_ll is not finite (:356-382), then the
+// last-maximal-index argmax (:385-390) into one state byte per (node, pattern).
+// ---------------------------------------------------------------------------------------------
+struct DownOp {
+    int32_t parent_slot;
+    int32_t child_begin, child_end; // range in DownChild
+    int32_t pad;
+};
+struct DownChild {
+    int32_t node;  // dense id: P matrix index and row of the states output
+    int32_t src;   // CLV slot (internal) or alignment row (leaf)
+    int32_t is_tip;
+    int32_t pad;
+};
+
+__device__ __forceinline__ int argmax_last(const double (&m)[4])
+{
+    int best = 0;
+#pragma unroll
+    for (int i = 1; i < 4; ++i)
+        if (!(m[best] > m[i])) best = i;
+    return best;
+}
+
+__device__ __forceinline__ void mix_weights(const double *__restrict__ cat_ll, size_t tile_pad, int64_t site,
+                                            double site_ll, int n_cat, double *w)
+{
+    if (isfinite(site_ll))
+        for (int c = 0; c < n_cat; ++c) w[c] = exp(cat_ll[(size_t)c * tile_pad + site] - site_ll);
+    else
+        for (int c = 0; c < n_cat; ++c) w[c] = 1.0 / (double)n_cat;
+}
+
+// Root: post = normalise(pi (.) up_root) per category (:304-316), in place; plus its own mixture.
+__global__ void __launch_bounds__(ROOT_THREADS)
+asr_root_kernel(double *__restrict__ root_clv, size_t tile_pad, int tile_len, ModelDev M,
+                const double *__restrict__ cat_ll, const double *__restrict__ site_ll /* + tile_off */,
+                uint8_t *__restrict__ states_row /* + tile_off */, double *__restrict__ post_row /* nullable, [site][4] */)
+{
+    int64_t site = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (site >= tile_len) return;
+    double w[MAX_CAT];
+    mix_weights(cat_ll, tile_pad, site, site_ll[site], M.n_cat, w);
+    double mixed[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int c = 0; c < M.n_cat; ++c) {
+        double *r = root_clv + (size_t)c * 4 * tile_pad + site;
+        double post[4], sum = 0.0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            post[i] = M.pi[i] * r[(size_t)i * tile_pad];
+            sum += post[i];
+        }
+        if (sum > 0.0) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) post[i] /= sum;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            r[(size_t)i * tile_pad] = post[i];
+            mixed[i] += w[c] * post[i];
+        }
+    }
+    double sum = mixed[0] + mixed[1] + mixed[2] + mixed[3];
+    if (sum > 0.0) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) mixed[i] /= sum;
+    }
+    states_row[site] = (uint8_t)argmax_last(mixed);
+    if (post_row) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) post_row[site * 4 + i] = mixed[i];
+    }
+}
+
+constexpr int DOWN_MAX_CHILDREN = 2; // register fast path; larger arities loop in chunks
+
+__global__ void __launch_bounds__(ROOT_THREADS)
+asr_down_level_kernel(const DownOp *__restrict__ ops, int n_ops, const DownChild *__restrict__ kids,
+                      ModelDev M, const double *__restrict__ Pmat, double *__restrict__ clv,
+                      size_t slot_stride, size_t tile_pad, int tile_len, int blocks_per_row,
+                      const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off,
+                      const double *__restrict__ cat_ll, const double *__restrict__ site_ll /* + tile_off */,
+                      uint8_t *__restrict__ states /* [node][P_pad] */, double *__restrict__ posteriors /* nullable [node][P_pad][4] */)
+{
+    int sb = blockIdx.x % blocks_per_row;
+    int opi = blockIdx.x / blocks_per_row;
+    if (opi >= n_ops) return;
+    int64_t site = (int64_t)sb * blockDim.x + threadIdx.x;
+    if (site >= tile_len) return;
+    const DownOp op = ops[opi];
+    double w[MAX_CAT];
+    mix_weights(cat_ll, tile_pad, site, site_ll[site], M.n_cat, w);
+    for (int k0 = op.child_begin; k0 < op.child_end; k0 += DOWN_MAX_CHILDREN) {
+        int nk = min(DOWN_MAX_CHILDREN, op.child_end - k0);
+        double mixed[DOWN_MAX_CHILDREN][4];
+#pragma unroll
+        for (int k = 0; k < DOWN_MAX_CHILDREN; ++k)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) mixed[k][i] = 0.0;
+        for (int c = 0; c < M.n_cat; ++c) {
+            const double *pp = clv + (size_t)op.parent_slot * slot_stride + (size_t)c * 4 * tile_pad + site;
+            double par[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) par[i] = pp[(size_t)i * tile_pad];
+#pragma unroll
+            for (int k = 0; k < DOWN_MAX_CHILDREN; ++k) {
+                if (k >= nk) break;
+                const DownChild ch = kids[k0 + k];
+                double p[16];
+                load_P(Pmat + ((size_t)ch.node * M.n_cat + c) * 16, p);
+                double up[4];
+                double *self = nullptr;
+                if (ch.is_tip) {
+                    uint32_t m = tips[(int64_t)ch.src * P_pad + tile_off + site];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) up[i] = ((m >> i) & 1u) ? 1.0 : 0.0;
+                } else {
+                    self = clv + (size_t)ch.src * slot_stride + (size_t)c * 4 * tile_pad + site;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) up[i] = self[(size_t)i * tile_pad];
+                }
+                double post[4], sum = 0.0;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { // msg_i = sum_j P[j][i] * par[j]  (P^T * post_parent)
+                    double msg = p[0 * 4 + i] * par[0] + p[1 * 4 + i] * par[1] + p[2 * 4 + i] * par[2] + p[3 * 4 + i] * par[3];
+                    post[i] = up[i] * msg;
+                    sum += post[i];
+                }
+                if (sum > 0.0) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) post[i] /= sum;
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    if (self) self[(size_t)i * tile_pad] = post[i];
+                    mixed[k][i] += w[c] * post[i];
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < DOWN_MAX_CHILDREN; ++k) {
+            if (k >= nk) break;
+            const DownChild ch = kids[k0 + k];
+            double sum = mixed[k][0] + mixed[k][1] + mixed[k][2] + mixed[k][3];
+            if (sum > 0.0) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) mixed[k][i] /= sum;
+            }
+            states[(int64_t)ch.node * P_pad + tile_off + site] = (uint8_t)argmax_last(mixed[k]);
+            if (posteriors) {
+                double *o = posteriors + ((int64_t)ch.node * P_pad + tile_off + site) * 4;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) o[i] = mixed[k][i];
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Synthetic alignment simulator (benchmark input generator): per site draw a rate
+// category ~ weights, a root state ~ pi, then walk the tree in pre-order drawing each child state
+// from row P(r_c t)[parent_state].  Counter-based RNG: splitmix64 of (seed, node, global site).
+// ---------------------------------------------------------------------------------------------
+__host__ __device__ inline uint64_t splitmix64(uint64_t x)
+{
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+__host__ __device__ inline double u01(uint64_t seed, uint64_t node, uint64_t site)
+{
+    uint64_t h = splitmix64(seed ^ splitmix64(node * 0xD1342543DE82EF95ull + 0x632BE59BD9B4E019ull) ^ splitmix64(site));
+    return (double)(h >> 11) * (1.0 / 9007199254740992.0);
+}
+
+__global__ void simulate_kernel(const int32_t *__restrict__ preorder, const int32_t *__restrict__ parent,
+                                const int32_t *__restrict__ depth, const int32_t *__restrict__ leaf_row,
+                                int n_nodes, int root, ModelDev M, const double *__restrict__ Pmat,
+                                uint8_t *__restrict__ stack /* [max_depth+1][P_pad] */,
+                                uint8_t *__restrict__ tips, int64_t P_pad, int64_t n_patterns,
+                                int64_t global_offset, uint64_t seed)
+{
+    int64_t site = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (site >= n_patterns) return;
+    uint64_t g = (uint64_t)(global_offset + site);
+    double u = u01(seed, 0xFFFFFFFFull, g);
+    int cat = M.n_cat - 1;
+    double acc = 0.0;
+    for (int c = 0; c < M.n_cat; ++c) {
+        acc += M.weights[c];
+        if (u < acc) { cat = c; break; }
+    }
+    for (int k = 0; k < n_nodes; ++k) {
+        int v = preorder[k];
+        int s = 3;
+        double uu = u01(seed, (uint64_t)v, g);
+        if (v == root) {
+            double a = 0.0;
+            for (int i = 0; i < 4; ++i) { a += M.pi[i]; if (uu < a) { s = i; break; } }
+        } else {
+            int ps = stack[(int64_t)(depth[v] - 1) * P_pad + site];
+            const double *row = Pmat + ((size_t)v * M.n_cat + cat) * 16 + ps * 4;
+            double a = 0.0;
+            for (int i = 0; i < 4; ++i) { a += row[i]; if (uu < a) { s = i; break; } }
+        }
+        stack[(int64_t)depth[v] * P_pad + site] = (uint8_t)s;
+        int r = leaf_row[v];
+        if (r >= 0) tips[(int64_t)r * P_pad + site] = (uint8_t)(1u << s);
+    }
+}
+
+// FP64 FMA peak microbenchmark (confirms the CLV kernel sits under the HBM roof, not the DFMA roof).
+__global__ void fp64_fma_kernel(double *out, int iters)
+{
+    double a0 = threadIdx.x * 1e-3, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+    const double b = 1.0000001, c = 1e-9;
+    for (int i = 0; i < iters; ++i) {
+        a0 = a0 * b + c; a1 = a1 * b + c; a2 = a2 * b + c; a3 = a3 * b + c;
+        a4 = a4 * b + c; a5 = a5 * b + c; a6 = a6 * b + c; a7 = a7 * b + c;
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+
+} // namespace phb

@@ -1,0 +1,1105 @@
+// phylo_b200.cu — context, host scheduler (H1) and C ABI of libphylo_b200.so.
+//
+// Replaces the bodies of the reference's engines (paths relative to /root/reference):
+//   compute_log_likelihood  src/tree/likelihood.rs:156-209
+//   compute_marginal_asr    src/tree/likelihood.rs:224-408
+// behind the C ABI declared in include/phylo_b200.h.  The host side turns the post-order into
+// levels (a node's level = 1 + max level of its children), assigns CLV slots, tiles the site axis
+// so that a tile's CLVs fit in HBM, and launches the kernels of kernels.cuh level by level.
+#include "kernels.cuh"
+#include "../../include/phylo_b200.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace phb;
+
+namespace {
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        cudaError_t e = cudaMalloc(&p, bytes ? bytes : 16);
+        if (e == cudaSuccess) cap = bytes ? bytes : 16;
+        return e;
+    }
+    void release()
+    {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <typename T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+// Host-side schedule derived from the flattened tree (phb_set_tree).
+struct TreeSched {
+    int n = 0, root = -1;
+    std::vector<int> child_off, children, parent, leaf_row, level, depth, slot;
+    std::vector<double> blen;
+    int n_internal = 0, n_levels = 0, max_depth = 0;
+    std::vector<NodeOp> ops;        // binary updates, grouped by level
+    std::vector<int> level_off;     // n_levels + 1 (level l in 1..n_levels -> index l-1)
+    std::vector<GenOp> gops;        // generic-arity updates, grouped by level
+    std::vector<GenChild> gkids;
+    std::vector<int> glevel_off;
+    std::vector<DownOp> dops;       // ASR pre-order ops (one per internal node), grouped by depth
+    std::vector<DownChild> dkids;
+    std::vector<int> dlevel_off;    // max_depth + 1
+    std::vector<int> leaf_nodes, leaf_rows;
+    double sum_one_plus_i = 0;      // sum over internal nodes of (1 + #internal children)
+    double sum_t = 0;               // total tip children
+    bool valid = false;
+
+    // Builds everything from child lists.  Returns a PHB status.
+    int build(std::string &err)
+    {
+        valid = false;
+        parent.assign(n, -1);
+        for (int v = 0; v < n; ++v)
+            for (int k = child_off[v]; k < child_off[v + 1]; ++k) {
+                int c = children[k];
+                if (c < 0 || c >= n || c == root || parent[c] != -1) {
+                    err = "tree: child id out of range or node with two parents";
+                    return PHB_ERR_NUMERICAL_INSTABILITY;
+                }
+                parent[c] = v;
+            }
+        // iterative left-to-right DFS from the root: post-order + depth
+        std::vector<int> post;
+        post.reserve(n);
+        depth.assign(n, 0);
+        {
+            std::vector<std::pair<int, int>> st;
+            st.emplace_back(root, child_off[root]);
+            while (!st.empty()) {
+                auto &top = st.back();
+                int v = top.first;
+                if (top.second < child_off[v + 1]) {
+                    int c = children[top.second++];
+                    depth[c] = depth[v] + 1;
+                    st.emplace_back(c, child_off[c]);
+                } else {
+                    post.push_back(v);
+                    st.pop_back();
+                }
+            }
+        }
+        if ((int)post.size() != n) {
+            err = "tree: not every node is reachable from the root";
+            return PHB_ERR_NUMERICAL_INSTABILITY;
+        }
+        level.assign(n, 0);
+        slot.assign(n, -1);
+        n_internal = 0;
+        n_levels = 0;
+        max_depth = 0;
+        leaf_nodes.clear();
+        leaf_rows.clear();
+        for (int v : post) {
+            max_depth = std::max(max_depth, depth[v]);
+            int nch = child_off[v + 1] - child_off[v];
+            if (nch == 0) {
+                leaf_nodes.push_back(v);
+                continue;
+            }
+            int lv = 0;
+            for (int k = child_off[v]; k < child_off[v + 1]; ++k) lv = std::max(lv, level[children[k]]);
+            level[v] = lv + 1;
+            n_levels = std::max(n_levels, level[v]);
+            slot[v] = n_internal++;
+        }
+        std::sort(leaf_nodes.begin(), leaf_nodes.end());
+        for (int v : leaf_nodes) leaf_rows.push_back(leaf_row[v]);
+        // group ops by level
+        std::vector<std::vector<int>> by_level(n_levels + 1);
+        for (int v : post)
+            if (level[v] > 0) by_level[level[v]].push_back(v);
+        ops.clear(); gops.clear(); gkids.clear();
+        level_off.assign(1, 0);
+        glevel_off.assign(1, 0);
+        sum_one_plus_i = 0;
+        sum_t = 0;
+        for (int l = 1; l <= n_levels; ++l) {
+            for (int v : by_level[l]) {
+                int b = child_off[v], e = child_off[v + 1];
+                int n_int = 0, n_tip = 0;
+                for (int k = b; k < e; ++k) (slot[children[k]] >= 0 ? n_int : n_tip)++;
+                sum_one_plus_i += 1 + n_int;
+                sum_t += n_tip;
+                if (e - b == 2) {
+                    int c0 = children[b], c1 = children[b + 1];
+                    NodeOp op;
+                    op.out_slot = slot[v];
+                    op.e0 = c0; op.e1 = c1;
+                    op.kind = (slot[c0] < 0 ? 1 : 0) | (slot[c1] < 0 ? 2 : 0);
+                    op.c0 = slot[c0] < 0 ? leaf_row[c0] : slot[c0];
+                    op.c1 = slot[c1] < 0 ? leaf_row[c1] : slot[c1];
+                    ops.push_back(op);
+                } else {
+                    GenOp g;
+                    g.out_slot = slot[v];
+                    g.child_begin = (int)gkids.size();
+                    for (int k = b; k < e; ++k) {
+                        int c = children[k];
+                        GenChild gc;
+                        gc.is_tip = slot[c] < 0;
+                        gc.src = gc.is_tip ? leaf_row[c] : slot[c];
+                        gc.edge = c;
+                        gc.pad = 0;
+                        gkids.push_back(gc);
+                    }
+                    g.child_end = (int)gkids.size();
+                    g.pad = 0;
+                    gops.push_back(g);
+                }
+            }
+            level_off.push_back((int)ops.size());
+            glevel_off.push_back((int)gops.size());
+        }
+        // ASR pre-order ops grouped by the parent's depth
+        std::vector<std::vector<int>> by_depth(max_depth + 1);
+        for (int v = 0; v < n; ++v)
+            if (slot[v] >= 0) by_depth[depth[v]].push_back(v);
+        dops.clear(); dkids.clear();
+        dlevel_off.assign(1, 0);
+        for (int d = 0; d <= max_depth; ++d) {
+            for (int v : by_depth[d]) {
+                DownOp o;
+                o.parent_slot = slot[v];
+                o.child_begin = (int)dkids.size();
+                for (int k = child_off[v]; k < child_off[v + 1]; ++k) {
+                    int c = children[k];
+                    DownChild dc;
+                    dc.node = c;
+                    dc.is_tip = slot[c] < 0;
+                    dc.src = dc.is_tip ? leaf_row[c] : slot[c];
+                    dc.pad = 0;
+                    dkids.push_back(dc);
+                }
+                o.child_end = (int)dkids.size();
+                o.pad = 0;
+                dops.push_back(o);
+            }
+            dlevel_off.push_back((int)dops.size());
+        }
+        valid = true;
+        return PHB_OK;
+    }
+};
+
+struct EventPair {
+    cudaEvent_t a = nullptr, b = nullptr;
+};
+
+struct Device {
+    int ordinal = 0;
+    cudaStream_t stream = nullptr;
+    int64_t p_begin = 0, P = 0, P_pad = 0; // shard of the global pattern range
+    DevBuf tips, mult, leaf_ls, inv_mask, per_pattern, row_invalid, Pmat, blen, clv, scale, cat_ll,
+        partials, total, ops, gops, gkids, dops, dkids, leaf_rows, states, posteriors, staging,
+        sim_pre, sim_parent, sim_depth, sim_leafrow, sim_stack, scratch;
+    double *h_total = nullptr; // pinned
+    int64_t tile_pad = 0;
+    int n_tiles = 0;
+    bool tip_constants_valid = false;
+    std::vector<int> tip_constants_rows;
+    // timing (device 0 only, PHB_FLAG_TIMING)
+    std::vector<EventPair> ev_pool;
+    size_t ev_used = 0;
+    std::vector<std::pair<int, size_t>> ev_log; // (phase, pool index)
+};
+
+enum Phase { PH_TRANSITION = 0, PH_CLV = 1, PH_ROOT = 2, PH_DOWN = 3 };
+
+} // namespace
+
+struct phb_ctx {
+    std::vector<Device> devs;
+    uint64_t flags = 0;
+    uint64_t clv_budget = 0;
+    std::string err;
+    // alignment
+    bool have_aln = false;
+    int n_rows = 0;
+    int64_t n_patterns = 0;
+    std::vector<int> row_invalid_host;
+    // model
+    bool have_model = false;
+    ModelDev model;      // as used by the lnL path (analytic +I unless LITERAL_INVARIANT)
+    ModelDev model_lit;  // literal categories (ASR path)
+    // tree
+    TreeSched tree;
+    bool tree_uploaded = false;
+    // stats
+    phb_stats stats;
+    int64_t launches = 0;
+
+    int fail(int code, const char *fmt, ...)
+    {
+        char buf[512];
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, sizeof buf, fmt, ap);
+        va_end(ap);
+        err = buf;
+        return code;
+    }
+};
+
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return ctx->fail(e_ == cudaErrorMemoryAllocation ? PHB_ERR_OOM : PHB_ERR_CUDA,         \
+                             "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+#define CHECK_LAUNCH()                                                                             \
+    do {                                                                                           \
+        ctx->launches++;                                                                           \
+        cudaError_t e_ = cudaGetLastError();                                                       \
+        if (e_ != cudaSuccess)                                                                     \
+            return ctx->fail(PHB_ERR_CUDA, "kernel launch failed: %s (%s:%d)", cudaGetErrorString(e_), \
+                             __FILE__, __LINE__);                                                  \
+    } while (0)
+
+namespace {
+
+inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+
+// timing helpers: bracket one launch with an event pair on device 0 when PHB_FLAG_TIMING is set
+struct ScopedTimer {
+    phb_ctx *ctx;
+    Device *d;
+    bool on;
+    size_t idx = 0;
+    ScopedTimer(phb_ctx *c, Device *dev, int phase) : ctx(c), d(dev)
+    {
+        on = (c->flags & PHB_FLAG_TIMING) && dev == &c->devs[0];
+        if (!on) return;
+        if (d->ev_used == d->ev_pool.size()) {
+            EventPair ep;
+            cudaEventCreate(&ep.a);
+            cudaEventCreate(&ep.b);
+            d->ev_pool.push_back(ep);
+        }
+        idx = d->ev_used++;
+        d->ev_log.emplace_back(phase, idx);
+        cudaEventRecord(d->ev_pool[idx].a, d->stream);
+    }
+    ~ScopedTimer()
+    {
+        if (on) cudaEventRecord(d->ev_pool[idx].b, d->stream);
+    }
+};
+
+void build_model_dev(const ModelDev &base, bool literal, ModelDev &out)
+{
+    out = base;
+    int n_clv = 0;
+    for (int c = 0; c < out.n_cat; ++c) {
+        if (!literal && out.rates[c] == 0.0) out.clv_idx[c] = -1;
+        else {
+            out.clv_idx[c] = n_clv;
+            out.cat_of_clv[n_clv] = c;
+            ++n_clv;
+        }
+    }
+    out.n_clv = n_clv;
+}
+
+int upload_tree(phb_ctx *ctx)
+{
+    TreeSched &T = ctx->tree;
+    for (Device &d : ctx->devs) {
+        CU(cudaSetDevice(d.ordinal));
+        auto up = [&](DevBuf &b, const void *src, size_t bytes) -> cudaError_t {
+            cudaError_t e = b.ensure(bytes);
+            if (e != cudaSuccess) return e;
+            if (bytes) return cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, d.stream);
+            return cudaSuccess;
+        };
+        CU(up(d.blen, T.blen.data(), sizeof(double) * T.n));
+        CU(up(d.ops, T.ops.data(), sizeof(NodeOp) * T.ops.size()));
+        CU(up(d.gops, T.gops.data(), sizeof(GenOp) * T.gops.size()));
+        CU(up(d.gkids, T.gkids.data(), sizeof(GenChild) * T.gkids.size()));
+        CU(up(d.dops, T.dops.data(), sizeof(DownOp) * T.dops.size()));
+        CU(up(d.dkids, T.dkids.data(), sizeof(DownChild) * T.dkids.size()));
+        CU(up(d.leaf_rows, T.leaf_rows.data(), sizeof(int) * T.leaf_rows.size()));
+        if (d.tip_constants_rows != T.leaf_rows) d.tip_constants_valid = false;
+        // the host vectors stay alive in ctx->tree until the next set_tree, which first syncs
+        CU(cudaStreamSynchronize(d.stream));
+    }
+    ctx->tree_uploaded = true;
+    return PHB_OK;
+}
+
+// Validation shared by both engines: every leaf needs a row (likelihood.rs:99-103) holding only
+// accepted bytes (likelihood.rs:105-107).
+int check_leaves(phb_ctx *ctx)
+{
+    const TreeSched &T = ctx->tree;
+    for (size_t i = 0; i < T.leaf_nodes.size(); ++i) {
+        int r = T.leaf_rows[i];
+        if (r < 0 || r >= ctx->n_rows)
+            return ctx->fail(PHB_ERR_INVALID_ALIGNMENT, "Leaf in tree not found in alignment leaf order (node %d)",
+                             T.leaf_nodes[i]);
+    }
+    for (size_t i = 0; i < T.leaf_nodes.size(); ++i)
+        if (ctx->row_invalid_host[T.leaf_rows[i]])
+            return ctx->fail(PHB_ERR_ALPHABET_MISMATCH, "Invalid char in alignment (row %d)", T.leaf_rows[i]);
+    return PHB_OK;
+}
+
+// Plans the site tiling of one device and (re)allocates the per-evaluation buffers.
+int plan_device(phb_ctx *ctx, Device &d, const ModelDev &M, bool asr, bool want_post)
+{
+    const TreeSched &T = ctx->tree;
+    CU(cudaSetDevice(d.ordinal));
+    if (asr) {
+        CU(d.states.ensure((size_t)T.n * (size_t)d.P_pad));
+        if (want_post) CU(d.posteriors.ensure((size_t)T.n * (size_t)d.P_pad * 4 * sizeof(double)));
+    }
+    CU(d.Pmat.ensure(sizeof(double) * 16 * (size_t)T.n * M.n_cat));
+    CU(d.per_pattern.ensure(sizeof(double) * (size_t)d.P_pad));
+    CU(d.leaf_ls.ensure(sizeof(double) * (size_t)d.P_pad));
+    CU(d.inv_mask.ensure((size_t)d.P_pad));
+    CU(d.total.ensure(sizeof(double)));
+    const int n_slots = std::max(T.n_internal, 1);
+    const size_t per_site = (size_t)n_slots * M.n_clv * 4 * sizeof(double);
+    size_t need_full = per_site * (size_t)d.P_pad;
+    size_t budget = ctx->clv_budget;
+    if (!budget) {
+        size_t free_b = 0, total_b = 0;
+        CU(cudaMemGetInfo(&free_b, &total_b));
+        budget = (size_t)((double)(free_b + d.clv.cap) * 0.85);
+    }
+    int64_t tile = d.P_pad;
+    if (need_full > budget) {
+        tile = (int64_t)(budget / per_site) / SITES_PER_BLOCK * SITES_PER_BLOCK;
+        if (tile < SITES_PER_BLOCK)
+            return ctx->fail(PHB_ERR_OOM, "CLV budget %zu B cannot hold one %d-site tile of %d slots", budget,
+                             SITES_PER_BLOCK, n_slots);
+    }
+    d.tile_pad = tile;
+    d.n_tiles = (int)((d.P + tile - 1) / tile);
+    if (d.P == 0) d.n_tiles = 0;
+    CU(d.clv.ensure(per_site * (size_t)tile));
+    CU(d.scale.ensure(sizeof(int) * (size_t)std::max(M.n_clv, 1) * (size_t)tile));
+    if (asr) CU(d.cat_ll.ensure(sizeof(double) * (size_t)M.n_cat * (size_t)tile));
+    size_t n_part = 0;
+    for (int t = 0; t < d.n_tiles; ++t) {
+        int64_t len = std::min<int64_t>(tile, d.P - (int64_t)t * tile);
+        n_part += (size_t)((len + ROOT_THREADS - 1) / ROOT_THREADS);
+    }
+    CU(d.partials.ensure(sizeof(double) * std::max<size_t>(n_part, 1)));
+    return PHB_OK;
+}
+
+// The up pass of one tile: all levels, then the root kernel.
+int run_tile_up(phb_ctx *ctx, Device &d, const ModelDev &M, int64_t tile_off, int tile_len, size_t part_off,
+                bool want_cat_ll)
+{
+    const TreeSched &T = ctx->tree;
+    const size_t tile_pad = (size_t)d.tile_pad;
+    const size_t slot_stride = (size_t)M.n_clv * 4 * tile_pad;
+    const int bpr = (tile_len + SITES_PER_BLOCK - 1) / SITES_PER_BLOCK;
+    if (M.n_clv > 0) CU(cudaMemsetAsync(d.scale.p, 0, sizeof(int) * (size_t)M.n_clv * tile_pad, d.stream));
+    if (T.n_internal == 0) {
+        // single-leaf tree: the root is a tip
+        if (M.n_clv > 0) {
+            ScopedTimer tm(ctx, &d, PH_CLV);
+            PHB_LAUNCH(clv_from_tip_kernel, dim3((tile_len + 255) / 256), dim3(256), d.stream, d.clv.as<double>(),
+                       slot_stride, 0, M.n_clv, tile_pad, tile_len, d.tips.as<uint8_t>(), d.P_pad, tile_off,
+                       T.leaf_row[T.root]);
+            CHECK_LAUNCH();
+        }
+    } else if (M.n_clv > 0) {
+        for (int l = 1; l <= T.n_levels; ++l) {
+            int nb = T.level_off[l] - T.level_off[l - 1];
+            if (nb > 0) {
+                ScopedTimer tm(ctx, &d, PH_CLV);
+                int64_t grid = (int64_t)nb * M.n_clv * bpr;
+                PHB_LAUNCH(clv_update_level_kernel, dim3((unsigned)grid), dim3(CLV_THREADS), d.stream,
+                           d.ops.as<NodeOp>() + T.level_off[l - 1], nb, M, d.Pmat.as<double>(), d.clv.as<double>(),
+                           slot_stride, tile_pad, tile_len, bpr, d.tips.as<uint8_t>(), d.P_pad, tile_off,
+                           d.scale.as<int>());
+                CHECK_LAUNCH();
+                if (&d == &ctx->devs[0]) ctx->stats.clv_launches++;
+            }
+            int ng = T.glevel_off[l] - T.glevel_off[l - 1];
+            if (ng > 0) {
+                ScopedTimer tm(ctx, &d, PH_CLV);
+                int64_t grid = (int64_t)ng * M.n_clv * bpr;
+                PHB_LAUNCH(clv_update_generic_kernel, dim3((unsigned)grid), dim3(CLV_THREADS), d.stream,
+                           d.gops.as<GenOp>() + T.glevel_off[l - 1], ng, d.gkids.as<GenChild>(), M,
+                           d.Pmat.as<double>(), d.clv.as<double>(), slot_stride, tile_pad, tile_len, bpr,
+                           d.tips.as<uint8_t>(), d.P_pad, tile_off, d.scale.as<int>());
+                CHECK_LAUNCH();
+                if (&d == &ctx->devs[0]) ctx->stats.clv_launches++;
+            }
+        }
+    }
+    {
+        ScopedTimer tm(ctx, &d, PH_ROOT);
+        int root_slot = T.n_internal == 0 ? 0 : T.slot[T.root];
+        PHB_LAUNCH(root_kernel, dim3((tile_len + ROOT_THREADS - 1) / ROOT_THREADS), dim3(ROOT_THREADS), d.stream,
+                   d.clv.as<double>() + (size_t)root_slot * slot_stride, tile_pad, tile_len, d.scale.as<int>(),
+                   d.leaf_ls.as<double>() + tile_off, d.inv_mask.as<uint8_t>() + tile_off,
+                   d.mult.as<double>() + tile_off, M, d.per_pattern.as<double>() + tile_off,
+                   want_cat_ll ? d.cat_ll.as<double>() : (double *)nullptr, d.partials.as<double>() + part_off);
+        CHECK_LAUNCH();
+    }
+    return PHB_OK;
+}
+
+int run_tile_down(phb_ctx *ctx, Device &d, const ModelDev &M, int64_t tile_off, int tile_len, bool want_post)
+{
+    const TreeSched &T = ctx->tree;
+    const size_t tile_pad = (size_t)d.tile_pad;
+    const size_t slot_stride = (size_t)M.n_clv * 4 * tile_pad;
+    const int bpr = (tile_len + ROOT_THREADS - 1) / ROOT_THREADS;
+    uint8_t *states = d.states.as<uint8_t>();
+    double *post = want_post ? d.posteriors.as<double>() : nullptr;
+    {
+        ScopedTimer tm(ctx, &d, PH_DOWN);
+        int root_slot = T.n_internal == 0 ? 0 : T.slot[T.root];
+        PHB_LAUNCH(asr_root_kernel, dim3(bpr), dim3(ROOT_THREADS), d.stream,
+                   d.clv.as<double>() + (size_t)root_slot * slot_stride, tile_pad, tile_len, M, d.cat_ll.as<double>(),
+                   d.per_pattern.as<double>() + tile_off, states + (int64_t)T.root * d.P_pad + tile_off,
+                   post ? post + ((int64_t)T.root * d.P_pad + tile_off) * 4 : (double *)nullptr);
+        CHECK_LAUNCH();
+    }
+    for (int dl = 0; dl <= T.max_depth; ++dl) {
+        int nb = T.dlevel_off[dl + 1] - T.dlevel_off[dl];
+        if (nb <= 0) continue;
+        ScopedTimer tm(ctx, &d, PH_DOWN);
+        int64_t grid = (int64_t)nb * bpr;
+        PHB_LAUNCH(asr_down_level_kernel, dim3((unsigned)grid), dim3(ROOT_THREADS), d.stream,
+                   d.dops.as<DownOp>() + T.dlevel_off[dl], nb, d.dkids.as<DownChild>(), M, d.Pmat.as<double>(),
+                   d.clv.as<double>(), slot_stride, tile_pad, tile_len, bpr, d.tips.as<uint8_t>(), d.P_pad, tile_off,
+                   d.cat_ll.as<double>(), d.per_pattern.as<double>() + tile_off, states, post);
+        CHECK_LAUNCH();
+    }
+    return PHB_OK;
+}
+
+// One full evaluation on every device.  asr=false: compute_log_likelihood; asr=true: + down pass.
+int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total)
+{
+    if (!ctx->have_aln || !ctx->have_model || !ctx->tree.valid)
+        return ctx->fail(PHB_ERR_STATE, "set_alignment, set_model and set_tree must precede an evaluation");
+    const TreeSched &T = ctx->tree;
+    ctx->stats.clv_launches = 0;
+    ctx->stats.clv_updates = 0;
+    ctx->stats.algorithmic_bytes = 0;
+    if (ctx->n_patterns == 0) { // empty alignment: the pattern loop never runs (likelihood.rs:185-208)
+        *total = 0.0;
+        return PHB_OK;
+    }
+    int rc = check_leaves(ctx);
+    if (rc) return rc;
+    if (!ctx->tree_uploaded) {
+        rc = upload_tree(ctx);
+        if (rc) return rc;
+    }
+    const ModelDev &M = asr ? ctx->model_lit : ctx->model;
+    Device &d0 = ctx->devs[0];
+    d0.ev_used = 0;
+    d0.ev_log.clear();
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+    const bool timing = ctx->flags & PHB_FLAG_TIMING;
+    for (Device &d : ctx->devs) {
+        rc = plan_device(ctx, d, M, asr, want_post);
+        if (rc) return rc;
+    }
+    if (timing) {
+        CU(cudaSetDevice(d0.ordinal));
+        CU(cudaEventCreate(&ev_begin));
+        CU(cudaEventCreate(&ev_end));
+        CU(cudaEventRecord(ev_begin, d0.stream));
+    }
+    // enqueue everything on every device's stream, then join
+    for (Device &d : ctx->devs) {
+        CU(cudaSetDevice(d.ordinal));
+        if (d.P == 0) {
+            *d.h_total = 0.0;
+            continue;
+        }
+        {
+            ScopedTimer tm(ctx, &d, PH_TRANSITION);
+            int nthreads = T.n * M.n_cat;
+            PHB_LAUNCH(transition_kernel, dim3((nthreads + 127) / 128), dim3(128), d.stream, d.blen.as<double>(), T.n, M,
+                       d.Pmat.as<double>());
+            CHECK_LAUNCH();
+        }
+        if (!d.tip_constants_valid) {
+            ScopedTimer tm(ctx, &d, PH_ROOT);
+            int64_t groups = d.P_pad / 4;
+            PHB_LAUNCH(tip_constants_kernel, dim3((unsigned)((groups + 255) / 256)), dim3(256), d.stream,
+                       d.tips.as<uint8_t>(), d.P_pad, d.leaf_rows.as<int32_t>(), (int)T.leaf_rows.size(), M,
+                       d.leaf_ls.as<double>(), d.inv_mask.as<uint8_t>());
+            CHECK_LAUNCH();
+            d.tip_constants_valid = true;
+            d.tip_constants_rows = T.leaf_rows;
+        }
+        size_t part_off = 0;
+        for (int t = 0; t < d.n_tiles; ++t) {
+            int64_t off = (int64_t)t * d.tile_pad;
+            int len = (int)std::min<int64_t>(d.tile_pad, d.P - off);
+            rc = run_tile_up(ctx, d, M, off, len, part_off, asr);
+            if (rc) return rc;
+            if (asr) {
+                rc = run_tile_down(ctx, d, M, off, len, want_post);
+                if (rc) return rc;
+            }
+            part_off += (size_t)((len + ROOT_THREADS - 1) / ROOT_THREADS);
+        }
+        {
+            ScopedTimer tm(ctx, &d, PH_ROOT);
+            PHB_LAUNCH(final_reduce_kernel, dim3(1), dim3(1024), d.stream, d.partials.as<double>(), (int)part_off,
+                       d.total.as<double>());
+            CHECK_LAUNCH();
+        }
+        CU(cudaMemcpyAsync(d.h_total, d.total.p, sizeof(double), cudaMemcpyDeviceToHost, d.stream));
+    }
+    if (timing) {
+        CU(cudaSetDevice(d0.ordinal));
+        CU(cudaEventRecord(ev_end, d0.stream));
+    }
+    double sum = 0.0;
+    for (Device &d : ctx->devs) { // rank-ordered host sum: deterministic
+        CU(cudaSetDevice(d.ordinal));
+        CU(cudaStreamSynchronize(d.stream));
+        sum += *d.h_total;
+    }
+    *total = sum;
+    // stats
+    phb_stats &S = ctx->stats;
+    S.n_patterns = ctx->n_patterns;
+    S.tile_patterns = d0.tile_pad;
+    S.n_tiles = d0.n_tiles;
+    S.n_levels = T.n_levels;
+    S.n_internal = T.n_internal;
+    S.n_clv_categories = M.n_clv;
+    S.kernel_launches = ctx->launches;
+    S.clv_updates = (int64_t)T.n_internal * ctx->n_patterns;
+    S.algorithmic_bytes = (32.0 * M.n_clv * T.sum_one_plus_i + T.sum_t) * (double)ctx->n_patterns;
+    if (timing) {
+        S.ms_transition = S.ms_clv = S.ms_root = S.ms_down = 0;
+        for (auto &pr : d0.ev_log) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, d0.ev_pool[pr.second].a, d0.ev_pool[pr.second].b);
+            (pr.first == PH_TRANSITION ? S.ms_transition : pr.first == PH_CLV ? S.ms_clv : pr.first == PH_ROOT ? S.ms_root : S.ms_down) += ms;
+        }
+        float ms = 0;
+        cudaEventElapsedTime(&ms, ev_begin, ev_end);
+        S.ms_total = ms;
+        cudaEventDestroy(ev_begin);
+        cudaEventDestroy(ev_end);
+    }
+    return PHB_OK;
+}
+
+} // namespace
+
+// =================================================================================================
+// C ABI
+// =================================================================================================
+extern "C" {
+
+const char *phb_version(void) { return "phylo_b200 0.1.0 (sm_100a)"; }
+
+const char *phb_last_error(phb_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int32_t phb_ctx_create(const int32_t *devices, int32_t n_dev, uint64_t flags, phb_ctx **out)
+{
+    if (!out) return PHB_ERR_INVALID_ARGUMENT;
+    *out = nullptr;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) return PHB_ERR_CUDA;
+    std::vector<int> ords;
+    if (!devices || n_dev <= 0) ords.push_back(0);
+    else ords.assign(devices, devices + n_dev);
+    phb_ctx *ctx = new phb_ctx();
+    ctx->flags = flags;
+    memset(&ctx->stats, 0, sizeof ctx->stats);
+    memset(&ctx->model, 0, sizeof ctx->model);
+    for (int o : ords) {
+        if (o < 0 || o >= count) {
+            delete ctx;
+            return PHB_ERR_INVALID_ARGUMENT;
+        }
+        int major = 0;
+        cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, o);
+        if (major != 10) { // the kernels exist only as sm_100a SASS; there is no other path
+            delete ctx;
+            return PHB_ERR_CUDA;
+        }
+    }
+    ctx->devs.resize(ords.size());
+    for (size_t i = 0; i < ords.size(); ++i) {
+        Device &d = ctx->devs[i];
+        d.ordinal = ords[i];
+        if (cudaSetDevice(d.ordinal) != cudaSuccess || cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaHostAlloc((void **)&d.h_total, sizeof(double), cudaHostAllocDefault) != cudaSuccess) {
+            phb_ctx_destroy(ctx);
+            return PHB_ERR_CUDA;
+        }
+    }
+    *out = ctx;
+    return PHB_OK;
+}
+
+void phb_ctx_destroy(phb_ctx *ctx)
+{
+    if (!ctx) return;
+    for (Device &d : ctx->devs) {
+        cudaSetDevice(d.ordinal);
+        if (d.stream) cudaStreamSynchronize(d.stream);
+        DevBuf *bufs[] = {&d.tips, &d.mult, &d.leaf_ls, &d.inv_mask, &d.per_pattern, &d.row_invalid, &d.Pmat, &d.blen,
+                          &d.clv, &d.scale, &d.cat_ll, &d.partials, &d.total, &d.ops, &d.gops, &d.gkids, &d.dops,
+                          &d.dkids, &d.leaf_rows, &d.states, &d.posteriors, &d.staging, &d.sim_pre, &d.sim_parent,
+                          &d.sim_depth, &d.sim_leafrow, &d.sim_stack, &d.scratch};
+        for (DevBuf *b : bufs) b->release();
+        for (auto &ep : d.ev_pool) {
+            cudaEventDestroy(ep.a);
+            cudaEventDestroy(ep.b);
+        }
+        if (d.h_total) cudaFreeHost(d.h_total);
+        if (d.stream) cudaStreamDestroy(d.stream);
+    }
+    delete ctx;
+}
+
+int32_t phb_set_clv_budget(phb_ctx *ctx, uint64_t bytes)
+{
+    if (!ctx) return PHB_ERR_INVALID_ARGUMENT;
+    ctx->clv_budget = bytes;
+    return PHB_OK;
+}
+
+// Shards [0, P) contiguously over the devices and sizes the per-device alignment buffers.
+static int shard_and_alloc(phb_ctx *ctx, int n_rows, int64_t P)
+{
+    const int G = (int)ctx->devs.size();
+    int64_t per = (P + G - 1) / G;
+    per = round_up(per, 2);
+    for (int g = 0; g < G; ++g) {
+        Device &d = ctx->devs[g];
+        d.p_begin = std::min<int64_t>((int64_t)g * per, P);
+        d.P = std::min<int64_t>(per, P - d.p_begin);
+        d.P_pad = std::max<int64_t>(round_up(d.P, SITES_PER_BLOCK), SITES_PER_BLOCK);
+        d.tip_constants_valid = false;
+        CU(cudaSetDevice(d.ordinal));
+        CU(d.tips.ensure((size_t)std::max(n_rows, 1) * (size_t)d.P_pad));
+        CU(d.mult.ensure(sizeof(double) * (size_t)d.P_pad));
+        CU(d.row_invalid.ensure(sizeof(int) * (size_t)std::max(n_rows, 1)));
+        CU(cudaMemsetAsync(d.row_invalid.p, 0, sizeof(int) * (size_t)std::max(n_rows, 1), d.stream));
+    }
+    ctx->n_rows = n_rows;
+    ctx->n_patterns = P;
+    return PHB_OK;
+}
+
+int32_t phb_set_alignment(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns, const uint8_t *bytes, int32_t layout,
+                          const uint64_t *multiplicity)
+{
+    if (!ctx) return PHB_ERR_INVALID_ARGUMENT;
+    if (n_rows < 0 || n_patterns < 0 || (layout != PHB_LAYOUT_PATTERN_MAJOR && layout != PHB_LAYOUT_ROW_MAJOR) ||
+        (!bytes && n_rows > 0 && n_patterns > 0))
+        return ctx->fail(PHB_ERR_INVALID_ARGUMENT, "set_alignment: bad arguments");
+    ctx->have_aln = false;
+    int rc = shard_and_alloc(ctx, n_rows, n_patterns);
+    if (rc) return rc;
+    ctx->row_invalid_host.assign(std::max(n_rows, 1), 0);
+    const size_t CHUNK = (size_t)256 << 20; // staging bytes per H2D copy
+    for (Device &d : ctx->devs) {
+        CU(cudaSetDevice(d.ordinal));
+        if (d.P > 0 && n_rows > 0) {
+            if (layout == PHB_LAYOUT_PATTERN_MAJOR) {
+                int64_t pp = std::max<int64_t>(1, (int64_t)(CHUNK / (size_t)n_rows));
+                pp = std::min<int64_t>(pp, d.P);
+                CU(d.staging.ensure((size_t)pp * n_rows));
+                for (int64_t p0 = 0; p0 < d.P; p0 += pp) {
+                    int64_t np = std::min<int64_t>(pp, d.P - p0);
+                    CU(cudaMemcpyAsync(d.staging.p, bytes + (size_t)(d.p_begin + p0) * n_rows, (size_t)np * n_rows,
+                                       cudaMemcpyHostToDevice, d.stream));
+                    dim3 grid((unsigned)((np + 31) / 32), (unsigned)((n_rows + 31) / 32));
+                    PHB_LAUNCH(pack_pattern_major_kernel, grid, dim3(32, 8), d.stream, d.staging.as<uint8_t>(), n_rows,
+                               np, (int64_t)0, d.tips.as<uint8_t>(), d.P_pad, p0, d.row_invalid.as<int>());
+                    CHECK_LAUNCH();
+                }
+            } else {
+                int64_t rr = std::max<int64_t>(1, (int64_t)(CHUNK / (size_t)d.P));
+                rr = std::min<int64_t>(std::min<int64_t>(rr, n_rows), 32768);
+                CU(d.staging.ensure((size_t)rr * d.P));
+                for (int64_t r0 = 0; r0 < n_rows; r0 += rr) {
+                    int64_t nr = std::min<int64_t>(rr, n_rows - r0);
+                    CU(cudaMemcpy2DAsync(d.staging.p, (size_t)d.P, bytes + (size_t)r0 * n_patterns + d.p_begin,
+                                         (size_t)n_patterns, (size_t)d.P, (size_t)nr, cudaMemcpyHostToDevice, d.stream));
+                    dim3 grid((unsigned)std::min<int64_t>((d.P + 255) / 256, 4096), (unsigned)nr);
+                    PHB_LAUNCH(pack_row_major_kernel, grid, dim3(256), d.stream, d.staging.as<uint8_t>(), (int)nr, d.P,
+                               d.P, (int64_t)0, d.tips.as<uint8_t>() + (size_t)r0 * d.P_pad, d.P_pad, (int64_t)0,
+                               d.row_invalid.as<int>() + r0);
+                    CHECK_LAUNCH();
+                }
+            }
+        }
+        for (int r0 = 0; r0 < n_rows && d.P_pad > d.P; r0 += 32768) {
+            dim3 grid((unsigned)((d.P_pad - d.P + 255) / 256), (unsigned)std::min(32768, n_rows - r0));
+            PHB_LAUNCH(fill_pad_kernel, grid, dim3(256), d.stream, d.tips.as<uint8_t>(), r0, d.P, d.P_pad);
+            CHECK_LAUNCH();
+        }
+        // multiplicities
+        const uint64_t *dm = nullptr;
+        if (multiplicity && d.P > 0) {
+            CU(d.scratch.ensure(sizeof(uint64_t) * (size_t)d.P));
+            CU(cudaMemcpyAsync(d.scratch.p, multiplicity + d.p_begin, sizeof(uint64_t) * (size_t)d.P,
+                               cudaMemcpyHostToDevice, d.stream));
+            dm = d.scratch.as<uint64_t>();
+        }
+        PHB_LAUNCH(mult_to_double_kernel, dim3((unsigned)std::min<int64_t>((d.P_pad + 255) / 256, 4096)), dim3(256),
+                   d.stream, dm, d.P, d.P_pad, d.mult.as<double>());
+        CHECK_LAUNCH();
+    }
+    // join + gather the per-row validity flags
+    std::vector<int> tmp(std::max(n_rows, 1));
+    for (Device &d : ctx->devs) {
+        CU(cudaSetDevice(d.ordinal));
+        CU(cudaMemcpyAsync(tmp.data(), d.row_invalid.p, sizeof(int) * (size_t)std::max(n_rows, 1), cudaMemcpyDeviceToHost,
+                           d.stream));
+        CU(cudaStreamSynchronize(d.stream));
+        for (int r = 0; r < n_rows; ++r) ctx->row_invalid_host[r] |= tmp[r];
+    }
+    ctx->have_aln = true;
+    return PHB_OK;
+}
+
+int32_t phb_set_model(phb_ctx *ctx, const double *lambda, const double *V, const double *pi, const double *sqrt_pi,
+                      const double *inv_sqrt_pi, int32_t n_cat, const double *rates, const double *weights)
+{
+    if (!ctx) return PHB_ERR_INVALID_ARGUMENT;
+    if (!lambda || !V || !pi || !sqrt_pi || !inv_sqrt_pi || !rates || !weights)
+        return ctx->fail(PHB_ERR_INVALID_ARGUMENT, "set_model: null pointer");
+    if (n_cat < 1 || n_cat > MAX_CAT)
+        return ctx->fail(PHB_ERR_INVALID_MODEL_PARAMETER, "set_model: n_cat must be in [1, %d]", MAX_CAT);
+    ModelDev M;
+    memset(&M, 0, sizeof M);
+    memcpy(M.lambda, lambda, sizeof M.lambda);
+    memcpy(M.V, V, sizeof M.V);
+    memcpy(M.pi, pi, sizeof M.pi);
+    memcpy(M.sqrt_pi, sqrt_pi, sizeof M.sqrt_pi);
+    memcpy(M.inv_sqrt_pi, inv_sqrt_pi, sizeof M.inv_sqrt_pi);
+    for (int c = 0; c < n_cat; ++c) {
+        M.rates[c] = rates[c];
+        M.weights[c] = weights[c];
+        M.ln_weights[c] = std::log(weights[c]);
+    }
+    // leaf Profile::scale() constants: ln(max) with max = 1, 0.5, 1/3, 0.25 (alphabet.rs:44-64)
+    M.ln_tip[0] = 0.0;
+    M.ln_tip[1] = 0.0;
+    M.ln_tip[2] = std::log(0.5);
+    M.ln_tip[3] = std::log(1.0 / 3.0);
+    M.ln_tip[4] = std::log(0.25);
+    M.n_cat = n_cat;
+    build_model_dev(M, (ctx->flags & PHB_FLAG_LITERAL_INVARIANT) != 0, ctx->model);
+    build_model_dev(M, true, ctx->model_lit);
+    ctx->have_model = true;
+    return PHB_OK;
+}
+
+int32_t phb_set_tree(phb_ctx *ctx, int32_t n_nodes, const int32_t *postorder, const int32_t *child_offsets,
+                     const int32_t *children, const double *branch_len, const int32_t *leaf_row, int32_t root)
+{
+    if (!ctx) return PHB_ERR_INVALID_ARGUMENT;
+    if (n_nodes < 1 || !postorder || !child_offsets || !branch_len || !leaf_row || root < 0 || root >= n_nodes)
+        return ctx->fail(PHB_ERR_INVALID_ARGUMENT, "set_tree: bad arguments");
+    if (child_offsets[0] != 0 || child_offsets[n_nodes] != n_nodes - 1 || (n_nodes > 1 && !children))
+        return ctx->fail(PHB_ERR_INVALID_ARGUMENT, "set_tree: child CSR must hold exactly n_nodes - 1 edges");
+    for (int v = 0; v < n_nodes; ++v)
+        if (child_offsets[v + 1] < child_offsets[v])
+            return ctx->fail(PHB_ERR_INVALID_ARGUMENT, "set_tree: child offsets must be non-decreasing");
+    for (Device &d : ctx->devs) { // previous uploads read the old host vectors
+        cudaSetDevice(d.ordinal);
+        cudaStreamSynchronize(d.stream);
+    }
+    TreeSched &T = ctx->tree;
+    T.n = n_nodes;
+    T.root = root;
+    T.child_off.assign(child_offsets, child_offsets + n_nodes + 1);
+    T.children.assign(children, children + (n_nodes - 1));
+    T.blen.assign(branch_len, branch_len + n_nodes);
+    T.leaf_row.assign(leaf_row, leaf_row + n_nodes);
+    ctx->tree_uploaded = false;
+    int rc = T.build(ctx->err);
+    if (rc) return rc;
+    // the caller's post-order must be a valid schedule (children before parents, root last)
+    {
+        std::vector<char> seen(n_nodes, 0);
+        for (int k = 0; k < n_nodes; ++k) {
+            int v = postorder[k];
+            if (v < 0 || v >= n_nodes || seen[v]) {
+                T.valid = false;
+                return ctx->fail(PHB_ERR_NUMERICAL_INSTABILITY, "set_tree: postorder is not a permutation");
+            }
+            for (int c = child_offsets[v]; c < child_offsets[v + 1]; ++c)
+                if (!seen[children[c]]) {
+                    T.valid = false;
+                    return ctx->fail(PHB_ERR_NUMERICAL_INSTABILITY, "set_tree: node %d precedes its child in postorder", v);
+                }
+            seen[v] = 1;
+        }
+    }
+    return upload_tree(ctx);
+}
+
+int32_t phb_log_likelihood(phb_ctx *ctx, double *total, double *per_pattern)
+{
+    if (!ctx || !total) return PHB_ERR_INVALID_ARGUMENT;
+    int rc = evaluate(ctx, false, false, total);
+    if (rc) return rc;
+    if (per_pattern) return phb_get_per_pattern(ctx, per_pattern);
+    return PHB_OK;
+}
+
+int32_t phb_get_per_pattern(phb_ctx *ctx, double *per_pattern)
+{
+    if (!ctx || !per_pattern) return PHB_ERR_INVALID_ARGUMENT;
+    for (Device &d : ctx->devs) {
+        if (d.P == 0) continue;
+        CU(cudaSetDevice(d.ordinal));
+        if (d.per_pattern.cap < sizeof(double) * (size_t)d.P)
+            return ctx->fail(PHB_ERR_STATE, "no evaluation has run yet");
+        CU(cudaMemcpyAsync(per_pattern + d.p_begin, d.per_pattern.p, sizeof(double) * (size_t)d.P, cudaMemcpyDeviceToHost,
+                           d.stream));
+        CU(cudaStreamSynchronize(d.stream));
+    }
+    return PHB_OK;
+}
+
+int32_t phb_marginal_asr(phb_ctx *ctx, uint8_t *states, double *posteriors, double *total)
+{
+    if (!ctx || !total || !states) return PHB_ERR_INVALID_ARGUMENT;
+    int rc = evaluate(ctx, true, posteriors != nullptr, total);
+    if (rc) return rc;
+    const int n = ctx->tree.n;
+    const int64_t P = ctx->n_patterns;
+    for (Device &d : ctx->devs) {
+        if (d.P == 0) continue;
+        CU(cudaSetDevice(d.ordinal));
+        CU(cudaMemcpy2DAsync(states + d.p_begin, (size_t)P, d.states.p, (size_t)d.P_pad, (size_t)d.P, (size_t)n,
+                             cudaMemcpyDeviceToHost, d.stream));
+        if (posteriors)
+            CU(cudaMemcpy2DAsync(posteriors + d.p_begin * 4, (size_t)P * 4 * sizeof(double), d.posteriors.p,
+                                 (size_t)d.P_pad * 4 * sizeof(double), (size_t)d.P * 4 * sizeof(double), (size_t)n,
+                                 cudaMemcpyDeviceToHost, d.stream));
+        CU(cudaStreamSynchronize(d.stream));
+    }
+    return PHB_OK;
+}
+
+int32_t phb_score_nni(phb_ctx *ctx, int32_t n_moves, const int32_t *node_id, const uint8_t *left_ch, double *totals)
+{
+    if (!ctx || n_moves < 0 || (n_moves > 0 && (!node_id || !left_ch || !totals))) return PHB_ERR_INVALID_ARGUMENT;
+    if (!ctx->tree.valid) return ctx->fail(PHB_ERR_STATE, "score_nni: set_tree first");
+    // Round-1 implementation: each neighbour is re-scheduled and scored from scratch (what the
+    // reference's caller loop does); path-only rescoring is the f2 follow-up.
+    TreeSched base = ctx->tree;
+    int rc = PHB_OK;
+    for (int m = 0; m < n_moves && rc == PHB_OK; ++m) {
+        int v = node_id[m];
+        totals[m] = NAN;
+        if (v < 0 || v >= base.n || v == base.root || base.child_off[v + 1] - base.child_off[v] < 2) continue;
+        // NNI::nni, src/tree.rs:1213-1242 on dense child lists
+        std::vector<std::vector<int>> ch(base.n);
+        for (int u = 0; u < base.n; ++u)
+            ch[u].assign(base.children.begin() + base.child_off[u], base.children.begin() + base.child_off[u + 1]);
+        int p = base.parent[v];
+        int c1 = ch[v][left_ch[m] ? 1 : 0];
+        int sib = -1;
+        for (int x : ch[p])
+            if (x != v) {
+                sib = x;
+                break;
+            }
+        if (sib < 0) continue;
+        ch[v].erase(std::find(ch[v].begin(), ch[v].end(), c1));
+        ch[p].erase(std::find(ch[p].begin(), ch[p].end(), sib));
+        ch[p].push_back(c1);
+        ch[v].push_back(sib);
+        TreeSched &T = ctx->tree;
+        T.children.clear();
+        for (int u = 0; u < base.n; ++u) {
+            T.child_off[u] = (int)T.children.size();
+            T.children.insert(T.children.end(), ch[u].begin(), ch[u].end());
+        }
+        T.child_off[base.n] = (int)T.children.size();
+        for (Device &d : ctx->devs) {
+            cudaSetDevice(d.ordinal);
+            cudaStreamSynchronize(d.stream);
+        }
+        rc = T.build(ctx->err);
+        if (rc) break;
+        ctx->tree_uploaded = false;
+        rc = evaluate(ctx, false, false, &totals[m]);
+    }
+    for (Device &d : ctx->devs) {
+        cudaSetDevice(d.ordinal);
+        cudaStreamSynchronize(d.stream);
+    }
+    ctx->tree = base;
+    ctx->tree_uploaded = false;
+    return rc;
+}
+
+int32_t phb_simulate_alignment(phb_ctx *ctx, int64_t n_patterns, int64_t global_offset, uint64_t seed)
+{
+    if (!ctx || n_patterns < 0) return PHB_ERR_INVALID_ARGUMENT;
+    if (!ctx->have_model || !ctx->tree.valid) return ctx->fail(PHB_ERR_STATE, "simulate: set_model and set_tree first");
+    TreeSched &T = ctx->tree;
+    const int n_leaves = (int)T.leaf_nodes.size();
+    // rows = leaves in ascending dense id
+    for (int v = 0; v < T.n; ++v) T.leaf_row[v] = -1;
+    for (int i = 0; i < n_leaves; ++i) T.leaf_row[T.leaf_nodes[i]] = i;
+    for (Device &d : ctx->devs) {
+        cudaSetDevice(d.ordinal);
+        cudaStreamSynchronize(d.stream);
+    }
+    int rc = T.build(ctx->err);
+    if (rc) return rc;
+    ctx->have_aln = false;
+    rc = shard_and_alloc(ctx, n_leaves, n_patterns);
+    if (rc) return rc;
+    rc = upload_tree(ctx);
+    if (rc) return rc;
+    ctx->row_invalid_host.assign(std::max(n_leaves, 1), 0);
+    // pre-order (left-to-right) for the walk
+    std::vector<int> pre;
+    pre.reserve(T.n);
+    {
+        std::vector<int> st(1, T.root);
+        while (!st.empty()) {
+            int v = st.back();
+            st.pop_back();
+            pre.push_back(v);
+            for (int k = T.child_off[v + 1] - 1; k >= T.child_off[v]; --k) st.push_back(T.children[k]);
+        }
+    }
+    const ModelDev &M = ctx->model_lit;
+    for (Device &d : ctx->devs) {
+        CU(cudaSetDevice(d.ordinal));
+        CU(d.Pmat.ensure(sizeof(double) * 16 * (size_t)T.n * M.n_cat));
+        CU(d.sim_pre.ensure(sizeof(int) * T.n));
+        CU(d.sim_parent.ensure(sizeof(int) * T.n));
+        CU(d.sim_depth.ensure(sizeof(int) * T.n));
+        CU(d.sim_leafrow.ensure(sizeof(int) * T.n));
+        CU(d.sim_stack.ensure((size_t)(T.max_depth + 1) * (size_t)d.P_pad));
+        CU(cudaMemcpyAsync(d.sim_pre.p, pre.data(), sizeof(int) * T.n, cudaMemcpyHostToDevice, d.stream));
+        CU(cudaMemcpyAsync(d.sim_parent.p, T.parent.data(), sizeof(int) * T.n, cudaMemcpyHostToDevice, d.stream));
+        CU(cudaMemcpyAsync(d.sim_depth.p, T.depth.data(), sizeof(int) * T.n, cudaMemcpyHostToDevice, d.stream));
+        CU(cudaMemcpyAsync(d.sim_leafrow.p, T.leaf_row.data(), sizeof(int) * T.n, cudaMemcpyHostToDevice, d.stream));
+        {
+            int nthreads = T.n * M.n_cat;
+            PHB_LAUNCH(transition_kernel, dim3((nthreads + 127) / 128), dim3(128), d.stream, d.blen.as<double>(), T.n, M,
+                       d.Pmat.as<double>());
+            CHECK_LAUNCH();
+        }
+        if (d.P > 0) {
+            PHB_LAUNCH(simulate_kernel, dim3((unsigned)((d.P + 127) / 128)), dim3(128), d.stream, d.sim_pre.as<int32_t>(),
+                       d.sim_parent.as<int32_t>(), d.sim_depth.as<int32_t>(), d.sim_leafrow.as<int32_t>(), T.n, T.root, M,
+                       d.Pmat.as<double>(), d.sim_stack.as<uint8_t>(), d.tips.as<uint8_t>(), d.P_pad, d.P,
+                       global_offset + d.p_begin, seed);
+            CHECK_LAUNCH();
+        }
+        for (int r0 = 0; r0 < n_leaves && d.P_pad > d.P; r0 += 32768) {
+            dim3 grid((unsigned)((d.P_pad - d.P + 255) / 256), (unsigned)std::min(32768, n_leaves - r0));
+            PHB_LAUNCH(fill_pad_kernel, grid, dim3(256), d.stream, d.tips.as<uint8_t>(), r0, d.P, d.P_pad);
+            CHECK_LAUNCH();
+        }
+        PHB_LAUNCH(mult_to_double_kernel, dim3((unsigned)std::min<int64_t>((d.P_pad + 255) / 256, 4096)), dim3(256),
+                   d.stream, (const uint64_t *)nullptr, d.P, d.P_pad, d.mult.as<double>());
+        CHECK_LAUNCH();
+        CU(cudaStreamSynchronize(d.stream)); // `pre` is a local
+        d.sim_stack.release();
+    }
+    ctx->have_aln = true;
+    return PHB_OK;
+}
+
+int32_t phb_get_alignment(phb_ctx *ctx, uint8_t *bytes, int32_t layout, int64_t first_pattern, int64_t n_patterns)
+{
+    if (!ctx || !bytes || first_pattern < 0 || n_patterns < 0) return PHB_ERR_INVALID_ARGUMENT;
+    if (!ctx->have_aln) return ctx->fail(PHB_ERR_STATE, "get_alignment: no alignment set");
+    if (first_pattern + n_patterns > ctx->n_patterns || (layout != 0 && layout != 1))
+        return ctx->fail(PHB_ERR_INVALID_ARGUMENT, "get_alignment: range or layout out of bounds");
+    const int n_rows = ctx->n_rows;
+    for (Device &d : ctx->devs) {
+        int64_t lo = std::max(first_pattern, d.p_begin), hi = std::min(first_pattern + n_patterns, d.p_begin + d.P);
+        if (hi <= lo || n_rows == 0) continue;
+        int64_t cnt = hi - lo;
+        CU(cudaSetDevice(d.ordinal));
+        CU(d.staging.ensure((size_t)cnt * n_rows));
+        for (int r0 = 0; r0 < n_rows; r0 += 32768) {
+            dim3 grid((unsigned)std::min<int64_t>((cnt + 255) / 256, 4096), (unsigned)std::min(32768, n_rows - r0));
+            PHB_LAUNCH(unpack_kernel, grid, dim3(256), d.stream, d.tips.as<uint8_t>(), n_rows, r0, d.P_pad,
+                       lo - d.p_begin, cnt, (int)layout, d.staging.as<uint8_t>());
+            CHECK_LAUNCH();
+        }
+        if (layout == PHB_LAYOUT_PATTERN_MAJOR)
+            CU(cudaMemcpyAsync(bytes + (size_t)(lo - first_pattern) * n_rows, d.staging.p, (size_t)cnt * n_rows,
+                               cudaMemcpyDeviceToHost, d.stream));
+        else
+            CU(cudaMemcpy2DAsync(bytes + (lo - first_pattern), (size_t)n_patterns, d.staging.p, (size_t)cnt, (size_t)cnt,
+                                 (size_t)n_rows, cudaMemcpyDeviceToHost, d.stream));
+        CU(cudaStreamSynchronize(d.stream));
+    }
+    return PHB_OK;
+}
+
+int32_t phb_get_stats(phb_ctx *ctx, phb_stats *out)
+{
+    if (!ctx || !out) return PHB_ERR_INVALID_ARGUMENT;
+    ctx->stats.kernel_launches = ctx->launches;
+    *out = ctx->stats;
+    return PHB_OK;
+}
+
+int32_t phb_measure_fp64_tflops(phb_ctx *ctx, double *tflops)
+{
+    if (!ctx || !tflops) return PHB_ERR_INVALID_ARGUMENT;
+    Device &d = ctx->devs[0];
+    CU(cudaSetDevice(d.ordinal));
+    const int blocks = 148 * 8, threads = 256, iters = 4096;
+    CU(d.scratch.ensure(sizeof(double) * blocks * threads));
+    cudaEvent_t a, b;
+    CU(cudaEventCreate(&a));
+    CU(cudaEventCreate(&b));
+    for (int rep = 0; rep < 2; ++rep) {
+        CU(cudaEventRecord(a, d.stream));
+        PHB_LAUNCH(fp64_fma_kernel, dim3(blocks), dim3(threads), d.stream, d.scratch.as<double>(), iters);
+        CHECK_LAUNCH();
+        CU(cudaEventRecord(b, d.stream));
+        CU(cudaStreamSynchronize(d.stream));
+    }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, a, b);
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    *tflops = 2.0 * 8.0 * (double)iters * blocks * threads / ((double)ms * 1e-3) / 1e12;
+    return PHB_OK;
+}
+
+} // extern "C"
