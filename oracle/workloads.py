@@ -1,0 +1,131 @@
+"""CPU ORACLE — seeded synthetic inputs for the parity tests (test infrastructure, NOT product code).
+
+Trees come from the restated Yule simulator (oracle/refhost.py: src/tree.rs:505-553) with i.i.d.
+Exp(mean 0.1) branch lengths clamped to [1e-4, 2.0] and rounded to f32 (the reference stores f32,
+src/tree.rs:45); alignments are simulated down the tree under the model with numpy.  SURVEY.md §8d.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import refhost
+
+MODELS = ("jc69", "hky_g4", "gtr", "gtr_g4", "gtr_i_g4", "gtr_i")
+PI = (0.30, 0.20, 0.20, 0.30)
+GTR_RATES = (1.0, 2.5, 1.0, 1.0, 2.5, 1.0)
+AMBIG = b"RYSWKMBDHVN-U"
+
+
+def make_model(name):
+    from . import RefModel
+
+    if name == "jc69":
+        return RefModel.jukes_cantor()
+    if name == "hky_g4":
+        return RefModel.hky85([0.25] * 4, 2.0).with_gamma(0.5, 4)
+    if name == "gtr":
+        return RefModel.gtr(PI, GTR_RATES)
+    if name == "gtr_g4":
+        return RefModel.gtr(PI, GTR_RATES).with_gamma(0.5, 4)
+    if name == "gtr_i_g4":
+        return RefModel.gtr(PI, GTR_RATES).with_gamma(0.5, 4).with_invariant(0.2)
+    if name == "gtr_i":
+        return RefModel.gtr(PI, GTR_RATES).with_invariant(0.3)
+    raise ValueError(name)
+
+
+def assign_branch_lengths(tree, rng, mean=0.1):
+    for nid in tree.get_node_ids():
+        if nid != tree.root:
+            t = min(max(rng.exponential(mean), 1e-4), 2.0)
+            tree.set_edge_weight(nid, np.float32(t))
+
+
+def simulate_patterns(ft, model, n_sites, rng):
+    """[n_sites][rows] ASCII bytes for the leaves of the flattened tree (rows = leaf_row order)."""
+    n = int(ft["n_nodes"])
+    rates, weights = model.rates, model.weights
+    cat = rng.choice(len(rates), size=n_sites, p=weights / weights.sum())
+    state = np.zeros((n, n_sites), np.int8)
+    pi = model.pi
+    n_rows = int(ft["leaf_row"].max()) + 1
+    out = np.full((n_sites, n_rows), ord("-"), np.uint8)
+    letters = np.frombuffer(b"ACGT", np.uint8)
+    for v in ft["preorder"]:
+        if v == ft["root"]:
+            state[v] = rng.choice(4, size=n_sites, p=pi / pi.sum())
+        else:
+            par = state[ft["parent"][v]]
+            u = rng.random(n_sites)
+            s = np.zeros(n_sites, np.int8)
+            for c in range(len(rates)):
+                sel = cat == c
+                if not sel.any():
+                    continue
+                P = model.transition(rates[c] * ft["blen"][v])
+                cum = np.cumsum(np.clip(P, 0, None), axis=1)
+                cum /= cum[:, -1:]
+                s[sel] = (u[sel, None] > cum[par[sel]]).sum(axis=1).clip(0, 3)
+            state[v] = s
+        r = ft["leaf_row"][v]
+        if r >= 0:
+            out[:, r] = letters[state[v]]
+    return out
+
+
+@dataclass
+class Case:
+    tree: object
+    ft: dict
+    model: object
+    model_name: str
+    patterns: np.ndarray  # [P][rows] ASCII
+    mult: np.ndarray      # [P] uint64
+    leaf_order: list
+
+
+def make_case(n_taxa, n_sites, model="gtr_g4", seed=1, ambiguity=0.0, compress=False):
+    rng = np.random.default_rng(seed)
+    tree = refhost.yule(n_taxa, rng)
+    assign_branch_lengths(tree, rng)
+    leaf_order = [tree.nodes[i].taxa for i in tree.get_node_ids() if tree.nodes[i].taxa is not None]
+    ft = flatten_fast(tree, leaf_order)
+    m = make_model(model)
+    pats = simulate_patterns(ft, m, n_sites, rng)
+    if ambiguity > 0:
+        mask = rng.random(pats.shape) < ambiguity
+        codes = np.frombuffer(AMBIG, np.uint8)
+        pats[mask] = codes[rng.integers(len(codes), size=int(mask.sum()))]
+    if compress:
+        uniq, inv, counts = np.unique(pats, axis=0, return_inverse=True, return_counts=True)
+        first = np.full(len(uniq), len(pats), np.int64)
+        np.minimum.at(first, inv.ravel(), np.arange(len(pats)))
+        order = np.argsort(first, kind="stable")  # first-appearance order (src/alignment.rs:104-120)
+        pats, mult = uniq[order], counts[order].astype(np.uint64)
+    else:
+        mult = np.ones(len(pats), np.uint64)
+    return Case(tree, ft, m, model, np.ascontiguousarray(pats), mult, leaf_order)
+
+
+def flatten_fast(tree, leaf_order):
+    """refhost.flatten with a dict for the name lookup (same result when labels are unique)."""
+    by_name = {}
+    for n in tree.nodes:
+        if n is not None and n.taxa is not None and n.taxa not in by_name:
+            by_name[n.taxa] = n.id
+    saved = tree.get_taxa_node_id
+    tree.get_taxa_node_id = lambda name: by_name.get(name)
+    try:
+        return refhost.flatten(tree, leaf_order)
+    finally:
+        tree.get_taxa_node_id = saved
+
+
+def load_into(ctx, case):
+    """Hand a Case to a phylo_rs_b200.capi.Context (the C-ABI product library)."""
+    m, ft = case.model, case.ft
+    ctx.set_alignment(case.patterns, multiplicity=case.mult)
+    ctx.set_model(m.eigenvalues, m.eigenvectors, m.pi, m.sqrt_pi, m.inv_sqrt_pi, m.rates, m.weights)
+    ctx.set_tree(ft["postorder"], ft["child_off"], ft["children"], ft["blen"], ft["leaf_row"], ft["root"])

@@ -1,0 +1,68 @@
+"""Shared parity checks: run a Case through a C-ABI library (real sm_100a build, or the emulation
+harness build for the CPU scheduler tests) and compare with the oracle.
+
+Tolerances are BASELINE.json's: total lnL 1e-9 relative, per-pattern lnL 1e-8 absolute, ASR argmax
+states bit-exact (sites whose top-2 mixed posteriors differ by < 1e-10 are audited, not hidden)."""
+import numpy as np
+
+import oracle
+from oracle import workloads
+from phylo_rs_b200 import capi
+
+REL_TOL = 1e-9
+ABS_TOL = 1e-8
+
+
+def run_lnl(lib, case, flags=0, devices=None, budget=None):
+    with capi.Context(devices=devices, flags=flags, library=lib) as ctx:
+        if budget:
+            ctx.set_clv_budget(budget)
+        workloads.load_into(ctx, case)
+        tot, per = ctx.log_likelihood(per_pattern=True)
+        st = ctx.stats()
+    return tot, per, st
+
+
+def run_asr(lib, case, want_post=False, devices=None, budget=None):
+    with capi.Context(devices=devices, library=lib) as ctx:
+        if budget:
+            ctx.set_clv_budget(budget)
+        workloads.load_into(ctx, case)
+        tot, states, post = ctx.marginal_asr(want_post)
+        per = ctx.per_pattern()
+    return tot, per, states, post
+
+
+def assert_lnl_close(tot, per, ref_tot, ref_per):
+    fin = np.isfinite(ref_per)
+    assert np.array_equal(np.isfinite(per), fin)
+    assert np.array_equal(per[~fin], ref_per[~fin]) or np.all(np.isneginf(per[~fin]) == np.isneginf(ref_per[~fin]))
+    if fin.any():
+        assert np.max(np.abs(per[fin] - ref_per[fin])) <= ABS_TOL
+    if np.isfinite(ref_tot):
+        assert abs(tot - ref_tot) <= REL_TOL * max(abs(ref_tot), 1e-300)
+    else:
+        assert tot == ref_tot or (np.isnan(tot) and np.isnan(ref_tot))
+
+
+def check_lnl(lib, case, **kw):
+    tot, per, st = run_lnl(lib, case, **kw)
+    ref_tot, ref_per = oracle.log_likelihood_flat(case.ft, case.model, case.patterns, case.mult, mode=0, n_threads=8)
+    assert_lnl_close(tot, per, ref_tot, ref_per)
+    return tot, per, st
+
+
+def check_asr(lib, case, want_post=False, **kw):
+    tot, per, states, post = run_asr(lib, case, want_post, **kw)
+    ref_tot, ref_per, ref_states, ref_post = oracle.marginal_asr_flat(
+        case.ft, case.model, case.patterns, case.mult, want_posteriors=True, n_threads=8)
+    assert_lnl_close(tot, per, ref_tot, ref_per)
+    diff = states != ref_states
+    if diff.any():
+        # bit-exact bar; a mismatch is tolerated ONLY at a numerical tie of the oracle's own top two
+        srt = np.sort(ref_post, axis=2)
+        gap = srt[..., 3] - srt[..., 2]
+        assert np.all(gap[diff] < 1e-10), f"{int(diff.sum())} ASR state mismatches away from ties"
+    if want_post:
+        assert np.max(np.abs(post - ref_post)) <= 1e-9
+    return int(diff.sum())

@@ -1,0 +1,37 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a real B200 (run with -m gpu on the GPU box)")
+
+
+@pytest.fixture(scope="session")
+def oracle_mod():
+    import oracle
+
+    oracle.build()
+    return oracle
+
+
+@pytest.fixture(scope="session")
+def emu_lib():
+    """The product .cu sources compiled with g++ against tests/emu's CUDA-runtime shim (test harness only)."""
+    import __graft_entry__ as g
+    from phylo_rs_b200 import capi
+
+    return capi.Library(g.build_emu())
+
+
+@pytest.fixture(scope="session")
+def gpu_lib():
+    """The real sm_100a library; the gpu tests call through its C ABI."""
+    from phylo_rs_b200 import capi
+
+    return capi.default_library()

@@ -1,0 +1,182 @@
+"""Parity of the real sm_100a library (through its C ABI) against the CPU oracle.  `-m gpu` only.
+
+Bars (BASELINE.json): total lnL within 1e-9 relative, per-pattern lnL within 1e-8 absolute (f64),
+marginal-ASR argmax states bit-exact."""
+import numpy as np
+import pytest
+
+import oracle
+from oracle import RefAlignment, RefModel, parse_newick, workloads
+from phylo_rs_b200 import capi
+
+import _cases
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("model", ["jc69", "gtr", "gtr_g4", "gtr_i_g4", "gtr_i", "hky_g4"])
+def test_lnl_models(gpu_lib, model):
+    case = workloads.make_case(32, 2000, model=model, seed=21, ambiguity=0.05)
+    _cases.check_lnl(gpu_lib, case)
+
+
+def test_config1_jc69_64x10k(gpu_lib):
+    """BASELINE.json configs[0]: JC69, 64-taxon Yule tree x 10k sites (compressed patterns + multiplicities)."""
+    case = workloads.make_case(64, 10_000, model="jc69", seed=0x5EED0001, compress=True)
+    _cases.check_lnl(gpu_lib, case)
+
+
+def test_gtr_g4_1000_taxa_sample(gpu_lib):
+    """configs[1] shape (1,000 taxa, GTR+G4) on a pattern sample the oracle finishes in seconds."""
+    case = workloads.make_case(1000, 1536, model="gtr_g4", seed=0x5EED0002)
+    _cases.check_lnl(gpu_lib, case)
+
+
+def test_gtr_i_g4_deep_tree_scaling(gpu_lib):
+    """2,500 taxa: per-site |lnL| ~ 1e4 and CLVs underflow without the exact power-of-two rescaling."""
+    case = workloads.make_case(2500, 384, model="gtr_i_g4", seed=0x5EED0003)
+    tot, per, _ = _cases.check_lnl(gpu_lib, case)
+    assert per.min() < -2000
+
+
+def test_literal_invariant_flag(gpu_lib):
+    case = workloads.make_case(40, 3000, model="gtr_i_g4", seed=23, ambiguity=0.1)
+    a = _cases.check_lnl(gpu_lib, case)[0]
+    b = _cases.check_lnl(gpu_lib, case, flags=capi.FLAG_LITERAL_INVARIANT)[0]
+    assert abs(a - b) <= 1e-10 * abs(a)
+
+
+def test_all_17_codes(gpu_lib):
+    case = workloads.make_case(24, 4000, model="gtr_g4", seed=24, ambiguity=0.5)
+    assert set(np.unique(case.patterns)) >= set(b"ACGTURYSWKMBDHVN-")
+    _cases.check_lnl(gpu_lib, case)
+    assert _cases.check_asr(gpu_lib, case) == 0
+
+
+def test_tiling_and_sharding_invariance(gpu_lib):
+    case = workloads.make_case(50, 20_000, model="gtr_g4", seed=25)
+    full = _cases.check_lnl(gpu_lib, case)
+    tiled = _cases.check_lnl(gpu_lib, case, budget=49 * 4 * 4 * 8 * 4096)
+    assert tiled[2]["n_tiles"] >= 4
+    assert np.array_equal(full[1], tiled[1])
+    split = _cases.check_lnl(gpu_lib, case, devices=[0, 0, 0])  # three virtual ranks on one device
+    assert np.array_equal(full[1], split[1])
+
+
+@pytest.mark.parametrize("model", ["jc69", "gtr_g4", "gtr_i_g4"])
+def test_asr_models(gpu_lib, model):
+    case = workloads.make_case(40, 1500, model=model, seed=26, ambiguity=0.05)
+    assert _cases.check_asr(gpu_lib, case, want_post=True) == 0
+
+
+def test_asr_500_taxa_sample(gpu_lib):
+    case = workloads.make_case(500, 512, model="gtr_g4", seed=0x5EED0004)
+    assert _cases.check_asr(gpu_lib, case) == 0
+
+
+def test_asr_tiled(gpu_lib):
+    case = workloads.make_case(30, 6000, model="gtr_g4", seed=27)
+    assert _cases.check_asr(gpu_lib, case, budget=29 * 4 * 4 * 8 * 1024) == 0
+
+
+def test_polytomy_unifurcation_internal_row(gpu_lib):
+    tree = parse_newick("((A:0.1,B:0.2,C:0.3)X:0.05,(D:0.1)Y:0.2,E:0.3)R;")
+    aln = RefAlignment.from_fasta_bytes(b">A\nACGTN\n>B\nACGAR\n>C\nAGGT-\n>D\nTCGTA\n>E\nACCTA\n>X\n?????\n")
+    m = RefModel.gtr([.3, .2, .2, .3], [1, 2.5, 1, 1, 2.5, 1]).with_gamma(0.5, 4)
+    pats, _s2p, mult, lo = aln.compress_columns()
+    case = workloads.Case(tree, oracle.flatten(tree, lo), m, "gtr_g4", pats, mult, lo)
+    _cases.check_lnl(gpu_lib, case)
+    assert _cases.check_asr(gpu_lib, case, want_post=True) == 0
+
+
+def test_reference_fixture_kats(gpu_lib):
+    """SURVEY.md §8c known answers through the CUDA path."""
+    tree = parse_newick("((A:0.601,B:0.301)C:0.100,D:0.200)E:0.001;")
+    aln = RefAlignment.from_fasta_bytes(
+        b">A\n" + b"ACGT" * 4 + b"\n>B\n" + b"AGGT" * 4 + b"\n>C\n" + b"ACGT" * 4 + b"\n>D\n" + b"T" * 16 + b"\n")
+    pats, _s2p, mult, lo = aln.compress_columns()
+    ft = oracle.flatten(tree, lo)
+    g4 = RefModel.gtr([.3, .2, .2, .3], [1, 2.5, 1, 1, 2.5, 1]).with_gamma(0.5, 4)
+    for m, want in ((RefModel.jukes_cantor(), -66.3080496020529), (RefModel.hky85([.3, .2, .2, .3], 2.5), -68.11049472687087),
+                    (g4, -69.66427000171137), (g4.with_invariant(0.2), -71.7982617885503)):
+        case = workloads.Case(tree, ft, m, "", pats, mult, lo)
+        tot, _per, _ = _cases.check_lnl(gpu_lib, case)
+        assert tot == pytest.approx(want, abs=1e-10)
+
+
+def test_zero_branch_conflict_and_all_gap(gpu_lib):
+    tree = parse_newick("((A:0,B:0)C:0,D:0)E:0;")
+    aln = RefAlignment.from_fasta_bytes(b">A\nAC-\n>B\nCC-\n>D\nGC-\n")
+    pats, _s2p, mult, lo = aln.compress_columns()
+    case = workloads.Case(tree, oracle.flatten(tree, lo), RefModel.jukes_cantor(), "jc69", pats, mult, lo)
+    tot, per, _ = _cases.check_lnl(gpu_lib, case)
+    assert tot == -np.inf and abs(per[2]) < 1e-13
+    assert _cases.check_asr(gpu_lib, case) == 0
+
+
+def test_errors_and_empty(gpu_lib):
+    case = workloads.make_case(6, 20, model="jc69", seed=2)
+    with capi.Context(library=gpu_lib) as ctx:
+        with pytest.raises(capi.PhbError):
+            ctx.log_likelihood()
+        workloads.load_into(ctx, case)
+        ft = case.ft
+        bad = case.patterns.copy()
+        leaf = int(np.where(ft["leaf_row"] >= 0)[0][0])
+        bad[3, ft["leaf_row"][leaf]] = ord("X")
+        ctx.set_alignment(bad)
+        with pytest.raises(capi.PhbError) as e:
+            ctx.log_likelihood()
+        assert e.value.variant == "AlphabetMismatch"
+        ctx.set_alignment(case.patterns[:0])
+        assert ctx.log_likelihood() == 0.0
+
+
+def test_score_nni(gpu_lib):
+    case = workloads.make_case(16, 500, model="gtr_g4", seed=28)
+    ft = case.ft
+    moves = [(v, lc) for v in range(ft["n_nodes"]) for lc in (0, 1)]
+    with capi.Context(library=gpu_lib) as ctx:
+        workloads.load_into(ctx, case)
+        got = ctx.score_nni([m[0] for m in moves], [m[1] for m in moves])
+    for (v, lc), val in zip(moves, got):
+        t = case.tree.clone()
+        if t.nni(int(ft["ids"][v]), bool(lc)):
+            assert np.isnan(val)
+            continue
+        ref, _ = oracle.log_likelihood_flat(workloads.flatten_fast(t, case.leaf_order), case.model, case.patterns, case.mult)
+        assert abs(val - ref) <= 1e-9 * abs(ref)
+
+
+def test_full_size_properties_config2(gpu_lib):
+    """configs[1] at FULL size (1,000 taxa x 100k sites, GTR+G4) through size-independent properties:
+    the device-simulated alignment is scored whole, in 3 virtual ranks and under a forced 5-way tiling —
+    per-pattern values must be identical; a 1,024-pattern sample is checked against the oracle; and
+    duplicating every pattern (multiplicity 2) must double the total (linearity in the weights)."""
+    case = workloads.make_case(1000, 8, model="gtr_g4", seed=0x5EED0002)
+    P = 100_000
+    with capi.Context(library=gpu_lib) as ctx:
+        workloads.load_into(ctx, case)
+        ctx.simulate_alignment(P, seed=0xA11C)
+        tot, per = ctx.log_likelihood(per_pattern=True)
+        pats = ctx.get_alignment(0, 1024)
+        ctx.set_clv_budget(999 * 4 * 4 * 8 * 20480)
+        tot_t, per_t = ctx.log_likelihood(per_pattern=True)
+        assert ctx.stats()["n_tiles"] >= 5
+        whole = ctx.get_alignment()
+    assert np.array_equal(per, per_t) and tot == tot_t
+    ft = dict(case.ft)
+    leaves = np.where(ft["child_off"][1:] == ft["child_off"][:-1])[0]
+    lr = np.full(ft["n_nodes"], -1, np.int32)
+    lr[leaves] = np.arange(len(leaves))
+    ft["leaf_row"] = lr
+    ref, ref_per = oracle.log_likelihood_flat(ft, case.model, pats, n_threads=8)
+    assert np.max(np.abs(per[:1024] - ref_per)) <= 1e-8
+    with capi.Context(devices=[0, 0, 0], library=gpu_lib) as ctx:
+        ctx.set_alignment(whole, multiplicity=np.full(P, 2, np.uint64))
+        m = case.model
+        ctx.set_model(m.eigenvalues, m.eigenvectors, m.pi, m.sqrt_pi, m.inv_sqrt_pi, m.rates, m.weights)
+        ctx.set_tree(ft["postorder"], ft["child_off"], ft["children"], ft["blen"], lr, ft["root"])
+        tot2, per2 = ctx.log_likelihood(per_pattern=True)
+    assert np.array_equal(per2, per)
+    assert abs(tot2 - 2 * tot) <= 1e-12 * abs(tot2)

@@ -1,0 +1,167 @@
+"""Host scheduler / tiling / sharding / ABI logic of the product sources, exercised on the CPU through
+the emulation-harness build (tests/emu: the same .cu files compiled by g++ against a CUDA-runtime shim).
+Numerical parity CLAIMS are made by tests/test_gpu_parity.py on the real sm_100a library; these tests
+exist so that indexing and scheduling bugs are found before GPU time is spent."""
+import numpy as np
+import pytest
+
+import oracle
+from oracle import RefAlignment, RefModel, parse_newick, workloads
+from phylo_rs_b200 import capi
+
+import _cases
+
+
+@pytest.mark.parametrize("model", ["jc69", "gtr", "gtr_g4", "gtr_i_g4", "gtr_i"])
+def test_lnl_small_models(emu_lib, model):
+    case = workloads.make_case(12, 300, model=model, seed=11, ambiguity=0.1)
+    _cases.check_lnl(emu_lib, case)
+
+
+def test_lnl_literal_invariant_flag(emu_lib):
+    case = workloads.make_case(10, 200, model="gtr_i_g4", seed=3, ambiguity=0.1)
+    a = _cases.check_lnl(emu_lib, case)[0]
+    b = _cases.check_lnl(emu_lib, case, flags=capi.FLAG_LITERAL_INVARIANT)[0]
+    assert abs(a - b) <= 1e-10 * abs(a)
+
+
+def test_tiling_is_result_invariant(emu_lib):
+    case = workloads.make_case(9, 1500, model="gtr_g4", seed=4)
+    full = _cases.check_lnl(emu_lib, case)
+    per_site = 8 * 4 * 4 * 8  # slots x cats x states x f64
+    tiled = _cases.check_lnl(emu_lib, case, budget=per_site * 512)
+    assert tiled[2]["n_tiles"] >= 3
+    assert np.array_equal(full[1], tiled[1])
+
+
+def test_device_sharding_is_result_invariant(emu_lib):
+    case = workloads.make_case(9, 1100, model="gtr_g4", seed=5)
+    one = _cases.check_lnl(emu_lib, case)
+    for devs in ([0, 1], [0, 1, 2, 3]):
+        many = _cases.check_lnl(emu_lib, case, devices=devs)
+        assert np.array_equal(one[1], many[1])
+        assert abs(one[0] - many[0]) <= 1e-12 * abs(one[0])
+
+
+def test_asr_small(emu_lib):
+    for model in ("jc69", "gtr_g4", "gtr_i_g4"):
+        case = workloads.make_case(10, 200, model=model, seed=6, ambiguity=0.1)
+        assert _cases.check_asr(emu_lib, case, want_post=True) == 0
+
+
+def test_asr_sharded_and_tiled(emu_lib):
+    case = workloads.make_case(8, 1300, model="gtr_g4", seed=8)
+    assert _cases.check_asr(emu_lib, case, devices=[0, 1], budget=7 * 4 * 4 * 8 * 512) == 0
+
+
+def test_polytomy_and_unifurcation(emu_lib):
+    tree = parse_newick("((A:0.1,B:0.2,C:0.3)X:0.05,(D:0.1)Y:0.2,E:0.3)R;")
+    aln = RefAlignment.from_fasta_bytes(b">A\nACGTN\n>B\nACGAR\n>C\nAGGT-\n>D\nTCGTA\n>E\nACCTA\n")
+    m = RefModel.gtr([.3, .2, .2, .3], [1, 2.5, 1, 1, 2.5, 1]).with_gamma(0.5, 4)
+    pats, _s2p, mult, lo = aln.compress_columns()
+    case = workloads.Case(tree, oracle.flatten(tree, lo), m, "gtr_g4", pats, mult, lo)
+    _cases.check_lnl(emu_lib, case)
+    assert _cases.check_asr(emu_lib, case, want_post=True) == 0
+
+
+def test_reference_fixture_and_internal_row(emu_lib):
+    # integration_test.rs:14-17 + :663 — row C names an internal node: ignored by pruning, never validated
+    tree = parse_newick("((A:0.601,B:0.301)C:0.100,D:0.200)E:0.001;")
+    aln = RefAlignment.from_fasta_bytes(b">A\nACGTACGT\n>B\nAGGTAGGT\n>C\nAC?TAC!T\n>D\nTTTTTTTT\n")
+    pats, _s2p, mult, lo = aln.compress_columns()
+    m = RefModel.jukes_cantor()
+    case = workloads.Case(tree, oracle.flatten(tree, lo), m, "jc69", pats, mult, lo)
+    _cases.check_lnl(emu_lib, case)
+
+
+def test_errors(emu_lib):
+    case = workloads.make_case(6, 20, model="jc69", seed=2)
+    with capi.Context(library=emu_lib) as ctx:
+        with pytest.raises(capi.PhbError) as e:
+            ctx.log_likelihood()
+        assert e.value.variant == "State"
+        workloads.load_into(ctx, case)
+        ft = case.ft
+        lr = ft["leaf_row"].copy()
+        leaf = int(np.where(lr >= 0)[0][0])
+        lr[leaf] = -1
+        ctx.set_tree(ft["postorder"], ft["child_off"], ft["children"], ft["blen"], lr, ft["root"])
+        with pytest.raises(capi.PhbError) as e:
+            ctx.log_likelihood()
+        assert e.value.variant == "InvalidAlignment"
+        bad = case.patterns.copy()
+        bad[3, ft["leaf_row"][leaf]] = ord("X")
+        ctx.set_alignment(bad)
+        ctx.set_tree(ft["postorder"], ft["child_off"], ft["children"], ft["blen"], ft["leaf_row"], ft["root"])
+        with pytest.raises(capi.PhbError) as e:
+            ctx.log_likelihood()
+        assert e.value.variant == "AlphabetMismatch"
+        with pytest.raises(capi.PhbError) as e:  # node before its child
+            ctx.set_tree(ft["postorder"][::-1], ft["child_off"], ft["children"], ft["blen"], ft["leaf_row"], ft["root"])
+        assert e.value.variant == "NumericalInstability"
+
+
+def test_empty_alignment_is_zero(emu_lib):
+    case = workloads.make_case(6, 5, model="jc69", seed=2)
+    case.patterns = case.patterns[:0]
+    case.mult = case.mult[:0]
+    with capi.Context(library=emu_lib) as ctx:
+        workloads.load_into(ctx, case)
+        assert ctx.log_likelihood() == 0.0
+
+
+def test_zero_branch_conflict_and_all_gap(emu_lib):
+    tree = parse_newick("((A:0,B:0)C:0,D:0)E:0;")
+    aln = RefAlignment.from_fasta_bytes(b">A\nAC-\n>B\nCC-\n>D\nGC-\n")
+    pats, _s2p, mult, lo = aln.compress_columns()
+    case = workloads.Case(tree, oracle.flatten(tree, lo), RefModel.jukes_cantor(), "jc69", pats, mult, lo)
+    tot, per, _ = _cases.check_lnl(emu_lib, case)
+    assert tot == -np.inf and np.isfinite(per[1]) and abs(per[2]) < 1e-13
+    assert _cases.check_asr(emu_lib, case) == 0
+
+
+def test_multiplicity_weights(emu_lib):
+    case = workloads.make_case(8, 400, model="gtr_g4", seed=9, compress=True)
+    assert case.mult.max() > 1
+    _cases.check_lnl(emu_lib, case)
+
+
+def test_score_nni_matches_rebuilt_trees(emu_lib):
+    case = workloads.make_case(10, 150, model="gtr_g4", seed=12)
+    ft = case.ft
+    moves = [(v, lc) for v in range(ft["n_nodes"]) for lc in (0, 1)]
+    with capi.Context(library=emu_lib) as ctx:
+        workloads.load_into(ctx, case)
+        base = ctx.log_likelihood()
+        got = ctx.score_nni([m[0] for m in moves], [m[1] for m in moves])
+        assert ctx.log_likelihood() == base  # the base tree is restored
+    ids = ft["ids"]
+    for (v, lc), val in zip(moves, got):
+        t = case.tree.clone()
+        err = t.nni(int(ids[v]), bool(lc))
+        if err:
+            assert np.isnan(val)
+            continue
+        ft2 = workloads.flatten_fast(t, case.leaf_order)
+        ref, _ = oracle.log_likelihood_flat(ft2, case.model, case.patterns, case.mult)
+        assert abs(val - ref) <= 1e-9 * abs(ref)
+
+
+def test_simulated_alignment_roundtrip(emu_lib):
+    case = workloads.make_case(7, 10, model="gtr_g4", seed=13)
+    with capi.Context(library=emu_lib) as ctx:
+        workloads.load_into(ctx, case)
+        ctx.simulate_alignment(700, seed=99)
+        pats = ctx.get_alignment()
+        assert pats.shape == (700, 7) and set(np.unique(pats)) <= set(b"ACGT")
+        tot, per = ctx.log_likelihood(per_pattern=True)
+        # shards of one logical alignment generated independently agree with the whole
+        ctx.simulate_alignment(300, global_offset=400, seed=99)
+        assert np.array_equal(ctx.get_alignment(), pats[400:])
+    ft = dict(case.ft)
+    leaves = np.where(ft["child_off"][1:] == ft["child_off"][:-1])[0]
+    lr = np.full(ft["n_nodes"], -1, np.int32)
+    lr[leaves] = np.arange(len(leaves))
+    ft["leaf_row"] = lr
+    ref, ref_per = oracle.log_likelihood_flat(ft, case.model, pats)
+    _cases.assert_lnl_close(tot, per, ref, ref_per)
