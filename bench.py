@@ -1,0 +1,332 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark: CLV site-node updates/s for GTR+I+G4 log-likelihood.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[2], the configuration the metric is quoted on): GTR+I+G4
+log-likelihood of a 10,000-taxon Yule tree x 1,000,000 site patterns (synthetic, simulated under the
+model on the device).  The pattern axis is sharded contiguously over the N ranks (strong scaling: the
+total stays 1M patterns); every rank holds the full tree and model; only the scalar partial
+log-likelihood crosses GPUs (one NCCL all-reduce per step).
+
+A "step" is one full evaluation through the C ABI (P(t) kernel, all CLV updates, root kernel, scalar
+back on the host).  `value` times K steps with the packed alignment resident in HBM; `e2e` times the
+same evaluation fed from HOST buffers (alignment bytes in pinned host memory, [pattern][row] as
+CompressedColumns.patterns) with the host->device copy, packing, tree/model upload and the result
+read-back inside the timed region.
+
+--impl reference: the reference's own algorithm (oracle port, reference-faithful mode: single thread,
+P(t) rebuilt per child, linear leaf search — `parallel`/rayon does not touch this path) timed on a
+bounded pattern sample of the same workload on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+N_TAXA = int(os.environ.get("PHB_BENCH_TAXA", 10_000))
+N_SITES = int(os.environ.get("PHB_BENCH_SITES", 1_000_000))
+TREE_SEED = 0x5EED0003
+ALN_SEED = TREE_SEED ^ 0xA11C
+METRIC = "CLV site-node updates/s (GTR+I+G4)"
+UNIT = "updates/s"
+WORKLOAD = f"GTR+I+G4 log-likelihood, {N_TAXA}-taxon Yule tree x {N_SITES} site patterns"
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.index)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def shard(P, world, rank):
+    per = (P + world - 1) // world
+    per += per & 1
+    lo = min(rank * per, P)
+    return lo, min(per, P - lo)
+
+
+# --------------------------------------------------------------------------------------------------
+# CPU legs (the only places that may execute oracle/)
+# --------------------------------------------------------------------------------------------------
+def cpu_sample(n_patterns, mode, threads, seed=0):
+    """Times the oracle on a bounded sample of the workload: the first `n_patterns` patterns of an
+    alignment simulated under the same tree and model.  Returns (updates/s, seconds)."""
+    import oracle
+    from oracle import workloads
+    from phylo_rs_b200 import synthetic
+
+    oracle.build()
+    ft = synthetic.yule_flat(N_TAXA, TREE_SEED)
+    ft["preorder"] = np.zeros(ft["n_nodes"], np.int32)
+    model = workloads.make_model("gtr_i_g4")
+    rng = np.random.default_rng(ALN_SEED + seed)
+    # pre-order for the simulator
+    pre, st = [], [ft["root"]]
+    co, ch = ft["child_off"], ft["children"]
+    while st:
+        v = st.pop()
+        pre.append(v)
+        st.extend(reversed(ch[co[v]:co[v + 1]].tolist()))
+    ft["preorder"] = np.asarray(pre, np.int32)
+    pats = workloads.simulate_patterns(ft, model, n_patterns, rng)
+    t0 = time.perf_counter()
+    tot, _ = oracle.log_likelihood_flat(ft, model, pats, mode=mode, n_threads=threads)
+    dt = time.perf_counter() - t0
+    assert np.isfinite(tot)
+    n_internal = int(np.sum(co[1:] != co[:-1]))
+    return n_internal * n_patterns / dt, dt
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    sample = int(os.environ.get("PHB_REF_SAMPLE", 32 if N_TAXA >= 5000 else 2048))
+    for i in range(args.warmup):
+        cpu_sample(max(sample // 8, 1), 1, 1, seed=i)
+    times, vals = [], []
+    for i in range(args.steps):
+        v, dt = cpu_sample(sample, 1, 1, seed=100 + i)
+        vals.append(v)
+        times.append(dt)
+    total_updates = sum(v * t for v, t in zip(vals, times))
+    value = total_updates / sum(times)
+    cores = os.cpu_count() or 1
+    opt_v, opt_dt = cpu_sample(sample * 64, 2, cores, seed=999)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * sum(times) / len(times), "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sample": f"{sample} patterns per step (patterns are independent; throughput per update is size-independent)"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port",
+                         "sample": f"oracle reference-faithful mode (likelihood.rs:83-143 loop nest, P(t) per child, linear leaf search), "
+                                   f"{sample} patterns x {args.steps} steps, 1 thread: the reference's `parallel` feature does not reach this path",
+                         "cpu_opt": {"value": opt_v, "unit": UNIT, "cores": cores,
+                                     "sample": f"oracle cpu_opt mode (P cached per edge x category, SoA, pthreads), {sample * 64} patterns, {opt_dt:.2f} s"}},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------------
+# GPU arm
+# --------------------------------------------------------------------------------------------------
+def run_gpu(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+
+    from phylo_rs_b200 import capi, synthetic
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    tree = synthetic.yule_flat(N_TAXA, TREE_SEED)
+    model = synthetic.gtr_model(alpha=0.5, k=4, p_inv=0.2)
+    n_internal = N_TAXA - 1
+    lo, cnt = shard(N_SITES, world, rank)
+    ctx = capi.Context(devices=[local_rank], flags=capi.FLAG_TIMING)
+    synthetic.load_into(ctx, tree, model)
+    ctx.simulate_alignment(cnt, global_offset=lo, seed=ALN_SEED)
+    red = torch.zeros(1, dtype=torch.float64, device="cuda")
+
+    def step():
+        v = ctx.log_likelihood()
+        if world > 1:
+            red[0] = v
+            dist.all_reduce(red)
+            return float(red.item())
+        return v
+
+    for _ in range(max(args.warmup, 3)):
+        lnl = step()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    launches0 = ctx.stats()["kernel_launches"]
+    ctx.timer_start()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        lnl = step()
+    dev_ms = ctx.timer_stop()
+    barrier()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    clocks = sampler.stop()
+    st = ctx.stats()
+    launches = st["kernel_launches"] - launches0
+    # ---- end to end from host buffers ------------------------------------------------------------
+    e2e_steps = max(1, min(args.steps, 3))
+    n_rows = tree["n_taxa"]
+    host = torch.empty((cnt, n_rows), dtype=torch.uint8, pin_memory=True)
+    chunk = max(1, (256 << 20) // n_rows)
+    for p0 in range(0, cnt, chunk):
+        c = min(chunk, cnt - p0)
+        host.numpy()[p0:p0 + c] = ctx.get_alignment(p0, c)
+
+    def e2e_step():
+        ctx.set_alignment_ptr(host.data_ptr(), n_rows, cnt)
+        synthetic.load_into(ctx, tree, model)
+        v = ctx.log_likelihood()
+        if world > 1:
+            red[0] = v
+            dist.all_reduce(red)
+            return float(red.item())
+        return v
+
+    lnl_e2e = e2e_step()
+    barrier()
+    t1 = time.perf_counter()
+    for _ in range(e2e_steps):
+        lnl_e2e = e2e_step()
+    barrier()
+    e2e_ms = (time.perf_counter() - t1) * 1e3 / e2e_steps
+    # ---- reduce over ranks ------------------------------------------------------------------------
+    tmax = torch.tensor([dev_ms, wall_ms, e2e_ms], dtype=torch.float64, device="cuda")
+    tsum = torch.tensor([float(launches)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+    dev_ms, wall_ms, e2e_ms = (float(x) for x in tmax.tolist())
+    launches = int(tsum.item())
+    if rank == 0:
+        peak, peak_src = peaks()
+        updates = n_internal * N_SITES
+        ms_step = dev_ms / args.steps
+        kern_ms = st["ms_clv"] / max(st["clv_launches"], 1)
+        bytes_launch = st["algorithmic_bytes"] / max(st["clv_launches"], 1)
+        achieved = bytes_launch / (kern_ms * 1e-3) / 1e9 if kern_ms > 0 else None
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                traffic = json.load(f).get("dram_bytes_per_launch")
+        except Exception:
+            pass
+        line = {
+            "metric": METRIC, "value": updates / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "model": "GTR+I+G4 (pi=.3,.2,.2,.3; rates 1,2.5,1,1,2.5,1; alpha=0.5, k=4; p_inv=0.2)",
+                       "patterns_per_gpu": cnt, "sharding": f"site patterns over {world} rank(s); scalar all-reduce",
+                       "l2": "inputs larger than L2 (tip codes + CLV tiles >> 126 MB)",
+                       "tiles_per_step": st["n_tiles"], "tile_patterns": st["tile_patterns"], "levels": st["n_levels"]},
+            "lnl": lnl, "lnl_e2e": lnl_e2e, "wall_ms_per_step": wall_ms / args.steps,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
+                         "kernel": "clv_update_level_kernel", "launches_per_step": st["clv_launches"],
+                         "avg_launch_ms": kern_ms, "algorithmic_bytes_per_launch": bytes_launch,
+                         "whole_step_frac": st["algorithmic_bytes"] / (ms_step * 1e-3) / 1e9 / peak},
+            "e2e": {"value": updates / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
+                    "h2d_bytes_per_step": int(cnt) * n_rows + 8 * 60 + 8 * 4 * tree["n_nodes"] + 4 * 4 * tree["n_nodes"],
+                    "d2h_bytes_per_step": 8 + 4 * n_rows, "steps": e2e_steps,
+                    "note": "per rank: pinned host [pattern][row] bytes -> H2D -> pack -> evaluate -> scalar back"},
+            "gpu_launches": launches,
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu:
+            sample = int(os.environ.get("PHB_REF_SAMPLE", 64 if N_TAXA >= 5000 else 4096))
+            v, dt = cpu_sample(sample, 1, 1)
+            cores = os.cpu_count() or 1
+            ov, odt = cpu_sample(sample * 64, 2, cores)
+            line["cpu_baseline"] = {
+                "value": v, "unit": UNIT, "cores": 1, "kind": "port",
+                "sample": f"oracle reference-faithful mode, first {sample} patterns of the same workload, {dt:.1f} s, 1 thread "
+                          "(the reference's rayon feature does not reach this path)",
+                "cpu_opt": {"value": ov, "unit": UNIT, "cores": cores, "sample": f"oracle cpu_opt mode, {sample * 64} patterns, {odt:.1f} s"}}
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if world == 1 and args.gpus > 1:
+        # launched without torchrun: re-exec under it
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29531"), os.path.abspath(__file__),
+               "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup)] + (["--no-cpu"] if args.no_cpu else [])
+        raise SystemExit(subprocess.call(cmd))
+    run_gpu(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

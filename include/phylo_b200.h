@@ -48,6 +48,9 @@ extern "C" {
 #define PHB_FLAG_LITERAL_INVARIANT (1ull << 0)
 /* Record CUDA events around every phase of an evaluation (see phb_get_stats). */
 #define PHB_FLAG_TIMING (1ull << 1)
+/* Log-likelihood through the level-batched kernels that keep every CLV in HBM (the marginal-ASR up
+ * pass always uses them) instead of the fused on-chip sweep. */
+#define PHB_FLAG_LEVEL_KERNELS (1ull << 2)
 
 /* ---- alignment layouts --------------------------------------------------------------------- */
 #define PHB_LAYOUT_PATTERN_MAJOR 0 /* bytes[pattern][row] — CompressedColumns.patterns, alignment.rs:129-138 */
@@ -159,6 +162,12 @@ typedef struct phb_stats {
     int32_t reserved;
 } phb_stats;
 int32_t phb_get_stats(phb_ctx *ctx, phb_stats *out);
+
+/* Device-side stopwatch for harnesses: phb_timer_start records a CUDA event on every device stream of
+ * the context, phb_timer_stop records a second one, waits for it, and returns the elapsed device time
+ * in ms (max over the context's devices).  Everything the context enqueued in between is covered. */
+int32_t phb_timer_start(phb_ctx *ctx);
+int32_t phb_timer_stop(phb_ctx *ctx, double *ms);
 
 /* FP64 FMA throughput microbenchmark on device 0 (TFLOP/s); confirms the path is HBM-bound. */
 int32_t phb_measure_fp64_tflops(phb_ctx *ctx, double *tflops);

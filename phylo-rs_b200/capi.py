@@ -24,6 +24,7 @@ STATUS_NAMES = {
 }
 FLAG_LITERAL_INVARIANT = 1 << 0
 FLAG_TIMING = 1 << 1
+FLAG_LEVEL_KERNELS = 1 << 2
 LAYOUT_PATTERN_MAJOR = 0
 LAYOUT_ROW_MAJOR = 1
 
@@ -32,6 +33,7 @@ EXPORTS = [
     "phb_ctx_create", "phb_ctx_destroy", "phb_set_clv_budget", "phb_set_alignment", "phb_set_model",
     "phb_set_tree", "phb_log_likelihood", "phb_marginal_asr", "phb_get_per_pattern", "phb_score_nni",
     "phb_simulate_alignment", "phb_get_alignment", "phb_get_stats", "phb_measure_fp64_tflops",
+    "phb_timer_start", "phb_timer_stop",
     "phb_last_error", "phb_version",
 ]
 
@@ -85,6 +87,8 @@ class Library:
         L.phb_get_alignment.argtypes = [vp, vp, C.c_int32, C.c_int64, C.c_int64]
         L.phb_get_stats.argtypes = [vp, C.POINTER(Stats)]
         L.phb_measure_fp64_tflops.argtypes = [vp, dp]
+        L.phb_timer_start.argtypes = [vp]
+        L.phb_timer_stop.argtypes = [vp, dp]
         L.phb_last_error.argtypes = [vp]
         L.phb_last_error.restype = C.c_char_p
         L.phb_version.argtypes = []
@@ -250,6 +254,14 @@ class Context:
         s = Stats()
         self._check(self.lib.L.phb_get_stats(self._h, C.byref(s)))
         return s.as_dict()
+
+    def timer_start(self):
+        self._check(self.lib.L.phb_timer_start(self._h))
+
+    def timer_stop(self):
+        v = C.c_double(0.0)
+        self._check(self.lib.L.phb_timer_stop(self._h, C.byref(v)))
+        return v.value
 
     def measure_fp64_tflops(self):
         v = C.c_double(0.0)

@@ -12,7 +12,12 @@
 #include "cuda_emu.h"
 #define PHB_LAUNCH(kernel, grid, block, stream, ...) \
     ::emu::launch((grid), (block), [&]() { kernel(__VA_ARGS__); })
+#define PHB_LAUNCH_SMEM(kernel, grid, block, smem, stream, ...) \
+    ::emu::launch((grid), (block), [&]() { kernel(__VA_ARGS__); }, (smem))
+#define PHB_DYN_SMEM(name) unsigned char *name = ::emu::dyn_smem
 #else
 #include <cuda_runtime.h>
 #define PHB_LAUNCH(kernel, grid, block, stream, ...) kernel<<<(grid), (block), 0, (stream)>>>(__VA_ARGS__)
+#define PHB_LAUNCH_SMEM(kernel, grid, block, smem, stream, ...) kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
+#define PHB_DYN_SMEM(name) extern __shared__ __align__(128) unsigned char name[]
 #endif

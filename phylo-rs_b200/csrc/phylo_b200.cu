@@ -7,6 +7,8 @@
 // levels (a node's level = 1 + max level of its children), assigns CLV slots, tiles the site axis
 // so that a tile's CLVs fit in HBM, and launches the kernels of kernels.cuh level by level.
 #include "kernels.cuh"
+#include "sweep.cuh"
+#include "sweep_sched.h"
 #include "../../include/phylo_b200.h"
 
 #include <algorithm>
@@ -209,8 +211,13 @@ struct Device {
     int64_t p_begin = 0, P = 0, P_pad = 0; // shard of the global pattern range
     DevBuf tips, mult, leaf_ls, inv_mask, per_pattern, row_invalid, Pmat, blen, clv, scale, cat_ll,
         partials, total, ops, gops, gkids, dops, dkids, leaf_rows, states, posteriors, staging,
-        sim_pre, sim_parent, sim_depth, sim_leafrow, sim_stack, scratch;
+        sim_pre, sim_parent, sim_depth, sim_leafrow, sim_stack, scratch, sw_descs, sw_blocks, sw_stream, sw_gstack,
+        sw_err;
+    bool sweep_uploaded = false;
+    int sm_count = 0;
+    size_t smem_optin = 0;
     double *h_total = nullptr; // pinned
+    cudaEvent_t tm_a = nullptr, tm_b = nullptr; // phb_timer_start / phb_timer_stop
     int64_t tile_pad = 0;
     int n_tiles = 0;
     bool tip_constants_valid = false;
@@ -242,6 +249,8 @@ struct phb_ctx {
     // tree
     TreeSched tree;
     bool tree_uploaded = false;
+    SweepSched sweep;      // fused-sweep op stream for (tree, n_clv)
+    SweepGeom sweep_geom;
     // stats
     phb_stats stats;
     int64_t launches = 0;
@@ -278,6 +287,7 @@ struct phb_ctx {
 namespace {
 
 inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+constexpr size_t TIPS_SLACK = 4096; // the sweep's last site block may read past the final row
 
 // timing helpers: bracket one launch with an event pair on device 0 when PHB_FLAG_TIMING is set
 struct ScopedTimer {
@@ -343,6 +353,7 @@ int upload_tree(phb_ctx *ctx)
         CU(cudaStreamSynchronize(d.stream));
     }
     ctx->tree_uploaded = true;
+    ctx->sweep.valid = false;
     return PHB_OK;
 }
 
@@ -364,10 +375,19 @@ int check_leaves(phb_ctx *ctx)
 }
 
 // Plans the site tiling of one device and (re)allocates the per-evaluation buffers.
-int plan_device(phb_ctx *ctx, Device &d, const ModelDev &M, bool asr, bool want_post)
+int plan_device(phb_ctx *ctx, Device &d, const ModelDev &M, bool asr, bool want_post, bool use_sweep)
 {
     const TreeSched &T = ctx->tree;
     CU(cudaSetDevice(d.ordinal));
+    if (use_sweep) { // no CLV tiles in HBM: the whole shard is one pass
+        CU(d.per_pattern.ensure(sizeof(double) * (size_t)d.P_pad));
+        CU(d.leaf_ls.ensure(sizeof(double) * (size_t)d.P_pad));
+        CU(d.inv_mask.ensure((size_t)d.P_pad));
+        CU(d.total.ensure(sizeof(double)));
+        d.tile_pad = d.P_pad;
+        d.n_tiles = d.P > 0 ? 1 : 0;
+        return PHB_OK;
+    }
     if (asr) {
         CU(d.states.ensure((size_t)T.n * (size_t)d.P_pad));
         if (want_post) CU(d.posteriors.ensure((size_t)T.n * (size_t)d.P_pad * 4 * sizeof(double)));
@@ -496,6 +516,104 @@ int run_tile_down(phb_ctx *ctx, Device &d, const ModelDev &M, int64_t tile_off, 
     return PHB_OK;
 }
 
+// ---- fused sweep (sweep.cuh) ---------------------------------------------------------------------
+// (Re)builds the op stream for the current tree and category count and uploads it to every device.
+int ensure_sweep(phb_ctx *ctx, const ModelDev &M)
+{
+    const TreeSched &T = ctx->tree;
+    SweepSched &S = ctx->sweep;
+    if (!S.valid || S.n_clv != M.n_clv) {
+        for (Device &d : ctx->devs) { // the old host image may still be in flight
+            cudaSetDevice(d.ordinal);
+            cudaStreamSynchronize(d.stream);
+            d.sweep_uploaded = false;
+        }
+        S.build(T.n, T.root, T.child_off, T.children, T.leaf_row, M.n_clv);
+        size_t smem_max = ctx->devs[0].smem_optin;
+        for (Device &d : ctx->devs) smem_max = std::min(smem_max, d.smem_optin);
+        if (!ctx->sweep_geom.plan(S, smem_max))
+            return ctx->fail(PHB_ERR_INVALID_MODEL_PARAMETER, "sweep: %d CLV categories do not fit one CTA", M.n_clv);
+    }
+    for (Device &d : ctx->devs) {
+        if (d.sweep_uploaded) continue;
+        CU(cudaSetDevice(d.ordinal));
+        CU(d.sw_descs.ensure(sizeof(SweepDesc) * S.descs.size()));
+        CU(d.sw_blocks.ensure(sizeof(SweepBlock) * S.blocks.size()));
+        CU(d.sw_stream.ensure(S.stream_bytes + 16));
+        CU(d.sw_err.ensure(sizeof(unsigned int)));
+        CU(cudaMemcpyAsync(d.sw_descs.p, S.descs.data(), sizeof(SweepDesc) * S.descs.size(), cudaMemcpyHostToDevice, d.stream));
+        CU(cudaMemcpyAsync(d.sw_blocks.p, S.blocks.data(), sizeof(SweepBlock) * S.blocks.size(), cudaMemcpyHostToDevice, d.stream));
+        CU(cudaMemcpyAsync(d.sw_stream.p, S.headers.data(), S.stream_bytes, cudaMemcpyHostToDevice, d.stream));
+        CU(cudaMemsetAsync(d.sw_err.p, 0, sizeof(unsigned int), d.stream));
+        d.sweep_uploaded = true;
+    }
+    return PHB_OK;
+}
+
+// compute_log_likelihood's pattern loop on one device: P(t) stream, one persistent sweep launch.
+int run_sweep(phb_ctx *ctx, Device &d, const ModelDev &M)
+{
+    const TreeSched &T = ctx->tree;
+    const SweepSched &S = ctx->sweep;
+    const SweepGeom &G = ctx->sweep_geom;
+    const int sites_per_block = 4 * G.Q;
+    const int64_t n_blocks = (d.P + sites_per_block - 1) / sites_per_block;
+    const int grid = (int)std::min<int64_t>(n_blocks, std::max(d.sm_count, 1));
+    CU(d.partials.ensure(sizeof(double) * (size_t)std::max<int64_t>(n_blocks, 1)));
+    if (G.g_levels > 0) CU(d.sw_gstack.ensure((size_t)grid * G.g_levels * G.level_bytes));
+    {
+        ScopedTimer tm(ctx, &d, PH_TRANSITION);
+        int nthreads = (int)S.blocks.size() * M.n_clv;
+        PHB_LAUNCH(sweep_transition_kernel, dim3((nthreads + 127) / 128), dim3(128), d.stream, d.sw_blocks.as<SweepBlock>(),
+                   (int)S.blocks.size(), d.blen.as<double>(), M, d.sw_stream.as<unsigned char>());
+        CHECK_LAUNCH();
+    }
+    SweepParams sp;
+    memset(&sp, 0, sizeof sp);
+    sp.descs = d.sw_descs.as<SweepDesc>();
+    sp.stream = d.sw_stream.as<unsigned char>();
+    sp.n_ops = S.n_ops;
+    sp.Q = G.Q;
+    sp.n_consumers = G.n_consumers;
+    sp.n_stages = G.n_stages;
+    sp.stage_bytes = G.stage_bytes;
+    sp.rec_cap = (S.rec_cap + 15) / 16 * 16;
+    sp.smem_levels = G.smem_levels;
+    sp.g_levels = G.g_levels;
+    sp.gstack = d.sw_gstack.as<double>();
+    sp.tips = d.tips.as<uint8_t>();
+    sp.P_pad = d.P_pad;
+    sp.P = d.P;
+    sp.n_blocks = n_blocks;
+    sp.leaf_ls = d.leaf_ls.as<double>();
+    sp.inv_mask = d.inv_mask.as<uint8_t>();
+    sp.mult = d.mult.as<double>();
+    sp.per_pattern = d.per_pattern.as<double>();
+    sp.partials = d.partials.as<double>();
+    sp.error_flag = d.sw_err.as<unsigned int>();
+    {
+        ScopedTimer tm(ctx, &d, PH_CLV);
+#ifndef PHB_HOST_EMU
+        static bool attr_set[64] = {false};
+        if (!attr_set[d.ordinal & 63]) {
+            CU(cudaFuncSetAttribute(sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)d.smem_optin));
+            attr_set[d.ordinal & 63] = true;
+        }
+#endif
+        PHB_LAUNCH_SMEM(sweep_kernel, dim3(grid), dim3(G.threads), G.smem_bytes, d.stream, sp, M);
+        CHECK_LAUNCH();
+        if (&d == &ctx->devs[0]) ctx->stats.clv_launches++;
+    }
+    {
+        ScopedTimer tm(ctx, &d, PH_ROOT);
+        PHB_LAUNCH(final_reduce_kernel, dim3(1), dim3(1024), d.stream, d.partials.as<double>(), (int)n_blocks,
+                   d.total.as<double>());
+        CHECK_LAUNCH();
+    }
+    (void)T;
+    return PHB_OK;
+}
+
 // One full evaluation on every device.  asr=false: compute_log_likelihood; asr=true: + down pass.
 int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total)
 {
@@ -516,13 +634,19 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total)
         if (rc) return rc;
     }
     const ModelDev &M = asr ? ctx->model_lit : ctx->model;
+    const bool use_sweep = !asr && !(ctx->flags & PHB_FLAG_LEVEL_KERNELS) && T.n_internal > 0 && M.n_clv > 0 &&
+                           M.n_cat <= 4 * M.n_clv;
+    if (use_sweep) {
+        rc = ensure_sweep(ctx, M);
+        if (rc) return rc;
+    }
     Device &d0 = ctx->devs[0];
     d0.ev_used = 0;
     d0.ev_log.clear();
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
     const bool timing = ctx->flags & PHB_FLAG_TIMING;
     for (Device &d : ctx->devs) {
-        rc = plan_device(ctx, d, M, asr, want_post);
+        rc = plan_device(ctx, d, M, asr, want_post, use_sweep);
         if (rc) return rc;
     }
     if (timing) {
@@ -538,7 +662,7 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total)
             *d.h_total = 0.0;
             continue;
         }
-        {
+        if (!use_sweep) {
             ScopedTimer tm(ctx, &d, PH_TRANSITION);
             int nthreads = T.n * M.n_cat;
             PHB_LAUNCH(transition_kernel, dim3((nthreads + 127) / 128), dim3(128), d.stream, d.blen.as<double>(), T.n, M,
@@ -554,6 +678,12 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total)
             CHECK_LAUNCH();
             d.tip_constants_valid = true;
             d.tip_constants_rows = T.leaf_rows;
+        }
+        if (use_sweep) {
+            rc = run_sweep(ctx, d, M);
+            if (rc) return rc;
+            CU(cudaMemcpyAsync(d.h_total, d.total.p, sizeof(double), cudaMemcpyDeviceToHost, d.stream));
+            continue;
         }
         size_t part_off = 0;
         for (int t = 0; t < d.n_tiles; ++t) {
@@ -653,6 +783,12 @@ int32_t phb_ctx_create(const int32_t *devices, int32_t n_dev, uint64_t flags, ph
     for (size_t i = 0; i < ords.size(); ++i) {
         Device &d = ctx->devs[i];
         d.ordinal = ords[i];
+        cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, d.ordinal);
+        {
+            int v = 0;
+            cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, d.ordinal);
+            d.smem_optin = (size_t)v;
+        }
         if (cudaSetDevice(d.ordinal) != cudaSuccess || cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking) != cudaSuccess ||
             cudaHostAlloc((void **)&d.h_total, sizeof(double), cudaHostAllocDefault) != cudaSuccess) {
             phb_ctx_destroy(ctx);
@@ -672,13 +808,16 @@ void phb_ctx_destroy(phb_ctx *ctx)
         DevBuf *bufs[] = {&d.tips, &d.mult, &d.leaf_ls, &d.inv_mask, &d.per_pattern, &d.row_invalid, &d.Pmat, &d.blen,
                           &d.clv, &d.scale, &d.cat_ll, &d.partials, &d.total, &d.ops, &d.gops, &d.gkids, &d.dops,
                           &d.dkids, &d.leaf_rows, &d.states, &d.posteriors, &d.staging, &d.sim_pre, &d.sim_parent,
-                          &d.sim_depth, &d.sim_leafrow, &d.sim_stack, &d.scratch};
+                          &d.sim_depth, &d.sim_leafrow, &d.sim_stack, &d.scratch, &d.sw_descs, &d.sw_blocks,
+                          &d.sw_stream, &d.sw_gstack, &d.sw_err};
         for (DevBuf *b : bufs) b->release();
         for (auto &ep : d.ev_pool) {
             cudaEventDestroy(ep.a);
             cudaEventDestroy(ep.b);
         }
         if (d.h_total) cudaFreeHost(d.h_total);
+        if (d.tm_a) cudaEventDestroy(d.tm_a);
+        if (d.tm_b) cudaEventDestroy(d.tm_b);
         if (d.stream) cudaStreamDestroy(d.stream);
     }
     delete ctx;
@@ -704,7 +843,8 @@ static int shard_and_alloc(phb_ctx *ctx, int n_rows, int64_t P)
         d.P_pad = std::max<int64_t>(round_up(d.P, SITES_PER_BLOCK), SITES_PER_BLOCK);
         d.tip_constants_valid = false;
         CU(cudaSetDevice(d.ordinal));
-        CU(d.tips.ensure((size_t)std::max(n_rows, 1) * (size_t)d.P_pad));
+        CU(d.tips.ensure((size_t)std::max(n_rows, 1) * (size_t)d.P_pad + TIPS_SLACK));
+        CU(cudaMemsetAsync(d.tips.as<uint8_t>() + (size_t)std::max(n_rows, 1) * (size_t)d.P_pad, CODE_GAP, TIPS_SLACK, d.stream));
         CU(d.mult.ensure(sizeof(double) * (size_t)d.P_pad));
         CU(d.row_invalid.ensure(sizeof(int) * (size_t)std::max(n_rows, 1)));
         CU(cudaMemsetAsync(d.row_invalid.p, 0, sizeof(int) * (size_t)std::max(n_rows, 1), d.stream));
@@ -1074,6 +1214,40 @@ int32_t phb_get_stats(phb_ctx *ctx, phb_stats *out)
     if (!ctx || !out) return PHB_ERR_INVALID_ARGUMENT;
     ctx->stats.kernel_launches = ctx->launches;
     *out = ctx->stats;
+    return PHB_OK;
+}
+
+int32_t phb_timer_start(phb_ctx *ctx)
+{
+    if (!ctx) return PHB_ERR_INVALID_ARGUMENT;
+    for (Device &d : ctx->devs) {
+        CU(cudaSetDevice(d.ordinal));
+        if (!d.tm_a) {
+            CU(cudaEventCreate(&d.tm_a));
+            CU(cudaEventCreate(&d.tm_b));
+        }
+        CU(cudaEventRecord(d.tm_a, d.stream));
+    }
+    return PHB_OK;
+}
+
+int32_t phb_timer_stop(phb_ctx *ctx, double *ms)
+{
+    if (!ctx || !ms) return PHB_ERR_INVALID_ARGUMENT;
+    double worst = 0.0;
+    for (Device &d : ctx->devs) {
+        if (!d.tm_a) return ctx->fail(PHB_ERR_STATE, "timer_stop without timer_start");
+        CU(cudaSetDevice(d.ordinal));
+        CU(cudaEventRecord(d.tm_b, d.stream));
+    }
+    for (Device &d : ctx->devs) {
+        CU(cudaSetDevice(d.ordinal));
+        CU(cudaStreamSynchronize(d.stream));
+        float t = 0;
+        cudaEventElapsedTime(&t, d.tm_a, d.tm_b);
+        worst = std::max(worst, (double)t);
+    }
+    *ms = worst;
     return PHB_OK;
 }
 

@@ -1,0 +1,190 @@
+// sweep_sched.h — host scheduler of the fused sweep (sweep.cuh): turns the child lists of the
+// flattened tree (phb_set_tree) into the op stream a CTA executes for every block of site patterns.
+//
+// The reference evaluates nodes in DFSPostOrderIterator order (src/iter.rs:112-138) and keeps every
+// node's profile in a HashMap (src/tree/likelihood.rs:95).  Any order that visits children before
+// parents gives the same per-node arithmetic; this scheduler picks the depth-first order that
+// minimises the number of partial results alive at once (Sethi–Ullman: among a node's internal
+// children the one whose subtree needs more stack levels goes first), and assigns every pending
+// sibling a STATIC stack level = need(subtree evaluated while it waits).  Nested waits have strictly
+// smaller needs, so levels never collide and the low (hot) levels can live in shared memory.
+#pragma once
+#include "sweep.cuh"
+
+#include <algorithm>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace phb {
+
+struct SweepSched {
+    bool valid = false;
+    int n_clv = 0;
+    int n_ops = 0;
+    int n_levels = 0;   // stack levels used (need(root))
+    int rec_cap = 0;    // largest record
+    size_t stream_bytes = 0;
+    std::vector<SweepDesc> descs;
+    std::vector<SweepBlock> blocks;
+    std::vector<unsigned char> headers; // stream image holding the record headers (blocks zero)
+    int count_kind[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+
+    // child_off/children: CSR child lists; leaf_row: alignment row per leaf; root must be internal.
+    void build(int n, int root, const std::vector<int> &child_off, const std::vector<int> &children,
+               const std::vector<int> &leaf_row, int n_clv_)
+    {
+        valid = false;
+        n_clv = n_clv_;
+        descs.clear();
+        blocks.clear();
+        for (int &c : count_kind) c = 0;
+        auto is_leaf = [&](int v) { return child_off[v + 1] == child_off[v]; };
+        // post-order (children before parents) for the need computation
+        std::vector<int> order;
+        order.reserve(n);
+        {
+            std::vector<int> st(1, root);
+            while (!st.empty()) {
+                int v = st.back();
+                st.pop_back();
+                order.push_back(v);
+                for (int k = child_off[v]; k < child_off[v + 1]; ++k) st.push_back(children[k]);
+            }
+            std::reverse(order.begin(), order.end());
+        }
+        std::vector<int> need(n, 0);
+        std::vector<std::vector<int>> ints(n), tips(n);
+        for (int v : order) {
+            if (is_leaf(v)) continue;
+            for (int k = child_off[v]; k < child_off[v + 1]; ++k) {
+                int c = children[k];
+                (is_leaf(c) ? tips[v] : ints[v]).push_back(c);
+            }
+            std::stable_sort(ints[v].begin(), ints[v].end(), [&](int a, int b) { return need[a] > need[b]; });
+            int nd = 0;
+            if (!ints[v].empty()) nd = need[ints[v][0]];
+            if (ints[v].size() >= 2) nd = std::max(nd, need[ints[v][1]] + 1);
+            need[v] = nd;
+        }
+        n_levels = need[root];
+
+        struct Rec { SweepHdr h; int edgeA, edgeB, rowA, rowB; bool tabA, tabB; };
+        std::vector<Rec> recs;
+        int pending_push = -1;
+        auto emit = [&](int kind, int level, int edgeA, bool tabA, int edgeB, bool tabB) {
+            Rec r;
+            memset(&r, 0, sizeof r);
+            r.h.kind = kind;
+            r.h.level = level;
+            if (kind == SW_TT || kind == SW_LOADTIP) {
+                if (pending_push >= 0) {
+                    r.h.flags |= SW_FLAG_PUSH;
+                    r.h.level = pending_push;
+                    pending_push = -1;
+                }
+            }
+            r.edgeA = edgeA; r.edgeB = edgeB; r.tabA = tabA; r.tabB = tabB;
+            r.h.szA = edgeA < 0 ? 0 : (tabA ? SW_TAB_BYTES : SW_P_BYTES);
+            r.h.szB = edgeB < 0 ? 0 : (tabB ? SW_TAB_BYTES : SW_P_BYTES);
+            r.rowA = (edgeA >= 0 && tabA) ? leaf_row[edgeA] : -1;
+            r.rowB = (edgeB >= 0 && tabB) ? leaf_row[edgeB] : -1;
+            recs.push_back(r);
+            count_kind[kind]++;
+        };
+        struct Frame { int v, j; bool ret; };
+        std::vector<Frame> st;
+        st.push_back({root, 0, false});
+        while (!st.empty()) {
+            Frame &f = st.back();
+            const int v = f.v;
+            const std::vector<int> &iv = ints[v], &tv = tips[v];
+            const bool binary = iv.size() + tv.size() == 2;
+            if (f.ret) { // child iv[j-1] just finished; its CLV is the running value
+                f.ret = false;
+                if (!binary) {
+                    emit(SW_APPLY, 0, iv[f.j - 1], false, -1, false);
+                    if (f.j - 1 >= 1) emit(SW_MULPOP, need[iv[f.j - 1]], -1, false, -1, false);
+                }
+            }
+            if (f.j < (int)iv.size()) {
+                if (f.j >= 1) pending_push = need[iv[f.j]];
+                f.ret = true;
+                int c = iv[f.j++];
+                st.push_back({c, 0, false});
+                continue;
+            }
+            if (binary) {
+                if (iv.size() == 2) emit(SW_II, need[iv[1]], iv[0], false, iv[1], false);
+                else if (iv.size() == 1) emit(SW_TI, 0, tv[0], true, iv[0], false);
+                else emit(SW_TT, 0, tv[0], true, tv[1], true);
+            } else if (iv.empty()) {
+                size_t k = 0;
+                if (tv.size() >= 2) {
+                    emit(SW_TT, 0, tv[0], true, tv[1], true);
+                    k = 2;
+                } else {
+                    emit(SW_LOADTIP, 0, tv[0], true, -1, false);
+                    k = 1;
+                }
+                for (; k < tv.size(); ++k) emit(SW_MULTIP, 0, tv[k], true, -1, false);
+            } else {
+                for (int tnode : tv) emit(SW_MULTIP, 0, tnode, true, -1, false);
+            }
+            recs.back().h.flags |= SW_FLAG_RESCALE;
+            st.pop_back();
+        }
+        // lay the records out in op order
+        n_ops = (int)recs.size();
+        size_t off = 0;
+        rec_cap = 0;
+        descs.resize(recs.size());
+        for (size_t k = 0; k < recs.size(); ++k) {
+            const Rec &r = recs[k];
+            const uint32_t per_cat = (uint32_t)(r.h.szA + r.h.szB);
+            const uint32_t bytes = SW_HDR_BYTES + (uint32_t)n_clv * per_cat;
+            SweepDesc &d = descs[k];
+            memset(&d, 0, sizeof d);
+            d.rec_off = off;
+            d.rec_bytes = bytes;
+            d.rowA = r.rowA;
+            d.rowB = r.rowB;
+            if (r.edgeA >= 0) blocks.push_back({off + SW_HDR_BYTES, per_cat, r.edgeA, r.tabA ? 1 : 0, 0});
+            if (r.edgeB >= 0) blocks.push_back({off + SW_HDR_BYTES + (uint32_t)r.h.szA, per_cat, r.edgeB, r.tabB ? 1 : 0, 0});
+            rec_cap = std::max(rec_cap, (int)bytes);
+            off += bytes;
+        }
+        stream_bytes = off;
+        headers.assign(stream_bytes + 16, 0);
+        for (size_t k = 0; k < recs.size(); ++k) memcpy(headers.data() + descs[k].rec_off, &recs[k].h, sizeof(SweepHdr));
+        valid = true;
+    }
+};
+
+// Launch geometry / shared-memory carve-up for a schedule.
+struct SweepGeom {
+    int Q = 0, n_consumers = 0, threads = 0, n_stages = 0, stage_bytes = 0, smem_levels = 0, g_levels = 0;
+    size_t level_bytes = 0, smem_bytes = 0;
+    bool plan(const SweepSched &S, size_t smem_max)
+    {
+        Q = (SW_MAX_CONSUMERS / S.n_clv) & ~3;
+        if (Q < 4) return false;
+        n_consumers = Q * S.n_clv;
+        threads = ((n_consumers + 31) / 32) * 32 + 32;
+        level_bytes = (size_t)n_consumers * SW_R * 32;
+        stage_bytes = (S.rec_cap + 2 * 4 * Q + 127) / 128 * 128;
+        const int want_levels = std::max(S.n_levels, 1);
+        for (n_stages = 8; n_stages >= 2; --n_stages) {
+            size_t fixed = SW_BAR_BYTES + (size_t)n_stages * stage_bytes;
+            if (fixed + level_bytes > smem_max) continue;
+            smem_levels = (int)std::min<size_t>((smem_max - fixed) / level_bytes, (size_t)want_levels);
+            if (smem_levels >= std::min(want_levels, 3) || n_stages == 2) break;
+        }
+        if (n_stages < 2) return false;
+        g_levels = std::max(0, S.n_levels - smem_levels);
+        smem_bytes = SW_BAR_BYTES + (size_t)n_stages * stage_bytes + (size_t)smem_levels * level_bytes;
+        return true;
+    }
+};
+
+} // namespace phb

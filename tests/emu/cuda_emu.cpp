@@ -9,6 +9,7 @@
 namespace emu {
 
 dim3 threadIdx, blockIdx, blockDim, gridDim;
+unsigned char *dyn_smem = nullptr;
 
 namespace {
 struct Fiber {
@@ -32,27 +33,64 @@ void fiber_entry()
 }
 } // namespace
 
-void syncthreads()
+void yield() { swapcontext(&g_fibers[g_current].ctx, &g_sched); }
+
+namespace {
+struct Bar { unsigned arrived = 0; unsigned long gen = 0; };
+Bar g_bars[16 + 64]; // 0..15: bar.sync ids (0 = __syncthreads), 16..: per-warp barriers
+unsigned g_nthreads = 0;
+void barrier(Bar &b, unsigned count)
 {
-    // yield; the scheduler resumes every live fiber once per round => barrier semantics
-    swapcontext(&g_fibers[g_current].ctx, &g_sched);
+    unsigned long gen = b.gen;
+    if (++b.arrived >= count) {
+        b.arrived = 0;
+        ++b.gen;
+        return;
+    }
+    while (b.gen == gen) yield();
+}
+unsigned lin_tid() { return threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z); }
+unsigned warp_size_of(unsigned warp) { unsigned lo = warp * 32; return g_nthreads - lo < 32 ? g_nthreads - lo : 32; }
+} // namespace
+
+void syncthreads() { barrier(g_bars[0], g_nthreads); }
+void named_barrier(int id, unsigned count) { barrier(g_bars[id & 15], count); }
+void syncwarp()
+{
+    unsigned w = lin_tid() >> 5;
+    barrier(g_bars[16 + (w & 63)], warp_size_of(w));
 }
 
 double shfl_down(double v, unsigned delta)
 {
-    unsigned lin = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
-    unsigned n = blockDim.x * blockDim.y * blockDim.z;
+    unsigned lin = lin_tid();
     g_xbuf[lin] = v;
-    syncthreads();
+    syncwarp();
     unsigned lane = lin & 31u, src = lin + delta;
-    double r = (lane + delta < 32u && src < n) ? g_xbuf[src] : v;
-    syncthreads();
+    double r = (lane + delta < 32u && src < g_nthreads) ? g_xbuf[src] : v;
+    syncwarp();
     return r;
 }
 
-void launch(dim3 grid, dim3 block, const std::function<void()> &body)
+double shfl_idx(double v, unsigned src_lane)
+{
+    unsigned lin = lin_tid();
+    g_xbuf[lin] = v;
+    syncwarp();
+    unsigned src = (lin & ~31u) + (src_lane & 31u);
+    double r = src < g_nthreads ? g_xbuf[src] : v;
+    syncwarp();
+    return r;
+}
+
+void launch(dim3 grid, dim3 block, const std::function<void()> &body, size_t dyn_smem_bytes)
 {
     const unsigned nthreads = block.x * block.y * block.z;
+    g_nthreads = nthreads;
+    static std::vector<unsigned char> smem_buf;
+    if (smem_buf.size() < dyn_smem_bytes + 256) smem_buf.resize(dyn_smem_bytes + 256);
+    dyn_smem = (unsigned char *)(((uintptr_t)smem_buf.data() + 127) & ~(uintptr_t)127);
+    for (auto &b : g_bars) b = Bar();
     if (g_fibers.size() < nthreads) {
         size_t old = g_fibers.size();
         g_fibers.resize(nthreads);
@@ -150,7 +188,15 @@ cudaError_t cudaGetDeviceCount(int *n)
     return cudaSuccess;
 }
 cudaError_t cudaSetDevice(int) { return cudaSuccess; }
-cudaError_t cudaDeviceGetAttribute(int *v, int, int) { *v = 10; return cudaSuccess; }
+cudaError_t cudaDeviceGetAttribute(int *v, int attr, int)
+{
+    if (attr == cudaDevAttrMultiProcessorCount) *v = 3;            // few "SMs": several site blocks per CTA
+    else if (attr == cudaDevAttrMaxSharedMemoryPerBlockOptin) {
+        const char *e = getenv("PHB_EMU_SMEM_BYTES");              // small values force global stack levels
+        *v = e ? atoi(e) : 232448;
+    } else *v = 10;
+    return cudaSuccess;
+}
 cudaError_t cudaStreamCreateWithFlags(cudaStream_t *s, unsigned) { *s = new emu_stream(); return cudaSuccess; }
 cudaError_t cudaStreamDestroy(cudaStream_t s) { delete s; return cudaSuccess; }
 cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }

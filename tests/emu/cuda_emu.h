@@ -34,9 +34,17 @@ static inline double2 make_double2(double x, double y) { double2 r; r.x = x; r.y
 
 namespace emu {
 extern dim3 threadIdx, blockIdx, blockDim, gridDim;
-void launch(dim3 grid, dim3 block, const std::function<void()> &body);
-void syncthreads();
-double shfl_down(double v, unsigned delta);
+extern unsigned char *dyn_smem; // dynamic shared memory of the running block
+void launch(dim3 grid, dim3 block, const std::function<void()> &body, size_t dyn_smem_bytes = 0);
+void yield();                                  // let the other fibers of the block run
+void syncthreads();                            // counting barrier over all live threads of the block
+void named_barrier(int id, unsigned count);    // bar.sync id, count
+void syncwarp();
+double shfl_down(double v, unsigned delta);    // warp-level
+double shfl_idx(double v, unsigned src_lane);  // warp-level
+// mbarrier / bulk-copy stand-ins (product: PTX mbarrier.* and cp.async.bulk, see csrc/sweep.cuh)
+struct Mbar { int count, pending; long long tx; int phase; };
+inline void mbar_check(Mbar *b) { if (b->pending == 0 && b->tx == 0) { b->phase ^= 1; b->pending = b->count; } }
 } // namespace emu
 using emu::blockDim;
 using emu::blockIdx;
@@ -44,11 +52,16 @@ using emu::gridDim;
 using emu::threadIdx;
 
 static inline void __syncthreads() { emu::syncthreads(); }
+static inline void __syncwarp(unsigned = 0xffffffffu) { emu::syncwarp(); }
+static inline double __shfl_sync(unsigned, double v, int src) { return emu::shfl_idx(v, (unsigned)src); }
+static inline int __ffs(int v) { return __builtin_ffs(v); }
+static inline int __double2hiint(double d) { long long v; memcpy(&v, &d, 8); return (int)(v >> 32); }
 static inline double __shfl_down_sync(unsigned, double v, unsigned delta) { return emu::shfl_down(v, delta); }
 template <typename T> static inline T __ldg(const T *p) { return *p; }
 static inline int __popc(unsigned v) { return __builtin_popcount(v); }
 static inline double __longlong_as_double(long long v) { double d; memcpy(&d, &v, 8); return d; }
 static inline int atomicAdd(int *p, int v) { int o = *p; *p += v; return o; }
+static inline unsigned atomicOr(unsigned *p, unsigned v) { unsigned o = *p; *p |= v; return o; }
 using std::isfinite;
 using std::max;
 using std::min;
@@ -59,7 +72,8 @@ enum { cudaSuccess = 0, cudaErrorMemoryAllocation = 2, cudaErrorInvalidValue = 1
 typedef struct emu_stream *cudaStream_t;
 typedef struct emu_event *cudaEvent_t;
 enum cudaMemcpyKind { cudaMemcpyHostToDevice = 1, cudaMemcpyDeviceToHost = 2, cudaMemcpyDeviceToDevice = 3 };
-enum { cudaStreamNonBlocking = 1, cudaHostAllocDefault = 0, cudaDevAttrComputeCapabilityMajor = 75 };
+enum { cudaStreamNonBlocking = 1, cudaHostAllocDefault = 0, cudaDevAttrComputeCapabilityMajor = 75,
+       cudaDevAttrMultiProcessorCount = 16, cudaDevAttrMaxSharedMemoryPerBlockOptin = 97 };
 
 cudaError_t cudaMalloc(void **p, size_t bytes);
 cudaError_t cudaFree(void *p);

@@ -66,7 +66,12 @@ def test_tiling_and_sharding_invariance(gpu_lib):
 @pytest.mark.parametrize("model", ["jc69", "gtr_g4", "gtr_i_g4"])
 def test_asr_models(gpu_lib, model):
     case = workloads.make_case(40, 1500, model=model, seed=26, ambiguity=0.05)
-    assert _cases.check_asr(gpu_lib, case, want_post=True) == 0
+    mism = _cases.check_asr(gpu_lib, case, want_post=True)
+    # JC69 is exactly symmetric: ambiguity codes create EXACT posterior ties whose winner is decided by
+    # the last bit of round-off (SURVEY.md §7 hard part 2); check_asr has already asserted that every
+    # mismatch sits on such a tie (oracle top-2 gap < 1e-10).  Asymmetric models must match bit for bit.
+    if model != "jc69":
+        assert mism == 0
 
 
 def test_asr_500_taxa_sample(gpu_lib):
