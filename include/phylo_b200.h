@@ -159,7 +159,12 @@ typedef struct phb_stats {
     double ms_down;            /* ... in the ASR pre-order kernels                                 */
     double ms_total;           /* ... first launch to last launch of the evaluation                */
     int32_t clv_launches;      /* number of CLV kernel launches in the last evaluation             */
-    int32_t reserved;
+    int32_t sweep_ops;         /* fused sweep: ops per site block (0 = the level kernels ran)       */
+    int32_t sweep_stack_levels;/* ... stack levels the schedule needs (Sethi-Ullman number)         */
+    int32_t sweep_smem_levels; /* ... of which held in shared memory (the rest: L2-resident stack)  */
+    int32_t sweep_stages;      /* ... TMA ring depth                                                */
+    int32_t sweep_block_sites; /* ... site patterns per CTA pass                                    */
+    int64_t sweep_stream_bytes;/* ... bytes of the op-ordered P(t)/tip-table stream                 */
 } phb_stats;
 int32_t phb_get_stats(phb_ctx *ctx, phb_stats *out);
 

@@ -54,7 +54,8 @@ class Stats(C.Structure):
         ("kernel_launches", C.c_int64), ("clv_updates", C.c_int64), ("algorithmic_bytes", C.c_double),
         ("ms_transition", C.c_double), ("ms_clv", C.c_double), ("ms_root", C.c_double),
         ("ms_down", C.c_double), ("ms_total", C.c_double), ("clv_launches", C.c_int32),
-        ("reserved", C.c_int32),
+        ("sweep_ops", C.c_int32), ("sweep_stack_levels", C.c_int32), ("sweep_smem_levels", C.c_int32),
+        ("sweep_stages", C.c_int32), ("sweep_block_sites", C.c_int32), ("sweep_stream_bytes", C.c_int64),
     ]
 
     def as_dict(self):

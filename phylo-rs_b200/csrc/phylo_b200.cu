@@ -727,6 +727,12 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total)
     S.kernel_launches = ctx->launches;
     S.clv_updates = (int64_t)T.n_internal * ctx->n_patterns;
     S.algorithmic_bytes = (32.0 * M.n_clv * T.sum_one_plus_i + T.sum_t) * (double)ctx->n_patterns;
+    S.sweep_ops = use_sweep ? ctx->sweep.n_ops : 0;
+    S.sweep_stack_levels = use_sweep ? ctx->sweep.n_levels : 0;
+    S.sweep_smem_levels = use_sweep ? ctx->sweep_geom.smem_levels : 0;
+    S.sweep_stages = use_sweep ? ctx->sweep_geom.n_stages : 0;
+    S.sweep_block_sites = use_sweep ? 4 * ctx->sweep_geom.Q : 0;
+    S.sweep_stream_bytes = use_sweep ? (int64_t)ctx->sweep.stream_bytes : 0;
     if (timing) {
         S.ms_transition = S.ms_clv = S.ms_root = S.ms_down = 0;
         for (auto &pr : d0.ev_log) {

@@ -427,6 +427,7 @@ sweep_kernel(SweepParams p, ModelDev M)
         // ---- root: per-category log-likelihoods, category mix, weights, block reduction ----
         // (src/tree/likelihood.rs:135-140, :61-68, :205).  The stack is idle here; its first bytes hold
         // the [model category][site] exchange buffer.
+        sw_consumer_barrier(n_cons_warps * 32); // warps drift: nobody may still be using stack level 0
         double *xch = reinterpret_cast<double *>(stack);
         const int64_t site0 = b * sites_per_block + 4 * q;
         if (active) {

@@ -17,7 +17,8 @@ def main():
     t0 = time.time()
     case = workloads.make_case(n_taxa, 4, model=model, seed=1)
     print("case built", time.time() - t0, flush=True)
-    with capi.Context(flags=capi.FLAG_TIMING) as ctx:
+    flags = capi.FLAG_TIMING | (capi.FLAG_LEVEL_KERNELS if len(sys.argv) > 4 and sys.argv[4] == 'levels' else 0)
+    with capi.Context(flags=flags) as ctx:
         print("fp64 TFLOP/s:", ctx.measure_fp64_tflops(), flush=True)
         workloads.load_into(ctx, case)
         ctx.simulate_alignment(P, seed=5)

@@ -39,6 +39,43 @@ def test_gtr_i_g4_deep_tree_scaling(gpu_lib):
     assert per.min() < -2000
 
 
+@pytest.mark.parametrize("model", ["jc69", "gtr_g4", "gtr_i_g4"])
+def test_level_kernels_flag(gpu_lib, model):
+    """The HBM-resident level-batched kernels (kept for the ASR up pass) stay parity-green for lnL too."""
+    case = workloads.make_case(200, 3000, model=model, seed=22, ambiguity=0.05)
+    _cases.check_lnl(gpu_lib, case, flags=capi.FLAG_LEVEL_KERNELS)
+
+
+def test_sweep_shapes(gpu_lib):
+    """Balanced tree (deepest stack), caterpillar (no stack), polytomies/unifurcations (generic ops)."""
+    def balanced(lo, hi):
+        if hi - lo == 1:
+            return f"t{lo}:0.{1 + lo % 7}"
+        mid = (lo + hi) // 2
+        return f"({balanced(lo, mid)},{balanced(mid, hi)}):0.0{1 + (lo + hi) % 9}"
+
+    def cater(n):
+        s = "(t0:0.1,t1:0.2)"
+        for i in range(2, n):
+            s = f"({s}:0.0{1 + i % 9},t{i}:0.1{i % 7})"
+        return s
+
+    poly = "(((a:0.1,b:0.2,c:0.1)x:0.05,(d:0.3,e:0.2)y:0.01,((f:0.1,g:0.2)z:0.1)w:0.2,h:0.3,i:0.1)r:0.1,(j:0.2)u:0.3);"
+    rng = np.random.default_rng(5)
+    for nwk, levels in ((balanced(0, 1024) + ";", 9), (cater(300) + ";", 0), (poly, None)):
+        tree = parse_newick(nwk)
+        names = [tree.nodes[i].taxa for i in tree.get_node_ids() if tree.is_leaf(i)]
+        ft = workloads.flatten_fast(tree, names)
+        for model in ("jc69", "gtr_i_g4"):
+            m = workloads.make_model(model)
+            pats = workloads.simulate_patterns(ft, m, 1500, rng)
+            pats[rng.random(pats.shape) < 0.1] = ord("N")
+            case = workloads.Case(tree, ft, m, model, pats, np.ones(1500, np.uint64), names)
+            st = _cases.check_lnl(gpu_lib, case)[2]
+            if levels is not None:
+                assert st["sweep_stack_levels"] == levels
+
+
 def test_literal_invariant_flag(gpu_lib):
     case = workloads.make_case(40, 3000, model="gtr_i_g4", seed=23, ambiguity=0.1)
     a = _cases.check_lnl(gpu_lib, case)[0]
@@ -55,12 +92,14 @@ def test_all_17_codes(gpu_lib):
 
 def test_tiling_and_sharding_invariance(gpu_lib):
     case = workloads.make_case(50, 20_000, model="gtr_g4", seed=25)
-    full = _cases.check_lnl(gpu_lib, case)
-    tiled = _cases.check_lnl(gpu_lib, case, budget=49 * 4 * 4 * 8 * 4096)
+    full = _cases.check_lnl(gpu_lib, case, flags=capi.FLAG_LEVEL_KERNELS)
+    tiled = _cases.check_lnl(gpu_lib, case, budget=49 * 4 * 4 * 8 * 4096, flags=capi.FLAG_LEVEL_KERNELS)
     assert tiled[2]["n_tiles"] >= 4
     assert np.array_equal(full[1], tiled[1])
+    sweep = _cases.check_lnl(gpu_lib, case)
+    assert sweep[2]["sweep_ops"] == 49 and np.max(np.abs(sweep[1] - full[1])) < 1e-10
     split = _cases.check_lnl(gpu_lib, case, devices=[0, 0, 0])  # three virtual ranks on one device
-    assert np.array_equal(full[1], split[1])
+    assert np.array_equal(sweep[1], split[1])
 
 
 @pytest.mark.parametrize("model", ["jc69", "gtr_g4", "gtr_i_g4"])
@@ -164,12 +203,20 @@ def test_full_size_properties_config2(gpu_lib):
         workloads.load_into(ctx, case)
         ctx.simulate_alignment(P, seed=0xA11C)
         tot, per = ctx.log_likelihood(per_pattern=True)
+        assert ctx.stats()["sweep_ops"] == 999
         pats = ctx.get_alignment(0, 1024)
+        whole = ctx.get_alignment()
+    with capi.Context(library=gpu_lib, flags=capi.FLAG_LEVEL_KERNELS) as ctx:  # HBM-resident CLVs, forced 5-way tiling
+        workloads.load_into(ctx, case)
+        ctx.set_alignment(whole)
+        lr0 = np.full(case.ft["n_nodes"], -1, np.int32)
+        lv = np.where(case.ft["child_off"][1:] == case.ft["child_off"][:-1])[0]
+        lr0[lv] = np.arange(len(lv))
+        ctx.set_tree(case.ft["postorder"], case.ft["child_off"], case.ft["children"], case.ft["blen"], lr0, case.ft["root"])
         ctx.set_clv_budget(999 * 4 * 4 * 8 * 20480)
         tot_t, per_t = ctx.log_likelihood(per_pattern=True)
         assert ctx.stats()["n_tiles"] >= 5
-        whole = ctx.get_alignment()
-    assert np.array_equal(per, per_t) and tot == tot_t
+    assert np.max(np.abs(per - per_t)) < 1e-9 and abs(tot - tot_t) < 1e-11 * abs(tot)
     ft = dict(case.ft)
     leaves = np.where(ft["child_off"][1:] == ft["child_off"][:-1])[0]
     lr = np.full(ft["n_nodes"], -1, np.int32)

@@ -27,11 +27,13 @@ def test_lnl_literal_invariant_flag(emu_lib):
 
 def test_tiling_is_result_invariant(emu_lib):
     case = workloads.make_case(9, 1500, model="gtr_g4", seed=4)
-    full = _cases.check_lnl(emu_lib, case)
+    full = _cases.check_lnl(emu_lib, case, flags=capi.FLAG_LEVEL_KERNELS)
     per_site = 8 * 4 * 4 * 8  # slots x cats x states x f64
-    tiled = _cases.check_lnl(emu_lib, case, budget=per_site * 512)
+    tiled = _cases.check_lnl(emu_lib, case, budget=per_site * 512, flags=capi.FLAG_LEVEL_KERNELS)
     assert tiled[2]["n_tiles"] >= 3
     assert np.array_equal(full[1], tiled[1])
+    sweep = _cases.check_lnl(emu_lib, case)  # the fused sweep agrees with the level kernels
+    assert np.max(np.abs(sweep[1] - full[1])) < 1e-11
 
 
 def test_device_sharding_is_result_invariant(emu_lib):
@@ -41,6 +43,59 @@ def test_device_sharding_is_result_invariant(emu_lib):
         many = _cases.check_lnl(emu_lib, case, devices=devs)
         assert np.array_equal(one[1], many[1])
         assert abs(one[0] - many[0]) <= 1e-12 * abs(one[0])
+
+
+@pytest.mark.parametrize("model", ["jc69", "gtr_g4", "gtr_i_g4"])
+def test_level_kernels_flag(emu_lib, model):
+    case = workloads.make_case(12, 300, model=model, seed=11, ambiguity=0.1)
+    _cases.check_lnl(emu_lib, case, flags=capi.FLAG_LEVEL_KERNELS)
+
+
+def test_sweep_many_blocks_per_cta(emu_lib):
+    """More site blocks than (emulated) SMs: every persistent CTA sweeps the tree several times."""
+    case = workloads.make_case(7, 2600, model="gtr_g4", seed=14)  # 256-site blocks -> 11 blocks on 3 CTAs
+    st = _cases.check_lnl(emu_lib, case)[2]
+    assert st["sweep_block_sites"] == 256 and st["sweep_ops"] == 6 and st["clv_launches"] == 1
+
+
+def test_sweep_global_stack_levels(emu_lib, monkeypatch):
+    """A balanced 64-leaf tree needs 5 stack levels; with little shared memory most spill to the global stack."""
+    def balanced(lo, hi):
+        if hi - lo == 1:
+            return f"t{lo}:0.{1 + lo % 7}"
+        mid = (lo + hi) // 2
+        return f"({balanced(lo, mid)},{balanced(mid, hi)}):0.0{1 + (lo + hi) % 9}"
+
+    tree = parse_newick(balanced(0, 64) + ";")
+    rng = np.random.default_rng(3)
+    lo = [f"t{i}" for i in range(64)]
+    ft = workloads.flatten_fast(tree, lo)
+    m = workloads.make_model("gtr_g4")
+    pats = workloads.simulate_patterns(ft, m, 700, rng)
+    case = workloads.Case(tree, ft, m, "gtr_g4", pats, np.ones(700, np.uint64), lo)
+    a = _cases.check_lnl(emu_lib, case)
+    monkeypatch.setenv("PHB_EMU_SMEM_BYTES", str(512 + 2 * 4736 + 2 * 32768))
+    b = _cases.check_lnl(emu_lib, case)
+    assert np.array_equal(a[1], b[1])
+    assert a[2]["sweep_stack_levels"] == 5 and a[2]["sweep_smem_levels"] == 5
+    assert b[2]["sweep_stack_levels"] == 5 and b[2]["sweep_smem_levels"] == 2 and b[2]["sweep_ops"] == 63
+
+
+def test_sweep_schedule_shapes(emu_lib):
+    """Caterpillar (need 0), polytomies and unifurcations through the generic ops."""
+    cat = "(((((a:0.1,b:0.2):0.05,c:0.1):0.02,d:0.3):0.01,e:0.2):0.03,f:0.1);"
+    poly = "(((a:0.1,b:0.2,c:0.1)x:0.05,(d:0.3,e:0.2)y:0.01,((f:0.1,g:0.2)z:0.1)w:0.2,h:0.3,i:0.1)r:0.1,(j:0.2)u:0.3);"
+    rng = np.random.default_rng(5)
+    for nwk in (cat, poly):
+        tree = parse_newick(nwk)
+        names = [tree.nodes[i].taxa for i in tree.get_node_ids() if tree.is_leaf(i)]
+        ft = workloads.flatten_fast(tree, names)
+        for model in ("jc69", "gtr_i_g4"):
+            m = workloads.make_model(model)
+            pats = workloads.simulate_patterns(ft, m, 90, rng)
+            pats[rng.random(pats.shape) < 0.2] = ord("N")
+            case = workloads.Case(tree, ft, m, model, pats, np.ones(90, np.uint64), names)
+            _cases.check_lnl(emu_lib, case)
 
 
 def test_asr_small(emu_lib):
