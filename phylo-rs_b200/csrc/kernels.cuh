@@ -17,12 +17,24 @@ constexpr int MAX_CAT = 32;
 constexpr int CLV_THREADS = 256;          // threads per block in the CLV kernels
 constexpr int SITES_PER_BLOCK = 2 * CLV_THREADS;
 
-// tip code: bits 0..3 = state mask over A,C,G,T; bit 4 = gap ('-': all-ones profile, log-scale 0);
-// 0xFF = byte outside Nucleotide::profile's 17 accepted codes (src/alphabet.rs:44-64).
-constexpr uint8_t CODE_GAP = 0x1F;
+// tip code: bits 0..3 = SLOT of the state mask over A,C,G,T (slot = row of the sweep's tip tables:
+// one-hot masks A,C,G,T are slots 0..3 = the state index, the 11 ambiguity masks follow); bit 4 = gap
+// ('-': all-ones profile, log-scale 0); 0xFF = byte outside Nucleotide::profile's 17 accepted codes
+// (src/alphabet.rs:44-64).
+constexpr uint8_t CODE_GAP = 0x1E;
 constexpr uint8_t CODE_INVALID = 0xFF;
 
-__host__ __device__ inline uint8_t encode_byte(uint8_t c)
+__host__ __device__ __forceinline__ uint32_t mask_to_slot(uint32_t mask)
+{
+    return (uint32_t)((0xEDCBA9837652410Full >> (4u * (mask & 15u))) & 15ull);
+}
+// state mask (bit i = state i allowed) of a tip code
+__host__ __device__ __forceinline__ uint32_t code_mask(uint32_t code)
+{
+    return (uint32_t)((0x0FEDCBA976538421ull >> (4u * (code & 15u))) & 15ull);
+}
+
+__host__ __device__ inline uint8_t encode_mask_byte(uint8_t c)
 {
     switch (c) {
     case 'A': return 1;
@@ -41,9 +53,16 @@ __host__ __device__ inline uint8_t encode_byte(uint8_t c)
     case 'H': return 1 | 2 | 8;
     case 'V': return 1 | 2 | 4;
     case 'N': return 15;
-    case '-': return CODE_GAP;
+    case '-': return 0x1F;
     default: return CODE_INVALID;
     }
+}
+
+__host__ __device__ inline uint8_t encode_byte(uint8_t c)
+{
+    uint8_t m = encode_mask_byte(c);
+    if (m == CODE_INVALID) return CODE_INVALID;
+    return (uint8_t)((m & 16u) | mask_to_slot(m));
 }
 
 __host__ __device__ inline uint8_t decode_code(uint8_t code)
@@ -51,7 +70,7 @@ __host__ __device__ inline uint8_t decode_code(uint8_t code)
     if (code == CODE_GAP) return '-';
     if (code > 15) return '?';
     const char *tab = "?ACMGRSVTWYHKDBN";
-    return (uint8_t)tab[code];
+    return (uint8_t)tab[code_mask(code)];
 }
 
 // Model handed to kernels by value (constant bank).  phb_set_model, include/phylo_b200.h.
@@ -217,7 +236,7 @@ __global__ void tip_constants_kernel(const uint8_t *__restrict__ tips, int64_t P
         uint32_t c[4] = {c4.x, c4.y, c4.z, c4.w};
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            uint32_t m = c[k] & 15u;
+            uint32_t m = code_mask(c[k]);
             inv[k] &= m;
             if (!(c[k] & 16u)) ls[k] += M.ln_tip[__popc(m)];
         }
@@ -289,10 +308,11 @@ __device__ __forceinline__ void contrib_tip(const double (&p)[16], const uint8_t
                                             double2 (&out)[4])
 {
     uchar2 c = *reinterpret_cast<const uchar2 *>(codes);
+    const uint32_t mx = code_mask(c.x), my = code_mask(c.y);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        out[i].x = masked_row(p, i, c.x);
-        out[i].y = masked_row(p, i, c.y);
+        out[i].x = masked_row(p, i, mx);
+        out[i].y = masked_row(p, i, my);
     }
 }
 
@@ -402,7 +422,7 @@ __global__ void clv_from_tip_kernel(double *__restrict__ clv, size_t slot_stride
 {
     int64_t site = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (site >= tile_len) return;
-    uint32_t m = tips[(int64_t)row * P_pad + tile_off + site];
+    uint32_t m = code_mask(tips[(int64_t)row * P_pad + tile_off + site]);
     for (int c = 0; c < n_clv; ++c)
         for (int i = 0; i < 4; ++i)
             clv[(size_t)out_slot * slot_stride + ((size_t)c * 4 + i) * tile_pad + site] = ((m >> i) & 1u) ? 1.0 : 0.0;
@@ -608,7 +628,7 @@ asr_down_level_kernel(const DownOp *__restrict__ ops, int n_ops, const DownChild
                 double up[4];
                 double *self = nullptr;
                 if (ch.is_tip) {
-                    uint32_t m = tips[(int64_t)ch.src * P_pad + tile_off + site];
+                    uint32_t m = code_mask(tips[(int64_t)ch.src * P_pad + tile_off + site]);
 #pragma unroll
                     for (int i = 0; i < 4; ++i) up[i] = ((m >> i) & 1u) ? 1.0 : 0.0;
                 } else {
@@ -703,7 +723,7 @@ __global__ void simulate_kernel(const int32_t *__restrict__ preorder, const int3
         }
         stack[(int64_t)depth[v] * P_pad + site] = (uint8_t)s;
         int r = leaf_row[v];
-        if (r >= 0) tips[(int64_t)r * P_pad + site] = (uint8_t)(1u << s);
+        if (r >= 0) tips[(int64_t)r * P_pad + site] = (uint8_t)s; // one-hot mask of state s has slot s
     }
 }
 

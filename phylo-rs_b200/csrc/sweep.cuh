@@ -64,12 +64,9 @@ struct SweepBlock {
     int32_t pad;
 };
 
-// Tip-table slot of a state mask: one-hot masks (A,C,G,T) first so that their 32-byte rows fall in
-// four different bank groups (conflict-free gathers on unambiguous data).
-__host__ __device__ __forceinline__ uint32_t sw_slot(uint32_t mask)
-{
-    return (uint32_t)((0xEDCBA9837652410Full >> (4u * (mask & 15u))) & 15ull);
-}
+// Tip tables are indexed by the SLOT that the packed tip codes already carry (kernels.cuh:
+// mask_to_slot): one-hot masks (A,C,G,T) are slots 0..3, so their 32-byte rows fall in four different
+// bank groups and gathers on unambiguous data are conflict-free.
 
 // ---- K1s: transition matrices / tip tables straight into the op-ordered stream --------------------
 __global__ void sweep_transition_kernel(const SweepBlock *__restrict__ blocks, int n_blocks,
@@ -106,7 +103,7 @@ __global__ void sweep_transition_kernel(const SweepBlock *__restrict__ blocks, i
         for (int i = 0; i < 16; ++i) out[i] = p[i];
     } else {
         for (uint32_t m = 0; m < 16; ++m) {
-            double *row = out + 4 * sw_slot(m);
+            double *row = out + 4 * mask_to_slot(m);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 double a = (m & 1u) ? p[4 * i] : 0.0;
@@ -221,7 +218,7 @@ __device__ __forceinline__ void sw_load_P(const unsigned char *blk, double (&p)[
 
 __device__ __forceinline__ void sw_load_tip(const unsigned char *tab, uint32_t code, double (&t)[4])
 {
-    const double2 *q = reinterpret_cast<const double2 *>(tab + 32u * sw_slot(code));
+    const double2 *q = reinterpret_cast<const double2 *>(tab + 32u * (code & 15u));
     double2 a = q[0], b = q[1];
     t[0] = a.x; t[1] = a.y; t[2] = b.x; t[3] = b.y;
 }
@@ -268,20 +265,26 @@ sweep_kernel(SweepParams p, ModelDev M)
     if (tid >= prod_tid0) {
         // ===================== producer warp: one lane feeds the ring =====================
         if (tid == prod_tid0) {
-            uint32_t g = 0; // ops issued so far (ring position)
+            int s = 0;
+            uint32_t parity = 1; // a fresh barrier passes a parity-1 wait
+            const int n_stages = p.n_stages, stage_bytes = p.stage_bytes, rec_cap = p.rec_cap, n_ops = p.n_ops;
             for (int64_t b = blockIdx.x; b < p.n_blocks; b += gridDim.x) {
                 const uint8_t *tip_base = p.tips + b * sites_per_block;
-                for (int k = 0; k < p.n_ops; ++k, ++g) {
-                    const int s = (int)(g % (uint32_t)p.n_stages);
-                    const uint32_t use = g / (uint32_t)p.n_stages;
-                    sw_mbar_wait(&empty[s], (use & 1u) ^ 1u);
-                    const SweepDesc d = p.descs[k];
-                    unsigned char *st = ring + (size_t)s * p.stage_bytes;
+                SweepDesc d = p.descs[0];
+                for (int k = 0; k < n_ops; ++k) {
+                    const SweepDesc nd = p.descs[k + 1 < n_ops ? k + 1 : k]; // prefetch the next descriptor
+                    sw_mbar_wait(&empty[s], parity);
+                    unsigned char *st = ring + (size_t)s * stage_bytes;
                     uint32_t bytes = d.rec_bytes + (d.rowA >= 0 ? code_bytes : 0) + (d.rowB >= 0 ? code_bytes : 0);
                     sw_mbar_expect_tx(&full[s], bytes);
                     sw_bulk_g2s(st, p.stream + d.rec_off, d.rec_bytes, &full[s]);
-                    if (d.rowA >= 0) sw_bulk_g2s(st + p.rec_cap, tip_base + (int64_t)d.rowA * p.P_pad, code_bytes, &full[s]);
-                    if (d.rowB >= 0) sw_bulk_g2s(st + p.rec_cap + code_bytes, tip_base + (int64_t)d.rowB * p.P_pad, code_bytes, &full[s]);
+                    if (d.rowA >= 0) sw_bulk_g2s(st + rec_cap, tip_base + (int64_t)d.rowA * p.P_pad, code_bytes, &full[s]);
+                    if (d.rowB >= 0) sw_bulk_g2s(st + rec_cap + code_bytes, tip_base + (int64_t)d.rowB * p.P_pad, code_bytes, &full[s]);
+                    d = nd;
+                    if (++s == n_stages) {
+                        s = 0;
+                        parity ^= 1u;
+                    }
                 }
             }
         }
@@ -294,11 +297,16 @@ sweep_kernel(SweepParams p, ModelDev M)
     const int cc = t / p.Q;           // CLV category of this thread
     const int q = t - cc * p.Q;       // site quad inside the block
     const int lane = tid & 31;
-    const size_t lvl_stride = (size_t)SW_R * 2 * p.n_consumers; // double2 elements per stack level
-    double2 *sstack = reinterpret_cast<double2 *>(stack);
-    double2 *gstack = reinterpret_cast<double2 *>(p.gstack) + (size_t)blockIdx.x * p.g_levels * lvl_stride;
+    const int n_cons = p.n_consumers;
+    const int n_stages = p.n_stages, stage_bytes = p.stage_bytes, n_ops = p.n_ops, smem_levels = p.smem_levels;
+    const int lvl_stride = SW_R * 2 * n_cons; // double2 elements per stack level
+    double2 *const sstack = reinterpret_cast<double2 *>(stack) + t;
+    double2 *const gstack = reinterpret_cast<double2 *>(p.gstack) + (size_t)blockIdx.x * p.g_levels * lvl_stride + t;
+    const int code_off = p.rec_cap + 4 * q;
 
-    uint32_t g = 0;
+    int s = 0;
+    uint32_t parity = 0;
+    const unsigned char *st = ring;
     for (int64_t b = blockIdx.x; b < p.n_blocks; b += gridDim.x) {
         double v[SW_R][4];
         int sc[SW_R];
@@ -308,28 +316,55 @@ sweep_kernel(SweepParams p, ModelDev M)
 #pragma unroll
             for (int i = 0; i < 4; ++i) v[r][i] = 1.0;
         }
-        for (int k = 0; k < p.n_ops; ++k, ++g) {
-            const int s = (int)(g % (uint32_t)p.n_stages);
-            const uint32_t use = g / (uint32_t)p.n_stages;
-            sw_mbar_wait(&full[s], use & 1u);
-            const unsigned char *st = ring + (size_t)s * p.stage_bytes;
-            const SweepHdr h = *reinterpret_cast<const SweepHdr *>(st);
-            const unsigned char *blkA = st + SW_HDR_BYTES + (size_t)cc * (h.szA + h.szB);
-            const unsigned char *blkB = blkA + h.szA;
-            const unsigned char *codesA = st + p.rec_cap + 4 * q;
+        for (int k = 0; k < n_ops; ++k) {
+            sw_mbar_wait(&full[s], parity);
+            const int4 h0 = *reinterpret_cast<const int4 *>(st); // kind, flags, level, szA
+            const int szB = *reinterpret_cast<const int *>(st + 16);
+            const int kind = h0.x, flags = h0.y, level = h0.z, szA = h0.w;
+            const unsigned char *blkA = st + SW_HDR_BYTES + cc * (szA + szB);
+            const unsigned char *blkB = blkA + szA;
+            const unsigned char *codesA = st + code_off;
             const unsigned char *codesB = codesA + code_bytes;
-            double2 *slot = nullptr;
-            if ((h.flags & SW_FLAG_PUSH) || h.kind == SW_II || h.kind == SW_MULPOP)
-                slot = (h.level < p.smem_levels ? sstack + (size_t)h.level * lvl_stride
-                                                : gstack + (size_t)(h.level - p.smem_levels) * lvl_stride) + t;
-            if ((h.flags & SW_FLAG_PUSH) && active) {
+            if (flags & SW_FLAG_PUSH) {
+                if (level < smem_levels) {
+                    double2 *slot = sstack + level * lvl_stride;
+                    if (active) {
 #pragma unroll
-                for (int r = 0; r < SW_R; ++r) {
-                    slot[(size_t)(2 * r) * p.n_consumers] = make_double2(v[r][0], v[r][1]);
-                    slot[(size_t)(2 * r + 1) * p.n_consumers] = make_double2(v[r][2], v[r][3]);
+                        for (int r = 0; r < SW_R; ++r) {
+                            slot[(2 * r) * n_cons] = make_double2(v[r][0], v[r][1]);
+                            slot[(2 * r + 1) * n_cons] = make_double2(v[r][2], v[r][3]);
+                        }
+                    }
+                } else {
+                    double2 *slot = gstack + (size_t)(level - smem_levels) * lvl_stride;
+                    if (active) {
+#pragma unroll
+                        for (int r = 0; r < SW_R; ++r) {
+                            slot[(2 * r) * n_cons] = make_double2(v[r][0], v[r][1]);
+                            slot[(2 * r + 1) * n_cons] = make_double2(v[r][2], v[r][3]);
+                        }
+                    }
                 }
             }
-            switch (h.kind) {
+            double x[SW_R][4]; // popped operand (II / MULPOP)
+            if (kind == SW_II || kind == SW_MULPOP) {
+                if (level < smem_levels) {
+                    const double2 *slot = sstack + level * lvl_stride;
+#pragma unroll
+                    for (int r = 0; r < SW_R; ++r) {
+                        const double2 a = slot[(2 * r) * n_cons], c = slot[(2 * r + 1) * n_cons];
+                        x[r][0] = a.x; x[r][1] = a.y; x[r][2] = c.x; x[r][3] = c.y;
+                    }
+                } else {
+                    const double2 *slot = gstack + (size_t)(level - smem_levels) * lvl_stride;
+#pragma unroll
+                    for (int r = 0; r < SW_R; ++r) {
+                        const double2 a = slot[(2 * r) * n_cons], c = slot[(2 * r + 1) * n_cons];
+                        x[r][0] = a.x; x[r][1] = a.y; x[r][2] = c.x; x[r][3] = c.y;
+                    }
+                }
+            }
+            switch (kind) {
             case SW_TT: {
                 const uchar4 ca = *reinterpret_cast<const uchar4 *>(codesA);
                 const uchar4 cb = *reinterpret_cast<const uchar4 *>(codesB);
@@ -352,8 +387,8 @@ sweep_kernel(SweepParams p, ModelDev M)
 #pragma unroll
                 for (int r = 0; r < SW_R; ++r) {
                     double y[4], ta[4];
-                    sw_matvec(P, v[r], y);
                     sw_load_tip(blkA, a4[r], ta);
+                    sw_matvec(P, v[r], y);
 #pragma unroll
                     for (int i = 0; i < 4; ++i) v[r][i] = ta[i] * y[i];
                 }
@@ -361,13 +396,13 @@ sweep_kernel(SweepParams p, ModelDev M)
             }
             case SW_II: {
                 double P[16];
-                double ya[SW_R][4];
                 sw_load_P(blkA, P);
 #pragma unroll
                 for (int r = 0; r < SW_R; ++r) {
-                    const double2 x01 = slot[(size_t)(2 * r) * p.n_consumers], x23 = slot[(size_t)(2 * r + 1) * p.n_consumers];
-                    const double x[4] = {x01.x, x01.y, x23.x, x23.y};
-                    sw_matvec(P, x, ya[r]);
+                    double y[4];
+                    sw_matvec(P, x[r], y);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) x[r][i] = y[i];
                 }
                 sw_load_P(blkB, P);
 #pragma unroll
@@ -375,7 +410,7 @@ sweep_kernel(SweepParams p, ModelDev M)
                     double y[4];
                     sw_matvec(P, v[r], y);
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) v[r][i] = ya[r][i] * y[i];
+                    for (int i = 0; i < 4; ++i) v[r][i] = x[r][i] * y[i];
                 }
                 break;
             }
@@ -400,28 +435,44 @@ sweep_kernel(SweepParams p, ModelDev M)
                     double ta[4];
                     sw_load_tip(blkA, a4[r], ta);
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) v[r][i] = (h.kind == SW_LOADTIP) ? ta[i] : v[r][i] * ta[i];
+                    for (int i = 0; i < 4; ++i) v[r][i] = (kind == SW_LOADTIP) ? ta[i] : v[r][i] * ta[i];
                 }
                 break;
             }
             case SW_MULPOP: {
 #pragma unroll
-                for (int r = 0; r < SW_R; ++r) {
-                    const double2 x01 = slot[(size_t)(2 * r) * p.n_consumers], x23 = slot[(size_t)(2 * r + 1) * p.n_consumers];
-                    v[r][0] *= x01.x; v[r][1] *= x01.y; v[r][2] *= x23.x; v[r][3] *= x23.y;
-                }
+                for (int r = 0; r < SW_R; ++r)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) v[r][i] *= x[r][i];
                 break;
             }
             default:
                 if (lane == 0) atomicOr(p.error_flag, 1u);
                 break;
             }
-            if (h.flags & SW_FLAG_RESCALE) {
+            if (flags & SW_FLAG_RESCALE) {
+                // one test for the four sites: the smallest per-site maximum decides
+                int hmin = 0x7fffffff;
+                int hs[SW_R];
 #pragma unroll
-                for (int r = 0; r < SW_R; ++r) sw_rescale(v[r], sc[r]);
+                for (int r = 0; r < SW_R; ++r) {
+                    hs[r] = max(max(__double2hiint(v[r][0]), __double2hiint(v[r][1])),
+                                max(__double2hiint(v[r][2]), __double2hiint(v[r][3])));
+                    hmin = min(hmin, hs[r]);
+                }
+                if (hmin < ((1023 - 256) << 20)) {
+#pragma unroll
+                    for (int r = 0; r < SW_R; ++r) sw_rescale(v[r], sc[r]);
+                }
             }
             __syncwarp();
             if (lane == 0) sw_mbar_arrive(&empty[s]);
+            st += stage_bytes;
+            if (++s == n_stages) {
+                s = 0;
+                st = ring;
+                parity ^= 1u;
+            }
         }
 
         // ---- root: per-category log-likelihoods, category mix, weights, block reduction ----
