@@ -192,7 +192,9 @@ def run_gpu(args, rank, world, local_rank):
     model = synthetic.gtr_model(alpha=0.5, k=4, p_inv=0.2)
     n_internal = N_TAXA - 1
     lo, cnt = shard(N_SITES, world, rank)
-    ctx = capi.Context(devices=[local_rank], flags=capi.FLAG_TIMING)
+    level_path = os.environ.get("PHB_BENCH_LEVELS") == "1"  # the HBM-resident level kernels, for comparison
+    ctx = capi.Context(devices=[local_rank], flags=capi.FLAG_TIMING | (capi.FLAG_LEVEL_KERNELS if level_path else 0))
+    fp64_peak = ctx.measure_fp64_tflops()
     synthetic.load_into(ctx, tree, model)
     ctx.simulate_alignment(cnt, global_offset=lo, seed=ALN_SEED)
     red = torch.zeros(1, dtype=torch.float64, device="cuda")
@@ -263,11 +265,16 @@ def run_gpu(args, rank, world, local_rank):
         bytes_launch = st["algorithmic_bytes"] / max(st["clv_launches"], 1)
         achieved = bytes_launch / (kern_ms * 1e-3) / 1e9 if kern_ms > 0 else None
         traffic = None
-        try:
+        kernel = "clv_update_level_kernel" if level_path else "sweep_kernel"
+        try:  # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu capture
             with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-                traffic = json.load(f).get("dram_bytes_per_launch")
+                tj = json.load(f).get(kernel, {})
+            if tj.get("patterns"):
+                traffic = tj["dram_bytes_per_launch"] * (cnt / tj["patterns"]) * (N_TAXA / tj["taxa"])
         except Exception:
             pass
+        nominal_flops = 68.0 * 4 * updates  # 68*K flop per binary update, K = 4 CLV categories
+        fp64_tflops = nominal_flops / (st["ms_clv"] * 1e-3) / 1e12 * (cnt / N_SITES)
         line = {
             "metric": METRIC, "value": updates / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
@@ -275,13 +282,22 @@ def run_gpu(args, rank, world, local_rank):
             "config": {"workload": WORKLOAD, "model": "GTR+I+G4 (pi=.3,.2,.2,.3; rates 1,2.5,1,1,2.5,1; alpha=0.5, k=4; p_inv=0.2)",
                        "patterns_per_gpu": cnt, "sharding": f"site patterns over {world} rank(s); scalar all-reduce",
                        "l2": "inputs larger than L2 (tip codes + CLV tiles >> 126 MB)",
-                       "tiles_per_step": st["n_tiles"], "tile_patterns": st["tile_patterns"], "levels": st["n_levels"]},
+                       "path": "level kernels" if level_path else "fused sweep",
+                       "tiles_per_step": st["n_tiles"], "tile_patterns": st["tile_patterns"], "levels": st["n_levels"],
+                       "sweep": {k: st[k] for k in st if k.startswith("sweep_")}},
             "lnl": lnl, "lnl_e2e": lnl_e2e, "wall_ms_per_step": wall_ms / args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
-                         "kernel": "clv_update_level_kernel", "launches_per_step": st["clv_launches"],
+                         "kernel": kernel, "launches_per_step": st["clv_launches"],
                          "avg_launch_ms": kern_ms, "algorithmic_bytes_per_launch": bytes_launch,
-                         "whole_step_frac": st["algorithmic_bytes"] / (ms_step * 1e-3) / 1e9 / peak},
+                         "whole_step_frac": st["algorithmic_bytes"] / (ms_step * 1e-3) / 1e9 / peak,
+                         "note": ("level-batched kernels: every CLV makes one HBM round trip" if level_path else
+                                  "fused sweep keeps CLVs in registers/shared memory, so the algorithmic HBM bytes of "
+                                  "SURVEY 8d are NOT moved (traffic = tip codes + the P(t) stream): frac > 1 means the "
+                                  "HBM roofline of the per-node formulation is beaten, the binding resources are the "
+                                  "FP64 pipe and shared-memory bandwidth (see fp64)"),
+                         "fp64": {"nominal_flop_per_update": 272, "achieved_tflops": fp64_tflops,
+                                  "peak_tflops_measured": fp64_peak, "frac": fp64_tflops / fp64_peak if fp64_peak else None}},
             "e2e": {"value": updates / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(cnt) * n_rows + 8 * 60 + 8 * 4 * tree["n_nodes"] + 4 * 4 * tree["n_nodes"],
                     "d2h_bytes_per_step": 8 + 4 * n_rows, "steps": e2e_steps,
