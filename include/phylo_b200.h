@@ -122,6 +122,12 @@ int32_t phb_log_likelihood(phb_ctx *ctx, double *total, double *per_pattern);
  * The shim expands patterns to sites through CompressedColumns.site_to_pattern (:391-398). */
 int32_t phb_marginal_asr(phb_ctx *ctx, uint8_t *states, double *posteriors, double *total);
 
+/* GtrModel::category_transition (src/models/gtr.rs:61-64) -> RateMatrix::transition
+ * (src/models/rate_matrix.rs:113-135), evaluated by the same device kernel the engines use:
+ *   out[(k * n_cat + c) * 16 + 4 * i + j] = P(rates[c] * t[k])[i][j]      (row-major 4x4)
+ * The exact identity when rates[c] * t[k] == 0.0.  Requires set_model. */
+int32_t phb_transition_matrices(phb_ctx *ctx, int32_t n_t, const double *t, double *out);
+
 /* Per-pattern log-likelihoods of the most recent evaluation (either entry point). */
 int32_t phb_get_per_pattern(phb_ctx *ctx, double *per_pattern);
 

@@ -216,6 +216,34 @@ class RefModel:
         return RefModel(pi, _symmetric_matrix(1.0, kappa1, 1.0, 1.0, kappa2, 1.0), True)
 
     @staticmethod
+    def k81(a, b, c):
+        """src/models/gtr.rs:207-216: AC=b, AG=a, AT=c, CG=c, CT=a, GT=b."""
+        for nm, v in (("a", a), ("b", b), ("c", c)):
+            _validate_positive(v, nm)
+        return RefModel([0.25] * 4, _symmetric_matrix(b, a, c, c, a, b), True)
+
+    @staticmethod
+    def tim(pi, kappa1, kappa2, a, b):
+        """src/models/gtr.rs:221-230: AC=a, AG=kappa1, AT=b, CG=b, CT=kappa2, GT=a."""
+        for nm, v in (("kappa1", kappa1), ("kappa2", kappa2), ("a", a), ("b", b)):
+            _validate_positive(v, nm)
+        return RefModel(pi, _symmetric_matrix(a, kappa1, b, b, kappa2, a), True)
+
+    @staticmethod
+    def tvm(pi, kappa, a, b, c):
+        """src/models/gtr.rs:234-244: GT is the geometric mean (a*b*c)^(1/3)."""
+        for nm, v in (("kappa", kappa), ("a", a), ("b", b), ("c", c)):
+            _validate_positive(v, nm)
+        return RefModel(pi, _symmetric_matrix(a, kappa, b, c, kappa, float(np.cbrt(a * b * c))), True)
+
+    @staticmethod
+    def sym(rates):
+        """src/models/gtr.rs:248-259."""
+        for nm, r in zip(("ac", "ag", "at", "cg", "ct", "gt"), rates):
+            _validate_positive(r, nm)
+        return RefModel([0.25] * 4, _symmetric_matrix(*rates), True)
+
+    @staticmethod
     def gtr(pi, rates):
         for nm, r in zip(("ac", "ag", "at", "cg", "ct", "gt"), rates):
             _validate_positive(r, nm)

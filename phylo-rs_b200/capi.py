@@ -33,7 +33,7 @@ EXPORTS = [
     "phb_ctx_create", "phb_ctx_destroy", "phb_set_clv_budget", "phb_set_alignment", "phb_set_model",
     "phb_set_tree", "phb_log_likelihood", "phb_marginal_asr", "phb_get_per_pattern", "phb_score_nni",
     "phb_simulate_alignment", "phb_get_alignment", "phb_get_stats", "phb_measure_fp64_tflops",
-    "phb_timer_start", "phb_timer_stop",
+    "phb_timer_start", "phb_timer_stop", "phb_transition_matrices",
     "phb_last_error", "phb_version",
 ]
 
@@ -88,6 +88,7 @@ class Library:
         L.phb_get_alignment.argtypes = [vp, vp, C.c_int32, C.c_int64, C.c_int64]
         L.phb_get_stats.argtypes = [vp, C.POINTER(Stats)]
         L.phb_measure_fp64_tflops.argtypes = [vp, dp]
+        L.phb_transition_matrices.argtypes = [vp, C.c_int32, dp, dp]
         L.phb_timer_start.argtypes = [vp]
         L.phb_timer_stop.argtypes = [vp, dp]
         L.phb_last_error.argtypes = [vp]
@@ -224,6 +225,13 @@ class Context:
         if P == 0:
             return tot.value, states[:, :0], (None if post is None else post[:, :0])
         return tot.value, states, post
+
+    def transition_matrices(self, t, n_cat):
+        """P(rate_c * t_k) for every t_k and model category: [len(t)][n_cat][4][4] (device-evaluated)."""
+        t = np.ascontiguousarray(np.atleast_1d(t), np.float64)
+        out = np.zeros((len(t), n_cat, 4, 4), np.float64)
+        self._check(self.lib.L.phb_transition_matrices(self._h, len(t), _dp(t), _dp(out)))
+        return out
 
     def per_pattern(self):
         pp = np.zeros(max(self.n_patterns, 1), np.float64)

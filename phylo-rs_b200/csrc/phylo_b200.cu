@@ -1257,6 +1257,26 @@ int32_t phb_timer_stop(phb_ctx *ctx, double *ms)
     return PHB_OK;
 }
 
+int32_t phb_transition_matrices(phb_ctx *ctx, int32_t n_t, const double *t, double *out)
+{
+    if (!ctx || n_t < 0 || (n_t > 0 && (!t || !out))) return ctx ? ctx->fail(PHB_ERR_INVALID_ARGUMENT, "transition_matrices: null/negative argument") : PHB_ERR_INVALID_ARGUMENT;
+    if (!ctx->have_model) return ctx->fail(PHB_ERR_STATE, "set_model must precede transition_matrices");
+    if (n_t == 0) return PHB_OK;
+    Device &d = ctx->devs[0];
+    const ModelDev &M = ctx->model_lit;
+    CU(cudaSetDevice(d.ordinal));
+    const size_t n_out = (size_t)n_t * M.n_cat * 16;
+    CU(d.scratch.ensure(sizeof(double) * ((size_t)n_t + n_out)));
+    double *d_t = d.scratch.as<double>(), *d_P = d_t + n_t;
+    CU(cudaMemcpyAsync(d_t, t, sizeof(double) * n_t, cudaMemcpyHostToDevice, d.stream));
+    int nthreads = n_t * M.n_cat;
+    PHB_LAUNCH(transition_kernel, dim3((nthreads + 127) / 128), dim3(128), d.stream, d_t, n_t, M, d_P);
+    CHECK_LAUNCH();
+    CU(cudaMemcpyAsync(out, d_P, sizeof(double) * n_out, cudaMemcpyDeviceToHost, d.stream));
+    CU(cudaStreamSynchronize(d.stream));
+    return PHB_OK;
+}
+
 int32_t phb_measure_fp64_tflops(phb_ctx *ctx, double *tflops)
 {
     if (!ctx || !tflops) return PHB_ERR_INVALID_ARGUMENT;
