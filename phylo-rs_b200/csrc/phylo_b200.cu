@@ -212,7 +212,7 @@ struct Device {
     DevBuf tips, mult, leaf_ls, inv_mask, per_pattern, row_invalid, Pmat, blen, clv, scale, cat_ll,
         partials, total, ops, gops, gkids, dops, dkids, leaf_rows, states, posteriors, staging,
         sim_pre, sim_parent, sim_depth, sim_leafrow, sim_stack, scratch, sw_descs, sw_blocks, sw_stream, sw_gstack,
-        sw_err;
+        sw_err, sw_ops;
     bool sweep_uploaded = false;
     int sm_count = 0;
     size_t smem_optin = 0;
@@ -543,7 +543,8 @@ int ensure_sweep(phb_ctx *ctx, const ModelDev &M)
         CU(d.sw_err.ensure(sizeof(unsigned int)));
         CU(cudaMemcpyAsync(d.sw_descs.p, S.descs.data(), sizeof(SweepDesc) * S.descs.size(), cudaMemcpyHostToDevice, d.stream));
         CU(cudaMemcpyAsync(d.sw_blocks.p, S.blocks.data(), sizeof(SweepBlock) * S.blocks.size(), cudaMemcpyHostToDevice, d.stream));
-        CU(cudaMemcpyAsync(d.sw_stream.p, S.headers.data(), S.stream_bytes, cudaMemcpyHostToDevice, d.stream));
+        CU(d.sw_ops.ensure(sizeof(SweepOp) * S.ops.size()));
+        CU(cudaMemcpyAsync(d.sw_ops.p, S.ops.data(), sizeof(SweepOp) * S.ops.size(), cudaMemcpyHostToDevice, d.stream));
         CU(cudaMemsetAsync(d.sw_err.p, 0, sizeof(unsigned int), d.stream));
         d.sweep_uploaded = true;
     }
@@ -570,6 +571,7 @@ int run_sweep(phb_ctx *ctx, Device &d, const ModelDev &M)
     }
     SweepParams sp;
     memset(&sp, 0, sizeof sp);
+    sp.ops = d.sw_ops.as<SweepOp>();
     sp.descs = d.sw_descs.as<SweepDesc>();
     sp.stream = d.sw_stream.as<unsigned char>();
     sp.n_ops = S.n_ops;
@@ -815,7 +817,7 @@ void phb_ctx_destroy(phb_ctx *ctx)
                           &d.clv, &d.scale, &d.cat_ll, &d.partials, &d.total, &d.ops, &d.gops, &d.gkids, &d.dops,
                           &d.dkids, &d.leaf_rows, &d.states, &d.posteriors, &d.staging, &d.sim_pre, &d.sim_parent,
                           &d.sim_depth, &d.sim_leafrow, &d.sim_stack, &d.scratch, &d.sw_descs, &d.sw_blocks,
-                          &d.sw_stream, &d.sw_gstack, &d.sw_err};
+                          &d.sw_stream, &d.sw_gstack, &d.sw_err, &d.sw_ops};
         for (DevBuf *b : bufs) b->release();
         for (auto &ep : d.ev_pool) {
             cudaEventDestroy(ep.a);

@@ -37,16 +37,18 @@ enum SweepKind : int32_t {
 };
 constexpr int SW_FLAG_PUSH = 1;    // push cur to `level` before executing (TT / LOADTIP only)
 constexpr int SW_FLAG_RESCALE = 2; // node complete: run the underflow check
+constexpr int SW_FLAG_U = 4;       // TT / TI: operate on the second register accumulator `u` (cur untouched)
+constexpr int SW_FLAG_XU = 8;      // II: the pending operand is `u`, not a stack level
 
 constexpr int SW_P_BYTES = 128;   // 4x4 f64 row-major
 constexpr int SW_TAB_BYTES = 512; // 16 masks x 4 f64, slot order SW_PERM
-constexpr int SW_HDR_BYTES = 32;
 constexpr int SW_BAR_BYTES = 512; // mbarrier area at the start of dynamic shared memory
 
-// Header at the start of every stream record (lands in shared memory with the record).
-struct SweepHdr {
-    int32_t kind, flags, level, szA; // szA/szB: per-category bytes of operand block A / B
-    int32_t szB, pad0, pad1, pad2;
+// Per-op header, one table for the whole tree in global memory (identical for every site block, so the
+// consumers prefetch it two ops ahead into registers: nothing on the op's critical path waits for it).
+//   w0 = kind | flags << 8 | level << 16      w1 = szA | szB << 16   (per-category bytes of operand A / B)
+struct SweepOp {
+    uint32_t w0, w1;
 };
 // Producer-side descriptor (global memory): where the record is and which tip rows it needs.
 struct SweepDesc {
@@ -176,6 +178,7 @@ constexpr int SW_R = 4;              // site patterns per thread
 constexpr int SW_MAX_CONSUMERS = 256; // consumer threads per CTA (+ one producer warp)
 
 struct SweepParams {
+    const SweepOp *ops;
     const SweepDesc *descs;
     const unsigned char *stream;
     int n_ops;
@@ -307,65 +310,43 @@ sweep_kernel(SweepParams p, ModelDev M)
     int s = 0;
     uint32_t parity = 0;
     const unsigned char *st = ring;
+    const uint2 *const optab = reinterpret_cast<const uint2 *>(p.ops);
     for (int64_t b = blockIdx.x; b < p.n_blocks; b += gridDim.x) {
-        double v[SW_R][4];
+        double v[SW_R][4]; // running result
+        double u[SW_R][4]; // second accumulator: a chain-shaped pending sibling is evaluated here (SW_FLAG_U)
         int sc[SW_R];
 #pragma unroll
         for (int r = 0; r < SW_R; ++r) {
             sc[r] = 0;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) v[r][i] = 1.0;
+            for (int i = 0; i < 4; ++i) v[r][i] = u[r][i] = 1.0;
         }
+        // op headers run two ops ahead of the arithmetic (same table for every block)
+        uint2 hq0 = __ldg(optab), hq1 = __ldg(optab + (n_ops > 1 ? 1 : 0));
         for (int k = 0; k < n_ops; ++k) {
+            const uint2 h = hq0;
+            hq0 = hq1;
+            hq1 = __ldg(optab + (k + 2 < n_ops ? k + 2 : n_ops - 1));
+            const int kind = h.x & 0xff, flags = (h.x >> 8) & 0xff, level = (int)(h.x >> 16);
+            const int szA = h.y & 0xffff, szB = (int)(h.y >> 16);
             sw_mbar_wait(&full[s], parity);
-            const int4 h0 = *reinterpret_cast<const int4 *>(st); // kind, flags, level, szA
-            const int szB = *reinterpret_cast<const int *>(st + 16);
-            const int kind = h0.x, flags = h0.y, level = h0.z, szA = h0.w;
-            const unsigned char *blkA = st + SW_HDR_BYTES + cc * (szA + szB);
+            const unsigned char *blkA = st + cc * (szA + szB);
             const unsigned char *blkB = blkA + szA;
             const unsigned char *codesA = st + code_off;
             const unsigned char *codesB = codesA + code_bytes;
             if (flags & SW_FLAG_PUSH) {
-                if (level < smem_levels) {
-                    double2 *slot = sstack + level * lvl_stride;
-                    if (active) {
+                double2 *slot = level < smem_levels ? sstack + level * lvl_stride
+                                                    : gstack + (size_t)(level - smem_levels) * lvl_stride;
+                if (active) {
 #pragma unroll
-                        for (int r = 0; r < SW_R; ++r) {
-                            slot[(2 * r) * n_cons] = make_double2(v[r][0], v[r][1]);
-                            slot[(2 * r + 1) * n_cons] = make_double2(v[r][2], v[r][3]);
-                        }
-                    }
-                } else {
-                    double2 *slot = gstack + (size_t)(level - smem_levels) * lvl_stride;
-                    if (active) {
-#pragma unroll
-                        for (int r = 0; r < SW_R; ++r) {
-                            slot[(2 * r) * n_cons] = make_double2(v[r][0], v[r][1]);
-                            slot[(2 * r + 1) * n_cons] = make_double2(v[r][2], v[r][3]);
-                        }
+                    for (int r = 0; r < SW_R; ++r) {
+                        slot[(2 * r) * n_cons] = make_double2(v[r][0], v[r][1]);
+                        slot[(2 * r + 1) * n_cons] = make_double2(v[r][2], v[r][3]);
                     }
                 }
             }
-            double x[SW_R][4]; // popped operand (II / MULPOP)
-            if (kind == SW_II || kind == SW_MULPOP) {
-                if (level < smem_levels) {
-                    const double2 *slot = sstack + level * lvl_stride;
-#pragma unroll
-                    for (int r = 0; r < SW_R; ++r) {
-                        const double2 a = slot[(2 * r) * n_cons], c = slot[(2 * r + 1) * n_cons];
-                        x[r][0] = a.x; x[r][1] = a.y; x[r][2] = c.x; x[r][3] = c.y;
-                    }
-                } else {
-                    const double2 *slot = gstack + (size_t)(level - smem_levels) * lvl_stride;
-#pragma unroll
-                    for (int r = 0; r < SW_R; ++r) {
-                        const double2 a = slot[(2 * r) * n_cons], c = slot[(2 * r + 1) * n_cons];
-                        x[r][0] = a.x; x[r][1] = a.y; x[r][2] = c.x; x[r][3] = c.y;
-                    }
-                }
-            }
-            switch (kind) {
-            case SW_TT: {
+            // ---- the op bodies, written once over the accumulator they update ----
+            auto op_tt = [&](double (&acc)[SW_R][4]) {
                 const uchar4 ca = *reinterpret_cast<const uchar4 *>(codesA);
                 const uchar4 cb = *reinterpret_cast<const uchar4 *>(codesB);
                 const uint32_t a4[4] = {ca.x, ca.y, ca.z, ca.w}, b4[4] = {cb.x, cb.y, cb.z, cb.w};
@@ -375,11 +356,10 @@ sweep_kernel(SweepParams p, ModelDev M)
                     sw_load_tip(blkA, a4[r], ta);
                     sw_load_tip(blkB, b4[r], tb);
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) v[r][i] = ta[i] * tb[i];
+                    for (int i = 0; i < 4; ++i) acc[r][i] = ta[i] * tb[i];
                 }
-                break;
-            }
-            case SW_TI: {
+            };
+            auto op_ti = [&](double (&acc)[SW_R][4]) {
                 const uchar4 ca = *reinterpret_cast<const uchar4 *>(codesA);
                 const uint32_t a4[4] = {ca.x, ca.y, ca.z, ca.w};
                 double P[16];
@@ -388,32 +368,64 @@ sweep_kernel(SweepParams p, ModelDev M)
                 for (int r = 0; r < SW_R; ++r) {
                     double y[4], ta[4];
                     sw_load_tip(blkA, a4[r], ta);
-                    sw_matvec(P, v[r], y);
+                    sw_matvec(P, acc[r], y);
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) v[r][i] = ta[i] * y[i];
+                    for (int i = 0; i < 4; ++i) acc[r][i] = ta[i] * y[i];
                 }
-                break;
-            }
-            case SW_II: {
-                double P[16];
+            };
+            // v = (P_A x) * (P_B v)
+            auto op_ii = [&](const double (&x)[SW_R][4]) {
+                double P[16], xa[SW_R][4];
                 sw_load_P(blkA, P);
 #pragma unroll
-                for (int r = 0; r < SW_R; ++r) {
-                    double y[4];
-                    sw_matvec(P, x[r], y);
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) x[r][i] = y[i];
-                }
+                for (int r = 0; r < SW_R; ++r) sw_matvec(P, x[r], xa[r]);
                 sw_load_P(blkB, P);
 #pragma unroll
                 for (int r = 0; r < SW_R; ++r) {
                     double y[4];
                     sw_matvec(P, v[r], y);
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) v[r][i] = x[r][i] * y[i];
+                    for (int i = 0; i < 4; ++i) v[r][i] = xa[r][i] * y[i];
+                }
+            };
+            auto pop = [&](double (&x)[SW_R][4]) {
+                const double2 *slot = level < smem_levels ? sstack + level * lvl_stride
+                                                          : gstack + (size_t)(level - smem_levels) * lvl_stride;
+#pragma unroll
+                for (int r = 0; r < SW_R; ++r) {
+                    const double2 a = slot[(2 * r) * n_cons], c = slot[(2 * r + 1) * n_cons];
+                    x[r][0] = a.x; x[r][1] = a.y; x[r][2] = c.x; x[r][3] = c.y;
+                }
+            };
+            // underflow guard: one test for the four sites, the smallest per-site maximum decides
+            auto guard = [&](double (&acc)[SW_R][4]) {
+                int hmin = 0x7fffffff;
+#pragma unroll
+                for (int r = 0; r < SW_R; ++r)
+                    hmin = min(hmin, max(max(__double2hiint(acc[r][0]), __double2hiint(acc[r][1])),
+                                         max(__double2hiint(acc[r][2]), __double2hiint(acc[r][3]))));
+                if (hmin < ((1023 - 256) << 20)) {
+#pragma unroll
+                    for (int r = 0; r < SW_R; ++r) sw_rescale(acc[r], sc[r]);
+                }
+            };
+            switch (kind) {
+            case SW_TT:
+                if (flags & SW_FLAG_U) op_tt(u);
+                else op_tt(v);
+                break;
+            case SW_TI:
+                if (flags & SW_FLAG_U) op_ti(u);
+                else op_ti(v);
+                break;
+            case SW_II:
+                if (flags & SW_FLAG_XU) op_ii(u);
+                else {
+                    double x[SW_R][4];
+                    pop(x);
+                    op_ii(x);
                 }
                 break;
-            }
             case SW_APPLY: {
                 double P[16];
                 sw_load_P(blkA, P);
@@ -440,6 +452,8 @@ sweep_kernel(SweepParams p, ModelDev M)
                 break;
             }
             case SW_MULPOP: {
+                double x[SW_R][4];
+                pop(x);
 #pragma unroll
                 for (int r = 0; r < SW_R; ++r)
 #pragma unroll
@@ -451,19 +465,8 @@ sweep_kernel(SweepParams p, ModelDev M)
                 break;
             }
             if (flags & SW_FLAG_RESCALE) {
-                // one test for the four sites: the smallest per-site maximum decides
-                int hmin = 0x7fffffff;
-                int hs[SW_R];
-#pragma unroll
-                for (int r = 0; r < SW_R; ++r) {
-                    hs[r] = max(max(__double2hiint(v[r][0]), __double2hiint(v[r][1])),
-                                max(__double2hiint(v[r][2]), __double2hiint(v[r][3])));
-                    hmin = min(hmin, hs[r]);
-                }
-                if (hmin < ((1023 - 256) << 20)) {
-#pragma unroll
-                    for (int r = 0; r < SW_R; ++r) sw_rescale(v[r], sc[r]);
-                }
+                if (flags & SW_FLAG_U) guard(u);
+                else guard(v);
             }
             __syncwarp();
             if (lane == 0) sw_mbar_arrive(&empty[s]);

@@ -27,8 +27,9 @@ struct SweepSched {
     size_t stream_bytes = 0;
     std::vector<SweepDesc> descs;
     std::vector<SweepBlock> blocks;
-    std::vector<unsigned char> headers; // stream image holding the record headers (blocks zero)
+    std::vector<SweepOp> ops;           // per-op header table (global memory, prefetched by the consumers)
     int count_kind[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int n_push = 0, n_reg_sibling = 0;  // pending siblings parked in the stack / kept in the second accumulator
 
     // child_off/children: CSR child lists; leaf_row: alignment row per leaf; root must be internal.
     void build(int n, int root, const std::vector<int> &child_off, const std::vector<int> &children,
@@ -68,20 +69,34 @@ struct SweepSched {
             need[v] = nd;
         }
         n_levels = need[root];
+        // chain[v]: the subtree of v is a chain of binary TT / TI updates (no internal x internal node, no
+        // polytomy): it runs entirely in ONE accumulator, so as the pending-side sibling of a binary node it
+        // can be evaluated in the second register accumulator `u` with no stack traffic at all.
+        std::vector<char> chain(n, 0);
+        for (int v : order) {
+            if (is_leaf(v)) continue;
+            const size_t ni = ints[v].size(), nt = tips[v].size();
+            chain[v] = ni + nt == 2 && (ni == 0 || (ni == 1 && chain[ints[v][0]]));
+        }
 
-        struct Rec { SweepHdr h; int edgeA, edgeB, rowA, rowB; bool tabA, tabB; };
+        struct Hdr { int kind, flags, level, szA, szB; };
+        struct Rec { Hdr h; int edgeA, edgeB, rowA, rowB; bool tabA, tabB; };
         std::vector<Rec> recs;
         int pending_push = -1;
+        bool u_mode = false;
+        n_push = n_reg_sibling = 0;
         auto emit = [&](int kind, int level, int edgeA, bool tabA, int edgeB, bool tabB) {
             Rec r;
             memset(&r, 0, sizeof r);
             r.h.kind = kind;
             r.h.level = level;
+            if (u_mode) r.h.flags |= SW_FLAG_U;
             if (kind == SW_TT || kind == SW_LOADTIP) {
                 if (pending_push >= 0) {
                     r.h.flags |= SW_FLAG_PUSH;
                     r.h.level = pending_push;
                     pending_push = -1;
+                    ++n_push;
                 }
             }
             r.edgeA = edgeA; r.edgeB = edgeB; r.tabA = tabA; r.tabB = tabB;
@@ -108,14 +123,27 @@ struct SweepSched {
                 }
             }
             if (f.j < (int)iv.size()) {
-                if (f.j >= 1) pending_push = need[iv[f.j]];
+                if (f.j >= 1) {
+                    if (binary && chain[iv[f.j]] && !u_mode) {
+                        u_mode = true; // the waiting sibling stays in v; this subtree runs in u
+                        ++n_reg_sibling;
+                    } else
+                        pending_push = need[iv[f.j]];
+                }
                 f.ret = true;
                 int c = iv[f.j++];
                 st.push_back({c, 0, false});
                 continue;
             }
             if (binary) {
-                if (iv.size() == 2) emit(SW_II, need[iv[1]], iv[0], false, iv[1], false);
+                if (iv.size() == 2) {
+                    const bool from_u = u_mode; // set when iv[1] was evaluated in u (chains hold no II, so no nesting)
+                    u_mode = false;
+                    // operand A is the waiting side: the popped CLV of iv[0], or u holding iv[1]
+                    if (from_u) emit(SW_II, need[iv[1]], iv[1], false, iv[0], false);
+                    else emit(SW_II, need[iv[1]], iv[0], false, iv[1], false);
+                    if (from_u) recs.back().h.flags |= SW_FLAG_XU;
+                }
                 else if (iv.size() == 1) emit(SW_TI, 0, tv[0], true, iv[0], false);
                 else emit(SW_TT, 0, tv[0], true, tv[1], true);
             } else if (iv.empty()) {
@@ -134,6 +162,18 @@ struct SweepSched {
             recs.back().h.flags |= SW_FLAG_RESCALE;
             st.pop_back();
         }
+        // dense renumbering of the stack levels actually used (the register accumulator usually frees level 0)
+        {
+            std::vector<int> used(n_levels + 2, 0);
+            for (const Rec &r : recs)
+                if ((r.h.flags & SW_FLAG_PUSH) || r.h.kind == SW_MULPOP || (r.h.kind == SW_II && !(r.h.flags & SW_FLAG_XU)))
+                    used[r.h.level] = 1;
+            int next = 0;
+            for (int &u : used) u = u ? next++ : -1;
+            for (Rec &r : recs)
+                if (used[r.h.level] >= 0) r.h.level = used[r.h.level];
+            n_levels = next;
+        }
         // lay the records out in op order
         n_ops = (int)recs.size();
         size_t off = 0;
@@ -142,21 +182,25 @@ struct SweepSched {
         for (size_t k = 0; k < recs.size(); ++k) {
             const Rec &r = recs[k];
             const uint32_t per_cat = (uint32_t)(r.h.szA + r.h.szB);
-            const uint32_t bytes = SW_HDR_BYTES + (uint32_t)n_clv * per_cat;
+            const uint32_t bytes = (uint32_t)n_clv * per_cat;
             SweepDesc &d = descs[k];
             memset(&d, 0, sizeof d);
             d.rec_off = off;
             d.rec_bytes = bytes;
             d.rowA = r.rowA;
             d.rowB = r.rowB;
-            if (r.edgeA >= 0) blocks.push_back({off + SW_HDR_BYTES, per_cat, r.edgeA, r.tabA ? 1 : 0, 0});
-            if (r.edgeB >= 0) blocks.push_back({off + SW_HDR_BYTES + (uint32_t)r.h.szA, per_cat, r.edgeB, r.tabB ? 1 : 0, 0});
+            if (r.edgeA >= 0) blocks.push_back({off, per_cat, r.edgeA, r.tabA ? 1 : 0, 0});
+            if (r.edgeB >= 0) blocks.push_back({off + (uint32_t)r.h.szA, per_cat, r.edgeB, r.tabB ? 1 : 0, 0});
             rec_cap = std::max(rec_cap, (int)bytes);
             off += bytes;
         }
         stream_bytes = off;
-        headers.assign(stream_bytes + 16, 0);
-        for (size_t k = 0; k < recs.size(); ++k) memcpy(headers.data() + descs[k].rec_off, &recs[k].h, sizeof(SweepHdr));
+        ops.resize(recs.size());
+        for (size_t k = 0; k < recs.size(); ++k) {
+            const Hdr &h = recs[k].h;
+            ops[k].w0 = (uint32_t)h.kind | ((uint32_t)h.flags << 8) | ((uint32_t)h.level << 16);
+            ops[k].w1 = (uint32_t)h.szA | ((uint32_t)h.szB << 16);
+        }
         valid = true;
     }
 };

@@ -62,7 +62,8 @@ def test_sweep_shapes(gpu_lib):
 
     poly = "(((a:0.1,b:0.2,c:0.1)x:0.05,(d:0.3,e:0.2)y:0.01,((f:0.1,g:0.2)z:0.1)w:0.2,h:0.3,i:0.1)r:0.1,(j:0.2)u:0.3);"
     rng = np.random.default_rng(5)
-    for nwk, levels in ((balanced(0, 1024) + ";", 9), (cater(300) + ";", 0), (poly, None)):
+    # balanced 1024: 9 pending siblings on the deepest path, the cherry-level one stays in the register accumulator
+    for nwk, levels in ((balanced(0, 1024) + ";", 8), (cater(300) + ";", 0), (poly, None)):
         tree = parse_newick(nwk)
         names = [tree.nodes[i].taxa for i in tree.get_node_ids() if tree.is_leaf(i)]
         ft = workloads.flatten_fast(tree, names)

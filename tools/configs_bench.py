@@ -1,0 +1,140 @@
+#!/usr/bin/env python
+"""Times BASELINE.json's other configurations (1, 2, 4, 5) and per-rank shards of config 3 on ONE GPU.
+
+bench.py measures the headline configuration; this harness produces the numbers quoted in DESIGN.md for
+the remaining rows of SURVEY.md §8 (same synthetic generators, same C ABI).  One JSON line per case.
+
+  python tools/configs_bench.py [--cases cfg1,cfg2,cfg3_rank8,cfg4,cfg5] [--reps 3]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from phylo_rs_b200 import capi, synthetic  # noqa: E402
+
+
+def model_for(name):
+    if name == "jc69":
+        return synthetic.gtr_model(pi=(0.25,) * 4, rates=(1.0,) * 6)
+    if name == "gtr_g4":
+        return synthetic.gtr_model(alpha=0.5, k=4)
+    if name == "gtr_i_g4":
+        return synthetic.gtr_model(alpha=0.5, k=4, p_inv=0.2)
+    raise ValueError(name)
+
+
+def timed(ctx, fn, reps):
+    fn()  # warm-up (allocations, schedule upload)
+    fn()
+    ms = []
+    for _ in range(reps):
+        ctx.timer_start()
+        t0 = time.perf_counter()
+        out = fn()
+        dev = ctx.timer_stop()
+        ms.append((dev, (time.perf_counter() - t0) * 1e3))
+    return out, min(m[0] for m in ms), min(m[1] for m in ms)
+
+
+def run_lnl(tag, n_taxa, n_sites, model, seed, reps, flags=0):
+    tree = synthetic.yule_flat(n_taxa, seed)
+    with capi.Context(flags=flags) as ctx:
+        synthetic.load_into(ctx, tree, model_for(model))
+        ctx.simulate_alignment(n_sites, seed=seed ^ 0xA11C)
+        lnl, dev_ms, wall_ms = timed(ctx, ctx.log_likelihood, reps)
+        st = ctx.stats()
+    upd = (n_taxa - 1) * n_sites
+    return dict(case=tag, taxa=n_taxa, patterns=n_sites, model=model, lnl=lnl, device_ms=dev_ms, wall_ms=wall_ms,
+                updates_per_s=upd / (wall_ms * 1e-3), algorithmic_GBps=st["algorithmic_bytes"] / (wall_ms * 1e-3) / 1e9,
+                sweep_block_sites=st["sweep_block_sites"], sweep_levels=st["sweep_stack_levels"],
+                sweep_smem_levels=st["sweep_smem_levels"], path="levels" if flags & capi.FLAG_LEVEL_KERNELS else "sweep")
+
+
+def run_asr(tag, n_taxa, n_sites, model, seed, reps):
+    tree = synthetic.yule_flat(n_taxa, seed)
+    K = 4
+    with capi.Context(flags=capi.FLAG_TIMING) as ctx:
+        synthetic.load_into(ctx, tree, model_for(model))
+        ctx.simulate_alignment(n_sites, seed=seed ^ 0xA11C)
+        states = np.zeros((tree["n_nodes"], n_sites), np.uint8)
+        tot = capi.C.c_double(0.0)
+
+        def call():
+            ctx._check(ctx.lib.L.phb_marginal_asr(ctx._h, states.ctypes.data_as(capi.C.POINTER(capi.C.c_uint8)), None,
+                                                  capi.C.byref(tot)))
+            return tot.value
+
+        lnl, dev_ms, wall_ms = timed(ctx, call, reps)
+        st = ctx.stats()
+    n = n_taxa
+    up_bytes = (32.0 * K * (2 * n - 3) + n) * n_sites
+    down_bytes = (32.0 * K * (4 * n - 4) + 3 * n - 1) * n_sites
+    node_sites = ((n - 1) + (2 * n - 1)) * n_sites
+    return dict(case=tag, taxa=n_taxa, patterns=n_sites, model=model, lnl=lnl, device_ms=dev_ms, wall_ms=wall_ms,
+                ms_up=st["ms_clv"], ms_down=st["ms_down"], ms_root=st["ms_root"], tiles=st["n_tiles"],
+                tile_patterns=st["tile_patterns"], node_site_updates_per_s=node_sites / (wall_ms * 1e-3),
+                algorithmic_GBps_device=(up_bytes + down_bytes) / (dev_ms * 1e-3) / 1e9,
+                states_d2h_bytes=int(states.nbytes), state_histogram=np.bincount(states[:, :4096].ravel(), minlength=4).tolist())
+
+
+def run_nni(tag, n_taxa, n_sites, model, seed, n_moves, reps):
+    tree = synthetic.yule_flat(n_taxa, seed)
+    co = tree["child_off"]
+    internal = [v for v in range(tree["n_nodes"]) if co[v + 1] > co[v] and v != tree["root"]]
+    moves = [(v, left) for v in internal for left in (0, 1)][:n_moves]
+    with capi.Context() as ctx:
+        synthetic.load_into(ctx, tree, model_for(model))
+        ctx.simulate_alignment(n_sites, seed=seed ^ 0xA11C)
+        base = ctx.log_likelihood()
+        ids, left = [m[0] for m in moves], [m[1] for m in moves]
+        t0 = time.perf_counter()
+        out = ctx.score_nni(ids, left)
+        wall_ms = (time.perf_counter() - t0) * 1e3
+        t0 = time.perf_counter()
+        ctx.log_likelihood()
+        full_ms = (time.perf_counter() - t0) * 1e3
+    return dict(case=tag, taxa=n_taxa, patterns=n_sites, model=model, n_moves=len(moves), base_lnl=base,
+                best_delta=float(np.nanmax(out) - base), wall_ms=wall_ms, ms_per_neighbour=wall_ms / len(moves),
+                full_evaluation_ms=full_ms, trees_per_s=len(moves) / (wall_ms * 1e-3),
+                equivalent_updates_per_s=len(moves) * (n_taxa - 1) * n_sites / (wall_ms * 1e-3))
+
+
+CASES = {
+    "cfg1": lambda r: run_lnl("cfg1 JC69 64 x 10k", 64, 10_000, "jc69", 0x5EED0001, r),
+    "cfg2": lambda r: run_lnl("cfg2 GTR+G4 1000 x 100k", 1000, 100_000, "gtr_g4", 0x5EED0002, r),
+    "cfg2_levels": lambda r: run_lnl("cfg2 GTR+G4 1000 x 100k (level kernels)", 1000, 100_000, "gtr_g4", 0x5EED0002, r,
+                                     capi.FLAG_LEVEL_KERNELS),
+    "cfg3_rank2": lambda r: run_lnl("cfg3 per-rank shard at 2 GPUs", 10_000, 500_000, "gtr_i_g4", 0x5EED0003, r),
+    "cfg3_rank4": lambda r: run_lnl("cfg3 per-rank shard at 4 GPUs", 10_000, 250_000, "gtr_i_g4", 0x5EED0003, r),
+    "cfg3_rank8": lambda r: run_lnl("cfg3 per-rank shard at 8 GPUs", 10_000, 125_000, "gtr_i_g4", 0x5EED0003, r),
+    "cfg4": lambda r: run_asr("cfg4 marginal ASR GTR+G4 5000 x 500k", 5000, 500_000, "gtr_g4", 0x5EED0004, r),
+    "cfg4_small": lambda r: run_asr("cfg4/10 marginal ASR GTR+G4 5000 x 50k", 5000, 50_000, "gtr_g4", 0x5EED0004, r),
+    "cfg5": lambda r: run_nni("cfg5 1024 NNI neighbours 2000 x 200k", 2000, 200_000, "gtr_g4", 0x5EED0005, 1024, r),
+    "cfg5_small": lambda r: run_nni("cfg5/8 128 NNI neighbours 2000 x 200k", 2000, 200_000, "gtr_g4", 0x5EED0005, 128, r),
+}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--cases", default="cfg1,cfg2,cfg3_rank8,cfg4_small,cfg5_small")
+    ap.add_argument("--reps", type=int, default=3)
+    args = ap.parse_args()
+    for name in args.cases.split(","):
+        try:
+            line = CASES[name](args.reps)
+        except Exception as e:  # keep going: one failing case must not hide the others
+            line = dict(case=name, error=f"{type(e).__name__}: {e}")
+        print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()
