@@ -14,7 +14,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-DEFAULT_LIB = os.path.join(_HERE, "csrc", "libphylo_b200.so")
+DEFAULT_LIB = os.environ.get("PHYLO_B200_LIB") or os.path.join(_HERE, "csrc", "libphylo_b200.so")
 
 PHB_OK = 0
 STATUS_NAMES = {

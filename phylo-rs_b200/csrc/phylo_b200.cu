@@ -522,6 +522,14 @@ int ensure_sweep(phb_ctx *ctx, const ModelDev &M)
 {
     const TreeSched &T = ctx->tree;
     SweepSched &S = ctx->sweep;
+    int64_t shard_P = 0;
+    for (Device &d : ctx->devs) shard_P = std::max(shard_P, d.P);
+    if (S.valid && S.n_clv == M.n_clv && ctx->sweep_geom.planned_P != shard_P) {
+        size_t smem_max = ctx->devs[0].smem_optin;
+        for (Device &d : ctx->devs) smem_max = std::min(smem_max, d.smem_optin);
+        if (!ctx->sweep_geom.plan(S, smem_max, shard_P, std::max(ctx->devs[0].sm_count, 1)))
+            return ctx->fail(PHB_ERR_INVALID_MODEL_PARAMETER, "sweep: %d CLV categories do not fit one CTA", M.n_clv);
+    }
     if (!S.valid || S.n_clv != M.n_clv) {
         for (Device &d : ctx->devs) { // the old host image may still be in flight
             cudaSetDevice(d.ordinal);
@@ -531,7 +539,7 @@ int ensure_sweep(phb_ctx *ctx, const ModelDev &M)
         S.build(T.n, T.root, T.child_off, T.children, T.leaf_row, M.n_clv);
         size_t smem_max = ctx->devs[0].smem_optin;
         for (Device &d : ctx->devs) smem_max = std::min(smem_max, d.smem_optin);
-        if (!ctx->sweep_geom.plan(S, smem_max))
+        if (!ctx->sweep_geom.plan(S, smem_max, shard_P, std::max(ctx->devs[0].sm_count, 1)))
             return ctx->fail(PHB_ERR_INVALID_MODEL_PARAMETER, "sweep: %d CLV categories do not fit one CTA", M.n_clv);
     }
     for (Device &d : ctx->devs) {

@@ -175,7 +175,10 @@ __device__ __forceinline__ void sw_consumer_barrier(int n) { asm volatile("bar.s
 
 // ---- kernel parameters -------------------------------------------------------------------------------
 constexpr int SW_R = 4;              // site patterns per thread
-constexpr int SW_MAX_CONSUMERS = 256; // consumer threads per CTA (+ one producer warp)
+#ifndef PHB_SW_CONSUMERS
+#define PHB_SW_CONSUMERS 320
+#endif
+constexpr int SW_MAX_CONSUMERS = PHB_SW_CONSUMERS; // consumer threads per CTA (+ one producer warp)
 
 struct SweepParams {
     const SweepOp *ops;

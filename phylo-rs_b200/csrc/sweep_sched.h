@@ -12,6 +12,7 @@
 #include "sweep.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -209,10 +210,34 @@ struct SweepSched {
 struct SweepGeom {
     int Q = 0, n_consumers = 0, threads = 0, n_stages = 0, stage_bytes = 0, smem_levels = 0, g_levels = 0;
     size_t level_bytes = 0, smem_bytes = 0;
-    bool plan(const SweepSched &S, size_t smem_max)
+    int64_t planned_P = -1;
+    // Picks the site quads per CTA pass (Q) for a shard of P patterns on n_sm SMs.  A pass over the op list
+    // costs about t(n) = 304 + 2.67 n clocks per op for n consumer threads (measured on B200 at n = 256 and
+    // 320), and the persistent grid needs ceil(blocks / n_sm) passes, so a slightly narrower or wider CTA
+    // can save a whole pass when the block count lands just above a multiple of the SM count (the strong-
+    // scaling shards of 125k-500k patterns).  PHB_SWEEP_Q overrides the choice (experiments).
+    bool plan(const SweepSched &S, size_t smem_max, int64_t P = 0, int n_sm = 148)
     {
-        Q = (SW_MAX_CONSUMERS / S.n_clv) & ~3;
-        if (Q < 4) return false;
+        const int q_max = (SW_MAX_CONSUMERS / S.n_clv) & ~3;
+        if (q_max < 4) return false;
+        Q = q_max;
+        if (P > 0 && n_sm > 0) {
+            double best = 1e300;
+            for (int q = q_max; q >= 8 && q >= q_max / 2; q -= 4) {
+                const int64_t blocks = (P + 4 * q - 1) / (4 * q);
+                const int64_t passes = (blocks + n_sm - 1) / n_sm;
+                const double cost = (double)passes * (304.0 + 2.67 * q * S.n_clv);
+                if (cost < best - 1e-9) {
+                    best = cost;
+                    Q = q;
+                }
+            }
+        }
+        if (const char *e = getenv("PHB_SWEEP_Q")) {
+            const int q = atoi(e) & ~3;
+            if (q >= 4 && q <= q_max) Q = q;
+        }
+        planned_P = P;
         n_consumers = Q * S.n_clv;
         threads = ((n_consumers + 31) / 32) * 32 + 32;
         level_bytes = (size_t)n_consumers * SW_R * 32;

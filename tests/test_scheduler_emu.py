@@ -53,9 +53,10 @@ def test_level_kernels_flag(emu_lib, model):
 
 def test_sweep_many_blocks_per_cta(emu_lib):
     """More site blocks than (emulated) SMs: every persistent CTA sweeps the tree several times."""
-    case = workloads.make_case(7, 2600, model="gtr_g4", seed=14)  # 256-site blocks -> 11 blocks on 3 CTAs
+    case = workloads.make_case(7, 2600, model="gtr_g4", seed=14)  # <= 320-site blocks -> >= 9 blocks on 3 CTAs
     st = _cases.check_lnl(emu_lib, case)[2]
-    assert st["sweep_block_sites"] == 256 and st["sweep_ops"] == 6 and st["clv_launches"] == 1
+    assert 160 <= st["sweep_block_sites"] <= 320 and st["sweep_block_sites"] % 16 == 0
+    assert st["sweep_ops"] == 6 and st["clv_launches"] == 1
 
 
 def test_sweep_global_stack_levels(emu_lib, monkeypatch):
