@@ -233,9 +233,9 @@ def run_gpu(args, rank, world, local_rank):
         host.numpy()[p0:p0 + c] = ctx.get_alignment(p0, c)
 
     def e2e_step():
-        ctx.set_alignment_ptr(host.data_ptr(), n_rows, cnt)
+        # the reference-facing call shape: model + tree + host alignment bytes in, lnL out
         synthetic.load_into(ctx, tree, model)
-        v = ctx.log_likelihood()
+        v = ctx.log_likelihood_host((host.data_ptr(), n_rows, cnt))
         if world > 1:
             red[0] = v
             dist.all_reduce(red)
@@ -301,7 +301,7 @@ def run_gpu(args, rank, world, local_rank):
             "e2e": {"value": updates / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(cnt) * n_rows + 8 * 60 + 8 * 4 * tree["n_nodes"] + 4 * 4 * tree["n_nodes"],
                     "d2h_bytes_per_step": 8 + 4 * n_rows, "steps": e2e_steps,
-                    "note": "per rank: pinned host [pattern][row] bytes -> H2D -> pack -> evaluate -> scalar back"},
+                    "note": "per rank: phb_log_likelihood_host on pinned host [pattern][row] bytes: chunked H2D overlapped with pack + sweep, tree/model upload, scalar back"},
             "gpu_launches": launches,
             "clocks": clocks,
         }

@@ -114,6 +114,16 @@ int32_t phb_set_tree(phb_ctx *ctx, int32_t n_nodes, const int32_t *postorder,
  *   per_pattern  nullable; n_patterns per-pattern log-likelihoods (site_ll before the multiplicity) */
 int32_t phb_log_likelihood(phb_ctx *ctx, double *total, double *per_pattern);
 
+/* The reference's call shape in ONE entry: `tree.log_likelihood(&model, &aln)` hands over the alignment on
+ * every call (src/tree/likelihood.rs:156-164), so the binding's natural unit is "host bytes in, lnL out".
+ * Equivalent to phb_set_alignment + phb_log_likelihood (same results bit for bit), but for the pattern-major
+ * layout the host->device copy of chunk k+1 overlaps the packing and the sweep of chunk k, so the call
+ * costs about max(PCIe copy, compute) instead of their sum.  Requires set_model + set_tree; leaves the
+ * alignment resident for later phb_log_likelihood / phb_marginal_asr / phb_score_nni calls. */
+int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns, const uint8_t *bytes,
+                                int32_t layout, const uint64_t *multiplicity, double *total,
+                                double *per_pattern);
+
 /* compute_marginal_asr (src/tree/likelihood.rs:224-408).
  *   states       [n_nodes][n_patterns] argmax state index 0..3 (A,C,G,T) for EVERY node incl. leaves
  *                (likelihood.rs:262-264), last-maximal-index tie rule (:385-390)

@@ -33,7 +33,7 @@ EXPORTS = [
     "phb_ctx_create", "phb_ctx_destroy", "phb_set_clv_budget", "phb_set_alignment", "phb_set_model",
     "phb_set_tree", "phb_log_likelihood", "phb_marginal_asr", "phb_get_per_pattern", "phb_score_nni",
     "phb_simulate_alignment", "phb_get_alignment", "phb_get_stats", "phb_measure_fp64_tflops",
-    "phb_timer_start", "phb_timer_stop", "phb_transition_matrices",
+    "phb_timer_start", "phb_timer_stop", "phb_transition_matrices", "phb_log_likelihood_host",
     "phb_last_error", "phb_version",
 ]
 
@@ -81,6 +81,7 @@ class Library:
         L.phb_set_model.argtypes = [vp, dp, dp, dp, dp, dp, C.c_int32, dp, dp]
         L.phb_set_tree.argtypes = [vp, C.c_int32, ip, ip, ip, dp, ip, C.c_int32]
         L.phb_log_likelihood.argtypes = [vp, dp, dp]
+        L.phb_log_likelihood_host.argtypes = [vp, C.c_int32, C.c_int64, vp, C.c_int32, u64p, dp, dp]
         L.phb_marginal_asr.argtypes = [vp, u8p, dp, dp]
         L.phb_get_per_pattern.argtypes = [vp, dp]
         L.phb_score_nni.argtypes = [vp, C.c_int32, ip, u8p, dp]
@@ -214,6 +215,24 @@ class Context:
         pp = np.zeros(max(self.n_patterns, 1), np.float64) if per_pattern else None
         self._check(self.lib.L.phb_log_likelihood(self._h, C.byref(tot), None if pp is None else _dp(pp)))
         return (tot.value, pp[: self.n_patterns]) if per_pattern else tot.value
+
+    def log_likelihood_host(self, data, layout=LAYOUT_PATTERN_MAJOR, multiplicity=None, per_pattern=False):
+        """set_alignment + log_likelihood in one call; the H2D copy is pipelined with the packing and the sweep.
+        data: uint8 array ([P][rows] / [rows][P]) or a (ptr, n_rows, n_patterns) tuple for raw (pinned) memory."""
+        if isinstance(data, tuple):
+            ptr, rows, P = data
+        else:
+            data = np.ascontiguousarray(data, np.uint8)
+            P, rows = data.shape if layout == LAYOUT_PATTERN_MAJOR else data.shape[::-1]
+            ptr = data.ctypes.data
+        m = None if multiplicity is None else np.ascontiguousarray(multiplicity, np.uint64)
+        tot = C.c_double(0.0)
+        pp = np.zeros(max(P, 1), np.float64) if per_pattern else None
+        self._check(self.lib.L.phb_log_likelihood_host(
+            self._h, rows, P, ptr, layout, None if m is None else m.ctypes.data_as(C.POINTER(C.c_uint64)),
+            C.byref(tot), None if pp is None else _dp(pp)))
+        self.n_rows, self.n_patterns = rows, P
+        return (tot.value, pp[:P]) if per_pattern else tot.value
 
     def marginal_asr(self, want_posteriors=False):
         n, P = self.n_nodes, self.n_patterns

@@ -142,6 +142,47 @@ __global__ void pack_pattern_major_kernel(const uint8_t *__restrict__ in, int n_
     }
 }
 
+// Wider tile for the same transpose: 64 patterns x 128 rows per block, 128 contiguous input bytes per
+// pattern (whole 128-byte lines, read once), four codes per 32-bit store on the pattern axis.  Requires
+// dst_off % 4 == 0 (the packing loops use chunk offsets that are multiples of 64).
+constexpr int PK_P = 64, PK_R = 128;
+__global__ void __launch_bounds__(256)
+pack_pattern_major_tile_kernel(const uint8_t *__restrict__ in, int n_rows, int64_t n_patterns,
+                               uint8_t *__restrict__ tips, int64_t P_pad, int64_t dst_off,
+                               int *__restrict__ row_invalid)
+{
+    __shared__ uint8_t tile[PK_P][PK_R + 4];
+    const int64_t p0 = (int64_t)blockIdx.x * PK_P;
+    const int r0 = blockIdx.y * PK_R;
+    for (int idx = threadIdx.x; idx < PK_P * PK_R; idx += 256) {
+        const int j = idx >> 7, r = idx & (PK_R - 1);
+        const int64_t p = p0 + j;
+        const int row = r0 + r;
+        uint8_t code = CODE_GAP;
+        if (p < n_patterns && row < n_rows) code = encode_byte(in[p * n_rows + row]);
+        tile[j][r] = code;
+    }
+    __syncthreads();
+    const int c = threadIdx.x & 15, rr = threadIdx.x >> 4;
+    const int64_t p = p0 + 4 * c;
+    for (int it = 0; it < PK_R / 16; ++it) {
+        const int r = it * 16 + rr, row = r0 + r;
+        if (row >= n_rows || p >= n_patterns) continue;
+        const uint32_t c0 = tile[4 * c][r], c1 = tile[4 * c + 1][r], c2 = tile[4 * c + 2][r], c3 = tile[4 * c + 3][r];
+        uint8_t *dst = tips + (int64_t)row * P_pad + dst_off + p;
+        if (p + 3 < n_patterns) {
+            *reinterpret_cast<uint32_t *>(dst) = c0 | (c1 << 8) | (c2 << 16) | (c3 << 24);
+            if (c0 == CODE_INVALID || c1 == CODE_INVALID || c2 == CODE_INVALID || c3 == CODE_INVALID) row_invalid[row] = 1;
+        } else {
+            const uint32_t cs[4] = {c0, c1, c2, c3};
+            for (int i = 0; i < 4 && p + i < n_patterns; ++i) {
+                dst[i] = (uint8_t)cs[i];
+                if (cs[i] == CODE_INVALID) row_invalid[row] = 1;
+            }
+        }
+    }
+}
+
 __global__ void pack_row_major_kernel(const uint8_t *__restrict__ in, int n_rows, int64_t n_patterns,
                                       int64_t in_stride, int64_t p_first, uint8_t *__restrict__ tips,
                                       int64_t P_pad, int64_t dst_off, int *__restrict__ row_invalid)
@@ -223,12 +264,13 @@ __global__ void transition_kernel(const double *__restrict__ blen, int n_nodes, 
 // ln 1/2, B,D,.. ln 1/3, N ln 1/4, gap 0);  inv_mask = AND of all leaf masks = the rate-0 (+I)
 // category's CLV at the root in closed form (src/models/gtr.rs:94-99).
 // ---------------------------------------------------------------------------------------------
-__global__ void tip_constants_kernel(const uint8_t *__restrict__ tips, int64_t P_pad,
+__global__ void tip_constants_kernel(const uint8_t *__restrict__ tips, int64_t P_pad, int64_t n_sites,
                                      const int32_t *__restrict__ leaf_rows, int n_leaves, ModelDev M,
                                      double *__restrict__ leaf_ls, uint8_t *__restrict__ inv_mask)
 {
+    // tips / leaf_ls / inv_mask may point at a pattern offset inside the shard; P_pad is the row stride
     int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; // group of 4 sites
-    if (q * 4 >= P_pad) return;
+    if (q * 4 >= n_sites) return;
     double ls[4] = {0.0, 0.0, 0.0, 0.0};
     uint32_t inv[4] = {15u, 15u, 15u, 15u};
     for (int l = 0; l < n_leaves; ++l) {

@@ -216,6 +216,9 @@ struct Device {
     bool sweep_uploaded = false;
     int sm_count = 0;
     size_t smem_optin = 0;
+    cudaStream_t copy_stream = nullptr;          // H2D of alignment chunks, overlapped with packing / sweeping
+    DevBuf staging2;                             // second staging buffer (double buffering)
+    cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
     double *h_total = nullptr; // pinned
     cudaEvent_t tm_a = nullptr, tm_b = nullptr; // phb_timer_start / phb_timer_stop
     int64_t tile_pad = 0;
@@ -559,24 +562,28 @@ int ensure_sweep(phb_ctx *ctx, const ModelDev &M)
     return PHB_OK;
 }
 
-// compute_log_likelihood's pattern loop on one device: P(t) stream, one persistent sweep launch.
-int run_sweep(phb_ctx *ctx, Device &d, const ModelDev &M)
+// P(t) / tip tables of every op, written straight into the op-ordered stream.
+int launch_sweep_transition(phb_ctx *ctx, Device &d, const ModelDev &M)
 {
-    const TreeSched &T = ctx->tree;
     const SweepSched &S = ctx->sweep;
-    const SweepGeom &G = ctx->sweep_geom;
+    ScopedTimer tm(ctx, &d, PH_TRANSITION);
+    int nthreads = (int)S.blocks.size() * M.n_clv;
+    PHB_LAUNCH(sweep_transition_kernel, dim3((nthreads + 127) / 128), dim3(128), d.stream, d.sw_blocks.as<SweepBlock>(),
+               (int)S.blocks.size(), d.blen.as<double>(), M, d.sw_stream.as<unsigned char>());
+    CHECK_LAUNCH();
+    return PHB_OK;
+}
+
+// One persistent sweep launch over patterns [p0, p0 + np) of the device's shard with geometry G; the per-block
+// partial sums land at partials[part_off ...].  p0 must be a multiple of 16 (TMA source alignment).
+int launch_sweep_range(phb_ctx *ctx, Device &d, const ModelDev &M, const SweepGeom &G, int64_t p0, int64_t np,
+                       size_t part_off)
+{
+    const SweepSched &S = ctx->sweep;
     const int sites_per_block = 4 * G.Q;
-    const int64_t n_blocks = (d.P + sites_per_block - 1) / sites_per_block;
+    const int64_t n_blocks = (np + sites_per_block - 1) / sites_per_block;
     const int grid = (int)std::min<int64_t>(n_blocks, std::max(d.sm_count, 1));
-    CU(d.partials.ensure(sizeof(double) * (size_t)std::max<int64_t>(n_blocks, 1)));
-    if (G.g_levels > 0) CU(d.sw_gstack.ensure((size_t)grid * G.g_levels * G.level_bytes));
-    {
-        ScopedTimer tm(ctx, &d, PH_TRANSITION);
-        int nthreads = (int)S.blocks.size() * M.n_clv;
-        PHB_LAUNCH(sweep_transition_kernel, dim3((nthreads + 127) / 128), dim3(128), d.stream, d.sw_blocks.as<SweepBlock>(),
-                   (int)S.blocks.size(), d.blen.as<double>(), M, d.sw_stream.as<unsigned char>());
-        CHECK_LAUNCH();
-    }
+    if (G.g_levels > 0) CU(d.sw_gstack.ensure((size_t)std::max(d.sm_count, 1) * G.g_levels * G.level_bytes));
     SweepParams sp;
     memset(&sp, 0, sizeof sp);
     sp.ops = d.sw_ops.as<SweepOp>();
@@ -591,37 +598,50 @@ int run_sweep(phb_ctx *ctx, Device &d, const ModelDev &M)
     sp.smem_levels = G.smem_levels;
     sp.g_levels = G.g_levels;
     sp.gstack = d.sw_gstack.as<double>();
-    sp.tips = d.tips.as<uint8_t>();
+    sp.tips = d.tips.as<uint8_t>() + p0;
     sp.P_pad = d.P_pad;
-    sp.P = d.P;
+    sp.P = np;
     sp.n_blocks = n_blocks;
-    sp.leaf_ls = d.leaf_ls.as<double>();
-    sp.inv_mask = d.inv_mask.as<uint8_t>();
-    sp.mult = d.mult.as<double>();
-    sp.per_pattern = d.per_pattern.as<double>();
-    sp.partials = d.partials.as<double>();
+    sp.leaf_ls = d.leaf_ls.as<double>() + p0;
+    sp.inv_mask = d.inv_mask.as<uint8_t>() + p0;
+    sp.mult = d.mult.as<double>() + p0;
+    sp.per_pattern = d.per_pattern.as<double>() + p0;
+    sp.partials = d.partials.as<double>() + part_off;
     sp.error_flag = d.sw_err.as<unsigned int>();
-    {
-        ScopedTimer tm(ctx, &d, PH_CLV);
+    ScopedTimer tm(ctx, &d, PH_CLV);
 #ifndef PHB_HOST_EMU
-        static bool attr_set[64] = {false};
-        if (!attr_set[d.ordinal & 63]) {
-            CU(cudaFuncSetAttribute(sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)d.smem_optin));
-            attr_set[d.ordinal & 63] = true;
-        }
+    static bool attr_set[64] = {false};
+    if (!attr_set[d.ordinal & 63]) {
+        CU(cudaFuncSetAttribute(sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)d.smem_optin));
+        attr_set[d.ordinal & 63] = true;
+    }
 #endif
-        PHB_LAUNCH_SMEM(sweep_kernel, dim3(grid), dim3(G.threads), G.smem_bytes, d.stream, sp, M);
-        CHECK_LAUNCH();
-        if (&d == &ctx->devs[0]) ctx->stats.clv_launches++;
-    }
-    {
-        ScopedTimer tm(ctx, &d, PH_ROOT);
-        PHB_LAUNCH(final_reduce_kernel, dim3(1), dim3(1024), d.stream, d.partials.as<double>(), (int)n_blocks,
-                   d.total.as<double>());
-        CHECK_LAUNCH();
-    }
-    (void)T;
+    PHB_LAUNCH_SMEM(sweep_kernel, dim3(grid), dim3(G.threads), G.smem_bytes, d.stream, sp, M);
+    CHECK_LAUNCH();
+    if (&d == &ctx->devs[0]) ctx->stats.clv_launches++;
     return PHB_OK;
+}
+
+int launch_sweep_reduce(phb_ctx *ctx, Device &d, size_t n_partials)
+{
+    ScopedTimer tm(ctx, &d, PH_ROOT);
+    PHB_LAUNCH(final_reduce_kernel, dim3(1), dim3(1024), d.stream, d.partials.as<double>(), (int)n_partials,
+               d.total.as<double>());
+    CHECK_LAUNCH();
+    return PHB_OK;
+}
+
+// compute_log_likelihood's pattern loop on one device: P(t) stream, one persistent sweep launch.
+int run_sweep(phb_ctx *ctx, Device &d, const ModelDev &M)
+{
+    const SweepGeom &G = ctx->sweep_geom;
+    const int64_t n_blocks = (d.P + 4 * G.Q - 1) / (4 * G.Q);
+    CU(d.partials.ensure(sizeof(double) * (size_t)std::max<int64_t>(n_blocks, 1)));
+    int rc = launch_sweep_transition(ctx, d, M);
+    if (rc) return rc;
+    rc = launch_sweep_range(ctx, d, M, G, 0, d.P, 0);
+    if (rc) return rc;
+    return launch_sweep_reduce(ctx, d, (size_t)n_blocks);
 }
 
 // One full evaluation on every device.  asr=false: compute_log_likelihood; asr=true: + down pass.
@@ -683,7 +703,7 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total)
             ScopedTimer tm(ctx, &d, PH_ROOT);
             int64_t groups = d.P_pad / 4;
             PHB_LAUNCH(tip_constants_kernel, dim3((unsigned)((groups + 255) / 256)), dim3(256), d.stream,
-                       d.tips.as<uint8_t>(), d.P_pad, d.leaf_rows.as<int32_t>(), (int)T.leaf_rows.size(), M,
+                       d.tips.as<uint8_t>(), d.P_pad, d.P_pad, d.leaf_rows.as<int32_t>(), (int)T.leaf_rows.size(), M,
                        d.leaf_ls.as<double>(), d.inv_mask.as<uint8_t>());
             CHECK_LAUNCH();
             d.tip_constants_valid = true;
@@ -806,6 +826,9 @@ int32_t phb_ctx_create(const int32_t *devices, int32_t n_dev, uint64_t flags, ph
             d.smem_optin = (size_t)v;
         }
         if (cudaSetDevice(d.ordinal) != cudaSuccess || cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaStreamCreateWithFlags(&d.copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreate(&d.ev_copied[0]) != cudaSuccess || cudaEventCreate(&d.ev_copied[1]) != cudaSuccess ||
+            cudaEventCreate(&d.ev_free[0]) != cudaSuccess || cudaEventCreate(&d.ev_free[1]) != cudaSuccess ||
             cudaHostAlloc((void **)&d.h_total, sizeof(double), cudaHostAllocDefault) != cudaSuccess) {
             phb_ctx_destroy(ctx);
             return PHB_ERR_CUDA;
@@ -820,6 +843,7 @@ void phb_ctx_destroy(phb_ctx *ctx)
     if (!ctx) return;
     for (Device &d : ctx->devs) {
         cudaSetDevice(d.ordinal);
+        if (d.copy_stream) cudaStreamSynchronize(d.copy_stream);
         if (d.stream) cudaStreamSynchronize(d.stream);
         DevBuf *bufs[] = {&d.tips, &d.mult, &d.leaf_ls, &d.inv_mask, &d.per_pattern, &d.row_invalid, &d.Pmat, &d.blen,
                           &d.clv, &d.scale, &d.cat_ll, &d.partials, &d.total, &d.ops, &d.gops, &d.gkids, &d.dops,
@@ -834,6 +858,12 @@ void phb_ctx_destroy(phb_ctx *ctx)
         if (d.h_total) cudaFreeHost(d.h_total);
         if (d.tm_a) cudaEventDestroy(d.tm_a);
         if (d.tm_b) cudaEventDestroy(d.tm_b);
+        d.staging2.release();
+        for (int i = 0; i < 2; ++i) {
+            if (d.ev_copied[i]) cudaEventDestroy(d.ev_copied[i]);
+            if (d.ev_free[i]) cudaEventDestroy(d.ev_free[i]);
+        }
+        if (d.copy_stream) cudaStreamDestroy(d.copy_stream);
         if (d.stream) cudaStreamDestroy(d.stream);
     }
     delete ctx;
@@ -870,6 +900,85 @@ static int shard_and_alloc(phb_ctx *ctx, int n_rows, int64_t P)
     return PHB_OK;
 }
 
+} // extern "C" (templates need C++ linkage)
+
+namespace {
+
+// Streams the pattern-major host bytes of device d's shard through two staging buffers: chunk c is copied
+// on copy_stream while chunk c-1 is packed (and whatever `after_chunk` enqueues runs) on d.stream.
+// bounds: ascending pattern offsets inside the shard, bounds.front() == 0, bounds.back() == d.P, every
+// interior bound a multiple of 64.
+template <class F>
+int stream_pattern_major(phb_ctx *ctx, Device &d, const uint8_t *bytes, int n_rows, const std::vector<int64_t> &bounds,
+                         F &&after_chunk)
+{
+    size_t max_bytes = 0;
+    for (size_t c = 0; c + 1 < bounds.size(); ++c) max_bytes = std::max(max_bytes, (size_t)(bounds[c + 1] - bounds[c]) * n_rows);
+    CU(d.staging.ensure(max_bytes));
+    if (bounds.size() > 2) CU(d.staging2.ensure(max_bytes));
+    // the staging buffers may still be read by packing kernels of an earlier call
+    CU(cudaEventRecord(d.ev_free[0], d.stream));
+    CU(cudaStreamWaitEvent(d.copy_stream, d.ev_free[0], 0));
+    for (size_t c = 0; c + 1 < bounds.size(); ++c) {
+        const int buf = (int)(c & 1);
+        const int64_t c0 = bounds[c], np = bounds[c + 1] - c0;
+        if (np <= 0) continue;
+        uint8_t *st = (buf ? d.staging2 : d.staging).as<uint8_t>();
+        if (c >= 2) CU(cudaStreamWaitEvent(d.copy_stream, d.ev_free[buf], 0));
+        CU(cudaMemcpyAsync(st, bytes + (size_t)(d.p_begin + c0) * n_rows, (size_t)np * n_rows, cudaMemcpyHostToDevice,
+                           d.copy_stream));
+        CU(cudaEventRecord(d.ev_copied[buf], d.copy_stream));
+        CU(cudaStreamWaitEvent(d.stream, d.ev_copied[buf], 0));
+        dim3 grid((unsigned)((np + PK_P - 1) / PK_P), (unsigned)((n_rows + PK_R - 1) / PK_R));
+        PHB_LAUNCH(pack_pattern_major_tile_kernel, grid, dim3(256), d.stream, st, n_rows, np, d.tips.as<uint8_t>(), d.P_pad,
+                   c0, d.row_invalid.as<int>());
+        CHECK_LAUNCH();
+        CU(cudaEventRecord(d.ev_free[buf], d.stream));
+        int rc = after_chunk(c0, np);
+        if (rc) return rc;
+    }
+    return PHB_OK;
+}
+
+// padding codes + multiplicities of one device's shard (everything of set_alignment except the bytes)
+int upload_pad_and_mult(phb_ctx *ctx, Device &d, int n_rows, const uint64_t *multiplicity)
+{
+    for (int r0 = 0; r0 < n_rows && d.P_pad > d.P; r0 += 32768) {
+        dim3 grid((unsigned)((d.P_pad - d.P + 255) / 256), (unsigned)std::min(32768, n_rows - r0));
+        PHB_LAUNCH(fill_pad_kernel, grid, dim3(256), d.stream, d.tips.as<uint8_t>(), r0, d.P, d.P_pad);
+        CHECK_LAUNCH();
+    }
+    const uint64_t *dm = nullptr;
+    if (multiplicity && d.P > 0) {
+        CU(d.scratch.ensure(sizeof(uint64_t) * (size_t)d.P));
+        CU(cudaMemcpyAsync(d.scratch.p, multiplicity + d.p_begin, sizeof(uint64_t) * (size_t)d.P, cudaMemcpyHostToDevice,
+                           d.stream));
+        dm = d.scratch.as<uint64_t>();
+    }
+    PHB_LAUNCH(mult_to_double_kernel, dim3((unsigned)std::min<int64_t>((d.P_pad + 255) / 256, 4096)), dim3(256), d.stream, dm,
+               d.P, d.P_pad, d.mult.as<double>());
+    CHECK_LAUNCH();
+    return PHB_OK;
+}
+
+// join + gather the per-row validity flags written by the packing kernels
+int gather_row_flags(phb_ctx *ctx, int n_rows)
+{
+    std::vector<int> tmp(std::max(n_rows, 1));
+    for (Device &d : ctx->devs) {
+        CU(cudaSetDevice(d.ordinal));
+        CU(cudaMemcpyAsync(tmp.data(), d.row_invalid.p, sizeof(int) * (size_t)std::max(n_rows, 1), cudaMemcpyDeviceToHost,
+                           d.stream));
+        CU(cudaStreamSynchronize(d.stream));
+        for (int r = 0; r < n_rows; ++r) ctx->row_invalid_host[r] |= tmp[r];
+    }
+    return PHB_OK;
+}
+
+} // namespace
+
+extern "C" {
+
 int32_t phb_set_alignment(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns, const uint8_t *bytes, int32_t layout,
                           const uint64_t *multiplicity)
 {
@@ -886,18 +995,12 @@ int32_t phb_set_alignment(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns, cons
         CU(cudaSetDevice(d.ordinal));
         if (d.P > 0 && n_rows > 0) {
             if (layout == PHB_LAYOUT_PATTERN_MAJOR) {
-                int64_t pp = std::max<int64_t>(1, (int64_t)(CHUNK / (size_t)n_rows));
-                pp = std::min<int64_t>(pp, d.P);
-                CU(d.staging.ensure((size_t)pp * n_rows));
-                for (int64_t p0 = 0; p0 < d.P; p0 += pp) {
-                    int64_t np = std::min<int64_t>(pp, d.P - p0);
-                    CU(cudaMemcpyAsync(d.staging.p, bytes + (size_t)(d.p_begin + p0) * n_rows, (size_t)np * n_rows,
-                                       cudaMemcpyHostToDevice, d.stream));
-                    dim3 grid((unsigned)((np + 31) / 32), (unsigned)((n_rows + 31) / 32));
-                    PHB_LAUNCH(pack_pattern_major_kernel, grid, dim3(32, 8), d.stream, d.staging.as<uint8_t>(), n_rows,
-                               np, (int64_t)0, d.tips.as<uint8_t>(), d.P_pad, p0, d.row_invalid.as<int>());
-                    CHECK_LAUNCH();
-                }
+                int64_t pp = std::max<int64_t>(64, (int64_t)(CHUNK / (size_t)n_rows) / 64 * 64);
+                std::vector<int64_t> bounds(1, 0);
+                while (d.P - bounds.back() > pp) bounds.push_back(bounds.back() + pp);
+                bounds.push_back(d.P);
+                rc = stream_pattern_major(ctx, d, bytes, n_rows, bounds, [](int64_t, int64_t) { return 0; });
+                if (rc) return rc;
             } else {
                 int64_t rr = std::max<int64_t>(1, (int64_t)(CHUNK / (size_t)d.P));
                 rr = std::min<int64_t>(std::min<int64_t>(rr, n_rows), 32768);
@@ -914,32 +1017,11 @@ int32_t phb_set_alignment(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns, cons
                 }
             }
         }
-        for (int r0 = 0; r0 < n_rows && d.P_pad > d.P; r0 += 32768) {
-            dim3 grid((unsigned)((d.P_pad - d.P + 255) / 256), (unsigned)std::min(32768, n_rows - r0));
-            PHB_LAUNCH(fill_pad_kernel, grid, dim3(256), d.stream, d.tips.as<uint8_t>(), r0, d.P, d.P_pad);
-            CHECK_LAUNCH();
-        }
-        // multiplicities
-        const uint64_t *dm = nullptr;
-        if (multiplicity && d.P > 0) {
-            CU(d.scratch.ensure(sizeof(uint64_t) * (size_t)d.P));
-            CU(cudaMemcpyAsync(d.scratch.p, multiplicity + d.p_begin, sizeof(uint64_t) * (size_t)d.P,
-                               cudaMemcpyHostToDevice, d.stream));
-            dm = d.scratch.as<uint64_t>();
-        }
-        PHB_LAUNCH(mult_to_double_kernel, dim3((unsigned)std::min<int64_t>((d.P_pad + 255) / 256, 4096)), dim3(256),
-                   d.stream, dm, d.P, d.P_pad, d.mult.as<double>());
-        CHECK_LAUNCH();
+        rc = upload_pad_and_mult(ctx, d, n_rows, multiplicity);
+        if (rc) return rc;
     }
-    // join + gather the per-row validity flags
-    std::vector<int> tmp(std::max(n_rows, 1));
-    for (Device &d : ctx->devs) {
-        CU(cudaSetDevice(d.ordinal));
-        CU(cudaMemcpyAsync(tmp.data(), d.row_invalid.p, sizeof(int) * (size_t)std::max(n_rows, 1), cudaMemcpyDeviceToHost,
-                           d.stream));
-        CU(cudaStreamSynchronize(d.stream));
-        for (int r = 0; r < n_rows; ++r) ctx->row_invalid_host[r] |= tmp[r];
-    }
+    rc = gather_row_flags(ctx, n_rows);
+    if (rc) return rc;
     ctx->have_aln = true;
     return PHB_OK;
 }
@@ -1027,6 +1109,122 @@ int32_t phb_log_likelihood(phb_ctx *ctx, double *total, double *per_pattern)
     if (!ctx || !total) return PHB_ERR_INVALID_ARGUMENT;
     int rc = evaluate(ctx, false, false, total);
     if (rc) return rc;
+    if (per_pattern) return phb_get_per_pattern(ctx, per_pattern);
+    return PHB_OK;
+}
+
+int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns, const uint8_t *bytes, int32_t layout,
+                                const uint64_t *multiplicity, double *total, double *per_pattern)
+{
+    if (!ctx || !total) return PHB_ERR_INVALID_ARGUMENT;
+    if (n_rows < 0 || n_patterns < 0 || (layout != PHB_LAYOUT_PATTERN_MAJOR && layout != PHB_LAYOUT_ROW_MAJOR) ||
+        (!bytes && n_rows > 0 && n_patterns > 0))
+        return ctx->fail(PHB_ERR_INVALID_ARGUMENT, "log_likelihood_host: bad arguments");
+    if (!ctx->have_model || !ctx->tree.valid)
+        return ctx->fail(PHB_ERR_STATE, "set_model and set_tree must precede log_likelihood_host");
+    const TreeSched &T = ctx->tree;
+    const ModelDev &M = ctx->model;
+    const bool fused = layout == PHB_LAYOUT_PATTERN_MAJOR && !(ctx->flags & PHB_FLAG_LEVEL_KERNELS) && T.n_internal > 0 &&
+                       M.n_clv > 0 && M.n_cat <= 4 * M.n_clv && n_patterns > 0 && n_rows > 0;
+    if (!fused) { // the general two-call path
+        int rc = phb_set_alignment(ctx, n_rows, n_patterns, bytes, layout, multiplicity);
+        if (rc) return rc;
+        return phb_log_likelihood(ctx, total, per_pattern);
+    }
+    // every leaf needs a row before anything is copied (likelihood.rs:99-103)
+    for (size_t i = 0; i < T.leaf_nodes.size(); ++i)
+        if (T.leaf_rows[i] < 0 || T.leaf_rows[i] >= n_rows)
+            return ctx->fail(PHB_ERR_INVALID_ALIGNMENT, "Leaf in tree not found in alignment leaf order (node %d)",
+                             T.leaf_nodes[i]);
+    ctx->have_aln = false;
+    int rc = shard_and_alloc(ctx, n_rows, n_patterns);
+    if (rc) return rc;
+    ctx->row_invalid_host.assign(std::max(n_rows, 1), 0);
+    if (!ctx->tree_uploaded) {
+        rc = upload_tree(ctx);
+        if (rc) return rc;
+    }
+    rc = ensure_sweep(ctx, M);
+    if (rc) return rc;
+    ctx->stats.clv_launches = 0;
+    const SweepSched &S = ctx->sweep;
+    Device &d0 = ctx->devs[0];
+    d0.ev_used = 0;
+    d0.ev_log.clear();
+    for (Device &d : ctx->devs) {
+        CU(cudaSetDevice(d.ordinal));
+        if (d.P == 0) {
+            *d.h_total = 0.0;
+            continue;
+        }
+        rc = plan_device(ctx, d, M, false, false, true);
+        if (rc) return rc;
+        rc = upload_pad_and_mult(ctx, d, n_rows, multiplicity);
+        if (rc) return rc;
+        rc = launch_sweep_transition(ctx, d, M);
+        if (rc) return rc;
+        // chunks of two full passes of the widest CTA; a short remainder joins the last chunk, which gets
+        // its own geometry so that it does not end in a nearly empty pass
+        const int n_sm = std::max(d.sm_count, 1);
+        const int q_max = (SW_MAX_CONSUMERS / M.n_clv) & ~3;
+        const int64_t pass = (int64_t)n_sm * 4 * q_max;
+        const int64_t chunk = round_up(2 * pass, 64);
+        std::vector<int64_t> bounds(1, 0);
+        while (d.P - bounds.back() > chunk + chunk / 2) bounds.push_back(bounds.back() + chunk);
+        bounds.push_back(d.P);
+        SweepGeom g_main, g_tail;
+        if (!g_main.plan(S, d.smem_optin, chunk, n_sm) || !g_tail.plan(S, d.smem_optin, d.P - bounds[bounds.size() - 2], n_sm))
+            return ctx->fail(PHB_ERR_INVALID_MODEL_PARAMETER, "sweep: %d CLV categories do not fit one CTA", M.n_clv);
+        size_t n_part_max = 0;
+        for (size_t c = 0; c + 1 < bounds.size(); ++c) {
+            const SweepGeom &G = c + 2 == bounds.size() ? g_tail : g_main;
+            n_part_max += (size_t)((bounds[c + 1] - bounds[c] + 4 * G.Q - 1) / (4 * G.Q));
+        }
+        CU(d.partials.ensure(sizeof(double) * std::max<size_t>(n_part_max, 1)));
+        size_t part_off = 0;
+        const int64_t last0 = bounds[bounds.size() - 2];
+        rc = stream_pattern_major(ctx, d, bytes, n_rows, bounds, [&](int64_t c0, int64_t np) -> int {
+            const SweepGeom &G = c0 == last0 ? g_tail : g_main;
+            const int64_t np4 = round_up(np, 4);
+            PHB_LAUNCH(tip_constants_kernel, dim3((unsigned)((np4 / 4 + 255) / 256)), dim3(256), d.stream,
+                       d.tips.as<uint8_t>() + c0, d.P_pad, np4, d.leaf_rows.as<int32_t>(), (int)T.leaf_rows.size(), M,
+                       d.leaf_ls.as<double>() + c0, d.inv_mask.as<uint8_t>() + c0);
+            CHECK_LAUNCH();
+            int r2 = launch_sweep_range(ctx, d, M, G, c0, np, part_off);
+            part_off += (size_t)((np + 4 * G.Q - 1) / (4 * G.Q));
+            return r2;
+        });
+        if (rc) return rc;
+        d.tip_constants_valid = true;
+        d.tip_constants_rows = T.leaf_rows;
+        rc = launch_sweep_reduce(ctx, d, part_off);
+        if (rc) return rc;
+        CU(cudaMemcpyAsync(d.h_total, d.total.p, sizeof(double), cudaMemcpyDeviceToHost, d.stream));
+    }
+    rc = gather_row_flags(ctx, n_rows); // joins every device stream
+    if (rc) return rc;
+    ctx->have_aln = true;
+    rc = check_leaves(ctx); // invalid byte in a leaf row (likelihood.rs:105-107): the result is discarded
+    if (rc) return rc;
+    double sum = 0.0;
+    for (Device &d : ctx->devs) sum += *d.h_total; // rank order: deterministic
+    *total = sum;
+    phb_stats &st = ctx->stats;
+    st.n_patterns = n_patterns;
+    st.tile_patterns = d0.P_pad;
+    st.n_tiles = 1;
+    st.n_levels = T.n_levels;
+    st.n_internal = T.n_internal;
+    st.n_clv_categories = M.n_clv;
+    st.kernel_launches = ctx->launches;
+    st.clv_updates = (int64_t)T.n_internal * n_patterns;
+    st.algorithmic_bytes = (32.0 * M.n_clv * T.sum_one_plus_i + T.sum_t) * (double)n_patterns;
+    st.sweep_ops = S.n_ops;
+    st.sweep_stack_levels = S.n_levels;
+    st.sweep_smem_levels = ctx->sweep_geom.smem_levels;
+    st.sweep_stages = ctx->sweep_geom.n_stages;
+    st.sweep_block_sites = 4 * ctx->sweep_geom.Q;
+    st.sweep_stream_bytes = (int64_t)S.stream_bytes;
     if (per_pattern) return phb_get_per_pattern(ctx, per_pattern);
     return PHB_OK;
 }

@@ -28,6 +28,7 @@ struct Api {
     decltype(&phb_set_model) set_model = nullptr;
     decltype(&phb_set_tree) set_tree = nullptr;
     decltype(&phb_log_likelihood) log_likelihood = nullptr;
+    decltype(&phb_log_likelihood_host) log_likelihood_host = nullptr;
     decltype(&phb_marginal_asr) marginal_asr = nullptr;
     decltype(&phb_score_nni) score_nni = nullptr;
     decltype(&phb_transition_matrices) transition_matrices = nullptr;
@@ -78,6 +79,7 @@ const Api &api()
     a.set_model = reinterpret_cast<decltype(a.set_model)>(sym("phb_set_model"));
     a.set_tree = reinterpret_cast<decltype(a.set_tree)>(sym("phb_set_tree"));
     a.log_likelihood = reinterpret_cast<decltype(a.log_likelihood)>(sym("phb_log_likelihood"));
+    a.log_likelihood_host = reinterpret_cast<decltype(a.log_likelihood_host)>(sym("phb_log_likelihood_host"));
     a.marginal_asr = reinterpret_cast<decltype(a.marginal_asr)>(sym("phb_marginal_asr"));
     a.score_nni = reinterpret_cast<decltype(a.score_nni)>(sym("phb_score_nni"));
     a.transition_matrices = reinterpret_cast<decltype(a.transition_matrices)>(sym("phb_transition_matrices"));
@@ -190,24 +192,40 @@ void load_model(phb_ctx *c, const GtrModel &m)
                              weights.data()));
 }
 
-// compress + resolve + upload; returns the compressed columns and the flattening for the caller's use
-phb_ctx *load_all(const PhyloTree &tree, const GtrModel &model, const Alignment &aln, CompressedColumns &comp, Flat &flat)
+// compress + resolve (host side, may throw the reference's errors before the device is touched), then
+// model and tree upload.  `pack` receives the patterns as [pattern][row] bytes + multiplicities.
+struct Packed {
+    std::vector<std::uint8_t> bytes;
+    std::vector<std::uint64_t> mult;
+    std::size_t rows = 0, P = 0;
+};
+
+phb_ctx *load_model_and_tree(const PhyloTree &tree, const GtrModel &model, const Alignment &aln, CompressedColumns &comp,
+                             Flat &flat, Packed &pk)
 {
-    // host-side errors (unknown taxon) surface before the device is touched, as in the reference
     comp = aln.compress_columns();
     flat = flatten(tree, comp.leaf_order);
-    phb_ctx *c = context();
-    const std::size_t rows = comp.leaf_order.size(), P = comp.patterns.size();
-    std::vector<std::uint8_t> bytes(std::max<std::size_t>(rows * P, 1));
-    std::vector<std::uint64_t> mult(std::max<std::size_t>(P, 1));
-    for (std::size_t p = 0; p < P; ++p) {
-        if (rows) std::memcpy(bytes.data() + p * rows, comp.patterns[p].data(), rows);
-        mult[p] = comp.multiplicity[p];
+    pk.rows = comp.leaf_order.size();
+    pk.P = comp.patterns.size();
+    pk.bytes.assign(std::max<std::size_t>(pk.rows * pk.P, 1), 0);
+    pk.mult.assign(std::max<std::size_t>(pk.P, 1), 0);
+    for (std::size_t p = 0; p < pk.P; ++p) {
+        if (pk.rows) std::memcpy(pk.bytes.data() + p * pk.rows, comp.patterns[p].data(), pk.rows);
+        pk.mult[p] = comp.multiplicity[p];
     }
-    check(c, api().set_alignment(c, (int32_t)rows, (int64_t)P, bytes.data(), PHB_LAYOUT_PATTERN_MAJOR, mult.data()));
+    phb_ctx *c = context();
     load_model(c, model);
     check(c, api().set_tree(c, (int32_t)flat.ids.size(), flat.post.data(), flat.off.data(), flat.kids.data(),
                             flat.blen.data(), flat.leaf_row.data(), flat.root));
+    return c;
+}
+
+// ... plus the alignment, for the engines that keep it resident (ASR, NNI batches)
+phb_ctx *load_all(const PhyloTree &tree, const GtrModel &model, const Alignment &aln, CompressedColumns &comp, Flat &flat)
+{
+    Packed pk;
+    phb_ctx *c = load_model_and_tree(tree, model, aln, comp, flat, pk);
+    check(c, api().set_alignment(c, (int32_t)pk.rows, (int64_t)pk.P, pk.bytes.data(), PHB_LAYOUT_PATTERN_MAJOR, pk.mult.data()));
     return c;
 }
 
@@ -262,11 +280,14 @@ std::array<double, 16> GtrModel::category_transition(std::size_t category, doubl
 // =====================================================================================================
 double PhyloTree::log_likelihood(const GtrModel &model, const Alignment &aln) const
 {
+    // one call: host bytes in, lnL out (the H2D copy is pipelined with the packing and the sweep)
     CompressedColumns comp;
     Flat flat;
-    phb_ctx *c = load_all(*this, model, aln, comp, flat);
+    Packed pk;
+    phb_ctx *c = load_model_and_tree(*this, model, aln, comp, flat, pk);
     double total = 0.0;
-    check(c, api().log_likelihood(c, &total, nullptr));
+    check(c, api().log_likelihood_host(c, (int32_t)pk.rows, (int64_t)pk.P, pk.bytes.data(), PHB_LAYOUT_PATTERN_MAJOR,
+                                       pk.mult.data(), &total, nullptr));
     return total;
 }
 

@@ -95,6 +95,7 @@ cudaError_t cudaStreamSynchronize(cudaStream_t s);
 cudaError_t cudaEventCreate(cudaEvent_t *e);
 cudaError_t cudaEventDestroy(cudaEvent_t e);
 cudaError_t cudaEventRecord(cudaEvent_t e, cudaStream_t s);
+cudaError_t cudaStreamWaitEvent(cudaStream_t s, cudaEvent_t e, unsigned flags = 0);
 cudaError_t cudaEventElapsedTime(float *ms, cudaEvent_t a, cudaEvent_t b);
 cudaError_t cudaGetLastError();
 const char *cudaGetErrorString(cudaError_t e);

@@ -233,3 +233,28 @@ def test_full_size_properties_config2(gpu_lib):
         tot2, per2 = ctx.log_likelihood(per_pattern=True)
     assert np.array_equal(per2, per)
     assert abs(tot2 - 2 * tot) <= 1e-12 * abs(tot2)
+
+
+def test_fused_host_call(gpu_lib):
+    """phb_log_likelihood_host: chunked H2D copy overlapped with pack + sweep == the two-call path (several chunks)."""
+    case = workloads.make_case(40, 230_000, model="gtr_i_g4", seed=31)
+    with capi.Context(library=gpu_lib) as ctx:
+        workloads.load_into(ctx, case)
+        ref_tot, ref_per = ctx.log_likelihood(per_pattern=True)
+        tot, per = ctx.log_likelihood_host(case.patterns, per_pattern=True)
+        assert np.array_equal(per, ref_per)
+        assert abs(tot - ref_tot) <= 1e-12 * abs(ref_tot)
+        assert ctx.log_likelihood() == ref_tot  # alignment left resident
+    small = workloads.make_case(40, 3000, model="gtr_i_g4", seed=31, ambiguity=0.05)
+    o_tot, o_per = oracle.log_likelihood_flat(small.ft, small.model, small.patterns, small.mult, mode=0, n_threads=4)
+    with capi.Context(library=gpu_lib) as ctx:
+        m, ft = small.model, small.ft
+        ctx.set_model(m.eigenvalues, m.eigenvectors, m.pi, m.sqrt_pi, m.inv_sqrt_pi, m.rates, m.weights)
+        ctx.set_tree(ft["postorder"], ft["child_off"], ft["children"], ft["blen"], ft["leaf_row"], ft["root"])
+        tot, per = ctx.log_likelihood_host(small.patterns, multiplicity=small.mult, per_pattern=True)
+        _cases.assert_lnl_close(tot, per, o_tot, o_per)
+        bad = small.patterns.copy()
+        bad[2999, 0] = ord("!")
+        with pytest.raises(capi.PhbError) as e:
+            ctx.log_likelihood_host(bad)
+        assert e.value.variant == "AlphabetMismatch"

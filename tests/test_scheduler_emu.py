@@ -223,3 +223,40 @@ def test_simulated_alignment_roundtrip(emu_lib):
     ft["leaf_row"] = lr
     ref, ref_per = oracle.log_likelihood_flat(ft, case.model, pats)
     _cases.assert_lnl_close(tot, per, ref, ref_per)
+
+
+def test_fused_host_call_matches_two_call_path(emu_lib):
+    """phb_log_likelihood_host (chunked copy -> pack -> sweep pipeline) == set_alignment + log_likelihood, bit for bit,
+    over several chunks, with multiplicities, on one and on three virtual devices, and for the row-major fallback."""
+    from phylo_rs_b200 import capi
+
+    case = workloads.make_case(9, 7000, model="gtr_i_g4", seed=21, ambiguity=0.03)
+    mult = (np.arange(7000) % 5 + 1).astype(np.uint64)
+    case.mult = mult
+    ref_tot, ref_per, _ = _cases.check_lnl(emu_lib, case)
+    for devices in (None, [0, 0, 0]):
+        with capi.Context(devices=devices, library=emu_lib) as ctx:
+            m, ft = case.model, case.ft
+            ctx.set_model(m.eigenvalues, m.eigenvectors, m.pi, m.sqrt_pi, m.inv_sqrt_pi, m.rates, m.weights)
+            ctx.set_tree(ft["postorder"], ft["child_off"], ft["children"], ft["blen"], ft["leaf_row"], ft["root"])
+            tot, per = ctx.log_likelihood_host(case.patterns, multiplicity=mult, per_pattern=True)
+            assert np.array_equal(per, ref_per)
+            if devices is None:
+                assert tot == ref_tot
+            else:
+                assert abs(tot - ref_tot) <= 1e-12 * abs(ref_tot)
+            # the alignment stays resident: the plain entry point gives the same number again
+            assert ctx.log_likelihood() == tot
+            tot_rm = ctx.log_likelihood_host(np.ascontiguousarray(case.patterns.T), layout=capi.LAYOUT_ROW_MAJOR,
+                                             multiplicity=mult)
+            assert tot_rm == tot
+            # errors: an invalid byte in a leaf row, and a leaf without a row
+            bad = case.patterns.copy()
+            bad[6500, 3] = ord("?")
+            with pytest.raises(capi.PhbError) as e:
+                ctx.log_likelihood_host(bad)
+            assert e.value.variant == "AlphabetMismatch"
+            with pytest.raises(capi.PhbError) as e:
+                ctx.log_likelihood_host(case.patterns[:, :-1].copy())
+            assert e.value.variant == "InvalidAlignment"
+            assert ctx.log_likelihood_host(case.patterns, multiplicity=mult) == tot
