@@ -593,13 +593,15 @@ __device__ __forceinline__ void mix_weights(const double *__restrict__ cat_ll, s
 // Root: post = normalise(pi (.) up_root) per category (:304-316), in place; plus its own mixture.
 __global__ void __launch_bounds__(ROOT_THREADS)
 asr_root_kernel(double *__restrict__ root_clv, size_t tile_pad, int tile_len, ModelDev M,
-                const double *__restrict__ cat_ll, const double *__restrict__ site_ll /* + tile_off */,
+                double *__restrict__ cat_ll /* in: per-category lnL; out: mixing weights */,
+                const double *__restrict__ site_ll /* + tile_off */,
                 uint8_t *__restrict__ states_row /* + tile_off */, double *__restrict__ post_row /* nullable, [site][4] */)
 {
     int64_t site = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (site >= tile_len) return;
     double w[MAX_CAT];
     mix_weights(cat_ll, tile_pad, site, site_ll[site], M.n_cat, w);
+    for (int c = 0; c < M.n_cat; ++c) cat_ll[(size_t)c * tile_pad + site] = w[c]; // reused by every down level
     double mixed[4] = {0.0, 0.0, 0.0, 0.0};
     for (int c = 0; c < M.n_cat; ++c) {
         double *r = root_clv + (size_t)c * 4 * tile_pad + site;
@@ -633,66 +635,73 @@ asr_root_kernel(double *__restrict__ root_clv, size_t tile_pad, int tile_len, Mo
 
 constexpr int DOWN_MAX_CHILDREN = 2; // register fast path; larger arities loop in chunks
 
+// One block = (parent node, 512 sites); one thread = a site PAIR (16-byte accesses on the site axis).
+// `mixw` holds the per-site category weights exp(cat_ll_c - site_ll) (likelihood.rs:356-363), written
+// once per tile by asr_root_kernel into the cat_ll buffer, so no exp() runs here.
 __global__ void __launch_bounds__(ROOT_THREADS)
 asr_down_level_kernel(const DownOp *__restrict__ ops, int n_ops, const DownChild *__restrict__ kids,
                       ModelDev M, const double *__restrict__ Pmat, double *__restrict__ clv,
                       size_t slot_stride, size_t tile_pad, int tile_len, int blocks_per_row,
                       const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off,
-                      const double *__restrict__ cat_ll, const double *__restrict__ site_ll /* + tile_off */,
+                      const double *__restrict__ mixw,
                       uint8_t *__restrict__ states /* [node][P_pad] */, double *__restrict__ posteriors /* nullable [node][P_pad][4] */)
 {
-    int sb = blockIdx.x % blocks_per_row;
-    int opi = blockIdx.x / blocks_per_row;
+    const int sb = blockIdx.x % blocks_per_row;
+    const int opi = blockIdx.x / blocks_per_row;
     if (opi >= n_ops) return;
-    int64_t site = (int64_t)sb * blockDim.x + threadIdx.x;
+    const int64_t site = ((int64_t)sb * blockDim.x + threadIdx.x) * 2;
     if (site >= tile_len) return;
+    const bool has2 = site + 1 < tile_len;
     const DownOp op = ops[opi];
-    double w[MAX_CAT];
-    mix_weights(cat_ll, tile_pad, site, site_ll[site], M.n_cat, w);
     for (int k0 = op.child_begin; k0 < op.child_end; k0 += DOWN_MAX_CHILDREN) {
-        int nk = min(DOWN_MAX_CHILDREN, op.child_end - k0);
-        double mixed[DOWN_MAX_CHILDREN][4];
+        const int nk = min(DOWN_MAX_CHILDREN, op.child_end - k0);
+        double2 mixed[DOWN_MAX_CHILDREN][4];
 #pragma unroll
         for (int k = 0; k < DOWN_MAX_CHILDREN; ++k)
 #pragma unroll
-            for (int i = 0; i < 4; ++i) mixed[k][i] = 0.0;
+            for (int i = 0; i < 4; ++i) mixed[k][i] = make_double2(0.0, 0.0);
         for (int c = 0; c < M.n_cat; ++c) {
             const double *pp = clv + (size_t)op.parent_slot * slot_stride + (size_t)c * 4 * tile_pad + site;
-            double par[4];
+            double2 par[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) par[i] = pp[(size_t)i * tile_pad];
+            for (int i = 0; i < 4; ++i) par[i] = *reinterpret_cast<const double2 *>(pp + (size_t)i * tile_pad);
+            const double2 w = *reinterpret_cast<const double2 *>(mixw + (size_t)c * tile_pad + site);
 #pragma unroll
             for (int k = 0; k < DOWN_MAX_CHILDREN; ++k) {
                 if (k >= nk) break;
                 const DownChild ch = kids[k0 + k];
                 double p[16];
                 load_P(Pmat + ((size_t)ch.node * M.n_cat + c) * 16, p);
-                double up[4];
+                double2 up[4];
                 double *self = nullptr;
                 if (ch.is_tip) {
-                    uint32_t m = code_mask(tips[(int64_t)ch.src * P_pad + tile_off + site]);
+                    const uint8_t *tp = tips + (int64_t)ch.src * P_pad + tile_off + site;
+                    const uint32_t m0 = code_mask(tp[0]), m1 = code_mask(tp[1]); // site + 1 < P_pad always
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) up[i] = ((m >> i) & 1u) ? 1.0 : 0.0;
+                    for (int i = 0; i < 4; ++i) up[i] = make_double2(((m0 >> i) & 1u) ? 1.0 : 0.0, ((m1 >> i) & 1u) ? 1.0 : 0.0);
                 } else {
                     self = clv + (size_t)ch.src * slot_stride + (size_t)c * 4 * tile_pad + site;
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) up[i] = self[(size_t)i * tile_pad];
+                    for (int i = 0; i < 4; ++i) up[i] = *reinterpret_cast<const double2 *>(self + (size_t)i * tile_pad);
                 }
-                double post[4], sum = 0.0;
+                double2 post[4], sum = make_double2(0.0, 0.0);
 #pragma unroll
                 for (int i = 0; i < 4; ++i) { // msg_i = sum_j P[j][i] * par[j]  (P^T * post_parent)
-                    double msg = p[0 * 4 + i] * par[0] + p[1 * 4 + i] * par[1] + p[2 * 4 + i] * par[2] + p[3 * 4 + i] * par[3];
-                    post[i] = up[i] * msg;
-                    sum += post[i];
+                    const double mx = p[0 * 4 + i] * par[0].x + p[1 * 4 + i] * par[1].x + p[2 * 4 + i] * par[2].x + p[3 * 4 + i] * par[3].x;
+                    const double my = p[0 * 4 + i] * par[0].y + p[1 * 4 + i] * par[1].y + p[2 * 4 + i] * par[2].y + p[3 * 4 + i] * par[3].y;
+                    post[i] = make_double2(up[i].x * mx, up[i].y * my);
+                    sum.x += post[i].x;
+                    sum.y += post[i].y;
                 }
-                if (sum > 0.0) {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) post[i] /= sum;
-                }
+                // normalise (skipped when the sum is not > 0: the vector stays as it is, likelihood.rs:337-341)
+                const double ix = sum.x > 0.0 ? 1.0 / sum.x : 1.0, iy = sum.y > 0.0 ? 1.0 / sum.y : 1.0;
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    if (self) self[(size_t)i * tile_pad] = post[i];
-                    mixed[k][i] += w[c] * post[i];
+                    post[i].x *= ix; // one reciprocal per site instead of four divisions (<= 1 ulp apart)
+                    post[i].y *= iy;
+                    if (self) *reinterpret_cast<double2 *>(self + (size_t)i * tile_pad) = post[i];
+                    mixed[k][i].x += w.x * post[i].x;
+                    mixed[k][i].y += w.y * post[i].y;
                 }
             }
         }
@@ -700,16 +709,28 @@ asr_down_level_kernel(const DownOp *__restrict__ ops, int n_ops, const DownChild
         for (int k = 0; k < DOWN_MAX_CHILDREN; ++k) {
             if (k >= nk) break;
             const DownChild ch = kids[k0 + k];
-            double sum = mixed[k][0] + mixed[k][1] + mixed[k][2] + mixed[k][3];
-            if (sum > 0.0) {
+            double m0[4] = {mixed[k][0].x, mixed[k][1].x, mixed[k][2].x, mixed[k][3].x};
+            double m1[4] = {mixed[k][0].y, mixed[k][1].y, mixed[k][2].y, mixed[k][3].y};
+            const double s0 = m0[0] + m0[1] + m0[2] + m0[3], s1 = m1[0] + m1[1] + m1[2] + m1[3];
+            if (s0 > 0.0) { // renormalised before the argmax, as the reference does (likelihood.rs:376-390)
 #pragma unroll
-                for (int i = 0; i < 4; ++i) mixed[k][i] /= sum;
+                for (int i = 0; i < 4; ++i) m0[i] /= s0;
             }
-            states[(int64_t)ch.node * P_pad + tile_off + site] = (uint8_t)argmax_last(mixed[k]);
+            if (s1 > 0.0) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) m1[i] /= s1;
+            }
+            uint8_t *so = states + (int64_t)ch.node * P_pad + tile_off + site;
+            so[0] = (uint8_t)argmax_last(m0);
+            if (has2) so[1] = (uint8_t)argmax_last(m1);
             if (posteriors) {
                 double *o = posteriors + ((int64_t)ch.node * P_pad + tile_off + site) * 4;
 #pragma unroll
-                for (int i = 0; i < 4; ++i) o[i] = mixed[k][i];
+                for (int i = 0; i < 4; ++i) o[i] = m0[i];
+                if (has2) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) o[4 + i] = m1[i];
+                }
             }
         }
     }

@@ -254,6 +254,9 @@ struct phb_ctx {
     bool tree_uploaded = false;
     SweepSched sweep;      // fused-sweep op stream for (tree, n_clv)
     SweepGeom sweep_geom;
+    // marginal ASR: caller's output buffers, so that a finished tile's states go home while the next tile runs
+    uint8_t *asr_states_out = nullptr;
+    double *asr_post_out = nullptr;
     // stats
     phb_stats stats;
     int64_t launches = 0;
@@ -416,6 +419,8 @@ int plan_device(phb_ctx *ctx, Device &d, const ModelDev &M, bool asr, bool want_
             return ctx->fail(PHB_ERR_OOM, "CLV budget %zu B cannot hold one %d-site tile of %d slots", budget,
                              SITES_PER_BLOCK, n_slots);
     }
+    if (asr && d.P_pad >= 8 * 32768) // at least 8 tiles: the D2H of a finished tile overlaps the next tile's kernels
+        tile = std::min<int64_t>(tile, round_up((d.P_pad + 7) / 8, SITES_PER_BLOCK));
     d.tile_pad = tile;
     d.n_tiles = (int)((d.P + tile - 1) / tile);
     if (d.P == 0) d.n_tiles = 0;
@@ -494,6 +499,7 @@ int run_tile_down(phb_ctx *ctx, Device &d, const ModelDev &M, int64_t tile_off, 
     const size_t tile_pad = (size_t)d.tile_pad;
     const size_t slot_stride = (size_t)M.n_clv * 4 * tile_pad;
     const int bpr = (tile_len + ROOT_THREADS - 1) / ROOT_THREADS;
+    const int bpr2 = (tile_len + 2 * ROOT_THREADS - 1) / (2 * ROOT_THREADS); // down kernel: a site pair per thread
     uint8_t *states = d.states.as<uint8_t>();
     double *post = want_post ? d.posteriors.as<double>() : nullptr;
     {
@@ -509,11 +515,11 @@ int run_tile_down(phb_ctx *ctx, Device &d, const ModelDev &M, int64_t tile_off, 
         int nb = T.dlevel_off[dl + 1] - T.dlevel_off[dl];
         if (nb <= 0) continue;
         ScopedTimer tm(ctx, &d, PH_DOWN);
-        int64_t grid = (int64_t)nb * bpr;
+        int64_t grid = (int64_t)nb * bpr2;
         PHB_LAUNCH(asr_down_level_kernel, dim3((unsigned)grid), dim3(ROOT_THREADS), d.stream,
                    d.dops.as<DownOp>() + T.dlevel_off[dl], nb, d.dkids.as<DownChild>(), M, d.Pmat.as<double>(),
-                   d.clv.as<double>(), slot_stride, tile_pad, tile_len, bpr, d.tips.as<uint8_t>(), d.P_pad, tile_off,
-                   d.cat_ll.as<double>(), d.per_pattern.as<double>() + tile_off, states, post);
+                   d.clv.as<double>(), slot_stride, tile_pad, tile_len, bpr2, d.tips.as<uint8_t>(), d.P_pad, tile_off,
+                   d.cat_ll.as<double>(), states, post);
         CHECK_LAUNCH();
     }
     return PHB_OK;
@@ -724,6 +730,19 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total)
             if (asr) {
                 rc = run_tile_down(ctx, d, M, off, len, want_post);
                 if (rc) return rc;
+                if (ctx->asr_states_out) { // ship this tile's states (and posteriors) on the copy stream
+                    const int buf = t & 1;
+                    CU(cudaEventRecord(d.ev_free[buf], d.stream));
+                    CU(cudaStreamWaitEvent(d.copy_stream, d.ev_free[buf], 0));
+                    const int64_t Ptot = ctx->n_patterns;
+                    CU(cudaMemcpy2DAsync(ctx->asr_states_out + d.p_begin + off, (size_t)Ptot, d.states.as<uint8_t>() + off,
+                                         (size_t)d.P_pad, (size_t)len, (size_t)T.n, cudaMemcpyDeviceToHost, d.copy_stream));
+                    if (ctx->asr_post_out && want_post)
+                        CU(cudaMemcpy2DAsync(ctx->asr_post_out + (d.p_begin + off) * 4, (size_t)Ptot * 4 * sizeof(double),
+                                             d.posteriors.as<double>() + off * 4, (size_t)d.P_pad * 4 * sizeof(double),
+                                             (size_t)len * 4 * sizeof(double), (size_t)T.n, cudaMemcpyDeviceToHost,
+                                             d.copy_stream));
+                }
             }
             part_off += (size_t)((len + ROOT_THREADS - 1) / ROOT_THREADS);
         }
@@ -743,6 +762,7 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total)
     for (Device &d : ctx->devs) { // rank-ordered host sum: deterministic
         CU(cudaSetDevice(d.ordinal));
         CU(cudaStreamSynchronize(d.stream));
+        if (asr && ctx->asr_states_out) CU(cudaStreamSynchronize(d.copy_stream));
         sum += *d.h_total;
     }
     *total = sum;
@@ -1247,22 +1267,14 @@ int32_t phb_get_per_pattern(phb_ctx *ctx, double *per_pattern)
 int32_t phb_marginal_asr(phb_ctx *ctx, uint8_t *states, double *posteriors, double *total)
 {
     if (!ctx || !total || !states) return PHB_ERR_INVALID_ARGUMENT;
+    // the outputs leave tile by tile on the copy stream while the next tile is computed (pinned host
+    // buffers get the full PCIe rate; pageable ones work, staged by the driver)
+    ctx->asr_states_out = states;
+    ctx->asr_post_out = posteriors;
     int rc = evaluate(ctx, true, posteriors != nullptr, total);
-    if (rc) return rc;
-    const int n = ctx->tree.n;
-    const int64_t P = ctx->n_patterns;
-    for (Device &d : ctx->devs) {
-        if (d.P == 0) continue;
-        CU(cudaSetDevice(d.ordinal));
-        CU(cudaMemcpy2DAsync(states + d.p_begin, (size_t)P, d.states.p, (size_t)d.P_pad, (size_t)d.P, (size_t)n,
-                             cudaMemcpyDeviceToHost, d.stream));
-        if (posteriors)
-            CU(cudaMemcpy2DAsync(posteriors + d.p_begin * 4, (size_t)P * 4 * sizeof(double), d.posteriors.p,
-                                 (size_t)d.P_pad * 4 * sizeof(double), (size_t)d.P * 4 * sizeof(double), (size_t)n,
-                                 cudaMemcpyDeviceToHost, d.stream));
-        CU(cudaStreamSynchronize(d.stream));
-    }
-    return PHB_OK;
+    ctx->asr_states_out = nullptr;
+    ctx->asr_post_out = nullptr;
+    return rc;
 }
 
 int32_t phb_score_nni(phb_ctx *ctx, int32_t n_moves, const int32_t *node_id, const uint8_t *left_ch, double *totals)

@@ -65,7 +65,10 @@ def run_asr(tag, n_taxa, n_sites, model, seed, reps):
     with capi.Context(flags=capi.FLAG_TIMING) as ctx:
         synthetic.load_into(ctx, tree, model_for(model))
         ctx.simulate_alignment(n_sites, seed=seed ^ 0xA11C)
-        states = np.zeros((tree["n_nodes"], n_sites), np.uint8)
+        import torch
+
+        states_t = torch.zeros((tree["n_nodes"], n_sites), dtype=torch.uint8, pin_memory=True)  # caller-owned, pinned
+        states = states_t.numpy()
         tot = capi.C.c_double(0.0)
 
         def call():
