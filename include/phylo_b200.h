@@ -51,6 +51,9 @@ extern "C" {
 /* Log-likelihood through the level-batched kernels that keep every CLV in HBM (the marginal-ASR up
  * pass always uses them) instead of the fused on-chip sweep. */
 #define PHB_FLAG_LEVEL_KERNELS (1ull << 2)
+/* phb_score_nni rescores every neighbour from scratch (the reference's caller loop) instead of walking
+ * v -> root against the cached CLVs of the base tree; for cross-checking the two. */
+#define PHB_FLAG_NNI_FULL (1ull << 3)
 
 /* ---- alignment layouts --------------------------------------------------------------------- */
 #define PHB_LAYOUT_PATTERN_MAJOR 0 /* bytes[pattern][row] — CompressedColumns.patterns, alignment.rs:129-138 */
@@ -181,6 +184,11 @@ typedef struct phb_stats {
     int32_t sweep_stages;      /* ... TMA ring depth                                                */
     int32_t sweep_block_sites; /* ... site patterns per CTA pass                                    */
     int64_t sweep_stream_bytes;/* ... bytes of the op-ordered P(t)/tip-table stream                 */
+    int32_t nni_path_moves;    /* last phb_score_nni: neighbours scored by the path-only kernel     */
+    int32_t nni_tiles;         /* ... CLV-cache tiles per device                                    */
+    int64_t nni_path_steps;    /* ... walk steps summed over those neighbours                       */
+    double nni_cache_bytes;    /* ... bytes of cached CLVs + subtree exponents per device (all tiles)*/
+    double nni_read_bytes;     /* ... algorithmic bytes the walks read (sibling CLVs, exponents, tips)*/
 } phb_stats;
 int32_t phb_get_stats(phb_ctx *ctx, phb_stats *out);
 

@@ -25,6 +25,7 @@ STATUS_NAMES = {
 FLAG_LITERAL_INVARIANT = 1 << 0
 FLAG_TIMING = 1 << 1
 FLAG_LEVEL_KERNELS = 1 << 2
+FLAG_NNI_FULL = 1 << 3
 LAYOUT_PATTERN_MAJOR = 0
 LAYOUT_ROW_MAJOR = 1
 
@@ -56,6 +57,8 @@ class Stats(C.Structure):
         ("ms_down", C.c_double), ("ms_total", C.c_double), ("clv_launches", C.c_int32),
         ("sweep_ops", C.c_int32), ("sweep_stack_levels", C.c_int32), ("sweep_smem_levels", C.c_int32),
         ("sweep_stages", C.c_int32), ("sweep_block_sites", C.c_int32), ("sweep_stream_bytes", C.c_int64),
+        ("nni_path_moves", C.c_int32), ("nni_tiles", C.c_int32), ("nni_path_steps", C.c_int64),
+        ("nni_cache_bytes", C.c_double), ("nni_read_bytes", C.c_double),
     ]
 
     def as_dict(self):

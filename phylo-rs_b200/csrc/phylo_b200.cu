@@ -8,6 +8,7 @@
 // so that a tile's CLVs fit in HBM, and launches the kernels of kernels.cuh level by level.
 #include "kernels.cuh"
 #include "sweep.cuh"
+#include "nni.cuh"
 #include "sweep_sched.h"
 #include "../../include/phylo_b200.h"
 
@@ -212,7 +213,7 @@ struct Device {
     DevBuf tips, mult, leaf_ls, inv_mask, per_pattern, row_invalid, Pmat, blen, clv, scale, cat_ll,
         partials, total, ops, gops, gkids, dops, dkids, leaf_rows, states, posteriors, staging,
         sim_pre, sim_parent, sim_depth, sim_leafrow, sim_stack, scratch, sw_descs, sw_blocks, sw_stream, sw_gstack,
-        sw_err, sw_ops;
+        sw_err, sw_ops, nni_exps, nni_partials, nni_totals, nni_moves, nni_steps;
     bool sweep_uploaded = false;
     int sm_count = 0;
     size_t smem_optin = 0;
@@ -799,6 +800,207 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total)
     return PHB_OK;
 }
 
+
+// ---- path-only NNI rescoring (nni.cuh) -----------------------------------------------------------
+// Host side: turns each valid move into a walk v -> root over the base tree, caches the base tree's
+// CLVs tile by tile with the level kernels, scores all walks of a tile with one launch per category
+// count, and sums the per-tile results per neighbour.  Only strictly binary trees take this path.
+bool nni_path_eligible(const phb_ctx *ctx)
+{
+    const TreeSched &T = ctx->tree;
+    const ModelDev &M = ctx->model;
+    return !(ctx->flags & PHB_FLAG_NNI_FULL) && T.gops.empty() && T.n_internal > 0 && M.n_clv >= 1 && M.n_clv <= 4;
+}
+
+int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uint8_t *left_ch, double *totals)
+{
+    const TreeSched &T = ctx->tree;
+    const ModelDev &M = ctx->model;
+    int rc = check_leaves(ctx);
+    if (rc) return rc;
+    if (!ctx->tree_uploaded) {
+        rc = upload_tree(ctx);
+        if (rc) return rc;
+    }
+    // pre-order rank of every node: neighbours are scored in DFS order of v
+    std::vector<int> rank(T.n, 0);
+    {
+        std::vector<int> st(1, T.root);
+        int r = 0;
+        while (!st.empty()) {
+            int v = st.back();
+            st.pop_back();
+            rank[v] = r++;
+            for (int k = T.child_off[v + 1] - 1; k >= T.child_off[v]; --k) st.push_back(T.children[k]);
+        }
+    }
+    std::vector<int> order;
+    order.reserve(n_moves);
+    for (int m = 0; m < n_moves; ++m) {
+        const int v = node_id[m];
+        totals[m] = NAN; // leaf / root / unknown id: NNI::nni errors (src/tree.rs:1213-1242)
+        if (v < 0 || v >= T.n || v == T.root || T.child_off[v + 1] - T.child_off[v] != 2) continue;
+        totals[m] = 0.0;
+        order.push_back(m);
+    }
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return rank[node_id[a]] < rank[node_id[b]]; });
+    std::vector<NniMove> moves;
+    std::vector<NniStep> steps;
+    moves.reserve(order.size());
+    double read_bytes_per_pattern = 0;
+    auto src_of = [&](int c) { return T.slot[c] < 0 ? T.leaf_row[c] : T.slot[c]; };
+    auto cost_of = [&](int c) { return T.slot[c] < 0 ? 1.0 : 36.0 * M.n_clv; };
+    auto other_child = [&](int par, int not_this) {
+        for (int k = T.child_off[par]; k < T.child_off[par + 1]; ++k)
+            if (T.children[k] != not_this) return T.children[k];
+        return -1;
+    };
+    for (int m : order) {
+        const int v = node_id[m];
+        const int p = T.parent[v];
+        const int k0 = T.children[T.child_off[v]], k1 = T.children[T.child_off[v] + 1];
+        const int c = left_ch[m] ? k1 : k0; // `left_ch as usize` indexes the child list: true => children[1]
+        const int a = left_ch[m] ? k0 : k1;
+        const int s = other_child(p, v);    // first child of p that is not v
+        NniMove mv;
+        memset(&mv, 0, sizeof mv);
+        mv.out = m;
+        mv.a_src = src_of(a);
+        mv.a_edge = a;
+        mv.a_is_tip = T.slot[a] < 0;
+        mv.step_begin = (int)steps.size();
+        read_bytes_per_pattern += cost_of(a);
+        auto push = [&](int sib, int up_node) {
+            NniStep st;
+            st.sib_src = src_of(sib);
+            st.sib_edge = sib;
+            st.sib_is_tip = T.slot[sib] < 0;
+            st.up_edge = up_node == T.root ? -1 : up_node;
+            steps.push_back(st);
+            read_bytes_per_pattern += cost_of(sib);
+        };
+        push(s, v);
+        push(c, p);
+        for (int g = p; g != T.root; g = T.parent[g]) push(other_child(T.parent[g], g), T.parent[g]);
+        mv.step_end = (int)steps.size();
+        moves.push_back(mv);
+    }
+    phb_stats &S = ctx->stats;
+    S.nni_path_moves = (int)moves.size();
+    S.nni_path_steps = (int64_t)steps.size();
+    S.nni_read_bytes = read_bytes_per_pattern * (double)ctx->n_patterns;
+    S.nni_tiles = 0;
+    S.nni_cache_bytes = 0;
+    if (moves.empty() || ctx->n_patterns == 0) return PHB_OK;
+    const int nm = (int)moves.size();
+    std::vector<std::vector<double>> dev_totals(ctx->devs.size());
+    for (size_t di = 0; di < ctx->devs.size(); ++di) {
+        Device &d = ctx->devs[di];
+        if (d.P == 0) continue;
+        CU(cudaSetDevice(d.ordinal));
+        CU(d.Pmat.ensure(sizeof(double) * 16 * (size_t)T.n * M.n_cat));
+        CU(d.leaf_ls.ensure(sizeof(double) * (size_t)d.P_pad));
+        CU(d.inv_mask.ensure((size_t)d.P_pad));
+        CU(d.nni_moves.ensure(sizeof(NniMove) * moves.size()));
+        CU(d.nni_steps.ensure(sizeof(NniStep) * steps.size()));
+        CU(d.nni_totals.ensure(sizeof(double) * (size_t)n_moves));
+        CU(cudaMemcpyAsync(d.nni_moves.p, moves.data(), sizeof(NniMove) * moves.size(), cudaMemcpyHostToDevice, d.stream));
+        CU(cudaMemcpyAsync(d.nni_steps.p, steps.data(), sizeof(NniStep) * steps.size(), cudaMemcpyHostToDevice, d.stream));
+        CU(cudaMemsetAsync(d.nni_totals.p, 0, sizeof(double) * (size_t)n_moves, d.stream));
+        // tile the pattern axis so that one tile's CLVs + subtree exponents fit the budget
+        const size_t per_site = (size_t)T.n_internal * M.n_clv * (4 * sizeof(double) + sizeof(int));
+        size_t budget = ctx->clv_budget;
+        if (!budget) {
+            size_t free_b = 0, total_b = 0;
+            CU(cudaMemGetInfo(&free_b, &total_b));
+            budget = (size_t)((double)(free_b + d.clv.cap + d.nni_exps.cap) * 0.85);
+        }
+        int64_t tile = d.P_pad;
+        if (per_site * (size_t)d.P_pad > budget) {
+            tile = (int64_t)(budget / per_site) / SITES_PER_BLOCK * SITES_PER_BLOCK;
+            if (tile < SITES_PER_BLOCK)
+                return ctx->fail(PHB_ERR_OOM, "CLV budget %zu B cannot hold one %d-site tile of %d cached nodes", budget,
+                                 SITES_PER_BLOCK, T.n_internal);
+        }
+        const int n_tiles = (int)((d.P + tile - 1) / tile);
+        const size_t tile_pad = (size_t)tile;
+        const size_t slot_stride = (size_t)M.n_clv * 4 * tile_pad;
+        CU(d.clv.ensure(sizeof(double) * slot_stride * (size_t)T.n_internal));
+        CU(d.nni_exps.ensure(sizeof(int) * (size_t)M.n_clv * tile_pad * (size_t)T.n_internal));
+        const int max_sb = (int)((std::min<int64_t>(tile, d.P) + NNI_THREADS - 1) / NNI_THREADS);
+        CU(d.nni_partials.ensure(sizeof(double) * (size_t)nm * (size_t)max_sb));
+        if (&d == &ctx->devs[0]) {
+            S.nni_tiles = n_tiles;
+            S.nni_cache_bytes = (double)per_site * (double)d.P;
+        }
+        {
+            ScopedTimer tm(ctx, &d, PH_TRANSITION);
+            int nthreads = T.n * M.n_cat;
+            PHB_LAUNCH(transition_kernel, dim3((nthreads + 127) / 128), dim3(128), d.stream, d.blen.as<double>(), T.n, M,
+                       d.Pmat.as<double>());
+            CHECK_LAUNCH();
+        }
+        if (!d.tip_constants_valid) {
+            int64_t groups = d.P_pad / 4;
+            PHB_LAUNCH(tip_constants_kernel, dim3((unsigned)((groups + 255) / 256)), dim3(256), d.stream,
+                       d.tips.as<uint8_t>(), d.P_pad, d.P_pad, d.leaf_rows.as<int32_t>(), (int)T.leaf_rows.size(), M,
+                       d.leaf_ls.as<double>(), d.inv_mask.as<uint8_t>());
+            CHECK_LAUNCH();
+            d.tip_constants_valid = true;
+            d.tip_constants_rows = T.leaf_rows;
+        }
+        for (int t = 0; t < n_tiles; ++t) {
+            const int64_t off = (int64_t)t * tile;
+            const int len = (int)std::min<int64_t>(tile, d.P - off);
+            const int bpr = (len + SITES_PER_BLOCK - 1) / SITES_PER_BLOCK;
+            for (int l = 1; l <= T.n_levels; ++l) { // cache the base tree's CLVs of this tile
+                const int nb = T.level_off[l] - T.level_off[l - 1];
+                if (nb <= 0) continue;
+                ScopedTimer tm(ctx, &d, PH_CLV);
+                PHB_LAUNCH(clv_cache_level_kernel, dim3((unsigned)((int64_t)nb * M.n_clv * bpr)), dim3(CLV_THREADS), d.stream,
+                           d.ops.as<NodeOp>() + T.level_off[l - 1], nb, M, d.Pmat.as<double>(), d.clv.as<double>(),
+                           slot_stride, tile_pad, len, bpr, d.tips.as<uint8_t>(), d.P_pad, off, d.nni_exps.as<int>());
+                CHECK_LAUNCH();
+            }
+            const int n_sb = (len + NNI_THREADS - 1) / NNI_THREADS;
+            const int chunk = std::max(1, (int)std::min<int64_t>(nm, (int64_t)0x7fffffff / std::max(n_sb, 1)));
+            for (int m0 = 0; m0 < nm; m0 += chunk) { // (the grid holds n_sb * moves-in-chunk CTAs)
+                const int cm = std::min(chunk, nm - m0);
+                ScopedTimer tm(ctx, &d, PH_DOWN);
+#define PHB_NNI_LAUNCH(NC)                                                                                             \
+    PHB_LAUNCH(nni_score_kernel<NC>, dim3((unsigned)((int64_t)n_sb * cm)), dim3(NNI_THREADS), d.stream,                \
+               d.nni_moves.as<NniMove>() + m0, cm, d.nni_steps.as<NniStep>(), M, d.Pmat.as<double>(), d.clv.as<double>(), \
+               slot_stride, tile_pad, len, d.nni_exps.as<int>(), d.tips.as<uint8_t>(), d.P_pad, off,                   \
+               d.leaf_ls.as<double>() + off, d.inv_mask.as<uint8_t>() + off, d.mult.as<double>() + off,                \
+               d.nni_partials.as<double>(), n_sb)
+                switch (M.n_clv) {
+                case 1: PHB_NNI_LAUNCH(1); break;
+                case 2: PHB_NNI_LAUNCH(2); break;
+                case 3: PHB_NNI_LAUNCH(3); break;
+                default: PHB_NNI_LAUNCH(4); break;
+                }
+#undef PHB_NNI_LAUNCH
+                CHECK_LAUNCH();
+                PHB_LAUNCH(nni_reduce_kernel, dim3(cm), dim3(ROOT_THREADS), d.stream, d.nni_moves.as<NniMove>() + m0,
+                           d.nni_partials.as<double>(), n_sb, d.nni_totals.as<double>());
+                CHECK_LAUNCH();
+            }
+        }
+        dev_totals[di].resize(n_moves);
+        CU(cudaMemcpyAsync(dev_totals[di].data(), d.nni_totals.p, sizeof(double) * (size_t)n_moves, cudaMemcpyDeviceToHost,
+                           d.stream));
+    }
+    for (size_t di = 0; di < ctx->devs.size(); ++di) { // rank-ordered host sum: deterministic
+        Device &d = ctx->devs[di];
+        if (d.P == 0) continue;
+        CU(cudaSetDevice(d.ordinal));
+        CU(cudaStreamSynchronize(d.stream));
+        for (const NniMove &mv : moves) totals[mv.out] += dev_totals[di][mv.out];
+    }
+    S.kernel_launches = ctx->launches;
+    return PHB_OK;
+}
+
 } // namespace
 
 // =================================================================================================
@@ -1281,8 +1483,16 @@ int32_t phb_score_nni(phb_ctx *ctx, int32_t n_moves, const int32_t *node_id, con
 {
     if (!ctx || n_moves < 0 || (n_moves > 0 && (!node_id || !left_ch || !totals))) return PHB_ERR_INVALID_ARGUMENT;
     if (!ctx->tree.valid) return ctx->fail(PHB_ERR_STATE, "score_nni: set_tree first");
-    // Round-1 implementation: each neighbour is re-scheduled and scored from scratch (what the
-    // reference's caller loop does); path-only rescoring is the f2 follow-up.
+    if (!ctx->have_aln || !ctx->have_model)
+        return ctx->fail(PHB_ERR_STATE, "score_nni: set_alignment and set_model first");
+    ctx->stats.nni_path_moves = 0;
+    ctx->stats.nni_path_steps = 0;
+    ctx->stats.nni_tiles = 0;
+    ctx->stats.nni_cache_bytes = ctx->stats.nni_read_bytes = 0;
+    // Binary trees: walk v -> root against the cached CLVs of the base tree (nni.cuh).
+    if (nni_path_eligible(ctx)) return score_nni_paths(ctx, n_moves, node_id, left_ch, totals);
+    // Otherwise (polytomies / unifurcations, PHB_FLAG_NNI_FULL): each neighbour is re-scheduled and scored
+    // from scratch, which is what the reference's caller loop does.
     TreeSched base = ctx->tree;
     int rc = PHB_OK;
     for (int m = 0; m < n_moves && rc == PHB_OK; ++m) {

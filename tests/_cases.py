@@ -66,3 +66,35 @@ def check_asr(lib, case, want_post=False, **kw):
     if want_post:
         assert np.max(np.abs(post - ref_post)) <= 1e-9
     return int(diff.sum())
+
+
+def check_nni(lib, case, moves=None, flags=0, budget=None, devices=None, expect_path=True):
+    """phb_score_nni against the oracle run on each rebuilt neighbour tree (the reference's caller loop:
+    clone, NNI::nni src/tree.rs:1213-1242, log_likelihood).  Returns (totals, stats)."""
+    ft = case.ft
+    if moves is None:
+        moves = [(v, lc) for v in range(ft["n_nodes"]) for lc in (0, 1)]
+    with capi.Context(devices=devices, flags=flags, library=lib) as ctx:
+        if budget:
+            ctx.set_clv_budget(budget)
+        workloads.load_into(ctx, case)
+        base = ctx.log_likelihood()
+        got = ctx.score_nni([m[0] for m in moves], [m[1] for m in moves])
+        st = ctx.stats()
+        assert ctx.log_likelihood() == base  # the base tree is untouched
+    ids = ft["ids"]
+    n_valid = 0
+    for (v, lc), val in zip(moves, got):
+        t = case.tree.clone()
+        if not (0 <= v < ft["n_nodes"]) or t.nni(int(ids[v]), bool(lc)):
+            assert np.isnan(val)
+            continue
+        n_valid += 1
+        ref, _ = oracle.log_likelihood_flat(workloads.flatten_fast(t, case.leaf_order), case.model, case.patterns, case.mult,
+                                            mode=2, n_threads=8)
+        if np.isfinite(ref):
+            assert abs(val - ref) <= REL_TOL * abs(ref), (v, lc, val, ref)
+        else:
+            assert val == ref
+    assert st["nni_path_moves"] == (n_valid if expect_path else 0)
+    return got, st

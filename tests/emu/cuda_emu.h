@@ -30,6 +30,7 @@ struct dim3 {
 struct alignas(16) double2 { double x, y; };
 struct uchar2 { unsigned char x, y; };
 struct alignas(16) int4 { int x, y, z, w; };
+struct alignas(8) int2 { int x, y; };
 struct uchar4 { unsigned char x, y, z, w; };
 struct uint2 { unsigned int x, y; };
 static inline double2 make_double2(double x, double y) { double2 r; r.x = x; r.y = y; return r; }

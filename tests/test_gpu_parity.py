@@ -178,19 +178,69 @@ def test_errors_and_empty(gpu_lib):
 
 
 def test_score_nni(gpu_lib):
+    """Path-only NNI rescoring (csrc/nni.cuh) vs the oracle on every rebuilt neighbour; vs full rescoring."""
     case = workloads.make_case(16, 500, model="gtr_g4", seed=28)
+    got, st = _cases.check_nni(gpu_lib, case)
+    assert st["nni_path_steps"] > 0
+    full, _ = _cases.check_nni(gpu_lib, case, flags=capi.FLAG_NNI_FULL, expect_path=False)
+    ok = np.isfinite(got)
+    assert np.array_equal(ok, np.isfinite(full))
+    assert np.max(np.abs(got[ok] - full[ok]) / np.abs(full[ok])) < 1e-12
+
+
+@pytest.mark.parametrize("model,amb", [("jc69", 0.0), ("gtr_i_g4", 0.1)])
+def test_score_nni_models_tiling(gpu_lib, model, amb):
+    case = workloads.make_case(20, 3000, model=model, seed=41, ambiguity=amb)
+    n_clv = 1 if model == "jc69" else 4
+    got, st = _cases.check_nni(gpu_lib, case, budget=19 * n_clv * 36 * 1024 + 1)
+    assert st["nni_tiles"] == 3
+    one, _ = _cases.check_nni(gpu_lib, case)
+    ok = np.isfinite(got)
+    assert np.max(np.abs(got[ok] - one[ok]) / np.abs(one[ok])) < 1e-13
+
+
+def test_score_nni_deep_tree(gpu_lib):
+    """800 taxa (subtree likelihoods below 2^-256: cached exponents + the walk's own rescales)."""
+    case = workloads.make_case(800, 300, model="gtr_i_g4", seed=43)
     ft = case.ft
-    moves = [(v, lc) for v in range(ft["n_nodes"]) for lc in (0, 1)]
+    rng = np.random.default_rng(6)
+    internal = [v for v in range(ft["n_nodes"]) if ft["child_off"][v + 1] > ft["child_off"][v]]
+    moves = [(int(v), int(lc)) for v in rng.choice(internal, 48, replace=False) for lc in (0, 1)]
+    _cases.check_nni(gpu_lib, case, moves=moves)
+
+
+def test_score_nni_full_size_config5_properties(gpu_lib):
+    """configs[4] at FULL size (2,000 taxa x 200k sites, GTR+G4; 1,024 neighbours) through size-independent
+    properties: path-only scores of a neighbour sample == full rescoring of the rebuilt tree (<= 1e-11 relative),
+    a forced 3-way tiling gives the same totals, and nni(v,0)/nni(v,1) of the same v differ from the base."""
+    from phylo_rs_b200 import synthetic
+    tree = synthetic.yule_flat(2000, 0x5EED0005)
+    model = synthetic.gtr_model(alpha=0.5, k=4)
+    co = tree["child_off"]
+    internal = [v for v in range(tree["n_nodes"]) if co[v + 1] > co[v] and v != tree["root"]]
+    moves = [(v, lc) for v in internal for lc in (0, 1)][:1024]
+    ids, left = [m[0] for m in moves], [m[1] for m in moves]
     with capi.Context(library=gpu_lib) as ctx:
-        workloads.load_into(ctx, case)
-        got = ctx.score_nni([m[0] for m in moves], [m[1] for m in moves])
-    for (v, lc), val in zip(moves, got):
-        t = case.tree.clone()
-        if t.nni(int(ft["ids"][v]), bool(lc)):
-            assert np.isnan(val)
-            continue
-        ref, _ = oracle.log_likelihood_flat(workloads.flatten_fast(t, case.leaf_order), case.model, case.patterns, case.mult)
-        assert abs(val - ref) <= 1e-9 * abs(ref)
+        synthetic.load_into(ctx, tree, model)
+        ctx.simulate_alignment(200_000, seed=0x5EED0005 ^ 0xA11C)
+        base = ctx.log_likelihood()
+        got = ctx.score_nni(ids, left)
+        st = ctx.stats()
+        assert st["nni_path_moves"] == 1024 and st["nni_tiles"] == 1
+        ctx.set_clv_budget(int(st["nni_cache_bytes"] / 2.5))
+        tiled = ctx.score_nni(ids, left)
+        assert ctx.stats()["nni_tiles"] == 3
+        assert np.max(np.abs(tiled - got) / np.abs(got)) < 1e-13
+        ctx.set_clv_budget(0)
+        assert ctx.log_likelihood() == base
+    assert np.all(np.isfinite(got)) and np.all(got != base)
+    sample = list(range(0, 1024, 128))
+    with capi.Context(library=gpu_lib, flags=capi.FLAG_NNI_FULL) as ctx:
+        synthetic.load_into(ctx, tree, model)
+        ctx.simulate_alignment(200_000, seed=0x5EED0005 ^ 0xA11C)
+        full = ctx.score_nni([ids[i] for i in sample], [left[i] for i in sample])
+        assert ctx.stats()["nni_path_moves"] == 0
+    assert np.max(np.abs(full - got[sample]) / np.abs(full)) < 1e-11
 
 
 def test_full_size_properties_config2(gpu_lib):

@@ -185,24 +185,49 @@ def test_multiplicity_weights(emu_lib):
 
 
 def test_score_nni_matches_rebuilt_trees(emu_lib):
+    """Path-only rescoring (csrc/nni.cuh) == the oracle on every rebuilt neighbour, incl. leaf/root moves (NaN)."""
     case = workloads.make_case(10, 150, model="gtr_g4", seed=12)
+    got, st = _cases.check_nni(emu_lib, case)
+    assert st["nni_tiles"] == 1 and st["nni_path_steps"] > 0
+    full, st_full = _cases.check_nni(emu_lib, case, flags=capi.FLAG_NNI_FULL, expect_path=False)
+    ok = np.isfinite(got)
+    assert np.array_equal(ok, np.isfinite(full))
+    assert np.max(np.abs(got[ok] - full[ok]) / np.abs(full[ok])) < 1e-12
+
+
+@pytest.mark.parametrize("model,amb", [("jc69", 0.0), ("gtr_i_g4", 0.1)])
+def test_score_nni_models_ambiguity_tiling(emu_lib, model, amb):
+    case = workloads.make_case(14, 1300, model=model, seed=31, ambiguity=amb, compress=(amb == 0.0))
+    n_int = 13
+    n_clv = 1 if model == "jc69" else 4
+    budget = n_int * n_clv * 36 * 512 + 1  # one 512-pattern tile of cached CLVs + exponents
+    got, st = _cases.check_nni(emu_lib, case, budget=budget)
+    assert st["nni_tiles"] == (len(case.patterns) + 511) // 512
+    one, _ = _cases.check_nni(emu_lib, case)
+    ok = np.isfinite(got)
+    assert np.max(np.abs(got[ok] - one[ok]) / np.abs(one[ok])) < 1e-13
+
+
+def test_score_nni_deep_tree_rescaling(emu_lib):
+    """600 taxa: subtree likelihoods fall below 2^-256, so the cached subtree exponents and the walk's own
+    rescales both take part."""
+    case = workloads.make_case(600, 24, model="gtr_g4", seed=33)
     ft = case.ft
-    moves = [(v, lc) for v in range(ft["n_nodes"]) for lc in (0, 1)]
-    with capi.Context(library=emu_lib) as ctx:
-        workloads.load_into(ctx, case)
-        base = ctx.log_likelihood()
-        got = ctx.score_nni([m[0] for m in moves], [m[1] for m in moves])
-        assert ctx.log_likelihood() == base  # the base tree is restored
-    ids = ft["ids"]
-    for (v, lc), val in zip(moves, got):
-        t = case.tree.clone()
-        err = t.nni(int(ids[v]), bool(lc))
-        if err:
-            assert np.isnan(val)
-            continue
-        ft2 = workloads.flatten_fast(t, case.leaf_order)
-        ref, _ = oracle.log_likelihood_flat(ft2, case.model, case.patterns, case.mult)
-        assert abs(val - ref) <= 1e-9 * abs(ref)
+    rng = np.random.default_rng(5)
+    internal = [v for v in range(ft["n_nodes"]) if ft["child_off"][v + 1] > ft["child_off"][v]]
+    moves = [(int(v), int(lc)) for v in rng.choice(internal, 40, replace=False) for lc in (0, 1)]
+    _cases.check_nni(emu_lib, case, moves=moves)
+
+
+def test_score_nni_polytomy_falls_back(emu_lib):
+    tree = parse_newick("((A:0.1,B:0.2,C:0.05)X:0.1,(D:0.3,E:0.1)Y:0.2)R;")
+    aln = RefAlignment.from_fasta_bytes(b">A\nACGTAC\n>B\nACGTTC\n>C\nAGGTAC\n>D\nACCTAC\n>E\nTCGTAC\n")
+    m = RefModel.gtr([.3, .2, .2, .3], [1, 2.5, 1, 1, 2.5, 1]).with_gamma(0.5, 4)
+    pats, _s2p, mult, lo = aln.compress_columns()
+    case = workloads.Case(tree, oracle.flatten(tree, lo), m, "gtr_g4", pats, mult, lo)
+    ft = case.ft
+    # moves on binary nodes only: the full-rescoring fallback treats nodes of other arity as invalid too
+    _cases.check_nni(emu_lib, case, expect_path=False)
 
 
 def test_simulated_alignment_roundtrip(emu_lib):

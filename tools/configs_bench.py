@@ -89,26 +89,29 @@ def run_asr(tag, n_taxa, n_sites, model, seed, reps):
                 states_d2h_bytes=int(states.nbytes), state_histogram=np.bincount(states[:, :4096].ravel(), minlength=4).tolist())
 
 
-def run_nni(tag, n_taxa, n_sites, model, seed, n_moves, reps):
+def run_nni(tag, n_taxa, n_sites, model, seed, n_moves, reps, flags=0):
     tree = synthetic.yule_flat(n_taxa, seed)
     co = tree["child_off"]
     internal = [v for v in range(tree["n_nodes"]) if co[v + 1] > co[v] and v != tree["root"]]
     moves = [(v, left) for v in internal for left in (0, 1)][:n_moves]
-    with capi.Context() as ctx:
+    with capi.Context(flags=flags | capi.FLAG_TIMING) as ctx:
         synthetic.load_into(ctx, tree, model_for(model))
         ctx.simulate_alignment(n_sites, seed=seed ^ 0xA11C)
         base = ctx.log_likelihood()
         ids, left = [m[0] for m in moves], [m[1] for m in moves]
-        t0 = time.perf_counter()
-        out = ctx.score_nni(ids, left)
-        wall_ms = (time.perf_counter() - t0) * 1e3
+        out, dev_ms, wall_ms = timed(ctx, lambda: ctx.score_nni(ids, left), reps if not flags else 1)
+        st = ctx.stats()
         t0 = time.perf_counter()
         ctx.log_likelihood()
         full_ms = (time.perf_counter() - t0) * 1e3
     return dict(case=tag, taxa=n_taxa, patterns=n_sites, model=model, n_moves=len(moves), base_lnl=base,
-                best_delta=float(np.nanmax(out) - base), wall_ms=wall_ms, ms_per_neighbour=wall_ms / len(moves),
+                best_delta=float(np.nanmax(out) - base), wall_ms=wall_ms, device_ms=dev_ms, ms_per_neighbour=wall_ms / len(moves),
                 full_evaluation_ms=full_ms, trees_per_s=len(moves) / (wall_ms * 1e-3),
-                equivalent_updates_per_s=len(moves) * (n_taxa - 1) * n_sites / (wall_ms * 1e-3))
+                equivalent_updates_per_s=len(moves) * (n_taxa - 1) * n_sites / (wall_ms * 1e-3),
+                path="full rescoring" if flags else "path-only walks over cached CLVs",
+                nni_path_moves=st["nni_path_moves"], nni_path_steps=st["nni_path_steps"], nni_tiles=st["nni_tiles"],
+                nni_cache_GB=st["nni_cache_bytes"] / 1e9, nni_read_GB=st["nni_read_bytes"] / 1e9,
+                walk_read_GBps=st["nni_read_bytes"] / (dev_ms * 1e-3) / 1e9)
 
 
 CASES = {
@@ -122,13 +125,15 @@ CASES = {
     "cfg4": lambda r: run_asr("cfg4 marginal ASR GTR+G4 5000 x 500k", 5000, 500_000, "gtr_g4", 0x5EED0004, r),
     "cfg4_small": lambda r: run_asr("cfg4/10 marginal ASR GTR+G4 5000 x 50k", 5000, 50_000, "gtr_g4", 0x5EED0004, r),
     "cfg5": lambda r: run_nni("cfg5 1024 NNI neighbours 2000 x 200k", 2000, 200_000, "gtr_g4", 0x5EED0005, 1024, r),
+    "cfg5_full_128": lambda r: run_nni("cfg5/8 128 NNI neighbours 2000 x 200k, full rescoring", 2000, 200_000, "gtr_g4",
+                                       0x5EED0005, 128, r, capi.FLAG_NNI_FULL),
     "cfg5_small": lambda r: run_nni("cfg5/8 128 NNI neighbours 2000 x 200k", 2000, 200_000, "gtr_g4", 0x5EED0005, 128, r),
 }
 
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--cases", default="cfg1,cfg2,cfg3_rank8,cfg4_small,cfg5_small")
+    ap.add_argument("--cases", default="cfg1,cfg2,cfg3_rank8,cfg4_small,cfg5")
     ap.add_argument("--reps", type=int, default=3)
     args = ap.parse_args()
     for name in args.cases.split(","):
