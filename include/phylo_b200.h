@@ -141,6 +141,14 @@ int32_t phb_marginal_asr(phb_ctx *ctx, uint8_t *states, double *posteriors, doub
  * The exact identity when rates[c] * t[k] == 0.0.  Requires set_model. */
 int32_t phb_transition_matrices(phb_ctx *ctx, int32_t n_t, const double *t, double *out);
 
+/* Replaces compute_joint_asr (src/tree/likelihood.rs:421-560; trait JointAsr::joint_asr src/tree/asr.rs:30-37,
+ * impl src/tree.rs:58-66): Viterbi reconstruction per rate category in log space, the category with the
+ * greatest ln(weight) + root maximum wins (first on ties), states by traceback.  states: [n_nodes][n_patterns]
+ * state indices 0..3 for EVERY node; a pattern for which no category has a value > -inf keeps state 0
+ * everywhere, as in the reference.  *total = sum_p multiplicity_p * best value_p (Reconstruction.log_likelihood);
+ * the per-pattern best values are available through phb_get_per_pattern. */
+int32_t phb_joint_asr(phb_ctx *ctx, uint8_t *states, double *total);
+
 /* Per-pattern log-likelihoods of the most recent evaluation (either entry point). */
 int32_t phb_get_per_pattern(phb_ctx *ctx, double *per_pattern);
 

@@ -79,6 +79,8 @@ def lib():
     L.orc_log_likelihood.restype = C.c_int
     L.orc_marginal_asr.argtypes = tree_args + model_args + aln_args + [C.c_int, C.POINTER(C.c_uint8), dp, dp, dp]
     L.orc_marginal_asr.restype = C.c_int
+    L.orc_joint_asr.argtypes = tree_args + model_args + aln_args + [C.c_int, C.POINTER(C.c_uint8), dp, dp]
+    L.orc_joint_asr.restype = C.c_int
     L.orc_bruteforce_site_likelihood.argtypes = [C.c_int, ip, ip, ip, dp, ip, C.c_int,
                                                  C.POINTER(_RateMatrix), C.c_double, C.POINTER(C.c_uint8)]
     L.orc_bruteforce_site_likelihood.restype = C.c_double
@@ -327,6 +329,63 @@ def marginal_asr_flat(ft, model, patterns, mult=None, want_posteriors=False, n_t
     if rc:
         raise OracleError(rc)
     return tot.value, per[:P], states[:, :P], (None if post is None else post[:, :P])
+
+
+def joint_asr_flat(ft, model, patterns, mult=None, n_threads=1):
+    """compute_joint_asr (src/tree/likelihood.rs:421-560) on a flattened tree.
+    Returns (total, per_pattern best ln(weight)+Viterbi value, states [node][P] uint8)."""
+    patterns = np.ascontiguousarray(patterns, np.uint8)
+    P, rows = patterns.shape
+    n = int(ft["n_nodes"])
+    rates, weights = np.ascontiguousarray(model.rates), np.ascontiguousarray(model.weights)
+    per = np.zeros(max(P, 1), np.float64)
+    states = np.zeros((n, max(P, 1)), np.uint8)
+    tot = C.c_double(0.0)
+    m = None if mult is None else np.ascontiguousarray(mult, np.uint64)
+    rc = lib().orc_joint_asr(
+        *_tree_args(ft), C.byref(model.rm), len(rates), _dp(rates), _dp(weights), rows, P,
+        patterns.ctypes.data_as(C.POINTER(C.c_uint8)),
+        None if m is None else m.ctypes.data_as(C.POINTER(C.c_uint64)),
+        int(n_threads), states.ctypes.data_as(C.POINTER(C.c_uint8)), C.byref(tot), _dp(per))
+    if rc:
+        raise OracleError(rc)
+    return tot.value, per[:P], states[:, :P]
+
+
+def joint_asr(tree, model, aln):
+    """JointAsr::joint_asr for PhyloTree (src/tree.rs:58-66) -> dict like Reconstruction (posteriors None)."""
+    patterns, s2p, mult, leaf_order = aln.compress_columns()
+    ft = flatten(tree, leaf_order)
+    tot, _per, states = joint_asr_flat(ft, model, patterns, mult)
+    seqs = {}
+    for k, nid in enumerate(ft["ids"]):
+        seqs[int(nid)] = states[k][s2p].astype(np.int64) if len(s2p) else np.zeros(0, np.int64)
+    return dict(sequences=seqs, posteriors=None, log_likelihood=tot)
+
+
+def joint_assignment_value(ft, model, pattern, states):
+    """max over categories of ln w_c + ln pi[root state] + sum over edges ln P_c[s_parent][s_child] + sum over
+    leaves ln profile[s_leaf]: the joint value compute_joint_asr maximises, evaluated for ONE given assignment
+    (pure Python; used to audit ties)."""
+    n = int(ft["n_nodes"])
+    co, ch, blen, leaf_row, root = ft["child_off"], ft["children"], ft["blen"], ft["leaf_row"], int(ft["root"])
+    best = -np.inf
+    with np.errstate(divide="ignore", invalid="ignore"):
+        for r, w in zip(model.rates, model.weights):
+            val = np.log(w) + np.log(model.rm.pi[int(states[root])])
+            for v in range(n):
+                for k in range(co[v], co[v + 1]):
+                    c = int(ch[k])
+                    P = np.zeros(16)
+                    lib().orc_transition(C.byref(model.rm), float(r * blen[c]), _dp(P))
+                    val += np.log(P[4 * int(states[v]) + int(states[c])])
+                if co[v + 1] == co[v]:
+                    prof = np.zeros(4)
+                    lib().orc_nucleotide_profile(int(pattern[leaf_row[v]]), _dp(prof))
+                    val += np.log(prof[int(states[v])])
+            if val > best:
+                best = val
+    return float(best)
 
 
 def log_likelihood(tree, model, aln):

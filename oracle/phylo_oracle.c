@@ -606,6 +606,103 @@ done:
     return NULL;
 }
 
+/* compute_joint_asr pattern loop, src/tree/likelihood.rs:421-560 (Viterbi in log space, per category;
+ * the category with the strictly greatest ln(weight) + root maximum wins, first on ties :525-527;
+ * first maximal index for every inner argmax :496-503, :517-523; no category with a finite value =>
+ * best_overall_states stays empty and every node keeps state 0 :458-459, :543-549).
+ * cvals: [n_nodes][NS], ptrs: [n_nodes][NS] (pointer of edge parent(v)->v, stored at v). */
+static void *joint_ref_worker(void *arg)
+{
+    orc_job *J = (orc_job *)arg;
+    const orc_tree *T = J->tree;
+    const int n = T->n_nodes, K = J->n_cat;
+    double *cvals = (double *)malloc(sizeof(double) * NS * (size_t)n);
+    int *ptrs = (int *)malloc(sizeof(int) * NS * (size_t)n);
+    int *st = (int *)malloc(sizeof(int) * (size_t)n);
+    int *best_states = (int *)malloc(sizeof(int) * (size_t)n);
+    double P[NS * NS];
+    for (int64_t p = J->p_begin; p < J->p_end; ++p) {
+        const uint8_t *pattern = J->patterns + (size_t)p * (size_t)J->n_rows;
+        double best_overall = -INFINITY;
+        int have_best = 0;
+        for (int c = 0; c < K; ++c) {
+            for (int k = 0; k < n; ++k) {
+                int v = T->postorder[k];
+                double *cv = cvals + (size_t)v * NS;
+                if (T->child_off[v + 1] == T->child_off[v]) {
+                    int pos = T->leaf_row[v];
+                    double prof[NS];
+                    if (pos < 0) {
+                        J->status = ORC_ERR_INVALID_ALIGNMENT; /* :469-473 */
+                        goto done;
+                    }
+                    if (!nucleotide_profile(pattern[pos], prof)) {
+                        J->status = ORC_ERR_ALPHABET_MISMATCH; /* :475-476 */
+                        goto done;
+                    }
+                    for (int i = 0; i < NS; ++i) /* :477-480 */
+                        cv[i] = prof[i] > 0.0 ? log(prof[i]) : -INFINITY;
+                } else {
+                    for (int i = 0; i < NS; ++i)
+                        cv[i] = 0.0;
+                    for (int ci = T->child_off[v]; ci < T->child_off[v + 1]; ++ci) {
+                        int ch = T->children[ci];
+                        const double *cc = cvals + (size_t)ch * NS;
+                        orc_transition(J->rm, J->rates[c] * T->blen[ch], P);
+                        for (int i = 0; i < NS; ++i) { /* :494-507 */
+                            double local_max = -INFINITY;
+                            int local_arg = 0;
+                            for (int j = 0; j < NS; ++j) {
+                                double val = log(P[i * NS + j]) + cc[j];
+                                if (val > local_max) {
+                                    local_max = val;
+                                    local_arg = j;
+                                }
+                            }
+                            cv[i] += local_max;
+                            ptrs[(size_t)ch * NS + i] = local_arg;
+                        }
+                    }
+                }
+            }
+            const double *rc = cvals + (size_t)T->root * NS;
+            int root_best = 0;
+            double root_max = -INFINITY;
+            for (int i = 0; i < NS; ++i) { /* :514-523 */
+                double ll = log(J->rm->pi[i]) + rc[i];
+                if (ll > root_max) {
+                    root_max = ll;
+                    root_best = i;
+                }
+            }
+            double cat_ll = log(J->weights[c]) + root_max;
+            if (cat_ll > best_overall) { /* :526-540 */
+                best_overall = cat_ll;
+                have_best = 1;
+                st[T->root] = root_best;
+                for (int k = 0; k < n; ++k) {
+                    int v = T->preorder[k];
+                    for (int ci = T->child_off[v]; ci < T->child_off[v + 1]; ++ci) {
+                        int ch = T->children[ci];
+                        st[ch] = ptrs[(size_t)ch * NS + st[v]];
+                    }
+                }
+                memcpy(best_states, st, sizeof(int) * (size_t)n);
+            }
+        }
+        J->per_pattern[p] = best_overall; /* :543 (the caller weights by multiplicity) */
+        if (J->states)
+            for (int v = 0; v < n; ++v)
+                J->states[(size_t)v * (size_t)J->n_patterns + (size_t)p] = have_best ? (uint8_t)best_states[v] : 0;
+    }
+done:
+    free(cvals);
+    free(ptrs);
+    free(st);
+    free(best_states);
+    return NULL;
+}
+
 /* ------------------------------------------------------------------------------------------
  * cpu_opt: same mathematics, P(t) cached per (edge, category), SoA blocks of OB patterns so the
  * inner loops vectorise, threads over pattern blocks.  The honest multi-core CPU competitor
@@ -826,6 +923,36 @@ int orc_marginal_asr(int n_nodes, const int *postorder, const int *preorder, con
     int status = run_jobs(asr_ref_worker, jobs, sizeof(orc_job), n_threads, n_patterns, 1);
     free(jobs);
     if (!status) {
+        double tot = 0.0;
+        for (int64_t p = 0; p < n_patterns; ++p)
+            tot += (mult ? (double)mult[p] : 1.0) * pp[p];
+        *total = tot;
+    }
+    if (!per_pattern)
+        free(pp);
+    return status;
+}
+
+int orc_joint_asr(int n_nodes, const int *postorder, const int *preorder, const int *child_off,
+                  const int *children, const int *parent, const double *blen, const int *leaf_row,
+                  int root, const orc_rate_matrix *rm, int n_cat, const double *rates,
+                  const double *weights, int n_rows, int64_t n_patterns, const uint8_t *patterns,
+                  const uint64_t *mult, int n_threads, uint8_t *states, double *total, double *per_pattern)
+{
+    orc_tree T = {n_nodes, postorder, preorder, child_off, children, parent, blen, leaf_row, root};
+    if (n_threads < 1)
+        n_threads = 1;
+    double *pp = per_pattern ? per_pattern : (double *)malloc(sizeof(double) * (size_t)(n_patterns > 0 ? n_patterns : 1));
+    orc_job *jobs = (orc_job *)calloc((size_t)n_threads, sizeof(orc_job));
+    for (int t = 0; t < n_threads; ++t) {
+        orc_job *J = &jobs[t];
+        J->tree = &T; J->rm = rm; J->n_cat = n_cat; J->rates = rates; J->weights = weights;
+        J->n_rows = n_rows; J->n_patterns = n_patterns; J->patterns = patterns; J->mult = mult;
+        J->per_pattern = pp; J->states = states;
+    }
+    int status = run_jobs(joint_ref_worker, jobs, sizeof(orc_job), n_threads, n_patterns, 1);
+    free(jobs);
+    if (!status) { /* likelihood.rs:543, sequential in pattern order */
         double tot = 0.0;
         for (int64_t p = 0; p < n_patterns; ++p)
             tot += (mult ? (double)mult[p] : 1.0) * pp[p];

@@ -74,6 +74,7 @@ def _lib():
             "phh_model_category_transition": [vp, sz, C.c_double, dp], "phh_discrete_gamma": [C.c_double, sz, dp],
             "phh_nucleotide_profile": [C.c_uint8, dp, ip],
             "phh_log_likelihood": [vp, vp, vp, dp], "phh_marginal_asr": [vp, vp, vp, C.c_int, vpp],
+            "phh_joint_asr": [vp, vp, vp, vpp],
             "phh_recon_sequence": [vp, sz, vp, sz, szp, ip], "phh_recon_posteriors": [vp, sz, vp, sz, ip],
             "phh_score_nni_neighbours": [vp, vp, vp, sz, vp, vp, dp],
         }
@@ -253,6 +254,12 @@ class PhyloTree(_Handle):
     def marginal_asr(self, model, aln, want_posteriors=False):
         h = C.c_void_p()
         _ck(_lib().phh_marginal_asr(self._h, model._h, aln._h, int(want_posteriors), C.byref(h)))
+        return Reconstruction(h, aln.width)
+
+    def joint_asr(self, model, aln):
+        """JointAsr::joint_asr (src/tree/asr.rs:30-37): Reconstruction with posteriors None."""
+        h = C.c_void_p()
+        _ck(_lib().phh_joint_asr(self._h, model._h, aln._h, C.byref(h)))
         return Reconstruction(h, aln.width)
 
     def score_nni_neighbours(self, model, aln, moves):

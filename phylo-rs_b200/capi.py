@@ -32,7 +32,7 @@ LAYOUT_ROW_MAJOR = 1
 # every symbol include/phylo_b200.h declares (checked by tests/test_abi.py)
 EXPORTS = [
     "phb_ctx_create", "phb_ctx_destroy", "phb_set_clv_budget", "phb_set_alignment", "phb_set_model",
-    "phb_set_tree", "phb_log_likelihood", "phb_marginal_asr", "phb_get_per_pattern", "phb_score_nni",
+    "phb_set_tree", "phb_log_likelihood", "phb_marginal_asr", "phb_joint_asr", "phb_get_per_pattern", "phb_score_nni",
     "phb_simulate_alignment", "phb_get_alignment", "phb_get_stats", "phb_measure_fp64_tflops",
     "phb_timer_start", "phb_timer_stop", "phb_transition_matrices", "phb_log_likelihood_host",
     "phb_last_error", "phb_version",
@@ -86,6 +86,7 @@ class Library:
         L.phb_log_likelihood.argtypes = [vp, dp, dp]
         L.phb_log_likelihood_host.argtypes = [vp, C.c_int32, C.c_int64, vp, C.c_int32, u64p, dp, dp]
         L.phb_marginal_asr.argtypes = [vp, u8p, dp, dp]
+        L.phb_joint_asr.argtypes = [vp, u8p, dp]
         L.phb_get_per_pattern.argtypes = [vp, dp]
         L.phb_score_nni.argtypes = [vp, C.c_int32, ip, u8p, dp]
         L.phb_simulate_alignment.argtypes = [vp, C.c_int64, C.c_int64, C.c_uint64]
@@ -247,6 +248,14 @@ class Context:
         if P == 0:
             return tot.value, states[:, :0], (None if post is None else post[:, :0])
         return tot.value, states, post
+
+    def joint_asr(self):
+        """phb_joint_asr: (Reconstruction.log_likelihood, states [node][pattern] uint8)."""
+        n, P = self.n_nodes, self.n_patterns
+        states = np.zeros((n, max(P, 1)), np.uint8)
+        tot = C.c_double(0.0)
+        self._check(self.lib.L.phb_joint_asr(self._h, states.ctypes.data_as(C.POINTER(C.c_uint8)), C.byref(tot)))
+        return tot.value, (states[:, :0] if P == 0 else states)
 
     def transition_matrices(self, t, n_cat):
         """P(rate_c * t_k) for every t_k and model category: [len(t)][n_cat][4][4] (device-evaluated)."""

@@ -9,6 +9,7 @@
 #include "kernels.cuh"
 #include "sweep.cuh"
 #include "nni.cuh"
+#include "joint.cuh"
 #include "sweep_sched.h"
 #include "../../include/phylo_b200.h"
 
@@ -57,6 +58,9 @@ struct TreeSched {
     std::vector<GenOp> gops;        // generic-arity updates, grouped by level
     std::vector<GenChild> gkids;
     std::vector<int> glevel_off;
+    std::vector<GenOp> uops;        // every internal node as an any-arity op, grouped by level (joint ASR)
+    std::vector<GenChild> ukids;
+    std::vector<int> ulevel_off;
     std::vector<DownOp> dops;       // ASR pre-order ops (one per internal node), grouped by depth
     std::vector<DownChild> dkids;
     std::vector<int> dlevel_off;    // max_depth + 1
@@ -129,9 +133,10 @@ struct TreeSched {
         std::vector<std::vector<int>> by_level(n_levels + 1);
         for (int v : post)
             if (level[v] > 0) by_level[level[v]].push_back(v);
-        ops.clear(); gops.clear(); gkids.clear();
+        ops.clear(); gops.clear(); gkids.clear(); uops.clear(); ukids.clear();
         level_off.assign(1, 0);
         glevel_off.assign(1, 0);
+        ulevel_off.assign(1, 0);
         sum_one_plus_i = 0;
         sum_t = 0;
         for (int l = 1; l <= n_levels; ++l) {
@@ -141,6 +146,23 @@ struct TreeSched {
                 for (int k = b; k < e; ++k) (slot[children[k]] >= 0 ? n_int : n_tip)++;
                 sum_one_plus_i += 1 + n_int;
                 sum_t += n_tip;
+                {
+                    GenOp u;
+                    u.out_slot = slot[v];
+                    u.child_begin = (int)ukids.size();
+                    for (int k = b; k < e; ++k) {
+                        int c = children[k];
+                        GenChild uc;
+                        uc.is_tip = slot[c] < 0;
+                        uc.src = uc.is_tip ? leaf_row[c] : slot[c];
+                        uc.edge = c;
+                        uc.pad = 0;
+                        ukids.push_back(uc);
+                    }
+                    u.child_end = (int)ukids.size();
+                    u.pad = 0;
+                    uops.push_back(u);
+                }
                 if (e - b == 2) {
                     int c0 = children[b], c1 = children[b + 1];
                     NodeOp op;
@@ -170,6 +192,7 @@ struct TreeSched {
             }
             level_off.push_back((int)ops.size());
             glevel_off.push_back((int)gops.size());
+            ulevel_off.push_back((int)uops.size());
         }
         // ASR pre-order ops grouped by the parent's depth
         std::vector<std::vector<int>> by_depth(max_depth + 1);
@@ -192,7 +215,7 @@ struct TreeSched {
                     dkids.push_back(dc);
                 }
                 o.child_end = (int)dkids.size();
-                o.pad = 0;
+                o.pad = v; // dense id of the parent: row of the states output (joint traceback)
                 dops.push_back(o);
             }
             dlevel_off.push_back((int)dops.size());
@@ -213,7 +236,7 @@ struct Device {
     DevBuf tips, mult, leaf_ls, inv_mask, per_pattern, row_invalid, Pmat, blen, clv, scale, cat_ll,
         partials, total, ops, gops, gkids, dops, dkids, leaf_rows, states, posteriors, staging,
         sim_pre, sim_parent, sim_depth, sim_leafrow, sim_stack, scratch, sw_descs, sw_blocks, sw_stream, sw_gstack,
-        sw_err, sw_ops, nni_exps, nni_partials, nni_totals, nni_moves, nni_steps;
+        sw_err, sw_ops, uops, ukids, lnP, jbest, nni_exps, nni_partials, nni_totals, nni_moves, nni_steps;
     bool sweep_uploaded = false;
     int sm_count = 0;
     size_t smem_optin = 0;
@@ -354,6 +377,8 @@ int upload_tree(phb_ctx *ctx)
         CU(up(d.gkids, T.gkids.data(), sizeof(GenChild) * T.gkids.size()));
         CU(up(d.dops, T.dops.data(), sizeof(DownOp) * T.dops.size()));
         CU(up(d.dkids, T.dkids.data(), sizeof(DownChild) * T.dkids.size()));
+        CU(up(d.uops, T.uops.data(), sizeof(GenOp) * T.uops.size()));
+        CU(up(d.ukids, T.ukids.data(), sizeof(GenChild) * T.ukids.size()));
         CU(up(d.leaf_rows, T.leaf_rows.data(), sizeof(int) * T.leaf_rows.size()));
         if (d.tip_constants_rows != T.leaf_rows) d.tip_constants_valid = false;
         // the host vectors stay alive in ctx->tree until the next set_tree, which first syncs
@@ -428,6 +453,10 @@ int plan_device(phb_ctx *ctx, Device &d, const ModelDev &M, bool asr, bool want_
     CU(d.clv.ensure(per_site * (size_t)tile));
     CU(d.scale.ensure(sizeof(int) * (size_t)std::max(M.n_clv, 1) * (size_t)tile));
     if (asr) CU(d.cat_ll.ensure(sizeof(double) * (size_t)M.n_cat * (size_t)tile));
+    if (asr) { // joint ASR: ln P table and the winning category per pattern
+        CU(d.lnP.ensure(sizeof(double) * 16 * (size_t)T.n * M.n_cat));
+        CU(d.jbest.ensure((size_t)tile));
+    }
     size_t n_part = 0;
     for (int t = 0; t < d.n_tiles; ++t) {
         int64_t len = std::min<int64_t>(tile, d.P - (int64_t)t * tile);
@@ -521,6 +550,49 @@ int run_tile_down(phb_ctx *ctx, Device &d, const ModelDev &M, int64_t tile_off, 
                    d.dops.as<DownOp>() + T.dlevel_off[dl], nb, d.dkids.as<DownChild>(), M, d.Pmat.as<double>(),
                    d.clv.as<double>(), slot_stride, tile_pad, tile_len, bpr2, d.tips.as<uint8_t>(), d.P_pad, tile_off,
                    d.cat_ll.as<double>(), states, post);
+        CHECK_LAUNCH();
+    }
+    return PHB_OK;
+}
+
+// Joint (Viterbi) ASR of one tile: max-plus up pass over all levels, root kernel, traceback (joint.cuh).
+int run_tile_joint(phb_ctx *ctx, Device &d, const ModelDev &M, int64_t tile_off, int tile_len, size_t part_off)
+{
+    const TreeSched &T = ctx->tree;
+    const size_t tile_pad = (size_t)d.tile_pad;
+    const size_t slot_stride = (size_t)M.n_clv * 4 * tile_pad; // literal categories: n_clv == n_cat
+    const int bpr = (tile_len + SITES_PER_BLOCK - 1) / SITES_PER_BLOCK;
+    uint8_t *states = d.states.as<uint8_t>();
+    for (int l = 1; l <= T.n_levels; ++l) {
+        const int nb = T.ulevel_off[l] - T.ulevel_off[l - 1];
+        if (nb <= 0) continue;
+        ScopedTimer tm(ctx, &d, PH_CLV);
+        PHB_LAUNCH(joint_up_level_kernel, dim3((unsigned)((int64_t)nb * M.n_cat * bpr)), dim3(CLV_THREADS), d.stream,
+                   d.uops.as<GenOp>() + T.ulevel_off[l - 1], nb, d.ukids.as<GenChild>(), M, d.lnP.as<double>(),
+                   d.clv.as<double>(), slot_stride, tile_pad, tile_len, bpr, d.tips.as<uint8_t>(), d.P_pad, tile_off);
+        CHECK_LAUNCH();
+        if (&d == &ctx->devs[0]) ctx->stats.clv_launches++;
+    }
+    {
+        ScopedTimer tm(ctx, &d, PH_ROOT);
+        const bool leaf_root = T.n_internal == 0;
+        const int root_slot = leaf_root ? 0 : T.slot[T.root];
+        PHB_LAUNCH(joint_root_kernel, dim3((tile_len + ROOT_THREADS - 1) / ROOT_THREADS), dim3(ROOT_THREADS), d.stream,
+                   d.clv.as<double>() + (size_t)root_slot * slot_stride, tile_pad, tile_len, M,
+                   leaf_root ? d.tips.as<uint8_t>() + (int64_t)T.leaf_row[T.root] * d.P_pad + tile_off : (const uint8_t *)nullptr,
+                   d.mult.as<double>() + tile_off, d.per_pattern.as<double>() + tile_off, d.jbest.as<uint8_t>(),
+                   states + (int64_t)T.root * d.P_pad + tile_off, d.partials.as<double>() + part_off);
+        CHECK_LAUNCH();
+    }
+    const int bpr1 = (tile_len + ROOT_THREADS - 1) / ROOT_THREADS;
+    for (int dl = 0; dl <= T.max_depth; ++dl) {
+        const int nb = T.dlevel_off[dl + 1] - T.dlevel_off[dl];
+        if (nb <= 0) continue;
+        ScopedTimer tm(ctx, &d, PH_DOWN);
+        PHB_LAUNCH(joint_down_level_kernel, dim3((unsigned)((int64_t)nb * bpr1)), dim3(ROOT_THREADS), d.stream,
+                   d.dops.as<DownOp>() + T.dlevel_off[dl], nb, d.dkids.as<DownChild>(), M, d.lnP.as<double>(),
+                   d.clv.as<double>(), slot_stride, tile_pad, tile_len, bpr1, d.tips.as<uint8_t>(), d.P_pad, tile_off,
+                   d.jbest.as<uint8_t>(), states);
         CHECK_LAUNCH();
     }
     return PHB_OK;
@@ -652,7 +724,7 @@ int run_sweep(phb_ctx *ctx, Device &d, const ModelDev &M)
 }
 
 // One full evaluation on every device.  asr=false: compute_log_likelihood; asr=true: + down pass.
-int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total)
+int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint = false)
 {
     if (!ctx->have_aln || !ctx->have_model || !ctx->tree.valid)
         return ctx->fail(PHB_ERR_STATE, "set_alignment, set_model and set_tree must precede an evaluation");
@@ -705,8 +777,14 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total)
             PHB_LAUNCH(transition_kernel, dim3((nthreads + 127) / 128), dim3(128), d.stream, d.blen.as<double>(), T.n, M,
                        d.Pmat.as<double>());
             CHECK_LAUNCH();
+            if (joint) {
+                const size_t n_ent = (size_t)16 * T.n * M.n_cat;
+                PHB_LAUNCH(log_transition_kernel, dim3((unsigned)((n_ent + 255) / 256)), dim3(256), d.stream,
+                           d.Pmat.as<double>(), n_ent, d.lnP.as<double>());
+                CHECK_LAUNCH();
+            }
         }
-        if (!d.tip_constants_valid) {
+        if (!d.tip_constants_valid && !joint) {
             ScopedTimer tm(ctx, &d, PH_ROOT);
             int64_t groups = d.P_pad / 4;
             PHB_LAUNCH(tip_constants_kernel, dim3((unsigned)((groups + 255) / 256)), dim3(256), d.stream,
@@ -726,10 +804,10 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total)
         for (int t = 0; t < d.n_tiles; ++t) {
             int64_t off = (int64_t)t * d.tile_pad;
             int len = (int)std::min<int64_t>(d.tile_pad, d.P - off);
-            rc = run_tile_up(ctx, d, M, off, len, part_off, asr);
+            rc = joint ? run_tile_joint(ctx, d, M, off, len, part_off) : run_tile_up(ctx, d, M, off, len, part_off, asr);
             if (rc) return rc;
             if (asr) {
-                rc = run_tile_down(ctx, d, M, off, len, want_post);
+                rc = joint ? PHB_OK : run_tile_down(ctx, d, M, off, len, want_post);
                 if (rc) return rc;
                 if (ctx->asr_states_out) { // ship this tile's states (and posteriors) on the copy stream
                     const int buf = t & 1;
@@ -1476,6 +1554,16 @@ int32_t phb_marginal_asr(phb_ctx *ctx, uint8_t *states, double *posteriors, doub
     int rc = evaluate(ctx, true, posteriors != nullptr, total);
     ctx->asr_states_out = nullptr;
     ctx->asr_post_out = nullptr;
+    return rc;
+}
+
+int32_t phb_joint_asr(phb_ctx *ctx, uint8_t *states, double *total)
+{
+    if (!ctx || !total || !states) return PHB_ERR_INVALID_ARGUMENT;
+    ctx->asr_states_out = states;
+    ctx->asr_post_out = nullptr;
+    int rc = evaluate(ctx, true, false, total, true);
+    ctx->asr_states_out = nullptr;
     return rc;
 }
 

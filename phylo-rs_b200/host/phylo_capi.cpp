@@ -303,6 +303,13 @@ int phh_marginal_asr(const void *t, const void *m, const void *a, int want_poste
             *static_cast<const GtrModel *>(m), *static_cast<const Alignment *>(a), want_posteriors != 0));
     });
 }
+int phh_joint_asr(const void *t, const void *m, const void *a, void **out)
+{
+    return guard([&] {
+        *out = new Reconstruction(static_cast<const PhyloTree *>(t)->joint_asr(*static_cast<const GtrModel *>(m),
+                                                                              *static_cast<const Alignment *>(a)));
+    });
+}
 void phh_recon_free(void *r) { delete static_cast<Reconstruction *>(r); }
 double phh_recon_log_likelihood(const void *r) { return static_cast<const Reconstruction *>(r)->log_likelihood; }
 size_t phh_recon_n_nodes(const void *r) { return static_cast<const Reconstruction *>(r)->sequences.size(); }

@@ -30,6 +30,7 @@ struct Api {
     decltype(&phb_log_likelihood) log_likelihood = nullptr;
     decltype(&phb_log_likelihood_host) log_likelihood_host = nullptr;
     decltype(&phb_marginal_asr) marginal_asr = nullptr;
+    decltype(&phb_joint_asr) joint_asr = nullptr;
     decltype(&phb_score_nni) score_nni = nullptr;
     decltype(&phb_transition_matrices) transition_matrices = nullptr;
     decltype(&phb_last_error) last_error = nullptr;
@@ -81,6 +82,7 @@ const Api &api()
     a.log_likelihood = reinterpret_cast<decltype(a.log_likelihood)>(sym("phb_log_likelihood"));
     a.log_likelihood_host = reinterpret_cast<decltype(a.log_likelihood_host)>(sym("phb_log_likelihood_host"));
     a.marginal_asr = reinterpret_cast<decltype(a.marginal_asr)>(sym("phb_marginal_asr"));
+    a.joint_asr = reinterpret_cast<decltype(a.joint_asr)>(sym("phb_joint_asr"));
     a.score_nni = reinterpret_cast<decltype(a.score_nni)>(sym("phb_score_nni"));
     a.transition_matrices = reinterpret_cast<decltype(a.transition_matrices)>(sym("phb_transition_matrices"));
     a.last_error = reinterpret_cast<decltype(a.last_error)>(sym("phb_last_error"));
@@ -319,6 +321,27 @@ Reconstruction PhyloTree::marginal_asr(const GtrModel &model, const Alignment &a
                 std::memcpy(pp[s].data(), prow + comp.site_to_pattern[s] * 4, sizeof(double) * 4);
             rec.posteriors->emplace(flat.ids[k], std::move(pp));
         }
+    }
+    return rec;
+}
+
+// =====================================================================================================
+// JointAsr::joint_asr (compute_joint_asr, likelihood.rs:421-560): posteriors stay None (:553-558)
+// =====================================================================================================
+Reconstruction PhyloTree::joint_asr(const GtrModel &model, const Alignment &aln) const
+{
+    CompressedColumns comp;
+    Flat flat;
+    phb_ctx *c = load_all(*this, model, aln, comp, flat);
+    const std::size_t n = flat.ids.size(), P = comp.patterns.size(), width = aln.width;
+    std::vector<std::uint8_t> states(std::max<std::size_t>(n * P, 1));
+    Reconstruction rec;
+    check(c, api().joint_asr(c, states.data(), &rec.log_likelihood));
+    for (std::size_t k = 0; k < n; ++k) { // every node id gets an entry (:453-456), expanded to sites (:545-551)
+        std::vector<std::size_t> seq(width, 0);
+        const std::uint8_t *row = states.data() + k * P;
+        for (std::size_t s = 0; s < width; ++s) seq[s] = row[comp.site_to_pattern[s]];
+        rec.sequences.emplace(flat.ids[k], std::move(seq));
     }
     return rec;
 }

@@ -135,6 +135,8 @@ class PhyloTree {
     double log_likelihood(const GtrModel &model, const Alignment &aln) const;
     // MarginalAsr::marginal_asr (asr.rs:19-27; impl tree.rs:47-56)
     Reconstruction marginal_asr(const GtrModel &model, const Alignment &aln, bool want_posteriors) const;
+    // JointAsr::joint_asr (asr.rs:30-37; impl tree.rs:58-66)
+    Reconstruction joint_asr(const GtrModel &model, const Alignment &aln) const;
     // Config-5 caller loop `for (v, left) in moves { t = self.clone(); t.nni(v, left); t.log_likelihood(..) }`
     // in one device batch.  Invalid moves give NaN.
     std::vector<double> score_nni_neighbours(const GtrModel &model, const Alignment &aln,

@@ -98,3 +98,24 @@ def check_nni(lib, case, moves=None, flags=0, budget=None, devices=None, expect_
             assert val == ref
     assert st["nni_path_moves"] == (n_valid if expect_path else 0)
     return got, st
+
+
+def check_joint(lib, case, devices=None, budget=None):
+    """phb_joint_asr against the oracle's compute_joint_asr restatement.  Per-pattern Viterbi values within
+    1e-8 absolute, total within 1e-9 relative, states bit-exact except at audited numerical ties: a differing
+    pattern is accepted only if the GPU's state assignment reaches the oracle's best value to 1e-9 under the
+    oracle's own arithmetic (two assignments of equal joint probability)."""
+    with capi.Context(devices=devices, library=lib) as ctx:
+        if budget:
+            ctx.set_clv_budget(budget)
+        workloads.load_into(ctx, case)
+        tot, states = ctx.joint_asr()
+        per = ctx.per_pattern()
+        st = ctx.stats()
+    ref_tot, ref_per, ref_states = oracle.joint_asr_flat(case.ft, case.model, case.patterns, case.mult, n_threads=8)
+    assert_lnl_close(tot, per, ref_tot, ref_per)
+    diff = np.nonzero((states != ref_states).any(axis=0))[0]
+    for p in diff:
+        val = oracle.joint_assignment_value(case.ft, case.model, case.patterns[p], states[:, p])
+        assert abs(val - ref_per[p]) <= 1e-9 * max(1.0, abs(ref_per[p])), f"pattern {p}: joint states differ away from a tie"
+    return len(diff), st

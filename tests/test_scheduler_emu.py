@@ -230,6 +230,30 @@ def test_score_nni_polytomy_falls_back(emu_lib):
     _cases.check_nni(emu_lib, case, expect_path=False)
 
 
+@pytest.mark.parametrize("model", ["jc69", "gtr_g4", "gtr_i_g4"])
+def test_joint_asr_models(emu_lib, model):
+    case = workloads.make_case(12, 300, model=model, seed=11, ambiguity=0.1)
+    _cases.check_joint(emu_lib, case)
+
+
+def test_joint_asr_tiling_sharding_and_shapes(emu_lib):
+    case = workloads.make_case(9, 1500, model="gtr_g4", seed=4, compress=True)
+    _cases.check_joint(emu_lib, case)
+    _, st = _cases.check_joint(emu_lib, case, budget=8 * 4 * 4 * 8 * 512)
+    assert st["n_tiles"] >= 2
+    _cases.check_joint(emu_lib, case, devices=[0, 0, 0])
+    tree = parse_newick("((A:0.1,B:0.2,C:0.3)X:0.05,(D:0.1)Y:0.2,E:0.3)R;")  # polytomy + unifurcation
+    aln = RefAlignment.from_fasta_bytes(b">A\nACGTN\n>B\nACGAR\n>C\nAGGT-\n>D\nTCGTA\n>E\nACCTA\n")
+    m = RefModel.gtr([.3, .2, .2, .3], [1, 2.5, 1, 1, 2.5, 1]).with_gamma(0.5, 4)
+    pats, _s2p, mult, lo = aln.compress_columns()
+    _cases.check_joint(emu_lib, workloads.Case(tree, oracle.flatten(tree, lo), m, "gtr_g4", pats, mult, lo))
+    zero = parse_newick("((A:0,B:0)C:0,D:0)E:0;")  # conflicting leaves at distance 0: -inf, state 0 everywhere
+    zaln = RefAlignment.from_fasta_bytes(b">A\nACGT\n>B\nAGGT\n>D\nTTTT\n")
+    pats, _s2p, mult, lo = zaln.compress_columns()
+    zc = workloads.Case(zero, oracle.flatten(zero, lo), RefModel.jukes_cantor(), "jc69", pats, mult, lo)
+    assert _cases.check_joint(emu_lib, zc)[0] == 0
+
+
 def test_simulated_alignment_roundtrip(emu_lib):
     case = workloads.make_case(7, 10, model="gtr_g4", seed=13)
     with capi.Context(library=emu_lib) as ctx:

@@ -89,6 +89,35 @@ def run_asr(tag, n_taxa, n_sites, model, seed, reps):
                 states_d2h_bytes=int(states.nbytes), state_histogram=np.bincount(states[:, :4096].ravel(), minlength=4).tolist())
 
 
+def run_joint(tag, n_taxa, n_sites, model, seed, reps):
+    tree = synthetic.yule_flat(n_taxa, seed)
+    K = 4
+    with capi.Context(flags=capi.FLAG_TIMING) as ctx:
+        synthetic.load_into(ctx, tree, model_for(model))
+        ctx.simulate_alignment(n_sites, seed=seed ^ 0xA11C)
+        import torch
+
+        states_t = torch.zeros((tree["n_nodes"], n_sites), dtype=torch.uint8, pin_memory=True)
+        states = states_t.numpy()
+        tot = capi.C.c_double(0.0)
+
+        def call():
+            ctx._check(ctx.lib.L.phb_joint_asr(ctx._h, states.ctypes.data_as(capi.C.POINTER(capi.C.c_uint8)), capi.C.byref(tot)))
+            return tot.value
+
+        val, dev_ms, wall_ms = timed(ctx, call, reps)
+        st = ctx.stats()
+        lnl = ctx.log_likelihood()
+    n = n_taxa
+    up_bytes = (32.0 * K * (2 * n - 3) + n) * n_sites          # as the marginal up pass
+    down_bytes = (34.0 * (n - 2) + 3.0 * n + 1) * n_sites       # per child: parent state + category + 4 C values / code + state out
+    return dict(case=tag, taxa=n_taxa, patterns=n_sites, model=model, joint_value=val, lnl=lnl, device_ms=dev_ms,
+                wall_ms=wall_ms, ms_up=st["ms_clv"], ms_down=st["ms_down"], tiles=st["n_tiles"],
+                node_site_updates_per_s=((n - 1) + (2 * n - 1)) * n_sites / (wall_ms * 1e-3),
+                algorithmic_GBps_device=(up_bytes + down_bytes) / (dev_ms * 1e-3) / 1e9,
+                state_histogram=np.bincount(states[:, :4096].ravel(), minlength=4).tolist())
+
+
 def run_nni(tag, n_taxa, n_sites, model, seed, n_moves, reps, flags=0):
     tree = synthetic.yule_flat(n_taxa, seed)
     co = tree["child_off"]
@@ -124,6 +153,8 @@ CASES = {
     "cfg3_rank8": lambda r: run_lnl("cfg3 per-rank shard at 8 GPUs", 10_000, 125_000, "gtr_i_g4", 0x5EED0003, r),
     "cfg4": lambda r: run_asr("cfg4 marginal ASR GTR+G4 5000 x 500k", 5000, 500_000, "gtr_g4", 0x5EED0004, r),
     "cfg4_small": lambda r: run_asr("cfg4/10 marginal ASR GTR+G4 5000 x 50k", 5000, 50_000, "gtr_g4", 0x5EED0004, r),
+    "joint_small": lambda r: run_joint("joint ASR GTR+G4 5000 x 50k", 5000, 50_000, "gtr_g4", 0x5EED0004, r),
+    "joint": lambda r: run_joint("joint ASR GTR+G4 5000 x 500k", 5000, 500_000, "gtr_g4", 0x5EED0004, r),
     "cfg5": lambda r: run_nni("cfg5 1024 NNI neighbours 2000 x 200k", 2000, 200_000, "gtr_g4", 0x5EED0005, 1024, r),
     "cfg5_full_128": lambda r: run_nni("cfg5/8 128 NNI neighbours 2000 x 200k, full rescoring", 2000, 200_000, "gtr_g4",
                                        0x5EED0005, 128, r, capi.FLAG_NNI_FULL),
