@@ -17,8 +17,9 @@
 //   clv_cache_level_kernel  level-batched up pass that also stores, per (node, category, pattern),
 //                           the exponent accumulated in the node's SUBTREE (exact power-of-two
 //                           rescaling stands in for Profile::scale, src/tree/likelihood/profile.rs:20-39)
-//   nni_score_kernel        one CTA = (neighbour, 128 patterns); one thread = one pattern, all CLV
-//                           categories in registers; reads one sibling CLV per step of the walk.
+//   nni_score_kernel        one CTA = (neighbour, 128..512 patterns); a warp = one CLV category of 64
+//                           patterns, a thread = a pattern pair; the walk's P matrices are staged in
+//                           shared memory; reads one sibling CLV per step of the walk.
 //                           CTAs are ordered pattern-block-major with neighbours sorted in DFS order
 //                           of v, so the siblings near the root, which almost every walk reads, are
 //                           served from the 126 MB L2 instead of HBM.
@@ -28,7 +29,6 @@
 
 namespace phb {
 
-constexpr int NNI_THREADS = 128;
 
 // One step of the walk: the CLV of the node being rebuilt is msg (.) (P[sib_edge] L_sib); unless it
 // is the root (up_edge < 0) the next message is P[up_edge] times that CLV.
@@ -133,39 +133,66 @@ clv_cache_level_kernel(const NodeOp *__restrict__ ops, int n_ops, ModelDev M,
 // ---------------------------------------------------------------------------------------------
 // Neighbour scoring.  grid = n_site_blocks * n_moves, blockIdx.x = site_block * n_moves + move
 // (moves pre-sorted by the host in DFS order of v: consecutive CTAs walk nearly the same path).
+//
+// CTA = NC * G warps (G = NNI_WARP_GROUPS[NC]); warp w works on CLV category w % NC for the 64 patterns
+// of group w / NC, one pattern PAIR per thread (16-byte CLV loads).  The walk's P matrices (two per step)
+// and step records are staged in shared memory, NNI_CHUNK steps at a time, so that the per-step matrix
+// fetches are shared-memory broadcasts instead of L1 traffic; the sibling CLV of step k+1 is requested
+// before the arithmetic of step k.  Categories meet in shared memory for the root's log-sum-exp.
 // ---------------------------------------------------------------------------------------------
-template <int NC>
-__device__ __forceinline__ void nni_matvec(const double *__restrict__ Pm, const double (&x)[4], double (&y)[4])
-{
-    double p[16];
-    load_P(Pm, p);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) y[i] = p[4 * i] * x[0] + p[4 * i + 1] * x[1] + p[4 * i + 2] * x[2] + p[4 * i + 3] * x[3];
-}
+constexpr int NNI_CHUNK = 24;                       // steps staged per pass
+__host__ __device__ constexpr int nni_groups(int nc) { return nc == 1 ? 8 : nc == 2 ? 4 : 2; }
+__host__ __device__ constexpr int nni_threads(int nc) { return 32 * nc * nni_groups(nc); }
+__host__ __device__ constexpr int nni_block_sites(int nc) { return 64 * nni_groups(nc); }
 
-// contribution of a subtree hanging off the walk: out[i] = sum_j P[i][j] L[j]; returns its exponent
-__device__ __forceinline__ int nni_contrib(const double *__restrict__ Pm, bool is_tip, int src, int cat_clv, int n_clv,
-                                           const double *__restrict__ clv, size_t slot_stride, size_t tile_pad,
-                                           const int *__restrict__ exps, const uint8_t *__restrict__ tips,
-                                           int64_t P_pad, int64_t tile_off, int64_t site, double (&out)[4])
+struct NniSib { // one sibling's data for a pattern pair, as loaded
+    double2 x[4];
+    int2 e;
+    uchar2 code;
+};
+
+__device__ __forceinline__ void nni_load_sib(NniSib &o, bool is_tip, int src, int cat, int n_clv,
+                                             const double *__restrict__ clv, size_t slot_stride, size_t tile_pad,
+                                             const int *__restrict__ exps, const uint8_t *__restrict__ tips, int64_t P_pad,
+                                             int64_t tile_off, int64_t site)
 {
-    double p[16];
-    load_P(Pm, p);
     if (is_tip) {
-        const uint32_t m = code_mask(tips[(int64_t)src * P_pad + tile_off + site]);
+        o.code = *reinterpret_cast<const uchar2 *>(tips + (int64_t)src * P_pad + tile_off + site);
+        o.e = make_int2(0, 0);
+    } else {
+        const double2 *s = reinterpret_cast<const double2 *>(clv + (size_t)src * slot_stride + (size_t)cat * 4 * tile_pad + (size_t)site);
+        const size_t stride2 = tile_pad / 2;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) out[i] = masked_row(p, i, m);
-        return 0;
+        for (int j = 0; j < 4; ++j) o.x[j] = s[j * stride2];
+        o.e = *reinterpret_cast<const int2 *>(exps + ((size_t)src * n_clv + cat) * tile_pad + (size_t)site);
     }
-    const double *s = clv + (size_t)src * slot_stride + (size_t)cat_clv * 4 * tile_pad + (size_t)site;
-    const double x0 = s[0], x1 = s[tile_pad], x2 = s[2 * tile_pad], x3 = s[3 * tile_pad];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) out[i] = p[4 * i] * x0 + p[4 * i + 1] * x1 + p[4 * i + 2] * x2 + p[4 * i + 3] * x3;
-    return exps[((size_t)src * n_clv + cat_clv) * tile_pad + (size_t)site];
 }
 
-template <int NC>
-__global__ void __launch_bounds__(NNI_THREADS)
+// out[i] = sum_j P[i][j] L[j] for both patterns; P (16 doubles) in shared memory
+__device__ __forceinline__ void nni_apply_sib(const double *__restrict__ Ps, const NniSib &sb, bool is_tip, double2 (&out)[4])
+{
+    double p[16];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const double2 t = reinterpret_cast<const double2 *>(Ps)[i];
+        p[2 * i] = t.x;
+        p[2 * i + 1] = t.y;
+    }
+    if (is_tip) {
+        const uint32_t mx = code_mask(sb.code.x), my = code_mask(sb.code.y);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) out[i] = make_double2(masked_row(p, i, mx), masked_row(p, i, my));
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            out[i].x = p[4 * i] * sb.x[0].x + p[4 * i + 1] * sb.x[1].x + p[4 * i + 2] * sb.x[2].x + p[4 * i + 3] * sb.x[3].x;
+            out[i].y = p[4 * i] * sb.x[0].y + p[4 * i + 1] * sb.x[1].y + p[4 * i + 2] * sb.x[2].y + p[4 * i + 3] * sb.x[3].y;
+        }
+    }
+}
+
+template <int NC, int MINB>
+__global__ void __launch_bounds__(nni_threads(NC), MINB)
 nni_score_kernel(const NniMove *__restrict__ moves, int n_moves, const NniStep *__restrict__ steps, ModelDev M,
                  const double *__restrict__ Pmat, const double *__restrict__ clv, size_t slot_stride, size_t tile_pad,
                  int tile_len, const int *__restrict__ exps, const uint8_t *__restrict__ tips, int64_t P_pad,
@@ -173,69 +200,129 @@ nni_score_kernel(const NniMove *__restrict__ moves, int n_moves, const NniStep *
                  const uint8_t *__restrict__ inv_mask /* + tile_off */, const double *__restrict__ mult /* + tile_off */,
                  double *__restrict__ partials /* [move][n_site_blocks] */, int n_site_blocks)
 {
+    constexpr int G = nni_groups(NC), BS = nni_block_sites(NC), NT = nni_threads(NC);
+    __shared__ __align__(16) double sP[(2 * NNI_CHUNK + 1) * NC * 16]; // [0]: first message; then per step: sibling, up
+    __shared__ NniStep sSteps[NNI_CHUNK];
+    __shared__ double sLL[NC][BS];
     const int mi = blockIdx.x % n_moves;
     const int sb = blockIdx.x / n_moves;
     const NniMove mv = moves[mi];
-    const int64_t site = (int64_t)sb * NNI_THREADS + threadIdx.x;
-    double contrib = 0.0;
-    if (site < tile_len) {
-        double msg[NC][4];
-        int ex[NC];
-        const int ncm = M.n_cat;
-#pragma unroll
-        for (int c = 0; c < NC; ++c)
-            ex[c] = nni_contrib(Pmat + ((size_t)mv.a_edge * ncm + M.cat_of_clv[c]) * 16, mv.a_is_tip != 0, mv.a_src, c, NC, clv,
-                                slot_stride, tile_pad, exps, tips, P_pad, tile_off, site, msg[c]);
-        for (int k = mv.step_begin; k < mv.step_end; ++k) {
-            const NniStep st = steps[k];
-#pragma unroll
-            for (int c = 0; c < NC; ++c) {
-                double sbv[4];
-                ex[c] += nni_contrib(Pmat + ((size_t)st.sib_edge * ncm + M.cat_of_clv[c]) * 16, st.sib_is_tip != 0, st.sib_src, c,
-                                     NC, clv, slot_stride, tile_pad, exps, tips, P_pad, tile_off, site, sbv);
-                double v[4];
-#pragma unroll
-                for (int i = 0; i < 4; ++i) v[i] = msg[c][i] * sbv[i];
-                ex[c] += rescale_site_local(v[0], v[1], v[2], v[3]);
-                if (st.up_edge >= 0) nni_matvec<NC>(Pmat + ((size_t)st.up_edge * ncm + M.cat_of_clv[c]) * 16, v, msg[c]);
-                else {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) msg[c][i] = v[i];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int cat = warp % NC, grp = warp / NC;
+    const int cat_model = M.cat_of_clv[cat];
+    const int ncm = M.n_cat;
+    const int local = grp * 64 + lane * 2;
+    const int64_t site = (int64_t)sb * BS + local;
+    const bool live = site < tile_len; // tile_pad is even and the tip rows are padded: the pair load is always in bounds
+    double2 msg[4];
+    int2 ex = make_int2(0, 0);
+    NniSib cur;
+    // first message: the child of v that stays
+    for (int i = threadIdx.x; i < NC * 16; i += NT) {
+        const int c = i >> 4;
+        sP[i] = Pmat[((size_t)mv.a_edge * ncm + M.cat_of_clv[c]) * 16 + (i & 15)];
+    }
+    if (live) nni_load_sib(cur, mv.a_is_tip != 0, mv.a_src, cat, NC, clv, slot_stride, tile_pad, exps, tips, P_pad, tile_off, site);
+    __syncthreads();
+    if (live) {
+        nni_apply_sib(sP + cat * 16, cur, mv.a_is_tip != 0, msg);
+        ex = cur.e;
+    }
+    for (int k0 = mv.step_begin; k0 < mv.step_end; k0 += NNI_CHUNK) {
+        const int nk = min(NNI_CHUNK, mv.step_end - k0);
+        __syncthreads(); // the previous chunk's matrices are no longer read
+        if (threadIdx.x < nk) sSteps[threadIdx.x] = steps[k0 + threadIdx.x];
+        for (int i = threadIdx.x; i < nk * 2 * NC * 16; i += NT) {
+            const int e = i & 15, c = (i >> 4) % NC, which = (i / (16 * NC)) & 1, k = i / (32 * NC);
+            const NniStep st = steps[k0 + k];
+            const int edge = which ? st.up_edge : st.sib_edge;
+            sP[NC * 16 + i] = edge >= 0 ? Pmat[((size_t)edge * ncm + M.cat_of_clv[c]) * 16 + e] : 0.0;
+        }
+        __syncthreads();
+        if (live) {
+            NniSib nxt;
+            {
+                const NniStep st = sSteps[0];
+                nni_load_sib(cur, st.sib_is_tip != 0, st.sib_src, cat, NC, clv, slot_stride, tile_pad, exps, tips, P_pad, tile_off, site);
+            }
+            for (int k = 0; k < nk; ++k) {
+                const NniStep st = sSteps[k];
+                if (k + 1 < nk) { // request the next sibling before this step's arithmetic
+                    const NniStep sn = sSteps[k + 1];
+                    nni_load_sib(nxt, sn.sib_is_tip != 0, sn.sib_src, cat, NC, clv, slot_stride, tile_pad, exps, tips, P_pad, tile_off, site);
                 }
+                const double *Pk = sP + NC * 16 + (size_t)k * 2 * NC * 16;
+                double2 sv[4];
+                nni_apply_sib(Pk + cat * 16, cur, st.sib_is_tip != 0, sv);
+                ex.x += cur.e.x;
+                ex.y += cur.e.y;
+                double vx[4], vy[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    vx[i] = msg[i].x * sv[i].x;
+                    vy[i] = msg[i].y * sv[i].y;
+                }
+                ex.x += rescale_site_local(vx[0], vx[1], vx[2], vx[3]);
+                ex.y += rescale_site_local(vy[0], vy[1], vy[2], vy[3]);
+                if (st.up_edge >= 0) {
+                    const double2 *Pu = reinterpret_cast<const double2 *>(Pk + NC * 16 + cat * 16);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const double2 a = Pu[2 * i], b = Pu[2 * i + 1];
+                        msg[i].x = a.x * vx[0] + a.y * vx[1] + b.x * vx[2] + b.y * vx[3];
+                        msg[i].y = a.x * vy[0] + a.y * vy[1] + b.x * vy[2] + b.y * vy[3];
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) msg[i] = make_double2(vx[i], vy[i]);
+                }
+                if (k + 1 < nk) cur = nxt;
             }
         }
-        // root formula, as root_kernel
+    }
+    // root formula, as root_kernel: this thread's category first, then one thread per pattern mixes them
+    if (live) {
+        double mx = 0.0, my = 0.0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            mx += M.pi[i] * msg[i].x;
+            my += M.pi[i] * msg[i].y;
+        }
+        double lsx = leaf_ls[site], lsy = leaf_ls[site + 1];
+        lsx -= (double)ex.x * LN2;
+        lsy -= (double)ex.y * LN2;
+        sLL[cat][local] = M.ln_weights[cat_model] + log(mx) + lsx;
+        sLL[cat][local + 1] = M.ln_weights[cat_model] + log(my) + lsy;
+    }
+    __syncthreads();
+    double contrib = 0.0;
+    for (int q = threadIdx.x; q < BS; q += NT) {
+        const int64_t s = (int64_t)sb * BS + q;
+        if (s >= tile_len) continue;
         double lls[MAX_CAT];
-        const double lls_leaf = leaf_ls[site];
-        double mx = -INFINITY;
+        double mxl = -INFINITY;
         for (int c = 0; c < M.n_cat; ++c) {
-            double mass = 0.0, ls = lls_leaf;
             const int cc = M.clv_idx[c];
-            if (cc >= 0) {
-#pragma unroll
-                for (int q = 0; q < NC; ++q)
-                    if (q == cc) {
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) mass += M.pi[i] * msg[q][i];
-                        ls -= (double)ex[q] * LN2;
-                    }
-            } else {
-                const uint32_t m = inv_mask[site];
+            double ll;
+            if (cc >= 0) ll = sLL[cc][q];
+            else {
+                double mass = 0.0;
+                const uint32_t m = inv_mask[s];
 #pragma unroll
                 for (int i = 0; i < 4; ++i) mass += M.pi[i] * (((m >> i) & 1u) ? 1.0 : 0.0);
+                ll = M.ln_weights[c] + log(mass) + leaf_ls[s];
             }
-            const double ll = M.ln_weights[c] + log(mass) + ls;
             lls[c] = ll;
-            mx = fmax(mx, ll);
+            mxl = fmax(mxl, ll);
         }
         double site_ll;
-        if (!isfinite(mx)) site_ll = mx;
+        if (!isfinite(mxl)) site_ll = mxl;
         else {
-            double s = 0.0;
-            for (int c = 0; c < M.n_cat; ++c) s += exp(lls[c] - mx);
-            site_ll = mx + log(s);
+            double acc = 0.0;
+            for (int c = 0; c < M.n_cat; ++c) acc += exp(lls[c] - mxl);
+            site_ll = mxl + log(acc);
         }
-        contrib = mult[site] * site_ll;
+        contrib += mult[s] * site_ll;
     }
     const double r = block_reduce_sum(contrib);
     if (threadIdx.x == 0) partials[(size_t)mi * n_site_blocks + sb] = r;

@@ -971,6 +971,7 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
     S.nni_cache_bytes = 0;
     if (moves.empty() || ctx->n_patterns == 0) return PHB_OK;
     const int nm = (int)moves.size();
+    static const bool nni_minb3 = [] { const char *e = getenv("PHB_NNI_MINB"); return e && atoi(e) == 3; }();
     std::vector<std::vector<double>> dev_totals(ctx->devs.size());
     for (size_t di = 0; di < ctx->devs.size(); ++di) {
         Device &d = ctx->devs[di];
@@ -1005,7 +1006,8 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
         const size_t slot_stride = (size_t)M.n_clv * 4 * tile_pad;
         CU(d.clv.ensure(sizeof(double) * slot_stride * (size_t)T.n_internal));
         CU(d.nni_exps.ensure(sizeof(int) * (size_t)M.n_clv * tile_pad * (size_t)T.n_internal));
-        const int max_sb = (int)((std::min<int64_t>(tile, d.P) + NNI_THREADS - 1) / NNI_THREADS);
+        const int nni_bs = nni_block_sites(M.n_clv);
+        const int max_sb = (int)((std::min<int64_t>(tile, d.P) + nni_bs - 1) / nni_bs);
         CU(d.nni_partials.ensure(sizeof(double) * (size_t)nm * (size_t)max_sb));
         if (&d == &ctx->devs[0]) {
             S.nni_tiles = n_tiles;
@@ -1040,22 +1042,26 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
                            slot_stride, tile_pad, len, bpr, d.tips.as<uint8_t>(), d.P_pad, off, d.nni_exps.as<int>());
                 CHECK_LAUNCH();
             }
-            const int n_sb = (len + NNI_THREADS - 1) / NNI_THREADS;
+            const int n_sb = (len + nni_bs - 1) / nni_bs;
             const int chunk = std::max(1, (int)std::min<int64_t>(nm, (int64_t)0x7fffffff / std::max(n_sb, 1)));
             for (int m0 = 0; m0 < nm; m0 += chunk) { // (the grid holds n_sb * moves-in-chunk CTAs)
                 const int cm = std::min(chunk, nm - m0);
                 ScopedTimer tm(ctx, &d, PH_DOWN);
-#define PHB_NNI_LAUNCH(NC)                                                                                             \
-    PHB_LAUNCH(nni_score_kernel<NC>, dim3((unsigned)((int64_t)n_sb * cm)), dim3(NNI_THREADS), d.stream,                \
+#define PHB_NNI_LAUNCH(NC, MINB)                                                                                       \
+    PHB_LAUNCH((nni_score_kernel<NC, MINB>), dim3((unsigned)((int64_t)n_sb * cm)), dim3(nni_threads(NC)), d.stream,    \
                d.nni_moves.as<NniMove>() + m0, cm, d.nni_steps.as<NniStep>(), M, d.Pmat.as<double>(), d.clv.as<double>(), \
                slot_stride, tile_pad, len, d.nni_exps.as<int>(), d.tips.as<uint8_t>(), d.P_pad, off,                   \
                d.leaf_ls.as<double>() + off, d.inv_mask.as<uint8_t>() + off, d.mult.as<double>() + off,                \
                d.nni_partials.as<double>(), n_sb)
-                switch (M.n_clv) {
-                case 1: PHB_NNI_LAUNCH(1); break;
-                case 2: PHB_NNI_LAUNCH(2); break;
-                case 3: PHB_NNI_LAUNCH(3); break;
-                default: PHB_NNI_LAUNCH(4); break;
+                switch (M.n_clv * 2 + (nni_minb3 ? 1 : 0)) {
+                case 2: PHB_NNI_LAUNCH(1, 2); break;
+                case 3: PHB_NNI_LAUNCH(1, 3); break;
+                case 4: PHB_NNI_LAUNCH(2, 2); break;
+                case 5: PHB_NNI_LAUNCH(2, 3); break;
+                case 6: PHB_NNI_LAUNCH(3, 2); break;
+                case 7: PHB_NNI_LAUNCH(3, 3); break;
+                case 8: PHB_NNI_LAUNCH(4, 2); break;
+                default: PHB_NNI_LAUNCH(4, 3); break;
                 }
 #undef PHB_NNI_LAUNCH
                 CHECK_LAUNCH();

@@ -22,6 +22,7 @@
 #define __forceinline__ inline __attribute__((always_inline))
 #define __launch_bounds__(...)
 #define __shared__ static
+#define __align__(n) __attribute__((aligned(n)))
 
 struct dim3 {
     unsigned x, y, z;
@@ -34,6 +35,7 @@ struct alignas(8) int2 { int x, y; };
 struct uchar4 { unsigned char x, y, z, w; };
 struct uint2 { unsigned int x, y; };
 static inline double2 make_double2(double x, double y) { double2 r; r.x = x; r.y = y; return r; }
+static inline int2 make_int2(int x, int y) { int2 r; r.x = x; r.y = y; return r; }
 
 namespace emu {
 extern dim3 threadIdx, blockIdx, blockDim, gridDim;
