@@ -94,6 +94,23 @@ int32_t phb_set_alignment(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns, cons
  * P(t) is evaluated on the device per (edge, category) as
  *   diag(inv_sqrt_pi) * V * diag(exp(lambda * rate * t)) * V^T * diag(sqrt_pi),
  * and is the exact identity when rate * t == 0.0 (rate_matrix.rs:115-117). */
+/* Replaces Alignment::compress_columns (src/alignment.rs:93-125) on the device and leaves the result as the
+ * context's alignment (as if phb_set_alignment had been called with CompressedColumns.patterns and
+ * .multiplicity, src/alignment.rs:129-138).  bytes: the alignment as the reference holds it, one sequence per
+ * row, [n_rows][width] raw bytes (already upper-cased by from_fasta_bytes); the caller's row order is
+ * CompressedColumns.leaf_order.  Columns are compared over ALL rows byte for byte ('T' != 'U'; rows naming
+ * internal nodes take part), and patterns are numbered in order of first appearance, exactly as the
+ * reference's HashMap walk does.  *n_patterns receives the pattern count; site_to_pattern (nullable) receives
+ * `width` indices; multiplicity (nullable, capacity `width`) receives *n_patterns counts.
+ * The canonical pattern bytes can be read back with phb_get_alignment. */
+int32_t phb_compress_columns(phb_ctx *ctx, int32_t n_rows, int64_t width, const uint8_t *bytes, int64_t *n_patterns,
+                             uint64_t *site_to_pattern, uint64_t *multiplicity);
+
+/* Same, with one pointer per row: rows[r] -> the `width` bytes of sequence r (the reference keeps each sequence
+ * in its own Vec<u8>, Alignment.seqs src/alignment.rs:5-10, so the Rust shim passes the Vec pointers as they are). */
+int32_t phb_compress_rows(phb_ctx *ctx, int32_t n_rows, int64_t width, const uint8_t *const *rows, int64_t *n_patterns,
+                          uint64_t *site_to_pattern, uint64_t *multiplicity);
+
 int32_t phb_set_model(phb_ctx *ctx, const double *lambda, const double *V, const double *pi,
                       const double *sqrt_pi, const double *inv_sqrt_pi, int32_t n_cat,
                       const double *rates, const double *weights);

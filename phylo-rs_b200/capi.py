@@ -31,7 +31,7 @@ LAYOUT_ROW_MAJOR = 1
 
 # every symbol include/phylo_b200.h declares (checked by tests/test_abi.py)
 EXPORTS = [
-    "phb_ctx_create", "phb_ctx_destroy", "phb_set_clv_budget", "phb_set_alignment", "phb_set_model",
+    "phb_ctx_create", "phb_ctx_destroy", "phb_set_clv_budget", "phb_set_alignment", "phb_compress_columns", "phb_compress_rows", "phb_set_model",
     "phb_set_tree", "phb_log_likelihood", "phb_marginal_asr", "phb_joint_asr", "phb_get_per_pattern", "phb_score_nni",
     "phb_simulate_alignment", "phb_get_alignment", "phb_get_stats", "phb_measure_fp64_tflops",
     "phb_timer_start", "phb_timer_stop", "phb_transition_matrices", "phb_log_likelihood_host",
@@ -81,6 +81,8 @@ class Library:
         L.phb_ctx_destroy.restype = None
         L.phb_set_clv_budget.argtypes = [vp, C.c_uint64]
         L.phb_set_alignment.argtypes = [vp, C.c_int32, C.c_int64, vp, C.c_int32, u64p]
+        L.phb_compress_columns.argtypes = [vp, C.c_int32, C.c_int64, vp, C.POINTER(C.c_int64), u64p, u64p]
+        L.phb_compress_rows.argtypes = [vp, C.c_int32, C.c_int64, C.POINTER(vp), C.POINTER(C.c_int64), u64p, u64p]
         L.phb_set_model.argtypes = [vp, dp, dp, dp, dp, dp, C.c_int32, dp, dp]
         L.phb_set_tree.argtypes = [vp, C.c_int32, ip, ip, ip, dp, ip, C.c_int32]
         L.phb_log_likelihood.argtypes = [vp, dp, dp]
@@ -168,6 +170,37 @@ class Context:
     # -- inputs ------------------------------------------------------------------------------
     def set_clv_budget(self, nbytes):
         self._check(self.lib.L.phb_set_clv_budget(self._h, int(nbytes)))
+
+    def compress_columns(self, rows):
+        """phb_compress_columns: rows = uint8 [n_rows][width] raw alignment bytes (one sequence per row).
+        Returns (n_patterns, site_to_pattern uint64[width], multiplicity uint64[n_patterns]); the compressed
+        patterns become the context's alignment."""
+        rows = np.ascontiguousarray(rows, np.uint8)
+        if rows.ndim != 2:
+            raise ValueError("rows must be 2-D")
+        n_rows, width = rows.shape
+        s2p = np.zeros(max(width, 1), np.uint64)
+        mult = np.zeros(max(width, 1), np.uint64)
+        n = C.c_int64(0)
+        self._check(self.lib.L.phb_compress_columns(
+            self._h, n_rows, width, rows.ctypes.data_as(C.c_void_p), C.byref(n),
+            s2p.ctypes.data_as(C.POINTER(C.c_uint64)), mult.ctypes.data_as(C.POINTER(C.c_uint64))))
+        self.n_rows, self.n_patterns = n_rows, int(n.value)
+        return int(n.value), s2p[:width], mult[: int(n.value)]
+
+    def compress_rows(self, seqs):
+        """phb_compress_rows: seqs = list of equal-length bytes objects / uint8 arrays, one per row."""
+        arrs = [np.ascontiguousarray(np.frombuffer(s, np.uint8) if isinstance(s, (bytes, bytearray)) else s, np.uint8) for s in seqs]
+        width = len(arrs[0]) if arrs else 0
+        ptrs = (C.c_void_p * max(len(arrs), 1))(*[a.ctypes.data for a in arrs])
+        s2p = np.zeros(max(width, 1), np.uint64)
+        mult = np.zeros(max(width, 1), np.uint64)
+        n = C.c_int64(0)
+        self._check(self.lib.L.phb_compress_rows(
+            self._h, len(arrs), width, ptrs, C.byref(n), s2p.ctypes.data_as(C.POINTER(C.c_uint64)),
+            mult.ctypes.data_as(C.POINTER(C.c_uint64))))
+        self.n_rows, self.n_patterns = len(arrs), int(n.value)
+        return int(n.value), s2p[:width], mult[: int(n.value)]
 
     def set_alignment(self, data, layout=LAYOUT_PATTERN_MAJOR, multiplicity=None):
         """data: uint8 array, [P][rows] (pattern-major) or [rows][P] (row-major) ASCII bytes."""

@@ -10,6 +10,7 @@
 #include "sweep.cuh"
 #include "nni.cuh"
 #include "joint.cuh"
+#include "compress.cuh"
 #include "sweep_sched.h"
 #include "../../include/phylo_b200.h"
 
@@ -1155,7 +1156,8 @@ void phb_ctx_destroy(phb_ctx *ctx)
                           &d.clv, &d.scale, &d.cat_ll, &d.partials, &d.total, &d.ops, &d.gops, &d.gkids, &d.dops,
                           &d.dkids, &d.leaf_rows, &d.states, &d.posteriors, &d.staging, &d.sim_pre, &d.sim_parent,
                           &d.sim_depth, &d.sim_leafrow, &d.sim_stack, &d.scratch, &d.sw_descs, &d.sw_blocks,
-                          &d.sw_stream, &d.sw_gstack, &d.sw_err, &d.sw_ops};
+                          &d.sw_stream, &d.sw_gstack, &d.sw_err, &d.sw_ops, &d.uops, &d.ukids, &d.lnP, &d.jbest,
+                          &d.nni_exps, &d.nni_partials, &d.nni_totals, &d.nni_moves, &d.nni_steps};
         for (DevBuf *b : bufs) b->release();
         for (auto &ep : d.ev_pool) {
             cudaEventDestroy(ep.a);
@@ -1330,6 +1332,202 @@ int32_t phb_set_alignment(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns, cons
     if (rc) return rc;
     ctx->have_aln = true;
     return PHB_OK;
+}
+
+// bytes: contiguous [n_rows][width], or null with row_ptrs[r] -> the `width` bytes of row r
+static int32_t compress_impl(phb_ctx *ctx, int32_t n_rows, int64_t width, const uint8_t *bytes, const uint8_t *const *row_ptrs,
+                             int64_t *n_patterns, uint64_t *site_to_pattern, uint64_t *multiplicity)
+{
+    if (!ctx || !n_patterns) return PHB_ERR_INVALID_ARGUMENT;
+    if (n_rows < 0 || width < 0 || width > 0x7fffffff || (!bytes && !row_ptrs && n_rows > 0 && width > 0))
+        return ctx->fail(PHB_ERR_INVALID_ARGUMENT, "compress_columns: bad arguments");
+    if (!bytes && row_ptrs)
+        for (int r = 0; r < n_rows && width > 0; ++r)
+            if (!row_ptrs[r]) return ctx->fail(PHB_ERR_INVALID_ARGUMENT, "compress_rows: row %d is null", r);
+    ctx->have_aln = false;
+    *n_patterns = 0;
+    if (width == 0) { // no sites: no patterns (alignment.rs:102 never iterates)
+        int rc0 = shard_and_alloc(ctx, n_rows, 0);
+        if (rc0) return rc0;
+        ctx->row_invalid_host.assign(std::max(n_rows, 1), 0);
+        for (Device &d : ctx->devs) {
+            rc0 = upload_pad_and_mult(ctx, d, n_rows, nullptr);
+            if (rc0) return rc0;
+        }
+        ctx->have_aln = true;
+        return PHB_OK;
+    }
+    Device &d0 = ctx->devs[0];
+    CU(cudaSetDevice(d0.ordinal));
+    const int64_t pitch = round_up(width, 16) + 16; // 8-site loads of the last thread stay inside the row
+    const int rows_alloc = std::max(n_rows, 1);
+    DevBuf raw, hash, keys, sites, sites2, head, gid, gstart, rep, isrep, size_at, pid, replist, s2p, mult, temp, flag, stage;
+    DevBuf *all[] = {&raw, &hash, &keys, &sites, &sites2, &head, &gid, &gstart, &rep, &isrep, &size_at, &pid, &replist,
+                     &s2p, &mult, &temp, &flag, &stage};
+    struct Cleanup {
+        DevBuf **b;
+        size_t n;
+        ~Cleanup() { for (size_t i = 0; i < n; ++i) b[i]->release(); }
+    } cleanup{all, sizeof all / sizeof all[0]};
+    const size_t W = (size_t)width;
+    CU(raw.ensure((size_t)rows_alloc * (size_t)pitch));
+    CU(hash.ensure(sizeof(uint64_t) * W));
+    CU(keys.ensure(sizeof(uint64_t) * W));
+    CU(sites.ensure(sizeof(uint32_t) * W));
+    CU(sites2.ensure(sizeof(uint32_t) * W));
+    CU(head.ensure(sizeof(uint32_t) * W));
+    CU(gid.ensure(sizeof(uint32_t) * W));
+    CU(gstart.ensure(sizeof(uint32_t) * W));
+    CU(rep.ensure(sizeof(uint32_t) * W));
+    CU(isrep.ensure(sizeof(uint32_t) * W));
+    CU(size_at.ensure(sizeof(uint32_t) * W));
+    CU(pid.ensure(sizeof(uint32_t) * W));
+    CU(replist.ensure(sizeof(uint32_t) * W));
+    CU(s2p.ensure(sizeof(uint64_t) * W));
+    CU(mult.ensure(sizeof(uint64_t) * W));
+    CU(flag.ensure(sizeof(unsigned int)));
+    const size_t temp_bytes = compress_temp_bytes(width);
+    CU(temp.ensure(temp_bytes));
+    // 1. bytes -> device, row chunk by row chunk on the copy stream; the first hash pass folds each chunk as it lands
+    CU(cudaEventRecord(d0.ev_free[0], d0.stream));
+    CU(cudaStreamWaitEvent(d0.copy_stream, d0.ev_free[0], 0));
+    const int rows_per_chunk = (int)std::max<int64_t>(1, std::min<int64_t>(std::max(n_rows, 1), ((int64_t)256 << 20) / width));
+    const unsigned hash_grid = (unsigned)((width + 256 * HASH_SITES_PER_THREAD - 1) / (256 * HASH_SITES_PER_THREAD));
+    const unsigned w_grid = (unsigned)((width + 255) / 256);
+    uint64_t seed = 0x243F6A8885A308D3ull;
+    std::vector<cudaEvent_t> chunk_events;
+    struct EvCleanup {
+        std::vector<cudaEvent_t> &v;
+        ~EvCleanup() { for (cudaEvent_t e : v) cudaEventDestroy(e); }
+    } evc{chunk_events};
+    int64_t P = 0;
+    for (int attempt = 0; attempt < 4; ++attempt) {
+        const uint64_t key = splitmix64(seed + attempt), mul = splitmix64(key) | 1ull;
+        for (int r0 = 0, ci = 0; r0 < std::max(n_rows, 1); r0 += rows_per_chunk, ++ci) {
+            const int nr = std::min(rows_per_chunk, n_rows - r0);
+            if (attempt == 0 && nr > 0) {
+                if (bytes)
+                    CU(cudaMemcpy2DAsync(raw.as<uint8_t>() + (size_t)r0 * pitch, (size_t)pitch, bytes + (size_t)r0 * W, W, W,
+                                         (size_t)nr, cudaMemcpyHostToDevice, d0.copy_stream));
+                else
+                    for (int r = r0; r < r0 + nr; ++r)
+                        CU(cudaMemcpyAsync(raw.as<uint8_t>() + (size_t)r * pitch, row_ptrs[r], W, cudaMemcpyHostToDevice,
+                                           d0.copy_stream));
+                cudaEvent_t e;
+                CU(cudaEventCreate(&e));
+                chunk_events.push_back(e);
+                CU(cudaEventRecord(e, d0.copy_stream));
+                CU(cudaStreamWaitEvent(d0.stream, e, 0));
+            }
+            const bool first = r0 == 0, last = r0 + rows_per_chunk >= n_rows;
+            PHB_LAUNCH(column_hash_kernel, dim3(hash_grid), dim3(256), d0.stream, raw.as<uint8_t>(), pitch, r0, std::max(nr, 0),
+                       width, key, mul, first ? 1 : 0, last ? 1 : 0, hash.as<uint64_t>());
+            CHECK_LAUNCH();
+        }
+        // 2. stable sort of (hash, site); groups of equal hash
+        PHB_LAUNCH(iota_kernel, dim3(w_grid), dim3(256), d0.stream, sites.as<uint32_t>(), width);
+        CHECK_LAUNCH();
+        CU(dev_sort_pairs(temp.p, temp_bytes, hash.as<uint64_t>(), keys.as<uint64_t>(), sites.as<uint32_t>(),
+                          sites2.as<uint32_t>(), width, d0.stream));
+        PHB_LAUNCH(group_head_kernel, dim3(w_grid), dim3(256), d0.stream, keys.as<uint64_t>(), width, head.as<uint32_t>());
+        CHECK_LAUNCH();
+        CU(dev_scan(temp.p, temp_bytes, head.as<uint32_t>(), gid.as<uint32_t>(), width, true, d0.stream));
+        PHB_LAUNCH(group_start_kernel, dim3(w_grid), dim3(256), d0.stream, head.as<uint32_t>(), gid.as<uint32_t>(), width,
+                   gstart.as<uint32_t>());
+        CHECK_LAUNCH();
+        uint32_t n_groups = 0;
+        CU(cudaMemcpyAsync(&n_groups, gid.as<uint32_t>() + (W - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, d0.stream));
+        CU(cudaStreamSynchronize(d0.stream));
+        PHB_LAUNCH(group_rep_kernel, dim3(w_grid), dim3(256), d0.stream, sites2.as<uint32_t>(), gid.as<uint32_t>(),
+                   gstart.as<uint32_t>(), n_groups, width, rep.as<uint32_t>(), isrep.as<uint32_t>(), size_at.as<uint32_t>());
+        CHECK_LAUNCH();
+        // 3. exact verification of every merged site against the first site of its group
+        CU(cudaMemsetAsync(flag.p, 0, sizeof(unsigned int), d0.stream));
+        if ((int64_t)n_groups < width && n_rows > 0) {
+            const int rpb = std::max(1, (n_rows + 63) / 64);
+            PHB_LAUNCH(column_verify_kernel, dim3(w_grid, (unsigned)((n_rows + rpb - 1) / rpb)), dim3(256), d0.stream,
+                       raw.as<uint8_t>(), pitch, n_rows, rpb, width, rep.as<uint32_t>(), flag.as<unsigned int>());
+            CHECK_LAUNCH();
+        }
+        unsigned int mismatch = 0;
+        CU(cudaMemcpyAsync(&mismatch, flag.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, d0.stream));
+        CU(cudaStreamSynchronize(d0.stream));
+        if (mismatch) { // two different columns share a 64-bit hash: hash again under another key
+            if (attempt == 3) return ctx->fail(PHB_ERR_NUMERICAL_INSTABILITY, "compress_columns: hash collisions under 4 keys");
+            continue;
+        }
+        P = (int64_t)n_groups;
+        break;
+    }
+    // 4. pattern ids in order of first appearance
+    CU(dev_scan(temp.p, temp_bytes, isrep.as<uint32_t>(), pid.as<uint32_t>(), width, false, d0.stream));
+    PHB_LAUNCH(pattern_index_kernel, dim3(w_grid), dim3(256), d0.stream, rep.as<uint32_t>(), isrep.as<uint32_t>(),
+               pid.as<uint32_t>(), size_at.as<uint32_t>(), width, replist.as<uint32_t>(), s2p.as<uint64_t>(), mult.as<uint64_t>());
+    CHECK_LAUNCH();
+    if (site_to_pattern)
+        CU(cudaMemcpyAsync(site_to_pattern, s2p.p, sizeof(uint64_t) * W, cudaMemcpyDeviceToHost, d0.stream));
+    if (multiplicity)
+        CU(cudaMemcpyAsync(multiplicity, mult.p, sizeof(uint64_t) * (size_t)P, cudaMemcpyDeviceToHost, d0.stream));
+    CU(cudaStreamSynchronize(d0.stream));
+    // 5. the unique columns become the context's alignment: tip codes [row][pattern] per device shard
+    int rc = shard_and_alloc(ctx, n_rows, P);
+    if (rc) return rc;
+    ctx->row_invalid_host.assign(std::max(n_rows, 1), 0);
+    for (Device &d : ctx->devs) {
+        const bool same = &d == &d0;
+        CU(cudaSetDevice(d0.ordinal));
+        uint8_t *dst_tips = d.tips.as<uint8_t>();
+        double *dst_mult = d.mult.as<double>();
+        int *dst_flags = d.row_invalid.as<int>();
+        if (!same) { // gather on device 0, then one device-to-device copy per buffer
+            const size_t need = (size_t)rows_alloc * (size_t)d.P_pad + sizeof(double) * (size_t)d.P_pad + sizeof(int) * (size_t)rows_alloc + 64;
+            CU(stage.ensure(need));
+            dst_mult = stage.as<double>();
+            dst_flags = reinterpret_cast<int *>(stage.as<uint8_t>() + sizeof(double) * (size_t)d.P_pad);
+            dst_tips = stage.as<uint8_t>() + sizeof(double) * (size_t)d.P_pad + sizeof(int) * (size_t)rows_alloc;
+            CU(cudaMemsetAsync(dst_flags, 0, sizeof(int) * (size_t)rows_alloc, d0.stream));
+            CU(cudaStreamSynchronize(d.stream)); // shard_and_alloc's memsets on the destination
+        }
+        for (int r0 = 0; r0 < n_rows && d.P > 0; r0 += 32768) {
+            const int nr = std::min(32768, n_rows - r0);
+            dim3 grid((unsigned)std::min<int64_t>((d.P + 255) / 256, 4096), (unsigned)nr);
+            PHB_LAUNCH(gather_patterns_kernel, grid, dim3(256), d0.stream, raw.as<uint8_t>() + (size_t)r0 * pitch, pitch,
+                       replist.as<uint32_t>(), d.p_begin, d.P, dst_tips + (size_t)r0 * d.P_pad, d.P_pad, (int64_t)0,
+                       dst_flags + r0);
+            CHECK_LAUNCH();
+        }
+        for (int r0 = 0; r0 < n_rows && d.P_pad > d.P; r0 += 32768) {
+            dim3 grid((unsigned)((d.P_pad - d.P + 255) / 256), (unsigned)std::min(32768, n_rows - r0));
+            PHB_LAUNCH(fill_pad_kernel, grid, dim3(256), d0.stream, dst_tips, r0, d.P, d.P_pad);
+            CHECK_LAUNCH();
+        }
+        PHB_LAUNCH(mult_u64_to_double_kernel, dim3((unsigned)std::min<int64_t>((d.P_pad + 255) / 256, 4096)), dim3(256), d0.stream,
+                   mult.as<uint64_t>(), d.p_begin, d.P, d.P_pad, dst_mult);
+        CHECK_LAUNCH();
+        if (!same) {
+            CU(cudaMemcpyAsync(d.tips.p, dst_tips, (size_t)rows_alloc * (size_t)d.P_pad, cudaMemcpyDeviceToDevice, d0.stream));
+            CU(cudaMemcpyAsync(d.mult.p, dst_mult, sizeof(double) * (size_t)d.P_pad, cudaMemcpyDeviceToDevice, d0.stream));
+            CU(cudaMemcpyAsync(d.row_invalid.p, dst_flags, sizeof(int) * (size_t)rows_alloc, cudaMemcpyDeviceToDevice, d0.stream));
+        }
+        CU(cudaStreamSynchronize(d0.stream));
+    }
+    rc = gather_row_flags(ctx, n_rows);
+    if (rc) return rc;
+    *n_patterns = P;
+    ctx->have_aln = true;
+    return PHB_OK;
+}
+
+int32_t phb_compress_columns(phb_ctx *ctx, int32_t n_rows, int64_t width, const uint8_t *bytes, int64_t *n_patterns,
+                             uint64_t *site_to_pattern, uint64_t *multiplicity)
+{
+    return compress_impl(ctx, n_rows, width, bytes, nullptr, n_patterns, site_to_pattern, multiplicity);
+}
+
+int32_t phb_compress_rows(phb_ctx *ctx, int32_t n_rows, int64_t width, const uint8_t *const *rows, int64_t *n_patterns,
+                          uint64_t *site_to_pattern, uint64_t *multiplicity)
+{
+    return compress_impl(ctx, n_rows, width, nullptr, rows, n_patterns, site_to_pattern, multiplicity);
 }
 
 int32_t phb_set_model(phb_ctx *ctx, const double *lambda, const double *V, const double *pi, const double *sqrt_pi,

@@ -25,6 +25,7 @@ struct Api {
     decltype(&phb_ctx_create) ctx_create = nullptr;
     decltype(&phb_ctx_destroy) ctx_destroy = nullptr;
     decltype(&phb_set_alignment) set_alignment = nullptr;
+    decltype(&phb_compress_rows) compress_rows = nullptr;
     decltype(&phb_set_model) set_model = nullptr;
     decltype(&phb_set_tree) set_tree = nullptr;
     decltype(&phb_log_likelihood) log_likelihood = nullptr;
@@ -77,6 +78,7 @@ const Api &api()
     a.ctx_create = reinterpret_cast<decltype(a.ctx_create)>(sym("phb_ctx_create"));
     a.ctx_destroy = reinterpret_cast<decltype(a.ctx_destroy)>(sym("phb_ctx_destroy"));
     a.set_alignment = reinterpret_cast<decltype(a.set_alignment)>(sym("phb_set_alignment"));
+    a.compress_rows = reinterpret_cast<decltype(a.compress_rows)>(sym("phb_compress_rows"));
     a.set_model = reinterpret_cast<decltype(a.set_model)>(sym("phb_set_model"));
     a.set_tree = reinterpret_cast<decltype(a.set_tree)>(sym("phb_set_tree"));
     a.log_likelihood = reinterpret_cast<decltype(a.log_likelihood)>(sym("phb_log_likelihood"));
@@ -194,40 +196,31 @@ void load_model(phb_ctx *c, const GtrModel &m)
                              weights.data()));
 }
 
-// compress + resolve (host side, may throw the reference's errors before the device is touched), then
-// model and tree upload.  `pack` receives the patterns as [pattern][row] bytes + multiplicities.
-struct Packed {
-    std::vector<std::uint8_t> bytes;
-    std::vector<std::uint64_t> mult;
-    std::size_t rows = 0, P = 0;
-};
-
-phb_ctx *load_model_and_tree(const PhyloTree &tree, const GtrModel &model, const Alignment &aln, CompressedColumns &comp,
-                             Flat &flat, Packed &pk)
+// The engines' common prologue with the column compression done ON THE DEVICE (phb_compress_rows replaces
+// Alignment::compress_columns, alignment.rs:93-125): rows resolve to nodes first (the reference's errors,
+// likelihood.rs:172-178), then model, tree, and the raw sequences go over as they lie in Alignment.seqs.
+// s2p (nullable) receives site_to_pattern; returns the pattern count through n_patterns.
+phb_ctx *load_device_compressed(const PhyloTree &tree, const GtrModel &model, const Alignment &aln, Flat &flat,
+                                std::vector<std::uint64_t> *s2p, std::size_t &n_patterns)
 {
-    comp = aln.compress_columns();
-    flat = flatten(tree, comp.leaf_order);
-    pk.rows = comp.leaf_order.size();
-    pk.P = comp.patterns.size();
-    pk.bytes.assign(std::max<std::size_t>(pk.rows * pk.P, 1), 0);
-    pk.mult.assign(std::max<std::size_t>(pk.P, 1), 0);
-    for (std::size_t p = 0; p < pk.P; ++p) {
-        if (pk.rows) std::memcpy(pk.bytes.data() + p * pk.rows, comp.patterns[p].data(), pk.rows);
-        pk.mult[p] = comp.multiplicity[p];
+    std::vector<std::string> leaf_order;
+    std::vector<const std::uint8_t *> rows;
+    leaf_order.reserve(aln.seqs.size());
+    for (const auto &kv : aln.seqs) {
+        leaf_order.push_back(kv.first);
+        rows.push_back(kv.second.data());
     }
+    flat = flatten(tree, leaf_order);
     phb_ctx *c = context();
     load_model(c, model);
     check(c, api().set_tree(c, (int32_t)flat.ids.size(), flat.post.data(), flat.off.data(), flat.kids.data(),
                             flat.blen.data(), flat.leaf_row.data(), flat.root));
-    return c;
-}
-
-// ... plus the alignment, for the engines that keep it resident (ASR, NNI batches)
-phb_ctx *load_all(const PhyloTree &tree, const GtrModel &model, const Alignment &aln, CompressedColumns &comp, Flat &flat)
-{
-    Packed pk;
-    phb_ctx *c = load_model_and_tree(tree, model, aln, comp, flat, pk);
-    check(c, api().set_alignment(c, (int32_t)pk.rows, (int64_t)pk.P, pk.bytes.data(), PHB_LAYOUT_PATTERN_MAJOR, pk.mult.data()));
+    if (s2p) s2p->assign(std::max<std::size_t>(aln.width, 1), 0);
+    if (rows.empty()) rows.push_back(nullptr);
+    int64_t P = 0;
+    check(c, api().compress_rows(c, (int32_t)aln.seqs.size(), (int64_t)aln.width, rows.data(), &P, s2p ? s2p->data() : nullptr,
+                                 nullptr));
+    n_patterns = (std::size_t)P;
     return c;
 }
 
@@ -282,14 +275,12 @@ std::array<double, 16> GtrModel::category_transition(std::size_t category, doubl
 // =====================================================================================================
 double PhyloTree::log_likelihood(const GtrModel &model, const Alignment &aln) const
 {
-    // one call: host bytes in, lnL out (the H2D copy is pipelined with the packing and the sweep)
-    CompressedColumns comp;
+    // raw sequences in, lnL out: compression (alignment.rs:93-125) and pruning (likelihood.rs:156-209) on the device
     Flat flat;
-    Packed pk;
-    phb_ctx *c = load_model_and_tree(*this, model, aln, comp, flat, pk);
+    std::size_t P = 0;
+    phb_ctx *c = load_device_compressed(*this, model, aln, flat, nullptr, P);
     double total = 0.0;
-    check(c, api().log_likelihood_host(c, (int32_t)pk.rows, (int64_t)pk.P, pk.bytes.data(), PHB_LAYOUT_PATTERN_MAJOR,
-                                       pk.mult.data(), &total, nullptr));
+    check(c, api().log_likelihood(c, &total, nullptr));
     return total;
 }
 
@@ -298,10 +289,11 @@ double PhyloTree::log_likelihood(const GtrModel &model, const Alignment &aln) co
 // =====================================================================================================
 Reconstruction PhyloTree::marginal_asr(const GtrModel &model, const Alignment &aln, bool want_posteriors) const
 {
-    CompressedColumns comp;
     Flat flat;
-    phb_ctx *c = load_all(*this, model, aln, comp, flat);
-    const std::size_t n = flat.ids.size(), P = comp.patterns.size(), width = aln.width;
+    std::vector<std::uint64_t> s2p;
+    std::size_t P = 0;
+    phb_ctx *c = load_device_compressed(*this, model, aln, flat, &s2p, P);
+    const std::size_t n = flat.ids.size(), width = aln.width;
     std::vector<std::uint8_t> states(std::max<std::size_t>(n * P, 1));
     std::vector<double> post;
     if (want_posteriors) post.resize(std::max<std::size_t>(n * P * 4, 1));
@@ -312,13 +304,13 @@ Reconstruction PhyloTree::marginal_asr(const GtrModel &model, const Alignment &a
     for (std::size_t k = 0; k < n; ++k) {
         std::vector<std::size_t> seq(width, 0);
         const std::uint8_t *row = states.data() + k * P;
-        for (std::size_t s = 0; s < width; ++s) seq[s] = row[comp.site_to_pattern[s]];
+        for (std::size_t s = 0; s < width; ++s) seq[s] = row[s2p[s]];
         rec.sequences.emplace(flat.ids[k], std::move(seq));
         if (want_posteriors) {
             std::vector<std::array<double, 4>> pp(width, std::array<double, 4>{0.0, 0.0, 0.0, 0.0});
             const double *prow = post.data() + k * P * 4;
             for (std::size_t s = 0; s < width; ++s)
-                std::memcpy(pp[s].data(), prow + comp.site_to_pattern[s] * 4, sizeof(double) * 4);
+                std::memcpy(pp[s].data(), prow + s2p[s] * 4, sizeof(double) * 4);
             rec.posteriors->emplace(flat.ids[k], std::move(pp));
         }
     }
@@ -330,17 +322,18 @@ Reconstruction PhyloTree::marginal_asr(const GtrModel &model, const Alignment &a
 // =====================================================================================================
 Reconstruction PhyloTree::joint_asr(const GtrModel &model, const Alignment &aln) const
 {
-    CompressedColumns comp;
     Flat flat;
-    phb_ctx *c = load_all(*this, model, aln, comp, flat);
-    const std::size_t n = flat.ids.size(), P = comp.patterns.size(), width = aln.width;
+    std::vector<std::uint64_t> s2p;
+    std::size_t P = 0;
+    phb_ctx *c = load_device_compressed(*this, model, aln, flat, &s2p, P);
+    const std::size_t n = flat.ids.size(), width = aln.width;
     std::vector<std::uint8_t> states(std::max<std::size_t>(n * P, 1));
     Reconstruction rec;
     check(c, api().joint_asr(c, states.data(), &rec.log_likelihood));
     for (std::size_t k = 0; k < n; ++k) { // every node id gets an entry (:453-456), expanded to sites (:545-551)
         std::vector<std::size_t> seq(width, 0);
         const std::uint8_t *row = states.data() + k * P;
-        for (std::size_t s = 0; s < width; ++s) seq[s] = row[comp.site_to_pattern[s]];
+        for (std::size_t s = 0; s < width; ++s) seq[s] = row[s2p[s]];
         rec.sequences.emplace(flat.ids[k], std::move(seq));
     }
     return rec;
@@ -352,9 +345,9 @@ Reconstruction PhyloTree::joint_asr(const GtrModel &model, const Alignment &aln)
 std::vector<double> PhyloTree::score_nni_neighbours(const GtrModel &model, const Alignment &aln,
                                                     const std::vector<std::pair<NodeID, bool>> &moves) const
 {
-    CompressedColumns comp;
     Flat flat;
-    phb_ctx *c = load_all(*this, model, aln, comp, flat);
+    std::size_t P = 0;
+    phb_ctx *c = load_device_compressed(*this, model, aln, flat, nullptr, P);
     std::vector<int32_t> ids(std::max<std::size_t>(moves.size(), 1), -1);
     std::vector<std::uint8_t> left(std::max<std::size_t>(moves.size(), 1), 0);
     for (std::size_t i = 0; i < moves.size(); ++i) {

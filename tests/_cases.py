@@ -119,3 +119,27 @@ def check_joint(lib, case, devices=None, budget=None):
         val = oracle.joint_assignment_value(case.ft, case.model, case.patterns[p], states[:, p])
         assert abs(val - ref_per[p]) <= 1e-9 * max(1.0, abs(ref_per[p])), f"pattern {p}: joint states differ away from a tie"
     return len(diff), st
+
+
+def check_compress(lib, rows, devices=None):
+    """phb_compress_columns against the oracle's restatement of Alignment::compress_columns
+    (src/alignment.rs:93-125): pattern count, site_to_pattern and multiplicity bit-exact, and the context's
+    alignment afterwards holds the patterns in first-appearance order (canonical bytes: U reads back as T)."""
+    from oracle import RefAlignment
+
+    rows = np.ascontiguousarray(rows, np.uint8)
+    n_rows, width = rows.shape
+    aln = RefAlignment({f"r{i}": bytes(rows[i]) for i in range(n_rows)}, width)
+    pats, s2p, mult, _lo = aln.compress_columns()
+    with capi.Context(devices=devices, library=lib) as ctx:
+        n, got_s2p, got_mult = ctx.compress_columns(rows)
+        back = ctx.get_alignment() if n and n_rows else None
+    assert n == len(pats)
+    assert np.array_equal(got_s2p.astype(np.int64), s2p)
+    assert np.array_equal(got_mult, mult)
+    if back is not None:
+        canon = pats.copy()
+        canon[canon == ord("U")] = ord("T")
+        valid = np.isin(canon, np.frombuffer(b"ACGTRYSWKMBDHVN-", np.uint8))
+        assert np.array_equal(back[valid], canon[valid]) and np.all(back[~valid] == ord("?"))
+    return n

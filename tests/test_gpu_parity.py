@@ -207,6 +207,45 @@ def test_joint_asr_edge_cases(gpu_lib):
     _cases.check_joint(gpu_lib, workloads.Case(t3, oracle.flatten(t3, lo), RefModel.jukes_cantor(), "jc69", pats, mult, lo))
 
 
+def test_compress_columns(gpu_lib):
+    rng = np.random.default_rng(78)
+    base = rng.choice(np.frombuffer(b"ACGTUN-R?", np.uint8), size=(11, 300))
+    _cases.check_compress(gpu_lib, base[:, rng.integers(0, 300, size=50_000)])
+    _cases.check_compress(gpu_lib, rng.choice(np.frombuffer(b"ACGT", np.uint8), size=(64, 10_000)))   # config-1 shape
+    _cases.check_compress(gpu_lib, rng.choice(np.frombuffer(b"ACGT", np.uint8), size=(4, 20_001)))    # <= 256 distinct columns
+    _cases.check_compress(gpu_lib, np.full((3, 17), ord("A"), np.uint8))
+    case = workloads.make_case(40, 6000, model="gtr_g4", seed=22)
+    host = workloads.make_case(40, 6000, model="gtr_g4", seed=22, compress=True)
+    ref, _ = oracle.log_likelihood_flat(host.ft, host.model, host.patterns, host.mult, mode=2, n_threads=8)
+    with capi.Context(library=gpu_lib) as ctx:
+        workloads.load_into(ctx, case)
+        n, s2p, mult = ctx.compress_columns(np.ascontiguousarray(case.patterns.T))
+        assert n == len(host.patterns) and np.array_equal(mult, host.mult)
+        tot = ctx.log_likelihood()
+    assert abs(tot - ref) <= 1e-9 * abs(ref)
+
+
+def test_compress_columns_full_size_properties(gpu_lib):
+    """1,000 rows x 1M sites drawn from 50,000 distinct columns: multiplicities sum to the width, site_to_pattern is
+    a first-appearance numbering (each new maximum exceeds the previous by exactly one), sites mapped to the same
+    pattern hold identical columns (sampled), and the pattern count equals numpy's unique count."""
+    rng = np.random.default_rng(79)
+    base = rng.choice(np.frombuffer(b"ACGT", np.uint8), size=(1000, 50_000))
+    pick = rng.integers(0, 50_000, size=1_000_000)
+    rows = np.ascontiguousarray(base[:, pick])
+    with capi.Context(library=gpu_lib) as ctx:
+        n, s2p, mult = ctx.compress_columns(rows)
+    s2p = s2p.astype(np.int64)
+    assert int(mult.sum()) == rows.shape[1] and np.array_equal(np.bincount(s2p, minlength=n).astype(np.uint64), mult)
+    run_max = np.maximum.accumulate(s2p)
+    new = np.nonzero(np.diff(np.concatenate([[-1], run_max])) > 0)[0]
+    assert np.array_equal(s2p[new], np.arange(n))           # first appearances are numbered 0,1,2,... in site order
+    # distinct columns of `base` may coincide by chance only with negligible probability at 1,000 rows
+    assert n == len(np.unique(pick))
+    for s in rng.integers(0, rows.shape[1], size=2000):
+        assert np.array_equal(rows[:, s], rows[:, new[s2p[s]]])
+
+
 def test_score_nni(gpu_lib):
     """Path-only NNI rescoring (csrc/nni.cuh) vs the oracle on every rebuilt neighbour; vs full rescoring."""
     case = workloads.make_case(16, 500, model="gtr_g4", seed=28)

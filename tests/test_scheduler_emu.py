@@ -254,6 +254,42 @@ def test_joint_asr_tiling_sharding_and_shapes(emu_lib):
     assert _cases.check_joint(emu_lib, zc)[0] == 0
 
 
+def test_compress_columns_matches_reference_walk(emu_lib):
+    rng = np.random.default_rng(77)
+    # few distinct columns, many repeats; T vs U and an invalid byte are distinct keys (raw bytes are compared)
+    base = rng.choice(np.frombuffer(b"ACGTUN-R?", np.uint8), size=(7, 40))
+    rows = base[:, rng.integers(0, 40, size=1000)]
+    n = _cases.check_compress(emu_lib, rows)
+    assert n <= 40
+    _cases.check_compress(emu_lib, rows, devices=[0, 0, 0])             # shards of the unique patterns
+    with capi.Context(library=emu_lib) as ctx:                          # one pointer per row (Alignment.seqs layout)
+        a = ctx.compress_columns(rows)
+        b = ctx.compress_rows([bytes(r) for r in rows])
+        assert a[0] == b[0] and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+    _cases.check_compress(emu_lib, rng.choice(np.frombuffer(b"ACGT", np.uint8), size=(30, 333)))  # (almost) all unique
+    _cases.check_compress(emu_lib, np.full((3, 17), ord("A"), np.uint8))  # one pattern
+    _cases.check_compress(emu_lib, rng.choice(np.frombuffer(b"AC", np.uint8), size=(1, 9)))       # a single row
+    with capi.Context(library=emu_lib) as ctx:
+        n, s2p, mult = ctx.compress_columns(np.zeros((4, 0), np.uint8))
+        assert n == 0 and len(s2p) == 0 and len(mult) == 0
+
+
+def test_compress_then_score_equals_host_compression(emu_lib):
+    """compress on the device, then evaluate: same lnL as handing over the host-compressed patterns."""
+    case = workloads.make_case(9, 700, model="gtr_i_g4", seed=21)
+    rows = np.ascontiguousarray(case.patterns.T)  # [row][site]: uncompressed simulated sites
+    host = workloads.make_case(9, 700, model="gtr_i_g4", seed=21, compress=True)
+    ref, _ = oracle.log_likelihood_flat(host.ft, host.model, host.patterns, host.mult)
+    with capi.Context(library=emu_lib) as ctx:
+        workloads.load_into(ctx, case)
+        n, s2p, mult = ctx.compress_columns(rows)
+        assert n == len(host.patterns) and np.array_equal(mult, host.mult)
+        tot, per = ctx.log_likelihood(per_pattern=True)
+        assert abs(tot - ref) <= 1e-9 * abs(ref)
+        tot_a, states, _ = ctx.marginal_asr()
+        assert states.shape == (case.ft["n_nodes"], n)
+
+
 def test_simulated_alignment_roundtrip(emu_lib):
     case = workloads.make_case(7, 10, model="gtr_g4", seed=13)
     with capi.Context(library=emu_lib) as ctx:

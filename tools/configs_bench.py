@@ -118,6 +118,47 @@ def run_joint(tag, n_taxa, n_sites, model, seed, reps):
                 state_histogram=np.bincount(states[:, :4096].ravel(), minlength=4).tolist())
 
 
+def run_compress(tag, n_taxa, n_sites, distinct, seed, reps):
+    """phb_compress_columns from pinned host rows [row][site]: H2D + hash + sort + verify + gather, end to end."""
+    import torch
+
+    tree = synthetic.yule_flat(n_taxa, seed)
+    with capi.Context(flags=capi.FLAG_TIMING) as ctx:
+        synthetic.load_into(ctx, tree, model_for("gtr_g4"))
+        n_sim = distinct or n_sites
+        ctx.simulate_alignment(n_sim, seed=seed ^ 0xA11C)
+        host = torch.empty((n_taxa, n_sites), dtype=torch.uint8, pin_memory=True)
+        h = host.numpy()
+        chunk = max(1, (256 << 20) // n_taxa)
+        rng = np.random.default_rng(seed)
+        pick = rng.integers(0, n_sim, size=n_sites) if distinct else None
+        if distinct:
+            base = ctx.get_alignment(0, n_sim).T  # [row][distinct]
+            for p0 in range(0, n_sites, chunk):
+                h[:, p0:p0 + chunk] = base[:, pick[p0:p0 + chunk]]
+        else:
+            for p0 in range(0, n_sites, chunk):
+                c = min(chunk, n_sites - p0)
+                h[:, p0:p0 + c] = ctx.get_alignment(p0, c).T
+        s2p = np.zeros(n_sites, np.uint64)
+        mult = np.zeros(n_sites, np.uint64)
+        n = capi.C.c_int64(0)
+        u64p = capi.C.POINTER(capi.C.c_uint64)
+
+        def call():
+            ctx._check(ctx.lib.L.phb_compress_columns(ctx._h, n_taxa, n_sites, capi.C.c_void_p(host.data_ptr()), capi.C.byref(n),
+                                                      s2p.ctypes.data_as(u64p), mult.ctypes.data_as(u64p)))
+            return n.value
+
+        P, dev_ms, wall_ms = timed(ctx, call, reps)
+        ctx.n_rows, ctx.n_patterns = n_taxa, int(P)
+        lnl = ctx.log_likelihood()
+    nbytes = n_taxa * n_sites
+    return dict(case=tag, rows=n_taxa, sites=n_sites, n_patterns=int(P), wall_ms=wall_ms, device_ms=dev_ms,
+                input_GB=nbytes / 1e9, end_to_end_GBps=nbytes / (wall_ms * 1e-3) / 1e9, lnl_after=lnl,
+                mult_sum=int(mult[:P].sum()), note="pinned host rows; includes the H2D copy of the whole alignment")
+
+
 def run_nni(tag, n_taxa, n_sites, model, seed, n_moves, reps, flags=0):
     tree = synthetic.yule_flat(n_taxa, seed)
     co = tree["child_off"]
@@ -155,6 +196,9 @@ CASES = {
     "cfg4_small": lambda r: run_asr("cfg4/10 marginal ASR GTR+G4 5000 x 50k", 5000, 50_000, "gtr_g4", 0x5EED0004, r),
     "joint_small": lambda r: run_joint("joint ASR GTR+G4 5000 x 50k", 5000, 50_000, "gtr_g4", 0x5EED0004, r),
     "joint": lambda r: run_joint("joint ASR GTR+G4 5000 x 500k", 5000, 500_000, "gtr_g4", 0x5EED0004, r),
+    "compress_dup": lambda r: run_compress("compress 1000 rows x 1M sites, 50k distinct columns", 1000, 1_000_000, 50_000, 0x5EED0002, r),
+    "compress_cfg2": lambda r: run_compress("compress cfg2 1000 rows x 100k sites (all distinct)", 1000, 100_000, 0, 0x5EED0002, r),
+    "compress_cfg3": lambda r: run_compress("compress cfg3 10000 rows x 1M sites (all distinct)", 10_000, 1_000_000, 0, 0x5EED0003, r),
     "cfg5": lambda r: run_nni("cfg5 1024 NNI neighbours 2000 x 200k", 2000, 200_000, "gtr_g4", 0x5EED0005, 1024, r),
     "cfg5_full_128": lambda r: run_nni("cfg5/8 128 NNI neighbours 2000 x 200k, full rescoring", 2000, 200_000, "gtr_g4",
                                        0x5EED0005, 128, r, capi.FLAG_NNI_FULL),
