@@ -54,6 +54,9 @@ extern "C" {
 /* phb_score_nni rescores every neighbour from scratch (the reference's caller loop) instead of walking
  * v -> root against the cached CLVs of the base tree; for cross-checking the two. */
 #define PHB_FLAG_NNI_FULL (1ull << 3)
+/* phb_score_nni walks v -> root per neighbour (one cached CLV read per ancestor) instead of using the
+ * pre-order "upper" partials that make a neighbour a constant-cost edge-local evaluation. */
+#define PHB_FLAG_NNI_WALK (1ull << 4)
 
 /* ---- alignment layouts --------------------------------------------------------------------- */
 #define PHB_LAYOUT_PATTERN_MAJOR 0 /* bytes[pattern][row] — CompressedColumns.patterns, alignment.rs:129-138 */

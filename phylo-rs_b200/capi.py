@@ -26,6 +26,7 @@ FLAG_LITERAL_INVARIANT = 1 << 0
 FLAG_TIMING = 1 << 1
 FLAG_LEVEL_KERNELS = 1 << 2
 FLAG_NNI_FULL = 1 << 3
+FLAG_NNI_WALK = 1 << 4
 LAYOUT_PATTERN_MAJOR = 0
 LAYOUT_ROW_MAJOR = 1
 

@@ -340,4 +340,238 @@ nni_reduce_kernel(const NniMove *__restrict__ moves, const double *__restrict__ 
     if (threadIdx.x == 0) totals[moves[mi].out] += r;
 }
 
+
+// =============================================================================================
+// Edge-local scoring with "upper" partials (the default for binary trees).
+//
+// upper_v[j] = P(all data outside the subtree of v, v in state j): one pre-order pass over the cached
+// CLVs, after which a neighbour costs a constant number of steps irrespective of the depth of v.  For
+// v with children k0, k1, parent p and sibling s, the two neighbours of the edge (p -> v) are
+//     lc = 0 (k0 moves up): v' = (P_k1 L_k1)(.)(P_s L_s),  site L = sum_i W_p[i] (P_v v')_i (P_k0 L_k0)_i
+//     lc = 1 (k1 moves up): v' = (P_k0 L_k0)(.)(P_s L_s),  site L = sum_i W_p[i] (P_v v')_i (P_k1 L_k1)_i
+// with W_p = upper_p (pi at the root) — the same sums the reference's full pruning pass forms at p and
+// above, regrouped (likelihood.rs:113-140); branch lengths travel with the child node (tree.rs:1213-1242).
+// =============================================================================================
+
+// Pre-order pass, one launch per depth.  One block = (parent, category, 512 patterns); a thread = a
+// pattern pair; both children of the (binary) parent are served from one read of the parent's upper.
+// upper / uexps are indexed by CLV slot like clv / exps.  DownOp::pad = the parent's dense node id.
+__global__ void __launch_bounds__(CLV_THREADS)
+upper_level_kernel(const DownOp *__restrict__ ops, int n_ops, const DownChild *__restrict__ kids, int root_node, ModelDev M,
+                   const double *__restrict__ Pmat, const double *__restrict__ clv, double *__restrict__ upper,
+                   size_t slot_stride, size_t tile_pad, int tile_len, int blocks_per_row, const int *__restrict__ exps,
+                   int *__restrict__ uexps, const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off)
+{
+    const int sb = blockIdx.x % blocks_per_row;
+    const int rest = blockIdx.x / blocks_per_row;
+    const int cat = rest % M.n_clv;
+    const int opi = rest / M.n_clv;
+    if (opi >= n_ops) return;
+    const int64_t site = ((int64_t)sb * CLV_THREADS + threadIdx.x) * 2;
+    if (site >= tile_len) return;
+    const DownOp op = ops[opi];
+    if (op.child_end - op.child_begin != 2) return; // binary trees only (the host checks)
+    const DownChild c0 = kids[op.child_begin], c1 = kids[op.child_begin + 1];
+    if (c0.is_tip && c1.is_tip) return;              // no internal child: nothing to produce
+    const int cat_model = M.cat_of_clv[cat];
+    const size_t stride2 = tile_pad / 2;
+    const size_t cat_off = (size_t)cat * 4 * tile_pad + (size_t)site;
+    const size_t exp_off = (size_t)cat * tile_pad + (size_t)site;
+    const size_t exp_stride = (size_t)M.n_clv * tile_pad;
+    double2 base[4];
+    int2 eb = make_int2(0, 0);
+    if (op.pad == root_node) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) base[i] = make_double2(M.pi[i], M.pi[i]);
+    } else {
+        const double2 *u = reinterpret_cast<const double2 *>(upper + (size_t)op.parent_slot * slot_stride + cat_off);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) base[i] = u[i * stride2];
+        eb = *reinterpret_cast<const int2 *>(uexps + (size_t)op.parent_slot * exp_stride + exp_off);
+    }
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+        const DownChild me = which ? c1 : c0, sib = which ? c0 : c1;
+        if (me.is_tip) continue;
+        double p[16];
+        double2 sv[4];
+        int2 e = eb;
+        load_P(Pmat + ((size_t)sib.node * M.n_cat + cat_model) * 16, p);
+        if (sib.is_tip) contrib_tip(p, tips + (int64_t)sib.src * P_pad + tile_off + site, sv);
+        else {
+            contrib_internal(p, reinterpret_cast<const double2 *>(clv + (size_t)sib.src * slot_stride + cat_off), stride2, sv);
+            const int2 es = *reinterpret_cast<const int2 *>(exps + (size_t)sib.src * exp_stride + exp_off);
+            e.x += es.x; e.y += es.y;
+        }
+        double wx[4], wy[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            wx[i] = base[i].x * sv[i].x;
+            wy[i] = base[i].y * sv[i].y;
+        }
+        load_P(Pmat + ((size_t)me.node * M.n_cat + cat_model) * 16, p);
+        double ox[4], oy[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { // upper_me[j] = sum_i P_me[i][j] W[i]
+            ox[j] = p[j] * wx[0] + p[4 + j] * wx[1] + p[8 + j] * wx[2] + p[12 + j] * wx[3];
+            oy[j] = p[j] * wy[0] + p[4 + j] * wy[1] + p[8 + j] * wy[2] + p[12 + j] * wy[3];
+        }
+        e.x += rescale_site_local(ox[0], ox[1], ox[2], ox[3]);
+        e.y += rescale_site_local(oy[0], oy[1], oy[2], oy[3]);
+        double2 *dst = reinterpret_cast<double2 *>(upper + (size_t)me.src * slot_stride + cat_off);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) dst[j * stride2] = make_double2(ox[j], oy[j]);
+        *reinterpret_cast<int2 *>(uexps + (size_t)me.src * exp_stride + exp_off) = e;
+    }
+}
+
+// One job = the edge (p -> v): up to two neighbours (out0: k0 moves up, out1: k1 moves up; -1 = not asked).
+struct NniEdgeJob {
+    int32_t k0_src, k0_edge, k0_is_tip;
+    int32_t k1_src, k1_edge, k1_is_tip;
+    int32_t s_src, s_edge, s_is_tip;
+    int32_t v_edge;       // dense id of v (its edge to p)
+    int32_t p_upper_slot; // CLV slot of p, -1 = p is the root (W = pi)
+    int32_t out0, out1;
+    int32_t pad[3];
+};
+
+template <int NC>
+__global__ void __launch_bounds__(nni_threads(NC), 2)
+nni_edge_kernel(const NniEdgeJob *__restrict__ jobs, int n_jobs, ModelDev M, const double *__restrict__ Pmat,
+                const double *__restrict__ clv, const double *__restrict__ upper, size_t slot_stride, size_t tile_pad,
+                int tile_len, const int *__restrict__ exps, const int *__restrict__ uexps, const uint8_t *__restrict__ tips,
+                int64_t P_pad, int64_t tile_off, const double *__restrict__ leaf_ls, const uint8_t *__restrict__ inv_mask,
+                const double *__restrict__ mult, double *__restrict__ partials /* [job][2][n_site_blocks] */, int n_site_blocks)
+{
+    constexpr int BS = nni_block_sites(NC), NT = nni_threads(NC);
+    __shared__ __align__(16) double sP[4 * NC * 16]; // k0, k1, s, v
+    __shared__ double sLL[2][NC][BS];
+    const int ji = blockIdx.x % n_jobs;
+    const int sb = blockIdx.x / n_jobs;
+    const NniEdgeJob jb = jobs[ji];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int cat = warp % NC, grp = warp / NC;
+    const int cat_model = M.cat_of_clv[cat];
+    const int ncm = M.n_cat;
+    const int local = grp * 64 + lane * 2;
+    const int64_t site = (int64_t)sb * BS + local;
+    const bool live = site < tile_len;
+    for (int i = threadIdx.x; i < 4 * NC * 16; i += NT) {
+        const int e = i & 15, c = (i >> 4) % NC, which = i / (16 * NC);
+        const int edge = which == 0 ? jb.k0_edge : which == 1 ? jb.k1_edge : which == 2 ? jb.s_edge : jb.v_edge;
+        sP[i] = Pmat[((size_t)edge * ncm + M.cat_of_clv[c]) * 16 + e];
+    }
+    NniSib d0, d1, ds;
+    double2 w[4];
+    int2 ew = make_int2(0, 0);
+    if (live) {
+        nni_load_sib(d0, jb.k0_is_tip != 0, jb.k0_src, cat, NC, clv, slot_stride, tile_pad, exps, tips, P_pad, tile_off, site);
+        nni_load_sib(d1, jb.k1_is_tip != 0, jb.k1_src, cat, NC, clv, slot_stride, tile_pad, exps, tips, P_pad, tile_off, site);
+        nni_load_sib(ds, jb.s_is_tip != 0, jb.s_src, cat, NC, clv, slot_stride, tile_pad, exps, tips, P_pad, tile_off, site);
+        if (jb.p_upper_slot >= 0) {
+            const double2 *u = reinterpret_cast<const double2 *>(upper + (size_t)jb.p_upper_slot * slot_stride +
+                                                                 (size_t)cat * 4 * tile_pad + (size_t)site);
+            const size_t stride2 = tile_pad / 2;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) w[i] = u[i * stride2];
+            ew = *reinterpret_cast<const int2 *>(uexps + ((size_t)jb.p_upper_slot * NC + cat) * tile_pad + (size_t)site);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) w[i] = make_double2(M.pi[i], M.pi[i]);
+        }
+    }
+    __syncthreads();
+    if (live) {
+        double2 c0[4], c1[4], cs[4];
+        nni_apply_sib(sP + (0 * NC + cat) * 16, d0, jb.k0_is_tip != 0, c0);
+        nni_apply_sib(sP + (1 * NC + cat) * 16, d1, jb.k1_is_tip != 0, c1);
+        nni_apply_sib(sP + (2 * NC + cat) * 16, ds, jb.s_is_tip != 0, cs);
+        const double2 *Pv = reinterpret_cast<const double2 *>(sP + (3 * NC + cat) * 16);
+        const double lsx = leaf_ls[site], lsy = leaf_ls[site + 1];
+#pragma unroll
+        for (int mvi = 0; mvi < 2; ++mvi) {
+            // mvi = 0: k0 moves up, k1 stays;  mvi = 1: k1 moves up, k0 stays
+            const double2(&stay)[4] = mvi ? c0 : c1;
+            const double2(&up)[4] = mvi ? c1 : c0;
+            int ex = ew.x + d0.e.x + d1.e.x + ds.e.x, ey = ew.y + d0.e.y + d1.e.y + ds.e.y;
+            double vx[4], vy[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                vx[i] = stay[i].x * cs[i].x;
+                vy[i] = stay[i].y * cs[i].y;
+            }
+            ex += rescale_site_local(vx[0], vx[1], vx[2], vx[3]);
+            ey += rescale_site_local(vy[0], vy[1], vy[2], vy[3]);
+            double mx = 0.0, my = 0.0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const double2 a = Pv[2 * i], b = Pv[2 * i + 1];
+                const double tx = a.x * vx[0] + a.y * vx[1] + b.x * vx[2] + b.y * vx[3];
+                const double ty = a.x * vy[0] + a.y * vy[1] + b.x * vy[2] + b.y * vy[3];
+                mx += w[i].x * (tx * up[i].x);
+                my += w[i].y * (ty * up[i].y);
+            }
+            sLL[mvi][cat][local] = M.ln_weights[cat_model] + log(mx) + (lsx - (double)ex * LN2);
+            sLL[mvi][cat][local + 1] = M.ln_weights[cat_model] + log(my) + (lsy - (double)ey * LN2);
+        }
+    }
+    __syncthreads();
+    double contrib0 = 0.0, contrib1 = 0.0;
+    for (int q = threadIdx.x; q < BS; q += NT) {
+        const int64_t sq = (int64_t)sb * BS + q;
+        if (sq >= tile_len) continue;
+        double inv_ll = 0.0;
+        bool have_inv = false;
+        for (int c = 0; c < M.n_cat; ++c)
+            if (M.clv_idx[c] < 0 && !have_inv) { // all rate-0 categories share the mass; weights differ
+                have_inv = true;
+                double mass = 0.0;
+                const uint32_t m = inv_mask[sq];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) mass += M.pi[i] * (((m >> i) & 1u) ? 1.0 : 0.0);
+                inv_ll = log(mass) + leaf_ls[sq];
+            }
+#pragma unroll
+        for (int mvi = 0; mvi < 2; ++mvi) {
+            double lls[MAX_CAT];
+            double mxl = -INFINITY;
+            for (int c = 0; c < M.n_cat; ++c) {
+                const int cc = M.clv_idx[c];
+                const double ll = cc >= 0 ? sLL[mvi][cc][q] : M.ln_weights[c] + inv_ll;
+                lls[c] = ll;
+                mxl = fmax(mxl, ll);
+            }
+            double site_ll;
+            if (!isfinite(mxl)) site_ll = mxl;
+            else {
+                double acc = 0.0;
+                for (int c = 0; c < M.n_cat; ++c) acc += exp(lls[c] - mxl);
+                site_ll = mxl + log(acc);
+            }
+            if (mvi) contrib1 += mult[sq] * site_ll;
+            else contrib0 += mult[sq] * site_ll;
+        }
+    }
+    const double r0 = block_reduce_sum(contrib0);
+    const double r1 = block_reduce_sum(contrib1);
+    if (threadIdx.x == 0) {
+        partials[((size_t)ji * 2 + 0) * n_site_blocks + sb] = r0;
+        partials[((size_t)ji * 2 + 1) * n_site_blocks + sb] = r1;
+    }
+}
+
+// totals[out[row]] += sum of row `row` of partials (fixed order); rows with out < 0 are skipped
+__global__ void __launch_bounds__(ROOT_THREADS)
+nni_reduce_rows_kernel(const int32_t *__restrict__ out, const double *__restrict__ partials, int n_site_blocks,
+                       double *__restrict__ totals)
+{
+    const int row = blockIdx.x;
+    const int o = out[row];
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < n_site_blocks; i += blockDim.x) acc += partials[(size_t)row * n_site_blocks + i];
+    const double r = block_reduce_sum(acc);
+    if (threadIdx.x == 0 && o >= 0) totals[o] += r;
+}
+
 } // namespace phb

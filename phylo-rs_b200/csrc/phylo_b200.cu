@@ -237,7 +237,7 @@ struct Device {
     DevBuf tips, mult, leaf_ls, inv_mask, per_pattern, row_invalid, Pmat, blen, clv, scale, cat_ll,
         partials, total, ops, gops, gkids, dops, dkids, leaf_rows, states, posteriors, staging,
         sim_pre, sim_parent, sim_depth, sim_leafrow, sim_stack, scratch, sw_descs, sw_blocks, sw_stream, sw_gstack,
-        sw_err, sw_ops, uops, ukids, lnP, jbest, nni_exps, nni_partials, nni_totals, nni_moves, nni_steps;
+        sw_err, sw_ops, uops, ukids, lnP, jbest, nni_upper, nni_uexps, nni_jobs, nni_rows, nni_exps, nni_partials, nni_totals, nni_moves, nni_steps;
     bool sweep_uploaded = false;
     int sm_count = 0;
     size_t smem_optin = 0;
@@ -964,9 +964,44 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
         mv.step_end = (int)steps.size();
         moves.push_back(mv);
     }
+    // edge-local jobs (upper partials): the two neighbours of one edge (p -> v) share every load
+    const bool use_upper = !(ctx->flags & PHB_FLAG_NNI_WALK);
+    std::vector<NniEdgeJob> jobs;
+    std::vector<int32_t> job_rows; // totals index of partial row 2*job + {0,1}
+    if (use_upper) {
+        read_bytes_per_pattern = 0;
+        std::vector<int> job_of(T.n, -1);
+        for (int m : order) {
+            const int v = node_id[m];
+            if (job_of[v] < 0) {
+                const int p = T.parent[v];
+                const int k0 = T.children[T.child_off[v]], k1 = T.children[T.child_off[v] + 1];
+                const int sn = other_child(p, v);
+                NniEdgeJob jb;
+                memset(&jb, 0, sizeof jb);
+                jb.k0_src = src_of(k0); jb.k0_edge = k0; jb.k0_is_tip = T.slot[k0] < 0;
+                jb.k1_src = src_of(k1); jb.k1_edge = k1; jb.k1_is_tip = T.slot[k1] < 0;
+                jb.s_src = src_of(sn); jb.s_edge = sn; jb.s_is_tip = T.slot[sn] < 0;
+                jb.v_edge = v;
+                jb.p_upper_slot = p == T.root ? -1 : T.slot[p];
+                jb.out0 = jb.out1 = -1;
+                job_of[v] = (int)jobs.size();
+                jobs.push_back(jb);
+                job_rows.push_back(-1);
+                job_rows.push_back(-1);
+                read_bytes_per_pattern += cost_of(k0) + cost_of(k1) + cost_of(sn) + (p == T.root ? 0.0 : 36.0 * M.n_clv);
+            }
+            // a repeated (v, left_ch) keeps its own output row: later duplicates are filled in on the host
+            const int j = job_of[v], w = left_ch[m] ? 1 : 0;
+            if (job_rows[2 * j + w] < 0) {
+                job_rows[2 * j + w] = m;
+                (w ? jobs[j].out1 : jobs[j].out0) = m;
+            }
+        }
+    }
     phb_stats &S = ctx->stats;
     S.nni_path_moves = (int)moves.size();
-    S.nni_path_steps = (int64_t)steps.size();
+    S.nni_path_steps = use_upper ? (int64_t)jobs.size() * 3 : (int64_t)steps.size();
     S.nni_read_bytes = read_bytes_per_pattern * (double)ctx->n_patterns;
     S.nni_tiles = 0;
     S.nni_cache_bytes = 0;
@@ -988,12 +1023,12 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
         CU(cudaMemcpyAsync(d.nni_steps.p, steps.data(), sizeof(NniStep) * steps.size(), cudaMemcpyHostToDevice, d.stream));
         CU(cudaMemsetAsync(d.nni_totals.p, 0, sizeof(double) * (size_t)n_moves, d.stream));
         // tile the pattern axis so that one tile's CLVs + subtree exponents fit the budget
-        const size_t per_site = (size_t)T.n_internal * M.n_clv * (4 * sizeof(double) + sizeof(int));
+        const size_t per_site = (size_t)T.n_internal * M.n_clv * (4 * sizeof(double) + sizeof(int)) * (use_upper ? 2 : 1);
         size_t budget = ctx->clv_budget;
         if (!budget) {
             size_t free_b = 0, total_b = 0;
             CU(cudaMemGetInfo(&free_b, &total_b));
-            budget = (size_t)((double)(free_b + d.clv.cap + d.nni_exps.cap) * 0.85);
+            budget = (size_t)((double)(free_b + d.clv.cap + d.nni_exps.cap + d.nni_upper.cap + d.nni_uexps.cap) * 0.85);
         }
         int64_t tile = d.P_pad;
         if (per_site * (size_t)d.P_pad > budget) {
@@ -1007,9 +1042,17 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
         const size_t slot_stride = (size_t)M.n_clv * 4 * tile_pad;
         CU(d.clv.ensure(sizeof(double) * slot_stride * (size_t)T.n_internal));
         CU(d.nni_exps.ensure(sizeof(int) * (size_t)M.n_clv * tile_pad * (size_t)T.n_internal));
+        if (use_upper) {
+            CU(d.nni_upper.ensure(sizeof(double) * slot_stride * (size_t)T.n_internal));
+            CU(d.nni_uexps.ensure(sizeof(int) * (size_t)M.n_clv * tile_pad * (size_t)T.n_internal));
+            CU(d.nni_jobs.ensure(sizeof(NniEdgeJob) * jobs.size()));
+            CU(d.nni_rows.ensure(sizeof(int32_t) * job_rows.size()));
+            CU(cudaMemcpyAsync(d.nni_jobs.p, jobs.data(), sizeof(NniEdgeJob) * jobs.size(), cudaMemcpyHostToDevice, d.stream));
+            CU(cudaMemcpyAsync(d.nni_rows.p, job_rows.data(), sizeof(int32_t) * job_rows.size(), cudaMemcpyHostToDevice, d.stream));
+        }
         const int nni_bs = nni_block_sites(M.n_clv);
         const int max_sb = (int)((std::min<int64_t>(tile, d.P) + nni_bs - 1) / nni_bs);
-        CU(d.nni_partials.ensure(sizeof(double) * (size_t)nm * (size_t)max_sb));
+        CU(d.nni_partials.ensure(sizeof(double) * (size_t)std::max<size_t>(nm, 2 * jobs.size()) * (size_t)max_sb));
         if (&d == &ctx->devs[0]) {
             S.nni_tiles = n_tiles;
             S.nni_cache_bytes = (double)per_site * (double)d.P;
@@ -1044,6 +1087,42 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
                 CHECK_LAUNCH();
             }
             const int n_sb = (len + nni_bs - 1) / nni_bs;
+            if (use_upper) {
+                for (int dl = 0; dl <= T.max_depth; ++dl) { // upper partials, root downwards
+                    const int nb = T.dlevel_off[dl + 1] - T.dlevel_off[dl];
+                    if (nb <= 0) continue;
+                    ScopedTimer tm(ctx, &d, PH_CLV);
+                    PHB_LAUNCH(upper_level_kernel, dim3((unsigned)((int64_t)nb * M.n_clv * bpr)), dim3(CLV_THREADS), d.stream,
+                               d.dops.as<DownOp>() + T.dlevel_off[dl], nb, d.dkids.as<DownChild>(), T.root, M, d.Pmat.as<double>(),
+                               d.clv.as<double>(), d.nni_upper.as<double>(), slot_stride, tile_pad, len, bpr, d.nni_exps.as<int>(),
+                               d.nni_uexps.as<int>(), d.tips.as<uint8_t>(), d.P_pad, off);
+                    CHECK_LAUNCH();
+                }
+                const int nj = (int)jobs.size();
+                const int jchunk = std::max(1, (int)std::min<int64_t>(nj, (int64_t)0x7fffffff / std::max(n_sb, 1)));
+                for (int j0 = 0; j0 < nj; j0 += jchunk) {
+                    const int cj = std::min(jchunk, nj - j0);
+                    ScopedTimer tm(ctx, &d, PH_DOWN);
+#define PHB_NNI_EDGE(NC)                                                                                               \
+    PHB_LAUNCH(nni_edge_kernel<NC>, dim3((unsigned)((int64_t)n_sb * cj)), dim3(nni_threads(NC)), d.stream,             \
+               d.nni_jobs.as<NniEdgeJob>() + j0, cj, M, d.Pmat.as<double>(), d.clv.as<double>(), d.nni_upper.as<double>(), \
+               slot_stride, tile_pad, len, d.nni_exps.as<int>(), d.nni_uexps.as<int>(), d.tips.as<uint8_t>(), d.P_pad, off, \
+               d.leaf_ls.as<double>() + off, d.inv_mask.as<uint8_t>() + off, d.mult.as<double>() + off,                \
+               d.nni_partials.as<double>(), n_sb)
+                    switch (M.n_clv) {
+                    case 1: PHB_NNI_EDGE(1); break;
+                    case 2: PHB_NNI_EDGE(2); break;
+                    case 3: PHB_NNI_EDGE(3); break;
+                    default: PHB_NNI_EDGE(4); break;
+                    }
+#undef PHB_NNI_EDGE
+                    CHECK_LAUNCH();
+                    PHB_LAUNCH(nni_reduce_rows_kernel, dim3(2 * cj), dim3(ROOT_THREADS), d.stream, d.nni_rows.as<int32_t>() + 2 * j0,
+                               d.nni_partials.as<double>(), n_sb, d.nni_totals.as<double>());
+                    CHECK_LAUNCH();
+                }
+                continue;
+            }
             const int chunk = std::max(1, (int)std::min<int64_t>(nm, (int64_t)0x7fffffff / std::max(n_sb, 1)));
             for (int m0 = 0; m0 < nm; m0 += chunk) { // (the grid holds n_sb * moves-in-chunk CTAs)
                 const int cm = std::min(chunk, nm - m0);
@@ -1081,6 +1160,14 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
         CU(cudaSetDevice(d.ordinal));
         CU(cudaStreamSynchronize(d.stream));
         for (const NniMove &mv : moves) totals[mv.out] += dev_totals[di][mv.out];
+    }
+    if (use_upper) { // a (v, left_ch) asked for more than once was scored once
+        std::vector<int> first(2 * (size_t)T.n, -1);
+        for (int m : order) {
+            int &f = first[2 * (size_t)node_id[m] + (left_ch[m] ? 1 : 0)];
+            if (f < 0) f = m;
+            else totals[m] = totals[f];
+        }
     }
     S.kernel_launches = ctx->launches;
     return PHB_OK;
@@ -1157,7 +1244,7 @@ void phb_ctx_destroy(phb_ctx *ctx)
                           &d.dkids, &d.leaf_rows, &d.states, &d.posteriors, &d.staging, &d.sim_pre, &d.sim_parent,
                           &d.sim_depth, &d.sim_leafrow, &d.sim_stack, &d.scratch, &d.sw_descs, &d.sw_blocks,
                           &d.sw_stream, &d.sw_gstack, &d.sw_err, &d.sw_ops, &d.uops, &d.ukids, &d.lnP, &d.jbest,
-                          &d.nni_exps, &d.nni_partials, &d.nni_totals, &d.nni_moves, &d.nni_steps};
+                          &d.nni_upper, &d.nni_uexps, &d.nni_jobs, &d.nni_rows, &d.nni_exps, &d.nni_partials, &d.nni_totals, &d.nni_moves, &d.nni_steps};
         for (DevBuf *b : bufs) b->release();
         for (auto &ep : d.ev_pool) {
             cudaEventDestroy(ep.a);

@@ -252,16 +252,18 @@ def test_score_nni(gpu_lib):
     got, st = _cases.check_nni(gpu_lib, case)
     assert st["nni_path_steps"] > 0
     full, _ = _cases.check_nni(gpu_lib, case, flags=capi.FLAG_NNI_FULL, expect_path=False)
+    walk, _ = _cases.check_nni(gpu_lib, case, flags=capi.FLAG_NNI_WALK)
     ok = np.isfinite(got)
-    assert np.array_equal(ok, np.isfinite(full))
+    assert np.array_equal(ok, np.isfinite(full)) and np.array_equal(ok, np.isfinite(walk))
     assert np.max(np.abs(got[ok] - full[ok]) / np.abs(full[ok])) < 1e-12
+    assert np.max(np.abs(got[ok] - walk[ok]) / np.abs(walk[ok])) < 1e-12
 
 
 @pytest.mark.parametrize("model,amb", [("jc69", 0.0), ("gtr_i_g4", 0.1)])
 def test_score_nni_models_tiling(gpu_lib, model, amb):
     case = workloads.make_case(20, 3000, model=model, seed=41, ambiguity=amb)
     n_clv = 1 if model == "jc69" else 4
-    got, st = _cases.check_nni(gpu_lib, case, budget=19 * n_clv * 36 * 1024 + 1)
+    got, st = _cases.check_nni(gpu_lib, case, budget=19 * n_clv * 72 * 1024 + 1)
     assert st["nni_tiles"] == 3
     one, _ = _cases.check_nni(gpu_lib, case)
     ok = np.isfinite(got)
@@ -276,6 +278,7 @@ def test_score_nni_deep_tree(gpu_lib):
     internal = [v for v in range(ft["n_nodes"]) if ft["child_off"][v + 1] > ft["child_off"][v]]
     moves = [(int(v), int(lc)) for v in rng.choice(internal, 48, replace=False) for lc in (0, 1)]
     _cases.check_nni(gpu_lib, case, moves=moves)
+    _cases.check_nni(gpu_lib, case, moves=moves, flags=capi.FLAG_NNI_WALK)
 
 
 def test_score_nni_full_size_config5_properties(gpu_lib):

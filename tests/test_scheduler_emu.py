@@ -190,9 +190,15 @@ def test_score_nni_matches_rebuilt_trees(emu_lib):
     got, st = _cases.check_nni(emu_lib, case)
     assert st["nni_tiles"] == 1 and st["nni_path_steps"] > 0
     full, st_full = _cases.check_nni(emu_lib, case, flags=capi.FLAG_NNI_FULL, expect_path=False)
+    walk, _ = _cases.check_nni(emu_lib, case, flags=capi.FLAG_NNI_WALK)  # v -> root walks instead of upper partials
     ok = np.isfinite(got)
-    assert np.array_equal(ok, np.isfinite(full))
+    assert np.array_equal(ok, np.isfinite(full)) and np.array_equal(ok, np.isfinite(walk))
     assert np.max(np.abs(got[ok] - full[ok]) / np.abs(full[ok])) < 1e-12
+    assert np.max(np.abs(got[ok] - walk[ok]) / np.abs(walk[ok])) < 1e-12
+    # repeated and half-asked edges: every request gets its own answer
+    internal = [v for v in range(case.ft["n_nodes"]) if case.ft["child_off"][v + 1] > case.ft["child_off"][v] and v != case.ft["root"]]
+    a, b = internal[0], internal[-1]
+    _cases.check_nni(emu_lib, case, moves=[(a, 1), (a, 1), (b, 0), (a, 0), (a, 1)])
 
 
 @pytest.mark.parametrize("model,amb", [("jc69", 0.0), ("gtr_i_g4", 0.1)])
@@ -200,7 +206,7 @@ def test_score_nni_models_ambiguity_tiling(emu_lib, model, amb):
     case = workloads.make_case(14, 1300, model=model, seed=31, ambiguity=amb, compress=(amb == 0.0))
     n_int = 13
     n_clv = 1 if model == "jc69" else 4
-    budget = n_int * n_clv * 36 * 512 + 1  # one 512-pattern tile of cached CLVs + exponents
+    budget = n_int * n_clv * 72 * 512 + 1  # one 512-pattern tile of cached CLVs + upper partials + exponents
     got, st = _cases.check_nni(emu_lib, case, budget=budget)
     assert st["nni_tiles"] == (len(case.patterns) + 511) // 512
     one, _ = _cases.check_nni(emu_lib, case)
@@ -217,6 +223,7 @@ def test_score_nni_deep_tree_rescaling(emu_lib):
     internal = [v for v in range(ft["n_nodes"]) if ft["child_off"][v + 1] > ft["child_off"][v]]
     moves = [(int(v), int(lc)) for v in rng.choice(internal, 40, replace=False) for lc in (0, 1)]
     _cases.check_nni(emu_lib, case, moves=moves)
+    _cases.check_nni(emu_lib, case, moves=moves[:20], flags=capi.FLAG_NNI_WALK)
 
 
 def test_score_nni_polytomy_falls_back(emu_lib):

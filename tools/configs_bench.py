@@ -169,7 +169,7 @@ def run_nni(tag, n_taxa, n_sites, model, seed, n_moves, reps, flags=0):
         ctx.simulate_alignment(n_sites, seed=seed ^ 0xA11C)
         base = ctx.log_likelihood()
         ids, left = [m[0] for m in moves], [m[1] for m in moves]
-        out, dev_ms, wall_ms = timed(ctx, lambda: ctx.score_nni(ids, left), reps if not flags else 1)
+        out, dev_ms, wall_ms = timed(ctx, lambda: ctx.score_nni(ids, left), 1 if flags & capi.FLAG_NNI_FULL else reps)
         st = ctx.stats()
         t0 = time.perf_counter()
         ctx.log_likelihood()
@@ -178,7 +178,8 @@ def run_nni(tag, n_taxa, n_sites, model, seed, n_moves, reps, flags=0):
                 best_delta=float(np.nanmax(out) - base), wall_ms=wall_ms, device_ms=dev_ms, ms_per_neighbour=wall_ms / len(moves),
                 full_evaluation_ms=full_ms, trees_per_s=len(moves) / (wall_ms * 1e-3),
                 equivalent_updates_per_s=len(moves) * (n_taxa - 1) * n_sites / (wall_ms * 1e-3),
-                path="full rescoring" if flags else "path-only walks over cached CLVs",
+                path=("full rescoring" if flags & capi.FLAG_NNI_FULL else "walks v->root over cached CLVs" if flags & capi.FLAG_NNI_WALK
+                      else "edge-local scoring with upper partials"),
                 nni_path_moves=st["nni_path_moves"], nni_path_steps=st["nni_path_steps"], nni_tiles=st["nni_tiles"],
                 nni_cache_GB=st["nni_cache_bytes"] / 1e9, nni_read_GB=st["nni_read_bytes"] / 1e9,
                 walk_read_GBps=st["nni_read_bytes"] / (dev_ms * 1e-3) / 1e9)
@@ -200,6 +201,9 @@ CASES = {
     "compress_cfg2": lambda r: run_compress("compress cfg2 1000 rows x 100k sites (all distinct)", 1000, 100_000, 0, 0x5EED0002, r),
     "compress_cfg3": lambda r: run_compress("compress cfg3 10000 rows x 1M sites (all distinct)", 10_000, 1_000_000, 0, 0x5EED0003, r),
     "cfg5": lambda r: run_nni("cfg5 1024 NNI neighbours 2000 x 200k", 2000, 200_000, "gtr_g4", 0x5EED0005, 1024, r),
+    "cfg5_walk": lambda r: run_nni("cfg5 1024 NNI neighbours 2000 x 200k (walk kernel)", 2000, 200_000, "gtr_g4", 0x5EED0005, 1024, r,
+                                   capi.FLAG_NNI_WALK),
+    "cfg5_all": lambda r: run_nni("cfg5+ all 3,996 NNI neighbours 2000 x 200k", 2000, 200_000, "gtr_g4", 0x5EED0005, 4000, r),
     "cfg5_full_128": lambda r: run_nni("cfg5/8 128 NNI neighbours 2000 x 200k, full rescoring", 2000, 200_000, "gtr_g4",
                                        0x5EED0005, 128, r, capi.FLAG_NNI_FULL),
     "cfg5_small": lambda r: run_nni("cfg5/8 128 NNI neighbours 2000 x 200k", 2000, 200_000, "gtr_g4", 0x5EED0005, 128, r),
