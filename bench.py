@@ -76,15 +76,22 @@ class ClockSampler:
 
     def _pump(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append([time.perf_counter()] + [x.strip() for x in line.split(",")])
 
-    def stop(self):
+    def stop(self, t_begin=None, t_end=None):
+        """Summary over the samples that arrived inside [t_begin, t_end] (the timed region); when the region is
+        shorter than the sampling period, over the samples since the sampler started (warm-up steps run the same
+        kernels) — `window` says which."""
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
         self.t.join(timeout=2)
         sm, mx, reasons = [], [], set()
-        for r in self.rows:
+        rows = [r[1:] for r in self.rows if t_begin is None or t_begin <= r[0] <= t_end + 0.15]
+        window = "timed region"
+        if not rows:
+            rows, window = [r[1:] for r in self.rows], "warm-up + timed region (timed region shorter than one sample)"
+        for r in rows:
             try:
                 sm.append(float(r[1]))
                 mx.append(float(r[2]))
@@ -94,7 +101,7 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "window": window}
 
 
 def shard(P, world, rank):
@@ -181,7 +188,11 @@ def run_gpu(args, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep stdout to the one JSON line (NCCL prints its version there)
+        # NCCL prints its version banner on fd 1 at communicator creation: point fd 1 at stderr for the run
+        # and keep the real stdout for the one JSON line
+        sys.stdout.flush()
+        _real_stdout = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():
@@ -208,11 +219,14 @@ def run_gpu(args, rank, world, local_rank):
             return float(red.item())
         return v
 
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    t_w = time.perf_counter()
     for _ in range(max(args.warmup, 3)):
         lnl = step()
-    sampler = ClockSampler(local_rank)
+    while time.perf_counter() - t_w < 0.6 and not sampler.rows:  # let nvidia-smi deliver its first sample under load
+        ctx.log_likelihood()  # local evaluation only: ranks may run different numbers of these
     barrier()
-    sampler.start()
     launches0 = ctx.stats()["kernel_launches"]
     ctx.timer_start()
     t0 = time.perf_counter()
@@ -221,7 +235,7 @@ def run_gpu(args, rank, world, local_rank):
     dev_ms = ctx.timer_stop()
     barrier()
     wall_ms = (time.perf_counter() - t0) * 1e3
-    clocks = sampler.stop()
+    clocks = sampler.stop(t0, t0 + wall_ms * 1e-3)
     st = ctx.stats()
     launches = st["kernel_launches"] - launches0
     # ---- end to end from host buffers ------------------------------------------------------------
@@ -316,7 +330,7 @@ def run_gpu(args, rank, world, local_rank):
                 "sample": f"oracle reference-faithful mode, first {sample} patterns of the same workload, {dt:.1f} s, 1 thread "
                           "(the reference's rayon feature does not reach this path)",
                 "cpu_opt": {"value": ov, "unit": UNIT, "cores": cores, "sample": f"oracle cpu_opt mode, {sample * 64} patterns, {odt:.1f} s"}}
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), flush=True, file=_real_stdout if world > 1 else sys.stdout)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
