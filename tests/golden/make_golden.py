@@ -100,8 +100,23 @@ def make_cases():
         srt = np.sort(post, axis=2)
         min_gap = float((srt[..., 3] - srt[..., 2]).min())
         seqs = {str(int(ft["ids"][k])): bytes(b"ACGT"[s] for s in states[k][s2p]).decode() for k in range(ft["n_nodes"])}
+        # joint (Viterbi) ASR, compute_joint_asr likelihood.rs:421-560
+        jtot, jper, jstates = oracle.joint_asr_flat(ft, case.model, pats, mult)
+        jseqs = {str(int(ft["ids"][k])): bytes(b"ACGT"[s] for s in jstates[k][s2p]).decode() for k in range(ft["n_nodes"])}
+        # NNI neighbours (caller loop clone + NNI::nni tree.rs:1213-1242 + log_likelihood), arena ids of the parsed tree
+        nni = []
+        for nid in tree2.get_node_ids():
+            for lc in (False, True):
+                t = tree2.clone()
+                if t.nni(int(nid), lc):
+                    continue
+                val, _ = oracle.log_likelihood_flat(oracle.flatten(t, lo), case.model, pats, mult, mode=0)
+                nni.append([int(nid), int(lc), float(val)])
         out.append(dict(name=name, model=model, newick=newick, fasta=fasta, log_likelihood=float(tot),
-                        per_site=[float(x) for x in per[s2p]], asr_sequences=seqs, asr_min_top2_gap=min_gap))
+                        per_site=[float(x) for x in per[s2p]], asr_sequences=seqs, asr_min_top2_gap=min_gap,
+                        joint_log_likelihood=float(jtot), joint_sequences=jseqs, nni_scores=nni,
+                        n_patterns=int(len(pats)), site_to_pattern=[int(x) for x in s2p],
+                        multiplicity=[int(x) for x in mult]))
     return out
 
 

@@ -66,6 +66,12 @@ def test_oracle_reproduces_cases():
         r = oracle.marginal_asr(tree, m, aln)
         for nid, s in c["asr_sequences"].items():
             assert oracle.sequence_string(r["sequences"][int(nid)]) == s
+        j = oracle.joint_asr(tree, m, aln)
+        assert j["log_likelihood"] == pytest.approx(c["joint_log_likelihood"], rel=1e-13)
+        for nid, s in c["joint_sequences"].items():
+            assert oracle.sequence_string(j["sequences"][int(nid)]) == s
+        pats, s2p, mult, _lo = aln.compress_columns()
+        assert len(pats) == c["n_patterns"] and list(s2p) == c["site_to_pattern"] and list(mult) == c["multiplicity"]
 
 
 # ---- product path against the fixtures ----------------------------------------------------------------------
@@ -102,6 +108,15 @@ def _product_vs_golden():
         assert c["asr_min_top2_gap"] > 1e-6
         for nid, s in c["asr_sequences"].items():
             assert rec.sequence_string(int(nid)) == s, (c["name"], nid)
+        # joint ASR and the NNI neighbourhood through the reference-shaped interface
+        jr = tree.joint_asr(model, aln)
+        assert abs(jr.log_likelihood - c["joint_log_likelihood"]) <= 1e-9 * abs(c["joint_log_likelihood"])
+        for nid, s in c["joint_sequences"].items():
+            assert jr.sequence_string(int(nid)) == s, (c["name"], "joint", nid)
+        moves = [(int(v), bool(lc)) for v, lc, _ in c["nni_scores"]]
+        got_nni = tree.score_nni_neighbours(model, aln, moves)
+        want_nni = np.asarray([x[2] for x in c["nni_scores"]])
+        assert np.max(np.abs(got_nni - want_nni) / np.abs(want_nni)) <= 1e-9, c["name"]
         # per-site values through the raw C ABI (the reference API does not expose them)
         from phylo_rs_b200 import capi
 
@@ -112,6 +127,12 @@ def _product_vs_golden():
             tot, per = ctx.log_likelihood(per_pattern=True)
         assert math.isclose(tot, c["log_likelihood"], rel_tol=1e-9)
         assert np.max(np.abs(per[comp.site_to_pattern] - np.asarray(c["per_site"]))) <= 1e-8
+        # device-side compress_columns against the fixture (bit-exact)
+        fa = dict(zip(c["fasta"].split()[0::2], c["fasta"].split()[1::2]))
+        rows = [fa[">" + nm].encode() for nm in comp.leaf_order]
+        with capi.Context(library=lib) as ctx:
+            n, s2p, mult = ctx.compress_rows(rows)
+        assert n == c["n_patterns"] and list(s2p) == c["site_to_pattern"] and list(mult) == c["multiplicity"]
 
 
 _LIB_PATH = [None]
