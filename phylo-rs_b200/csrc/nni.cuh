@@ -356,7 +356,8 @@ nni_reduce_kernel(const NniMove *__restrict__ moves, const double *__restrict__ 
 // Pre-order pass, one launch per depth.  One block = (parent, category, 512 patterns); a thread = a
 // pattern pair; both children of the (binary) parent are served from one read of the parent's upper.
 // upper / uexps are indexed by CLV slot like clv / exps.  DownOp::pad = the parent's dense node id.
-__global__ void __launch_bounds__(CLV_THREADS)
+template <int MINB>
+__global__ void __launch_bounds__(CLV_THREADS, MINB)
 upper_level_kernel(const DownOp *__restrict__ ops, int n_ops, const DownChild *__restrict__ kids, int root_node, ModelDev M,
                    const double *__restrict__ Pmat, const double *__restrict__ clv, double *__restrict__ upper,
                    size_t slot_stride, size_t tile_pad, int tile_len, int blocks_per_row, const int *__restrict__ exps,

@@ -1007,6 +1007,7 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
     S.nni_cache_bytes = 0;
     if (moves.empty() || ctx->n_patterns == 0) return PHB_OK;
     const int nm = (int)moves.size();
+    static const int upper_minb = [] { const char *e = getenv("PHB_UPPER_MINB"); return e ? atoi(e) : 3; }();
     static const bool nni_minb3 = [] { const char *e = getenv("PHB_NNI_MINB"); return e && atoi(e) == 3; }();
     std::vector<std::vector<double>> dev_totals(ctx->devs.size());
     for (size_t di = 0; di < ctx->devs.size(); ++di) {
@@ -1092,10 +1093,15 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
                     const int nb = T.dlevel_off[dl + 1] - T.dlevel_off[dl];
                     if (nb <= 0) continue;
                     ScopedTimer tm(ctx, &d, PH_CLV);
-                    PHB_LAUNCH(upper_level_kernel, dim3((unsigned)((int64_t)nb * M.n_clv * bpr)), dim3(CLV_THREADS), d.stream,
-                               d.dops.as<DownOp>() + T.dlevel_off[dl], nb, d.dkids.as<DownChild>(), T.root, M, d.Pmat.as<double>(),
-                               d.clv.as<double>(), d.nni_upper.as<double>(), slot_stride, tile_pad, len, bpr, d.nni_exps.as<int>(),
-                               d.nni_uexps.as<int>(), d.tips.as<uint8_t>(), d.P_pad, off);
+#define PHB_UPPER_LAUNCH(MINB)                                                                                         \
+    PHB_LAUNCH(upper_level_kernel<MINB>, dim3((unsigned)((int64_t)nb * M.n_clv * bpr)), dim3(CLV_THREADS), d.stream,   \
+               d.dops.as<DownOp>() + T.dlevel_off[dl], nb, d.dkids.as<DownChild>(), T.root, M, d.Pmat.as<double>(),    \
+               d.clv.as<double>(), d.nni_upper.as<double>(), slot_stride, tile_pad, len, bpr, d.nni_exps.as<int>(),    \
+               d.nni_uexps.as<int>(), d.tips.as<uint8_t>(), d.P_pad, off)
+                    if (upper_minb == 2) PHB_UPPER_LAUNCH(2);
+                    else if (upper_minb == 4) PHB_UPPER_LAUNCH(4);
+                    else PHB_UPPER_LAUNCH(3);
+#undef PHB_UPPER_LAUNCH
                     CHECK_LAUNCH();
                 }
                 const int nj = (int)jobs.size();
