@@ -619,7 +619,7 @@ int ensure_sweep(phb_ctx *ctx, const ModelDev &M)
             cudaStreamSynchronize(d.stream);
             d.sweep_uploaded = false;
         }
-        S.build(T.n, T.root, T.child_off, T.children, T.leaf_row, M.n_clv);
+        S.build(T.n, T.root, T.child_off, T.children, T.leaf_row, M.n_clv, T.slot);
         size_t smem_max = ctx->devs[0].smem_optin;
         for (Device &d : ctx->devs) smem_max = std::min(smem_max, d.smem_optin);
         if (!ctx->sweep_geom.plan(S, smem_max, shard_P, std::max(ctx->devs[0].sm_count, 1)))
@@ -656,8 +656,10 @@ int launch_sweep_transition(phb_ctx *ctx, Device &d, const ModelDev &M)
 
 // One persistent sweep launch over patterns [p0, p0 + np) of the device's shard with geometry G; the per-block
 // partial sums land at partials[part_off ...].  p0 must be a multiple of 16 (TMA source alignment).
+// clv_out != null selects the storing variant (marginal-ASR up pass): CLVs of the launch's patterns go to
+// clv_out[slot][cat][state][site - p0] with row stride tile_pad, per-category log-likelihoods to cat_ll_out.
 int launch_sweep_range(phb_ctx *ctx, Device &d, const ModelDev &M, const SweepGeom &G, int64_t p0, int64_t np,
-                       size_t part_off)
+                       size_t part_off, double *clv_out = nullptr, double *cat_ll_out = nullptr, size_t tile_pad = 0)
 {
     const SweepSched &S = ctx->sweep;
     const int sites_per_block = 4 * G.Q;
@@ -688,15 +690,21 @@ int launch_sweep_range(phb_ctx *ctx, Device &d, const ModelDev &M, const SweepGe
     sp.per_pattern = d.per_pattern.as<double>() + p0;
     sp.partials = d.partials.as<double>() + part_off;
     sp.error_flag = d.sw_err.as<unsigned int>();
+    sp.clv_out = clv_out;
+    sp.cat_ll_out = cat_ll_out;
+    sp.tile_pad = tile_pad;
+    sp.slot_stride = (size_t)M.n_clv * 4 * tile_pad;
     ScopedTimer tm(ctx, &d, PH_CLV);
 #ifndef PHB_HOST_EMU
     static bool attr_set[64] = {false};
     if (!attr_set[d.ordinal & 63]) {
-        CU(cudaFuncSetAttribute(sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)d.smem_optin));
+        CU(cudaFuncSetAttribute(sweep_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)d.smem_optin));
+        CU(cudaFuncSetAttribute(sweep_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)d.smem_optin));
         attr_set[d.ordinal & 63] = true;
     }
 #endif
-    PHB_LAUNCH_SMEM(sweep_kernel, dim3(grid), dim3(G.threads), G.smem_bytes, d.stream, sp, M);
+    if (clv_out) PHB_LAUNCH_SMEM(sweep_kernel<true>, dim3(grid), dim3(G.threads), G.smem_bytes, d.stream, sp, M);
+    else PHB_LAUNCH_SMEM(sweep_kernel<false>, dim3(grid), dim3(G.threads), G.smem_bytes, d.stream, sp, M);
     CHECK_LAUNCH();
     if (&d == &ctx->devs[0]) ctx->stats.clv_launches++;
     return PHB_OK;
@@ -746,7 +754,10 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
     const ModelDev &M = asr ? ctx->model_lit : ctx->model;
     const bool use_sweep = !asr && !(ctx->flags & PHB_FLAG_LEVEL_KERNELS) && T.n_internal > 0 && M.n_clv > 0 &&
                            M.n_cat <= 4 * M.n_clv;
-    if (use_sweep) {
+    // marginal ASR: the up pass is the storing sweep (each CLV written once, never read back by the up pass)
+    const bool asr_sweep = asr && !joint && !(ctx->flags & PHB_FLAG_LEVEL_KERNELS) && T.n_internal > 0 && M.n_clv > 0 &&
+                           M.n_clv <= SW_MAX_CONSUMERS / 8;
+    if (use_sweep || asr_sweep) {
         rc = ensure_sweep(ctx, M);
         if (rc) return rc;
     }
@@ -802,10 +813,24 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
             continue;
         }
         size_t part_off = 0;
+        SweepGeom tile_geom;
+        if (asr_sweep) { // geometry for one tile's worth of patterns; partial sums are per sweep block
+            size_t smem_max = d.smem_optin;
+            if (!tile_geom.plan(ctx->sweep, smem_max, std::min<int64_t>(d.tile_pad, d.P), std::max(d.sm_count, 1)))
+                return ctx->fail(PHB_ERR_INVALID_MODEL_PARAMETER, "sweep: %d CLV categories do not fit one CTA", M.n_clv);
+            const int64_t bs = 4 * tile_geom.Q;
+            CU(d.partials.ensure(sizeof(double) * (size_t)(d.n_tiles * ((d.tile_pad + bs - 1) / bs + 1))));
+            rc = launch_sweep_transition(ctx, d, M);
+            if (rc) return rc;
+        }
         for (int t = 0; t < d.n_tiles; ++t) {
             int64_t off = (int64_t)t * d.tile_pad;
             int len = (int)std::min<int64_t>(d.tile_pad, d.P - off);
-            rc = joint ? run_tile_joint(ctx, d, M, off, len, part_off) : run_tile_up(ctx, d, M, off, len, part_off, asr);
+            if (asr_sweep) {
+                rc = launch_sweep_range(ctx, d, M, tile_geom, off, len, part_off, d.clv.as<double>(), d.cat_ll.as<double>(),
+                                        (size_t)d.tile_pad);
+            } else
+                rc = joint ? run_tile_joint(ctx, d, M, off, len, part_off) : run_tile_up(ctx, d, M, off, len, part_off, asr);
             if (rc) return rc;
             if (asr) {
                 rc = joint ? PHB_OK : run_tile_down(ctx, d, M, off, len, want_post);
@@ -824,7 +849,8 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
                                              d.copy_stream));
                 }
             }
-            part_off += (size_t)((len + ROOT_THREADS - 1) / ROOT_THREADS);
+            if (asr_sweep) part_off += (size_t)((len + 4 * tile_geom.Q - 1) / (4 * tile_geom.Q));
+            else part_off += (size_t)((len + ROOT_THREADS - 1) / ROOT_THREADS);
         }
         {
             ScopedTimer tm(ctx, &d, PH_ROOT);
@@ -857,12 +883,12 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
     S.kernel_launches = ctx->launches;
     S.clv_updates = (int64_t)T.n_internal * ctx->n_patterns;
     S.algorithmic_bytes = (32.0 * M.n_clv * T.sum_one_plus_i + T.sum_t) * (double)ctx->n_patterns;
-    S.sweep_ops = use_sweep ? ctx->sweep.n_ops : 0;
-    S.sweep_stack_levels = use_sweep ? ctx->sweep.n_levels : 0;
-    S.sweep_smem_levels = use_sweep ? ctx->sweep_geom.smem_levels : 0;
-    S.sweep_stages = use_sweep ? ctx->sweep_geom.n_stages : 0;
-    S.sweep_block_sites = use_sweep ? 4 * ctx->sweep_geom.Q : 0;
-    S.sweep_stream_bytes = use_sweep ? (int64_t)ctx->sweep.stream_bytes : 0;
+    S.sweep_ops = (use_sweep || asr_sweep) ? ctx->sweep.n_ops : 0;
+    S.sweep_stack_levels = (use_sweep || asr_sweep) ? ctx->sweep.n_levels : 0;
+    S.sweep_smem_levels = (use_sweep || asr_sweep) ? ctx->sweep_geom.smem_levels : 0;
+    S.sweep_stages = (use_sweep || asr_sweep) ? ctx->sweep_geom.n_stages : 0;
+    S.sweep_block_sites = (use_sweep || asr_sweep) ? 4 * ctx->sweep_geom.Q : 0;
+    S.sweep_stream_bytes = (use_sweep || asr_sweep) ? (int64_t)ctx->sweep.stream_bytes : 0;
     if (timing) {
         S.ms_transition = S.ms_clv = S.ms_root = S.ms_down = 0;
         for (auto &pr : d0.ev_log) {

@@ -47,8 +47,9 @@ constexpr int SW_BAR_BYTES = 512; // mbarrier area at the start of dynamic share
 // Per-op header, one table for the whole tree in global memory (identical for every site block, so the
 // consumers prefetch it two ops ahead into registers: nothing on the op's critical path waits for it).
 //   w0 = kind | flags << 8 | level << 16      w1 = szA | szB << 16   (per-category bytes of operand A / B)
+//   w2 = CLV slot of the node this op completes (valid with SW_FLAG_RESCALE; used by the storing variant)
 struct SweepOp {
-    uint32_t w0, w1;
+    uint32_t w0, w1, w2, w3;
 };
 // Producer-side descriptor (global memory): where the record is and which tip rows it needs.
 struct SweepDesc {
@@ -203,6 +204,12 @@ struct SweepParams {
     double *per_pattern;
     double *partials; // [n_blocks]
     unsigned int *error_flag;
+    // storing variant (marginal-ASR up pass): every completed node's CLV goes to clv_out[slot][cat][state][site]
+    // (site relative to the first pattern of this launch), the per-category log-likelihoods to cat_ll_out[cat][site]
+    double *clv_out;
+    double *cat_ll_out;
+    size_t slot_stride; // n_clv * 4 * tile_pad
+    size_t tile_pad;
 };
 
 __device__ __forceinline__ void sw_matvec(const double (&p)[16], const double (&x)[4], double (&y)[4])
@@ -246,6 +253,11 @@ __device__ __forceinline__ void sw_rescale(double (&v)[4], int &sc)
 
 // The fused sweep.  grid = min(n_blocks, #SMs) persistent CTAs; block = n_consumers (padded to a warp
 // multiple) + 32 producer threads; dynamic shared memory = barriers + ring + stack.
+// STORE = true is the up pass of compute_marginal_asr (src/tree/likelihood.rs:286-298): the same sweep, but
+// every completed node's CLV is also written to HBM ONCE (the level kernels write it and read it back), at
+// whatever power-of-two scale it has in registers — the pre-order pass normalises per node and category
+// (:330-342), so only the per-category totals, which the root stage writes to cat_ll_out, carry exponents.
+template <bool STORE>
 __global__ void __launch_bounds__(SW_MAX_CONSUMERS + 32, 1)
 sweep_kernel(SweepParams p, ModelDev M)
 {
@@ -313,7 +325,7 @@ sweep_kernel(SweepParams p, ModelDev M)
     int s = 0;
     uint32_t parity = 0;
     const unsigned char *st = ring;
-    const uint2 *const optab = reinterpret_cast<const uint2 *>(p.ops);
+    const uint4 *const optab = reinterpret_cast<const uint4 *>(p.ops);
     for (int64_t b = blockIdx.x; b < p.n_blocks; b += gridDim.x) {
         double v[SW_R][4]; // running result
         double u[SW_R][4]; // second accumulator: a chain-shaped pending sibling is evaluated here (SW_FLAG_U)
@@ -325,9 +337,9 @@ sweep_kernel(SweepParams p, ModelDev M)
             for (int i = 0; i < 4; ++i) v[r][i] = u[r][i] = 1.0;
         }
         // op headers run two ops ahead of the arithmetic (same table for every block)
-        uint2 hq0 = __ldg(optab), hq1 = __ldg(optab + (n_ops > 1 ? 1 : 0));
+        uint4 hq0 = __ldg(optab), hq1 = __ldg(optab + (n_ops > 1 ? 1 : 0));
         for (int k = 0; k < n_ops; ++k) {
-            const uint2 h = hq0;
+            const uint4 h = hq0;
             hq0 = hq1;
             hq1 = __ldg(optab + (k + 2 < n_ops ? k + 2 : n_ops - 1));
             const int kind = h.x & 0xff, flags = (h.x >> 8) & 0xff, level = (int)(h.x >> 16);
@@ -470,6 +482,26 @@ sweep_kernel(SweepParams p, ModelDev M)
             if (flags & SW_FLAG_RESCALE) {
                 if (flags & SW_FLAG_U) guard(u);
                 else guard(v);
+                if (STORE && active) {
+                    const int64_t rel = b * sites_per_block + 4 * q; // first of this thread's 4 patterns, launch-relative
+                    double *dst = p.clv_out + (size_t)h.z * p.slot_stride + (size_t)cc * 4 * p.tile_pad + (size_t)rel;
+                    const bool use_u = flags & SW_FLAG_U;
+                    if (rel + 3 < p.P) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            double2 *d2 = reinterpret_cast<double2 *>(dst + (size_t)i * p.tile_pad);
+                            d2[0] = use_u ? make_double2(u[0][i], u[1][i]) : make_double2(v[0][i], v[1][i]);
+                            d2[1] = use_u ? make_double2(u[2][i], u[3][i]) : make_double2(v[2][i], v[3][i]);
+                        }
+                    } else {
+#pragma unroll
+                        for (int r = 0; r < SW_R; ++r)
+                            if (rel + r < p.P) {
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) dst[(size_t)i * p.tile_pad + r] = use_u ? u[r][i] : v[r][i];
+                            }
+                    }
+                }
             }
             __syncwarp();
             if (lane == 0) sw_mbar_arrive(&empty[s]);
@@ -500,6 +532,7 @@ sweep_kernel(SweepParams p, ModelDev M)
                     ll = M.ln_weights[cat] + log(mass) + (p.leaf_ls[site] - (double)sc[r] * LN2);
                 }
                 xch[(size_t)cat * sites_per_block + 4 * q + r] = ll;
+                if (STORE && site < p.P) p.cat_ll_out[(size_t)cat * p.tile_pad + (size_t)site] = ll;
             }
             if (cc == 0 && M.n_clv < M.n_cat) { // rate-0 (+I) categories in closed form from the tip masks
                 for (int c = 0; c < M.n_cat; ++c) {
@@ -516,6 +549,7 @@ sweep_kernel(SweepParams p, ModelDev M)
                             ll = M.ln_weights[c] + log(mass) + p.leaf_ls[site];
                         }
                         xch[(size_t)c * sites_per_block + 4 * q + r] = ll;
+                        if (STORE && site < p.P) p.cat_ll_out[(size_t)c * p.tile_pad + (size_t)site] = ll;
                     }
                 }
             }

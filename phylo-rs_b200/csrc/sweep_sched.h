@@ -33,8 +33,9 @@ struct SweepSched {
     int n_push = 0, n_reg_sibling = 0;  // pending siblings parked in the stack / kept in the second accumulator
 
     // child_off/children: CSR child lists; leaf_row: alignment row per leaf; root must be internal.
+    // slot: CLV slot per node (-1 for leaves), recorded in the header of the op that completes the node.
     void build(int n, int root, const std::vector<int> &child_off, const std::vector<int> &children,
-               const std::vector<int> &leaf_row, int n_clv_)
+               const std::vector<int> &leaf_row, int n_clv_, const std::vector<int> &slot = std::vector<int>())
     {
         valid = false;
         n_clv = n_clv_;
@@ -81,7 +82,7 @@ struct SweepSched {
         }
 
         struct Hdr { int kind, flags, level, szA, szB; };
-        struct Rec { Hdr h; int edgeA, edgeB, rowA, rowB; bool tabA, tabB; };
+        struct Rec { Hdr h; int edgeA, edgeB, rowA, rowB; bool tabA, tabB; int node; };
         std::vector<Rec> recs;
         int pending_push = -1;
         bool u_mode = false;
@@ -161,6 +162,7 @@ struct SweepSched {
                 for (int tnode : tv) emit(SW_MULTIP, 0, tnode, true, -1, false);
             }
             recs.back().h.flags |= SW_FLAG_RESCALE;
+            recs.back().node = v;
             st.pop_back();
         }
         // dense renumbering of the stack levels actually used (the register accumulator usually frees level 0)
@@ -201,6 +203,9 @@ struct SweepSched {
             const Hdr &h = recs[k].h;
             ops[k].w0 = (uint32_t)h.kind | ((uint32_t)h.flags << 8) | ((uint32_t)h.level << 16);
             ops[k].w1 = (uint32_t)h.szA | ((uint32_t)h.szB << 16);
+            const int nd = (h.flags & SW_FLAG_RESCALE) ? recs[k].node : -1;
+            ops[k].w2 = (nd >= 0 && (size_t)nd < slot.size() && slot[nd] >= 0) ? (uint32_t)slot[nd] : 0u;
+            ops[k].w3 = 0;
         }
         valid = true;
     }

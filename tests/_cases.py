@@ -23,8 +23,8 @@ def run_lnl(lib, case, flags=0, devices=None, budget=None):
     return tot, per, st
 
 
-def run_asr(lib, case, want_post=False, devices=None, budget=None):
-    with capi.Context(devices=devices, library=lib) as ctx:
+def run_asr(lib, case, want_post=False, devices=None, budget=None, flags=0):
+    with capi.Context(devices=devices, flags=flags, library=lib) as ctx:
         if budget:
             ctx.set_clv_budget(budget)
         workloads.load_into(ctx, case)

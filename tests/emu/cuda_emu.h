@@ -31,6 +31,7 @@ struct dim3 {
 struct alignas(16) double2 { double x, y; };
 struct uchar2 { unsigned char x, y; };
 struct alignas(16) int4 { int x, y, z, w; };
+struct alignas(16) uint4 { unsigned int x, y, z, w; };
 struct alignas(8) int2 { int x, y; };
 struct uchar4 { unsigned char x, y, z, w; };
 struct uint2 { unsigned int x, y; };

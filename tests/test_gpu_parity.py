@@ -119,6 +119,16 @@ def test_asr_500_taxa_sample(gpu_lib):
     assert _cases.check_asr(gpu_lib, case) == 0
 
 
+def test_asr_up_pass_sweep_equals_level_kernels(gpu_lib):
+    case = workloads.make_case(60, 5000, model="gtr_i_g4", seed=37, ambiguity=0.05)
+    a = _cases.run_asr(gpu_lib, case, want_post=True)
+    b = _cases.run_asr(gpu_lib, case, want_post=True, flags=capi.FLAG_LEVEL_KERNELS)
+    assert np.array_equal(a[2], b[2]) and np.max(np.abs(a[3] - b[3])) < 1e-12 and abs(a[0] - b[0]) < 1e-9 * abs(b[0])
+    assert _cases.check_asr(gpu_lib, case, want_post=True, flags=capi.FLAG_LEVEL_KERNELS) == 0
+    deep = workloads.make_case(1500, 700, model="gtr_g4", seed=38)
+    assert _cases.check_asr(gpu_lib, deep) == 0
+
+
 def test_asr_tiled(gpu_lib):
     case = workloads.make_case(30, 6000, model="gtr_g4", seed=27)
     assert _cases.check_asr(gpu_lib, case, budget=29 * 4 * 4 * 8 * 1024) == 0

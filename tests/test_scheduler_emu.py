@@ -297,6 +297,23 @@ def test_compress_then_score_equals_host_compression(emu_lib):
         assert states.shape == (case.ft["n_nodes"], n)
 
 
+def test_asr_up_pass_sweep_equals_level_kernels(emu_lib):
+    """The marginal-ASR up pass runs as the storing sweep by default; PHB_FLAG_LEVEL_KERNELS selects the level
+    kernels.  Same states, same posteriors (to round-off), both against the oracle."""
+    case = workloads.make_case(13, 700, model="gtr_i_g4", seed=17, ambiguity=0.1)
+    assert _cases.check_asr(emu_lib, case, want_post=True) == 0
+    assert _cases.check_asr(emu_lib, case, want_post=True, flags=capi.FLAG_LEVEL_KERNELS) == 0
+    a = _cases.run_asr(emu_lib, case, want_post=True)
+    b = _cases.run_asr(emu_lib, case, want_post=True, flags=capi.FLAG_LEVEL_KERNELS)
+    assert np.array_equal(a[2], b[2]) and np.max(np.abs(a[3] - b[3])) < 1e-12 and abs(a[0] - b[0]) < 1e-9 * abs(b[0])
+    with capi.Context(library=emu_lib) as ctx:
+        workloads.load_into(ctx, case)
+        ctx.marginal_asr()
+        assert ctx.stats()["sweep_ops"] > 0
+    deep = workloads.make_case(500, 40, model="gtr_g4", seed=18)  # exponents: stored CLVs are rescaled mid-tree
+    assert _cases.check_asr(emu_lib, deep) == 0
+
+
 def test_simulated_alignment_roundtrip(emu_lib):
     case = workloads.make_case(7, 10, model="gtr_g4", seed=13)
     with capi.Context(library=emu_lib) as ctx:
