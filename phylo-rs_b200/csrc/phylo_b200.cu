@@ -408,7 +408,7 @@ int check_leaves(phb_ctx *ctx)
 }
 
 // Plans the site tiling of one device and (re)allocates the per-evaluation buffers.
-int plan_device(phb_ctx *ctx, Device &d, const ModelDev &M, bool asr, bool want_post, bool use_sweep)
+int plan_device(phb_ctx *ctx, Device &d, const ModelDev &M, bool asr, bool want_post, bool use_sweep, int64_t wave_sites = 0)
 {
     const TreeSched &T = ctx->tree;
     CU(cudaSetDevice(d.ordinal));
@@ -448,6 +448,8 @@ int plan_device(phb_ctx *ctx, Device &d, const ModelDev &M, bool asr, bool want_
     }
     if (asr && d.P_pad >= 8 * 32768) // at least 8 tiles: the D2H of a finished tile overlaps the next tile's kernels
         tile = std::min<int64_t>(tile, round_up((d.P_pad + 7) / 8, SITES_PER_BLOCK));
+    // storing sweep: a tile that is a whole number of persistent-grid passes (SMs x patterns per CTA pass)
+    if (wave_sites >= 16 && wave_sites % 16 == 0 && tile > wave_sites && tile < d.P_pad) tile = tile / wave_sites * wave_sites;
     d.tile_pad = tile;
     d.n_tiles = (int)((d.P + tile - 1) / tile);
     if (d.P == 0) d.n_tiles = 0;
@@ -542,10 +544,33 @@ int run_tile_down(phb_ctx *ctx, Device &d, const ModelDev &M, int64_t tile_off, 
                    post ? post + ((int64_t)T.root * d.P_pad + tile_off) * 4 : (double *)nullptr);
         CHECK_LAUNCH();
     }
+    static const bool down_v1 = [] { const char *e = getenv("PHB_ASR_DOWN_V1"); return e && atoi(e) == 1; }();
     for (int dl = 0; dl <= T.max_depth; ++dl) {
         int nb = T.dlevel_off[dl + 1] - T.dlevel_off[dl];
         if (nb <= 0) continue;
         ScopedTimer tm(ctx, &d, PH_DOWN);
+        if (M.n_cat <= DOWN_CAT_MAX && !down_v1) { // category-parallel: one HBM round trip per thread
+            const int sp = down_cat_pairs(M.n_cat);
+            const int bprc = (tile_len + 2 * sp - 1) / (2 * sp);
+#define PHB_DOWN_CAT(KK)                                                                                               \
+    PHB_LAUNCH(asr_down_cat_kernel<KK>, dim3((unsigned)((int64_t)nb * bprc)), dim3(KK * down_cat_pairs(KK)), d.stream,  \
+               d.dops.as<DownOp>() + T.dlevel_off[dl], nb, d.dkids.as<DownChild>(), M, d.Pmat.as<double>(),             \
+               d.clv.as<double>(), slot_stride, tile_pad, tile_len, bprc, d.tips.as<uint8_t>(), d.P_pad, tile_off,      \
+               d.cat_ll.as<double>(), states, post)
+            switch (M.n_cat) {
+            case 1: PHB_DOWN_CAT(1); break;
+            case 2: PHB_DOWN_CAT(2); break;
+            case 3: PHB_DOWN_CAT(3); break;
+            case 4: PHB_DOWN_CAT(4); break;
+            case 5: PHB_DOWN_CAT(5); break;
+            case 6: PHB_DOWN_CAT(6); break;
+            case 7: PHB_DOWN_CAT(7); break;
+            default: PHB_DOWN_CAT(8); break;
+            }
+#undef PHB_DOWN_CAT
+            CHECK_LAUNCH();
+            continue;
+        }
         int64_t grid = (int64_t)nb * bpr2;
         PHB_LAUNCH(asr_down_level_kernel, dim3((unsigned)grid), dim3(ROOT_THREADS), d.stream,
                    d.dops.as<DownOp>() + T.dlevel_off[dl], nb, d.dkids.as<DownChild>(), M, d.Pmat.as<double>(),
@@ -767,7 +792,8 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
     const bool timing = ctx->flags & PHB_FLAG_TIMING;
     for (Device &d : ctx->devs) {
-        rc = plan_device(ctx, d, M, asr, want_post, use_sweep);
+        const int64_t wave = asr_sweep ? (int64_t)std::max(d.sm_count, 1) * 4 * ((SW_MAX_CONSUMERS / M.n_clv) & ~3) : 0;
+        rc = plan_device(ctx, d, M, asr, want_post, use_sweep, wave);
         if (rc) return rc;
     }
     if (timing) {
