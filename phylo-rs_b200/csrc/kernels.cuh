@@ -736,131 +736,6 @@ asr_down_level_kernel(const DownOp *__restrict__ ops, int n_ops, const DownChild
     }
 }
 
-// Category-parallel variant (K <= 8): one block = (parent node, SP pattern pairs); warp w works on category
-// w / (SP / 32), so a thread makes ONE round trip to HBM (parent posterior, children's CLVs in; children's
-// posteriors out) instead of K dependent ones, and K times as many independent loads are in flight per SM.
-// The category mixture meets in shared memory: sh[c][child][state][pair] holds w_c * post; after the barrier
-// thread (c, pair) with c < children-in-chunk sums child c over the categories in category order — the same
-// order of additions as the reference's loop (likelihood.rs:365-375) — normalises, takes the last-max argmax.
-constexpr int DOWN_CAT_MAX = 8;
-__host__ __device__ constexpr int down_cat_pairs(int K) { return K <= 2 ? 128 : K <= 4 ? 64 : 32; }
-
-template <int K>
-__global__ void __launch_bounds__(K * down_cat_pairs(K))
-asr_down_cat_kernel(const DownOp *__restrict__ ops, int n_ops, const DownChild *__restrict__ kids,
-                    ModelDev M, const double *__restrict__ Pmat, double *__restrict__ clv,
-                    size_t slot_stride, size_t tile_pad, int tile_len, int blocks_per_row,
-                    const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off,
-                    const double *__restrict__ mixw,
-                    uint8_t *__restrict__ states /* [node][P_pad] */, double *__restrict__ posteriors /* nullable [node][P_pad][4] */)
-{
-    constexpr int SP = down_cat_pairs(K);
-    __shared__ double2 sh[K][2][4][SP];
-    const int sb = blockIdx.x % blocks_per_row;
-    const int opi = blockIdx.x / blocks_per_row;
-    if (opi >= n_ops) return;
-    const int c = threadIdx.x / SP, pr = threadIdx.x - c * SP;
-    const int64_t site = ((int64_t)sb * SP + pr) * 2;
-    const bool live = site < tile_len;
-    const bool has2 = site + 1 < tile_len;
-    const DownOp op = ops[opi];
-    double2 par[4], w = make_double2(0.0, 0.0);
-    if (live) {
-        const double *pp = clv + (size_t)op.parent_slot * slot_stride + (size_t)c * 4 * tile_pad + site;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) par[i] = *reinterpret_cast<const double2 *>(pp + (size_t)i * tile_pad);
-        w = *reinterpret_cast<const double2 *>(mixw + (size_t)c * tile_pad + site);
-    }
-    for (int k0 = op.child_begin; k0 < op.child_end; k0 += 2) {
-        const int nk = min(2, op.child_end - k0);
-        if (live) {
-            double2 up[2][4];
-            double *self[2] = {nullptr, nullptr};
-            // all loads of the chunk first
-#pragma unroll
-            for (int k = 0; k < 2; ++k) {
-                if (k >= nk) break;
-                const DownChild ch = kids[k0 + k];
-                if (ch.is_tip) {
-                    const uint8_t *tp = tips + (int64_t)ch.src * P_pad + tile_off + site;
-                    const uint32_t m0 = code_mask(tp[0]), m1 = code_mask(tp[1]);
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) up[k][i] = make_double2(((m0 >> i) & 1u) ? 1.0 : 0.0, ((m1 >> i) & 1u) ? 1.0 : 0.0);
-                } else {
-                    self[k] = clv + (size_t)ch.src * slot_stride + (size_t)c * 4 * tile_pad + site;
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) up[k][i] = *reinterpret_cast<const double2 *>(self[k] + (size_t)i * tile_pad);
-                }
-            }
-#pragma unroll
-            for (int k = 0; k < 2; ++k) {
-                if (k >= nk) break;
-                const DownChild ch = kids[k0 + k];
-                double p[16];
-                load_P(Pmat + ((size_t)ch.node * M.n_cat + c) * 16, p);
-                double2 post[4], sum = make_double2(0.0, 0.0);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) { // msg_i = sum_j P[j][i] * par[j]  (P^T * post_parent)
-                    const double mx = p[0 * 4 + i] * par[0].x + p[1 * 4 + i] * par[1].x + p[2 * 4 + i] * par[2].x + p[3 * 4 + i] * par[3].x;
-                    const double my = p[0 * 4 + i] * par[0].y + p[1 * 4 + i] * par[1].y + p[2 * 4 + i] * par[2].y + p[3 * 4 + i] * par[3].y;
-                    post[i] = make_double2(up[k][i].x * mx, up[k][i].y * my);
-                    sum.x += post[i].x;
-                    sum.y += post[i].y;
-                }
-                const double ix = sum.x > 0.0 ? 1.0 / sum.x : 1.0, iy = sum.y > 0.0 ? 1.0 / sum.y : 1.0;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    post[i].x *= ix;
-                    post[i].y *= iy;
-                    if (self[k]) *reinterpret_cast<double2 *>(self[k] + (size_t)i * tile_pad) = post[i];
-                    sh[c][k][i][pr] = make_double2(w.x * post[i].x, w.y * post[i].y);
-                }
-            }
-        }
-        __syncthreads();
-        // mixture, normalisation, argmax: thread (c, pr) serves child c of the chunk (K = 1: both children)
-        for (int k = c; k < nk; k += K) {
-            if (!live) break;
-            const DownChild ch = kids[k0 + k];
-            double m0[4], m1[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                double ax = 0.0, ay = 0.0;
-#pragma unroll
-                for (int cc = 0; cc < K; ++cc) {
-                    const double2 t = sh[cc][k][i][pr];
-                    ax += t.x;
-                    ay += t.y;
-                }
-                m0[i] = ax;
-                m1[i] = ay;
-            }
-            const double s0 = m0[0] + m0[1] + m0[2] + m0[3], s1 = m1[0] + m1[1] + m1[2] + m1[3];
-            if (s0 > 0.0) {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) m0[i] /= s0;
-            }
-            if (s1 > 0.0) {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) m1[i] /= s1;
-            }
-            uint8_t *so = states + (int64_t)ch.node * P_pad + tile_off + site;
-            so[0] = (uint8_t)argmax_last(m0);
-            if (has2) so[1] = (uint8_t)argmax_last(m1);
-            if (posteriors) {
-                double *o = posteriors + ((int64_t)ch.node * P_pad + tile_off + site) * 4;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) o[i] = m0[i];
-                if (has2) {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) o[4 + i] = m1[i];
-                }
-            }
-        }
-        __syncthreads(); // sh is reused by the next chunk
-    }
-}
-
 // ---------------------------------------------------------------------------------------------
 // Synthetic alignment simulator (benchmark input generator): per site draw a rate
 // category ~ weights, a root state ~ pi, then walk the tree in pre-order drawing each child state

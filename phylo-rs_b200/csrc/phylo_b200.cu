@@ -544,33 +544,10 @@ int run_tile_down(phb_ctx *ctx, Device &d, const ModelDev &M, int64_t tile_off, 
                    post ? post + ((int64_t)T.root * d.P_pad + tile_off) * 4 : (double *)nullptr);
         CHECK_LAUNCH();
     }
-    static const bool down_v1 = [] { const char *e = getenv("PHB_ASR_DOWN_V1"); return e && atoi(e) == 1; }();
     for (int dl = 0; dl <= T.max_depth; ++dl) {
         int nb = T.dlevel_off[dl + 1] - T.dlevel_off[dl];
         if (nb <= 0) continue;
         ScopedTimer tm(ctx, &d, PH_DOWN);
-        if (M.n_cat <= DOWN_CAT_MAX && !down_v1) { // category-parallel: one HBM round trip per thread
-            const int sp = down_cat_pairs(M.n_cat);
-            const int bprc = (tile_len + 2 * sp - 1) / (2 * sp);
-#define PHB_DOWN_CAT(KK)                                                                                               \
-    PHB_LAUNCH(asr_down_cat_kernel<KK>, dim3((unsigned)((int64_t)nb * bprc)), dim3(KK * down_cat_pairs(KK)), d.stream,  \
-               d.dops.as<DownOp>() + T.dlevel_off[dl], nb, d.dkids.as<DownChild>(), M, d.Pmat.as<double>(),             \
-               d.clv.as<double>(), slot_stride, tile_pad, tile_len, bprc, d.tips.as<uint8_t>(), d.P_pad, tile_off,      \
-               d.cat_ll.as<double>(), states, post)
-            switch (M.n_cat) {
-            case 1: PHB_DOWN_CAT(1); break;
-            case 2: PHB_DOWN_CAT(2); break;
-            case 3: PHB_DOWN_CAT(3); break;
-            case 4: PHB_DOWN_CAT(4); break;
-            case 5: PHB_DOWN_CAT(5); break;
-            case 6: PHB_DOWN_CAT(6); break;
-            case 7: PHB_DOWN_CAT(7); break;
-            default: PHB_DOWN_CAT(8); break;
-            }
-#undef PHB_DOWN_CAT
-            CHECK_LAUNCH();
-            continue;
-        }
         int64_t grid = (int64_t)nb * bpr2;
         PHB_LAUNCH(asr_down_level_kernel, dim3((unsigned)grid), dim3(ROOT_THREADS), d.stream,
                    d.dops.as<DownOp>() + T.dlevel_off[dl], nb, d.dkids.as<DownChild>(), M, d.Pmat.as<double>(),
