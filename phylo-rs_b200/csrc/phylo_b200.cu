@@ -1789,12 +1789,13 @@ int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns
         if (rc) return rc;
         rc = launch_sweep_transition(ctx, d, M);
         if (rc) return rc;
-        // chunks of two full passes of the widest CTA; a short remainder joins the last chunk, which gets
+        // chunks of whole passes of the widest CTA (2 by default: measured 246 / 217 / 213 / 231 / 250 ms end to end for 1 / 2 / 3 / 4 / 8); a short remainder joins the last chunk, which gets
         // its own geometry so that it does not end in a nearly empty pass
         const int n_sm = std::max(d.sm_count, 1);
         const int q_max = (SW_MAX_CONSUMERS / M.n_clv) & ~3;
         const int64_t pass = (int64_t)n_sm * 4 * q_max;
-        const int64_t chunk = round_up(2 * pass, 64);
+        static const int chunk_passes = [] { const char *e = getenv("PHB_HOST_CHUNK_PASSES"); int v = e ? atoi(e) : 2; return v >= 1 && v <= 16 ? v : 2; }();
+        const int64_t chunk = round_up(chunk_passes * pass, 64);
         std::vector<int64_t> bounds(1, 0);
         while (d.P - bounds.back() > chunk + chunk / 2) bounds.push_back(bounds.back() + chunk);
         bounds.push_back(d.P);

@@ -212,6 +212,8 @@ def test_score_nni_models_ambiguity_tiling(emu_lib, model, amb):
     one, _ = _cases.check_nni(emu_lib, case)
     ok = np.isfinite(got)
     assert np.max(np.abs(got[ok] - one[ok]) / np.abs(one[ok])) < 1e-13
+    sharded, _ = _cases.check_nni(emu_lib, case, devices=[0, 0, 0])  # three pattern shards, host sum per neighbour
+    assert np.max(np.abs(sharded[ok] - one[ok]) / np.abs(one[ok])) < 1e-13
 
 
 def test_score_nni_deep_tree_rescaling(emu_lib):
