@@ -200,7 +200,7 @@ nni_score_kernel(const NniMove *__restrict__ moves, int n_moves, const NniStep *
                  const uint8_t *__restrict__ inv_mask /* + tile_off */, const double *__restrict__ mult /* + tile_off */,
                  double *__restrict__ partials /* [move][n_site_blocks] */, int n_site_blocks)
 {
-    constexpr int G = nni_groups(NC), BS = nni_block_sites(NC), NT = nni_threads(NC);
+    constexpr int BS = nni_block_sites(NC), NT = nni_threads(NC);
     __shared__ __align__(16) double sP[(2 * NNI_CHUNK + 1) * NC * 16]; // [0]: first message; then per step: sibling, up
     __shared__ NniStep sSteps[NNI_CHUNK];
     __shared__ double sLL[NC][BS];

@@ -26,7 +26,8 @@ def emu_lib():
     import __graft_entry__ as g
     from phylo_rs_b200 import capi
 
-    return capi.Library(g.build_emu())
+    alt = os.environ.get("PHB_EMU_LIB")  # e.g. an AddressSanitizer build of the same sources (LD_PRELOAD libasan)
+    return capi.Library(alt if alt else g.build_emu())
 
 
 @pytest.fixture(scope="session")
