@@ -424,23 +424,37 @@ sweep_kernel(SweepParams p, ModelDev M)
                     for (int r = 0; r < SW_R; ++r) sw_rescale(acc[r], sc[r]);
                 }
             };
-            switch (kind) {
+            // dense dispatch code: kind, +8 when the op works on / takes its pending operand from `u`
+            const bool on_u = flags & (SW_FLAG_U | SW_FLAG_XU);
+            const bool resc = flags & SW_FLAG_RESCALE;
+            switch (kind | (on_u ? 8 : 0)) {
             case SW_TT:
-                if (flags & SW_FLAG_U) op_tt(u);
-                else op_tt(v);
+                op_tt(v);
+                if (resc) guard(v);
+                break;
+            case SW_TT | 8:
+                op_tt(u);
+                if (resc) guard(u);
                 break;
             case SW_TI:
-                if (flags & SW_FLAG_U) op_ti(u);
-                else op_ti(v);
+                op_ti(v);
+                if (resc) guard(v);
                 break;
-            case SW_II:
-                if (flags & SW_FLAG_XU) op_ii(u);
-                else {
-                    double x[SW_R][4];
-                    pop(x);
-                    op_ii(x);
-                }
+            case SW_TI | 8:
+                op_ti(u);
+                if (resc) guard(u);
                 break;
+            case SW_II | 8:
+                op_ii(u);
+                if (resc) guard(v);
+                break;
+            case SW_II: {
+                double x[SW_R][4];
+                pop(x);
+                op_ii(x);
+                if (resc) guard(v);
+                break;
+            }
             case SW_APPLY: {
                 double P[16];
                 sw_load_P(blkA, P);
@@ -451,6 +465,7 @@ sweep_kernel(SweepParams p, ModelDev M)
 #pragma unroll
                     for (int i = 0; i < 4; ++i) v[r][i] = y[i];
                 }
+                if (resc) guard(v);
                 break;
             }
             case SW_MULTIP:
@@ -464,6 +479,7 @@ sweep_kernel(SweepParams p, ModelDev M)
 #pragma unroll
                     for (int i = 0; i < 4; ++i) v[r][i] = (kind == SW_LOADTIP) ? ta[i] : v[r][i] * ta[i];
                 }
+                if (resc) guard(v);
                 break;
             }
             case SW_MULPOP: {
@@ -473,34 +489,31 @@ sweep_kernel(SweepParams p, ModelDev M)
                 for (int r = 0; r < SW_R; ++r)
 #pragma unroll
                     for (int i = 0; i < 4; ++i) v[r][i] *= x[r][i];
+                if (resc) guard(v);
                 break;
             }
             default:
                 if (lane == 0) atomicOr(p.error_flag, 1u);
                 break;
             }
-            if (flags & SW_FLAG_RESCALE) {
-                if (flags & SW_FLAG_U) guard(u);
-                else guard(v);
-                if (STORE && active) {
-                    const int64_t rel = b * sites_per_block + 4 * q; // first of this thread's 4 patterns, launch-relative
-                    double *dst = p.clv_out + (size_t)h.z * p.slot_stride + (size_t)cc * 4 * p.tile_pad + (size_t)rel;
-                    const bool use_u = flags & SW_FLAG_U;
-                    if (rel + 3 < p.P) {
+            if (STORE && resc && active) {
+                const int64_t rel = b * sites_per_block + 4 * q; // first of this thread's 4 patterns, launch-relative
+                double *dst = p.clv_out + (size_t)h.z * p.slot_stride + (size_t)cc * 4 * p.tile_pad + (size_t)rel;
+                const bool use_u = flags & SW_FLAG_U;
+                if (rel + 3 < p.P) {
 #pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            double2 *d2 = reinterpret_cast<double2 *>(dst + (size_t)i * p.tile_pad);
-                            d2[0] = use_u ? make_double2(u[0][i], u[1][i]) : make_double2(v[0][i], v[1][i]);
-                            d2[1] = use_u ? make_double2(u[2][i], u[3][i]) : make_double2(v[2][i], v[3][i]);
-                        }
-                    } else {
-#pragma unroll
-                        for (int r = 0; r < SW_R; ++r)
-                            if (rel + r < p.P) {
-#pragma unroll
-                                for (int i = 0; i < 4; ++i) dst[(size_t)i * p.tile_pad + r] = use_u ? u[r][i] : v[r][i];
-                            }
+                    for (int i = 0; i < 4; ++i) {
+                        double2 *d2 = reinterpret_cast<double2 *>(dst + (size_t)i * p.tile_pad);
+                        d2[0] = use_u ? make_double2(u[0][i], u[1][i]) : make_double2(v[0][i], v[1][i]);
+                        d2[1] = use_u ? make_double2(u[2][i], u[3][i]) : make_double2(v[2][i], v[3][i]);
                     }
+                } else {
+#pragma unroll
+                    for (int r = 0; r < SW_R; ++r)
+                        if (rel + r < p.P) {
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) dst[(size_t)i * p.tile_pad + r] = use_u ? u[r][i] : v[r][i];
+                        }
                 }
             }
             __syncwarp();
