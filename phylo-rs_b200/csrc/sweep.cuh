@@ -349,7 +349,8 @@ sweep_kernel(SweepParams p, ModelDev M)
             const unsigned char *blkB = blkA + szA;
             const unsigned char *codesA = st + code_off;
             const unsigned char *codesB = codesA + code_bytes;
-            if (flags & SW_FLAG_PUSH) {
+            // ---- the op bodies, written once over the accumulator they update ----
+            auto push = [&]() { // park the running result before a TT / LOADTIP overwrites it
                 double2 *slot = level < smem_levels ? sstack + level * lvl_stride
                                                     : gstack + (size_t)(level - smem_levels) * lvl_stride;
                 if (active) {
@@ -359,8 +360,7 @@ sweep_kernel(SweepParams p, ModelDev M)
                         slot[(2 * r + 1) * n_cons] = make_double2(v[r][2], v[r][3]);
                     }
                 }
-            }
-            // ---- the op bodies, written once over the accumulator they update ----
+            };
             auto op_tt = [&](double (&acc)[SW_R][4]) {
                 const uchar4 ca = *reinterpret_cast<const uchar4 *>(codesA);
                 const uchar4 cb = *reinterpret_cast<const uchar4 *>(codesB);
@@ -429,6 +429,7 @@ sweep_kernel(SweepParams p, ModelDev M)
             const bool resc = flags & SW_FLAG_RESCALE;
             switch (kind | (on_u ? 8 : 0)) {
             case SW_TT:
+                if (flags & SW_FLAG_PUSH) push();
                 op_tt(v);
                 if (resc) guard(v);
                 break;
@@ -470,6 +471,7 @@ sweep_kernel(SweepParams p, ModelDev M)
             }
             case SW_MULTIP:
             case SW_LOADTIP: {
+                if (flags & SW_FLAG_PUSH) push();
                 const uchar4 ca = *reinterpret_cast<const uchar4 *>(codesA);
                 const uint32_t a4[4] = {ca.x, ca.y, ca.z, ca.w};
 #pragma unroll
