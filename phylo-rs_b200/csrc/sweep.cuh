@@ -46,7 +46,8 @@ constexpr int SW_BAR_BYTES = 512; // mbarrier area at the start of dynamic share
 
 // Per-op header, one table for the whole tree in global memory (identical for every site block, so the
 // consumers prefetch it two ops ahead into registers: nothing on the op's critical path waits for it).
-//   w0 = kind | flags << 8 | level << 16      w1 = szA | szB << 16   (per-category bytes of operand A / B)
+//   w0 = code | flags << 8 | level << 16      w1 = szA | szB << 16   (per-category bytes of operand A / B)
+//        code = kind, + 8 when the op works on / takes its pending operand from the second accumulator `u`
 //   w2 = CLV slot of the node this op completes (valid with SW_FLAG_RESCALE; used by the storing variant)
 struct SweepOp {
     uint32_t w0, w1, w2, w3;
@@ -134,6 +135,7 @@ __device__ inline void sw_bulk_g2s(void *dst, const void *src, uint32_t bytes, s
     emu::mbar_check(b);
 }
 __device__ inline void sw_consumer_barrier(int n) { emu::named_barrier(1, (unsigned)n); }
+__device__ inline void sw_prefetch_l1(const void *) {}
 #else
 typedef unsigned long long sw_mbar_t;
 __device__ __forceinline__ uint32_t sw_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -172,6 +174,7 @@ __device__ __forceinline__ void sw_bulk_g2s(void *dst, const void *src, uint32_t
                  : "memory");
 }
 __device__ __forceinline__ void sw_consumer_barrier(int n) { asm volatile("bar.sync 1, %0;" ::"r"(n) : "memory"); }
+__device__ __forceinline__ void sw_prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 #endif
 
 // ---- kernel parameters -------------------------------------------------------------------------------
@@ -342,7 +345,7 @@ sweep_kernel(SweepParams p, ModelDev M)
             const uint4 h = hq0;
             hq0 = hq1;
             hq1 = __ldg(optab + (k + 2 < n_ops ? k + 2 : n_ops - 1));
-            const int kind = h.x & 0xff, flags = (h.x >> 8) & 0xff, level = (int)(h.x >> 16);
+            const int code = h.x & 0xff, kind = code & 7, flags = (h.x >> 8) & 0xff, level = (int)(h.x >> 16);
             const int szA = h.y & 0xffff, szB = (int)(h.y >> 16);
             sw_mbar_wait(&full[s], parity);
             const unsigned char *blkA = st + cc * (szA + szB);
@@ -424,10 +427,8 @@ sweep_kernel(SweepParams p, ModelDev M)
                     for (int r = 0; r < SW_R; ++r) sw_rescale(acc[r], sc[r]);
                 }
             };
-            // dense dispatch code: kind, +8 when the op works on / takes its pending operand from `u`
-            const bool on_u = flags & (SW_FLAG_U | SW_FLAG_XU);
             const bool resc = flags & SW_FLAG_RESCALE;
-            switch (kind | (on_u ? 8 : 0)) {
+            switch (code) { // dense dispatch code, precomputed by the host scheduler
             case SW_TT:
                 if (flags & SW_FLAG_PUSH) push();
                 op_tt(v);
@@ -516,6 +517,14 @@ sweep_kernel(SweepParams p, ModelDev M)
 #pragma unroll
                             for (int i = 0; i < 4; ++i) dst[(size_t)i * p.tile_pad + r] = use_u ? u[r][i] : v[r][i];
                         }
+                }
+            }
+            { // the next op pops a level that lives in the L2-resident global stack: pull it towards L1 now
+                const int ncode = hq0.x & 0xff, nlevel = (int)(hq0.x >> 16);
+                if ((ncode == SW_II || ncode == SW_MULPOP) && nlevel >= smem_levels) {
+                    const double2 *slot = gstack + (size_t)(nlevel - smem_levels) * lvl_stride;
+#pragma unroll
+                    for (int r = 0; r < 2 * SW_R; ++r) sw_prefetch_l1(slot + r * n_cons);
                 }
             }
             __syncwarp();

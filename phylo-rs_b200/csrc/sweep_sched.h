@@ -201,7 +201,8 @@ struct SweepSched {
         ops.resize(recs.size());
         for (size_t k = 0; k < recs.size(); ++k) {
             const Hdr &h = recs[k].h;
-            ops[k].w0 = (uint32_t)h.kind | ((uint32_t)h.flags << 8) | ((uint32_t)h.level << 16);
+            const uint32_t code = (uint32_t)h.kind | ((h.flags & (SW_FLAG_U | SW_FLAG_XU)) ? 8u : 0u);
+            ops[k].w0 = code | ((uint32_t)h.flags << 8) | ((uint32_t)h.level << 16);
             ops[k].w1 = (uint32_t)h.szA | ((uint32_t)h.szB << 16);
             const int nd = (h.flags & SW_FLAG_RESCALE) ? recs[k].node : -1;
             ops[k].w2 = (nd >= 0 && (size_t)nd < slot.size() && slot[nd] >= 0) ? (uint32_t)slot[nd] : 0u;
