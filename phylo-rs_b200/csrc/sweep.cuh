@@ -135,7 +135,6 @@ __device__ inline void sw_bulk_g2s(void *dst, const void *src, uint32_t bytes, s
     emu::mbar_check(b);
 }
 __device__ inline void sw_consumer_barrier(int n) { emu::named_barrier(1, (unsigned)n); }
-__device__ inline void sw_prefetch_l1(const void *) {}
 #else
 typedef unsigned long long sw_mbar_t;
 __device__ __forceinline__ uint32_t sw_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -174,7 +173,6 @@ __device__ __forceinline__ void sw_bulk_g2s(void *dst, const void *src, uint32_t
                  : "memory");
 }
 __device__ __forceinline__ void sw_consumer_barrier(int n) { asm volatile("bar.sync 1, %0;" ::"r"(n) : "memory"); }
-__device__ __forceinline__ void sw_prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 #endif
 
 // ---- kernel parameters -------------------------------------------------------------------------------
@@ -517,14 +515,6 @@ sweep_kernel(SweepParams p, ModelDev M)
 #pragma unroll
                             for (int i = 0; i < 4; ++i) dst[(size_t)i * p.tile_pad + r] = use_u ? u[r][i] : v[r][i];
                         }
-                }
-            }
-            { // the next op pops a level that lives in the L2-resident global stack: pull it towards L1 now
-                const int ncode = hq0.x & 0xff, nlevel = (int)(hq0.x >> 16);
-                if ((ncode == SW_II || ncode == SW_MULPOP) && nlevel >= smem_levels) {
-                    const double2 *slot = gstack + (size_t)(nlevel - smem_levels) * lvl_stride;
-#pragma unroll
-                    for (int r = 0; r < 2 * SW_R; ++r) sw_prefetch_l1(slot + r * n_cons);
                 }
             }
             __syncwarp();
