@@ -638,7 +638,14 @@ constexpr int DOWN_MAX_CHILDREN = 2; // register fast path; larger arities loop 
 // One block = (parent node, 512 sites); one thread = a site PAIR (16-byte accesses on the site axis).
 // `mixw` holds the per-site category weights exp(cat_ll_c - site_ll) (likelihood.rs:356-363), written
 // once per tile by asr_root_kernel into the cat_ll buffer, so no exp() runs here.
-__global__ void __launch_bounds__(ROOT_THREADS)
+#ifndef PHB_DOWN_THREADS
+#define PHB_DOWN_THREADS 128
+#endif
+constexpr int DOWN_THREADS = PHB_DOWN_THREADS; // a block covers 2 * DOWN_THREADS patterns of one parent
+#ifndef PHB_DOWN_MINB
+#define PHB_DOWN_MINB 5 // measured on B200 (5k x 500k): 128 threads x >= 5 blocks 241 ms; 256 x 1: 262; 128 x 6: 251; 128 x 8: 334
+#endif
+__global__ void __launch_bounds__(DOWN_THREADS, PHB_DOWN_MINB)
 asr_down_level_kernel(const DownOp *__restrict__ ops, int n_ops, const DownChild *__restrict__ kids,
                       ModelDev M, const double *__restrict__ Pmat, double *__restrict__ clv,
                       size_t slot_stride, size_t tile_pad, int tile_len, int blocks_per_row,

@@ -532,7 +532,7 @@ int run_tile_down(phb_ctx *ctx, Device &d, const ModelDev &M, int64_t tile_off, 
     const size_t tile_pad = (size_t)d.tile_pad;
     const size_t slot_stride = (size_t)M.n_clv * 4 * tile_pad;
     const int bpr = (tile_len + ROOT_THREADS - 1) / ROOT_THREADS;
-    const int bpr2 = (tile_len + 2 * ROOT_THREADS - 1) / (2 * ROOT_THREADS); // down kernel: a site pair per thread
+    const int bpr2 = (tile_len + 2 * DOWN_THREADS - 1) / (2 * DOWN_THREADS); // down kernel: a site pair per thread
     uint8_t *states = d.states.as<uint8_t>();
     double *post = want_post ? d.posteriors.as<double>() : nullptr;
     {
@@ -549,7 +549,7 @@ int run_tile_down(phb_ctx *ctx, Device &d, const ModelDev &M, int64_t tile_off, 
         if (nb <= 0) continue;
         ScopedTimer tm(ctx, &d, PH_DOWN);
         int64_t grid = (int64_t)nb * bpr2;
-        PHB_LAUNCH(asr_down_level_kernel, dim3((unsigned)grid), dim3(ROOT_THREADS), d.stream,
+        PHB_LAUNCH(asr_down_level_kernel, dim3((unsigned)grid), dim3(DOWN_THREADS), d.stream,
                    d.dops.as<DownOp>() + T.dlevel_off[dl], nb, d.dkids.as<DownChild>(), M, d.Pmat.as<double>(),
                    d.clv.as<double>(), slot_stride, tile_pad, tile_len, bpr2, d.tips.as<uint8_t>(), d.P_pad, tile_off,
                    d.cat_ll.as<double>(), states, post);
