@@ -37,14 +37,16 @@ __device__ __forceinline__ double joint_tip_value(uint32_t code, int j, const Mo
     return (code & 16u) ? 0.0 : M.ln_tip[__popc(m)];
 }
 
-// max_j (lnp[4*i + j] + c[j]) with the reference's sequential `val > local_max` semantics: a NaN never wins
-// and an all-NaN / all -inf row yields -inf — exactly what fmax (which returns its non-NaN operand) computes.
+// max_j (lnp[4*i + j] + c[j]) with the reference's sequential `val > local_max` semantics (NaN never wins)
 __device__ __forceinline__ double joint_row_max(const double (&lnp)[16], int i, const double (&c)[4])
 {
-    const double a = fmax(lnp[4 * i + 0] + c[0], lnp[4 * i + 1] + c[1]);
-    const double b = fmax(lnp[4 * i + 2] + c[2], lnp[4 * i + 3] + c[3]);
-    const double neg_inf = -INFINITY;
-    return fmax(neg_inf, fmax(a, b));
+    double best = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const double val = lnp[4 * i + j] + c[j];
+        if (val > best) best = val;
+    }
+    return best;
 }
 __device__ __forceinline__ int joint_row_argmax(const double *__restrict__ lnp_row, const double (&c)[4])
 {
