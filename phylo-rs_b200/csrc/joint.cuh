@@ -113,6 +113,87 @@ joint_up_level_kernel(const GenOp *__restrict__ ops, int n_ops, const GenChild *
     for (int i = 0; i < 4; ++i) dst[i * stride2] = make_double2(vx[i], vy[i]);
 }
 
+// Binary nodes (the common case): both children's loads are issued before any arithmetic.
+template <bool TIP0, bool TIP1>
+__device__ __forceinline__ void joint_up_pair(const NodeOp &op, int cat, const ModelDev &M, const double *__restrict__ lnP,
+                                              double *__restrict__ cbuf, size_t slot_stride, size_t tile_pad,
+                                              const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off, int64_t site)
+{
+    const size_t stride2 = tile_pad / 2;
+    const size_t cat_off = (size_t)cat * 4 * tile_pad + (size_t)site;
+    double ax[4], ay[4], bx[4], by[4];
+    if (TIP0) {
+        const uchar2 code = *reinterpret_cast<const uchar2 *>(tips + (int64_t)op.c0 * P_pad + tile_off + site);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            ax[j] = joint_tip_value(code.x, j, M);
+            ay[j] = joint_tip_value(code.y, j, M);
+        }
+    } else {
+        const double2 *src = reinterpret_cast<const double2 *>(cbuf + (size_t)op.c0 * slot_stride + cat_off);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const double2 t = src[j * stride2];
+            ax[j] = t.x;
+            ay[j] = t.y;
+        }
+    }
+    if (TIP1) {
+        const uchar2 code = *reinterpret_cast<const uchar2 *>(tips + (int64_t)op.c1 * P_pad + tile_off + site);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            bx[j] = joint_tip_value(code.x, j, M);
+            by[j] = joint_tip_value(code.y, j, M);
+        }
+    } else {
+        const double2 *src = reinterpret_cast<const double2 *>(cbuf + (size_t)op.c1 * slot_stride + cat_off);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const double2 t = src[j * stride2];
+            bx[j] = t.x;
+            by[j] = t.y;
+        }
+    }
+    double lnp[16];
+    double vx[4], vy[4];
+    load_P(lnP + ((size_t)op.e0 * M.n_cat + cat) * 16, lnp);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { // the reference starts from 0.0 and adds child by child (likelihood.rs:483, :505)
+        vx[i] = 0.0 + joint_row_max(lnp, i, ax);
+        vy[i] = 0.0 + joint_row_max(lnp, i, ay);
+    }
+    load_P(lnP + ((size_t)op.e1 * M.n_cat + cat) * 16, lnp);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        vx[i] += joint_row_max(lnp, i, bx);
+        vy[i] += joint_row_max(lnp, i, by);
+    }
+    double2 *dst = reinterpret_cast<double2 *>(cbuf + (size_t)op.out_slot * slot_stride + cat_off);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) dst[i * stride2] = make_double2(vx[i], vy[i]);
+}
+
+__global__ void __launch_bounds__(CLV_THREADS)
+joint_up_binary_kernel(const NodeOp *__restrict__ ops, int n_ops, ModelDev M, const double *__restrict__ lnP,
+                       double *__restrict__ cbuf, size_t slot_stride, size_t tile_pad, int tile_len, int blocks_per_row,
+                       const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off)
+{
+    const int sb = blockIdx.x % blocks_per_row;
+    const int rest = blockIdx.x / blocks_per_row;
+    const int cat = rest % M.n_cat;
+    const int opi = rest / M.n_cat;
+    if (opi >= n_ops) return;
+    const int64_t site = ((int64_t)sb * CLV_THREADS + threadIdx.x) * 2;
+    if (site >= tile_len) return;
+    const NodeOp op = ops[opi];
+    switch (op.kind & 3) {
+    case 0: joint_up_pair<false, false>(op, cat, M, lnP, cbuf, slot_stride, tile_pad, tips, P_pad, tile_off, site); break;
+    case 1: joint_up_pair<true, false>(op, cat, M, lnP, cbuf, slot_stride, tile_pad, tips, P_pad, tile_off, site); break;
+    case 2: joint_up_pair<false, true>(op, cat, M, lnP, cbuf, slot_stride, tile_pad, tips, P_pad, tile_off, site); break;
+    default: joint_up_pair<true, true>(op, cat, M, lnP, cbuf, slot_stride, tile_pad, tips, P_pad, tile_off, site); break;
+    }
+}
+
 // Root: winning category, root state, per-pattern value, weighted partial sums.
 // root_is_tip: the tree is a single leaf (its C values come from the tip code).
 __global__ void __launch_bounds__(ROOT_THREADS)

@@ -567,14 +567,24 @@ int run_tile_joint(phb_ctx *ctx, Device &d, const ModelDev &M, int64_t tile_off,
     const int bpr = (tile_len + SITES_PER_BLOCK - 1) / SITES_PER_BLOCK;
     uint8_t *states = d.states.as<uint8_t>();
     for (int l = 1; l <= T.n_levels; ++l) {
-        const int nb = T.ulevel_off[l] - T.ulevel_off[l - 1];
-        if (nb <= 0) continue;
-        ScopedTimer tm(ctx, &d, PH_CLV);
-        PHB_LAUNCH(joint_up_level_kernel, dim3((unsigned)((int64_t)nb * M.n_cat * bpr)), dim3(CLV_THREADS), d.stream,
-                   d.uops.as<GenOp>() + T.ulevel_off[l - 1], nb, d.ukids.as<GenChild>(), M, d.lnP.as<double>(),
-                   d.clv.as<double>(), slot_stride, tile_pad, tile_len, bpr, d.tips.as<uint8_t>(), d.P_pad, tile_off);
-        CHECK_LAUNCH();
-        if (&d == &ctx->devs[0]) ctx->stats.clv_launches++;
+        const int nb = T.level_off[l] - T.level_off[l - 1]; // binary nodes: both children loaded up front
+        if (nb > 0) {
+            ScopedTimer tm(ctx, &d, PH_CLV);
+            PHB_LAUNCH(joint_up_binary_kernel, dim3((unsigned)((int64_t)nb * M.n_cat * bpr)), dim3(CLV_THREADS), d.stream,
+                       d.ops.as<NodeOp>() + T.level_off[l - 1], nb, M, d.lnP.as<double>(), d.clv.as<double>(), slot_stride,
+                       tile_pad, tile_len, bpr, d.tips.as<uint8_t>(), d.P_pad, tile_off);
+            CHECK_LAUNCH();
+            if (&d == &ctx->devs[0]) ctx->stats.clv_launches++;
+        }
+        const int ng = T.glevel_off[l] - T.glevel_off[l - 1]; // any other arity
+        if (ng > 0) {
+            ScopedTimer tm(ctx, &d, PH_CLV);
+            PHB_LAUNCH(joint_up_level_kernel, dim3((unsigned)((int64_t)ng * M.n_cat * bpr)), dim3(CLV_THREADS), d.stream,
+                       d.gops.as<GenOp>() + T.glevel_off[l - 1], ng, d.gkids.as<GenChild>(), M, d.lnP.as<double>(),
+                       d.clv.as<double>(), slot_stride, tile_pad, tile_len, bpr, d.tips.as<uint8_t>(), d.P_pad, tile_off);
+            CHECK_LAUNCH();
+            if (&d == &ctx->devs[0]) ctx->stats.clv_launches++;
+        }
     }
     {
         ScopedTimer tm(ctx, &d, PH_ROOT);
