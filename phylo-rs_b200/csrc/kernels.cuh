@@ -264,29 +264,68 @@ __global__ void transition_kernel(const double *__restrict__ blen, int n_nodes, 
 // ln 1/2, B,D,.. ln 1/3, N ln 1/4, gap 0);  inv_mask = AND of all leaf masks = the rate-0 (+I)
 // category's CLV at the root in closed form (src/models/gtr.rs:94-99).
 // ---------------------------------------------------------------------------------------------
-__global__ void tip_constants_kernel(const uint8_t *__restrict__ tips, int64_t P_pad, int64_t n_sites,
-                                     const int32_t *__restrict__ leaf_rows, int n_leaves, ModelDev M,
-                                     double *__restrict__ leaf_ls, uint8_t *__restrict__ inv_mask)
+// One block = 128 sites x TIPC_SLICES leaf slices (one warp per slice, a lane = 4 sites, the leaf loop
+// unrolled so that several 128-byte row segments are in flight per warp: the kernel is also launched on
+// the narrow chunks of the host-streaming path, where one thread per site group walking all leaves was
+// latency-bound).  The popcount classes are COUNTED (integers, combined with shared-memory atomics), so
+// the result does not depend on how the leaves are split: ls = n2 ln(1/2) + n3 ln(1/3) + n4 ln(1/4).
+constexpr int TIPC_SLICES = 8;
+constexpr int TIPC_THREADS = 32 * TIPC_SLICES;
+constexpr int TIPC_SITES = 128;
+__global__ void __launch_bounds__(TIPC_THREADS)
+tip_constants_kernel(const uint8_t *__restrict__ tips, int64_t P_pad, int64_t n_sites,
+                     const int32_t *__restrict__ leaf_rows, int n_leaves, ModelDev M,
+                     double *__restrict__ leaf_ls, uint8_t *__restrict__ inv_mask)
 {
     // tips / leaf_ls / inv_mask may point at a pattern offset inside the shard; P_pad is the row stride
-    int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; // group of 4 sites
-    if (q * 4 >= n_sites) return;
-    double ls[4] = {0.0, 0.0, 0.0, 0.0};
-    uint32_t inv[4] = {15u, 15u, 15u, 15u};
-    for (int l = 0; l < n_leaves; ++l) {
-        uchar4 c4 = *reinterpret_cast<const uchar4 *>(tips + (int64_t)leaf_rows[l] * P_pad + q * 4);
-        uint32_t c[4] = {c4.x, c4.y, c4.z, c4.w};
+    __shared__ int s_cnt[3][TIPC_SITES];
+    __shared__ int s_inv[TIPC_SITES];
+    const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
+    if (threadIdx.x < TIPC_SITES) {
+        s_cnt[0][threadIdx.x] = 0;
+        s_cnt[1][threadIdx.x] = 0;
+        s_cnt[2][threadIdx.x] = 0;
+        s_inv[threadIdx.x] = 15;
+    }
+    __syncthreads();
+    const int64_t site = (int64_t)blockIdx.x * TIPC_SITES + lane * 4;
+    if (site < n_sites) { // n_sites is a multiple of 4
+        int cnt[3][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}, {0, 0, 0, 0}};
+        uint32_t inv = 0x0F0F0F0Fu;
+        const uint8_t *base = tips + site;
+#pragma unroll 8
+        for (int l = slice; l < n_leaves; l += TIPC_SLICES) {
+            const uchar4 c4 = *reinterpret_cast<const uchar4 *>(base + (int64_t)leaf_rows[l] * P_pad);
+            const uint32_t c[4] = {c4.x, c4.y, c4.z, c4.w};
+            uint32_t m4 = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t m = code_mask(c[k]);
+                m4 |= m << (8 * k);
+                const int pc = (c[k] & 16u) ? 0 : __popc(m);
+                cnt[0][k] += pc == 2;
+                cnt[1][k] += pc == 3;
+                cnt[2][k] += pc == 4;
+            }
+            inv &= m4;
+        }
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            uint32_t m = code_mask(c[k]);
-            inv[k] &= m;
-            if (!(c[k] & 16u)) ls[k] += M.ln_tip[__popc(m)];
+            const int s = lane * 4 + k;
+            if (cnt[0][k]) atomicAdd(&s_cnt[0][s], cnt[0][k]);
+            if (cnt[1][k]) atomicAdd(&s_cnt[1][s], cnt[1][k]);
+            if (cnt[2][k]) atomicAdd(&s_cnt[2][s], cnt[2][k]);
+            atomicAnd(&s_inv[s], (int)((inv >> (8 * k)) & 15u));
         }
     }
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        leaf_ls[q * 4 + k] = ls[k];
-        inv_mask[q * 4 + k] = (uint8_t)inv[k];
+    __syncthreads();
+    if (threadIdx.x < TIPC_SITES) {
+        const int64_t s = (int64_t)blockIdx.x * TIPC_SITES + threadIdx.x;
+        if (s < n_sites) {
+            leaf_ls[s] = (double)s_cnt[0][threadIdx.x] * M.ln_tip[2] + (double)s_cnt[1][threadIdx.x] * M.ln_tip[3] +
+                         (double)s_cnt[2][threadIdx.x] * M.ln_tip[4];
+            inv_mask[s] = (uint8_t)s_inv[threadIdx.x];
+        }
     }
 }
 

@@ -812,7 +812,7 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
         if (!d.tip_constants_valid && !joint) {
             ScopedTimer tm(ctx, &d, PH_ROOT);
             int64_t groups = d.P_pad / 4;
-            PHB_LAUNCH(tip_constants_kernel, dim3((unsigned)((groups + 255) / 256)), dim3(256), d.stream,
+            PHB_LAUNCH(tip_constants_kernel, dim3((unsigned)((groups * 4 + TIPC_SITES - 1) / TIPC_SITES)), dim3(TIPC_THREADS), d.stream,
                        d.tips.as<uint8_t>(), d.P_pad, d.P_pad, d.leaf_rows.as<int32_t>(), (int)T.leaf_rows.size(), M,
                        d.leaf_ls.as<double>(), d.inv_mask.as<uint8_t>());
             CHECK_LAUNCH();
@@ -1106,7 +1106,7 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
         }
         if (!d.tip_constants_valid) {
             int64_t groups = d.P_pad / 4;
-            PHB_LAUNCH(tip_constants_kernel, dim3((unsigned)((groups + 255) / 256)), dim3(256), d.stream,
+            PHB_LAUNCH(tip_constants_kernel, dim3((unsigned)((groups * 4 + TIPC_SITES - 1) / TIPC_SITES)), dim3(TIPC_THREADS), d.stream,
                        d.tips.as<uint8_t>(), d.P_pad, d.P_pad, d.leaf_rows.as<int32_t>(), (int)T.leaf_rows.size(), M,
                        d.leaf_ls.as<double>(), d.inv_mask.as<uint8_t>());
             CHECK_LAUNCH();
@@ -1799,12 +1799,14 @@ int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns
         if (rc) return rc;
         rc = launch_sweep_transition(ctx, d, M);
         if (rc) return rc;
-        // chunks of whole passes of the widest CTA (2 by default: measured 246 / 217 / 213 / 231 / 250 ms end to end for 1 / 2 / 3 / 4 / 8); a short remainder joins the last chunk, which gets
-        // its own geometry so that it does not end in a nearly empty pass
+        // chunks of whole passes of the widest CTA (1 by default: measured 195.2 / 199.9 / 207.9 ms end to end for
+        // 1 / 2 / 3 passes at 10k x 1M — the copy engine is the bottleneck, so smaller chunks only shorten the
+        // un-overlapped tail); a short remainder joins the last chunk, which gets its own geometry so that it
+        // does not end in a nearly empty pass
         const int n_sm = std::max(d.sm_count, 1);
         const int q_max = (SW_MAX_CONSUMERS / M.n_clv) & ~3;
         const int64_t pass = (int64_t)n_sm * 4 * q_max;
-        static const int chunk_passes = [] { const char *e = getenv("PHB_HOST_CHUNK_PASSES"); int v = e ? atoi(e) : 2; return v >= 1 && v <= 16 ? v : 2; }();
+        static const int chunk_passes = [] { const char *e = getenv("PHB_HOST_CHUNK_PASSES"); int v = e ? atoi(e) : 1; return v >= 1 && v <= 16 ? v : 1; }();
         const int64_t chunk = round_up(chunk_passes * pass, 64);
         std::vector<int64_t> bounds(1, 0);
         while (d.P - bounds.back() > chunk + chunk / 2) bounds.push_back(bounds.back() + chunk);
@@ -1823,7 +1825,7 @@ int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns
         rc = stream_pattern_major(ctx, d, bytes, n_rows, bounds, [&](int64_t c0, int64_t np) -> int {
             const SweepGeom &G = c0 == last0 ? g_tail : g_main;
             const int64_t np4 = round_up(np, 4);
-            PHB_LAUNCH(tip_constants_kernel, dim3((unsigned)((np4 / 4 + 255) / 256)), dim3(256), d.stream,
+            PHB_LAUNCH(tip_constants_kernel, dim3((unsigned)((np4 + TIPC_SITES - 1) / TIPC_SITES)), dim3(TIPC_THREADS), d.stream,
                        d.tips.as<uint8_t>() + c0, d.P_pad, np4, d.leaf_rows.as<int32_t>(), (int)T.leaf_rows.size(), M,
                        d.leaf_ls.as<double>() + c0, d.inv_mask.as<uint8_t>() + c0);
             CHECK_LAUNCH();

@@ -68,6 +68,7 @@ static inline int __popc(unsigned v) { return __builtin_popcount(v); }
 static inline double __longlong_as_double(long long v) { double d; memcpy(&d, &v, 8); return d; }
 static inline int atomicAdd(int *p, int v) { int o = *p; *p += v; return o; }
 static inline unsigned atomicOr(unsigned *p, unsigned v) { unsigned o = *p; *p |= v; return o; }
+static inline int atomicAnd(int *p, int v) { int o = *p; *p &= v; return o; }
 using std::isfinite;
 using std::max;
 using std::min;
