@@ -1348,9 +1348,10 @@ namespace {
 // on copy_stream while chunk c-1 is packed (and whatever `after_chunk` enqueues runs) on d.stream.
 // bounds: ascending pattern offsets inside the shard, bounds.front() == 0, bounds.back() == d.P, every
 // interior bound a multiple of 64.
-template <class F>
-int stream_pattern_major(phb_ctx *ctx, Device &d, const uint8_t *bytes, int n_rows, const std::vector<int64_t> &bounds,
-                         F &&after_chunk)
+// `begin` puts the copies of the first two chunks on the wire and returns how many it issued, so that a
+// caller can do its host-side preparation (schedules, uploads) under them; the main loop then skips those.
+int stream_pattern_major_begin(phb_ctx *ctx, Device &d, const uint8_t *bytes, int n_rows, const std::vector<int64_t> &bounds,
+                               int *issued)
 {
     size_t max_bytes = 0;
     for (size_t c = 0; c + 1 < bounds.size(); ++c) max_bytes = std::max(max_bytes, (size_t)(bounds[c + 1] - bounds[c]) * n_rows);
@@ -1359,15 +1360,40 @@ int stream_pattern_major(phb_ctx *ctx, Device &d, const uint8_t *bytes, int n_ro
     // the staging buffers may still be read by packing kernels of an earlier call
     CU(cudaEventRecord(d.ev_free[0], d.stream));
     CU(cudaStreamWaitEvent(d.copy_stream, d.ev_free[0], 0));
+    *issued = 0;
+    for (size_t c = 0; c + 1 < bounds.size() && c < 2; ++c) {
+        const int buf = (int)(c & 1);
+        const int64_t c0 = bounds[c], np = bounds[c + 1] - c0;
+        if (np > 0) {
+            uint8_t *st = (buf ? d.staging2 : d.staging).as<uint8_t>();
+            CU(cudaMemcpyAsync(st, bytes + (size_t)(d.p_begin + c0) * n_rows, (size_t)np * n_rows, cudaMemcpyHostToDevice,
+                               d.copy_stream));
+            CU(cudaEventRecord(d.ev_copied[buf], d.copy_stream));
+        }
+        *issued = (int)c + 1;
+    }
+    return PHB_OK;
+}
+
+template <class F>
+int stream_pattern_major(phb_ctx *ctx, Device &d, const uint8_t *bytes, int n_rows, const std::vector<int64_t> &bounds,
+                         F &&after_chunk, int issued = -1)
+{
+    if (issued < 0) {
+        int rc0 = stream_pattern_major_begin(ctx, d, bytes, n_rows, bounds, &issued);
+        if (rc0) return rc0;
+    }
     for (size_t c = 0; c + 1 < bounds.size(); ++c) {
         const int buf = (int)(c & 1);
         const int64_t c0 = bounds[c], np = bounds[c + 1] - c0;
         if (np <= 0) continue;
         uint8_t *st = (buf ? d.staging2 : d.staging).as<uint8_t>();
-        if (c >= 2) CU(cudaStreamWaitEvent(d.copy_stream, d.ev_free[buf], 0));
-        CU(cudaMemcpyAsync(st, bytes + (size_t)(d.p_begin + c0) * n_rows, (size_t)np * n_rows, cudaMemcpyHostToDevice,
-                           d.copy_stream));
-        CU(cudaEventRecord(d.ev_copied[buf], d.copy_stream));
+        if ((int)c >= issued) {
+            if (c >= 2) CU(cudaStreamWaitEvent(d.copy_stream, d.ev_free[buf], 0));
+            CU(cudaMemcpyAsync(st, bytes + (size_t)(d.p_begin + c0) * n_rows, (size_t)np * n_rows, cudaMemcpyHostToDevice,
+                               d.copy_stream));
+            CU(cudaEventRecord(d.ev_copied[buf], d.copy_stream));
+        }
         CU(cudaStreamWaitEvent(d.stream, d.ev_copied[buf], 0));
         dim3 grid((unsigned)((np + PK_P - 1) / PK_P), (unsigned)((n_rows + PK_R - 1) / PK_R));
         PHB_LAUNCH(pack_pattern_major_tile_kernel, grid, dim3(256), d.stream, st, n_rows, np, d.tips.as<uint8_t>(), d.P_pad,
@@ -1776,44 +1802,68 @@ int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns
     int rc = shard_and_alloc(ctx, n_rows, n_patterns);
     if (rc) return rc;
     ctx->row_invalid_host.assign(std::max(n_rows, 1), 0);
+    // Chunks of whole passes of the widest CTA (1 by default: measured 195.2 / 199.9 / 207.9 ms end to end for
+    // 1 / 2 / 3 passes at 10k x 1M — the copy engine is the bottleneck, so smaller chunks only shorten the
+    // un-overlapped tail); a short remainder joins the last chunk, which gets its own geometry so that it does
+    // not end in a nearly empty pass.  The first two copies go on the wire BEFORE the host-side preparation
+    // (tree upload, sweep schedule, plans), which then costs nothing on top of them.
+    std::vector<std::vector<int64_t>> all_bounds(ctx->devs.size());
+    std::vector<int> issued(ctx->devs.size(), 0);
+    std::vector<int64_t> chunk_of(ctx->devs.size(), 0);
+    auto drain = [&](int code) { // the caller's buffer must not be in flight when an error goes back
+        for (Device &d : ctx->devs) {
+            cudaSetDevice(d.ordinal);
+            cudaStreamSynchronize(d.copy_stream);
+        }
+        return code;
+    };
+    for (size_t di = 0; di < ctx->devs.size(); ++di) {
+        Device &d = ctx->devs[di];
+        if (d.P == 0) continue;
+        CU(cudaSetDevice(d.ordinal));
+        const int n_sm = std::max(d.sm_count, 1);
+        const int q_max = (SW_MAX_CONSUMERS / M.n_clv) & ~3;
+        const int64_t pass = (int64_t)n_sm * 4 * q_max;
+        static const int chunk_passes = [] { const char *e = getenv("PHB_HOST_CHUNK_PASSES"); int v = e ? atoi(e) : 1; return v >= 1 && v <= 16 ? v : 1; }();
+        const int64_t chunk = round_up(chunk_passes * pass, 64);
+        std::vector<int64_t> &bounds = all_bounds[di];
+        bounds.assign(1, 0);
+        while (d.P - bounds.back() > chunk + chunk / 2) bounds.push_back(bounds.back() + chunk);
+        bounds.push_back(d.P);
+        chunk_of[di] = chunk;
+        rc = stream_pattern_major_begin(ctx, d, bytes, n_rows, bounds, &issued[di]);
+        if (rc) return drain(rc);
+    }
     if (!ctx->tree_uploaded) {
         rc = upload_tree(ctx);
-        if (rc) return rc;
+        if (rc) return drain(rc);
     }
     rc = ensure_sweep(ctx, M);
-    if (rc) return rc;
+    if (rc) return drain(rc);
     ctx->stats.clv_launches = 0;
     const SweepSched &S = ctx->sweep;
     Device &d0 = ctx->devs[0];
     d0.ev_used = 0;
     d0.ev_log.clear();
-    for (Device &d : ctx->devs) {
+    for (size_t di = 0; di < ctx->devs.size(); ++di) {
+        Device &d = ctx->devs[di];
         CU(cudaSetDevice(d.ordinal));
         if (d.P == 0) {
             *d.h_total = 0.0;
             continue;
         }
         rc = plan_device(ctx, d, M, false, false, true);
-        if (rc) return rc;
+        if (rc) return drain(rc);
         rc = upload_pad_and_mult(ctx, d, n_rows, multiplicity);
-        if (rc) return rc;
+        if (rc) return drain(rc);
         rc = launch_sweep_transition(ctx, d, M);
-        if (rc) return rc;
-        // chunks of whole passes of the widest CTA (1 by default: measured 195.2 / 199.9 / 207.9 ms end to end for
-        // 1 / 2 / 3 passes at 10k x 1M — the copy engine is the bottleneck, so smaller chunks only shorten the
-        // un-overlapped tail); a short remainder joins the last chunk, which gets its own geometry so that it
-        // does not end in a nearly empty pass
+        if (rc) return drain(rc);
         const int n_sm = std::max(d.sm_count, 1);
-        const int q_max = (SW_MAX_CONSUMERS / M.n_clv) & ~3;
-        const int64_t pass = (int64_t)n_sm * 4 * q_max;
-        static const int chunk_passes = [] { const char *e = getenv("PHB_HOST_CHUNK_PASSES"); int v = e ? atoi(e) : 1; return v >= 1 && v <= 16 ? v : 1; }();
-        const int64_t chunk = round_up(chunk_passes * pass, 64);
-        std::vector<int64_t> bounds(1, 0);
-        while (d.P - bounds.back() > chunk + chunk / 2) bounds.push_back(bounds.back() + chunk);
-        bounds.push_back(d.P);
+        const int64_t chunk = chunk_of[di];
+        const std::vector<int64_t> &bounds = all_bounds[di];
         SweepGeom g_main, g_tail;
         if (!g_main.plan(S, d.smem_optin, chunk, n_sm) || !g_tail.plan(S, d.smem_optin, d.P - bounds[bounds.size() - 2], n_sm))
-            return ctx->fail(PHB_ERR_INVALID_MODEL_PARAMETER, "sweep: %d CLV categories do not fit one CTA", M.n_clv);
+            return drain(ctx->fail(PHB_ERR_INVALID_MODEL_PARAMETER, "sweep: %d CLV categories do not fit one CTA", M.n_clv));
         size_t n_part_max = 0;
         for (size_t c = 0; c + 1 < bounds.size(); ++c) {
             const SweepGeom &G = c + 2 == bounds.size() ? g_tail : g_main;
@@ -1832,8 +1882,8 @@ int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns
             int r2 = launch_sweep_range(ctx, d, M, G, c0, np, part_off);
             part_off += (size_t)((np + 4 * G.Q - 1) / (4 * G.Q));
             return r2;
-        });
-        if (rc) return rc;
+        }, issued[di]);
+        if (rc) return drain(rc);
         d.tip_constants_valid = true;
         d.tip_constants_rows = T.leaf_rows;
         rc = launch_sweep_reduce(ctx, d, part_off);
