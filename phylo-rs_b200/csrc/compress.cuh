@@ -142,16 +142,43 @@ __global__ void pattern_index_kernel(const uint32_t *__restrict__ rep, const uin
     }
 }
 
-// unique columns [p0, p0 + np) -> tip codes of one device shard: tips[row][dst_off + (p - p0)]
-__global__ void gather_patterns_kernel(const uint8_t *__restrict__ raw, int64_t pitch, const uint32_t *__restrict__ rep_list,
-                                       int64_t p0, int64_t np, uint8_t *__restrict__ tips, int64_t P_pad, int64_t dst_off,
-                                       int *__restrict__ row_invalid)
+// unique columns [p0, p0 + np) -> tip codes of one device shard: tips[row][dst_off + (p - p0)].
+// One thread = 4 consecutive patterns x GATHER_ROWS rows: the four column indices are read once and stay in
+// registers, every row costs four byte loads (neighbouring threads read neighbouring columns whenever the
+// unique columns are mostly in site order) and one 32-bit store.  P_pad and dst_off are multiples of 4.
+constexpr int GATHER_ROWS = 16;
+__global__ void __launch_bounds__(256)
+gather_patterns_kernel(const uint8_t *__restrict__ raw, int64_t pitch, const uint32_t *__restrict__ rep_list, int64_t p0,
+                       int64_t np, int n_rows, uint8_t *__restrict__ tips, int64_t P_pad, int64_t dst_off,
+                       int *__restrict__ row_invalid)
 {
-    const int r = blockIdx.y;
-    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < np; p += (int64_t)gridDim.x * blockDim.x) {
-        const uint8_t code = encode_byte(raw[(int64_t)r * pitch + rep_list[p0 + p]]);
-        tips[(int64_t)r * P_pad + dst_off + p] = code;
-        if (code == CODE_INVALID) row_invalid[r] = 1;
+    __shared__ uint8_t lut[256]; // byte -> tip code (blockDim.x == 256)
+    lut[threadIdx.x] = encode_byte((uint8_t)threadIdx.x);
+    __syncthreads();
+    const int64_t p = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (p >= np) return;
+    const int n = (int)min((int64_t)4, np - p);
+    uint32_t col[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) col[k] = rep_list[p0 + p + (k < n ? k : 0)];
+    const int r0 = blockIdx.y * GATHER_ROWS, r1 = min(n_rows, r0 + GATHER_ROWS);
+    for (int r = r0; r < r1; ++r) {
+        const uint8_t *src = raw + (int64_t)r * pitch;
+        uint32_t c[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) c[k] = lut[src[col[k]]];
+        uint8_t *dst = tips + (int64_t)r * P_pad + dst_off + p;
+        bool bad = false;
+        if (n == 4) {
+            *reinterpret_cast<uint32_t *>(dst) = c[0] | (c[1] << 8) | (c[2] << 16) | (c[3] << 24);
+            bad = c[0] == CODE_INVALID || c[1] == CODE_INVALID || c[2] == CODE_INVALID || c[3] == CODE_INVALID;
+        } else {
+            for (int k = 0; k < n; ++k) {
+                dst[k] = (uint8_t)c[k];
+                bad |= c[k] == CODE_INVALID;
+            }
+        }
+        if (bad) row_invalid[r] = 1;
     }
 }
 

@@ -152,6 +152,9 @@ pack_pattern_major_tile_kernel(const uint8_t *__restrict__ in, int n_rows, int64
                                int *__restrict__ row_invalid)
 {
     __shared__ uint8_t tile[PK_P][PK_R + 4];
+    __shared__ uint8_t lut[256]; // byte -> tip code (blockDim.x == 256)
+    lut[threadIdx.x] = encode_byte((uint8_t)threadIdx.x);
+    __syncthreads();
     const int64_t p0 = (int64_t)blockIdx.x * PK_P;
     const int r0 = blockIdx.y * PK_R;
     for (int idx = threadIdx.x; idx < PK_P * PK_R; idx += 256) {
@@ -159,7 +162,7 @@ pack_pattern_major_tile_kernel(const uint8_t *__restrict__ in, int n_rows, int64
         const int64_t p = p0 + j;
         const int row = r0 + r;
         uint8_t code = CODE_GAP;
-        if (p < n_patterns && row < n_rows) code = encode_byte(in[p * n_rows + row]);
+        if (p < n_patterns && row < n_rows) code = lut[in[p * n_rows + row]];
         tile[j][r] = code;
     }
     __syncthreads();

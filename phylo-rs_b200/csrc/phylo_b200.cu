@@ -20,6 +20,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <chrono>
 #include <vector>
 
 using namespace phb;
@@ -1517,6 +1518,15 @@ static int32_t compress_impl(phb_ctx *ctx, int32_t n_rows, int64_t width, const 
     }
     Device &d0 = ctx->devs[0];
     CU(cudaSetDevice(d0.ordinal));
+    static const bool trace = getenv("PHB_COMPRESS_TRACE") != nullptr; // stage wall times on stderr
+    auto t_prev = std::chrono::steady_clock::now();
+    auto lap = [&](const char *what) {
+        if (!trace) return;
+        cudaStreamSynchronize(d0.stream);
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[phb compress] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_prev).count());
+        t_prev = now;
+    };
     const int64_t pitch = round_up(width, 16) + 16; // 8-site loads of the last thread stay inside the row
     const int rows_alloc = std::max(n_rows, 1);
     DevBuf raw, hash, keys, sites, sites2, head, gid, gstart, rep, isrep, size_at, pid, replist, s2p, mult, temp, flag, stage;
@@ -1546,6 +1556,7 @@ static int32_t compress_impl(phb_ctx *ctx, int32_t n_rows, int64_t width, const 
     CU(flag.ensure(sizeof(unsigned int)));
     const size_t temp_bytes = compress_temp_bytes(width);
     CU(temp.ensure(temp_bytes));
+    lap("allocations");
     // 1. bytes -> device, row chunk by row chunk on the copy stream; the first hash pass folds each chunk as it lands
     CU(cudaEventRecord(d0.ev_free[0], d0.stream));
     CU(cudaStreamWaitEvent(d0.copy_stream, d0.ev_free[0], 0));
@@ -1582,6 +1593,7 @@ static int32_t compress_impl(phb_ctx *ctx, int32_t n_rows, int64_t width, const 
                        width, key, mul, first ? 1 : 0, last ? 1 : 0, hash.as<uint64_t>());
             CHECK_LAUNCH();
         }
+        lap("copy + column hash");
         // 2. stable sort of (hash, site); groups of equal hash
         PHB_LAUNCH(iota_kernel, dim3(w_grid), dim3(256), d0.stream, sites.as<uint32_t>(), width);
         CHECK_LAUNCH();
@@ -1596,6 +1608,7 @@ static int32_t compress_impl(phb_ctx *ctx, int32_t n_rows, int64_t width, const 
         uint32_t n_groups = 0;
         CU(cudaMemcpyAsync(&n_groups, gid.as<uint32_t>() + (W - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, d0.stream));
         CU(cudaStreamSynchronize(d0.stream));
+        lap("sort + groups");
         PHB_LAUNCH(group_rep_kernel, dim3(w_grid), dim3(256), d0.stream, sites2.as<uint32_t>(), gid.as<uint32_t>(),
                    gstart.as<uint32_t>(), n_groups, width, rep.as<uint32_t>(), isrep.as<uint32_t>(), size_at.as<uint32_t>());
         CHECK_LAUNCH();
@@ -1610,6 +1623,7 @@ static int32_t compress_impl(phb_ctx *ctx, int32_t n_rows, int64_t width, const 
         unsigned int mismatch = 0;
         CU(cudaMemcpyAsync(&mismatch, flag.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, d0.stream));
         CU(cudaStreamSynchronize(d0.stream));
+        lap("verification");
         if (mismatch) { // two different columns share a 64-bit hash: hash again under another key
             if (attempt == 3) return ctx->fail(PHB_ERR_NUMERICAL_INSTABILITY, "compress_columns: hash collisions under 4 keys");
             continue;
@@ -1627,10 +1641,12 @@ static int32_t compress_impl(phb_ctx *ctx, int32_t n_rows, int64_t width, const 
     if (multiplicity)
         CU(cudaMemcpyAsync(multiplicity, mult.p, sizeof(uint64_t) * (size_t)P, cudaMemcpyDeviceToHost, d0.stream));
     CU(cudaStreamSynchronize(d0.stream));
+    lap("pattern ids + results to host");
     // 5. the unique columns become the context's alignment: tip codes [row][pattern] per device shard
     int rc = shard_and_alloc(ctx, n_rows, P);
     if (rc) return rc;
     ctx->row_invalid_host.assign(std::max(n_rows, 1), 0);
+    lap("shard_and_alloc");
     for (Device &d : ctx->devs) {
         const bool same = &d == &d0;
         CU(cudaSetDevice(d0.ordinal));
@@ -1646,11 +1662,12 @@ static int32_t compress_impl(phb_ctx *ctx, int32_t n_rows, int64_t width, const 
             CU(cudaMemsetAsync(dst_flags, 0, sizeof(int) * (size_t)rows_alloc, d0.stream));
             CU(cudaStreamSynchronize(d.stream)); // shard_and_alloc's memsets on the destination
         }
-        for (int r0 = 0; r0 < n_rows && d.P > 0; r0 += 32768) {
-            const int nr = std::min(32768, n_rows - r0);
-            dim3 grid((unsigned)std::min<int64_t>((d.P + 255) / 256, 4096), (unsigned)nr);
+        const int rows_per_launch = 32768 * GATHER_ROWS;
+        for (int r0 = 0; r0 < n_rows && d.P > 0; r0 += rows_per_launch) {
+            const int nr = std::min(rows_per_launch, n_rows - r0);
+            dim3 grid((unsigned)((d.P + 1023) / 1024), (unsigned)((nr + GATHER_ROWS - 1) / GATHER_ROWS));
             PHB_LAUNCH(gather_patterns_kernel, grid, dim3(256), d0.stream, raw.as<uint8_t>() + (size_t)r0 * pitch, pitch,
-                       replist.as<uint32_t>(), d.p_begin, d.P, dst_tips + (size_t)r0 * d.P_pad, d.P_pad, (int64_t)0,
+                       replist.as<uint32_t>(), d.p_begin, d.P, nr, dst_tips + (size_t)r0 * d.P_pad, d.P_pad, (int64_t)0,
                        dst_flags + r0);
             CHECK_LAUNCH();
         }
@@ -1669,6 +1686,7 @@ static int32_t compress_impl(phb_ctx *ctx, int32_t n_rows, int64_t width, const 
         }
         CU(cudaStreamSynchronize(d0.stream));
     }
+    lap("gather to tip codes");
     rc = gather_row_flags(ctx, n_rows);
     if (rc) return rc;
     *n_patterns = P;
