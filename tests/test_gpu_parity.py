@@ -367,6 +367,84 @@ def test_full_size_properties_config2(gpu_lib):
     assert abs(tot2 - 2 * tot) <= 1e-12 * abs(tot2)
 
 
+def test_full_size_properties_config3(gpu_lib):
+    """configs[2] at FULL size (10,000 taxa x 1M site patterns, GTR+I+G4 — the bench workload) through
+    size-independent properties: the device-simulated alignment scored whole, in 4 virtual ranks (the multi-GPU
+    shard arithmetic on one device) and with the HBM-resident level kernels under their tiling must give the same
+    per-pattern values; the total is the sum of the per-pattern values; the first 256 patterns are checked against
+    the oracle."""
+    case = workloads.make_case(10_000, 8, model="gtr_i_g4", seed=0x5EED0003)
+    P = 1_000_000
+    with capi.Context(library=gpu_lib) as ctx:
+        workloads.load_into(ctx, case)
+        ctx.simulate_alignment(P, seed=0xB200)
+        tot, per = ctx.log_likelihood(per_pattern=True)
+        assert ctx.stats()["sweep_ops"] == 9999
+        assert ctx.log_likelihood() == tot  # re-evaluation is bit-reproducible
+        pats = ctx.get_alignment(0, 256)
+    assert np.all(np.isfinite(per)) and abs(tot - float(np.sum(per))) <= 1e-11 * abs(tot)
+    ft = dict(case.ft)
+    leaves = np.where(ft["child_off"][1:] == ft["child_off"][:-1])[0]
+    lr = np.full(ft["n_nodes"], -1, np.int32)
+    lr[leaves] = np.arange(len(leaves))
+    ft["leaf_row"] = lr
+    _ref, ref_per = oracle.log_likelihood_flat(ft, case.model, pats, n_threads=8)
+    assert np.max(np.abs(per[:256] - ref_per)) <= 1e-8
+    with capi.Context(devices=[0, 0, 0, 0], library=gpu_lib) as ctx:
+        workloads.load_into(ctx, case)
+        ctx.simulate_alignment(P, seed=0xB200)
+        tot4, per4 = ctx.log_likelihood(per_pattern=True)
+    assert np.array_equal(per4, per) and abs(tot4 - tot) <= 1e-12 * abs(tot)
+    with capi.Context(library=gpu_lib, flags=capi.FLAG_LEVEL_KERNELS) as ctx:
+        workloads.load_into(ctx, case)
+        ctx.simulate_alignment(P, seed=0xB200)
+        tot_l, per_l = ctx.log_likelihood(per_pattern=True)
+        assert ctx.stats()["n_tiles"] >= 2
+    assert np.max(np.abs(per_l - per)) < 1e-8 and abs(tot_l - tot) <= 1e-11 * abs(tot)
+
+
+def test_full_size_properties_config4(gpu_lib):
+    """configs[3] at FULL size (marginal ASR, GTR+G4, 5,000 taxa x 500k site patterns) through size-independent
+    properties: the device-simulated alignment reconstructed whole (tiled by the CLV budget) and in 3 virtual
+    ranks gives identical states and per-pattern values; leaves keep their observed state; the joint
+    reconstruction agrees with it at the leaves too; the first 128 patterns match the oracle state for state."""
+    case = workloads.make_case(5_000, 8, model="gtr_g4", seed=0x5EED0004)
+    P = 500_000
+    code = np.full(256, 255, np.uint8)
+    code[[ord(c) for c in "ACGT"]] = np.arange(4)
+    with capi.Context(library=gpu_lib) as ctx:
+        workloads.load_into(ctx, case)
+        ctx.simulate_alignment(P, seed=0xA5A5)
+        tot, states, _ = ctx.marginal_asr(False)
+        per = ctx.per_pattern()
+        assert ctx.stats()["n_tiles"] >= 2
+        assert abs(ctx.log_likelihood() - tot) <= 1e-11 * abs(tot)
+        pats = ctx.get_alignment(0, 128)
+        sample = ctx.get_alignment(250_000, 4096)
+        jtot, jstates = ctx.joint_asr()
+    assert states.shape == (case.ft["n_nodes"], P) and states.max() <= 3
+    ft = dict(case.ft)
+    leaves = np.where(ft["child_off"][1:] == ft["child_off"][:-1])[0]
+    lr = np.full(ft["n_nodes"], -1, np.int32)
+    lr[leaves] = np.arange(len(leaves))
+    ft["leaf_row"] = lr
+    obs = code[sample].T  # [row][pattern]; the simulator emits A, C, G, T only
+    assert obs.max() <= 3
+    assert np.array_equal(states[leaves, 250_000:254_096], obs)
+    assert np.array_equal(jstates[leaves, 250_000:254_096], obs) and jtot < tot
+    ref_tot, ref_per, ref_states, _ = oracle.marginal_asr_flat(ft, case.model, pats, None, want_posteriors=False, n_threads=8)
+    assert np.max(np.abs(per[:128] - ref_per)) <= 1e-8
+    assert np.array_equal(states[:, :128], ref_states)
+    del jstates
+    with capi.Context(devices=[0, 0, 0], library=gpu_lib) as ctx:
+        workloads.load_into(ctx, case)
+        ctx.simulate_alignment(P, seed=0xA5A5)
+        tot3, states3, _ = ctx.marginal_asr(False)
+        per3 = ctx.per_pattern()
+    assert np.array_equal(per3, per) and abs(tot3 - tot) <= 1e-12 * abs(tot)
+    assert np.array_equal(states3, states)
+
+
 def test_fused_host_call(gpu_lib):
     """phb_log_likelihood_host: chunked H2D copy overlapped with pack + sweep == the two-call path (several chunks)."""
     case = workloads.make_case(40, 230_000, model="gtr_i_g4", seed=31)
