@@ -437,6 +437,12 @@ struct NniEdgeJob {
     int32_t pad[3];
 };
 
+// 2^k for k <= 0 (0 below the normal range: such a term is far below one ulp of the sum)
+__device__ __forceinline__ double pow2_nonpositive(int k)
+{
+    return k < -1022 ? 0.0 : __longlong_as_double((long long)(1023 + k) << 52);
+}
+
 template <int NC>
 __global__ void __launch_bounds__(nni_threads(NC), 2)
 nni_edge_kernel(const NniEdgeJob *__restrict__ jobs, int n_jobs, ModelDev M, const double *__restrict__ Pmat,
@@ -447,7 +453,8 @@ nni_edge_kernel(const NniEdgeJob *__restrict__ jobs, int n_jobs, ModelDev M, con
 {
     constexpr int BS = nni_block_sites(NC), NT = nni_threads(NC);
     __shared__ __align__(16) double sP[4 * NC * 16]; // k0, k1, s, v
-    __shared__ double sLL[2][NC][BS];
+    __shared__ double sV[2][NC][BS]; // root sums per (move, category, site) and their power-of-two exponents:
+    __shared__ int sE[2][NC][BS];    // true value = sV * 2^-sE
     const int ji = blockIdx.x % n_jobs;
     const int sb = blockIdx.x / n_jobs;
     const NniEdgeJob jb = jobs[ji];
@@ -489,7 +496,6 @@ nni_edge_kernel(const NniEdgeJob *__restrict__ jobs, int n_jobs, ModelDev M, con
         nni_apply_sib(sP + (1 * NC + cat) * 16, d1, jb.k1_is_tip != 0, c1);
         nni_apply_sib(sP + (2 * NC + cat) * 16, ds, jb.s_is_tip != 0, cs);
         const double2 *Pv = reinterpret_cast<const double2 *>(sP + (3 * NC + cat) * 16);
-        const double lsx = leaf_ls[site], lsy = leaf_ls[site + 1];
 #pragma unroll
         for (int mvi = 0; mvi < 2; ++mvi) {
             // mvi = 0: k0 moves up, k1 stays;  mvi = 1: k1 moves up, k0 stays
@@ -513,45 +519,51 @@ nni_edge_kernel(const NniEdgeJob *__restrict__ jobs, int n_jobs, ModelDev M, con
                 mx += w[i].x * (tx * up[i].x);
                 my += w[i].y * (ty * up[i].y);
             }
-            sLL[mvi][cat][local] = M.ln_weights[cat_model] + log(mx) + (lsx - (double)ex * LN2);
-            sLL[mvi][cat][local + 1] = M.ln_weights[cat_model] + log(my) + (lsy - (double)ey * LN2);
+            sV[mvi][cat][local] = M.weights[cat_model] * mx;
+            sV[mvi][cat][local + 1] = M.weights[cat_model] * my;
+            sE[mvi][cat][local] = ex;
+            sE[mvi][cat][local + 1] = ey;
         }
     }
     __syncthreads();
+    // Categories are mixed in the linear domain after aligning their exponents — one logarithm per site and move
+    // instead of a log per category plus a log-sum-exp:  ln( sum_c w_c v_c 2^(e_min - e_c) ) - e_min ln 2 + leaf_ls.
+    // The rate-0 (+I) categories enter with exponent 0 and value weight x stationary mass of the shared states.
     double contrib0 = 0.0, contrib1 = 0.0;
     for (int q = threadIdx.x; q < BS; q += NT) {
         const int64_t sq = (int64_t)sb * BS + q;
         if (sq >= tile_len) continue;
-        double inv_ll = 0.0;
-        bool have_inv = false;
-        for (int c = 0; c < M.n_cat; ++c)
-            if (M.clv_idx[c] < 0 && !have_inv) { // all rate-0 categories share the mass; weights differ
-                have_inv = true;
-                double mass = 0.0;
-                const uint32_t m = inv_mask[sq];
+        double inv_w = 0.0;
+        if (M.n_clv < M.n_cat) {
+            double mass = 0.0;
+            const uint32_t m = inv_mask[sq];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) mass += M.pi[i] * (((m >> i) & 1u) ? 1.0 : 0.0);
-                inv_ll = log(mass) + leaf_ls[sq];
-            }
+            for (int i = 0; i < 4; ++i) mass += M.pi[i] * (((m >> i) & 1u) ? 1.0 : 0.0);
+            for (int c = 0; c < M.n_cat; ++c)
+                if (M.clv_idx[c] < 0) inv_w += M.weights[c] * mass;
+        }
+        const double ls = leaf_ls[sq], mu = mult[sq];
 #pragma unroll
         for (int mvi = 0; mvi < 2; ++mvi) {
-            double lls[MAX_CAT];
-            double mxl = -INFINITY;
-            for (int c = 0; c < M.n_cat; ++c) {
-                const int cc = M.clv_idx[c];
-                const double ll = cc >= 0 ? sLL[mvi][cc][q] : M.ln_weights[c] + inv_ll;
-                lls[c] = ll;
-                mxl = fmax(mxl, ll);
+            int e_min = 0x7fffffff;
+#pragma unroll
+            for (int cc = 0; cc < NC; ++cc)
+                if (!(sV[mvi][cc][q] <= 0.0)) e_min = min(e_min, sE[mvi][cc][q]); // positive or NaN
+            if (inv_w > 0.0) e_min = min(e_min, 0);
+            double acc = inv_w, site_ll;
+            if (e_min == 0x7fffffff) { // nothing positive: ln 0 = -inf (a NaN propagates)
+#pragma unroll
+                for (int cc = 0; cc < NC; ++cc) acc += sV[mvi][cc][q];
+                site_ll = log(acc) + ls;
+            } else {
+                acc = inv_w > 0.0 ? inv_w * pow2_nonpositive(e_min) : 0.0; // e_min <= 0 whenever inv_w > 0
+#pragma unroll
+                for (int cc = 0; cc < NC; ++cc)
+                    if (!(sV[mvi][cc][q] <= 0.0)) acc += sV[mvi][cc][q] * pow2_nonpositive(e_min - sE[mvi][cc][q]);
+                site_ll = log(acc) + (ls - (double)e_min * LN2);
             }
-            double site_ll;
-            if (!isfinite(mxl)) site_ll = mxl;
-            else {
-                double acc = 0.0;
-                for (int c = 0; c < M.n_cat; ++c) acc += exp(lls[c] - mxl);
-                site_ll = mxl + log(acc);
-            }
-            if (mvi) contrib1 += mult[sq] * site_ll;
-            else contrib0 += mult[sq] * site_ll;
+            if (mvi) contrib1 += mu * site_ll;
+            else contrib0 += mu * site_ll;
         }
     }
     const double r0 = block_reduce_sum(contrib0);
