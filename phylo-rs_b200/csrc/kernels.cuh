@@ -611,7 +611,7 @@ struct DownChild {
     int32_t node;  // dense id: P matrix index and row of the states output
     int32_t src;   // CLV slot (internal) or alignment row (leaf)
     int32_t is_tip;
-    int32_t pad;
+    int32_t pad;   // 1: internal node with an internal child (the NNI upper pass computes partials only for these)
 };
 
 __device__ __forceinline__ int argmax_last(const double (&m)[4])

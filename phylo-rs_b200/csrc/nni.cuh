@@ -373,7 +373,9 @@ upper_level_kernel(const DownOp *__restrict__ ops, int n_ops, const DownChild *_
     const DownOp op = ops[opi];
     if (op.child_end - op.child_begin != 2) return; // binary trees only (the host checks)
     const DownChild c0 = kids[op.child_begin], c1 = kids[op.child_begin + 1];
-    if (c0.is_tip && c1.is_tip) return;              // no internal child: nothing to produce
+    // upper_v is read by the edges v -> (internal child) and by v's own children's partials: a child without an
+    // internal child of its own (a tip, a cherry) needs none
+    if (!c0.pad && !c1.pad) return;
     const int cat_model = M.cat_of_clv[cat];
     const size_t stride2 = tile_pad / 2;
     const size_t cat_off = (size_t)cat * 4 * tile_pad + (size_t)site;
@@ -393,7 +395,7 @@ upper_level_kernel(const DownOp *__restrict__ ops, int n_ops, const DownChild *_
 #pragma unroll
     for (int which = 0; which < 2; ++which) {
         const DownChild me = which ? c1 : c0, sib = which ? c0 : c1;
-        if (me.is_tip) continue;
+        if (!me.pad) continue;
         double p[16];
         double2 sv[4];
         int2 e = eb;

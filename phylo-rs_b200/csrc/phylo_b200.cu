@@ -213,7 +213,10 @@ struct TreeSched {
                     dc.node = c;
                     dc.is_tip = slot[c] < 0;
                     dc.src = dc.is_tip ? leaf_row[c] : slot[c];
-                    dc.pad = 0;
+                    dc.pad = 0; // 1: internal child with an internal child of its own (the only upper partials ever read)
+                    if (!dc.is_tip)
+                        for (int k2 = child_off[c]; k2 < child_off[c + 1]; ++k2)
+                            if (slot[children[k2]] >= 0) dc.pad = 1;
                     dkids.push_back(dc);
                 }
                 o.child_end = (int)dkids.size();
