@@ -361,7 +361,8 @@ __global__ void __launch_bounds__(CLV_THREADS, MINB)
 upper_level_kernel(const DownOp *__restrict__ ops, int n_ops, const DownChild *__restrict__ kids, int root_node, ModelDev M,
                    const double *__restrict__ Pmat, const double *__restrict__ clv, double *__restrict__ upper,
                    size_t slot_stride, size_t tile_pad, int tile_len, int blocks_per_row, const int *__restrict__ exps,
-                   int *__restrict__ uexps, const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off)
+                   int *__restrict__ uexps, const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off,
+                   const uint8_t *__restrict__ need /* per dense node: on the path from a scored edge to the root; null = all */)
 {
     const int sb = blockIdx.x % blocks_per_row;
     const int rest = blockIdx.x / blocks_per_row;
@@ -375,7 +376,8 @@ upper_level_kernel(const DownOp *__restrict__ ops, int n_ops, const DownChild *_
     const DownChild c0 = kids[op.child_begin], c1 = kids[op.child_begin + 1];
     // upper_v is read by the edges v -> (internal child) and by v's own children's partials: a child without an
     // internal child of its own (a tip, a cherry) needs none
-    if (!c0.pad && !c1.pad) return;
+    const bool want0 = c0.pad && (!need || need[c0.node]), want1 = c1.pad && (!need || need[c1.node]);
+    if (!want0 && !want1) return;
     const int cat_model = M.cat_of_clv[cat];
     const size_t stride2 = tile_pad / 2;
     const size_t cat_off = (size_t)cat * 4 * tile_pad + (size_t)site;
@@ -395,7 +397,7 @@ upper_level_kernel(const DownOp *__restrict__ ops, int n_ops, const DownChild *_
 #pragma unroll
     for (int which = 0; which < 2; ++which) {
         const DownChild me = which ? c1 : c0, sib = which ? c0 : c1;
-        if (!me.pad) continue;
+        if (!(which ? want1 : want0)) continue;
         double p[16];
         double2 sv[4];
         int2 e = eb;

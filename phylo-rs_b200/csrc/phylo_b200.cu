@@ -241,7 +241,7 @@ struct Device {
     DevBuf tips, mult, leaf_ls, inv_mask, per_pattern, row_invalid, Pmat, blen, clv, scale, cat_ll,
         partials, total, ops, gops, gkids, dops, dkids, leaf_rows, states, posteriors, staging,
         sim_pre, sim_parent, sim_depth, sim_leafrow, sim_stack, scratch, sw_descs, sw_blocks, sw_stream, sw_gstack,
-        sw_err, sw_ops, uops, ukids, lnP, jbest, nni_upper, nni_uexps, nni_jobs, nni_rows, nni_exps, nni_partials, nni_totals, nni_moves, nni_steps;
+        sw_err, sw_ops, uops, ukids, lnP, jbest, nni_upper, nni_uexps, nni_jobs, nni_rows, nni_exps, nni_partials, nni_totals, nni_moves, nni_steps, nni_need;
     bool sweep_uploaded = false;
     int sm_count = 0;
     size_t smem_optin = 0;
@@ -1042,6 +1042,18 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
             }
         }
     }
+    // upper partials are read at the upper end p of a scored edge and, recursively, by p's own partials:
+    // only the ancestors of the scored edges get them
+    std::vector<uint8_t> need_upper(std::max(T.n, 1), 0);
+    if (use_upper)
+        for (int m : order)
+            for (int g = T.parent[node_id[m]]; g != T.root && g >= 0 && !need_upper[g]; g = T.parent[g]) need_upper[g] = 1;
+    bool need_all = true; // every node that could carry upper partials is wanted: the kernel skips the lookup
+    for (int v = 0; v < T.n && use_upper; ++v) {
+        if (v == T.root || T.slot[v] < 0 || need_upper[v]) continue;
+        for (int k = T.child_off[v]; k < T.child_off[v + 1]; ++k)
+            if (T.slot[T.children[k]] >= 0) need_all = false;
+    }
     phb_stats &S = ctx->stats;
     S.nni_path_moves = (int)moves.size();
     S.nni_path_steps = use_upper ? (int64_t)jobs.size() * 3 : (int64_t)steps.size();
@@ -1091,6 +1103,8 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
             CU(d.nni_uexps.ensure(sizeof(int) * (size_t)M.n_clv * tile_pad * (size_t)T.n_internal));
             CU(d.nni_jobs.ensure(sizeof(NniEdgeJob) * jobs.size()));
             CU(d.nni_rows.ensure(sizeof(int32_t) * job_rows.size()));
+            CU(d.nni_need.ensure(need_upper.size()));
+            CU(cudaMemcpyAsync(d.nni_need.p, need_upper.data(), need_upper.size(), cudaMemcpyHostToDevice, d.stream));
             CU(cudaMemcpyAsync(d.nni_jobs.p, jobs.data(), sizeof(NniEdgeJob) * jobs.size(), cudaMemcpyHostToDevice, d.stream));
             CU(cudaMemcpyAsync(d.nni_rows.p, job_rows.data(), sizeof(int32_t) * job_rows.size(), cudaMemcpyHostToDevice, d.stream));
         }
@@ -1140,7 +1154,7 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
     PHB_LAUNCH(upper_level_kernel<MINB>, dim3((unsigned)((int64_t)nb * M.n_clv * bpr)), dim3(CLV_THREADS), d.stream,   \
                d.dops.as<DownOp>() + T.dlevel_off[dl], nb, d.dkids.as<DownChild>(), T.root, M, d.Pmat.as<double>(),    \
                d.clv.as<double>(), d.nni_upper.as<double>(), slot_stride, tile_pad, len, bpr, d.nni_exps.as<int>(),    \
-               d.nni_uexps.as<int>(), d.tips.as<uint8_t>(), d.P_pad, off)
+               d.nni_uexps.as<int>(), d.tips.as<uint8_t>(), d.P_pad, off, need_all ? (const uint8_t *)nullptr : d.nni_need.as<uint8_t>())
                     if (upper_minb == 2) PHB_UPPER_LAUNCH(2);
                     else if (upper_minb == 4) PHB_UPPER_LAUNCH(4);
                     else PHB_UPPER_LAUNCH(3);
@@ -1293,7 +1307,7 @@ void phb_ctx_destroy(phb_ctx *ctx)
                           &d.dkids, &d.leaf_rows, &d.states, &d.posteriors, &d.staging, &d.sim_pre, &d.sim_parent,
                           &d.sim_depth, &d.sim_leafrow, &d.sim_stack, &d.scratch, &d.sw_descs, &d.sw_blocks,
                           &d.sw_stream, &d.sw_gstack, &d.sw_err, &d.sw_ops, &d.uops, &d.ukids, &d.lnP, &d.jbest,
-                          &d.nni_upper, &d.nni_uexps, &d.nni_jobs, &d.nni_rows, &d.nni_exps, &d.nni_partials, &d.nni_totals, &d.nni_moves, &d.nni_steps};
+                          &d.nni_upper, &d.nni_uexps, &d.nni_jobs, &d.nni_rows, &d.nni_exps, &d.nni_partials, &d.nni_totals, &d.nni_moves, &d.nni_steps, &d.nni_need};
         for (DevBuf *b : bufs) b->release();
         for (auto &ep : d.ev_pool) {
             cudaEventDestroy(ep.a);
