@@ -48,8 +48,9 @@ extern "C" {
 #define PHB_FLAG_LITERAL_INVARIANT (1ull << 0)
 /* Record CUDA events around every phase of an evaluation (see phb_get_stats). */
 #define PHB_FLAG_TIMING (1ull << 1)
-/* Log-likelihood through the level-batched kernels that keep every CLV in HBM (the marginal-ASR up
- * pass always uses them) instead of the fused on-chip sweep. */
+/* Level-batched kernels that keep every CLV in HBM, for the log-likelihood AND for the up pass of
+ * phb_marginal_asr, instead of the fused on-chip sweep (default log-likelihood path) and its storing
+ * variant (default marginal-ASR up pass).  Same results; kept for cross-checking. */
 #define PHB_FLAG_LEVEL_KERNELS (1ull << 2)
 /* phb_score_nni rescores every neighbour from scratch (the reference's caller loop) instead of walking
  * v -> root against the cached CLVs of the base tree; for cross-checking the two. */

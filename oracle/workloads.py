@@ -109,6 +109,35 @@ def make_case(n_taxa, n_sites, model="gtr_g4", seed=1, ambiguity=0.0, compress=F
     return Case(tree, ft, m, model, np.ascontiguousarray(pats), mult, leaf_order)
 
 
+def polytomy_case(k, depth, n_sites, model="gtr_g4", seed=1, blen=0.9):
+    """A root with k children.  depth >= 2: every child is a `depth`-leaf caterpillar (deep subtrees under a
+    high-arity node: each child's CLV carries a large scale); depth == 1: a star of k tips
+    (the reference's own product of k contributions underflows for k >~ 460: likelihood.rs:123-125).
+    All branches `blen`, i.i.d. uniform ACGT columns."""
+    from . import parse_newick
+
+    names = []
+
+    def cat(j):
+        if depth == 1:
+            names.append(f"s{j}")
+            return f"s{j}:{blen}"
+        names.append(f"c{j}_0")
+        names.append(f"c{j}_1")
+        s = f"(c{j}_0:{blen},c{j}_1:{blen})"
+        for i in range(2, depth):
+            names.append(f"c{j}_{i}")
+            s = f"({s}:{blen},c{j}_{i}:{blen})"
+        return s + f":{blen}"
+
+    nwk = "(" + ",".join(cat(j) for j in range(k)) + ");"
+    tree = parse_newick(nwk)
+    rng = np.random.default_rng(seed)
+    ft = flatten_fast(tree, names)
+    pats = np.frombuffer(b"ACGT", np.uint8)[rng.integers(4, size=(n_sites, len(names)))]
+    return Case(tree, ft, make_model(model), model, np.ascontiguousarray(pats), np.ones(n_sites, np.uint64), names)
+
+
 def flatten_fast(tree, leaf_order):
     """refhost.flatten with a dict for the name lookup (same result when labels are unique)."""
     by_name = {}

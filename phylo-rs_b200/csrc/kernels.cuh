@@ -455,8 +455,24 @@ clv_update_level_kernel(const NodeOp *__restrict__ ops, int n_ops, ModelDev M,
     }
 }
 
-// Generic arity (1 child, or > 2 children): running product, rescaled after every child so a
-// polytomy cannot underflow between rescales.
+// power-of-two normalisation of one site's four states to a maximum in [1,2); returns the exponent added
+__device__ __forceinline__ int normalize_site(double &v0, double &v1, double &v2, double &v3)
+{
+    const int h = max(max(__double2hiint(v0), __double2hiint(v1)), max(__double2hiint(v2), __double2hiint(v3)));
+    if (h <= 0) return 0; // zero / negative maxima are left alone (Profile::scale's max_val <= 0 return)
+    int s = 1023 - (h >> 20);
+    if (s > 1000) s = 1000;
+    const double f = __longlong_as_double((long long)(1023 + s) << 52);
+    v0 *= f; v1 *= f; v2 *= f; v3 *= f;
+    return s;
+}
+
+// Generic arity (1 child, or > 2 children): running product over the children (likelihood.rs:113-131).
+// The reference multiplies child contributions whose profiles Profile::scale() left at max == 1 and scales
+// once per node, so a node with very many children underflows there (a star of >= ~500 tips gives -inf).
+// To leave the normal f64 range at the same place, internal children of a node with >= 3 children are first
+// brought to a maximum in [1,2) (exact power of two, exponent accumulated) and the product is rescaled only
+// once, at the end -- the same arithmetic as the fused sweep's SW_FLAG_NORM.
 __global__ void __launch_bounds__(CLV_THREADS)
 clv_update_generic_kernel(const GenOp *__restrict__ ops, int n_ops, const GenChild *__restrict__ kids,
                           ModelDev M, const double *__restrict__ Pmat, double *__restrict__ clv,
@@ -476,6 +492,8 @@ clv_update_generic_kernel(const GenOp *__restrict__ ops, int n_ops, const GenChi
     const size_t stride2 = tile_pad / 2;
     const size_t cat_off = (size_t)cat_clv * 4 * tile_pad + (size_t)site;
     int *sc = scale + (size_t)cat_clv * tile_pad + site;
+    const bool norm = op.child_end - op.child_begin >= 3;
+    int ex = 0, ey = 0;
     double2 v[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) v[i] = make_double2(1.0, 1.0);
@@ -485,15 +503,29 @@ clv_update_generic_kernel(const GenOp *__restrict__ ops, int n_ops, const GenChi
         double2 a[4];
         load_P(Pmat + ((size_t)ch.edge * M.n_cat + cat_model) * 16, p);
         if (ch.is_tip) contrib_tip(p, tips + (int64_t)ch.src * P_pad + tile_off + site, a);
-        else contrib_internal(p, reinterpret_cast<const double2 *>(clv + (size_t)ch.src * slot_stride + cat_off), stride2, a);
+        else {
+            const double2 *src = reinterpret_cast<const double2 *>(clv + (size_t)ch.src * slot_stride + cat_off);
+            double2 x0 = src[0], x1 = src[stride2], x2 = src[2 * stride2], x3 = src[3 * stride2];
+            if (norm) {
+                ex += normalize_site(x0.x, x1.x, x2.x, x3.x);
+                ey += normalize_site(x0.y, x1.y, x2.y, x3.y);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                a[i].x = p[4 * i] * x0.x + p[4 * i + 1] * x1.x + p[4 * i + 2] * x2.x + p[4 * i + 3] * x3.x;
+                a[i].y = p[4 * i] * x0.y + p[4 * i + 1] * x1.y + p[4 * i + 2] * x2.y + p[4 * i + 3] * x3.y;
+            }
+        }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             v[i].x *= a[i].x;
             v[i].y *= a[i].y;
         }
-        rescale_site(v[0].x, v[1].x, v[2].x, v[3].x, sc);
-        rescale_site(v[0].y, v[1].y, v[2].y, v[3].y, sc + 1);
     }
+    if (ex) atomicAdd(sc, ex);
+    if (ey) atomicAdd(sc + 1, ey);
+    rescale_site(v[0].x, v[1].x, v[2].x, v[3].x, sc);
+    rescale_site(v[0].y, v[1].y, v[2].y, v[3].y, sc + 1);
     double2 *dst = reinterpret_cast<double2 *>(clv + (size_t)op.out_slot * slot_stride + cat_off);
 #pragma unroll
     for (int i = 0; i < 4; ++i) dst[i * stride2] = v[i];
@@ -585,12 +617,19 @@ root_kernel(const double *__restrict__ root_clv /* slot base */, size_t tile_pad
 }
 
 // K4: final deterministic reduction of the per-block partials to one double per GPU.
-__global__ void final_reduce_kernel(const double *__restrict__ partials, int n, double *__restrict__ out)
+// out[1] carries the fused sweep's error word (an op code the kernel does not know: a corrupted or mis-built
+// op table), which is re-armed here for the next evaluation.
+__global__ void final_reduce_kernel(const double *__restrict__ partials, int n, double *__restrict__ out,
+                                    unsigned int *__restrict__ sweep_err)
 {
     double acc = 0.0;
     for (int i = threadIdx.x; i < n; i += blockDim.x) acc += partials[i];
     double r = block_reduce_sum(acc);
-    if (threadIdx.x == 0) *out = r;
+    if (threadIdx.x == 0) {
+        out[0] = r;
+        out[1] = sweep_err ? (double)*sweep_err : 0.0;
+        if (sweep_err) *sweep_err = 0u;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -273,7 +273,8 @@ struct phb_ctx {
     bool have_aln = false;
     int n_rows = 0;
     int64_t n_patterns = 0;
-    std::vector<int> row_invalid_host;
+    std::vector<int> row_invalid_host;   // per row: an unaccepted byte somewhere in the row
+    std::vector<uint8_t> row_first_invalid; // per row: the byte of pattern 0 is unaccepted (error precedence, check_leaves)
     // model
     bool have_model = false;
     ModelDev model;      // as used by the lnL path (analytic +I unless LITERAL_INVARIANT)
@@ -396,14 +397,21 @@ int upload_tree(phb_ctx *ctx)
 
 // Validation shared by both engines: every leaf needs a row (likelihood.rs:99-103) holding only
 // accepted bytes (likelihood.rs:105-107).
+// The reference meets these errors pattern by pattern, walking the leaves in post-order: on pattern 0 a leaf
+// without a row (InvalidAlignment) or with an unaccepted byte IN PATTERN 0 (AlphabetMismatch), whichever leaf
+// comes first; an unaccepted byte in a later pattern can only surface once pattern 0 went through, i.e. when
+// every leaf has a row.  leaf_nodes is in that post-order (children in stored order, src/iter.rs:112-138).
 int check_leaves(phb_ctx *ctx)
 {
     const TreeSched &T = ctx->tree;
+    const bool have_first = ctx->row_first_invalid.size() >= (size_t)ctx->n_rows;
     for (size_t i = 0; i < T.leaf_nodes.size(); ++i) {
         int r = T.leaf_rows[i];
         if (r < 0 || r >= ctx->n_rows)
             return ctx->fail(PHB_ERR_INVALID_ALIGNMENT, "Leaf in tree not found in alignment leaf order (node %d)",
                              T.leaf_nodes[i]);
+        if (have_first && ctx->row_first_invalid[r])
+            return ctx->fail(PHB_ERR_ALPHABET_MISMATCH, "Invalid char in alignment (row %d)", r);
     }
     for (size_t i = 0; i < T.leaf_nodes.size(); ++i)
         if (ctx->row_invalid_host[T.leaf_rows[i]])
@@ -420,7 +428,7 @@ int plan_device(phb_ctx *ctx, Device &d, const ModelDev &M, bool asr, bool want_
         CU(d.per_pattern.ensure(sizeof(double) * (size_t)d.P_pad));
         CU(d.leaf_ls.ensure(sizeof(double) * (size_t)d.P_pad));
         CU(d.inv_mask.ensure((size_t)d.P_pad));
-        CU(d.total.ensure(sizeof(double)));
+        CU(d.total.ensure(2 * sizeof(double)));
         d.tile_pad = d.P_pad;
         d.n_tiles = d.P > 0 ? 1 : 0;
         return PHB_OK;
@@ -433,7 +441,7 @@ int plan_device(phb_ctx *ctx, Device &d, const ModelDev &M, bool asr, bool want_
     CU(d.per_pattern.ensure(sizeof(double) * (size_t)d.P_pad));
     CU(d.leaf_ls.ensure(sizeof(double) * (size_t)d.P_pad));
     CU(d.inv_mask.ensure((size_t)d.P_pad));
-    CU(d.total.ensure(sizeof(double)));
+    CU(d.total.ensure(2 * sizeof(double)));
     const int n_slots = std::max(T.n_internal, 1);
     const size_t per_site = (size_t)n_slots * M.n_clv * 4 * sizeof(double);
     size_t need_full = per_site * (size_t)d.P_pad;
@@ -730,7 +738,7 @@ int launch_sweep_reduce(phb_ctx *ctx, Device &d, size_t n_partials)
 {
     ScopedTimer tm(ctx, &d, PH_ROOT);
     PHB_LAUNCH(final_reduce_kernel, dim3(1), dim3(1024), d.stream, d.partials.as<double>(), (int)n_partials,
-               d.total.as<double>());
+               d.total.as<double>(), d.sw_err.as<unsigned int>());
     CHECK_LAUNCH();
     return PHB_OK;
 }
@@ -797,7 +805,7 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
     for (Device &d : ctx->devs) {
         CU(cudaSetDevice(d.ordinal));
         if (d.P == 0) {
-            *d.h_total = 0.0;
+            d.h_total[0] = d.h_total[1] = 0.0;
             continue;
         }
         if (!use_sweep) {
@@ -826,7 +834,7 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
         if (use_sweep) {
             rc = run_sweep(ctx, d, M);
             if (rc) return rc;
-            CU(cudaMemcpyAsync(d.h_total, d.total.p, sizeof(double), cudaMemcpyDeviceToHost, d.stream));
+            CU(cudaMemcpyAsync(d.h_total, d.total.p, 2 * sizeof(double), cudaMemcpyDeviceToHost, d.stream));
             continue;
         }
         size_t part_off = 0;
@@ -872,10 +880,10 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
         {
             ScopedTimer tm(ctx, &d, PH_ROOT);
             PHB_LAUNCH(final_reduce_kernel, dim3(1), dim3(1024), d.stream, d.partials.as<double>(), (int)part_off,
-                       d.total.as<double>());
+                       d.total.as<double>(), asr_sweep ? d.sw_err.as<unsigned int>() : (unsigned int *)nullptr);
             CHECK_LAUNCH();
         }
-        CU(cudaMemcpyAsync(d.h_total, d.total.p, sizeof(double), cudaMemcpyDeviceToHost, d.stream));
+        CU(cudaMemcpyAsync(d.h_total, d.total.p, 2 * sizeof(double), cudaMemcpyDeviceToHost, d.stream));
     }
     if (timing) {
         CU(cudaSetDevice(d0.ordinal));
@@ -886,7 +894,9 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
         CU(cudaSetDevice(d.ordinal));
         CU(cudaStreamSynchronize(d.stream));
         if (asr && ctx->asr_states_out) CU(cudaStreamSynchronize(d.copy_stream));
-        sum += *d.h_total;
+        sum += d.h_total[0];
+        if (d.h_total[1] != 0.0)
+            return ctx->fail(PHB_ERR_NUMERICAL_INSTABILITY, "fused sweep: unknown op code in the schedule (device %d)", d.ordinal);
     }
     *total = sum;
     // stats
@@ -1286,7 +1296,7 @@ int32_t phb_ctx_create(const int32_t *devices, int32_t n_dev, uint64_t flags, ph
             cudaStreamCreateWithFlags(&d.copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
             cudaEventCreate(&d.ev_copied[0]) != cudaSuccess || cudaEventCreate(&d.ev_copied[1]) != cudaSuccess ||
             cudaEventCreate(&d.ev_free[0]) != cudaSuccess || cudaEventCreate(&d.ev_free[1]) != cudaSuccess ||
-            cudaHostAlloc((void **)&d.h_total, sizeof(double), cudaHostAllocDefault) != cudaSuccess) {
+            cudaHostAlloc((void **)&d.h_total, 2 * sizeof(double), cudaHostAllocDefault) != cudaSuccess) {
             phb_ctx_destroy(ctx);
             return PHB_ERR_CUDA;
         }
@@ -1456,6 +1466,17 @@ int gather_row_flags(phb_ctx *ctx, int n_rows)
         CU(cudaStreamSynchronize(d.stream));
         for (int r = 0; r < n_rows; ++r) ctx->row_invalid_host[r] |= tmp[r];
     }
+    // the codes of global pattern 0 (first column of the first non-empty shard)
+    ctx->row_first_invalid.assign(std::max(n_rows, 1), 0);
+    for (Device &d : ctx->devs) {
+        if (d.P == 0 || n_rows == 0) continue;
+        CU(cudaSetDevice(d.ordinal));
+        CU(cudaMemcpy2DAsync(ctx->row_first_invalid.data(), 1, d.tips.p, (size_t)d.P_pad, 1, (size_t)n_rows,
+                             cudaMemcpyDeviceToHost, d.stream));
+        CU(cudaStreamSynchronize(d.stream));
+        for (int r = 0; r < n_rows; ++r) ctx->row_first_invalid[r] = ctx->row_first_invalid[r] == CODE_INVALID;
+        break;
+    }
     return PHB_OK;
 }
 
@@ -1474,6 +1495,7 @@ int32_t phb_set_alignment(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns, cons
     int rc = shard_and_alloc(ctx, n_rows, n_patterns);
     if (rc) return rc;
     ctx->row_invalid_host.assign(std::max(n_rows, 1), 0);
+    ctx->row_first_invalid.clear();
     const size_t CHUNK = (size_t)256 << 20; // staging bytes per H2D copy
     for (Device &d : ctx->devs) {
         CU(cudaSetDevice(d.ordinal));
@@ -1526,6 +1548,7 @@ static int32_t compress_impl(phb_ctx *ctx, int32_t n_rows, int64_t width, const 
         int rc0 = shard_and_alloc(ctx, n_rows, 0);
         if (rc0) return rc0;
         ctx->row_invalid_host.assign(std::max(n_rows, 1), 0);
+        ctx->row_first_invalid.clear();
         for (Device &d : ctx->devs) {
             rc0 = upload_pad_and_mult(ctx, d, n_rows, nullptr);
             if (rc0) return rc0;
@@ -1663,6 +1686,7 @@ static int32_t compress_impl(phb_ctx *ctx, int32_t n_rows, int64_t width, const 
     int rc = shard_and_alloc(ctx, n_rows, P);
     if (rc) return rc;
     ctx->row_invalid_host.assign(std::max(n_rows, 1), 0);
+    ctx->row_first_invalid.clear();
     lap("shard_and_alloc");
     for (Device &d : ctx->devs) {
         const bool same = &d == &d0;
@@ -1837,6 +1861,7 @@ int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns
     int rc = shard_and_alloc(ctx, n_rows, n_patterns);
     if (rc) return rc;
     ctx->row_invalid_host.assign(std::max(n_rows, 1), 0);
+    ctx->row_first_invalid.clear();
     // Chunks of whole passes of the widest CTA (1 by default: measured 195.2 / 199.9 / 207.9 ms end to end for
     // 1 / 2 / 3 passes at 10k x 1M — the copy engine is the bottleneck, so smaller chunks only shorten the
     // un-overlapped tail); a short remainder joins the last chunk, which gets its own geometry so that it does
@@ -1884,7 +1909,7 @@ int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns
         Device &d = ctx->devs[di];
         CU(cudaSetDevice(d.ordinal));
         if (d.P == 0) {
-            *d.h_total = 0.0;
+            d.h_total[0] = d.h_total[1] = 0.0;
             continue;
         }
         rc = plan_device(ctx, d, M, false, false, true);
@@ -1922,8 +1947,8 @@ int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns
         d.tip_constants_valid = true;
         d.tip_constants_rows = T.leaf_rows;
         rc = launch_sweep_reduce(ctx, d, part_off);
-        if (rc) return rc;
-        CU(cudaMemcpyAsync(d.h_total, d.total.p, sizeof(double), cudaMemcpyDeviceToHost, d.stream));
+        if (rc) return drain(rc);
+        CU(cudaMemcpyAsync(d.h_total, d.total.p, 2 * sizeof(double), cudaMemcpyDeviceToHost, d.stream));
     }
     rc = gather_row_flags(ctx, n_rows); // joins every device stream
     if (rc) return rc;
@@ -1931,7 +1956,11 @@ int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns
     rc = check_leaves(ctx); // invalid byte in a leaf row (likelihood.rs:105-107): the result is discarded
     if (rc) return rc;
     double sum = 0.0;
-    for (Device &d : ctx->devs) sum += *d.h_total; // rank order: deterministic
+    for (Device &d : ctx->devs) {
+        sum += d.h_total[0]; // rank order: deterministic
+        if (d.h_total[1] != 0.0)
+            return ctx->fail(PHB_ERR_NUMERICAL_INSTABILITY, "fused sweep: unknown op code in the schedule (device %d)", d.ordinal);
+    }
     *total = sum;
     phb_stats &st = ctx->stats;
     st.n_patterns = n_patterns;
@@ -2074,6 +2103,7 @@ int32_t phb_simulate_alignment(phb_ctx *ctx, int64_t n_patterns, int64_t global_
     rc = upload_tree(ctx);
     if (rc) return rc;
     ctx->row_invalid_host.assign(std::max(n_leaves, 1), 0);
+    ctx->row_first_invalid.clear();
     // pre-order (left-to-right) for the walk
     std::vector<int> pre;
     pre.reserve(T.n);

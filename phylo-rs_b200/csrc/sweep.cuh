@@ -39,6 +39,9 @@ constexpr int SW_FLAG_PUSH = 1;    // push cur to `level` before executing (TT /
 constexpr int SW_FLAG_RESCALE = 2; // node complete: run the underflow check
 constexpr int SW_FLAG_U = 4;       // TT / TI: operate on the second register accumulator `u` (cur untouched)
 constexpr int SW_FLAG_XU = 8;      // II: the pending operand is `u`, not a stack level
+constexpr int SW_FLAG_NORM = 16;   // APPLY of a child of a node with >= 3 children: bring the child's CLV to max in [1,2)
+                                   // first (exact power of two), as the reference's Profile::scale() leaves every child
+                                   // at max == 1 before the parent's product (profile.rs:20-39, likelihood.rs:113-131)
 
 constexpr int SW_P_BYTES = 128;   // 4x4 f64 row-major
 constexpr int SW_TAB_BYTES = 512; // 16 masks x 4 f64, slot order SW_PERM
@@ -237,11 +240,13 @@ __device__ __forceinline__ void sw_load_tip(const unsigned char *tab, uint32_t c
     t[0] = a.x; t[1] = a.y; t[2] = b.x; t[3] = b.y;
 }
 
-// exact power-of-two rescale of one site's 4 states when the largest drops below 2^-256
+// exact power-of-two rescale of one site's 4 states when the largest drops below 2^-256 (ALWAYS = false), or
+// unconditionally to a maximum in [1,2) (ALWAYS = true: the child of a polytomy, see SW_FLAG_NORM)
+template <bool ALWAYS = false>
 __device__ __forceinline__ void sw_rescale(double (&v)[4], int &sc)
 {
     int h = max(max(__double2hiint(v[0]), __double2hiint(v[1])), max(__double2hiint(v[2]), __double2hiint(v[3])));
-    if (h < ((1023 - 256) << 20) && h > 0) { // positive and small (zero / negative maxima are left alone)
+    if ((ALWAYS || h < ((1023 - 256) << 20)) && h > 0) { // positive (zero / negative maxima are left alone)
         int e = h >> 20;                     // biased exponent of the maximum (0 = subnormal)
         int s = 1023 - e;
         if (s > 1000) s = 1000;
@@ -296,7 +301,7 @@ sweep_kernel(SweepParams p, ModelDev M)
                     unsigned char *st = ring + (size_t)s * stage_bytes;
                     uint32_t bytes = d.rec_bytes + (d.rowA >= 0 ? code_bytes : 0) + (d.rowB >= 0 ? code_bytes : 0);
                     sw_mbar_expect_tx(&full[s], bytes);
-                    sw_bulk_g2s(st, p.stream + d.rec_off, d.rec_bytes, &full[s]);
+                    if (d.rec_bytes) sw_bulk_g2s(st, p.stream + d.rec_off, d.rec_bytes, &full[s]); // MULPOP has no record
                     if (d.rowA >= 0) sw_bulk_g2s(st + rec_cap, tip_base + (int64_t)d.rowA * p.P_pad, code_bytes, &full[s]);
                     if (d.rowB >= 0) sw_bulk_g2s(st + rec_cap + code_bytes, tip_base + (int64_t)d.rowB * p.P_pad, code_bytes, &full[s]);
                     d = nd;
@@ -456,6 +461,10 @@ sweep_kernel(SweepParams p, ModelDev M)
                 break;
             }
             case SW_APPLY: {
+                if (flags & SW_FLAG_NORM) {
+#pragma unroll
+                    for (int r = 0; r < SW_R; ++r) sw_rescale<true>(v[r], sc[r]);
+                }
                 double P[16];
                 sw_load_P(blkA, P);
 #pragma unroll

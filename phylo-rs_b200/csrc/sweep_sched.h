@@ -121,6 +121,10 @@ struct SweepSched {
                 f.ret = false;
                 if (!binary) {
                     emit(SW_APPLY, 0, iv[f.j - 1], false, -1, false);
+                    // a product of >= 3 child contributions: every child enters at max in [1,2), as in the
+                    // reference (children are max-normalised, profile.rs:20-39), so the product leaves the
+                    // normal range exactly where the reference's own product does
+                    if (iv.size() + tv.size() >= 3) recs.back().h.flags |= SW_FLAG_NORM;
                     if (f.j - 1 >= 1) emit(SW_MULPOP, need[iv[f.j - 1]], -1, false, -1, false);
                 }
             }

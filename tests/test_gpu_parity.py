@@ -77,6 +77,23 @@ def test_sweep_shapes(gpu_lib):
                 assert st["sweep_stack_levels"] == levels
 
 
+@pytest.mark.parametrize("k,depth", [(4, 110), (6, 110), (8, 110), (16, 110), (300, 1), (800, 1)])
+def test_high_arity_with_deep_subtrees(gpu_lib, k, depth):
+    """A root with k children, each a 110-leaf caterpillar (branches 0.9, random ACGT), and stars of 300 / 800 tips
+    (likelihood.rs:113-131 multiplies any number of max-normalised child contributions, profile.rs:20-39).  The
+    default fused sweep, the level kernels and both marginal-ASR up passes against the oracle; the 800-star
+    underflows in the reference itself (-inf) and must do so here on every path."""
+    case = workloads.polytomy_case(k, depth, 48, model="gtr_g4", seed=100 + k)
+    tot, per, _ = _cases.check_lnl(gpu_lib, case)
+    tot_l, per_l, _ = _cases.check_lnl(gpu_lib, case, flags=capi.FLAG_LEVEL_KERNELS)
+    if (k, depth) == (800, 1):
+        assert tot == -np.inf and tot_l == -np.inf
+    else:
+        assert np.isfinite(tot) and np.max(np.abs(per - per_l)) < 1e-9
+    assert _cases.check_asr(gpu_lib, case) == 0
+    assert _cases.check_asr(gpu_lib, case, flags=capi.FLAG_LEVEL_KERNELS) == 0
+
+
 def test_literal_invariant_flag(gpu_lib):
     case = workloads.make_case(40, 3000, model="gtr_i_g4", seed=23, ambiguity=0.1)
     a = _cases.check_lnl(gpu_lib, case)[0]

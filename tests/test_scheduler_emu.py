@@ -122,6 +122,23 @@ def test_polytomy_and_unifurcation(emu_lib):
     assert _cases.check_asr(emu_lib, case, want_post=True) == 0
 
 
+@pytest.mark.parametrize("k,depth", [(4, 110), (6, 110), (16, 110), (300, 1), (800, 1)])
+def test_high_arity_with_deep_subtrees(emu_lib, k, depth):
+    """a root with k children, each a 110-leaf caterpillar (branches 0.9), and stars of 300 /
+    800 tips.  Every child CLV enters the product max-normalised (profile.rs:20-39), so the product leaves the
+    f64 range only where the reference's does (the 800-star is -inf there too).  Default sweep, level kernels and
+    the marginal-ASR up passes must all agree with the oracle."""
+    case = workloads.polytomy_case(k, depth, 12, model="gtr_g4", seed=100 + k)
+    tot, per, _ = _cases.check_lnl(emu_lib, case)
+    tot_l, per_l, _ = _cases.check_lnl(emu_lib, case, flags=capi.FLAG_LEVEL_KERNELS)
+    if (k, depth) == (800, 1):
+        assert tot == -np.inf and tot_l == -np.inf  # the reference's own underflow (likelihood.rs:123-125)
+    else:
+        assert np.isfinite(tot) and np.max(np.abs(per - per_l)) < 1e-9
+    assert _cases.check_asr(emu_lib, case) == 0
+    assert _cases.check_asr(emu_lib, case, flags=capi.FLAG_LEVEL_KERNELS) == 0
+
+
 def test_reference_fixture_and_internal_row(emu_lib):
     # integration_test.rs:14-17 + :663 — row C names an internal node: ignored by pruning, never validated
     tree = parse_newick("((A:0.601,B:0.301)C:0.100,D:0.200)E:0.001;")
@@ -157,6 +174,28 @@ def test_errors(emu_lib):
         with pytest.raises(capi.PhbError) as e:  # node before its child
             ctx.set_tree(ft["postorder"][::-1], ft["child_off"], ft["children"], ft["blen"], ft["leaf_row"], ft["root"])
         assert e.value.variant == "NumericalInstability"
+
+
+def test_error_precedence_follows_the_reference(emu_lib):
+    """likelihood.rs:97-107 walks the leaves in post-order on pattern 0: a leaf without a row and a leaf with an
+    unaccepted byte IN PATTERN 0 are reported in the order they are met; an unaccepted byte in a later pattern
+    can only surface after pattern 0 went through (so a missing row wins)."""
+    case = workloads.make_case(6, 20, model="jc69", seed=2)
+    ft = case.ft
+    leaves = [int(v) for v in ft["postorder"] if ft["leaf_row"][v] >= 0]
+    first, last = leaves[0], leaves[-1]
+    lr = ft["leaf_row"].copy()
+    lr[last] = -1  # the LAST leaf of the post-order has no row
+    for pat, want in ((0, "AlphabetMismatch"), (3, "InvalidAlignment")):
+        bad = case.patterns.copy()
+        bad[pat, ft["leaf_row"][first]] = ord("X")  # the FIRST leaf holds an unaccepted byte in pattern `pat`
+        with capi.Context(library=emu_lib) as ctx:
+            workloads.load_into(ctx, case)
+            ctx.set_alignment(bad)
+            ctx.set_tree(ft["postorder"], ft["child_off"], ft["children"], ft["blen"], lr, ft["root"])
+            with pytest.raises(capi.PhbError) as e:
+                ctx.log_likelihood()
+            assert e.value.variant == want
 
 
 def test_empty_alignment_is_zero(emu_lib):
