@@ -239,6 +239,13 @@ def run_gpu(args, rank, world, local_rank):
     st = ctx.stats()
     launches = st["kernel_launches"] - launches0
     # ---- end to end from host buffers ------------------------------------------------------------
+    if os.environ.get("PHB_BENCH_KERNEL_ONLY") == "1":  # profiling runs (ncu): the device-timed part only, no JSON contract
+        if rank == 0:
+            print(json.dumps({"kernel_only": True, "ms_per_step": dev_ms / args.steps, "sweep": {k: st[k] for k in st if k.startswith("sweep_")}}), flush=True)
+        ctx.close()
+        if world > 1:
+            dist.destroy_process_group()
+        return
     e2e_steps = max(1, min(args.steps, 3))
     n_rows = tree["n_taxa"]
     host = torch.empty((cnt, n_rows), dtype=torch.uint8, pin_memory=True)

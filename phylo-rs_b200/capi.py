@@ -60,6 +60,7 @@ class Stats(C.Structure):
         ("sweep_stages", C.c_int32), ("sweep_block_sites", C.c_int32), ("sweep_stream_bytes", C.c_int64),
         ("nni_path_moves", C.c_int32), ("nni_tiles", C.c_int32), ("nni_path_steps", C.c_int64),
         ("nni_cache_bytes", C.c_double), ("nni_read_bytes", C.c_double),
+        ("sweep_guards", C.c_int32), ("sweep_normouts", C.c_int32),
     ]
 
     def as_dict(self):
@@ -117,7 +118,7 @@ _DEFAULT = None
 def default_library():
     global _DEFAULT
     if _DEFAULT is None:
-        _DEFAULT = Library()
+        _DEFAULT = Library(os.environ.get("PHB_LIB"))  # PHB_LIB: another build of the same sources (kernel experiments)
     return _DEFAULT
 
 

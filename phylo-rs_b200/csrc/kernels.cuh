@@ -18,20 +18,21 @@ constexpr int CLV_THREADS = 256;          // threads per block in the CLV kernel
 constexpr int SITES_PER_BLOCK = 2 * CLV_THREADS;
 
 // tip code: bits 0..3 = SLOT of the state mask over A,C,G,T (slot = row of the sweep's tip tables:
-// one-hot masks A,C,G,T are slots 0..3 = the state index, the 11 ambiguity masks follow); bit 4 = gap
-// ('-': all-ones profile, log-scale 0); 0xFF = byte outside Nucleotide::profile's 17 accepted codes
-// (src/alphabet.rs:44-64).
-constexpr uint8_t CODE_GAP = 0x1E;
+// one-hot masks A,C,G,T are slots 0..3 = the state index, the all-ones mask (N, gap) is slot 4 -- so the five
+// codes that make up almost all real data are 0..4 and index the sweep's 5x5 cherry tables directly -- and the
+// 10 partial ambiguity masks follow); bit 4 = gap ('-': all-ones profile, log-scale 0); 0xFF = byte outside
+// Nucleotide::profile's 17 accepted codes (src/alphabet.rs:44-64).
+constexpr uint8_t CODE_GAP = 0x14;
 constexpr uint8_t CODE_INVALID = 0xFF;
 
 __host__ __device__ __forceinline__ uint32_t mask_to_slot(uint32_t mask)
 {
-    return (uint32_t)((0xEDCBA9837652410Full >> (4u * (mask & 15u))) & 15ull);
+    return (uint32_t)((0x4EDCBA938762510Full >> (4u * (mask & 15u))) & 15ull);
 }
 // state mask (bit i = state i allowed) of a tip code
 __host__ __device__ __forceinline__ uint32_t code_mask(uint32_t code)
 {
-    return (uint32_t)((0x0FEDCBA976538421ull >> (4u * (code & 15u))) & 15ull);
+    return (uint32_t)((0x0EDCBA97653F8421ull >> (4u * (code & 15u))) & 15ull);
 }
 
 __host__ __device__ inline uint8_t encode_mask_byte(uint8_t c)

@@ -243,6 +243,7 @@ struct Device {
         sim_pre, sim_parent, sim_depth, sim_leafrow, sim_stack, scratch, sw_descs, sw_blocks, sw_stream, sw_gstack,
         sw_err, sw_ops, uops, ukids, lnP, jbest, nni_upper, nni_uexps, nni_jobs, nni_rows, nni_exps, nni_partials, nni_totals, nni_moves, nni_steps, nni_need;
     bool sweep_uploaded = false;
+    bool sweep_ops_stale = false; // the guard flags of the op table changed since the last upload
     int sm_count = 0;
     size_t smem_optin = 0;
     cudaStream_t copy_stream = nullptr;          // H2D of alignment chunks, overlapped with packing / sweeping
@@ -284,6 +285,7 @@ struct phb_ctx {
     bool tree_uploaded = false;
     SweepSched sweep;      // fused-sweep op stream for (tree, n_clv)
     SweepGeom sweep_geom;
+    bool sweep_guards_valid = false; // guard flags planned for the current branch lengths and rates
     // marginal ASR: caller's output buffers, so that a finished tile's states go home while the next tile runs
     uint8_t *asr_states_out = nullptr;
     double *asr_post_out = nullptr;
@@ -644,24 +646,52 @@ int ensure_sweep(phb_ctx *ctx, const ModelDev &M)
             d.sweep_uploaded = false;
         }
         S.build(T.n, T.root, T.child_off, T.children, T.leaf_row, M.n_clv, T.slot);
+        ctx->sweep_guards_valid = false;
+        if (getenv("PHB_SWEEP_TRACE"))
+            fprintf(stderr, "sweep schedule: ops %d (TT %d TI %d II %d APPLY %d MULTIP %d MULPOP %d LOADTIP %d) pushes %d "
+                            "register siblings %d levels %d stream %zu B\n", S.n_ops, S.count_kind[0], S.count_kind[1],
+                    S.count_kind[2], S.count_kind[3], S.count_kind[4], S.count_kind[5], S.count_kind[6], S.n_push,
+                    S.n_reg_sibling, S.n_levels, S.stream_bytes);
         size_t smem_max = ctx->devs[0].smem_optin;
         for (Device &d : ctx->devs) smem_max = std::min(smem_max, d.smem_optin);
         if (!ctx->sweep_geom.plan(S, smem_max, shard_P, std::max(ctx->devs[0].sm_count, 1)))
             return ctx->fail(PHB_ERR_INVALID_MODEL_PARAMETER, "sweep: %d CLV categories do not fit one CTA", M.n_clv);
     }
+    if (!ctx->sweep_guards_valid) { // branch lengths or rates changed: re-plan where the underflow guard runs
+        std::vector<double> gb, gbd;
+        sweep_guard_bounds(M, T.blen, gb, gbd);
+        std::vector<uint32_t> before(S.ops.size());
+        for (size_t k = 0; k < S.ops.size(); ++k) before[k] = S.ops[k].w0;
+        for (Device &d : ctx->devs) // the host image of the op table may still be in flight
+            if (d.sweep_uploaded) {
+                cudaSetDevice(d.ordinal);
+                cudaStreamSynchronize(d.stream);
+            }
+        S.plan_guards(gb, gbd);
+        bool changed = false;
+        for (size_t k = 0; k < S.ops.size() && !changed; ++k) changed = before[k] != S.ops[k].w0;
+        if (changed)
+            for (Device &d : ctx->devs) d.sweep_ops_stale = true;
+        ctx->sweep_guards_valid = true;
+        if (getenv("PHB_SWEEP_TRACE"))
+            fprintf(stderr, "sweep guards: %d lazy + %d full of %d nodes\n", S.n_guards, S.n_normout, T.n_internal);
+    }
     for (Device &d : ctx->devs) {
-        if (d.sweep_uploaded) continue;
+        if (d.sweep_uploaded && !d.sweep_ops_stale) continue;
         CU(cudaSetDevice(d.ordinal));
-        CU(d.sw_descs.ensure(sizeof(SweepDesc) * S.descs.size()));
-        CU(d.sw_blocks.ensure(sizeof(SweepBlock) * S.blocks.size()));
-        CU(d.sw_stream.ensure(S.stream_bytes + 16));
-        CU(d.sw_err.ensure(sizeof(unsigned int)));
-        CU(cudaMemcpyAsync(d.sw_descs.p, S.descs.data(), sizeof(SweepDesc) * S.descs.size(), cudaMemcpyHostToDevice, d.stream));
-        CU(cudaMemcpyAsync(d.sw_blocks.p, S.blocks.data(), sizeof(SweepBlock) * S.blocks.size(), cudaMemcpyHostToDevice, d.stream));
-        CU(d.sw_ops.ensure(sizeof(SweepOp) * S.ops.size()));
+        if (!d.sweep_uploaded) {
+            CU(d.sw_descs.ensure(sizeof(SweepDesc) * S.descs.size()));
+            CU(d.sw_blocks.ensure(sizeof(SweepBlock) * S.blocks.size()));
+            CU(d.sw_stream.ensure(S.stream_bytes + 16));
+            CU(d.sw_err.ensure(sizeof(unsigned int)));
+            CU(cudaMemcpyAsync(d.sw_descs.p, S.descs.data(), sizeof(SweepDesc) * S.descs.size(), cudaMemcpyHostToDevice, d.stream));
+            CU(cudaMemcpyAsync(d.sw_blocks.p, S.blocks.data(), sizeof(SweepBlock) * S.blocks.size(), cudaMemcpyHostToDevice, d.stream));
+            CU(d.sw_ops.ensure(sizeof(SweepOp) * S.ops.size()));
+            CU(cudaMemsetAsync(d.sw_err.p, 0, sizeof(unsigned int), d.stream));
+        }
         CU(cudaMemcpyAsync(d.sw_ops.p, S.ops.data(), sizeof(SweepOp) * S.ops.size(), cudaMemcpyHostToDevice, d.stream));
-        CU(cudaMemsetAsync(d.sw_err.p, 0, sizeof(unsigned int), d.stream));
         d.sweep_uploaded = true;
+        d.sweep_ops_stale = false;
     }
     return PHB_OK;
 }
@@ -671,9 +701,10 @@ int launch_sweep_transition(phb_ctx *ctx, Device &d, const ModelDev &M)
 {
     const SweepSched &S = ctx->sweep;
     ScopedTimer tm(ctx, &d, PH_TRANSITION);
-    int nthreads = (int)S.blocks.size() * M.n_clv;
+    int nthreads = (int)S.blocks.size() * M.n_clv + S.n_ops;
     PHB_LAUNCH(sweep_transition_kernel, dim3((nthreads + 127) / 128), dim3(128), d.stream, d.sw_blocks.as<SweepBlock>(),
-               (int)S.blocks.size(), d.blen.as<double>(), M, d.sw_stream.as<unsigned char>());
+               (int)S.blocks.size(), d.blen.as<double>(), M, d.sw_stream.as<unsigned char>(), d.sw_ops.as<SweepOp>(),
+               d.sw_descs.as<SweepDesc>(), S.n_ops);
     CHECK_LAUNCH();
     return PHB_OK;
 }
@@ -916,6 +947,8 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
     S.sweep_stages = (use_sweep || asr_sweep) ? ctx->sweep_geom.n_stages : 0;
     S.sweep_block_sites = (use_sweep || asr_sweep) ? 4 * ctx->sweep_geom.Q : 0;
     S.sweep_stream_bytes = (use_sweep || asr_sweep) ? (int64_t)ctx->sweep.stream_bytes : 0;
+    S.sweep_guards = (use_sweep || asr_sweep) ? ctx->sweep.n_guards : 0;
+    S.sweep_normouts = (use_sweep || asr_sweep) ? ctx->sweep.n_normout : 0;
     if (timing) {
         S.ms_transition = S.ms_clv = S.ms_root = S.ms_down = 0;
         for (auto &pr : d0.ev_log) {
@@ -1777,6 +1810,7 @@ int32_t phb_set_model(phb_ctx *ctx, const double *lambda, const double *V, const
     build_model_dev(M, (ctx->flags & PHB_FLAG_LITERAL_INVARIANT) != 0, ctx->model);
     build_model_dev(M, true, ctx->model_lit);
     ctx->have_model = true;
+    ctx->sweep_guards_valid = false; // the guard plan depends on the rates
     return PHB_OK;
 }
 
@@ -1978,6 +2012,8 @@ int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns
     st.sweep_stages = ctx->sweep_geom.n_stages;
     st.sweep_block_sites = 4 * ctx->sweep_geom.Q;
     st.sweep_stream_bytes = (int64_t)S.stream_bytes;
+    st.sweep_guards = S.n_guards;
+    st.sweep_normouts = S.n_normout;
     if (per_pattern) return phb_get_per_pattern(ctx, per_pattern);
     return PHB_OK;
 }

@@ -12,6 +12,7 @@
 #include "sweep.cuh"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <string>
@@ -31,6 +32,13 @@ struct SweepSched {
     std::vector<SweepOp> ops;           // per-op header table (global memory, prefetched by the consumers)
     int count_kind[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     int n_push = 0, n_reg_sibling = 0;  // pending siblings parked in the stack / kept in the second accumulator
+    // guard planning (plan_guards): the op that completes each node, the flags the schedule itself needs, and the
+    // tree in post-order
+    std::vector<int> done_op;           // node -> index of the op that completes it (-1: leaf)
+    std::vector<uint32_t> base_w0;      // per op: w0 without SW_FLAG_GUARD / SW_FLAG_NORMOUT
+    std::vector<int> post_order;        // children before parents
+    std::vector<int> kid_off, kids;     // copy of the child lists
+    int n_guards = 0, n_normout = 0;
 
     // child_off/children: CSR child lists; leaf_row: alignment row per leaf; root must be internal.
     // slot: CLV slot per node (-1 for leaves), recorded in the header of the op that completes the node.
@@ -56,6 +64,9 @@ struct SweepSched {
             }
             std::reverse(order.begin(), order.end());
         }
+        post_order = order;
+        kid_off = child_off;
+        kids = children;
         std::vector<int> need(n, 0);
         std::vector<std::vector<int>> ints(n), tips(n);
         for (int v : order) {
@@ -104,6 +115,10 @@ struct SweepSched {
             r.edgeA = edgeA; r.edgeB = edgeB; r.tabA = tabA; r.tabB = tabB;
             r.h.szA = edgeA < 0 ? 0 : (tabA ? SW_TAB_BYTES : SW_P_BYTES);
             r.h.szB = edgeB < 0 ? 0 : (tabB ? SW_TAB_BYTES : SW_P_BYTES);
+            if (kind == SW_TT) { // one 5x5 table of products for the cherry instead of two tip tables, followed by
+                r.h.szA = SW_TAB2_BYTES; // the two P(t) for the sites that carry a partial ambiguity code
+                r.h.szB = 2 * SW_P_BYTES;
+            }
             r.rowA = (edgeA >= 0 && tabA) ? leaf_row[edgeA] : -1;
             r.rowB = (edgeB >= 0 && tabB) ? leaf_row[edgeB] : -1;
             recs.push_back(r);
@@ -165,7 +180,7 @@ struct SweepSched {
             } else {
                 for (int tnode : tv) emit(SW_MULTIP, 0, tnode, true, -1, false);
             }
-            recs.back().h.flags |= SW_FLAG_RESCALE;
+            recs.back().h.flags |= SW_FLAG_DONE;
             recs.back().node = v;
             st.pop_back();
         }
@@ -185,36 +200,165 @@ struct SweepSched {
         n_ops = (int)recs.size();
         size_t off = 0;
         rec_cap = 0;
-        descs.resize(recs.size());
+        descs.assign(recs.size() + 1, SweepDesc()); // + one padding entry (the producer prefetches k + 1)
+        memset(descs.data(), 0, sizeof(SweepDesc) * descs.size());
+        descs.back().rowA = descs.back().rowB = -1;
         for (size_t k = 0; k < recs.size(); ++k) {
             const Rec &r = recs[k];
             const uint32_t per_cat = (uint32_t)(r.h.szA + r.h.szB);
-            const uint32_t bytes = (uint32_t)n_clv * per_cat;
+            const uint32_t bytes = (uint32_t)SW_HDR_BYTES + (uint32_t)n_clv * per_cat; // next op's header + operand blocks
             SweepDesc &d = descs[k];
             memset(&d, 0, sizeof d);
             d.rec_off = off;
             d.rec_bytes = bytes;
             d.rowA = r.rowA;
             d.rowB = r.rowB;
-            if (r.edgeA >= 0) blocks.push_back({off, per_cat, r.edgeA, r.tabA ? 1 : 0, 0});
-            if (r.edgeB >= 0) blocks.push_back({off + (uint32_t)r.h.szA, per_cat, r.edgeB, r.tabB ? 1 : 0, 0});
+            const size_t b0 = off + SW_HDR_BYTES;
+            if (r.h.kind == SW_TT) {
+                blocks.push_back({b0, per_cat, r.edgeA, 2, r.edgeB});
+                blocks.push_back({b0 + (uint32_t)SW_TAB2_BYTES, per_cat, r.edgeA, 0, -1});
+                blocks.push_back({b0 + (uint32_t)(SW_TAB2_BYTES + SW_P_BYTES), per_cat, r.edgeB, 0, -1});
+            } else {
+                if (r.edgeA >= 0) blocks.push_back({b0, per_cat, r.edgeA, r.tabA ? 1 : 0, -1});
+                if (r.edgeB >= 0) blocks.push_back({b0 + (uint32_t)r.h.szA, per_cat, r.edgeB, r.tabB ? 1 : 0, -1});
+            }
             rec_cap = std::max(rec_cap, (int)bytes);
             off += bytes;
         }
         stream_bytes = off;
-        ops.resize(recs.size());
+        ops.assign(recs.size() + 2, SweepOp{0, 0, 0, 0}); // + two padding entries (the consumers prefetch k + 2)
+        base_w0.assign(recs.size(), 0);
+        done_op.assign(n, -1);
         for (size_t k = 0; k < recs.size(); ++k) {
             const Hdr &h = recs[k].h;
             const uint32_t code = (uint32_t)h.kind | ((h.flags & (SW_FLAG_U | SW_FLAG_XU)) ? 8u : 0u);
-            ops[k].w0 = code | ((uint32_t)h.flags << 8) | ((uint32_t)h.level << 16);
-            ops[k].w1 = (uint32_t)h.szA | ((uint32_t)h.szB << 16);
-            const int nd = (h.flags & SW_FLAG_RESCALE) ? recs[k].node : -1;
+            base_w0[k] = code | ((uint32_t)h.flags << 8) | ((uint32_t)h.level << 16);
+            ops[k].w1 = (uint32_t)(h.szA + h.szB) | ((uint32_t)h.szA << 16);
+            const int nd = (h.flags & SW_FLAG_DONE) ? recs[k].node : -1;
+            if (nd >= 0) done_op[nd] = (int)k;
             ops[k].w2 = (nd >= 0 && (size_t)nd < slot.size() && slot[nd] >= 0) ? (uint32_t)slot[nd] : 0u;
             ops[k].w3 = 0;
         }
+        plan_guards(std::vector<double>(), std::vector<double>()); // until bounds are known: guard after every node
         valid = true;
     }
+
+    // Decides where the underflow guard runs.  A guard after every node costs ~13 dependent integer instructions per
+    // op; almost all of them are provably idle.  b[v] / bd[v] bound, in bits, how much the edge above node v can
+    // shrink a vector's maximum: every entry of P_v is >= 2^-b[v], every diagonal entry >= 2^-bd[v] (worst rate
+    // category; sweep_guard_bounds).  For a binary node p = (a, c):
+    //     max(CLV_p) >= max(CLV_a) * max(CLV_c) * 2^-s,   s = min(b[a] + bd[c], bd[a] + b[c])
+    // (take the row where one child's maximum sits: its own P contributes a diagonal entry, the other child's P at
+    // least its smallest entry; a tip child's table entry is a sum of entries of P).  E[v] is the resulting lower
+    // bound on log2 max(CLV_v), accumulated over the unguarded part of v's subtree.  Whenever it would fall below
+    // -LIM the children get a guard (their maxima are then >= 2^-256), and if even that is not enough -- the edge
+    // pair alone can shrink by more than LIM - 512 bits, i.e. r*t below ~1e-25 -- they are normalised to [1,2) on
+    // completion, which is the reference's own operating point (Profile::scale leaves max == 1).  LIM = 600 keeps
+    // >= 422 bits of dynamic range below the maximum before an entry turns subnormal.  Nodes that are not binary
+    // are always guarded.  Empty bounds: guard after every node (the schedule's state before set_model / blen).
+    // Rescaling is an exact power of two, so the placement changes no bit of any CLV.
+    void plan_guards(const std::vector<double> &b, const std::vector<double> &bd)
+    {
+        const int n = (int)done_op.size();
+        const double LIM = 600.0, T = 256.0;
+        std::vector<char> guard(n, 0), normout(n, 0);
+        if ((int)b.size() != n || (int)bd.size() != n || getenv("PHB_SWEEP_GUARD_ALL")) {
+            for (int v = 0; v < n; ++v) guard[v] = done_op[v] >= 0;
+        } else {
+            std::vector<double> Epre(n, 0.0), Epost(n, 0.0);
+            auto leaf = [&](int v) { return kid_off[v + 1] == kid_off[v]; };
+            auto set_guard = [&](int c) {
+                if (leaf(c)) return;
+                guard[c] = 1;
+                Epost[c] = std::max(Epre[c], -T);
+            };
+            for (int v : post_order) {
+                if (leaf(v)) continue;
+                const int nk = kid_off[v + 1] - kid_off[v];
+                if (nk != 2) {
+                    for (int k = kid_off[v]; k < kid_off[v + 1]; ++k) set_guard(kids[k]);
+                    guard[v] = 1;
+                    Epre[v] = Epost[v] = -T;
+                    continue;
+                }
+                const int a = kids[kid_off[v]], c = kids[kid_off[v] + 1];
+                const double s = std::min(b[a] + bd[c], bd[a] + b[c]);
+                double E = Epost[a] + Epost[c] - s;
+                if (!(E >= -LIM)) {
+                    set_guard(a);
+                    set_guard(c);
+                    E = Epost[a] + Epost[c] - s;
+                    if (!(E >= -LIM)) {
+                        for (int x : {a, c})
+                            if (!leaf(x)) {
+                                normout[x] = 1;
+                                Epost[x] = 0.0;
+                            }
+                        E = Epost[a] + Epost[c] - s;
+                        if (!(E >= -LIM)) E = -LIM; // the edge pair alone: same exposure as the reference's own product
+                    }
+                }
+                Epre[v] = Epost[v] = E;
+            }
+        }
+        n_guards = n_normout = 0;
+        for (size_t k = 0; k < base_w0.size(); ++k) ops[k].w0 = base_w0[k];
+        for (int v = 0; v < n; ++v) {
+            if (done_op[v] < 0) continue;
+            if (normout[v]) {
+                ops[done_op[v]].w0 |= (uint32_t)SW_FLAG_NORMOUT << 8;
+                ++n_normout;
+            } else if (guard[v]) {
+                ops[done_op[v]].w0 |= (uint32_t)SW_FLAG_GUARD << 8;
+                ++n_guards;
+            }
+        }
+    }
 };
+
+// Per-edge shrink bounds for SweepSched::plan_guards, from the model's eigen-system (phb_set_model) and the branch
+// lengths.  Q = diag(1/sqrt(pi)) V diag(lambda) V^T diag(sqrt(pi)); with mu = max_i |Q_ii| and q = min_{i != j} Q_ij,
+// uniformisation (P(t) = sum_k Poisson(k; mu t) R^k, R = I + Q/mu >= 0) gives, term k = 1 and k = 0,
+//     P_ij(t) >= e^{-mu t} t q  (i != j),      P_ii(t) >= e^{-mu t},
+// and because P(t + s) = P(s) P(t) with stochastic P(s), the smallest entry of P(t) never decreases with t: the
+// bound is evaluated at t* = min(t, 1/mu).  Worst rate category (smallest positive rate; a rate-0 category has
+// P = I, whose off-diagonal zeros bound nothing: b = inf).  One bit of slack covers host/device rounding.
+inline void sweep_guard_bounds(const ModelDev &M, const std::vector<double> &blen, std::vector<double> &b, std::vector<double> &bd)
+{
+    const size_t n = blen.size();
+    b.assign(n, INFINITY);
+    bd.assign(n, 0.0);
+    double Q[16], mu = 0.0, qmin = INFINITY;
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j) {
+            double acc = 0.0;
+            for (int k = 0; k < 4; ++k) acc += M.V[i + 4 * k] * M.lambda[k] * M.V[j + 4 * k];
+            Q[4 * i + j] = M.inv_sqrt_pi[i] * acc * M.sqrt_pi[j];
+            if (i == j) mu = std::max(mu, std::fabs(Q[4 * i + j]));
+            else qmin = std::min(qmin, Q[4 * i + j]);
+        }
+    double rmin = INFINITY, rmax = 0.0;
+    bool zero_rate = false;
+    for (int c = 0; c < M.n_clv; ++c) {
+        const double r = M.rates[M.cat_of_clv[c]];
+        if (r > 0.0) {
+            rmin = std::min(rmin, r);
+            rmax = std::max(rmax, r);
+        } else
+            zero_rate = true;
+    }
+    if (!(mu > 0.0) || !(qmin > 0.0) || !std::isfinite(mu) || !std::isfinite(rmin) || zero_rate) return; // b = inf: always guard
+    const double LOG2E = 1.4426950408889634;
+    for (size_t v = 0; v < n; ++v) {
+        const double t = blen[v];
+        if (!(t > 0.0) || !std::isfinite(t)) continue;
+        // smallest entry: worst at the slowest category; smallest diagonal entry: worst at the fastest
+        const double tau = rmin * t, ts = std::min(tau, 1.0 / mu);
+        const double floor_bits = mu * ts * LOG2E - std::log2(ts * qmin); // -log2(e^{-mu t*} t* q)
+        b[v] = floor_bits + 1.0;
+        bd[v] = std::min(mu * rmax * t * LOG2E, floor_bits) + 1.0;
+    }
+}
 
 // Launch geometry / shared-memory carve-up for a schedule.
 struct SweepGeom {
@@ -253,7 +397,7 @@ struct SweepGeom {
         level_bytes = (size_t)n_consumers * SW_R * 32;
         stage_bytes = (S.rec_cap + 2 * 4 * Q + 127) / 128 * 128;
         const int want_levels = std::max(S.n_levels, 1);
-        for (n_stages = 8; n_stages >= 2; --n_stages) {
+        for (n_stages = 8; n_stages >= 2; n_stages /= 2) { // a power of two: the kernel wraps with a mask
             size_t fixed = SW_BAR_BYTES + (size_t)n_stages * stage_bytes;
             if (fixed + level_bytes > smem_max) continue;
             smem_levels = (int)std::min<size_t>((smem_max - fixed) / level_bytes, (size_t)want_levels);

@@ -139,6 +139,45 @@ def test_high_arity_with_deep_subtrees(emu_lib, k, depth):
     assert _cases.check_asr(emu_lib, case, flags=capi.FLAG_LEVEL_KERNELS) == 0
 
 
+def test_guard_plan_matches_guard_everywhere(emu_lib, monkeypatch):
+    """The host places the underflow guard only where its bound on the accumulated shrink needs it
+    (sweep_sched.h plan_guards).  Rescaling is an exact power of two, so the placement changes no CLV bit: the
+    per-pattern lnL agrees with the guard-after-every-node run to round-off of the final logarithm."""
+    case = workloads.make_case(700, 24, model="gtr_i_g4", seed=31)
+    a = _cases.check_lnl(emu_lib, case)
+    assert 0 < a[2]["sweep_guards"] < 0.25 * a[2]["n_internal"] and a[2]["sweep_normouts"] == 0
+    monkeypatch.setenv("PHB_SWEEP_GUARD_ALL", "1")
+    b = _cases.check_lnl(emu_lib, case)
+    assert b[2]["sweep_guards"] == b[2]["n_internal"]
+    assert np.max(np.abs(a[1] - b[1])) < 1e-9 and a[1].min() < -300
+
+
+def test_guard_plan_extreme_branch_lengths(emu_lib):
+    """Branches of 1e-30 .. 1e-3 under a very skewed Gamma (alpha = 0.05: the slowest category's rate is ~1e-12) make
+    single edges able to shrink a CLV by hundreds of bits: their children are normalised on completion."""
+    rng = np.random.default_rng(77)
+    case = workloads.make_case(120, 40, model="gtr_g4", seed=32)
+    ft = case.ft
+    ft["blen"] = np.where(rng.random(ft["n_nodes"]) < 0.5, 10.0 ** rng.uniform(-30, -3, ft["n_nodes"]), ft["blen"]).astype(np.float32).astype(np.float64)
+    case.model = RefModel.gtr(workloads.PI, workloads.GTR_RATES).with_gamma(0.05, 4)
+    rngp = np.random.default_rng(78)
+    case.patterns = workloads.simulate_patterns(dict(ft, preorder=_preorder(ft)), case.model, 40, rngp)
+    case.patterns[rngp.random(case.patterns.shape) < 0.3] = ord("A")  # conflicts across near-zero branches
+    tot, per, st = _cases.check_lnl(emu_lib, case)
+    assert st["sweep_normouts"] > 0
+    _cases.check_lnl(emu_lib, case, flags=capi.FLAG_LEVEL_KERNELS)
+
+
+def _preorder(ft):
+    pre, st = [], [int(ft["root"])]
+    co, ch = ft["child_off"], ft["children"]
+    while st:
+        v = st.pop()
+        pre.append(v)
+        st.extend(reversed(ch[co[v]:co[v + 1]].tolist()))
+    return np.asarray(pre, np.int32)
+
+
 def test_reference_fixture_and_internal_row(emu_lib):
     # integration_test.rs:14-17 + :663 — row C names an internal node: ignored by pruning, never validated
     tree = parse_newick("((A:0.601,B:0.301)C:0.100,D:0.200)E:0.001;")
