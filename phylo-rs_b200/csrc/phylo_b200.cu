@@ -240,7 +240,7 @@ struct Device {
     int64_t p_begin = 0, P = 0, P_pad = 0; // shard of the global pattern range
     DevBuf tips, mult, leaf_ls, inv_mask, per_pattern, row_invalid, Pmat, blen, clv, scale, cat_ll,
         partials, total, ops, gops, gkids, dops, dkids, leaf_rows, states, posteriors, staging,
-        sim_pre, sim_parent, sim_depth, sim_leafrow, sim_stack, scratch, sw_descs, sw_blocks, sw_stream, sw_gstack,
+        sim_pre, sim_parent, sim_depth, sim_leafrow, sim_stack, scratch, sw_descs, sw_opoff, sw_blocks, sw_stream, sw_gstack,
         sw_err, sw_ops, uops, ukids, lnP, jbest, nni_upper, nni_uexps, nni_jobs, nni_rows, nni_exps, nni_partials, nni_totals, nni_moves, nni_steps, nni_need;
     bool sweep_uploaded = false;
     bool sweep_ops_stale = false; // the guard flags of the op table changed since the last upload
@@ -627,39 +627,45 @@ int run_tile_joint(phb_ctx *ctx, Device &d, const ModelDev &M, int64_t tile_off,
 
 // ---- fused sweep (sweep.cuh) ---------------------------------------------------------------------
 // (Re)builds the op stream for the current tree and category count and uploads it to every device.
-int ensure_sweep(phb_ctx *ctx, const ModelDev &M)
+int ensure_sweep(phb_ctx *ctx, const ModelDev &M, bool store)
 {
     const TreeSched &T = ctx->tree;
     SweepSched &S = ctx->sweep;
     int64_t shard_P = 0;
     for (Device &d : ctx->devs) shard_P = std::max(shard_P, d.P);
-    if (S.valid && S.n_clv == M.n_clv && ctx->sweep_geom.planned_P != shard_P) {
-        size_t smem_max = ctx->devs[0].smem_optin;
-        for (Device &d : ctx->devs) smem_max = std::min(smem_max, d.smem_optin);
-        if (!ctx->sweep_geom.plan(S, smem_max, shard_P, std::max(ctx->devs[0].sm_count, 1)))
-            return ctx->fail(PHB_ERR_INVALID_MODEL_PARAMETER, "sweep: %d CLV categories do not fit one CTA", M.n_clv);
+    size_t smem_max = ctx->devs[0].smem_optin;
+    for (Device &d : ctx->devs) smem_max = std::min(smem_max, d.smem_optin);
+    // the plain sweep folds cherries into their parents' ops (sweep_sched.h); the storing one needs every node's CLV
+    const bool collapse = !store && !getenv("PHB_SWEEP_NO_COLLAPSE");
+    std::vector<double> gb, gbd;
+    std::vector<char> no_collapse;
+    const bool replan = !S.valid || S.n_clv != M.n_clv || S.collapsed_build != collapse || !ctx->sweep_guards_valid;
+    if (replan) { // per-edge shrink bounds: which cherries may be folded, where the underflow guard runs
+        sweep_guard_bounds(M, T.blen, gb, gbd);
+        if (collapse) sweep_no_collapse(T.child_off, T.children, gb, gbd, no_collapse);
     }
-    if (!S.valid || S.n_clv != M.n_clv) {
+    if (!S.valid || S.n_clv != M.n_clv || S.collapsed_build != collapse || (replan && collapse && no_collapse != S.built_no_collapse)) {
         for (Device &d : ctx->devs) { // the old host image may still be in flight
             cudaSetDevice(d.ordinal);
             cudaStreamSynchronize(d.stream);
             d.sweep_uploaded = false;
         }
-        S.build(T.n, T.root, T.child_off, T.children, T.leaf_row, M.n_clv, T.slot);
+        S.build(T.n, T.root, T.child_off, T.children, T.leaf_row, M.n_clv, T.slot, collapse, no_collapse);
+        S.built_no_collapse = no_collapse;
         ctx->sweep_guards_valid = false;
+        ctx->sweep_geom.planned_P = -1;
         if (getenv("PHB_SWEEP_TRACE"))
-            fprintf(stderr, "sweep schedule: ops %d (TT %d TI %d II %d APPLY %d MULTIP %d MULPOP %d LOADTIP %d) pushes %d "
-                            "register siblings %d levels %d stream %zu B\n", S.n_ops, S.count_kind[0], S.count_kind[1],
-                    S.count_kind[2], S.count_kind[3], S.count_kind[4], S.count_kind[5], S.count_kind[6], S.n_push,
-                    S.n_reg_sibling, S.n_levels, S.stream_bytes);
-        size_t smem_max = ctx->devs[0].smem_optin;
-        for (Device &d : ctx->devs) smem_max = std::min(smem_max, d.smem_optin);
+            fprintf(stderr, "sweep schedule: ops %d (TT %d TI %d II %d TS %d SI %d APPLY %d MULTIP %d MULPOP %d LOADTIP %d) pushes %d "
+                            "register siblings %d levels %d stream %zu B record cap %d B rows %d\n", S.n_ops, S.count_kind[SW_TT],
+                    S.count_kind[SW_TI], S.count_kind[SW_II], S.count_kind[SW_TS], S.count_kind[SW_SI], S.count_kind[SW_APPLY],
+                    S.count_kind[SW_MULTIP], S.count_kind[SW_MULPOP], S.count_kind[SW_LOADTIP], S.n_push, S.n_reg_sibling,
+                    S.n_levels, S.stream_bytes, S.rec_cap, S.max_rows);
+    }
+    if (ctx->sweep_geom.planned_P != shard_P) {
         if (!ctx->sweep_geom.plan(S, smem_max, shard_P, std::max(ctx->devs[0].sm_count, 1)))
             return ctx->fail(PHB_ERR_INVALID_MODEL_PARAMETER, "sweep: %d CLV categories do not fit one CTA", M.n_clv);
     }
     if (!ctx->sweep_guards_valid) { // branch lengths or rates changed: re-plan where the underflow guard runs
-        std::vector<double> gb, gbd;
-        sweep_guard_bounds(M, T.blen, gb, gbd);
         std::vector<uint32_t> before(S.ops.size());
         for (size_t k = 0; k < S.ops.size(); ++k) before[k] = S.ops[k].w0;
         for (Device &d : ctx->devs) // the host image of the op table may still be in flight
@@ -680,11 +686,13 @@ int ensure_sweep(phb_ctx *ctx, const ModelDev &M)
         if (d.sweep_uploaded && !d.sweep_ops_stale) continue;
         CU(cudaSetDevice(d.ordinal));
         if (!d.sweep_uploaded) {
-            CU(d.sw_descs.ensure(sizeof(SweepDesc) * S.descs.size()));
+            CU(d.sw_descs.ensure(sizeof(SweepStage) * S.stages.size()));
+            CU(d.sw_opoff.ensure(sizeof(uint64_t) * std::max<size_t>(S.op_off.size(), 1)));
             CU(d.sw_blocks.ensure(sizeof(SweepBlock) * S.blocks.size()));
             CU(d.sw_stream.ensure(S.stream_bytes + 16));
             CU(d.sw_err.ensure(sizeof(unsigned int)));
-            CU(cudaMemcpyAsync(d.sw_descs.p, S.descs.data(), sizeof(SweepDesc) * S.descs.size(), cudaMemcpyHostToDevice, d.stream));
+            CU(cudaMemcpyAsync(d.sw_descs.p, S.stages.data(), sizeof(SweepStage) * S.stages.size(), cudaMemcpyHostToDevice, d.stream));
+            CU(cudaMemcpyAsync(d.sw_opoff.p, S.op_off.data(), sizeof(uint64_t) * S.op_off.size(), cudaMemcpyHostToDevice, d.stream));
             CU(cudaMemcpyAsync(d.sw_blocks.p, S.blocks.data(), sizeof(SweepBlock) * S.blocks.size(), cudaMemcpyHostToDevice, d.stream));
             CU(d.sw_ops.ensure(sizeof(SweepOp) * S.ops.size()));
             CU(cudaMemsetAsync(d.sw_err.p, 0, sizeof(unsigned int), d.stream));
@@ -704,7 +712,7 @@ int launch_sweep_transition(phb_ctx *ctx, Device &d, const ModelDev &M)
     int nthreads = (int)S.blocks.size() * M.n_clv + S.n_ops;
     PHB_LAUNCH(sweep_transition_kernel, dim3((nthreads + 127) / 128), dim3(128), d.stream, d.sw_blocks.as<SweepBlock>(),
                (int)S.blocks.size(), d.blen.as<double>(), M, d.sw_stream.as<unsigned char>(), d.sw_ops.as<SweepOp>(),
-               d.sw_descs.as<SweepDesc>(), S.n_ops);
+               d.sw_opoff.as<uint64_t>(), S.n_ops);
     CHECK_LAUNCH();
     return PHB_OK;
 }
@@ -724,14 +732,15 @@ int launch_sweep_range(phb_ctx *ctx, Device &d, const ModelDev &M, const SweepGe
     SweepParams sp;
     memset(&sp, 0, sizeof sp);
     sp.ops = d.sw_ops.as<SweepOp>();
-    sp.descs = d.sw_descs.as<SweepDesc>();
+    sp.stages = d.sw_descs.as<SweepStage>();
+    sp.n_stage_descs = S.n_stage_descs;
     sp.stream = d.sw_stream.as<unsigned char>();
     sp.n_ops = S.n_ops;
     sp.Q = G.Q;
     sp.n_consumers = G.n_consumers;
     sp.n_stages = G.n_stages;
     sp.stage_bytes = G.stage_bytes;
-    sp.rec_cap = (S.rec_cap + 15) / 16 * 16;
+    sp.rec_cap = (S.stage_rec_cap + 15) / 16 * 16;
     sp.smem_levels = G.smem_levels;
     sp.g_levels = G.g_levels;
     sp.gstack = d.sw_gstack.as<double>();
@@ -813,7 +822,7 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
     const bool asr_sweep = asr && !joint && !(ctx->flags & PHB_FLAG_LEVEL_KERNELS) && T.n_internal > 0 && M.n_clv > 0 &&
                            M.n_clv <= SW_MAX_CONSUMERS / 8;
     if (use_sweep || asr_sweep) {
-        rc = ensure_sweep(ctx, M);
+        rc = ensure_sweep(ctx, M, asr_sweep);
         if (rc) return rc;
     }
     Device &d0 = ctx->devs[0];
@@ -822,7 +831,7 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
     const bool timing = ctx->flags & PHB_FLAG_TIMING;
     for (Device &d : ctx->devs) {
-        const int64_t wave = asr_sweep ? (int64_t)std::max(d.sm_count, 1) * 4 * ((SW_MAX_CONSUMERS / M.n_clv) & ~3) : 0;
+        const int64_t wave = asr_sweep ? (int64_t)std::max(d.sm_count, 1) * 4 * sweep_q_max(M.n_clv) : 0;
         rc = plan_device(ctx, d, M, asr, want_post, use_sweep, wave);
         if (rc) return rc;
     }
@@ -1349,7 +1358,7 @@ void phb_ctx_destroy(phb_ctx *ctx)
                           &d.clv, &d.scale, &d.cat_ll, &d.partials, &d.total, &d.ops, &d.gops, &d.gkids, &d.dops,
                           &d.dkids, &d.leaf_rows, &d.states, &d.posteriors, &d.staging, &d.sim_pre, &d.sim_parent,
                           &d.sim_depth, &d.sim_leafrow, &d.sim_stack, &d.scratch, &d.sw_descs, &d.sw_blocks,
-                          &d.sw_stream, &d.sw_gstack, &d.sw_err, &d.sw_ops, &d.uops, &d.ukids, &d.lnP, &d.jbest,
+                          &d.sw_stream, &d.sw_gstack, &d.sw_err, &d.sw_opoff, &d.sw_ops, &d.uops, &d.ukids, &d.lnP, &d.jbest,
                           &d.nni_upper, &d.nni_uexps, &d.nni_jobs, &d.nni_rows, &d.nni_exps, &d.nni_partials, &d.nni_totals, &d.nni_moves, &d.nni_steps, &d.nni_need};
         for (DevBuf *b : bufs) b->release();
         for (auto &ep : d.ev_pool) {
@@ -1916,7 +1925,7 @@ int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns
         if (d.P == 0) continue;
         CU(cudaSetDevice(d.ordinal));
         const int n_sm = std::max(d.sm_count, 1);
-        const int q_max = (SW_MAX_CONSUMERS / M.n_clv) & ~3;
+        const int q_max = sweep_q_max(M.n_clv);
         const int64_t pass = (int64_t)n_sm * 4 * q_max;
         static const int chunk_passes = [] { const char *e = getenv("PHB_HOST_CHUNK_PASSES"); int v = e ? atoi(e) : 1; return v >= 1 && v <= 16 ? v : 1; }();
         const int64_t chunk = round_up(chunk_passes * pass, 64);
@@ -1932,7 +1941,7 @@ int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns
         rc = upload_tree(ctx);
         if (rc) return drain(rc);
     }
-    rc = ensure_sweep(ctx, M);
+    rc = ensure_sweep(ctx, M, false);
     if (rc) return drain(rc);
     ctx->stats.clv_launches = 0;
     const SweepSched &S = ctx->sweep;

@@ -35,7 +35,13 @@ enum SweepKind : int32_t {
     SW_MULTIP = 4,  // cur = cur * tip(A)
     SW_MULPOP = 5,  // cur = cur * pop(level)
     SW_LOADTIP = 6, // cur = tip(A)                             [optional push of cur first]
+    SW_TS = 7,      // cur = tip(A) * super(B)                  [optional push of cur first]
+    SW_SI = 8,      // cur = super(A) * (P_B cur)
 };
+// dispatch code of an op: 2 * kind + 1 when the op works on / takes its pending operand from the second accumulator
+// `u` -- dense, so that the op loop's switch becomes one indexed branch
+constexpr int SW_CODE_U = 1;
+__host__ __device__ constexpr int sw_code(int kind, bool u) { return 2 * kind + (u ? SW_CODE_U : 0); }
 constexpr int SW_FLAG_PUSH = 1;    // push cur to `level` before executing (TT / LOADTIP only)
 constexpr int SW_FLAG_DONE = 2;    // this op completes a node (the storing variant writes its CLV out)
 constexpr int SW_FLAG_U = 4;       // TT / TI: operate on the second register accumulator `u` (cur untouched)
@@ -47,10 +53,14 @@ constexpr int SW_FLAG_GUARD = 32;  // after the op: rescale the sites whose maxi
                                    // where the bound on the accumulated shrink requires it, sweep_sched.h plan_guards)
 constexpr int SW_FLAG_NORMOUT = 64; // after the op: rescale every site to max in [1,2) (child of an op whose own
                                     // worst-case shrink leaves no room for a lazily scaled operand)
+constexpr int SW_FLAG_FIRST = 128; // first op of a ring stage: wait for the stage's data before touching it
+constexpr int SW_FLAG_LAST = 256;  // last op of a ring stage: hand the stage back to the producer afterwards
 
 constexpr int SW_P_BYTES = 128;    // 4x4 f64 row-major
-constexpr int SW_TAB_BYTES = 512;  // 16 masks x 4 f64, slot order (kernels.cuh mask_to_slot)
-constexpr int SW_TAB2_BYTES = 800; // cherry table: 5 x 5 code pairs (A,C,G,T,N/gap) x 4 f64, row = a + 5 b
+// Tables are PLANAR with a 16-byte row stride: states 0,1 of all rows, then states 2,3.  The rows that carry almost
+// every site (A,C,G,T; the pairs a == b) then fall in different bank groups of a quarter-warp's LDS.128.
+constexpr int SW_TIP_BYTES = 160;  // tip table: the 5 codes A,C,G,T,N/gap x 4 f64 (any other ambiguity code = sum of rows)
+constexpr int SW_TAB2_BYTES = 800; // cherry / super-tip table: 5 x 5 code pairs x 4 f64, row = a + 5 b
 constexpr int SW_BAR_BYTES = 512;  // mbarrier area at the start of dynamic shared memory
 constexpr int SW_HDR_BYTES = 16;   // every record starts with the header of the NEXT op
 
@@ -58,26 +68,33 @@ constexpr int SW_HDR_BYTES = 16;   // every record starts with the header of the
 // k + 1 to the front of record k, so a consumer picks up the next op's header from the ring stage it is working
 // on -- one warp-uniform LDS whose latency the current op's arithmetic hides -- and only the first header of a
 // site block comes from global memory.
-//   w0 = code | flags << 8 | level << 16      w1 = per-category record bytes | szA << 16 (operand B at +szA)
-//        code = kind, + 8 when the op works on / takes its pending operand from the second accumulator `u`
+//   w0 = code | flags << 8 | level << 18     w1 = per-category record bytes | szA << 16 (operand B at +szA)
+//        code = sw_code(kind, works on / takes its pending operand from the second accumulator `u`)
+//   w3 = byte offset of the op's record inside its ring stage | first tip-code row slot of the op << 16
 //   w2 = CLV slot of the node this op completes (valid with SW_FLAG_DONE; used by the storing variant)
 struct SweepOp {
     uint32_t w0, w1, w2, w3;
 };
-// Producer-side descriptor (global memory): where the record is and which tip rows it needs.
-struct SweepDesc {
-    uint64_t rec_off;  // byte offset of the record in the stream
+// Producer-side descriptor of one ring stage (global memory): several consecutive ops share a stage -- their records
+// are adjacent in the stream and arrive with ONE bulk copy, their tip-code rows with one copy each -- so the
+// full / empty handshake, the stage arithmetic and the producer's issue work are paid once per stage, not per op.
+constexpr int SW_STAGE_ROWS = 8;        // tip-code row slots per stage
+constexpr int SW_STAGE_REC_BYTES = 8192; // record bytes per stage (at least the largest single record)
+struct SweepStage {
+    uint64_t rec_off;  // byte offset of the stage's first record in the stream
     uint32_t rec_bytes;
-    int32_t rowA, rowB; // alignment rows of tip operands, -1 = none
-    int32_t pad[3];
+    int32_t n_rows;
+    int32_t rows[SW_STAGE_ROWS]; // alignment rows whose tip codes the stage's ops read, in slot order
 };
 // One operand block the transition kernel has to fill.
 struct SweepBlock {
     uint64_t dst_off; // byte offset of category 0's block; category c at dst_off + c * cat_stride
     uint32_t cat_stride;
     int32_t edge;     // dense node id whose branch length parametrises P
-    int32_t is_table; // 0: P(t) 4x4; 1: tip table of `edge`; 2: cherry table of (edge, edge2)
-    int32_t edge2;
+    int32_t is_table; // 0: P(t) 4x4; 1: tip table of `edge`; 2: cherry table tip(edge) (.) tip(edge2);
+                      // 3: super-tip table P(edge) * (tip(edge2) (.) tip(edge3))
+    int32_t edge2, edge3;
+    int32_t pad;
 };
 
 // ---- K1s: transition matrices / tip tables straight into the op-ordered stream --------------------
@@ -116,12 +133,12 @@ __device__ __forceinline__ double sw_masked(const double (&p)[16], int i, uint32
 __global__ void sweep_transition_kernel(const SweepBlock *__restrict__ blocks, int n_blocks,
                                         const double *__restrict__ blen, ModelDev M,
                                         unsigned char *__restrict__ stream, const SweepOp *__restrict__ ops,
-                                        const SweepDesc *__restrict__ descs, int n_ops)
+                                        const uint64_t *__restrict__ op_off, int n_ops)
 {
     int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= n_blocks * M.n_clv) {
         const int k = idx - n_blocks * M.n_clv;
-        if (k < n_ops) *reinterpret_cast<uint4 *>(stream + descs[k].rec_off) = *reinterpret_cast<const uint4 *>(ops + k + 1);
+        if (k < n_ops) *reinterpret_cast<uint4 *>(stream + op_off[k]) = *reinterpret_cast<const uint4 *>(ops + k + 1);
         return;
     }
     int b = idx / M.n_clv, cc = idx - b * M.n_clv;
@@ -134,22 +151,34 @@ __global__ void sweep_transition_kernel(const SweepBlock *__restrict__ blocks, i
 #pragma unroll
         for (int i = 0; i < 16; ++i) out[i] = p[i];
     } else if (blk.is_table == 1) {
-        for (uint32_t m = 0; m < 16; ++m) {
-            double *row = out + 4 * mask_to_slot(m);
+        for (uint32_t a = 0; a < 5; ++a) { // two planes of 5 x 16 bytes
+            double *lo = out + 2 * a, *hi = lo + SW_TIP_BYTES / 16;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) row[i] = sw_masked(p, i, m);
+            for (int i = 0; i < 2; ++i) {
+                lo[i] = sw_masked(p, i, code_mask(a));
+                hi[i] = sw_masked(p, i + 2, code_mask(a));
+            }
         }
     } else {
-        double q[16];
-        sw_transition(M, M.rates[cat] * blen[blk.edge2], q);
+        // tip(x) (.) tip(y) for the 25 code pairs; is_table == 3: carried through the cherry's own edge
+        double x[16], y[16];
+        const bool super = blk.is_table == 3;
+        sw_transition(M, M.rates[cat] * blen[super ? blk.edge2 : blk.edge], x);
+        sw_transition(M, M.rates[cat] * blen[super ? blk.edge3 : blk.edge2], y);
         for (uint32_t a = 0; a < 5; ++a)
             for (uint32_t c = 0; c < 5; ++c) { // two planes of 25 x 16 bytes: states 0,1 | states 2,3
-                double *lo = out + 2 * (a + 5 * c), *hi = lo + SW_TAB2_BYTES / 16;
+                double ch[4], w[4];
 #pragma unroll
-                for (int i = 0; i < 2; ++i) {
-                    lo[i] = sw_masked(p, i, code_mask(a)) * sw_masked(q, i, code_mask(c));
-                    hi[i] = sw_masked(p, i + 2, code_mask(a)) * sw_masked(q, i + 2, code_mask(c));
+                for (int j = 0; j < 4; ++j) ch[j] = sw_masked(x, j, code_mask(a)) * sw_masked(y, j, code_mask(c));
+                if (super) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) w[i] = p[4 * i] * ch[0] + p[4 * i + 1] * ch[1] + p[4 * i + 2] * ch[2] + p[4 * i + 3] * ch[3];
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) w[i] = ch[i];
                 }
+                double *lo = out + 2 * (a + 5 * c), *hi = lo + SW_TAB2_BYTES / 16;
+                lo[0] = w[0]; lo[1] = w[1]; hi[0] = w[2]; hi[1] = w[3];
             }
     }
 }
@@ -295,14 +324,15 @@ constexpr int SW_MAX_CONSUMERS = PHB_SW_CONSUMERS; // consumer threads per CTA (
 
 struct SweepParams {
     const SweepOp *ops;
-    const SweepDesc *descs;
+    const SweepStage *stages;
     const unsigned char *stream;
     int n_ops;
+    int n_stage_descs; // ring stages one sweep of the tree consists of
     int Q;            // site quads per CTA; consumer threads = Q * n_clv
     int n_consumers;  // Q * n_clv
     int n_stages;     // ring depth (a power of two)
-    int stage_bytes;  // bytes per ring stage (record + two code rows)
-    int rec_cap;      // max record bytes (offset of the code rows inside a stage)
+    int stage_bytes;  // bytes per ring stage (records + SW_STAGE_ROWS code rows)
+    int rec_cap;      // record bytes per stage (offset of the code rows inside a stage)
     int smem_levels;  // stack levels held in shared memory; deeper ones go to gstack
     int g_levels;     // levels available in gstack per CTA
     double *gstack;   // [cta][g_level][R][2][n_consumers] double2
@@ -340,21 +370,89 @@ __device__ __forceinline__ void sw_load_P(sw_sptr blk, double (&p)[16])
     }
 }
 
-// one 32-byte row of a tip table
-__device__ __forceinline__ void sw_load_row(sw_sptr tab, uint32_t row, double (&t)[4])
-{
-    const sw_sptr a = tab + 32u * row;
-    double2 x = sw_lds128(a), y = sw_lds128(a + 16u);
-    t[0] = x.x; t[1] = x.y; t[2] = y.x; t[3] = y.y;
-}
-// one row of a cherry table: states 0,1 in the first plane, 2,3 in the second (16-byte row stride: the four
-// rows a == b, which carry most sites, fall in four different bank groups)
-__device__ __forceinline__ void sw_load_row2(sw_sptr tab, uint32_t row, double (&t)[4])
+// one row of a planar table: states 0,1 at tab + 16 row, states 2,3 one plane further
+__device__ __forceinline__ void sw_load_prow(sw_sptr tab, uint32_t plane, uint32_t row, double (&t)[4])
 {
     const sw_sptr a = tab + 16u * row;
-    double2 x = sw_lds128(a), y = sw_lds128(a + (uint32_t)(SW_TAB2_BYTES / 2));
+    double2 x = sw_lds128(a), y = sw_lds128(a + plane);
     t[0] = x.x; t[1] = x.y; t[2] = y.x; t[3] = y.y;
 }
+// a byte of w is > 4 (a code other than A,C,G,T,N/gap)  <=>  bit 3 set, or bit 2 together with bit 0 or 1
+__device__ __forceinline__ uint32_t sw_rare(uint32_t w) { return (w & 0x08080808u) | (w & 0x04040404u & ((w << 1) | (w << 2))); }
+// ---- partial ambiguity codes (R,Y,S,W,K,M,B,D,H,V): rare, kept OUT OF LINE so that their loops cost the op bodies
+// no registers.  Tip vector for such a code: the sum of the table rows of the code's states in ascending order -- the
+// order in which the reference's P * profile accumulates them, so the sum is bit-identical to the masked column sum
+// (likelihood.rs:121, alphabet.rs:44-64).
+struct sw_vec4 {
+    double t[4];
+};
+#ifdef PHB_HOST_EMU
+#define SW_NOINLINE __attribute__((noinline))
+#else
+#define SW_NOINLINE __noinline__
+#endif
+__device__ SW_NOINLINE sw_vec4 sw_tip_slow(sw_sptr tab, uint32_t code)
+{
+    sw_vec4 o;
+    const uint32_t m = code_mask(code);
+    bool first = true;
+    for (uint32_t s = 0; s < 4; ++s) {
+        if (!((m >> s) & 1u)) continue;
+        double r[4];
+        sw_load_prow(tab, SW_TIP_BYTES / 2, s, r);
+        for (int i = 0; i < 4; ++i) o.t[i] = first ? r[i] : o.t[i] + r[i];
+        first = false;
+    }
+    if (first)
+        for (int i = 0; i < 4; ++i) o.t[i] = 0.0;
+    return o;
+}
+// Row of a 5x5 pair table for a pair with a partial code: the table is linear in each tip's profile, so it is the sum
+// of the rows of the codes' states (differs from product-of-sums by round-off only; the storing variant never comes
+// here for an explicit cherry, its records carry the two P(t)).
+__device__ SW_NOINLINE sw_vec4 sw_pair_slow(sw_sptr tab, uint32_t x, uint32_t y)
+{
+    sw_vec4 o;
+    const uint32_t mx = x <= 4u ? (x == 4u ? 15u : 1u << x) : code_mask(x), my = y <= 4u ? (y == 4u ? 15u : 1u << y) : code_mask(y);
+    bool first = true;
+    // a code among A,C,G,T,N/gap keeps its own row index (N/gap is one row, not four)
+    for (uint32_t b = 0; b < 4; ++b) {
+        if (!((my >> b) & 1u)) continue;
+        for (uint32_t a = 0; a < 4; ++a) {
+            if (!((mx >> a) & 1u)) continue;
+            double r[4];
+            sw_load_prow(tab, SW_TAB2_BYTES / 2, (x <= 4u ? x : a) + 5u * (y <= 4u ? y : b), r);
+            for (int i = 0; i < 4; ++i) o.t[i] = first ? r[i] : o.t[i] + r[i];
+            first = false;
+            if (x <= 4u) break;
+        }
+        if (y <= 4u) break;
+    }
+    if (first)
+        for (int i = 0; i < 4; ++i) o.t[i] = 0.0;
+    return o;
+}
+__device__ __forceinline__ void sw_tip_any(sw_sptr tab, uint32_t code, double (&t)[4])
+{
+    if (code <= 4u) sw_load_prow(tab, SW_TIP_BYTES / 2, code, t);
+    else {
+        const sw_vec4 o = sw_tip_slow(tab, code);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) t[i] = o.t[i];
+    }
+}
+__device__ __forceinline__ void sw_pair_any(sw_sptr tab, uint32_t x, uint32_t y, double (&t)[4])
+{
+    if (x <= 4u && y <= 4u) sw_load_prow(tab, SW_TAB2_BYTES / 2, x + 5u * y, t);
+    else {
+        const sw_vec4 o = sw_pair_slow(tab, x, y);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) t[i] = o.t[i];
+    }
+}
+
+struct sw_false { static constexpr bool value = false; };
+struct sw_true { static constexpr bool value = true; };
 
 // exact power-of-two rescale of one site's 4 states when the largest drops below 2^-256 (ALWAYS = false), or
 // unconditionally to a maximum in [1,2) (ALWAYS = true: SW_FLAG_NORM / SW_FLAG_NORMOUT)
@@ -407,32 +505,37 @@ sweep_kernel(SweepParams p, ModelDev M)
 
     if (tid >= prod_tid0) {
         // ===================== producer warp =====================
-        // Lane 0 waits for the stage and posts the byte count; lanes 0..2 then issue one bulk copy each (the
-        // record and the two tip-code rows).
+        // Lane 0 waits for the stage and posts the byte count; lanes 0..8 then issue one bulk copy each (the
+        // records of the stage's ops and up to eight tip-code rows).
         const int pl = tid - prod_tid0;
         uint32_t s = 0, parity = 1; // a fresh barrier passes a parity-1 wait
         const uint32_t rec_cap = (uint32_t)p.rec_cap;
+        const int n_sd = p.n_stage_descs;
+        const int my_row = pl >= 1 && pl <= SW_STAGE_ROWS ? pl - 1 : 0; // lane i + 1 copies row slot i
         for (int64_t b = blockIdx.x; b < p.n_blocks; b += gridDim.x) {
             const uint8_t *tip_base = p.tips + b * sites_per_block;
-            SweepDesc d = p.descs[0];
+            // this lane's view of the stage descriptor, one stage ahead: record (lane 0) or one row (lanes 1..8)
+            uint64_t rec_off = p.stages[0].rec_off;
+            uint32_t rec_bytes = p.stages[0].rec_bytes;
+            int n_rows = p.stages[0].n_rows, row = p.stages[0].rows[my_row];
 #pragma unroll 1
-            for (int k = 0; k < n_ops; ++k) {
-                const SweepDesc nd = p.descs[k + 1]; // the table carries one padding entry
+            for (int k = 0; k < n_sd; ++k) {
+                const SweepStage *nx = p.stages + k + 1; // the table carries one padding entry
+                const uint64_t n_rec_off = nx->rec_off;
+                const uint32_t n_rec_bytes = nx->rec_bytes;
+                const int n_n_rows = nx->n_rows, n_row = nx->rows[my_row];
                 const sw_sptr st = ring + s * stage_bytes;
-                const uint32_t bytes = d.rec_bytes + (d.rowA >= 0 ? code_bytes : 0u) + (d.rowB >= 0 ? code_bytes : 0u);
                 if (pl == 0) {
                     sw_mbar_wait(bars, n_stages + (int)s, parity);
-                    sw_mbar_expect_tx(bars, (int)s, bytes);
+                    sw_mbar_expect_tx(bars, (int)s, rec_bytes + (uint32_t)n_rows * code_bytes);
                 }
                 __syncwarp();
-                if (pl == 0) {
-                    if (d.rec_bytes) sw_bulk_g2s(st, p.stream + d.rec_off, d.rec_bytes, bars, (int)s); // MULPOP has no record
-                } else if (pl == 1) {
-                    if (d.rowA >= 0) sw_bulk_g2s(st + rec_cap, tip_base + (int64_t)d.rowA * p.P_pad, code_bytes, bars, (int)s);
-                } else if (pl == 2) {
-                    if (d.rowB >= 0) sw_bulk_g2s(st + rec_cap + code_bytes, tip_base + (int64_t)d.rowB * p.P_pad, code_bytes, bars, (int)s);
-                }
-                d = nd;
+                if (pl == 0) sw_bulk_g2s(st, p.stream + rec_off, rec_bytes, bars, (int)s);
+                else if (pl <= n_rows) sw_bulk_g2s(st + rec_cap + (uint32_t)(pl - 1) * code_bytes, tip_base + (int64_t)row * p.P_pad, code_bytes, bars, (int)s);
+                rec_off = n_rec_off;
+                rec_bytes = n_rec_bytes;
+                n_rows = n_n_rows;
+                row = n_row;
                 s = (s + 1u) & smask;
                 parity ^= (s == 0u) ? 1u : 0u;
             }
@@ -441,8 +544,7 @@ sweep_kernel(SweepParams p, ModelDev M)
     }
 
     // ===================== consumer warps =====================
-    const bool active = tid < p.n_consumers;
-    const int t = active ? tid : 0;   // inactive lanes of the last warp shadow thread 0 (no stores)
+    const int t = tid;                // n_consumers is a multiple of 32 (SweepGeom::plan): every consumer lane works
     const int cc = t / p.Q;           // CLV category of this thread
     const int q = t - cc * p.Q;       // site quad inside the block
     const int lane = tid & 31;
@@ -468,20 +570,24 @@ sweep_kernel(SweepParams p, ModelDev M)
         }
         uint4 hn = __ldg(optab); // header of the first op; every later one arrives with the previous op's record
 #pragma unroll 1
-        for (int k = 0; k < n_ops; ++k) {
+        for (int k = 0; k < n_ops;) { // one ring stage per trip: wait, run its ops, hand it back
+        const sw_sptr st = ring + s * stage_bytes;
+        sw_mbar_wait(bars, (int)s, parity);
+        uint32_t flags;
+#pragma unroll 1
+        do {
+            ++k;
             const uint4 h = hn;
-            const uint32_t code = h.x & 0xffu, flags = h.x >> 8;
-            const sw_sptr st = ring + s * stage_bytes;
-            const sw_sptr blkA = st + (uint32_t)SW_HDR_BYTES + (uint32_t)cc * (h.y & 0xffffu);
+            const uint32_t code = h.x & 0xffu;
+            flags = (h.x >> 8) & 0x3ffu;
+            const sw_sptr rec = st + (h.w & 0xffffu);
+            const sw_sptr blkA = rec + (uint32_t)SW_HDR_BYTES + (uint32_t)cc * (h.y & 0xffffu);
             const sw_sptr blkB = blkA + (h.y >> 16);
-            const sw_sptr codesA = st + code_off;
-            const sw_sptr codesB = codesA + code_bytes;
-            sw_mbar_wait(bars, (int)s, parity);
-            hn = sw_lds128u(st);
+            const sw_sptr codes0 = st + code_off + (h.w >> 16) * code_bytes; // this thread's four codes in the op's first row slot
+            hn = sw_lds128u(rec);
             // ---- the op bodies, written once over the accumulator they update ----
-            const int level = (int)((h.x >> 16) & 0xffu);
+            const int level = (int)(h.x >> 18);
             auto push = [&]() { // park the running result before a TT / LOADTIP overwrites it
-                if (!active) return;
                 if (level < smem_levels) {
                     uint32_t row_stride = row_stride0; // opaque here: keeps the seven multiples out of every op's prologue
                     SW_OPAQUE(row_stride);
@@ -523,42 +629,82 @@ sweep_kernel(SweepParams p, ModelDev M)
                     }
                 }
             };
-            // cherry: one row of the 5x5 product table per site when both codes are among A,C,G,T,N/gap (slots
-            // 0..4); a site with any other ambiguity code sums the masked columns of the two P(t) that follow the
-            // table, in the reference's order (rare, divergent)
+            // explicit cherry: one row of the 5x5 product table per site when both codes are among A,C,G,T,N/gap
+            // (slots 0..4).  Any other code: the storing variant's records carry the two P(t) and the masked column
+            // sums are formed in the reference's order; the plain records do not, and the table rows are summed.
             auto op_tt = [&](double (&acc)[SW_R][4]) {
-                const uint32_t ca = sw_lds32(codesA) & 0x0f0f0f0fu, cb = sw_lds32(codesB) & 0x0f0f0f0fu;
-                // a byte is <= 4  <=>  bit 3 is clear and bit 2 does not come with bit 0 or 1
-                const uint32_t bad = (ca & 0x08080808u) | (ca & 0x04040404u & ((ca << 1) | (ca << 2))) |
-                                     (cb & 0x08080808u) | (cb & 0x04040404u & ((cb << 1) | (cb << 2)));
-                const bool fast = bad == 0u;
-                if (fast) {
+                const uint32_t ca = sw_lds32(codes0) & 0x0f0f0f0fu, cb = sw_lds32(codes0 + code_bytes) & 0x0f0f0f0fu;
+                if ((sw_rare(ca) | sw_rare(cb)) == 0u) {
                     const uint32_t idx = ca + 5u * cb; // per byte a + 5 b <= 24: no carries
 #pragma unroll
-                    for (int r = 0; r < SW_R; ++r) sw_load_row2(blkA, (idx >> (8 * r)) & 0xffu, acc[r]);
-                } else {
+                    for (int r = 0; r < SW_R; ++r) sw_load_prow(blkA, SW_TAB2_BYTES / 2, (idx >> (8 * r)) & 0xffu, acc[r]);
+                } else if ((h.y & 0xffffu) > (uint32_t)SW_TAB2_BYTES) { // the record carries the two P(t) behind the table
                     double PA[16], PB[16];
-                    sw_load_P(blkB, PA);
-                    sw_load_P(blkB + SW_P_BYTES, PB);
+                    sw_load_P(blkA + SW_TAB2_BYTES, PA);
+                    sw_load_P(blkA + SW_TAB2_BYTES + SW_P_BYTES, PB);
 #pragma unroll
                     for (int r = 0; r < SW_R; ++r) {
                         const uint32_t ma = code_mask((ca >> (8 * r)) & 15u), mb = code_mask((cb >> (8 * r)) & 15u);
 #pragma unroll
                         for (int i = 0; i < 4; ++i) acc[r][i] = sw_masked(PA, i, ma) * sw_masked(PB, i, mb);
                     }
+                } else {
+#pragma unroll
+                    for (int r = 0; r < SW_R; ++r) sw_pair_any(blkA, (ca >> (8 * r)) & 15u, (cb >> (8 * r)) & 15u, acc[r]);
                 }
             };
-            auto op_ti = [&](double (&acc)[SW_R][4]) {
-                const uint32_t ca = sw_lds32(codesA);
+            // tip x super-tip: two lookups and a product, no matrix-vector product at all
+            auto op_ts = [&](double (&acc)[SW_R][4]) {
+                const uint32_t ca = sw_lds32(codes0) & 0x0f0f0f0fu, cx = sw_lds32(codes0 + code_bytes) & 0x0f0f0f0fu,
+                               cy = sw_lds32(codes0 + 2u * code_bytes) & 0x0f0f0f0fu;
+                if ((sw_rare(ca) | sw_rare(cx) | sw_rare(cy)) == 0u) {
+                    const uint32_t idx = cx + 5u * cy;
+#pragma unroll
+                    for (int r = 0; r < SW_R; ++r) {
+                        double ta[4], w[4];
+                        sw_load_prow(blkA, SW_TIP_BYTES / 2, (ca >> (8 * r)) & 0xffu, ta);
+                        sw_load_prow(blkB, SW_TAB2_BYTES / 2, (idx >> (8 * r)) & 0xffu, w);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) acc[r][i] = ta[i] * w[i];
+                    }
+                } else {
+#pragma unroll
+                    for (int r = 0; r < SW_R; ++r) {
+                        double ta[4], w[4];
+                        sw_tip_any(blkA, (ca >> (8 * r)) & 15u, ta);
+                        sw_pair_any(blkB, (cx >> (8 * r)) & 15u, (cy >> (8 * r)) & 15u, w);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) acc[r][i] = ta[i] * w[i];
+                    }
+                }
+            };
+            // SUPER = false: tip(A) (.) (P_B acc);  SUPER = true: super-tip(A) (.) (P_B acc)
+            auto op_ti = [&](double (&acc)[SW_R][4], auto super_tag) {
+                constexpr bool SUPER = decltype(super_tag)::value;
+                const uint32_t ca = sw_lds32(codes0) & 0x0f0f0f0fu;
+                const uint32_t cb = SUPER ? (sw_lds32(codes0 + code_bytes) & 0x0f0f0f0fu) : 0u;
                 double P[16];
                 sw_load_P(blkB, P);
+                if ((sw_rare(ca) | sw_rare(cb)) == 0u) {
+                    const uint32_t idx = ca + 5u * cb;
 #pragma unroll
-                for (int r = 0; r < SW_R; ++r) {
-                    double y[4], ta[4];
-                    sw_load_row(blkA, (ca >> (8 * r)) & 15u, ta);
-                    sw_matvec(P, acc[r], y);
+                    for (int r = 0; r < SW_R; ++r) {
+                        double y[4], ta[4];
+                        sw_load_prow(blkA, SUPER ? SW_TAB2_BYTES / 2 : SW_TIP_BYTES / 2, (idx >> (8 * r)) & 0xffu, ta);
+                        sw_matvec(P, acc[r], y);
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) acc[r][i] = ta[i] * y[i];
+                        for (int i = 0; i < 4; ++i) acc[r][i] = ta[i] * y[i];
+                    }
+                } else {
+#pragma unroll
+                    for (int r = 0; r < SW_R; ++r) {
+                        double y[4], ta[4];
+                        if (SUPER) sw_pair_any(blkA, (ca >> (8 * r)) & 15u, (cb >> (8 * r)) & 15u, ta);
+                        else sw_tip_any(blkA, (ca >> (8 * r)) & 15u, ta);
+                        sw_matvec(P, acc[r], y);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) acc[r][i] = ta[i] * y[i];
+                    }
                 }
             };
             // v = (P_A u) * (P_B v).  The pending operand is ALWAYS in `u`: either the chain-shaped sibling was
@@ -601,35 +747,41 @@ sweep_kernel(SweepParams p, ModelDev M)
                     for (int r = 0; r < SW_R; ++r) sw_rescale(acc[r], sc[r]);
                 }
             };
-            const bool resc = flags & (SW_FLAG_GUARD | SW_FLAG_NORMOUT);
             switch (code) { // dense dispatch code, precomputed by the host scheduler
-            case SW_TI:
-                op_ti(v);
-                if (resc) guard(v);
+            case sw_code(SW_TI, false):
+                op_ti(v, sw_false());
                 break;
-            case SW_TI | 8:
-                op_ti(u);
-                if (resc) guard(u);
+            case sw_code(SW_TI, true):
+                op_ti(u, sw_false());
                 break;
-            case SW_II | 8:
+            case sw_code(SW_SI, false):
+                op_ti(v, sw_true());
+                break;
+            case sw_code(SW_SI, true):
+                op_ti(u, sw_true());
+                break;
+            case sw_code(SW_II, true):
                 op_ii();
-                if (resc) guard(v);
                 break;
-            case SW_TT | 8:
-                op_tt(u);
-                if (resc) guard(u);
-                break;
-            case SW_TT:
-                if (flags & SW_FLAG_PUSH) push();
-                op_tt(v);
-                if (resc) guard(v);
-                break;
-            case SW_II:
+            case sw_code(SW_II, false):
                 pop(u);
                 op_ii();
-                if (resc) guard(v);
                 break;
-            case SW_APPLY: {
+            case sw_code(SW_TS, true):
+                op_ts(u);
+                break;
+            case sw_code(SW_TS, false):
+                if (flags & SW_FLAG_PUSH) push();
+                op_ts(v);
+                break;
+            case sw_code(SW_TT, true):
+                op_tt(u);
+                break;
+            case sw_code(SW_TT, false):
+                if (flags & SW_FLAG_PUSH) push();
+                op_tt(v);
+                break;
+            case sw_code(SW_APPLY, false): {
                 if (flags & SW_FLAG_NORM) {
 #pragma unroll
                     for (int r = 0; r < SW_R; ++r) sw_rescale<true>(v[r], sc[r]);
@@ -643,36 +795,37 @@ sweep_kernel(SweepParams p, ModelDev M)
 #pragma unroll
                     for (int i = 0; i < 4; ++i) v[r][i] = y[i];
                 }
-                if (resc) guard(v);
                 break;
             }
-            case SW_MULTIP:
-            case SW_LOADTIP: {
+            case sw_code(SW_MULTIP, false):
+            case sw_code(SW_LOADTIP, false): {
                 if (flags & SW_FLAG_PUSH) push();
-                const uint32_t ca = sw_lds32(codesA);
+                const uint32_t ca = sw_lds32(codes0) & 0x0f0f0f0fu;
 #pragma unroll
                 for (int r = 0; r < SW_R; ++r) {
                     double ta[4];
-                    sw_load_row(blkA, (ca >> (8 * r)) & 15u, ta);
+                    sw_tip_any(blkA, (ca >> (8 * r)) & 15u, ta);
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) v[r][i] = (code == SW_LOADTIP) ? ta[i] : v[r][i] * ta[i];
+                    for (int i = 0; i < 4; ++i) v[r][i] = (code == (uint32_t)sw_code(SW_LOADTIP, false)) ? ta[i] : v[r][i] * ta[i];
                 }
-                if (resc) guard(v);
                 break;
             }
-            case SW_MULPOP:
+            case sw_code(SW_MULPOP, false):
                 pop(u);
 #pragma unroll
                 for (int r = 0; r < SW_R; ++r)
 #pragma unroll
                     for (int i = 0; i < 4; ++i) v[r][i] *= u[r][i];
-                if (resc) guard(v);
                 break;
             default:
                 if (lane == 0) atomicOr(p.error_flag, 1u);
                 break;
             }
-            if (STORE && (flags & SW_FLAG_DONE) && active) {
+            if (flags & (SW_FLAG_GUARD | SW_FLAG_NORMOUT)) { // the accumulator the op wrote: u for the U-flagged chain ops
+                if (flags & SW_FLAG_U) guard(u);
+                else guard(v);
+            }
+            if (STORE && (flags & SW_FLAG_DONE)) {
                 const int64_t rel = b * sites_per_block + 4 * q; // first of this thread's 4 patterns, launch-relative
                 double *dst = p.clv_out + (size_t)h.z * p.slot_stride + (size_t)cc * 4 * p.tile_pad + (size_t)rel;
                 const bool use_u = flags & SW_FLAG_U;
@@ -692,9 +845,10 @@ sweep_kernel(SweepParams p, ModelDev M)
                         }
                 }
             }
-            sw_mbar_arrive_elect(bars, n_stages + (int)s); // every lane's reads of the stage have been consumed by now
-            s = (s + 1u) & smask;
-            parity ^= (s == 0u) ? 1u : 0u;
+        } while (!(flags & SW_FLAG_LAST));
+        sw_mbar_arrive_elect(bars, n_stages + (int)s); // every lane's reads of the stage have been consumed by now
+        s = (s + 1u) & smask;
+        parity ^= (s == 0u) ? 1u : 0u;
         }
 
         // ---- root: per-category log-likelihoods, category mix, weights, block reduction ----
@@ -703,7 +857,7 @@ sweep_kernel(SweepParams p, ModelDev M)
         sw_consumer_barrier(n_cons_warps * 32); // warps drift: nobody may still be using stack level 0
         double *xch = reinterpret_cast<double *>(stack);
         const int64_t site0 = b * sites_per_block + 4 * q;
-        if (active) {
+        {
             const int cat = M.cat_of_clv[cc];
 #pragma unroll
             for (int r = 0; r < SW_R; ++r) {
@@ -740,7 +894,7 @@ sweep_kernel(SweepParams p, ModelDev M)
         }
         sw_consumer_barrier(n_cons_warps * 32);
         double contrib = 0.0;
-        if (active && cc == 0) {
+        if (cc == 0) {
 #pragma unroll
             for (int r = 0; r < SW_R; ++r) {
                 const int64_t site = site0 + r;

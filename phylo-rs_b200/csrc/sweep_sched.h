@@ -26,11 +26,15 @@ struct SweepSched {
     int n_ops = 0;
     int n_levels = 0;   // stack levels used (need(root))
     int rec_cap = 0;    // largest record
+    int max_rows = 0;   // most tip-code rows any op needs (<= 3: a tip and a super-tip)
+    int n_stage_descs = 0;
     size_t stream_bytes = 0;
-    std::vector<SweepDesc> descs;
+    std::vector<SweepStage> stages;      // ring stages (+ one padding entry): the producer's work list
+    std::vector<uint64_t> op_off;        // stream offset of every op's record (the transition kernel drops the headers there)
+    int stage_rec_cap = 0;               // record bytes a ring stage must hold
     std::vector<SweepBlock> blocks;
     std::vector<SweepOp> ops;           // per-op header table (global memory, prefetched by the consumers)
-    int count_kind[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int count_kind[16] = {0};
     int n_push = 0, n_reg_sibling = 0;  // pending siblings parked in the stack / kept in the second accumulator
     // guard planning (plan_guards): the op that completes each node, the flags the schedule itself needs, and the
     // tree in post-order
@@ -42,17 +46,30 @@ struct SweepSched {
 
     // child_off/children: CSR child lists; leaf_row: alignment row per leaf; root must be internal.
     // slot: CLV slot per node (-1 for leaves), recorded in the header of the op that completes the node.
+    // collapse: fold every cherry (two leaf children) whose parent is binary into its parent's op as a SUPER-TIP:
+    //   the parent reads P_cherry-edge * (tip(x) (.) tip(y)) for the code pair of its two leaves from a 25-row
+    //   table, exactly as it reads a tip's masked column sums -- the cherry's own op, its product and its
+    //   parent's matrix-vector product all disappear (a third of the ops and of the FP64 work of a Yule tree).
+    //   Not for the storing variant (the pre-order pass needs every node's CLV), and not for a cherry whose
+    //   `no_collapse` mark is set (plan_guards: branch x rate so small that the unscaled table could underflow).
+    bool collapsed_build = false;
+    std::vector<char> pseudo;            // node is a cherry folded into its parent
+    std::vector<char> built_no_collapse; // the mask the current schedule was built with
     void build(int n, int root, const std::vector<int> &child_off, const std::vector<int> &children,
-               const std::vector<int> &leaf_row, int n_clv_, const std::vector<int> &slot = std::vector<int>())
+               const std::vector<int> &leaf_row, int n_clv_, const std::vector<int> &slot = std::vector<int>(),
+               bool collapse = false, const std::vector<char> &no_collapse = std::vector<char>())
     {
         valid = false;
         n_clv = n_clv_;
-        descs.clear();
+        collapsed_build = collapse;
+        stages.clear();
+        op_off.clear();
         blocks.clear();
         for (int &c : count_kind) c = 0;
         auto is_leaf = [&](int v) { return child_off[v + 1] == child_off[v]; };
+        auto arity = [&](int v) { return child_off[v + 1] - child_off[v]; };
         // post-order (children before parents) for the need computation
-        std::vector<int> order;
+        std::vector<int> order, parent(n, -1);
         order.reserve(n);
         {
             std::vector<int> st(1, root);
@@ -60,20 +77,36 @@ struct SweepSched {
                 int v = st.back();
                 st.pop_back();
                 order.push_back(v);
-                for (int k = child_off[v]; k < child_off[v + 1]; ++k) st.push_back(children[k]);
+                for (int k = child_off[v]; k < child_off[v + 1]; ++k) {
+                    parent[children[k]] = v;
+                    st.push_back(children[k]);
+                }
             }
             std::reverse(order.begin(), order.end());
         }
         post_order = order;
         kid_off = child_off;
         kids = children;
+        pseudo.assign(n, 0);
+        if (collapse)
+            for (int v = 0; v < n; ++v) {
+                if (arity(v) != 2 || v == root || arity(parent[v]) != 2) continue;
+                if (!is_leaf(children[child_off[v]]) || !is_leaf(children[child_off[v] + 1])) continue;
+                if ((size_t)v < no_collapse.size() && no_collapse[v]) continue;
+                pseudo[v] = 1;
+            }
+        // a node with two cherry children keeps one of them as an ordinary cherry op (the record of an op with two
+        // super-tips would be the largest by far and set the size of every ring stage)
+        for (int v = 0; v < n; ++v)
+            if (arity(v) == 2 && pseudo[children[child_off[v]]] && pseudo[children[child_off[v] + 1]]) pseudo[children[child_off[v]]] = 0;
+        auto tipish = [&](int v) { return is_leaf(v) || pseudo[v]; };
         std::vector<int> need(n, 0);
         std::vector<std::vector<int>> ints(n), tips(n);
         for (int v : order) {
-            if (is_leaf(v)) continue;
+            if (tipish(v)) continue;
             for (int k = child_off[v]; k < child_off[v + 1]; ++k) {
                 int c = children[k];
-                (is_leaf(c) ? tips[v] : ints[v]).push_back(c);
+                (tipish(c) ? tips[v] : ints[v]).push_back(c);
             }
             std::stable_sort(ints[v].begin(), ints[v].end(), [&](int a, int b) { return need[a] > need[b]; });
             int nd = 0;
@@ -82,29 +115,44 @@ struct SweepSched {
             need[v] = nd;
         }
         n_levels = need[root];
-        // chain[v]: the subtree of v is a chain of binary TT / TI updates (no internal x internal node, no
-        // polytomy): it runs entirely in ONE accumulator, so as the pending-side sibling of a binary node it
+        // chain[v]: the subtree of v is a chain of binary tip x tip / tip x internal updates (no internal x internal
+        // node, no polytomy): it runs entirely in ONE accumulator, so as the pending-side sibling of a binary node it
         // can be evaluated in the second register accumulator `u` with no stack traffic at all.
         std::vector<char> chain(n, 0);
         for (int v : order) {
-            if (is_leaf(v)) continue;
+            if (tipish(v)) continue;
             const size_t ni = ints[v].size(), nt = tips[v].size();
             chain[v] = ni + nt == 2 && (ni == 0 || (ni == 1 && chain[ints[v][0]]));
         }
 
-        struct Hdr { int kind, flags, level, szA, szB; };
-        struct Rec { Hdr h; int edgeA, edgeB, rowA, rowB; bool tabA, tabB; int node; };
+        // operand of an op: a tip (5-row table of its edge, one code row), a super-tip (25-row table of a folded
+        // cherry, two code rows), the transition matrix of an edge, or -- SW_TT only -- the product table of the
+        // two tip edges of an explicit cherry
+        enum { O_NONE = 0, O_TIP, O_SUPER, O_P, O_CHERRY };
+        struct Opd { int type, node; };
+        struct Hdr { int kind, flags, level, szA, szB, nrowA; };
+        struct Rec { Hdr h; Opd A, B; int rows[4]; int node; };
         std::vector<Rec> recs;
         int pending_push = -1;
         bool u_mode = false;
         n_push = n_reg_sibling = 0;
-        auto emit = [&](int kind, int level, int edgeA, bool tabA, int edgeB, bool tabB) {
+        auto opd_tip = [&](int v) { return Opd{pseudo[v] ? O_SUPER : O_TIP, v}; };
+        auto opd_bytes = [&](const Opd &o, bool store_p) {
+            switch (o.type) {
+            case O_TIP: return SW_TIP_BYTES;
+            case O_SUPER: return SW_TAB2_BYTES;
+            case O_P: return SW_P_BYTES;
+            case O_CHERRY: return SW_TAB2_BYTES + (store_p ? 2 * SW_P_BYTES : 0);
+            default: return 0;
+            }
+        };
+        auto emit = [&](int kind, int level, Opd A, Opd B) {
             Rec r;
             memset(&r, 0, sizeof r);
             r.h.kind = kind;
             r.h.level = level;
             if (u_mode) r.h.flags |= SW_FLAG_U;
-            if (kind == SW_TT || kind == SW_LOADTIP) {
+            if (kind == SW_TT || kind == SW_TS || kind == SW_LOADTIP) { // ops that START a value
                 if (pending_push >= 0) {
                     r.h.flags |= SW_FLAG_PUSH;
                     r.h.level = pending_push;
@@ -112,18 +160,34 @@ struct SweepSched {
                     ++n_push;
                 }
             }
-            r.edgeA = edgeA; r.edgeB = edgeB; r.tabA = tabA; r.tabB = tabB;
-            r.h.szA = edgeA < 0 ? 0 : (tabA ? SW_TAB_BYTES : SW_P_BYTES);
-            r.h.szB = edgeB < 0 ? 0 : (tabB ? SW_TAB_BYTES : SW_P_BYTES);
-            if (kind == SW_TT) { // one 5x5 table of products for the cherry instead of two tip tables, followed by
-                r.h.szA = SW_TAB2_BYTES; // the two P(t) for the sites that carry a partial ambiguity code
-                r.h.szB = 2 * SW_P_BYTES;
+            r.A = A;
+            r.B = B;
+            // the storing variant keeps the two P(t) behind an explicit cherry's table: its ambiguity-code path then
+            // follows the reference's summation order bit for bit (posterior ties); the plain variant sums table rows
+            r.h.szA = opd_bytes(A, !collapse);
+            r.h.szB = opd_bytes(B, false);
+            int nr = 0;
+            auto add_rows = [&](const Opd &o) {
+                if (o.type == O_TIP) r.rows[nr++] = leaf_row[o.node];
+                else if (o.type == O_SUPER) {
+                    r.rows[nr++] = leaf_row[children[child_off[o.node]]];
+                    r.rows[nr++] = leaf_row[children[child_off[o.node] + 1]];
+                }
+            };
+            for (int &x : r.rows) x = -1;
+            if (A.type == O_CHERRY) { // the two tip edges ride in A.node (first leaf) and B.node (second leaf)
+                r.rows[nr++] = leaf_row[A.node];
+                r.rows[nr++] = leaf_row[B.node];
+                r.h.nrowA = 1;
+            } else {
+                add_rows(A);
+                r.h.nrowA = nr;
+                add_rows(B);
             }
-            r.rowA = (edgeA >= 0 && tabA) ? leaf_row[edgeA] : -1;
-            r.rowB = (edgeB >= 0 && tabB) ? leaf_row[edgeB] : -1;
             recs.push_back(r);
             count_kind[kind]++;
         };
+        const Opd none{O_NONE, -1};
         struct Frame { int v, j; bool ret; };
         std::vector<Frame> st;
         st.push_back({root, 0, false});
@@ -135,12 +199,12 @@ struct SweepSched {
             if (f.ret) { // child iv[j-1] just finished; its CLV is the running value
                 f.ret = false;
                 if (!binary) {
-                    emit(SW_APPLY, 0, iv[f.j - 1], false, -1, false);
+                    emit(SW_APPLY, 0, Opd{O_P, iv[f.j - 1]}, none);
                     // a product of >= 3 child contributions: every child enters at max in [1,2), as in the
                     // reference (children are max-normalised, profile.rs:20-39), so the product leaves the
                     // normal range exactly where the reference's own product does
                     if (iv.size() + tv.size() >= 3) recs.back().h.flags |= SW_FLAG_NORM;
-                    if (f.j - 1 >= 1) emit(SW_MULPOP, need[iv[f.j - 1]], -1, false, -1, false);
+                    if (f.j - 1 >= 1) emit(SW_MULPOP, need[iv[f.j - 1]], none, none);
                 }
             }
             if (f.j < (int)iv.size()) {
@@ -161,24 +225,30 @@ struct SweepSched {
                     const bool from_u = u_mode; // set when iv[1] was evaluated in u (chains hold no II, so no nesting)
                     u_mode = false;
                     // operand A is the waiting side: the popped CLV of iv[0], or u holding iv[1]
-                    if (from_u) emit(SW_II, need[iv[1]], iv[1], false, iv[0], false);
-                    else emit(SW_II, need[iv[1]], iv[0], false, iv[1], false);
+                    if (from_u) emit(SW_II, need[iv[1]], Opd{O_P, iv[1]}, Opd{O_P, iv[0]});
+                    else emit(SW_II, need[iv[1]], Opd{O_P, iv[0]}, Opd{O_P, iv[1]});
                     if (from_u) recs.back().h.flags |= SW_FLAG_XU;
+                } else if (iv.size() == 1) {
+                    if (pseudo[tv[0]]) emit(SW_SI, 0, Opd{O_SUPER, tv[0]}, Opd{O_P, iv[0]});
+                    else emit(SW_TI, 0, Opd{O_TIP, tv[0]}, Opd{O_P, iv[0]});
+                } else {
+                    int a = tv[0], c = tv[1];
+                    if (pseudo[a]) std::swap(a, c); // at most one of the two is a super-tip: it goes second
+                    if (pseudo[c]) emit(SW_TS, 0, Opd{O_TIP, a}, Opd{O_SUPER, c});
+                    else emit(SW_TT, 0, Opd{O_CHERRY, a}, Opd{O_NONE, c});
                 }
-                else if (iv.size() == 1) emit(SW_TI, 0, tv[0], true, iv[0], false);
-                else emit(SW_TT, 0, tv[0], true, tv[1], true);
             } else if (iv.empty()) {
                 size_t k = 0;
                 if (tv.size() >= 2) {
-                    emit(SW_TT, 0, tv[0], true, tv[1], true);
+                    emit(SW_TT, 0, Opd{O_CHERRY, tv[0]}, Opd{O_NONE, tv[1]});
                     k = 2;
                 } else {
-                    emit(SW_LOADTIP, 0, tv[0], true, -1, false);
+                    emit(SW_LOADTIP, 0, Opd{O_TIP, tv[0]}, none);
                     k = 1;
                 }
-                for (; k < tv.size(); ++k) emit(SW_MULTIP, 0, tv[k], true, -1, false);
+                for (; k < tv.size(); ++k) emit(SW_MULTIP, 0, Opd{O_TIP, tv[k]}, none);
             } else {
-                for (int tnode : tv) emit(SW_MULTIP, 0, tnode, true, -1, false);
+                for (int tnode : tv) emit(SW_MULTIP, 0, Opd{O_TIP, tnode}, none);
             }
             recs.back().h.flags |= SW_FLAG_DONE;
             recs.back().node = v;
@@ -196,48 +266,84 @@ struct SweepSched {
                 if (used[r.h.level] >= 0) r.h.level = used[r.h.level];
             n_levels = next;
         }
-        // lay the records out in op order
+        // lay the records out in op order and pack consecutive ops into ring stages (greedy: up to
+        // SW_STAGE_REC_BYTES of records and SW_STAGE_ROWS tip-code rows per stage)
         n_ops = (int)recs.size();
         size_t off = 0;
         rec_cap = 0;
-        descs.assign(recs.size() + 1, SweepDesc()); // + one padding entry (the producer prefetches k + 1)
-        memset(descs.data(), 0, sizeof(SweepDesc) * descs.size());
-        descs.back().rowA = descs.back().rowB = -1;
+        max_rows = 0;
+        op_off.assign(recs.size(), 0);
+        std::vector<uint32_t> op_w3(recs.size(), 0);
+        std::vector<char> op_first(recs.size(), 0), op_last(recs.size(), 0);
+        auto add_block = [&](size_t at, uint32_t per_cat, const Opd &o, const Opd &other, bool store_p) {
+            auto kid = [&](int c, int i) { return children[child_off[c] + i]; };
+            switch (o.type) {
+            case O_TIP: blocks.push_back({at, per_cat, o.node, 1, -1, -1, 0}); break;
+            case O_P: blocks.push_back({at, per_cat, o.node, 0, -1, -1, 0}); break;
+            case O_SUPER: blocks.push_back({at, per_cat, o.node, 3, kid(o.node, 0), kid(o.node, 1), 0}); break;
+            case O_CHERRY:
+                blocks.push_back({at, per_cat, o.node, 2, other.node, -1, 0});
+                if (store_p) {
+                    blocks.push_back({at + (uint32_t)SW_TAB2_BYTES, per_cat, o.node, 0, -1, -1, 0});
+                    blocks.push_back({at + (uint32_t)(SW_TAB2_BYTES + SW_P_BYTES), per_cat, other.node, 0, -1, -1, 0});
+                }
+                break;
+            default: break;
+            }
+        };
+        for (size_t k = 0; k < recs.size(); ++k) {
+            const Rec &r = recs[k];
+            const uint32_t per_cat = (uint32_t)(r.h.szA + r.h.szB);
+            rec_cap = std::max(rec_cap, (int)(SW_HDR_BYTES + n_clv * per_cat));
+        }
+        stage_rec_cap = std::max(rec_cap, SW_STAGE_REC_BYTES);
+        SweepStage cur;
+        memset(&cur, 0, sizeof cur);
+        auto flush = [&](size_t k_last) {
+            op_last[k_last] = 1;
+            stages.push_back(cur);
+            memset(&cur, 0, sizeof cur);
+        };
         for (size_t k = 0; k < recs.size(); ++k) {
             const Rec &r = recs[k];
             const uint32_t per_cat = (uint32_t)(r.h.szA + r.h.szB);
             const uint32_t bytes = (uint32_t)SW_HDR_BYTES + (uint32_t)n_clv * per_cat; // next op's header + operand blocks
-            SweepDesc &d = descs[k];
-            memset(&d, 0, sizeof d);
-            d.rec_off = off;
-            d.rec_bytes = bytes;
-            d.rowA = r.rowA;
-            d.rowB = r.rowB;
-            const size_t b0 = off + SW_HDR_BYTES;
-            if (r.h.kind == SW_TT) {
-                blocks.push_back({b0, per_cat, r.edgeA, 2, r.edgeB});
-                blocks.push_back({b0 + (uint32_t)SW_TAB2_BYTES, per_cat, r.edgeA, 0, -1});
-                blocks.push_back({b0 + (uint32_t)(SW_TAB2_BYTES + SW_P_BYTES), per_cat, r.edgeB, 0, -1});
-            } else {
-                if (r.edgeA >= 0) blocks.push_back({b0, per_cat, r.edgeA, r.tabA ? 1 : 0, -1});
-                if (r.edgeB >= 0) blocks.push_back({b0 + (uint32_t)r.h.szA, per_cat, r.edgeB, r.tabB ? 1 : 0, -1});
+            int nr = 0;
+            for (int i = 0; i < 4; ++i) nr += r.rows[i] >= 0;
+            max_rows = std::max(max_rows, nr);
+            if (cur.rec_bytes > 0 && (cur.rec_bytes + bytes > (uint32_t)stage_rec_cap || cur.n_rows + nr > SW_STAGE_ROWS)) flush(k - 1);
+            if (cur.rec_bytes == 0) {
+                cur.rec_off = off;
+                op_first[k] = 1;
             }
-            rec_cap = std::max(rec_cap, (int)bytes);
+            op_off[k] = off;
+            op_w3[k] = cur.rec_bytes | ((uint32_t)cur.n_rows << 16);
+            for (int i = 0; i < 4; ++i)
+                if (r.rows[i] >= 0) cur.rows[cur.n_rows++] = r.rows[i];
+            cur.rec_bytes += bytes;
+            const size_t b0 = off + SW_HDR_BYTES;
+            add_block(b0, per_cat, r.A, r.B, !collapse);
+            if (r.A.type != O_CHERRY) add_block(b0 + (uint32_t)r.h.szA, per_cat, r.B, r.A, false);
             off += bytes;
         }
+        if (!recs.empty()) flush(recs.size() - 1);
+        n_stage_descs = (int)stages.size();
+        memset(&cur, 0, sizeof cur);
+        stages.push_back(cur); // padding entry: the producer reads one stage ahead
         stream_bytes = off;
-        ops.assign(recs.size() + 2, SweepOp{0, 0, 0, 0}); // + two padding entries (the consumers prefetch k + 2)
+        ops.assign(recs.size() + 2, SweepOp{0, 0, 0, 0}); // + two padding entries
         base_w0.assign(recs.size(), 0);
         done_op.assign(n, -1);
         for (size_t k = 0; k < recs.size(); ++k) {
             const Hdr &h = recs[k].h;
-            const uint32_t code = (uint32_t)h.kind | ((h.flags & (SW_FLAG_U | SW_FLAG_XU)) ? 8u : 0u);
-            base_w0[k] = code | ((uint32_t)h.flags << 8) | ((uint32_t)h.level << 16);
+            const uint32_t code = (uint32_t)sw_code(h.kind, (h.flags & (SW_FLAG_U | SW_FLAG_XU)) != 0);
+            const uint32_t fl = (uint32_t)h.flags | (op_first[k] ? (uint32_t)SW_FLAG_FIRST : 0u) | (op_last[k] ? (uint32_t)SW_FLAG_LAST : 0u);
+            base_w0[k] = code | (fl << 8) | ((uint32_t)h.level << 18);
             ops[k].w1 = (uint32_t)(h.szA + h.szB) | ((uint32_t)h.szA << 16);
             const int nd = (h.flags & SW_FLAG_DONE) ? recs[k].node : -1;
             if (nd >= 0) done_op[nd] = (int)k;
             ops[k].w2 = (nd >= 0 && (size_t)nd < slot.size() && slot[nd] >= 0) ? (uint32_t)slot[nd] : 0u;
-            ops[k].w3 = 0;
+            ops[k].w3 = op_w3[k];
         }
         plan_guards(std::vector<double>(), std::vector<double>()); // until bounds are known: guard after every node
         valid = true;
@@ -268,7 +374,7 @@ struct SweepSched {
             std::vector<double> Epre(n, 0.0), Epost(n, 0.0);
             auto leaf = [&](int v) { return kid_off[v + 1] == kid_off[v]; };
             auto set_guard = [&](int c) {
-                if (leaf(c)) return;
+                if (leaf(c) || done_op[c] < 0) return; // a folded cherry has no op of its own: nothing to guard
                 guard[c] = 1;
                 Epost[c] = std::max(Epre[c], -T);
             };
@@ -277,7 +383,7 @@ struct SweepSched {
                 const int nk = kid_off[v + 1] - kid_off[v];
                 if (nk != 2) {
                     for (int k = kid_off[v]; k < kid_off[v + 1]; ++k) set_guard(kids[k]);
-                    guard[v] = 1;
+                    guard[v] = done_op[v] >= 0;
                     Epre[v] = Epost[v] = -T;
                     continue;
                 }
@@ -290,7 +396,7 @@ struct SweepSched {
                     E = Epost[a] + Epost[c] - s;
                     if (!(E >= -LIM)) {
                         for (int x : {a, c})
-                            if (!leaf(x)) {
+                            if (!leaf(x) && done_op[x] >= 0) {
                                 normout[x] = 1;
                                 Epost[x] = 0.0;
                             }
@@ -360,6 +466,33 @@ inline void sweep_guard_bounds(const ModelDev &M, const std::vector<double> &ble
     }
 }
 
+// Cherries that must stay explicit ops: the folded table holds P_v (tip_x (.) tip_y) UNSCALED, so its entries can be as
+// small as 2^-(s + b[v]), s the cherry's own shrink bound; beyond 400 bits (branch x rate below ~1e-60) the explicit
+// op with its guard / normalisation is kept.
+inline void sweep_no_collapse(const std::vector<int> &child_off, const std::vector<int> &children, const std::vector<double> &b,
+                              const std::vector<double> &bd, std::vector<char> &out)
+{
+    const int n = (int)child_off.size() - 1;
+    out.assign(n, 0);
+    if ((int)b.size() != n) return;
+    for (int v = 0; v < n; ++v) {
+        if (child_off[v + 1] - child_off[v] != 2) continue;
+        const int a = children[child_off[v]], c = children[child_off[v] + 1];
+        const double s = std::min(b[a] + bd[c], bd[a] + b[c]);
+        out[v] = !(s + b[v] <= 400.0);
+    }
+}
+
+// Site quads per CTA: consumer warps are always full, so Q * n_clv is a multiple of 32 (and Q of 4: 16-byte
+// tip-code rows for the bulk copies).
+inline int sweep_q_step(int n_clv)
+{
+    int step = 4;
+    while ((step * n_clv) % 32) step += 4;
+    return step;
+}
+inline int sweep_q_max(int n_clv) { return SW_MAX_CONSUMERS / n_clv / sweep_q_step(n_clv) * sweep_q_step(n_clv); }
+
 // Launch geometry / shared-memory carve-up for a schedule.
 struct SweepGeom {
     int Q = 0, n_consumers = 0, threads = 0, n_stages = 0, stage_bytes = 0, smem_levels = 0, g_levels = 0;
@@ -372,12 +505,12 @@ struct SweepGeom {
     // scaling shards of 125k-500k patterns).  PHB_SWEEP_Q overrides the choice (experiments).
     bool plan(const SweepSched &S, size_t smem_max, int64_t P = 0, int n_sm = 148)
     {
-        const int q_max = (SW_MAX_CONSUMERS / S.n_clv) & ~3;
-        if (q_max < 4) return false;
+        const int step = sweep_q_step(S.n_clv), q_max = sweep_q_max(S.n_clv);
+        if (q_max < step) return false;
         Q = q_max;
         if (P > 0 && n_sm > 0) {
             double best = 1e300;
-            for (int q = q_max; q >= 8 && q >= q_max / 2; q -= 4) {
+            for (int q = q_max; q >= step && q >= q_max / 2; q -= step) {
                 const int64_t blocks = (P + 4 * q - 1) / (4 * q);
                 const int64_t passes = (blocks + n_sm - 1) / n_sm;
                 const double cost = (double)passes * (304.0 + 2.67 * q * S.n_clv);
@@ -388,16 +521,16 @@ struct SweepGeom {
             }
         }
         if (const char *e = getenv("PHB_SWEEP_Q")) {
-            const int q = atoi(e) & ~3;
-            if (q >= 4 && q <= q_max) Q = q;
+            const int q = atoi(e) / step * step;
+            if (q >= step && q <= q_max) Q = q;
         }
         planned_P = P;
         n_consumers = Q * S.n_clv;
-        threads = ((n_consumers + 31) / 32) * 32 + 32;
+        threads = n_consumers + 32;
         level_bytes = (size_t)n_consumers * SW_R * 32;
-        stage_bytes = (S.rec_cap + 2 * 4 * Q + 127) / 128 * 128;
+        stage_bytes = ((S.stage_rec_cap + 15) / 16 * 16 + SW_STAGE_ROWS * 4 * Q + 127) / 128 * 128;
         const int want_levels = std::max(S.n_levels, 1);
-        for (n_stages = 8; n_stages >= 2; n_stages /= 2) { // a power of two: the kernel wraps with a mask
+        for (n_stages = 4; n_stages >= 2; n_stages /= 2) { // a power of two: the kernel wraps with a mask
             size_t fixed = SW_BAR_BYTES + (size_t)n_stages * stage_bytes;
             if (fixed + level_bytes > smem_max) continue;
             smem_levels = (int)std::min<size_t>((smem_max - fixed) / level_bytes, (size_t)want_levels);

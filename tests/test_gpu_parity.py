@@ -62,8 +62,9 @@ def test_sweep_shapes(gpu_lib):
 
     poly = "(((a:0.1,b:0.2,c:0.1)x:0.05,(d:0.3,e:0.2)y:0.01,((f:0.1,g:0.2)z:0.1)w:0.2,h:0.3,i:0.1)r:0.1,(j:0.2)u:0.3);"
     rng = np.random.default_rng(5)
-    # balanced 1024: 9 pending siblings on the deepest path, the cherry-level one stays in the register accumulator
-    for nwk, levels in ((balanced(0, 1024) + ";", 8), (cater(300) + ";", 0), (poly, None)):
+    # balanced 1024: half the cherries are folded into their parents' ops, the cherry-level pending sibling stays in
+    # the register accumulator, the other 7 pending siblings of the deepest path are stack levels
+    for nwk, levels in ((balanced(0, 1024) + ";", 7), (cater(300) + ";", 0), (poly, None)):
         tree = parse_newick(nwk)
         names = [tree.nodes[i].taxa for i in tree.get_node_ids() if tree.is_leaf(i)]
         ft = workloads.flatten_fast(tree, names)
@@ -115,7 +116,7 @@ def test_tiling_and_sharding_invariance(gpu_lib):
     assert tiled[2]["n_tiles"] >= 4
     assert np.array_equal(full[1], tiled[1])
     sweep = _cases.check_lnl(gpu_lib, case)
-    assert sweep[2]["sweep_ops"] == 49 and np.max(np.abs(sweep[1] - full[1])) < 1e-10
+    assert 25 <= sweep[2]["sweep_ops"] < 49 and np.max(np.abs(sweep[1] - full[1])) < 1e-10  # 49 nodes, cherries folded
     split = _cases.check_lnl(gpu_lib, case, devices=[0, 0, 0])  # three virtual ranks on one device
     assert np.array_equal(sweep[1], split[1])
 
@@ -353,7 +354,7 @@ def test_full_size_properties_config2(gpu_lib):
         workloads.load_into(ctx, case)
         ctx.simulate_alignment(P, seed=0xA11C)
         tot, per = ctx.log_likelihood(per_pattern=True)
-        assert ctx.stats()["sweep_ops"] == 999
+        assert 500 <= ctx.stats()["sweep_ops"] < 999  # cherries folded into their parents' ops
         pats = ctx.get_alignment(0, 1024)
         whole = ctx.get_alignment()
     with capi.Context(library=gpu_lib, flags=capi.FLAG_LEVEL_KERNELS) as ctx:  # HBM-resident CLVs, forced 5-way tiling
@@ -396,7 +397,7 @@ def test_full_size_properties_config3(gpu_lib):
         workloads.load_into(ctx, case)
         ctx.simulate_alignment(P, seed=0xB200)
         tot, per = ctx.log_likelihood(per_pattern=True)
-        assert ctx.stats()["sweep_ops"] == 9999
+        assert 5000 <= ctx.stats()["sweep_ops"] < 9999  # cherries folded into their parents' ops
         assert ctx.log_likelihood() == tot  # re-evaluation is bit-reproducible
         pats = ctx.get_alignment(0, 256)
     assert np.all(np.isfinite(per)) and abs(tot - float(np.sum(per))) <= 1e-11 * abs(tot)

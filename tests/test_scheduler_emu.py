@@ -55,14 +55,14 @@ def test_sweep_many_blocks_per_cta(emu_lib):
     """More site blocks than (emulated) SMs: every persistent CTA sweeps the tree several times."""
     case = workloads.make_case(7, 2600, model="gtr_g4", seed=14)  # <= 320-site blocks -> >= 9 blocks on 3 CTAs
     st = _cases.check_lnl(emu_lib, case)[2]
-    assert 160 <= st["sweep_block_sites"] <= 320 and st["sweep_block_sites"] % 16 == 0
-    assert st["sweep_ops"] == 6 and st["clv_launches"] == 1
+    assert 160 <= st["sweep_block_sites"] <= 352 and st["sweep_block_sites"] % 16 == 0
+    assert 3 <= st["sweep_ops"] < 6 and st["clv_launches"] == 1  # 6 internal nodes, the cherries folded into their parents' ops
 
 
 def test_sweep_global_stack_levels(emu_lib, monkeypatch):
-    """A balanced 64-leaf tree needs 5 pending siblings on its deepest path; the cherry-level one lives in the
-    second register accumulator, the other 4 are stack levels; with little shared memory most spill to the
-    global stack."""
+    """A balanced 64-leaf tree: 16 of the 32 cherries are folded into their parents' ops (the other cherry of each
+    pair stays an op), the cherry-level pending sibling lives in the second register accumulator, the rest are stack
+    levels; with little shared memory most spill to the global stack."""
     def balanced(lo, hi):
         if hi - lo == 1:
             return f"t{lo}:0.{1 + lo % 7}"
@@ -80,8 +80,8 @@ def test_sweep_global_stack_levels(emu_lib, monkeypatch):
     monkeypatch.setenv("PHB_EMU_SMEM_BYTES", str(512 + 2 * 4736 + 2 * 32768))
     b = _cases.check_lnl(emu_lib, case)
     assert np.array_equal(a[1], b[1])
-    assert a[2]["sweep_stack_levels"] == 4 and a[2]["sweep_smem_levels"] == 4
-    assert b[2]["sweep_stack_levels"] == 4 and b[2]["sweep_smem_levels"] == 2 and b[2]["sweep_ops"] == 63
+    assert a[2]["sweep_stack_levels"] == 3 and a[2]["sweep_smem_levels"] == 3 and a[2]["sweep_ops"] == 63 - 16
+    assert b[2]["sweep_stack_levels"] == 3 and 1 <= b[2]["sweep_smem_levels"] < 3
 
 
 def test_sweep_schedule_shapes(emu_lib):
@@ -139,6 +139,20 @@ def test_high_arity_with_deep_subtrees(emu_lib, k, depth):
     assert _cases.check_asr(emu_lib, case, flags=capi.FLAG_LEVEL_KERNELS) == 0
 
 
+def test_folded_cherries_match_explicit_cherries(emu_lib, monkeypatch):
+    """The plain sweep folds every cherry under a binary parent into the parent's op (a 25-row table of
+    P_cherry (tip_x (.) tip_y)); with PHB_SWEEP_NO_COLLAPSE the cherries stay ops.  Same per-pattern lnL to round-off,
+    with ambiguity codes (the folded tables sum rows for the partial codes) and with gaps."""
+    for model, amb in (("jc69", 0.0), ("gtr_i_g4", 0.25)):
+        case = workloads.make_case(60, 80, model=model, seed=41, ambiguity=amb)
+        a = _cases.check_lnl(emu_lib, case)
+        monkeypatch.setenv("PHB_SWEEP_NO_COLLAPSE", "1")
+        b = _cases.check_lnl(emu_lib, case)
+        monkeypatch.delenv("PHB_SWEEP_NO_COLLAPSE")
+        assert a[2]["sweep_ops"] < b[2]["sweep_ops"] == b[2]["n_internal"]
+        assert np.max(np.abs(a[1] - b[1])) < 1e-10
+
+
 def test_guard_plan_matches_guard_everywhere(emu_lib, monkeypatch):
     """The host places the underflow guard only where its bound on the accumulated shrink needs it
     (sweep_sched.h plan_guards).  Rescaling is an exact power of two, so the placement changes no CLV bit: the
@@ -148,7 +162,7 @@ def test_guard_plan_matches_guard_everywhere(emu_lib, monkeypatch):
     assert 0 < a[2]["sweep_guards"] < 0.25 * a[2]["n_internal"] and a[2]["sweep_normouts"] == 0
     monkeypatch.setenv("PHB_SWEEP_GUARD_ALL", "1")
     b = _cases.check_lnl(emu_lib, case)
-    assert b[2]["sweep_guards"] == b[2]["n_internal"]
+    assert b[2]["sweep_guards"] == b[2]["sweep_ops"] < b[2]["n_internal"]  # one per op; folded cherries have none
     assert np.max(np.abs(a[1] - b[1])) < 1e-9 and a[1].min() < -300
 
 
@@ -434,11 +448,12 @@ def test_fused_host_call_matches_two_call_path(emu_lib):
                 assert tot == ref_tot
             else:
                 assert abs(tot - ref_tot) <= 1e-12 * abs(ref_tot)
-            # the alignment stays resident: the plain entry point gives the same number again
-            assert ctx.log_likelihood() == tot
+            # the alignment stays resident: the plain entry point gives the same number again (its site blocks may be
+            # cut differently from the streamed chunks', so the block partial sums add up in another order)
+            assert abs(ctx.log_likelihood() - tot) <= 1e-13 * abs(tot)
             tot_rm = ctx.log_likelihood_host(np.ascontiguousarray(case.patterns.T), layout=capi.LAYOUT_ROW_MAJOR,
                                              multiplicity=mult)
-            assert tot_rm == tot
+            assert abs(tot_rm - tot) <= 1e-13 * abs(tot)
             # errors: an invalid byte in a leaf row, and a leaf without a row
             bad = case.patterns.copy()
             bad[6500, 3] = ord("?")
