@@ -271,6 +271,20 @@ def run_gpu(args, rank, world, local_rank):
         lnl_e2e = e2e_step()
     barrier()
     e2e_ms = (time.perf_counter() - t1) * 1e3 / e2e_steps
+    # the same call from PAGEABLE host memory (a caller's plain Vec<u8>): one step, reported beside the pinned figure
+    e2e_pageable_ms = None
+    if world == 1 and os.environ.get("PHB_BENCH_PAGEABLE", "1") == "1":
+        pageable = np.empty((cnt, n_rows), np.uint8)
+        np.copyto(pageable, host.numpy())
+        synthetic.load_into(ctx, tree, model)
+        ctx.log_likelihood_host((pageable.ctypes.data, n_rows, cnt))  # first touch
+        torch.cuda.synchronize()
+        tp = time.perf_counter()
+        synthetic.load_into(ctx, tree, model)
+        lnl_pg = ctx.log_likelihood_host((pageable.ctypes.data, n_rows, cnt))
+        e2e_pageable_ms = (time.perf_counter() - tp) * 1e3
+        assert abs(lnl_pg - lnl_e2e) <= 1e-12 * abs(lnl_e2e)
+        del pageable
     # ---- reduce over ranks ------------------------------------------------------------------------
     tmax = torch.tensor([dev_ms, wall_ms, e2e_ms], dtype=torch.float64, device="cuda")
     tsum = torch.tensor([float(launches)], dtype=torch.float64, device="cuda")
@@ -286,17 +300,28 @@ def run_gpu(args, rank, world, local_rank):
         kern_ms = st["ms_clv"] / max(st["clv_launches"], 1)
         bytes_launch = st["algorithmic_bytes"] / max(st["clv_launches"], 1)
         achieved = bytes_launch / (kern_ms * 1e-3) / 1e9 if kern_ms > 0 else None
-        traffic = None
+        traffic, traffic_note = None, None
         kernel = "clv_update_level_kernel" if level_path else "sweep_kernel"
-        try:  # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu capture
+        try:  # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu capture of THIS kernel source
+            import hashlib
+
             with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
                 tj = json.load(f).get(kernel, {})
-            if tj.get("patterns"):
+            src = os.path.join(ROOT, "phylo-rs_b200", "csrc", tj.get("source_file", "sweep.cuh"))
+            sha = hashlib.sha256(open(src, "rb").read()).hexdigest()
+            if tj.get("patterns") and tj.get("source_sha256") == sha:
                 traffic = tj["dram_bytes_per_launch"] * (cnt / tj["patterns"]) * (N_TAXA / tj["taxa"])
+                traffic_note = f"ncu capture {tj.get('capture')} of {tj.get('source_file')} at {sha[:12]}"
+            else:
+                traffic_note = "no ncu capture on file for the current kernel source (profiles/traffic.json is for another revision)"
         except Exception:
             pass
-        nominal_flops = 68.0 * 4 * updates  # 68*K flop per binary update, K = 4 CLV categories
-        fp64_tflops = nominal_flops / (st["ms_clv"] * 1e-3) / 1e12 * (cnt / N_SITES)
+        # FP64 pipe: the instructions the schedule actually executes (tip operands are table lookups and cost none)
+        fp64_instr = st.get("sweep_fp64_instr", 0.0) * st["n_clv_categories"] * cnt
+        fp64_flops = st.get("sweep_flops", 0.0) * st["n_clv_categories"] * cnt
+        t_clv = st["ms_clv"] * 1e-3
+        fp64_tflops = fp64_flops / t_clv / 1e12 if t_clv > 0 else None
+        fp64_pipe_frac = (fp64_instr / t_clv) / (fp64_peak * 1e12 / 2.0) if (t_clv > 0 and fp64_peak) else None
         line = {
             "metric": METRIC, "value": updates / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
@@ -309,7 +334,8 @@ def run_gpu(args, rank, world, local_rank):
                        "sweep": {k: st[k] for k in st if k.startswith("sweep_")}},
             "lnl": lnl, "lnl_e2e": lnl_e2e, "wall_ms_per_step": wall_ms / args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
+                         "frac": (achieved / peak) if achieved else None, "traffic": traffic, "traffic_source": traffic_note,
+                         "peak_source": peak_src,
                          "kernel": kernel, "launches_per_step": st["clv_launches"],
                          "avg_launch_ms": kern_ms, "algorithmic_bytes_per_launch": bytes_launch,
                          "whole_step_frac": st["algorithmic_bytes"] / (ms_step * 1e-3) / 1e9 / peak,
@@ -318,12 +344,19 @@ def run_gpu(args, rank, world, local_rank):
                                   "SURVEY 8d are NOT moved (traffic = tip codes + the P(t) stream): frac > 1 means the "
                                   "HBM roofline of the per-node formulation is beaten, the binding resources are the "
                                   "FP64 pipe and shared-memory bandwidth (see fp64)"),
-                         "fp64": {"nominal_flop_per_update": 272, "achieved_tflops": fp64_tflops,
-                                  "peak_tflops_measured": fp64_peak, "frac": fp64_tflops / fp64_peak if fp64_peak else None}},
+                         "fp64": {"executed_flops_per_pattern": st.get("sweep_flops", 0.0) * st["n_clv_categories"],
+                                  "executed_fp64_instructions_per_pattern": st.get("sweep_fp64_instr", 0.0) * st["n_clv_categories"],
+                                  "achieved_tflops": fp64_tflops, "peak_tflops_measured": fp64_peak,
+                                  "pipe_frac": fp64_pipe_frac,
+                                  "note": "pipe_frac = executed DMUL+DFMA per second / (measured DFMA rate): the figure "
+                                          "to hold against ncu's sm__inst_executed_pipe_fp64; flops count a DFMA as 2"}},
             "e2e": {"value": updates / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(cnt) * n_rows + 8 * 60 + 8 * 4 * tree["n_nodes"] + 4 * 4 * tree["n_nodes"],
                     "d2h_bytes_per_step": 8 + 4 * n_rows, "steps": e2e_steps,
-                    "note": "per rank: phb_log_likelihood_host on pinned host [pattern][row] bytes: chunked H2D overlapped with pack + sweep, tree/model upload, scalar back"},
+                    "pageable_ms_per_step": e2e_pageable_ms,
+                    "note": "per rank: phb_log_likelihood_host on pinned host [pattern][row] bytes: chunked H2D overlapped with pack + sweep, "
+                            "tree/model upload, scalar back; pageable_ms_per_step: the same call on plain malloc'ed memory (N=1 only); "
+                            "compress_columns is not in this figure (configs.compress times it)"},
             "gpu_launches": launches,
             "clocks": clocks,
         }
@@ -337,6 +370,15 @@ def run_gpu(args, rank, world, local_rank):
                 "sample": f"oracle reference-faithful mode, first {sample} patterns of the same workload, {dt:.1f} s, 1 thread "
                           "(the reference's rayon feature does not reach this path)",
                 "cpu_opt": {"value": ov, "unit": UNIT, "cores": cores, "sample": f"oracle cpu_opt mode, {sample * 64} patterns, {odt:.1f} s"}}
+        if world == 1 and not args.no_configs:
+            # BASELINE.json's other configurations on this GPU, each with parity deltas against the oracle (outside `value`)
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import configs_bench
+
+            del host
+            ctx.close()
+            torch.cuda.empty_cache()
+            line["configs"] = configs_bench.driver_configs(peak, reps=3)
         print(json.dumps(line), flush=True, file=_real_stdout if world > 1 else sys.stdout)
     ctx.close()
     if world > 1:
@@ -350,6 +392,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--no-configs", action="store_true", help="skip the `configs` object (BASELINE configs 2, 4, 5, joint ASR, compression)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
@@ -361,7 +404,7 @@ def main():
         # launched without torchrun: re-exec under it
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29531"), os.path.abspath(__file__),
-               "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup)] + (["--no-cpu"] if args.no_cpu else [])
+               "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup)] + (["--no-cpu"] if args.no_cpu else []) + (["--no-configs"] if args.no_configs else [])
         raise SystemExit(subprocess.call(cmd))
     run_gpu(args, rank, world, local_rank)
 

@@ -220,6 +220,11 @@ typedef struct phb_stats {
     double nni_read_bytes;     /* ... algorithmic bytes the walks read (sibling CLVs, exponents, tips)*/
     int32_t sweep_guards;      /* fused sweep: nodes followed by the lazy underflow check (2^-256 threshold) */
     int32_t sweep_normouts;    /* ... nodes normalised to max in [1,2) on completion (extreme branch x rate)  */
+    double sweep_fp64_instr;   /* ... FP64 instructions (DMUL/DFMA) one sweep executes per (pattern, CLV category) */
+    double sweep_flops;        /* ... the same in flops (DFMA = 2)                                           */
+    double ms_nni_cache;       /* PHB_FLAG_TIMING, last phb_score_nni: device ms caching the base tree's CLVs  */
+    double ms_nni_upper;       /* ... in the pre-order pass that forms the upper partials                      */
+    double ms_nni_edge;        /* ... in the edge kernel that scores the neighbours (+ its row reduction)      */
 } phb_stats;
 int32_t phb_get_stats(phb_ctx *ctx, phb_stats *out);
 

@@ -61,6 +61,8 @@ class Stats(C.Structure):
         ("nni_path_moves", C.c_int32), ("nni_tiles", C.c_int32), ("nni_path_steps", C.c_int64),
         ("nni_cache_bytes", C.c_double), ("nni_read_bytes", C.c_double),
         ("sweep_guards", C.c_int32), ("sweep_normouts", C.c_int32),
+        ("sweep_fp64_instr", C.c_double), ("sweep_flops", C.c_double),
+        ("ms_nni_cache", C.c_double), ("ms_nni_upper", C.c_double), ("ms_nni_edge", C.c_double),
     ]
 
     def as_dict(self):

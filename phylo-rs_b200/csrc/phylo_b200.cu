@@ -261,7 +261,7 @@ struct Device {
     std::vector<std::pair<int, size_t>> ev_log; // (phase, pool index)
 };
 
-enum Phase { PH_TRANSITION = 0, PH_CLV = 1, PH_ROOT = 2, PH_DOWN = 3 };
+enum Phase { PH_TRANSITION = 0, PH_CLV = 1, PH_ROOT = 2, PH_DOWN = 3, PH_UPPER = 4 };
 
 } // namespace
 
@@ -393,7 +393,8 @@ int upload_tree(phb_ctx *ctx)
         CU(cudaStreamSynchronize(d.stream));
     }
     ctx->tree_uploaded = true;
-    ctx->sweep.valid = false;
+    if (!ctx->sweep.same_topology(T.root, T.child_off, T.children, T.leaf_row, T.slot)) ctx->sweep.valid = false;
+    ctx->sweep_guards_valid = false; // branch lengths may have changed: re-plan the guards (and re-check the folded cherries)
     return PHB_OK;
 }
 
@@ -629,6 +630,16 @@ int run_tile_joint(phb_ctx *ctx, Device &d, const ModelDev &M, int64_t tile_off,
 // (Re)builds the op stream for the current tree and category count and uploads it to every device.
 int ensure_sweep(phb_ctx *ctx, const ModelDev &M, bool store)
 {
+    const auto t_begin = std::chrono::steady_clock::now();
+    struct Trace {
+        std::chrono::steady_clock::time_point t0;
+        ~Trace()
+        {
+            if (getenv("PHB_SWEEP_TRACE"))
+                fprintf(stderr, "ensure_sweep: %.3f ms on the host\n",
+                        std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+        }
+    } trace{t_begin};
     const TreeSched &T = ctx->tree;
     SweepSched &S = ctx->sweep;
     int64_t shard_P = 0;
@@ -958,6 +969,8 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
     S.sweep_stream_bytes = (use_sweep || asr_sweep) ? (int64_t)ctx->sweep.stream_bytes : 0;
     S.sweep_guards = (use_sweep || asr_sweep) ? ctx->sweep.n_guards : 0;
     S.sweep_normouts = (use_sweep || asr_sweep) ? ctx->sweep.n_normout : 0;
+    S.sweep_fp64_instr = (use_sweep || asr_sweep) ? ctx->sweep.fp64_instr : 0;
+    S.sweep_flops = (use_sweep || asr_sweep) ? ctx->sweep.flops : 0;
     if (timing) {
         S.ms_transition = S.ms_clv = S.ms_root = S.ms_down = 0;
         for (auto &pr : d0.ev_log) {
@@ -1160,6 +1173,10 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
             CU(cudaMemcpyAsync(d.nni_jobs.p, jobs.data(), sizeof(NniEdgeJob) * jobs.size(), cudaMemcpyHostToDevice, d.stream));
             CU(cudaMemcpyAsync(d.nni_rows.p, job_rows.data(), sizeof(int32_t) * job_rows.size(), cudaMemcpyHostToDevice, d.stream));
         }
+        if (&d == &ctx->devs[0]) {
+            d.ev_used = 0;
+            d.ev_log.clear();
+        }
         const int nni_bs = nni_block_sites(M.n_clv);
         const int max_sb = (int)((std::min<int64_t>(tile, d.P) + nni_bs - 1) / nni_bs);
         CU(d.nni_partials.ensure(sizeof(double) * (size_t)std::max<size_t>(nm, 2 * jobs.size()) * (size_t)max_sb));
@@ -1201,7 +1218,7 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
                 for (int dl = 0; dl <= T.max_depth; ++dl) { // upper partials, root downwards
                     const int nb = T.dlevel_off[dl + 1] - T.dlevel_off[dl];
                     if (nb <= 0) continue;
-                    ScopedTimer tm(ctx, &d, PH_CLV);
+                    ScopedTimer tm(ctx, &d, PH_UPPER);
 #define PHB_UPPER_LAUNCH(MINB)                                                                                         \
     PHB_LAUNCH(upper_level_kernel<MINB>, dim3((unsigned)((int64_t)nb * M.n_clv * bpr)), dim3(CLV_THREADS), d.stream,   \
                d.dops.as<DownOp>() + T.dlevel_off[dl], nb, d.dkids.as<DownChild>(), T.root, M, d.Pmat.as<double>(),    \
@@ -1285,6 +1302,17 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
         }
     }
     S.kernel_launches = ctx->launches;
+    if (ctx->flags & PHB_FLAG_TIMING) { // per-phase device time of the last call (device 0)
+        Device &d0 = ctx->devs[0];
+        S.ms_nni_cache = S.ms_nni_upper = S.ms_nni_edge = 0;
+        for (auto &pr : d0.ev_log) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, d0.ev_pool[pr.second].a, d0.ev_pool[pr.second].b);
+            if (pr.first == PH_CLV) S.ms_nni_cache += ms;
+            else if (pr.first == PH_UPPER) S.ms_nni_upper += ms;
+            else if (pr.first == PH_DOWN) S.ms_nni_edge += ms;
+        }
+    }
     return PHB_OK;
 }
 
@@ -2023,6 +2051,8 @@ int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns
     st.sweep_stream_bytes = (int64_t)S.stream_bytes;
     st.sweep_guards = S.n_guards;
     st.sweep_normouts = S.n_normout;
+    st.sweep_fp64_instr = S.fp64_instr;
+    st.sweep_flops = S.flops;
     if (per_pattern) return phb_get_per_pattern(ctx, per_pattern);
     return PHB_OK;
 }

@@ -28,6 +28,9 @@ struct SweepSched {
     int rec_cap = 0;    // largest record
     int max_rows = 0;   // most tip-code rows any op needs (<= 3: a tip and a super-tip)
     int n_stage_descs = 0;
+    // arithmetic one sweep executes per (site pattern, CLV category), fast paths: FP64 instructions (DMUL / DFMA) and
+    // flops (DFMA = 2).  A 4x4 matrix-vector product is 4 DMUL + 12 DFMA; lookups cost none.
+    double fp64_instr = 0, flops = 0;
     size_t stream_bytes = 0;
     std::vector<SweepStage> stages;      // ring stages (+ one padding entry): the producer's work list
     std::vector<uint64_t> op_off;        // stream offset of every op's record (the transition kernel drops the headers there)
@@ -42,6 +45,16 @@ struct SweepSched {
     std::vector<uint32_t> base_w0;      // per op: w0 without SW_FLAG_GUARD / SW_FLAG_NORMOUT
     std::vector<int> post_order;        // children before parents
     std::vector<int> kid_off, kids;     // copy of the child lists
+    std::vector<int> built_leaf_row;    // and of the leaf -> alignment row map, root and slots the schedule was built for
+    std::vector<int> built_slot;
+    int built_root = -1;
+    // the schedule depends on the topology only (branch lengths enter through the stream and the guard plan): a
+    // set_tree with the same child lists, rows and root -- every step of a branch-length optimisation -- reuses it
+    bool same_topology(int root, const std::vector<int> &child_off, const std::vector<int> &children,
+                       const std::vector<int> &leaf_row, const std::vector<int> &slot) const
+    {
+        return valid && root == built_root && child_off == kid_off && children == kids && leaf_row == built_leaf_row && slot == built_slot;
+    }
     int n_guards = 0, n_normout = 0;
 
     // child_off/children: CSR child lists; leaf_row: alignment row per leaf; root must be internal.
@@ -87,6 +100,9 @@ struct SweepSched {
         post_order = order;
         kid_off = child_off;
         kids = children;
+        built_leaf_row = leaf_row;
+        built_slot = slot;
+        built_root = root;
         pseudo.assign(n, 0);
         if (collapse)
             for (int v = 0; v < n; ++v) {
@@ -331,6 +347,19 @@ struct SweepSched {
         memset(&cur, 0, sizeof cur);
         stages.push_back(cur); // padding entry: the producer reads one stage ahead
         stream_bytes = off;
+        fp64_instr = flops = 0;
+        for (const Rec &r : recs) {
+            int mv = 0, mul = 0; // matrix-vector products, elementwise products of 4
+            switch (r.h.kind) {
+            case SW_TI: case SW_SI: mv = 1; mul = 1; break;
+            case SW_II: mv = 2; mul = 1; break;
+            case SW_TS: case SW_MULTIP: case SW_MULPOP: mul = 1; break;
+            case SW_APPLY: mv = 1; break;
+            default: break; // TT, LOADTIP: table rows only
+            }
+            fp64_instr += 16.0 * mv + 4.0 * mul;
+            flops += 28.0 * mv + 4.0 * mul;
+        }
         ops.assign(recs.size() + 2, SweepOp{0, 0, 0, 0}); // + two padding entries
         base_w0.assign(recs.size(), 0);
         done_op.assign(n, -1);

@@ -153,6 +153,27 @@ def test_folded_cherries_match_explicit_cherries(emu_lib, monkeypatch):
         assert np.max(np.abs(a[1] - b[1])) < 1e-10
 
 
+def test_schedule_reuse_across_branch_length_updates(emu_lib):
+    """set_tree with the same topology and new branch lengths (a branch-length optimiser's loop) reuses the sweep
+    schedule; the stream and the guard plan follow the new lengths: same result as a fresh context."""
+    case = workloads.make_case(40, 120, model="gtr_i_g4", seed=51, ambiguity=0.05)
+    ft = case.ft
+    rng = np.random.default_rng(52)
+    with capi.Context(library=emu_lib) as ctx:
+        workloads.load_into(ctx, case)
+        first = ctx.log_likelihood()
+        for _ in range(3):
+            ft["blen"] = np.clip(rng.exponential(0.3, ft["n_nodes"]), 1e-6, 5.0).astype(np.float32).astype(np.float64)
+            ctx.set_tree(ft["postorder"], ft["child_off"], ft["children"], ft["blen"], ft["leaf_row"], ft["root"])
+            tot, per = ctx.log_likelihood(per_pattern=True)
+            with capi.Context(library=emu_lib) as fresh:
+                workloads.load_into(fresh, case)
+                assert fresh.log_likelihood() == tot
+            ref_tot, ref_per = oracle.log_likelihood_flat(ft, case.model, case.patterns, case.mult, mode=0, n_threads=4)
+            _cases.assert_lnl_close(tot, per, ref_tot, ref_per)
+        assert tot != first
+
+
 def test_guard_plan_matches_guard_everywhere(emu_lib, monkeypatch):
     """The host places the underflow guard only where its bound on the accumulated shrink needs it
     (sweep_sched.h plan_guards).  Rescaling is an exact power of two, so the placement changes no CLV bit: the

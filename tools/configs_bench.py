@@ -210,6 +210,197 @@ CASES = {
 }
 
 
+# --------------------------------------------------------------------------------------------------
+# bench.py's `configs` object: BASELINE.json configs 2, 4, 5 + joint ASR + compression at full size on one GPU,
+# each with its device time, its throughput, the fraction of the measured HBM copy rate its algorithmic bytes
+# amount to, and parity deltas against the CPU oracle on a small pattern sample of the SAME data.
+# (The oracle is the checker here, never the thing timed.)
+# --------------------------------------------------------------------------------------------------
+def _oracle_model(name):
+    from oracle import workloads
+
+    return workloads.make_model(name)
+
+
+def _sample_patterns(ctx, n):
+    return ctx.get_alignment(0, n)
+
+
+def _oracle_tree(tree):
+    """the flat tree as the oracle wants it (adds the pre-order)"""
+    ft = dict(tree)
+    pre, st = [], [int(ft["root"])]
+    co, ch = ft["child_off"], ft["children"]
+    while st:
+        v = st.pop()
+        pre.append(v)
+        st.extend(reversed(ch[co[v]:co[v + 1]].tolist()))
+    ft["preorder"] = np.asarray(pre, np.int32)
+    return ft
+
+
+def driver_configs(hbm_gbs, reps=3, which=("cfg2", "cfg4", "joint", "cfg5", "compress")):
+    import oracle
+
+    oracle.build()
+    out = {}
+
+    def guard(name, fn):
+        if name not in which:
+            return
+        try:
+            out[name] = fn()
+        except Exception as e:  # one failing case must not hide the others or the headline
+            out[name] = {"error": f"{type(e).__name__}: {e}"}
+
+    def cfg2():
+        n, P, seed = 1000, 100_000, 0x5EED0002
+        tree = synthetic.yule_flat(n, seed)
+        with capi.Context() as ctx:
+            synthetic.load_into(ctx, tree, model_for("gtr_g4"))
+            ctx.simulate_alignment(P, seed=seed ^ 0xA11C)
+            _, dev_ms, wall_ms = timed(ctx, ctx.log_likelihood, reps)
+            tot, per = ctx.log_likelihood(per_pattern=True)
+            st = ctx.stats()
+            pats = _sample_patterns(ctx, 256)
+        _r, ref_per = oracle.log_likelihood_flat(_oracle_tree(tree), _oracle_model("gtr_g4"), pats, mode=0, n_threads=8)
+        return dict(workload="GTR+G4 log-likelihood, 1000 taxa x 100k patterns", device_ms=dev_ms, wall_ms=wall_ms,
+                    updates_per_s=(n - 1) * P / (dev_ms * 1e-3),
+                    algorithmic_frac_of_hbm=st["algorithmic_bytes"] / (dev_ms * 1e-3) / 1e9 / hbm_gbs,
+                    parity=dict(sample_patterns=256, max_abs_per_pattern_lnl=float(np.max(np.abs(per[:256] - ref_per))),
+                                total_equals_sum_rel=float(abs(tot - per.sum()) / abs(tot))))
+
+    def cfg4():
+        import torch
+
+        n, P, seed, K = 5000, 500_000, 0x5EED0004, 4
+        tree = synthetic.yule_flat(n, seed)
+        with capi.Context(flags=capi.FLAG_TIMING) as ctx:
+            synthetic.load_into(ctx, tree, model_for("gtr_g4"))
+            ctx.simulate_alignment(P, seed=seed ^ 0xA11C)
+            states = torch.zeros((tree["n_nodes"], P), dtype=torch.uint8, pin_memory=True).numpy()
+            tot = capi.C.c_double(0.0)
+
+            def call():
+                ctx._check(ctx.lib.L.phb_marginal_asr(ctx._h, states.ctypes.data_as(capi.C.POINTER(capi.C.c_uint8)), None,
+                                                      capi.C.byref(tot)))
+                return tot.value
+
+            _, dev_ms, wall_ms = timed(ctx, call, reps)
+            st = ctx.stats()
+            pats = _sample_patterns(ctx, 64)
+        rt, rper, rstates, rpost = oracle.marginal_asr_flat(_oracle_tree(tree), _oracle_model("gtr_g4"), pats, want_posteriors=True, n_threads=8)
+        diff = states[:, :64] != rstates
+        srt = np.sort(rpost, axis=2)
+        gap = srt[..., 3] - srt[..., 2]
+        up_bytes = (32.0 * K * (2 * n - 3) + n) * P
+        down_bytes = (32.0 * K * (4 * n - 4) + 3 * n - 1) * P
+        return dict(workload="marginal ASR GTR+G4, 5000 taxa x 500k patterns (states to pinned host memory)", device_ms=dev_ms,
+                    wall_ms=wall_ms, ms_up=st["ms_clv"], ms_down=st["ms_down"],
+                    node_site_updates_per_s=((n - 1) + (2 * n - 1)) * P / (dev_ms * 1e-3),
+                    algorithmic_frac_of_hbm=(up_bytes + down_bytes) / (dev_ms * 1e-3) / 1e9 / hbm_gbs,
+                    d2h_bytes=int(states.nbytes),
+                    parity=dict(sample_patterns=64, state_mismatches=int(diff.sum()),
+                                state_mismatches_away_from_ties=int((diff & (gap >= 1e-10)).sum()), states_compared=int(diff.size)))
+
+    def joint():
+        import torch
+
+        n, P, seed, K = 5000, 500_000, 0x5EED0004, 4
+        tree = synthetic.yule_flat(n, seed)
+        with capi.Context(flags=capi.FLAG_TIMING) as ctx:
+            synthetic.load_into(ctx, tree, model_for("gtr_g4"))
+            ctx.simulate_alignment(P, seed=seed ^ 0xA11C)
+            states = torch.zeros((tree["n_nodes"], P), dtype=torch.uint8, pin_memory=True).numpy()
+            tot = capi.C.c_double(0.0)
+
+            def call():
+                ctx._check(ctx.lib.L.phb_joint_asr(ctx._h, states.ctypes.data_as(capi.C.POINTER(capi.C.c_uint8)), capi.C.byref(tot)))
+                return tot.value
+
+            _, dev_ms, wall_ms = timed(ctx, call, reps)
+            per = ctx.per_pattern()
+            pats = _sample_patterns(ctx, 32)
+        rt, rper, rstates = oracle.joint_asr_flat(_oracle_tree(tree), _oracle_model("gtr_g4"), pats, n_threads=8)
+        up_bytes = (32.0 * K * (2 * n - 3) + n) * P
+        down_bytes = (34.0 * (n - 2) + 3.0 * n + 1) * P
+        return dict(workload="joint (Viterbi) ASR GTR+G4, 5000 taxa x 500k patterns", device_ms=dev_ms, wall_ms=wall_ms,
+                    node_site_updates_per_s=((n - 1) + (2 * n - 1)) * P / (dev_ms * 1e-3),
+                    algorithmic_frac_of_hbm=(up_bytes + down_bytes) / (dev_ms * 1e-3) / 1e9 / hbm_gbs,
+                    parity=dict(sample_patterns=32, max_abs_per_pattern_value=float(np.max(np.abs(per[:32] - rper))),
+                                patterns_with_state_mismatch=int((states[:, :32] != rstates).any(axis=0).sum())))
+
+    def cfg5():
+        n, P, seed, n_moves = 2000, 200_000, 0x5EED0005, 1024
+        tree = synthetic.yule_flat(n, seed)
+        co = tree["child_off"]
+        internal = [v for v in range(tree["n_nodes"]) if co[v + 1] > co[v] and v != tree["root"]]
+        moves = [(v, left) for v in internal for left in (0, 1)][:n_moves]
+        ids, left = [m[0] for m in moves], [m[1] for m in moves]
+        with capi.Context(flags=capi.FLAG_TIMING) as ctx:
+            synthetic.load_into(ctx, tree, model_for("gtr_g4"))
+            ctx.simulate_alignment(P, seed=seed ^ 0xA11C)
+            base, base_per = ctx.log_likelihood(per_pattern=True)
+            got, dev_ms, wall_ms = timed(ctx, lambda: ctx.score_nni(ids, left), reps)
+            st = ctx.stats()
+            pats = _sample_patterns(ctx, 64)
+        with capi.Context(flags=capi.FLAG_NNI_FULL) as ctx:  # the reference's caller loop: rebuild + full evaluation
+            synthetic.load_into(ctx, tree, model_for("gtr_g4"))
+            ctx.simulate_alignment(P, seed=seed ^ 0xA11C)
+            pick = [0, 1, len(moves) // 2, len(moves) - 1]
+            full = ctx.score_nni([ids[i] for i in pick], [left[i] for i in pick])
+        _r, ref_per = oracle.log_likelihood_flat(_oracle_tree(tree), _oracle_model("gtr_g4"), pats, mode=0, n_threads=8)
+        return dict(workload="1,024 NNI neighbours of a 2000-taxon tree x 200k patterns (GTR+G4), path-only rescoring",
+                    device_ms=dev_ms, wall_ms=wall_ms, trees_per_s=len(moves) / (dev_ms * 1e-3),
+                    equivalent_updates_per_s=len(moves) * (n - 1) * P / (dev_ms * 1e-3),
+                    read_frac_of_hbm=st["nni_read_bytes"] / (dev_ms * 1e-3) / 1e9 / hbm_gbs, cache_GB=st["nni_cache_bytes"] / 1e9,
+                    phases_ms=dict(cache_pass=st["ms_nni_cache"], upper_pass=st["ms_nni_upper"], edge_kernel=st["ms_nni_edge"]),
+                    parity=dict(base_tree_sample_patterns=64, base_max_abs_per_pattern_lnl=float(np.max(np.abs(base_per[:64] - ref_per))),
+                                neighbours_rescored_in_full=len(pick),
+                                max_rel_vs_full_rescoring=float(np.max(np.abs(got[pick] - full) / np.abs(full)))))
+
+    def compress():
+        import torch
+
+        n, W, seed = 10_000, 1_000_000, 0x5EED0003
+        tree = synthetic.yule_flat(n, seed)
+        with capi.Context(flags=capi.FLAG_TIMING) as ctx:
+            synthetic.load_into(ctx, tree, model_for("gtr_g4"))
+            ctx.simulate_alignment(W, seed=seed ^ 0xA11C)
+            host = torch.empty((n, W), dtype=torch.uint8, pin_memory=True)
+            h = host.numpy()
+            chunk = max(1, (256 << 20) // n)
+            for p0 in range(0, W, chunk):
+                c = min(chunk, W - p0)
+                h[:, p0:p0 + c] = ctx.get_alignment(p0, c, layout=capi.LAYOUT_ROW_MAJOR)
+            h[:, W - 1000:] = h[:, :1000]  # the last 1,000 columns repeat the first 1,000: known duplicates
+            s2p = np.zeros(W, np.uint64)
+            mult = np.zeros(W, np.uint64)
+            npat = capi.C.c_int64(0)
+            u64p = capi.C.POINTER(capi.C.c_uint64)
+
+            def call():
+                ctx._check(ctx.lib.L.phb_compress_columns(ctx._h, n, W, capi.C.c_void_p(host.data_ptr()), capi.C.byref(npat),
+                                                          s2p.ctypes.data_as(u64p), mult.ctypes.data_as(u64p)))
+                return npat.value
+
+            Pn, dev_ms, wall_ms = timed(ctx, call, max(1, reps - 1))
+        # first-appearance numbering (alignment.rs:104-120): distinct columns keep their order, the repeats map back
+        ok_s2p = bool(np.array_equal(s2p[:W - 1000], np.arange(W - 1000, dtype=np.uint64)) and
+                      np.array_equal(s2p[W - 1000:], np.arange(1000, dtype=np.uint64)))
+        ok_mult = bool(np.all(mult[:1000] == 2) and np.all(mult[1000:Pn] == 1))
+        return dict(workload="compress_columns, 10,000 rows x 1M sites from pinned host rows (999,000 distinct columns)",
+                    wall_ms=wall_ms, device_ms=dev_ms, input_GB=n * W / 1e9, end_to_end_GBps=n * W / (wall_ms * 1e-3) / 1e9,
+                    parity=dict(n_patterns=int(Pn), expected_patterns=W - 1000, site_to_pattern_exact=ok_s2p, multiplicity_exact=ok_mult))
+
+    guard("cfg2", cfg2)
+    guard("cfg4", cfg4)
+    guard("joint", joint)
+    guard("cfg5", cfg5)
+    guard("compress", compress)
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--cases", default="cfg1,cfg2,cfg3_rank8,cfg4_small,cfg5")

@@ -1,0 +1,54 @@
+#!/usr/bin/env python
+"""Writes profiles/traffic.json from an `ncu --set full` report of bench.py's top kernel: DRAM bytes per launch
+(dram__bytes_read.sum + dram__bytes_write.sum) together with the SHA-256 of the kernel source it was taken from.
+bench.py quotes `roofline.traffic` only while that hash still matches the source in the tree.
+
+  python tools/traffic_from_ncu.py gpurun_out/<report>.ncu-rep [--kernel sweep_kernel] [--source sweep.cuh]
+"""
+import argparse
+import csv
+import hashlib
+import json
+import os
+import subprocess
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("report")
+    ap.add_argument("--kernel", default="sweep_kernel")
+    ap.add_argument("--source", default="sweep.cuh")
+    ap.add_argument("--taxa", type=int, default=10_000)
+    ap.add_argument("--patterns", type=int, default=1_000_000)
+    args = ap.parse_args()
+    out = subprocess.run(["ncu", "-i", args.report, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr, units, data = rows[0], rows[1], rows[2]
+    col = {h: i for i, h in enumerate(hdr)}
+
+    def val(name):
+        v = float(data[col[name]].replace(",", ""))
+        u = units[col[name]].lower()
+        return v * {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9, "tbyte": 1e12}.get(u, 1)
+
+    rd, wr = val("dram__bytes_read.sum"), val("dram__bytes_write.sum")
+    src = os.path.join(ROOT, "phylo-rs_b200", "csrc", args.source)
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        tj = json.load(open(path))
+    except Exception:
+        tj = {}
+    tj[args.kernel] = {
+        "dram_bytes_per_launch": rd + wr, "dram_read": rd, "dram_write": wr, "patterns": args.patterns, "taxa": args.taxa,
+        "duration_ms_under_ncu": val("gpu__time_duration.sum") / 1e6 if "gpu__time_duration.sum" in col else None,
+        "capture": os.path.basename(args.report), "source_file": args.source,
+        "source_sha256": hashlib.sha256(open(src, "rb").read()).hexdigest(),
+    }
+    json.dump(tj, open(path, "w"), indent=1)
+    print(json.dumps(tj[args.kernel], indent=1))
+
+
+if __name__ == "__main__":
+    main()
