@@ -12,6 +12,7 @@
 #include "joint.cuh"
 #include "compress.cuh"
 #include "sweep_sched.h"
+#include "down_sweep.cuh"
 #include "../../include/phylo_b200.h"
 
 #include <algorithm>
@@ -241,9 +242,10 @@ struct Device {
     DevBuf tips, mult, leaf_ls, inv_mask, per_pattern, row_invalid, Pmat, blen, clv, scale, cat_ll,
         partials, total, ops, gops, gkids, dops, dkids, leaf_rows, states, posteriors, staging,
         sim_pre, sim_parent, sim_depth, sim_leafrow, sim_stack, scratch, sw_descs, sw_opoff, sw_blocks, sw_stream, sw_gstack,
-        sw_err, sw_ops, uops, ukids, lnP, jbest, nni_upper, nni_uexps, nni_jobs, nni_rows, nni_exps, nni_partials, nni_totals, nni_moves, nni_steps, nni_need;
+        sw_err, sw_ops, dn_ops, dn_descs, dn_blocks, dn_stream, dn_opoff, dn_gstack, uops, ukids, lnP, jbest, nni_upper, nni_uexps, nni_jobs, nni_rows, nni_exps, nni_partials, nni_totals, nni_moves, nni_steps, nni_need;
     bool sweep_uploaded = false;
     bool sweep_ops_stale = false; // the guard flags of the op table changed since the last upload
+    bool down_uploaded = false;   // pre-order sweep schedule (down_sweep.cuh)
     int sm_count = 0;
     size_t smem_optin = 0;
     cudaStream_t copy_stream = nullptr;          // H2D of alignment chunks, overlapped with packing / sweeping
@@ -286,6 +288,7 @@ struct phb_ctx {
     SweepSched sweep;      // fused-sweep op stream for (tree, n_clv)
     SweepGeom sweep_geom;
     bool sweep_guards_valid = false; // guard flags planned for the current branch lengths and rates
+    DownSched down;        // pre-order sweep schedule of the marginal-ASR down pass for (tree, n_clv)
     // marginal ASR: caller's output buffers, so that a finished tile's states go home while the next tile runs
     uint8_t *asr_states_out = nullptr;
     double *asr_post_out = nullptr;
@@ -468,7 +471,7 @@ int plan_device(phb_ctx *ctx, Device &d, const ModelDev &M, bool asr, bool want_
     d.tile_pad = tile;
     d.n_tiles = (int)((d.P + tile - 1) / tile);
     if (d.P == 0) d.n_tiles = 0;
-    CU(d.clv.ensure(per_site * (size_t)tile));
+    CU(d.clv.ensure(per_site * (size_t)(tile + 512))); // + slack: the blocked layout of the sweep path rounds the tile up to whole blocks
     CU(d.scale.ensure(sizeof(int) * (size_t)std::max(M.n_clv, 1) * (size_t)tile));
     if (asr) CU(d.cat_ll.ensure(sizeof(double) * (size_t)M.n_cat * (size_t)tile));
     if (asr) { // joint ASR: ln P table and the winning category per pattern
@@ -733,7 +736,8 @@ int launch_sweep_transition(phb_ctx *ctx, Device &d, const ModelDev &M)
 // clv_out != null selects the storing variant (marginal-ASR up pass): CLVs of the launch's patterns go to
 // clv_out[slot][cat][state][site - p0] with row stride tile_pad, per-category log-likelihoods to cat_ll_out.
 int launch_sweep_range(phb_ctx *ctx, Device &d, const ModelDev &M, const SweepGeom &G, int64_t p0, int64_t np,
-                       size_t part_off, double *clv_out = nullptr, double *cat_ll_out = nullptr, size_t tile_pad = 0)
+                       size_t part_off, double *clv_out = nullptr, double *cat_ll_out = nullptr, size_t tile_pad = 0,
+                       bool blocked = false)
 {
     const SweepSched &S = ctx->sweep;
     const int sites_per_block = 4 * G.Q;
@@ -768,7 +772,8 @@ int launch_sweep_range(phb_ctx *ctx, Device &d, const ModelDev &M, const SweepGe
     sp.clv_out = clv_out;
     sp.cat_ll_out = cat_ll_out;
     sp.tile_pad = tile_pad;
-    sp.slot_stride = (size_t)M.n_clv * 4 * tile_pad;
+    sp.slot_stride = blocked ? (size_t)n_blocks * M.n_clv * 4 * sites_per_block : (size_t)M.n_clv * 4 * tile_pad;
+    sp.blocked = blocked ? 1 : 0;
     ScopedTimer tm(ctx, &d, PH_CLV);
 #ifndef PHB_HOST_EMU
     static bool attr_set[64] = {false};
@@ -790,6 +795,130 @@ int launch_sweep_reduce(phb_ctx *ctx, Device &d, size_t n_partials)
     ScopedTimer tm(ctx, &d, PH_ROOT);
     PHB_LAUNCH(final_reduce_kernel, dim3(1), dim3(1024), d.stream, d.partials.as<double>(), (int)n_partials,
                d.total.as<double>(), d.sw_err.as<unsigned int>());
+    CHECK_LAUNCH();
+    return PHB_OK;
+}
+
+// ---- pre-order sweep of the marginal-ASR down pass (down_sweep.cuh) ---------------------------------
+constexpr int DN_MAX_K = 5; // categories the pre-order kernel is instantiated for (GTR+I+G4 carries 5 literal ones)
+
+int ensure_down(phb_ctx *ctx, const ModelDev &M)
+{
+    const TreeSched &T = ctx->tree;
+    DownSched &D = ctx->down;
+    if (!D.same_topology(T.root, T.child_off, T.children, T.leaf_row, T.slot, M.n_clv)) {
+        for (Device &d : ctx->devs) { // the old host image may still be in flight
+            cudaSetDevice(d.ordinal);
+            cudaStreamSynchronize(d.stream);
+            d.down_uploaded = false;
+        }
+        D.build(T.n, T.root, T.child_off, T.children, T.leaf_row, T.slot, M.n_clv);
+        if (getenv("PHB_SWEEP_TRACE"))
+            fprintf(stderr, "pre-order schedule: ops %d (LEAF %d DESCEND %d DEFER %d RESUME %d) levels %d stream %zu B\n", D.n_ops,
+                    D.count_kind[DN_LEAF], D.count_kind[DN_DESCEND], D.count_kind[DN_DEFER], D.count_kind[DN_RESUME], D.n_levels,
+                    D.stream_bytes);
+    }
+    for (Device &d : ctx->devs) {
+        if (d.down_uploaded) continue;
+        CU(cudaSetDevice(d.ordinal));
+        CU(d.dn_ops.ensure(sizeof(SweepOp) * D.ops.size()));
+        CU(d.dn_descs.ensure(sizeof(DownDesc) * D.descs.size()));
+        CU(d.dn_blocks.ensure(sizeof(SweepBlock) * std::max<size_t>(D.blocks.size(), 1)));
+        CU(d.dn_opoff.ensure(sizeof(uint64_t) * std::max<size_t>(D.op_off.size(), 1)));
+        CU(d.dn_stream.ensure(D.stream_bytes + 16));
+        CU(cudaMemcpyAsync(d.dn_ops.p, D.ops.data(), sizeof(SweepOp) * D.ops.size(), cudaMemcpyHostToDevice, d.stream));
+        CU(cudaMemcpyAsync(d.dn_descs.p, D.descs.data(), sizeof(DownDesc) * D.descs.size(), cudaMemcpyHostToDevice, d.stream));
+        CU(cudaMemcpyAsync(d.dn_blocks.p, D.blocks.data(), sizeof(SweepBlock) * D.blocks.size(), cudaMemcpyHostToDevice, d.stream));
+        CU(cudaMemcpyAsync(d.dn_opoff.p, D.op_off.data(), sizeof(uint64_t) * D.op_off.size(), cudaMemcpyHostToDevice, d.stream));
+        d.down_uploaded = true;
+    }
+    return PHB_OK;
+}
+
+// transposed P(t) of every edge + the op headers, written into the pre-order stream (once per evaluation)
+int launch_down_transition(phb_ctx *ctx, Device &d, const ModelDev &M)
+{
+    const DownSched &D = ctx->down;
+    ScopedTimer tm(ctx, &d, PH_TRANSITION);
+    const int nthreads = (int)D.blocks.size() * M.n_clv + D.n_ops;
+    PHB_LAUNCH(sweep_transition_kernel, dim3((nthreads + 127) / 128), dim3(128), d.stream, d.dn_blocks.as<SweepBlock>(),
+               (int)D.blocks.size(), d.blen.as<double>(), M, d.dn_stream.as<unsigned char>(), d.dn_ops.as<SweepOp>(),
+               d.dn_opoff.as<uint64_t>(), D.n_ops);
+    CHECK_LAUNCH();
+    return PHB_OK;
+}
+
+// One persistent pre-order launch over patterns [p0, p0 + np) whose up-pass CLVs the storing sweep left in blocked
+// layout with block width S.
+int launch_down_sweep(phb_ctx *ctx, Device &d, const ModelDev &M, int S, int64_t p0, int64_t np, bool want_post)
+{
+    const DownSched &D = ctx->down;
+    const TreeSched &T = ctx->tree;
+    const int K = M.n_clv;
+    const int64_t n_blocks = (np + S - 1) / S;
+    const size_t tile_bytes = (size_t)K * 4 * S * 8;
+    const int data_off = (DN_STAGE_OPS * D.rec_bytes + 127) / 128 * 128;
+    const int rows_off = data_off + (int)((tile_bytes + 127) / 128 * 128);
+    const int row_pitch = (S + 15) / 16 * 16;
+    const int stage_bytes = (rows_off + DN_STAGE_ROWS * row_pitch + 127) / 128 * 128;
+    // stages first (each holds one node's tile: they are what hides the HBM latency), the rest is the stack
+    int n_stages = 3, smem_levels = 0;
+    if (const char *e = getenv("PHB_DOWN_STAGES")) n_stages = std::max(2, std::min(6, atoi(e)));
+    while (n_stages > 2 && SW_BAR_BYTES + (size_t)n_stages * stage_bytes > d.smem_optin) --n_stages;
+    if (SW_BAR_BYTES + (size_t)n_stages * stage_bytes > d.smem_optin)
+        return ctx->fail(PHB_ERR_INVALID_MODEL_PARAMETER, "pre-order sweep: %d categories do not fit one CTA", K);
+    smem_levels = (int)std::min<size_t>((d.smem_optin - SW_BAR_BYTES - (size_t)n_stages * stage_bytes) / tile_bytes, (size_t)D.n_levels);
+    const int g_levels = std::max(0, D.n_levels - smem_levels);
+    const size_t smem_bytes = SW_BAR_BYTES + (size_t)n_stages * stage_bytes + (size_t)smem_levels * tile_bytes;
+    const int grid = (int)std::min<int64_t>(n_blocks, std::max(d.sm_count, 1));
+    if (g_levels > 0) CU(d.dn_gstack.ensure((size_t)std::max(d.sm_count, 1) * g_levels * tile_bytes));
+    DownParams dp;
+    memset(&dp, 0, sizeof dp);
+    dp.ops = d.dn_ops.as<SweepOp>();
+    dp.descs = d.dn_descs.as<DownDesc>();
+    dp.stream = d.dn_stream.as<unsigned char>();
+    dp.n_ops = D.n_ops;
+    dp.n_stage_descs = D.n_stage_descs;
+    dp.rows_off = rows_off;
+    dp.row_pitch = row_pitch;
+    dp.S = S;
+    dp.n_stages = n_stages;
+    dp.stage_bytes = stage_bytes;
+    dp.data_off = data_off;
+    dp.smem_levels = smem_levels;
+    dp.g_levels = g_levels;
+    dp.gstack = d.dn_gstack.as<double>();
+    dp.clv = d.clv.as<double>();
+    dp.slot_stride = (size_t)n_blocks * K * 4 * S;
+    dp.tips = d.tips.as<uint8_t>() + p0;
+    dp.P_pad = d.P_pad;
+    dp.P = np;
+    dp.n_blocks = n_blocks;
+    dp.cat_ll = d.cat_ll.as<double>();
+    dp.tile_pad = (size_t)d.tile_pad;
+    dp.site_ll = d.per_pattern.as<double>() + p0;
+    dp.states = d.states.as<uint8_t>() + p0;
+    dp.posteriors = want_post ? d.posteriors.as<double>() + p0 * 4 : nullptr;
+    (void)T;
+    ScopedTimer tm(ctx, &d, PH_DOWN);
+#ifndef PHB_HOST_EMU
+    static bool attr_set[64] = {false};
+    if (!attr_set[d.ordinal & 63]) {
+        CU(cudaFuncSetAttribute(asr_down_sweep_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)d.smem_optin));
+        CU(cudaFuncSetAttribute(asr_down_sweep_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)d.smem_optin));
+        CU(cudaFuncSetAttribute(asr_down_sweep_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)d.smem_optin));
+        CU(cudaFuncSetAttribute(asr_down_sweep_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)d.smem_optin));
+        CU(cudaFuncSetAttribute(asr_down_sweep_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)d.smem_optin));
+        attr_set[d.ordinal & 63] = true;
+    }
+#endif
+    switch (K) {
+    case 1: PHB_LAUNCH_SMEM(asr_down_sweep_kernel<1>, dim3(grid), dim3(S + 32), smem_bytes, d.stream, dp, M); break;
+    case 2: PHB_LAUNCH_SMEM(asr_down_sweep_kernel<2>, dim3(grid), dim3(S + 32), smem_bytes, d.stream, dp, M); break;
+    case 3: PHB_LAUNCH_SMEM(asr_down_sweep_kernel<3>, dim3(grid), dim3(S + 32), smem_bytes, d.stream, dp, M); break;
+    case 4: PHB_LAUNCH_SMEM(asr_down_sweep_kernel<4>, dim3(grid), dim3(S + 32), smem_bytes, d.stream, dp, M); break;
+    default: PHB_LAUNCH_SMEM(asr_down_sweep_kernel<5>, dim3(grid), dim3(S + 32), smem_bytes, d.stream, dp, M); break;
+    }
     CHECK_LAUNCH();
     return PHB_OK;
 }
@@ -832,8 +961,14 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
     // marginal ASR: the up pass is the storing sweep (each CLV written once, never read back by the up pass)
     const bool asr_sweep = asr && !joint && !(ctx->flags & PHB_FLAG_LEVEL_KERNELS) && T.n_internal > 0 && M.n_clv > 0 &&
                            M.n_clv <= SW_MAX_CONSUMERS / 8;
+    // ... and its pre-order pass the on-chip pre-order sweep (every up-pass CLV read once, nothing but states written)
+    const bool asr_blocked = asr_sweep && M.n_clv <= DN_MAX_K && M.n_clv == M.n_cat && !getenv("PHB_ASR_LEVEL_DOWN");
     if (use_sweep || asr_sweep) {
         rc = ensure_sweep(ctx, M, asr_sweep);
+        if (rc) return rc;
+    }
+    if (asr_blocked) {
+        rc = ensure_down(ctx, M);
         if (rc) return rc;
     }
     Device &d0 = ctx->devs[0];
@@ -842,7 +977,7 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
     const bool timing = ctx->flags & PHB_FLAG_TIMING;
     for (Device &d : ctx->devs) {
-        const int64_t wave = asr_sweep ? (int64_t)std::max(d.sm_count, 1) * 4 * sweep_q_max(M.n_clv) : 0;
+        const int64_t wave = asr_sweep ? (int64_t)std::max(d.sm_count, 1) * 4 * (asr_blocked ? sweep_q_asr(M.n_clv) : sweep_q_max(M.n_clv)) : 0;
         rc = plan_device(ctx, d, M, asr, want_post, use_sweep, wave);
         if (rc) return rc;
     }
@@ -892,24 +1027,30 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
         SweepGeom tile_geom;
         if (asr_sweep) { // geometry for one tile's worth of patterns; partial sums are per sweep block
             size_t smem_max = d.smem_optin;
-            if (!tile_geom.plan(ctx->sweep, smem_max, std::min<int64_t>(d.tile_pad, d.P), std::max(d.sm_count, 1)))
+            if (!tile_geom.plan(ctx->sweep, smem_max, std::min<int64_t>(d.tile_pad, d.P), std::max(d.sm_count, 1),
+                                asr_blocked ? sweep_q_asr(M.n_clv) : 0))
                 return ctx->fail(PHB_ERR_INVALID_MODEL_PARAMETER, "sweep: %d CLV categories do not fit one CTA", M.n_clv);
             const int64_t bs = 4 * tile_geom.Q;
             CU(d.partials.ensure(sizeof(double) * (size_t)(d.n_tiles * ((d.tile_pad + bs - 1) / bs + 1))));
             rc = launch_sweep_transition(ctx, d, M);
             if (rc) return rc;
+            if (asr_blocked) {
+                rc = launch_down_transition(ctx, d, M);
+                if (rc) return rc;
+            }
         }
         for (int t = 0; t < d.n_tiles; ++t) {
             int64_t off = (int64_t)t * d.tile_pad;
             int len = (int)std::min<int64_t>(d.tile_pad, d.P - off);
             if (asr_sweep) {
                 rc = launch_sweep_range(ctx, d, M, tile_geom, off, len, part_off, d.clv.as<double>(), d.cat_ll.as<double>(),
-                                        (size_t)d.tile_pad);
+                                        (size_t)d.tile_pad, asr_blocked);
             } else
                 rc = joint ? run_tile_joint(ctx, d, M, off, len, part_off) : run_tile_up(ctx, d, M, off, len, part_off, asr);
             if (rc) return rc;
             if (asr) {
-                rc = joint ? PHB_OK : run_tile_down(ctx, d, M, off, len, want_post);
+                rc = joint ? PHB_OK : asr_blocked ? launch_down_sweep(ctx, d, M, 4 * tile_geom.Q, off, len, want_post)
+                                                  : run_tile_down(ctx, d, M, off, len, want_post);
                 if (rc) return rc;
                 if (ctx->asr_states_out) { // ship this tile's states (and posteriors) on the copy stream
                     const int buf = t & 1;
@@ -1386,7 +1527,7 @@ void phb_ctx_destroy(phb_ctx *ctx)
                           &d.clv, &d.scale, &d.cat_ll, &d.partials, &d.total, &d.ops, &d.gops, &d.gkids, &d.dops,
                           &d.dkids, &d.leaf_rows, &d.states, &d.posteriors, &d.staging, &d.sim_pre, &d.sim_parent,
                           &d.sim_depth, &d.sim_leafrow, &d.sim_stack, &d.scratch, &d.sw_descs, &d.sw_blocks,
-                          &d.sw_stream, &d.sw_gstack, &d.sw_err, &d.sw_opoff, &d.sw_ops, &d.uops, &d.ukids, &d.lnP, &d.jbest,
+                          &d.sw_stream, &d.sw_gstack, &d.sw_err, &d.sw_opoff, &d.dn_ops, &d.dn_descs, &d.dn_blocks, &d.dn_stream, &d.dn_opoff, &d.dn_gstack, &d.sw_ops, &d.uops, &d.ukids, &d.lnP, &d.jbest,
                           &d.nni_upper, &d.nni_uexps, &d.nni_jobs, &d.nni_rows, &d.nni_exps, &d.nni_partials, &d.nni_totals, &d.nni_moves, &d.nni_steps, &d.nni_need};
         for (DevBuf *b : bufs) b->release();
         for (auto &ep : d.ev_pool) {

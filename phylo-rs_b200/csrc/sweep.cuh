@@ -92,7 +92,7 @@ struct SweepBlock {
     uint32_t cat_stride;
     int32_t edge;     // dense node id whose branch length parametrises P
     int32_t is_table; // 0: P(t) 4x4; 1: tip table of `edge`; 2: cherry table tip(edge) (.) tip(edge2);
-                      // 3: super-tip table P(edge) * (tip(edge2) (.) tip(edge3))
+                      // 3: super-tip table P(edge) * (tip(edge2) (.) tip(edge3)); 4: P(t) transposed (down_sweep.cuh)
     int32_t edge2, edge3;
     int32_t pad;
 };
@@ -150,6 +150,9 @@ __global__ void sweep_transition_kernel(const SweepBlock *__restrict__ blocks, i
     if (blk.is_table == 0) {
 #pragma unroll
         for (int i = 0; i < 16; ++i) out[i] = p[i];
+    } else if (blk.is_table == 4) { // P^T, row-major (the pre-order sweep's message is P^T post_parent)
+#pragma unroll
+        for (int i = 0; i < 16; ++i) out[i] = p[(i & 3) * 4 + (i >> 2)];
     } else if (blk.is_table == 1) {
         for (uint32_t a = 0; a < 5; ++a) { // two planes of 5 x 16 bytes
             double *lo = out + 2 * a, *hi = lo + SW_TIP_BYTES / 16;
@@ -350,8 +353,9 @@ struct SweepParams {
     // (site relative to the first pattern of this launch), the per-category log-likelihoods to cat_ll_out[cat][site]
     double *clv_out;
     double *cat_ll_out;
-    size_t slot_stride; // n_clv * 4 * tile_pad
+    size_t slot_stride; // n_clv * 4 * tile_pad; blocked layout: n_blocks * n_clv * 4 * (4 Q)
     size_t tile_pad;
+    int blocked;        // clv_out is [slot][site block][cat][state][4 Q]: one node's block is contiguous (down_sweep.cuh)
 };
 
 __device__ __forceinline__ void sw_matvec(const double (&p)[16], const double (&x)[4], double (&y)[4])
@@ -826,23 +830,33 @@ sweep_kernel(SweepParams p, ModelDev M)
                 else guard(v);
             }
             if (STORE && (flags & SW_FLAG_DONE)) {
-                const int64_t rel = b * sites_per_block + 4 * q; // first of this thread's 4 patterns, launch-relative
-                double *dst = p.clv_out + (size_t)h.z * p.slot_stride + (size_t)cc * 4 * p.tile_pad + (size_t)rel;
                 const bool use_u = flags & SW_FLAG_U;
-                if (rel + 3 < p.P) {
+                if (p.blocked) { // whole blocks: the buffer covers n_blocks * 4 Q patterns
+                    double *dst = p.clv_out + (size_t)h.z * p.slot_stride + ((size_t)b * M.n_clv + cc) * (size_t)(4 * sites_per_block) + 4 * q;
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
-                        double2 *d2 = reinterpret_cast<double2 *>(dst + (size_t)i * p.tile_pad);
+                        double2 *d2 = reinterpret_cast<double2 *>(dst + (size_t)i * sites_per_block);
                         d2[0] = use_u ? make_double2(u[0][i], u[1][i]) : make_double2(v[0][i], v[1][i]);
                         d2[1] = use_u ? make_double2(u[2][i], u[3][i]) : make_double2(v[2][i], v[3][i]);
                     }
                 } else {
+                    const int64_t rel = b * sites_per_block + 4 * q; // first of this thread's 4 patterns, launch-relative
+                    double *dst = p.clv_out + (size_t)h.z * p.slot_stride + (size_t)cc * 4 * p.tile_pad + (size_t)rel;
+                    if (rel + 3 < p.P) {
 #pragma unroll
-                    for (int r = 0; r < SW_R; ++r)
-                        if (rel + r < p.P) {
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) dst[(size_t)i * p.tile_pad + r] = use_u ? u[r][i] : v[r][i];
+                        for (int i = 0; i < 4; ++i) {
+                            double2 *d2 = reinterpret_cast<double2 *>(dst + (size_t)i * p.tile_pad);
+                            d2[0] = use_u ? make_double2(u[0][i], u[1][i]) : make_double2(v[0][i], v[1][i]);
+                            d2[1] = use_u ? make_double2(u[2][i], u[3][i]) : make_double2(v[2][i], v[3][i]);
                         }
+                    } else {
+#pragma unroll
+                        for (int r = 0; r < SW_R; ++r)
+                            if (rel + r < p.P) {
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) dst[(size_t)i * p.tile_pad + r] = use_u ? u[r][i] : v[r][i];
+                            }
+                    }
                 }
             }
         } while (!(flags & SW_FLAG_LAST));

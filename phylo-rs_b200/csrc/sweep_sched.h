@@ -522,6 +522,16 @@ inline int sweep_q_step(int n_clv)
 }
 inline int sweep_q_max(int n_clv) { return SW_MAX_CONSUMERS / n_clv / sweep_q_step(n_clv) * sweep_q_step(n_clv); }
 
+// Block width shared by the storing sweep and the pre-order sweep (down_sweep.cuh): 4 Q patterns, where 4 Q is also
+// the pre-order kernel's consumer thread count (a multiple of 32, at most 352 so that 12 warps keep 168 registers).
+inline int sweep_q_asr(int n_clv)
+{
+    int step = sweep_q_step(n_clv);
+    while (step % 8) step += sweep_q_step(n_clv);
+    const int cap = std::min(88, SW_MAX_CONSUMERS / n_clv);
+    return cap / step * step;
+}
+
 // Launch geometry / shared-memory carve-up for a schedule.
 struct SweepGeom {
     int Q = 0, n_consumers = 0, threads = 0, n_stages = 0, stage_bytes = 0, smem_levels = 0, g_levels = 0;
@@ -532,12 +542,13 @@ struct SweepGeom {
     // 320), and the persistent grid needs ceil(blocks / n_sm) passes, so a slightly narrower or wider CTA
     // can save a whole pass when the block count lands just above a multiple of the SM count (the strong-
     // scaling shards of 125k-500k patterns).  PHB_SWEEP_Q overrides the choice (experiments).
-    bool plan(const SweepSched &S, size_t smem_max, int64_t P = 0, int n_sm = 148)
+    bool plan(const SweepSched &S, size_t smem_max, int64_t P = 0, int n_sm = 148, int force_q = 0)
     {
         const int step = sweep_q_step(S.n_clv), q_max = sweep_q_max(S.n_clv);
         if (q_max < step) return false;
         Q = q_max;
-        if (P > 0 && n_sm > 0) {
+        if (force_q > 0) Q = force_q; // the storing sweep writes blocks the pre-order sweep reads back: fixed width
+        else if (P > 0 && n_sm > 0) {
             double best = 1e300;
             for (int q = q_max; q >= step && q >= q_max / 2; q -= step) {
                 const int64_t blocks = (P + 4 * q - 1) / (4 * q);
@@ -549,7 +560,7 @@ struct SweepGeom {
                 }
             }
         }
-        if (const char *e = getenv("PHB_SWEEP_Q")) {
+        if (const char *e = force_q > 0 ? nullptr : getenv("PHB_SWEEP_Q")) {
             const int q = atoi(e) / step * step;
             if (q >= step && q <= q_max) Q = q;
         }
