@@ -56,7 +56,9 @@ extern "C" {
  * v -> root against the cached CLVs of the base tree; for cross-checking the two. */
 #define PHB_FLAG_NNI_FULL (1ull << 3)
 /* phb_score_nni walks v -> root per neighbour (one cached CLV read per ancestor) instead of using the
- * pre-order "upper" partials that make a neighbour a constant-cost edge-local evaluation. */
+ * pre-order "upper" partials that make a neighbour a constant-cost edge-local evaluation.  The walk kernel is a
+ * cross-check only: it is compiled with -DPHB_WITH_WALK (the CPU emulation harness does); the product build
+ * ignores the flag. */
 #define PHB_FLAG_NNI_WALK (1ull << 4)
 
 /* ---- alignment layouts --------------------------------------------------------------------- */

@@ -5,7 +5,7 @@ Layers (DESIGN.md):
   csrc/   hand-written CUDA kernels + the C-ABI shared library libphylo_b200.so (include/phylo_b200.h)
   capi    ctypes binding of that C ABI (what a Rust `extern "C"` block would bind)
   host/   C++ mirror of the reference's host-side interface (PhyloTree / GtrModel / Alignment /
-          TreeLikelihood / MarginalAsr) above the C ABI, plus its Python binding `api`
+          TreeLikelihood / MarginalAsr) above the C ABI (driven from pytest through tests/hostshim/)
 There is no CPU implementation of the path in this package: without the CUDA library and a B200
 the entry points raise.
 """

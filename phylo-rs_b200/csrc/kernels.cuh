@@ -116,34 +116,7 @@ struct GenChild {
 // K0: alignment packing.  ASCII bytes -> tip codes, transposed to [row][P_pad].
 // Replaces the byte->profile step of src/tree/likelihood.rs:104-108 (Nucleotide::profile).
 // ---------------------------------------------------------------------------------------------
-__global__ void pack_pattern_major_kernel(const uint8_t *__restrict__ in, int n_rows, int64_t n_patterns,
-                                          int64_t p_first, uint8_t *__restrict__ tips, int64_t P_pad,
-                                          int64_t dst_off, int *__restrict__ row_invalid)
-{
-    // 32x32 byte tile transpose through shared memory; in[(p_first + p) * n_rows + r]
-    __shared__ uint8_t tile[32][33];
-    int64_t p0 = (int64_t)blockIdx.x * 32;
-    int r0 = blockIdx.y * 32;
-    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
-        int64_t p = p0 + j;
-        int r = r0 + threadIdx.x;
-        uint8_t code = CODE_GAP;
-        if (p < n_patterns && r < n_rows) code = encode_byte(in[(p_first + p) * n_rows + r]);
-        tile[j][threadIdx.x] = code;
-    }
-    __syncthreads();
-    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
-        int r = r0 + j;
-        int64_t p = p0 + threadIdx.x;
-        if (r < n_rows && p < n_patterns) {
-            uint8_t code = tile[threadIdx.x][j];
-            tips[(int64_t)r * P_pad + dst_off + p] = code;
-            if (code == CODE_INVALID) row_invalid[r] = 1;
-        }
-    }
-}
-
-// Wider tile for the same transpose: 64 patterns x 128 rows per block, 128 contiguous input bytes per
+// Tile transpose through shared memory: 64 patterns x 128 rows per block, 128 contiguous input bytes per
 // pattern (whole 128-byte lines, read once), four codes per 32-bit store on the pattern axis.  Requires
 // dst_off % 4 == 0 (the packing loops use chunk offsets that are multiples of 64).
 constexpr int PK_P = 64, PK_R = 128;

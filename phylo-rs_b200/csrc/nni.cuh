@@ -191,6 +191,7 @@ __device__ __forceinline__ void nni_apply_sib(const double *__restrict__ Ps, con
     }
 }
 
+#ifdef PHB_WITH_WALK // the earlier walk design: built for the emulation harness (cross-check in the CPU tests) only
 template <int NC, int MINB>
 __global__ void __launch_bounds__(nni_threads(NC), MINB)
 nni_score_kernel(const NniMove *__restrict__ moves, int n_moves, const NniStep *__restrict__ steps, ModelDev M,
@@ -339,6 +340,7 @@ nni_reduce_kernel(const NniMove *__restrict__ moves, const double *__restrict__ 
     const double r = block_reduce_sum(acc);
     if (threadIdx.x == 0) totals[moves[mi].out] += r;
 }
+#endif // PHB_WITH_WALK
 
 
 // =============================================================================================

@@ -1214,7 +1214,11 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
         moves.push_back(mv);
     }
     // edge-local jobs (upper partials): the two neighbours of one edge (p -> v) share every load
+#ifdef PHB_WITH_WALK
     const bool use_upper = !(ctx->flags & PHB_FLAG_NNI_WALK);
+#else
+    const bool use_upper = true; // the walk kernel is not part of the product build: PHB_FLAG_NNI_WALK is ignored
+#endif
     std::vector<NniEdgeJob> jobs;
     std::vector<int32_t> job_rows; // totals index of partial row 2*job + {0,1}
     if (use_upper) {
@@ -1396,6 +1400,7 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
                 }
                 continue;
             }
+#ifdef PHB_WITH_WALK
             const int chunk = std::max(1, (int)std::min<int64_t>(nm, (int64_t)0x7fffffff / std::max(n_sb, 1)));
             for (int m0 = 0; m0 < nm; m0 += chunk) { // (the grid holds n_sb * moves-in-chunk CTAs)
                 const int cm = std::min(chunk, nm - m0);
@@ -1422,6 +1427,7 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
                            d.nni_partials.as<double>(), n_sb, d.nni_totals.as<double>());
                 CHECK_LAUNCH();
             }
+#endif
         }
         dev_totals[di].resize(n_moves);
         CU(cudaMemcpyAsync(dev_totals[di].data(), d.nni_totals.p, sizeof(double) * (size_t)n_moves, cudaMemcpyDeviceToHost,

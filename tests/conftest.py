@@ -6,6 +6,9 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
+HOSTSHIM = os.path.join(ROOT, "tests", "hostshim")  # phh_* facade + ctypes binding that let pytest drive the C++ mirror
+if HOSTSHIM not in sys.path:
+    sys.path.insert(0, HOSTSHIM)
 
 
 def pytest_configure(config):

@@ -1,4 +1,6 @@
-"""Python binding of the C++ host mirror (host/libphylo_host.so, facade `phh_*` in host/phylo_capi.cpp).
+"""TEST HARNESS: Python binding of the C++ host mirror (phylo-rs_b200/host/, the reference-shaped consumer of the C ABI)
+through the `phh_*` C facade in tests/hostshim/phylo_capi.cpp, so that pytest can drive the C++ classes.  Neither the
+facade nor this module is part of the product: the product is libphylo_b200.so (C ABI) + the C++ mirror above it.
 
 The classes carry the reference's names and call shapes so that tests read like the reference's own
 (`src/tree/likelihood/integration_test.rs`):
@@ -20,7 +22,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-HOST_LIB = os.path.join(_HERE, "host", "libphylo_host.so")
+HOST_LIB = os.path.join(_HERE, "libphylo_hostshim.so")
 
 
 class AsrError(RuntimeError):
@@ -37,7 +39,7 @@ def _lib():
     global _L
     if _L is None:
         if not os.path.exists(HOST_LIB):
-            raise RuntimeError(f"{HOST_LIB} not found: run __graft_entry__.build() first")
+            raise RuntimeError(f"{HOST_LIB} not found: run __graft_entry__.build() first (build_hostshim)")
         L = C.CDLL(HOST_LIB)
         L.phh_last_error.restype = C.c_char_p
         L.phh_error_kind_name.restype = C.c_char_p

@@ -12,8 +12,8 @@ import os
 import numpy as np
 import pytest
 
-from phylo_rs_b200 import api
-from phylo_rs_b200.api import Alignment, GtrModel, PhyloTree
+import hostapi as api
+from hostapi import Alignment, GtrModel, PhyloTree
 
 HERE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 KAT = json.load(open(os.path.join(HERE, "kat.json")))

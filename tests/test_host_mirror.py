@@ -1,4 +1,4 @@
-"""The reference's own hot-path tests, re-stated against the C++ host mirror (phylo_rs_b200.api ->
+"""The reference's own hot-path tests, re-stated against the C++ host mirror (tests/hostshim/hostapi ->
 host/libphylo_host.so -> C ABI -> CUDA kernels).  Names follow `src/tree/likelihood/integration_test.rs`
 and the unit tests in `src/models/*.rs`, `src/alignment.rs`, `tests/tree-tests.rs`.
 
@@ -14,8 +14,8 @@ import pytest
 
 import oracle
 from oracle import RefAlignment, RefModel, parse_newick
-from phylo_rs_b200 import api
-from phylo_rs_b200.api import Alignment, AsrError, GtrModel, Nucleotide, PhyloTree
+import hostapi as api
+from hostapi import Alignment, AsrError, GtrModel, Nucleotide, PhyloTree
 
 TINY = b"((A:0.601,B:0.301)C:0.100,D:0.200)E:0.001;"  # integration_test.rs:14-17
 ALN4 = b">A\nACGT\n>B\nAGGT\n>C\nACGT\n>D\nTTTT\n"
