@@ -182,6 +182,24 @@ int32_t phb_get_per_pattern(phb_ctx *ctx, double *per_pattern);
 int32_t phb_score_nni(phb_ctx *ctx, int32_t n_moves, const int32_t *node_id, const uint8_t *left_ch,
                       double *totals);
 
+/* A flattened candidate tree, with the arguments of phb_set_tree. */
+typedef struct phb_tree_desc {
+    int32_t n_nodes;
+    const int32_t *postorder;
+    const int32_t *child_offsets;
+    const int32_t *children;
+    const double *branch_len;
+    const int32_t *leaf_row;
+    int32_t root;
+} phb_tree_desc;
+
+/* Replaces the caller loop of any rearrangement other than NNI -- SPR::spr (src/tree/ops.rs:34-41: prune + graft),
+ * rerooting, ... --  `let mut t = base.clone(); t.spr(e1, e2)?; t.log_likelihood(&model, &aln)?`  with one call:
+ * totals[i] = log-likelihood of trees[i] against the context's resident alignment and model (no per-candidate
+ * compress_columns, no re-upload).  The context's own tree is untouched.  A candidate that cannot be scheduled
+ * (malformed child lists, a leaf without an alignment row, an unaccepted byte in one of its rows) scores NaN. */
+int32_t phb_score_trees(phb_ctx *ctx, int32_t n_trees, const phb_tree_desc *trees, double *totals);
+
 /* ---- synthetic inputs (benchmark harness) ------------------------------------ */
 /* Simulate `n_patterns` site patterns down the current tree under the current model directly into
  * the context's device-resident alignment (rows = leaves in ascending dense id, multiplicity 1).

@@ -33,7 +33,7 @@ LAYOUT_ROW_MAJOR = 1
 # every symbol include/phylo_b200.h declares (checked by tests/test_abi.py)
 EXPORTS = [
     "phb_ctx_create", "phb_ctx_destroy", "phb_set_clv_budget", "phb_set_alignment", "phb_compress_columns", "phb_compress_rows", "phb_set_model",
-    "phb_set_tree", "phb_log_likelihood", "phb_marginal_asr", "phb_joint_asr", "phb_get_per_pattern", "phb_score_nni",
+    "phb_set_tree", "phb_log_likelihood", "phb_marginal_asr", "phb_joint_asr", "phb_get_per_pattern", "phb_score_nni", "phb_score_trees",
     "phb_simulate_alignment", "phb_get_alignment", "phb_get_stats", "phb_measure_fp64_tflops",
     "phb_timer_start", "phb_timer_stop", "phb_transition_matrices", "phb_log_likelihood_host",
     "phb_last_error", "phb_version",
@@ -69,6 +69,13 @@ class Stats(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}
 
 
+class TreeDesc(C.Structure):
+    """phb_tree_desc: a flattened candidate tree (the arguments of phb_set_tree)."""
+    _fields_ = [("n_nodes", C.c_int32), ("postorder", C.POINTER(C.c_int32)), ("child_offsets", C.POINTER(C.c_int32)),
+                ("children", C.POINTER(C.c_int32)), ("branch_len", C.POINTER(C.c_double)), ("leaf_row", C.POINTER(C.c_int32)),
+                ("root", C.c_int32)]
+
+
 class Library:
     def __init__(self, path=None):
         path = path or DEFAULT_LIB
@@ -95,6 +102,7 @@ class Library:
         L.phb_joint_asr.argtypes = [vp, u8p, dp]
         L.phb_get_per_pattern.argtypes = [vp, dp]
         L.phb_score_nni.argtypes = [vp, C.c_int32, ip, u8p, dp]
+        L.phb_score_trees.argtypes = [vp, C.c_int32, C.POINTER(TreeDesc), dp]
         L.phb_simulate_alignment.argtypes = [vp, C.c_int64, C.c_int64, C.c_uint64]
         L.phb_get_alignment.argtypes = [vp, vp, C.c_int32, C.c_int64, C.c_int64]
         L.phb_get_stats.argtypes = [vp, C.POINTER(Stats)]
@@ -312,6 +320,19 @@ class Context:
         out = np.zeros(max(len(ids), 1), np.float64)
         self._check(self.lib.L.phb_score_nni(self._h, len(ids), _ip(ids), lc.ctypes.data_as(C.POINTER(C.c_uint8)), _dp(out)))
         return out[: len(ids)]
+
+    def score_trees(self, trees):
+        """phb_score_trees: trees = list of (postorder, child_off, children, branch_len, leaf_row, root) flattened
+        candidates; returns their log-likelihoods against the resident alignment and model (NaN: unschedulable)."""
+        keep, descs = [], (TreeDesc * max(len(trees), 1))()
+        for i, (post, co, ch, bl, lr, root) in enumerate(trees):
+            a = [np.ascontiguousarray(post, np.int32), np.ascontiguousarray(co, np.int32), np.ascontiguousarray(ch, np.int32),
+                 np.ascontiguousarray(bl, np.float64), np.ascontiguousarray(lr, np.int32)]
+            keep.append(a)
+            descs[i] = TreeDesc(len(a[0]), _ip(a[0]), _ip(a[1]), _ip(a[2]), _dp(a[3]), _ip(a[4]), int(root))
+        out = np.zeros(max(len(trees), 1), np.float64)
+        self._check(self.lib.L.phb_score_trees(self._h, len(trees), descs, _dp(out)))
+        return out[: len(trees)]
 
     # -- harness -----------------------------------------------------------------------------
     def simulate_alignment(self, n_patterns, global_offset=0, seed=0):

@@ -2304,6 +2304,40 @@ int32_t phb_score_nni(phb_ctx *ctx, int32_t n_moves, const int32_t *node_id, con
     return rc;
 }
 
+// The caller loop of any other rearrangement (SPR::spr src/tree/ops.rs:34-41, rerooting, ...):
+//     let mut t = base.clone(); t.spr(e1, e2)?; t.log_likelihood(&model, &aln)?
+// as ONE call: every candidate arrives as a flattened tree, is scheduled and scored in full against the resident
+// alignment and model (no re-compression, no re-upload of the alignment), and the context's own tree is left as it
+// was.  A candidate the library cannot schedule (malformed child lists, a leaf without a row) scores NaN.
+int32_t phb_score_trees(phb_ctx *ctx, int32_t n_trees, const phb_tree_desc *trees, double *totals)
+{
+    if (!ctx || n_trees < 0 || (n_trees > 0 && (!trees || !totals))) return PHB_ERR_INVALID_ARGUMENT;
+    if (!ctx->have_aln || !ctx->have_model) return ctx->fail(PHB_ERR_STATE, "score_trees: set_alignment and set_model first");
+    const bool had_tree = ctx->tree.valid;
+    for (Device &d : ctx->devs) {
+        cudaSetDevice(d.ordinal);
+        cudaStreamSynchronize(d.stream);
+    }
+    const TreeSched base = ctx->tree;
+    int rc = PHB_OK;
+    for (int i = 0; i < n_trees && rc == PHB_OK; ++i) {
+        const phb_tree_desc &t = trees[i];
+        totals[i] = NAN;
+        int r2 = phb_set_tree(ctx, t.n_nodes, t.postorder, t.child_offsets, t.children, t.branch_len, t.leaf_row, t.root);
+        if (r2 == PHB_OK) r2 = evaluate(ctx, false, false, &totals[i]);
+        if (r2 == PHB_ERR_CUDA || r2 == PHB_ERR_OOM) rc = r2; // device trouble ends the batch; a bad candidate does not
+        else if (r2 != PHB_OK) totals[i] = NAN;
+    }
+    for (Device &d : ctx->devs) {
+        cudaSetDevice(d.ordinal);
+        cudaStreamSynchronize(d.stream);
+    }
+    ctx->tree = base;
+    ctx->tree.valid = had_tree;
+    ctx->tree_uploaded = false;
+    return rc;
+}
+
 int32_t phb_simulate_alignment(phb_ctx *ctx, int64_t n_patterns, int64_t global_offset, uint64_t seed)
 {
     if (!ctx || n_patterns < 0) return PHB_ERR_INVALID_ARGUMENT;
