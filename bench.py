@@ -186,6 +186,17 @@ def run_gpu(args, rank, world, local_rank):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
     torch.cuda.set_device(local_rank)
+    # each rank's thread -- and with it the first-touch placement of its pinned host buffer -- goes to the CPUs that
+    # are local to its GPU (tools/pcie_probe.py); PHB_BENCH_BIND=0 switches it off
+    binding = {"bound": False}
+    if os.environ.get("PHB_BENCH_BIND", "1") == "1":
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import pcie_probe
+
+            binding = pcie_probe.bind_to_gpu(local_rank, local_rank, world)
+        except Exception as e:  # binding is an optimisation, never a reason to fail
+            binding = {"bound": False, "why": f"{type(e).__name__}: {e}"}
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         # NCCL prints its version banner on fd 1 at communicator creation: point fd 1 at stderr for the run
@@ -271,6 +282,29 @@ def run_gpu(args, rank, world, local_rank):
         lnl_e2e = e2e_step()
     barrier()
     e2e_ms = (time.perf_counter() - t1) * 1e3 / e2e_steps
+    # what the end-to-end step is made of, measured apart (all ranks at once): the H2D copy of this rank's bytes alone,
+    # and the host-side preparation alone (model + tree upload, schedule, plans: one call on a 64-pattern alignment)
+    dev_buf = torch.empty(min(cnt * n_rows, 1 << 31), dtype=torch.uint8, device="cuda")
+    flat = host.view(-1)
+    barrier()
+    ev_a, ev_b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev_a.record()
+    for off in range(0, flat.numel(), dev_buf.numel()):
+        seg = flat[off:off + dev_buf.numel()]
+        dev_buf[:seg.numel()].copy_(seg, non_blocking=True)
+    ev_b.record()
+    torch.cuda.synchronize()
+    copy_only_ms = ev_a.elapsed_time(ev_b)
+    del dev_buf
+    small = np.ascontiguousarray(host.numpy()[:64])
+    with capi.Context(devices=[local_rank]) as c2:
+        synthetic.load_into(c2, tree, model)
+        c2.log_likelihood_host(small)
+        t2 = time.perf_counter()
+        for _ in range(3):
+            synthetic.load_into(c2, tree, model)
+            c2.log_likelihood_host(small)
+        host_prep_ms = (time.perf_counter() - t2) * 1e3 / 3
     # the same call from PAGEABLE host memory (a caller's plain Vec<u8>): one step, reported beside the pinned figure
     e2e_pageable_ms = None
     if world == 1 and os.environ.get("PHB_BENCH_PAGEABLE", "1") == "1":
@@ -286,12 +320,12 @@ def run_gpu(args, rank, world, local_rank):
         assert abs(lnl_pg - lnl_e2e) <= 1e-12 * abs(lnl_e2e)
         del pageable
     # ---- reduce over ranks ------------------------------------------------------------------------
-    tmax = torch.tensor([dev_ms, wall_ms, e2e_ms], dtype=torch.float64, device="cuda")
+    tmax = torch.tensor([dev_ms, wall_ms, e2e_ms, copy_only_ms, host_prep_ms], dtype=torch.float64, device="cuda")
     tsum = torch.tensor([float(launches)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-    dev_ms, wall_ms, e2e_ms = (float(x) for x in tmax.tolist())
+    dev_ms, wall_ms, e2e_ms, copy_only_ms, host_prep_ms = (float(x) for x in tmax.tolist())
     launches = int(tsum.item())
     if rank == 0:
         peak, peak_src = peaks()
@@ -354,6 +388,10 @@ def run_gpu(args, rank, world, local_rank):
                     "h2d_bytes_per_step": int(cnt) * n_rows + 8 * 60 + 8 * 4 * tree["n_nodes"] + 4 * 4 * tree["n_nodes"],
                     "d2h_bytes_per_step": 8 + 4 * n_rows, "steps": e2e_steps,
                     "pageable_ms_per_step": e2e_pageable_ms,
+                    "breakdown_ms": {"h2d_copy_alone": copy_only_ms, "device_compute_alone": ms_step, "host_prep_alone": host_prep_ms,
+                                     "note": "max over ranks, each measured apart with all ranks active: the copy and the compute "
+                                             "overlap inside the step, the host preparation runs while the first chunks are on the wire"},
+                    "cpu_binding_rank0": binding,
                     "note": "per rank: phb_log_likelihood_host on pinned host [pattern][row] bytes: chunked H2D overlapped with pack + sweep, "
                             "tree/model upload, scalar back; pageable_ms_per_step: the same call on plain malloc'ed memory (N=1 only); "
                             "compress_columns is not in this figure (configs.compress times it)"},
