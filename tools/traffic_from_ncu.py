@@ -31,7 +31,8 @@ def main():
     def val(name):
         v = float(data[col[name]].replace(",", ""))
         u = units[col[name]].lower()
-        return v * {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9, "tbyte": 1e12}.get(u, 1)
+        return v * {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9, "tbyte": 1e12,
+                    "ns": 1e-6, "nsecond": 1e-6, "us": 1e-3, "usecond": 1e-3, "ms": 1, "msecond": 1, "s": 1e3, "second": 1e3}.get(u, 1)
 
     rd, wr = val("dram__bytes_read.sum"), val("dram__bytes_write.sum")
     src = os.path.join(ROOT, "phylo-rs_b200", "csrc", args.source)
@@ -42,7 +43,7 @@ def main():
         tj = {}
     tj[args.kernel] = {
         "dram_bytes_per_launch": rd + wr, "dram_read": rd, "dram_write": wr, "patterns": args.patterns, "taxa": args.taxa,
-        "duration_ms_under_ncu": val("gpu__time_duration.sum") / 1e6 if "gpu__time_duration.sum" in col else None,
+        "duration_ms_under_ncu": val("gpu__time_duration.sum") if "gpu__time_duration.sum" in col else None,
         "capture": os.path.basename(args.report), "source_file": args.source,
         "source_sha256": hashlib.sha256(open(src, "rb").read()).hexdigest(),
     }
