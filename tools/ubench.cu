@@ -46,6 +46,40 @@ __global__ void lds_kernel(double *out, int iters)
     out[blockIdx.x * blockDim.x + threadIdx.x] = acc.x + acc.y;
 }
 
+// gather patterns of the tip-table lookups: every lane picks one of NROWS rows (pseudo-random, fixed per lane and k);
+// W = 8: rows of 8 bytes read with LDS.64, W = 16: rows of 16 bytes read with LDS.128.  Reports SM clocks per warp
+// instruction, i.e. the cost of delivering W bytes to each lane.
+template <int W, int NROWS>
+__global__ void gather_kernel(double *out, int iters)
+{
+    __shared__ double2 buf[1024];
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) buf[i] = make_double2(i, 1.0);
+    __syncthreads();
+    unsigned off[16];
+    unsigned h = threadIdx.x * 2654435761u + 12345u;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        h = h * 1664525u + 1013904223u;
+        off[k] = ((h >> 16) % NROWS) * W + k * 16 * ((NROWS * W + 15) / 16);
+    }
+    double acc = 0, acc2 = 0;
+    const char *base = reinterpret_cast<const char *>(buf);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            const unsigned o = (off[k] + (it & 1) * 4096u) & 16383u;
+            if (W == 8) {
+                acc += *reinterpret_cast<const double *>(base + o);
+            } else {
+                double2 v = *reinterpret_cast<const double2 *>(base + o);
+                acc += v.x;
+                acc2 += v.y;
+            }
+        }
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = acc + acc2;
+}
+
 // the op-loop mix: per iteration 8 broadcast LDS.128 (a 4x4 matrix), 4 sites x (16 FMA + 4 MUL)
 template <int R>
 __global__ void mix_kernel(double *out, int iters)
@@ -129,6 +163,15 @@ int main()
         float mg = time_ms([&] { lds_kernel<1><<<n_sm, 32 * w>>>(out, iters / 4); });
         auto clk = [&](float ms) { return ms * 1e-3 * khz * 1e3 / ((double)(iters / 4) * 16 * w); }; // SM clocks per warp LDS.128
         printf("{\"bench\": \"lds128\", \"warps_per_sm\": %d, \"clk_per_warp_lds_broadcast\": %.2f, \"clk_per_warp_lds_gather4rows\": %.2f}\n", w, clk(mb), clk(mg));
+    }
+    for (int w : {4, 12, 16}) {
+        auto clk = [&](float ms) { return ms * 1e-3 * khz * 1e3 / ((double)(iters / 4) * 16 * w); };
+        float a = time_ms([&] { gather_kernel<8, 5><<<n_sm, 32 * w>>>(out, iters / 4); });
+        float b = time_ms([&] { gather_kernel<16, 5><<<n_sm, 32 * w>>>(out, iters / 4); });
+        float c = time_ms([&] { gather_kernel<8, 25><<<n_sm, 32 * w>>>(out, iters / 4); });
+        float d = time_ms([&] { gather_kernel<16, 25><<<n_sm, 32 * w>>>(out, iters / 4); });
+        printf("{\"bench\": \"gather\", \"warps_per_sm\": %d, \"clk_lds64_5rows\": %.2f, \"clk_lds128_5rows\": %.2f, \"clk_lds64_25rows\": %.2f, "
+               "\"clk_lds128_25rows\": %.2f}\n", w, clk(a), clk(b), clk(c), clk(d));
     }
     for (int w : {4, 8, 10, 12, 16}) {
         float m4 = time_ms([&] { mix_kernel<4><<<n_sm, 32 * w>>>(out, iters); });
