@@ -89,6 +89,9 @@ pub struct phb_stats {
     pub ms_nni_edge: f64,
 }
 
+/// Size of the fixed device staging array behind `phb_transition_matrices_noalloc`.
+pub const PHB_NOALLOC_SCRATCH_BYTES: usize = 2 << 20;
+
 extern "C" {
     pub fn phb_version() -> *const c_char;
     pub fn phb_last_error(ctx: *mut phb_ctx) -> *const c_char;
@@ -170,6 +173,8 @@ extern "C" {
     pub fn phb_timer_start(ctx: *mut phb_ctx) -> i32;
     pub fn phb_timer_stop(ctx: *mut phb_ctx, ms: *mut f64) -> i32;
     pub fn phb_transition_matrices(ctx: *mut phb_ctx, n_t: i32, t: *const f64, out: *mut f64) -> i32;
+    /// Allocation-free variant (fixed device staging array of `PHB_NOALLOC_SCRATCH_BYTES`; no reference counterpart).
+    pub fn phb_transition_matrices_noalloc(ctx: *mut phb_ctx, n_t: i32, t: *const f64, out: *mut f64) -> i32;
     pub fn phb_measure_fp64_tflops(ctx: *mut phb_ctx, tflops: *mut f64) -> i32;
 }
 

@@ -164,6 +164,20 @@ int32_t phb_marginal_asr(phb_ctx *ctx, uint8_t *states, double *posteriors, doub
  * The exact identity when rates[c] * t[k] == 0.0.  Requires set_model. */
 int32_t phb_transition_matrices(phb_ctx *ctx, int32_t n_t, const double *t, double *out);
 
+/* Allocation-free variant of phb_transition_matrices.  It has no counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments, same result (bit for bit: the same kernel), but the
+ * device staging memory is a fixed file-scope device array of PHB_NOALLOC_SCRATCH_BYTES that every GPU loading the
+ * library holds until exit, and the call performs no cudaMalloc / cudaFree / allocating library call.
+ *   limit    8 * n_t * (1 + 16 * n_cat) <= PHB_NOALLOC_SCRATCH_BYTES (n_cat = categories incl. the invariant one:
+ *            4,032 branch lengths for GTR+G4, 3,236 for GTR+I+G4); beyond it PHB_ERR_INVALID_ARGUMENT with a message
+ *            naming the limit, nothing launched
+ *   sharing  every call on a device uses the same array, which keeps the previous call's contents; nothing in it has
+ *            to start at zero (each call overwrites all it reads back).  Calls that overlap on one GPU -- two contexts,
+ *            two threads -- race on it: serialise them.  The call returns after its stream has drained. */
+#define PHB_NOALLOC_SCRATCH_BYTES (2u << 20)
+int32_t phb_transition_matrices_noalloc(phb_ctx *ctx, int32_t n_t, const double *t, double *out);
+
 /* Replaces compute_joint_asr (src/tree/likelihood.rs:421-560; trait JointAsr::joint_asr src/tree/asr.rs:30-37,
  * impl src/tree.rs:58-66): Viterbi reconstruction per rate category in log space, the category with the
  * greatest ln(weight) + root maximum wins (first on ties), states by traceback.  states: [n_nodes][n_patterns]

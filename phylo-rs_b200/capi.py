@@ -35,7 +35,7 @@ EXPORTS = [
     "phb_ctx_create", "phb_ctx_destroy", "phb_set_clv_budget", "phb_set_alignment", "phb_compress_columns", "phb_compress_rows", "phb_set_model",
     "phb_set_tree", "phb_log_likelihood", "phb_marginal_asr", "phb_joint_asr", "phb_get_per_pattern", "phb_score_nni", "phb_score_trees",
     "phb_simulate_alignment", "phb_get_alignment", "phb_get_stats", "phb_measure_fp64_tflops",
-    "phb_timer_start", "phb_timer_stop", "phb_transition_matrices", "phb_log_likelihood_host",
+    "phb_timer_start", "phb_timer_stop", "phb_transition_matrices", "phb_transition_matrices_noalloc", "phb_log_likelihood_host",
     "phb_last_error", "phb_version",
 ]
 
@@ -307,6 +307,14 @@ class Context:
         t = np.ascontiguousarray(np.atleast_1d(t), np.float64)
         out = np.zeros((len(t), n_cat, 4, 4), np.float64)
         self._check(self.lib.L.phb_transition_matrices(self._h, len(t), _dp(t), _dp(out)))
+        return out
+
+    def transition_matrices_noalloc(self, t, n_cat):
+        """As transition_matrices, through the allocation-free entry point (fixed device staging array; fails with
+        InvalidArgument beyond PHB_NOALLOC_SCRATCH_BYTES)."""
+        t = np.ascontiguousarray(np.atleast_1d(t), np.float64)
+        out = np.zeros((len(t), n_cat, 4, 4), np.float64)
+        self._check(self.lib.L.phb_transition_matrices_noalloc(self._h, len(t), _dp(t), _dp(out)))
         return out
 
     def per_pattern(self):

@@ -20,6 +20,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <chrono>
 #include <vector>
@@ -2496,6 +2497,63 @@ int32_t phb_transition_matrices(phb_ctx *ctx, int32_t n_t, const double *t, doub
     const size_t n_out = (size_t)n_t * M.n_cat * 16;
     CU(d.scratch.ensure(sizeof(double) * ((size_t)n_t + n_out)));
     double *d_t = d.scratch.as<double>(), *d_P = d_t + n_t;
+    CU(cudaMemcpyAsync(d_t, t, sizeof(double) * n_t, cudaMemcpyHostToDevice, d.stream));
+    int nthreads = n_t * M.n_cat;
+    PHB_LAUNCH(transition_kernel, dim3((nthreads + 127) / 128), dim3(128), d.stream, d_t, n_t, M, d_P);
+    CHECK_LAUNCH();
+    CU(cudaMemcpyAsync(out, d_P, sizeof(double) * n_out, cudaMemcpyDeviceToHost, d.stream));
+    CU(cudaStreamSynchronize(d.stream));
+    return PHB_OK;
+}
+
+// ---- allocation-free variant of phb_transition_matrices ---------------------------------------------------------
+// The staging memory of transition_kernel (branch lengths in, matrices out) lives in a file-scope device array instead
+// of the context's grow-on-demand scratch buffer, so the call performs no cudaMalloc / cudaFree.  Every GPU that loads
+// the library holds the array until exit.  In host code the array's NAME is a host-side stand-in, not a device
+// address: the kernel gets the pointer cudaGetSymbolAddress returns, resolved once per device with that device current.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[PHB_NOALLOC_SCRATCH_BYTES];
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static void *g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {nullptr};
+static std::mutex g_noalloc_mu;
+
+// `ordinal` must be the current device
+static cudaError_t noalloc_scratch_ptr(int ordinal, void **out)
+{
+    if (ordinal < 0 || ordinal >= NOALLOC_MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[ordinal]) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        g_noalloc_ptr[ordinal] = p;
+    }
+    *out = g_noalloc_ptr[ordinal];
+    return cudaSuccess;
+}
+
+int32_t phb_transition_matrices_noalloc(phb_ctx *ctx, int32_t n_t, const double *t, double *out)
+{
+    if (!ctx || n_t < 0 || (n_t > 0 && (!t || !out)))
+        return ctx ? ctx->fail(PHB_ERR_INVALID_ARGUMENT, "transition_matrices_noalloc: null/negative argument") : PHB_ERR_INVALID_ARGUMENT;
+    if (!ctx->have_model) return ctx->fail(PHB_ERR_STATE, "set_model must precede transition_matrices_noalloc");
+    if (n_t == 0) return PHB_OK;
+    Device &d = ctx->devs[0];
+    const ModelDev &M = ctx->model_lit;
+    const size_t n_out = (size_t)n_t * M.n_cat * 16;
+    const size_t need = sizeof(double) * ((size_t)n_t + n_out);
+    if (need > (size_t)PHB_NOALLOC_SCRATCH_BYTES)
+        return ctx->fail(PHB_ERR_INVALID_ARGUMENT,
+                         "transition_matrices_noalloc: %d branch lengths x %d categories need %zu bytes of staging, the fixed device "
+                         "array holds %zu (at most %zu branch lengths for this model); use phb_transition_matrices",
+                         (int)n_t, M.n_cat, need, (size_t)PHB_NOALLOC_SCRATCH_BYTES,
+                         (size_t)PHB_NOALLOC_SCRATCH_BYTES / (sizeof(double) * (1 + 16 * (size_t)M.n_cat)));
+    CU(cudaSetDevice(d.ordinal));
+    void *base = nullptr;
+    CU(noalloc_scratch_ptr(d.ordinal, &base));
+    // nothing has to start at zero: the kernel reads the n_t branch lengths copied in below and writes every one of the
+    // n_out matrix entries that is copied out; whatever an earlier call left beyond them is never read
+    double *d_t = static_cast<double *>(base), *d_P = d_t + n_t;
     CU(cudaMemcpyAsync(d_t, t, sizeof(double) * n_t, cudaMemcpyHostToDevice, d.stream));
     int nthreads = n_t * M.n_cat;
     PHB_LAUNCH(transition_kernel, dim3((nthreads + 127) / 128), dim3(128), d.stream, d_t, n_t, M, d_P);

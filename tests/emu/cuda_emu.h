@@ -75,7 +75,7 @@ using std::min;
 
 // ---- runtime API subset -------------------------------------------------------------------------
 typedef int cudaError_t;
-enum { cudaSuccess = 0, cudaErrorMemoryAllocation = 2, cudaErrorInvalidValue = 1 };
+enum { cudaSuccess = 0, cudaErrorMemoryAllocation = 2, cudaErrorInvalidValue = 1, cudaErrorInvalidSymbol = 13, cudaErrorInvalidDevice = 101 };
 typedef struct emu_stream *cudaStream_t;
 typedef struct emu_event *cudaEvent_t;
 enum cudaMemcpyKind { cudaMemcpyHostToDevice = 1, cudaMemcpyDeviceToHost = 2, cudaMemcpyDeviceToDevice = 3 };
@@ -83,6 +83,13 @@ enum { cudaStreamNonBlocking = 1, cudaHostAllocDefault = 0, cudaDevAttrComputeCa
        cudaDevAttrMultiProcessorCount = 16, cudaDevAttrMaxSharedMemoryPerBlockOptin = 97 };
 
 cudaError_t cudaMalloc(void **p, size_t bytes);
+// emulated device memory is host memory: a __device__ array's address is the array itself
+template <typename T>
+inline cudaError_t cudaGetSymbolAddress(void **p, const T &symbol)
+{
+    *p = const_cast<void *>(static_cast<const void *>(&symbol));
+    return cudaSuccess;
+}
 cudaError_t cudaFree(void *p);
 cudaError_t cudaHostAlloc(void **p, size_t bytes, unsigned flags);
 cudaError_t cudaFreeHost(void *p);
