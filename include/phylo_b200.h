@@ -61,6 +61,19 @@ extern "C" {
  * ignores the flag. */
 #define PHB_FLAG_NNI_WALK (1ull << 4)
 
+/* The context evaluates the 20-state AminoAcid alphabet (src/alphabet.rs:66-116; the reference's engines are generic
+ * over A: Alphabet, likelihood.rs:156-166, 224-235, with GtrModel<A>::new(pi, W, normalize), gtr.rs:39-50) instead of
+ * Nucleotide.  In such a context
+ *   phb_set_alignment        accepts AminoAcid::profile's bytes: ACDEFGHIKLMNPQRSTVWY, B, Z, J (two states at 0.5 --
+ *                            the state INDICES the reference sets: 3|11, 4|14, 8|9), X and '-' (all ones);
+ *   phb_set_model            takes lambda[20], V[400] (V[i + 20*k]), pi / sqrt_pi / inv_sqrt_pi[20];
+ *   phb_set_tree, phb_log_likelihood, phb_get_per_pattern, phb_set_clv_budget   as documented below;
+ *   phb_marginal_asr         states are indices 0..19 into CANONICAL, posteriors [n_nodes][n_patterns][20];
+ *   phb_transition_matrices  out[(k * n_cat + c) * 400 + 20 * i + j];
+ * rate-0 categories are evaluated literally (identity P).  One device per context.  Every other entry point returns
+ * PHB_ERR_STATE. */
+#define PHB_FLAG_AMINO_ACID (1ull << 5)
+
 /* ---- alignment layouts --------------------------------------------------------------------- */
 #define PHB_LAYOUT_PATTERN_MAJOR 0 /* bytes[pattern][row] — CompressedColumns.patterns, alignment.rs:129-138 */
 #define PHB_LAYOUT_ROW_MAJOR 1     /* bytes[row][pattern] */

@@ -25,7 +25,8 @@ _LIB = None
 def build(force=False):
     """Compile the C restatement (gcc).  Called by __graft_entry__.build()."""
     src = os.path.join(_HERE, "phylo_oracle.c")
-    outs = [os.path.join(_HERE, "libphylo_oracle.so"), os.path.join(_HERE, "libphylo_oracle_v3.so")]
+    outs = [os.path.join(_HERE, "libphylo_oracle.so"), os.path.join(_HERE, "libphylo_oracle_v3.so"),
+            os.path.join(_HERE, "libphylo_oracle_aa.so")]
     stale = force or any((not os.path.exists(o)) or os.path.getmtime(o) < os.path.getmtime(src) for o in outs)
     if stale:
         subprocess.run(["make", "-C", _HERE, "-B", "all"], check=True, capture_output=True)
@@ -43,9 +44,47 @@ def _has_avx2():
     return False
 
 
-class _RateMatrix(C.Structure):
-    _fields_ = [("pi", C.c_double * 4), ("lam", C.c_double * 4), ("V", C.c_double * 16),
-                ("sqrt_pi", C.c_double * 4), ("inv_sqrt_pi", C.c_double * 4)]
+def _rate_matrix_struct(ns):
+    class RM(C.Structure):
+        _fields_ = [("pi", C.c_double * ns), ("lam", C.c_double * ns), ("V", C.c_double * (ns * ns)),
+                    ("sqrt_pi", C.c_double * ns), ("inv_sqrt_pi", C.c_double * ns)]
+    return RM
+
+
+_RateMatrix = _rate_matrix_struct(4)
+_RateMatrixAA = _rate_matrix_struct(20)  # libphylo_oracle_aa.so (-DNS=20)
+_LIB_AA = None
+
+
+def _bind(L, RM, profile_fn):
+    dp, ip = C.POINTER(C.c_double), C.POINTER(C.c_int)
+    L.orc_discrete_gamma.argtypes = [C.c_double, C.c_int, dp]
+    L.orc_discrete_gamma.restype = C.c_int
+    L.orc_rate_matrix_new.argtypes = [dp, dp, C.c_int, C.POINTER(RM)]
+    L.orc_rate_matrix_new.restype = C.c_int
+    L.orc_transition.argtypes = [C.POINTER(RM), C.c_double, dp]
+    L.orc_transition.restype = None
+    getattr(L, profile_fn).argtypes = [C.c_uint8, dp]
+    getattr(L, profile_fn).restype = C.c_int
+    for nm in ("orc_test_ln_gamma", "orc_test_inverse_normal_cdf"):
+        getattr(L, nm).argtypes = [C.c_double]
+        getattr(L, nm).restype = C.c_double
+    L.orc_test_incomplete_gamma.argtypes = [C.c_double, C.c_double]
+    L.orc_test_incomplete_gamma.restype = C.c_double
+    tree_args = [C.c_int, ip, ip, ip, ip, ip, dp, ip, C.c_int]
+    model_args = [C.POINTER(RM), C.c_int, dp, dp]
+    aln_args = [C.c_int, C.c_int64, C.POINTER(C.c_uint8), C.POINTER(C.c_uint64)]
+    L.orc_log_likelihood.argtypes = tree_args + model_args + aln_args + [C.c_int, C.c_int, dp, dp]
+    L.orc_log_likelihood.restype = C.c_int
+    L.orc_marginal_asr.argtypes = tree_args + model_args + aln_args + [C.c_int, C.POINTER(C.c_uint8), dp, dp, dp]
+    L.orc_marginal_asr.restype = C.c_int
+    L.orc_joint_asr.argtypes = tree_args + model_args + aln_args + [C.c_int, C.POINTER(C.c_uint8), dp, dp]
+    L.orc_joint_asr.restype = C.c_int
+    L.orc_bruteforce_site_likelihood.argtypes = [C.c_int, ip, ip, ip, dp, ip, C.c_int,
+                                                 C.POINTER(RM), C.c_double, C.POINTER(C.c_uint8)]
+    L.orc_bruteforce_site_likelihood.restype = C.c_double
+    L.orc_n_states.argtypes = []
+    L.orc_n_states.restype = C.c_int
 
 
 def lib():
@@ -58,34 +97,23 @@ def lib():
         build()
     path = v3 if (_has_avx2() and os.path.exists(v3)) else base
     L = C.CDLL(path)
-    dp, ip = C.POINTER(C.c_double), C.POINTER(C.c_int)
-    L.orc_discrete_gamma.argtypes = [C.c_double, C.c_int, dp]
-    L.orc_discrete_gamma.restype = C.c_int
-    L.orc_rate_matrix_new.argtypes = [dp, dp, C.c_int, C.POINTER(_RateMatrix)]
-    L.orc_rate_matrix_new.restype = C.c_int
-    L.orc_transition.argtypes = [C.POINTER(_RateMatrix), C.c_double, dp]
-    L.orc_transition.restype = None
-    L.orc_nucleotide_profile.argtypes = [C.c_uint8, dp]
-    L.orc_nucleotide_profile.restype = C.c_int
-    for nm in ("orc_test_ln_gamma", "orc_test_inverse_normal_cdf"):
-        getattr(L, nm).argtypes = [C.c_double]
-        getattr(L, nm).restype = C.c_double
-    L.orc_test_incomplete_gamma.argtypes = [C.c_double, C.c_double]
-    L.orc_test_incomplete_gamma.restype = C.c_double
-    tree_args = [C.c_int, ip, ip, ip, ip, ip, dp, ip, C.c_int]
-    model_args = [C.POINTER(_RateMatrix), C.c_int, dp, dp]
-    aln_args = [C.c_int, C.c_int64, C.POINTER(C.c_uint8), C.POINTER(C.c_uint64)]
-    L.orc_log_likelihood.argtypes = tree_args + model_args + aln_args + [C.c_int, C.c_int, dp, dp]
-    L.orc_log_likelihood.restype = C.c_int
-    L.orc_marginal_asr.argtypes = tree_args + model_args + aln_args + [C.c_int, C.POINTER(C.c_uint8), dp, dp, dp]
-    L.orc_marginal_asr.restype = C.c_int
-    L.orc_joint_asr.argtypes = tree_args + model_args + aln_args + [C.c_int, C.POINTER(C.c_uint8), dp, dp]
-    L.orc_joint_asr.restype = C.c_int
-    L.orc_bruteforce_site_likelihood.argtypes = [C.c_int, ip, ip, ip, dp, ip, C.c_int,
-                                                 C.POINTER(_RateMatrix), C.c_double, C.POINTER(C.c_uint8)]
-    L.orc_bruteforce_site_likelihood.restype = C.c_double
+    _bind(L, _RateMatrix, "orc_nucleotide_profile")
     _LIB = L
     return L
+
+
+def lib_aa():
+    """The 20-state (AminoAcid, src/alphabet.rs:66-116) build of the same C restatement."""
+    global _LIB_AA
+    if _LIB_AA is None:
+        path = os.path.join(_HERE, "libphylo_oracle_aa.so")
+        if not os.path.exists(path):
+            build(force=True)
+        L = C.CDLL(path)
+        _bind(L, _RateMatrixAA, "orc_amino_acid_profile")
+        assert L.orc_n_states() == 20
+        _LIB_AA = L
+    return _LIB_AA
 
 
 ERRORS = {1: "MissingBranchLength", 2: "AlphabetMismatch", 3: "InvalidAlignment",
@@ -133,18 +161,22 @@ def _validate_positive(v, name):
 class RefModel:
     """GtrModel<Nucleotide>, src/models/gtr.rs:30-34 (+ RateMatrix, src/models/rate_matrix.rs)."""
 
+    NS = 4
+    _RM = _RateMatrix
+    _lib = staticmethod(lambda: lib())
+
     def __init__(self, pi, w, normalize=True, _rm=None, _cats=None):
         if _rm is not None:
             self.rm, self.categories = _rm, list(_cats)
             return
         pi = np.ascontiguousarray(pi, np.float64)
         w = np.ascontiguousarray(w, np.float64)
-        if pi.shape != (4,):
+        if pi.shape != (self.NS,):
             raise OracleError(2, "pi length does not match alphabet states")
-        if w.shape != (4, 4):
+        if w.shape != (self.NS, self.NS):
             raise OracleError(2, "W matrix dimensions do not match alphabet states")
-        self.rm = _RateMatrix()
-        rc = lib().orc_rate_matrix_new(_dp(pi), _dp(w), int(bool(normalize)), C.byref(self.rm))
+        self.rm = self._RM()
+        rc = self._lib().orc_rate_matrix_new(_dp(pi), _dp(w), int(bool(normalize)), C.byref(self.rm))
         if rc:
             raise OracleError(rc, "RateMatrix::new")
         self.categories = [(1.0, 1.0)]  # (rate, weight), src/models/gtr.rs:43-46
@@ -161,7 +193,7 @@ class RefModel:
     @property
     def eigenvectors(self):
         """4x4, [i, k] = component i of eigenvector k."""
-        return np.array(self.rm.V[:]).reshape(4, 4).T.copy()
+        return np.array(self.rm.V[:]).reshape(self.NS, self.NS).T.copy()
 
     @property
     def sqrt_pi(self):
@@ -184,9 +216,9 @@ class RefModel:
 
     def transition(self, t):
         """RateMatrix::transition, src/models/rate_matrix.rs:113-135 -> 4x4 row-major."""
-        P = np.zeros(16)
-        lib().orc_transition(C.byref(self.rm), float(t), _dp(P))
-        return P.reshape(4, 4)
+        P = np.zeros(self.NS * self.NS)
+        self._lib().orc_transition(C.byref(self.rm), float(t), _dp(P))
+        return P.reshape(self.NS, self.NS)
 
     def category_transition(self, cat, t):
         """src/models/gtr.rs:61-64."""
@@ -264,7 +296,7 @@ class RefModel:
             cats.append((0.0, p_inv))
         for r in rates:
             cats.append((float(r), vw / float(k)))
-        return RefModel(None, None, _rm=self.rm, _cats=cats)
+        return type(self)(None, None, _rm=self.rm, _cats=cats)
 
     def with_invariant(self, p_inv):
         """src/models/gtr.rs:117-165."""
@@ -281,7 +313,22 @@ class RefModel:
             cats.append((r, w * scale))
         if all(r == 0.0 for r, _ in cats):
             cats.append((1.0, new_vw))
-        return RefModel(None, None, _rm=self.rm, _cats=cats)
+        return type(self)(None, None, _rm=self.rm, _cats=cats)
+
+
+class AaModel(RefModel):
+    """GtrModel<AminoAcid> (src/models/gtr.rs:30-58 with A::N_STATES = 20): GtrModel::new(pi, W, normalize) and the
+    rate-heterogeneity builders; the named constructors of gtr.rs:180-278 are Nucleotide-only in the reference too."""
+    NS = 20
+    _RM = _RateMatrixAA
+    _lib = staticmethod(lambda: lib_aa())
+    CANONICAL = b"ACDEFGHIKLMNPQRSTVWY"  # src/alphabet.rs:73
+
+
+def amino_acid_profile(c):
+    """AminoAcid::profile, src/alphabet.rs:76-116 -> 20 values or None."""
+    p = np.zeros(20)
+    return p if lib_aa().orc_amino_acid_profile(int(c), _dp(p)) else None
 
 
 def _tree_args(ft):
@@ -298,7 +345,7 @@ def log_likelihood_flat(ft, model, patterns, mult=None, mode=0, n_threads=1):
     per = np.zeros(max(P, 1), np.float64)
     tot = C.c_double(0.0)
     m = None if mult is None else np.ascontiguousarray(mult, np.uint64)
-    rc = lib().orc_log_likelihood(
+    rc = model._lib().orc_log_likelihood(
         *_tree_args(ft), C.byref(model.rm), len(rates), _dp(rates), _dp(weights), rows, P,
         patterns.ctypes.data_as(C.POINTER(C.c_uint8)),
         None if m is None else m.ctypes.data_as(C.POINTER(C.c_uint64)),
@@ -317,10 +364,10 @@ def marginal_asr_flat(ft, model, patterns, mult=None, want_posteriors=False, n_t
     rates, weights = np.ascontiguousarray(model.rates), np.ascontiguousarray(model.weights)
     per = np.zeros(max(P, 1), np.float64)
     states = np.zeros((n, max(P, 1)), np.uint8)
-    post = np.zeros((n, max(P, 1), 4), np.float64) if want_posteriors else None
+    post = np.zeros((n, max(P, 1), model.NS), np.float64) if want_posteriors else None
     tot = C.c_double(0.0)
     m = None if mult is None else np.ascontiguousarray(mult, np.uint64)
-    rc = lib().orc_marginal_asr(
+    rc = model._lib().orc_marginal_asr(
         *_tree_args(ft), C.byref(model.rm), len(rates), _dp(rates), _dp(weights), rows, P,
         patterns.ctypes.data_as(C.POINTER(C.c_uint8)),
         None if m is None else m.ctypes.data_as(C.POINTER(C.c_uint64)),
@@ -342,7 +389,7 @@ def joint_asr_flat(ft, model, patterns, mult=None, n_threads=1):
     states = np.zeros((n, max(P, 1)), np.uint8)
     tot = C.c_double(0.0)
     m = None if mult is None else np.ascontiguousarray(mult, np.uint64)
-    rc = lib().orc_joint_asr(
+    rc = model._lib().orc_joint_asr(
         *_tree_args(ft), C.byref(model.rm), len(rates), _dp(rates), _dp(weights), rows, P,
         patterns.ctypes.data_as(C.POINTER(C.c_uint8)),
         None if m is None else m.ctypes.data_as(C.POINTER(C.c_uint64)),
@@ -412,7 +459,7 @@ def marginal_asr(tree, model, aln, want_posteriors=False):
 
 def bruteforce_site_likelihood(ft, model, pattern, rate=1.0):
     pattern = np.ascontiguousarray(pattern, np.uint8)
-    return lib().orc_bruteforce_site_likelihood(
+    return model._lib().orc_bruteforce_site_likelihood(
         int(ft["n_nodes"]), _ip(ft["child_off"]), _ip(ft["children"]), _ip(ft["parent"]), _dp(ft["blen"]),
         _ip(ft["leaf_row"]), int(ft["root"]), C.byref(model.rm), float(rate),
         pattern.ctypes.data_as(C.POINTER(C.c_uint8)))

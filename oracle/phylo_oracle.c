@@ -29,7 +29,12 @@
 #include <string.h>
 #include <pthread.h>
 
-#define NS 4 /* Nucleotide::N_STATES, src/alphabet.rs:26 */
+/* Number of states: 4 = Nucleotide (src/alphabet.rs:26), the default build; 20 = AminoAcid (src/alphabet.rs:72),
+ * built as libphylo_oracle_aa.so with -DNS=20.  Everything below the alphabet section is written over NS, as the
+ * reference is generic over A: Alphabet (likelihood.rs:156-166, gtr.rs:36-40). */
+#ifndef NS
+#define NS 4
+#endif
 
 /* status codes mirror AsrError, src/error.rs:106-125 */
 enum {
@@ -333,7 +338,7 @@ void orc_transition(const orc_rate_matrix *m, double t, double *P)
 /* ------------------------------------------------------------------------------------------
  * alphabet.rs: Nucleotide::profile (src/alphabet.rs:44-64)
  * ---------------------------------------------------------------------------------------- */
-static int nucleotide_profile(uint8_t c, double *p)
+static int __attribute__((unused)) nucleotide_profile(uint8_t c, double *p)
 {
     const double t = 1.0 / 3.0;
     switch (c) {
@@ -357,7 +362,42 @@ static int nucleotide_profile(uint8_t c, double *p)
     default: return 0;
     }
 }
+
+/* AminoAcid::profile, src/alphabet.rs:76-116: CANONICAL = "ACDEFGHIKLMNPQRSTVWY" (index_of = position), B = D|N,
+ * Z = E|Q, J = I|L at 0.5 each, X and the gap all ones. */
+static int __attribute__((unused)) amino_acid_profile(uint8_t c, double *p)
+{
+    static const char canonical[] = "ACDEFGHIKLMNPQRSTVWY";
+    for (int i = 0; i < 20; ++i)
+        p[i] = 0.0;
+    for (int i = 0; i < 20; ++i)
+        if ((uint8_t)canonical[i] == c) {
+            p[i] = 1.0;
+            return 1;
+        }
+    switch (c) {
+    case 'B': p[3] = 0.5; p[11] = 0.5; return 1;  /* written as in the reference: indices 3 and 11 */
+    case 'Z': p[4] = 0.5; p[14] = 0.5; return 1;  /* 4 and 14 */
+    case 'J': p[8] = 0.5; p[9] = 0.5; return 1;   /* 8 and 9 */
+    case 'X':
+    case '-':
+        for (int i = 0; i < 20; ++i)
+            p[i] = 1.0;
+        return 1;
+    default: return 0;
+    }
+}
+
+#if NS == 4
+#define alphabet_profile nucleotide_profile
 int orc_nucleotide_profile(uint8_t c, double *p) { return nucleotide_profile(c, p); }
+#elif NS == 20
+#define alphabet_profile amino_acid_profile
+int orc_amino_acid_profile(uint8_t c, double *p) { return amino_acid_profile(c, p); }
+#else
+#error "NS must be 4 or 20"
+#endif
+int orc_n_states(void) { return NS; }
 
 /* Profile::scale, src/tree/likelihood/profile.rs:20-39 */
 static void profile_scale(double *v, double *log_scale)
@@ -449,19 +489,21 @@ static int prune_pattern_category(const orc_job *J, int cat, const uint8_t *patt
                 pos = T->leaf_row[v];
             if (pos < 0)
                 return ORC_ERR_INVALID_ALIGNMENT; /* :100 */
-            if (!nucleotide_profile(pattern[pos], pv))
+            if (!alphabet_profile(pattern[pos], pv))
                 return ORC_ERR_ALPHABET_MISMATCH; /* :106 */
             ls[v] = 0.0;
             profile_scale(pv, &ls[v]); /* :108 */
         } else {
-            double vals[NS] = {1.0, 1.0, 1.0, 1.0};
+            double vals[NS];
+            for (int i = 0; i < NS; ++i)
+                vals[i] = 1.0;
             double sum_ls = 0.0;
             for (int ci = T->child_off[v]; ci < T->child_off[v + 1]; ++ci) {
                 int c = T->children[ci];
                 const double *pc = prof + (size_t)c * NS;
                 orc_transition(J->rm, J->rates[cat] * T->blen[c], P); /* gtr.rs:61-64 */
                 double contrib[NS];
-                for (int i = 0; i < NS; ++i) /* gemv, column order j = 0..3 */
+                for (int i = 0; i < NS; ++i) /* gemv, column order j = 0..NS-1 */
                     contrib[i] = P[i * NS + 0] * pc[0];
                 for (int j = 1; j < NS; ++j)
                     for (int i = 0; i < NS; ++i)
@@ -574,7 +616,7 @@ static void *asr_ref_worker(void *arg)
             for (int c = 0; c < K; ++c)
                 mixw[c] = 1.0 / (double)K;
         for (int v = 0; v < n; ++v) { /* :365-398 */
-            double mixed[NS] = {0.0, 0.0, 0.0, 0.0};
+            double mixed[NS] = {0.0};
             for (int c = 0; c < K; ++c) {
                 const double *pv = post + ((size_t)c * n + (size_t)v) * NS;
                 for (int i = 0; i < NS; ++i)
@@ -636,7 +678,7 @@ static void *joint_ref_worker(void *arg)
                         J->status = ORC_ERR_INVALID_ALIGNMENT; /* :469-473 */
                         goto done;
                     }
-                    if (!nucleotide_profile(pattern[pos], prof)) {
+                    if (!alphabet_profile(pattern[pos], prof)) {
                         J->status = ORC_ERR_ALPHABET_MISMATCH; /* :475-476 */
                         goto done;
                     }
@@ -711,7 +753,7 @@ done:
 #define OB 8
 typedef struct {
     orc_job job;
-    const double *Pcache; /* [node][cat][16] row-major; identity for rate*t == 0 */
+    const double *Pcache; /* [node][cat][NS*NS] row-major; identity for rate*t == 0 */
 } orc_optjob;
 
 static void *lnl_opt_worker(void *arg)
@@ -738,7 +780,7 @@ static void *lnl_opt_worker(void *arg)
                 for (int b = 0; b < OB; ++b) {
                     double pv[NS] = {1, 1, 1, 1}, l = 0.0;
                     if (b < nb) {
-                        if (!nucleotide_profile(J->patterns[(size_t)(p0 + b) * J->n_rows + row], pv)) {
+                        if (!alphabet_profile(J->patterns[(size_t)(p0 + b) * J->n_rows + row], pv)) {
                             J->status = ORC_ERR_ALPHABET_MISMATCH;
                             goto done;
                         }
@@ -760,7 +802,7 @@ static void *lnl_opt_worker(void *arg)
                         lo[b] = 0.0;
                     for (int ci = T->child_off[v]; ci < T->child_off[v + 1]; ++ci) {
                         int ch = T->children[ci];
-                        const double *P = OJ->Pcache + ((size_t)ch * K + c) * 16;
+                        const double *P = OJ->Pcache + ((size_t)ch * K + c) * (NS * NS);
                         const double *in = clv + ((size_t)ch * K + c) * NS * OB;
                         const double *li = ls + ((size_t)ch * K + c) * OB;
                         for (int i = 0; i < NS; ++i)
@@ -864,10 +906,10 @@ int orc_log_likelihood(int n_nodes, const int *postorder, const int *preorder, c
     double *pp = per_pattern ? per_pattern : (double *)malloc(sizeof(double) * (size_t)(n_patterns > 0 ? n_patterns : 1));
     int status;
     if (mode == 2) {
-        double *Pc = (double *)malloc(sizeof(double) * 16 * (size_t)n_nodes * (size_t)n_cat);
+        double *Pc = (double *)malloc(sizeof(double) * (NS * NS) * (size_t)n_nodes * (size_t)n_cat);
         for (int v = 0; v < n_nodes; ++v)
             for (int c = 0; c < n_cat; ++c)
-                orc_transition(rm, rates[c] * blen[v], Pc + ((size_t)v * n_cat + c) * 16);
+                orc_transition(rm, rates[c] * blen[v], Pc + ((size_t)v * n_cat + c) * (NS * NS));
         orc_optjob *jobs = (orc_optjob *)calloc((size_t)n_threads, sizeof(orc_optjob));
         for (int t = 0; t < n_threads; ++t) {
             orc_job *J = &jobs[t].job;
@@ -979,9 +1021,9 @@ double orc_bruteforce_site_likelihood(int n_nodes, const int *child_off, const i
             internal[n_int++] = v;
     if (n_int > 12)
         return NAN;
-    double *P = (double *)malloc(sizeof(double) * 16 * (size_t)n_nodes);
+    double *P = (double *)malloc(sizeof(double) * (NS * NS) * (size_t)n_nodes);
     for (int v = 0; v < n_nodes; ++v)
-        orc_transition(rm, rate * blen[v], P + (size_t)v * 16);
+        orc_transition(rm, rate * blen[v], P + (size_t)v * (NS * NS));
     int *state = (int *)calloc((size_t)n_nodes, sizeof(int));
     long combos = 1;
     for (int i = 0; i < n_int; ++i)
@@ -998,12 +1040,12 @@ double orc_bruteforce_site_likelihood(int n_nodes, const int *child_off, const i
             if (v == root)
                 continue;
             int par = parent[v];
-            const double *Pv = P + (size_t)v * 16;
+            const double *Pv = P + (size_t)v * (NS * NS);
             if (child_off[v + 1] - child_off[v] > 0) {
                 pr *= Pv[state[par] * NS + state[v]];
             } else {
                 double prof[NS];
-                nucleotide_profile(pattern[leaf_row[v]], prof);
+                alphabet_profile(pattern[leaf_row[v]], prof);
                 double s = 0.0;
                 for (int j = 0; j < NS; ++j)
                     s += Pv[state[par] * NS + j] * prof[j];

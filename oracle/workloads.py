@@ -16,6 +16,9 @@ MODELS = ("jc69", "hky_g4", "gtr", "gtr_g4", "gtr_i_g4", "gtr_i")
 PI = (0.30, 0.20, 0.20, 0.30)
 GTR_RATES = (1.0, 2.5, 1.0, 1.0, 2.5, 1.0)
 AMBIG = b"RYSWKMBDHVN-U"
+AA_LETTERS = b"ACDEFGHIKLMNPQRSTVWY"  # AminoAcid::CANONICAL, src/alphabet.rs:73
+AA_AMBIG = b"BZJX-"
+AA_MODELS = ("aa", "aa_g4", "aa_i_g4")
 
 
 def make_model(name):
@@ -33,7 +36,27 @@ def make_model(name):
         return RefModel.gtr(PI, GTR_RATES).with_gamma(0.5, 4).with_invariant(0.2)
     if name == "gtr_i":
         return RefModel.gtr(PI, GTR_RATES).with_invariant(0.3)
+    if name in AA_MODELS:
+        return make_aa_model(name)
     raise ValueError(name)
+
+
+def make_aa_model(name, seed=0xAA20):
+    """A seeded general 20-state GTR (GtrModel::<AminoAcid>::new(pi, W, true), src/models/gtr.rs:39-50): the reference
+    ships no named protein matrices, the caller brings pi and the symmetric exchangeabilities."""
+    from . import AaModel
+
+    rng = np.random.default_rng(seed)
+    pi = rng.dirichlet(np.full(20, 8.0))
+    w = rng.gamma(1.5, 1.0, (20, 20)) + 0.05
+    w = (w + w.T) / 2
+    np.fill_diagonal(w, 0.0)
+    m = AaModel(pi, w, True)
+    if name == "aa_g4":
+        m = m.with_gamma(0.6, 4)
+    elif name == "aa_i_g4":
+        m = m.with_gamma(0.6, 4).with_invariant(0.15)
+    return m
 
 
 def assign_branch_lengths(tree, rng, mean=0.1):
@@ -52,10 +75,11 @@ def simulate_patterns(ft, model, n_sites, rng):
     pi = model.pi
     n_rows = int(ft["leaf_row"].max()) + 1
     out = np.full((n_sites, n_rows), ord("-"), np.uint8)
-    letters = np.frombuffer(b"ACGT", np.uint8)
+    ns = len(pi)
+    letters = np.frombuffer(b"ACGT" if ns == 4 else AA_LETTERS, np.uint8)
     for v in ft["preorder"]:
         if v == ft["root"]:
-            state[v] = rng.choice(4, size=n_sites, p=pi / pi.sum())
+            state[v] = rng.choice(ns, size=n_sites, p=pi / pi.sum())
         else:
             par = state[ft["parent"][v]]
             u = rng.random(n_sites)
@@ -67,7 +91,7 @@ def simulate_patterns(ft, model, n_sites, rng):
                 P = model.transition(rates[c] * ft["blen"][v])
                 cum = np.cumsum(np.clip(P, 0, None), axis=1)
                 cum /= cum[:, -1:]
-                s[sel] = (u[sel, None] > cum[par[sel]]).sum(axis=1).clip(0, 3)
+                s[sel] = (u[sel, None] > cum[par[sel]]).sum(axis=1).clip(0, ns - 1)
             state[v] = s
         r = ft["leaf_row"][v]
         if r >= 0:
@@ -96,7 +120,7 @@ def make_case(n_taxa, n_sites, model="gtr_g4", seed=1, ambiguity=0.0, compress=F
     pats = simulate_patterns(ft, m, n_sites, rng)
     if ambiguity > 0:
         mask = rng.random(pats.shape) < ambiguity
-        codes = np.frombuffer(AMBIG, np.uint8)
+        codes = np.frombuffer(AA_AMBIG if model in AA_MODELS else AMBIG, np.uint8)
         pats[mask] = codes[rng.integers(len(codes), size=int(mask.sum()))]
     if compress:
         uniq, inv, counts = np.unique(pats, axis=0, return_inverse=True, return_counts=True)

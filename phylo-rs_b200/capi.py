@@ -27,6 +27,7 @@ FLAG_TIMING = 1 << 1
 FLAG_LEVEL_KERNELS = 1 << 2
 FLAG_NNI_FULL = 1 << 3
 FLAG_NNI_WALK = 1 << 4
+FLAG_AMINO_ACID = 1 << 5  # 20-state context (AminoAcid, src/alphabet.rs:66-116)
 LAYOUT_PATTERN_MAJOR = 0
 LAYOUT_ROW_MAJOR = 1
 
@@ -154,6 +155,7 @@ class Context:
         if rc:
             self._h = C.c_void_p()
             raise PhbError(rc, "phb_ctx_create failed (no usable B200 / CUDA device?)")
+        self.n_states = 20 if (flags & FLAG_AMINO_ACID) else 4
         self.n_rows = 0
         self.n_patterns = 0
         self.n_nodes = 0
@@ -241,7 +243,9 @@ class Context:
     def set_model(self, eigenvalues, eigenvectors, pi, sqrt_pi, inv_sqrt_pi, rates, weights):
         """eigenvectors: 4x4 with [i, k] = component i of eigenvector k (passed column-major)."""
         lam = np.ascontiguousarray(eigenvalues, np.float64)
-        V = np.ascontiguousarray(np.asarray(eigenvectors, np.float64).T).ravel()  # V[i + 4k]
+        V = np.ascontiguousarray(np.asarray(eigenvectors, np.float64).T).ravel()  # V[i + ns * k]
+        if lam.shape != (self.n_states,) or V.shape != (self.n_states * self.n_states,):
+            raise ValueError(f"this context evaluates {self.n_states} states")
         pi, sp, isp = (np.ascontiguousarray(x, np.float64) for x in (pi, sqrt_pi, inv_sqrt_pi))
         r, w = np.ascontiguousarray(rates, np.float64), np.ascontiguousarray(weights, np.float64)
         self._check(self.lib.L.phb_set_model(self._h, _dp(lam), _dp(V), _dp(pi), _dp(sp), _dp(isp), len(r), _dp(r), _dp(w)))
@@ -286,7 +290,7 @@ class Context:
     def marginal_asr(self, want_posteriors=False):
         n, P = self.n_nodes, self.n_patterns
         states = np.zeros((n, max(P, 1)), np.uint8)
-        post = np.zeros((n, max(P, 1), 4), np.float64) if want_posteriors else None
+        post = np.zeros((n, max(P, 1), self.n_states), np.float64) if want_posteriors else None
         tot = C.c_double(0.0)
         self._check(self.lib.L.phb_marginal_asr(
             self._h, states.ctypes.data_as(C.POINTER(C.c_uint8)), None if post is None else _dp(post), C.byref(tot)))
@@ -303,9 +307,9 @@ class Context:
         return tot.value, (states[:, :0] if P == 0 else states)
 
     def transition_matrices(self, t, n_cat):
-        """P(rate_c * t_k) for every t_k and model category: [len(t)][n_cat][4][4] (device-evaluated)."""
+        """P(rate_c * t_k) for every t_k and model category: [len(t)][n_cat][ns][ns] (device-evaluated)."""
         t = np.ascontiguousarray(np.atleast_1d(t), np.float64)
-        out = np.zeros((len(t), n_cat, 4, 4), np.float64)
+        out = np.zeros((len(t), n_cat, self.n_states, self.n_states), np.float64)
         self._check(self.lib.L.phb_transition_matrices(self._h, len(t), _dp(t), _dp(out)))
         return out
 

@@ -1,0 +1,370 @@
+// aa.cuh — the 20-state (AminoAcid, src/alphabet.rs:66-116) instance of the engines: SURVEY §8 f4.
+//
+// The reference's engines are generic over A: Alphabet (likelihood.rs:156-166, 224-235; GtrModel<A>, gtr.rs:30-58) and
+// the nucleotide kernels of kernels.cuh / sweep.cuh are specialised to 4 states down to their register layout, so the
+// 20-state instance is a set of kernels of its own, level-batched with every CLV in HBM:
+//   aa_transition_kernel   P(r_c t) per (edge, category), 20x20          rate_matrix.rs:113-135
+//   aa_tip_const_kernel    sum of the leaves' Profile::scale() log-scales likelihood.rs:108 (B, Z, J: ln 0.5 each)
+//   aa_clv_kernel          one level of prune_pattern_category            likelihood.rs:110-131
+//   aa_root_kernel         root mass, ln weights, log_sum_exp, weighting  likelihood.rs:135-140, 61-68, 205-206
+//   aa_down_kernel         one depth of the marginal pre-order pass       likelihood.rs:303-390
+// Work split: one thread = one site pattern of one rate category (all categories in the down pass, where the mixture
+// over categories is thread-local); a block works on ONE (node, category), so every P(t) it touches is block-uniform
+// and is staged once in shared memory and read by broadcast.  Per internal child that is a 20x20 mat-vec per thread
+// (400 DFMA against 160 bytes of CLV read): the kernel is FP64-bound, not HBM-bound, at 20 states.
+// CLV layout: clv[slot][category][state][pattern of the tile] (pattern fastest: coalesced), one int32 exponent per
+// (slot, category, pattern); a stored CLV has its maximum in [1,2) (exact power-of-two scaling, as everywhere else).
+#pragma once
+#include "kernels.cuh"
+
+namespace phb {
+
+constexpr int AA_NS = 20;
+constexpr int AA_THREADS = 128;
+// tip codes: 0..19 = position in AminoAcid::CANONICAL "ACDEFGHIKLMNPQRSTVWY" (alphabet.rs:73-79)
+constexpr uint8_t AA_CODE_B = 20, AA_CODE_Z = 21, AA_CODE_J = 22, AA_CODE_X = 23, AA_CODE_GAP = 24;
+
+// AminoAcid::profile's accepted bytes (alphabet.rs:85-115); anything else is CODE_INVALID
+__host__ __device__ inline uint8_t aa_encode_byte(uint8_t c)
+{
+    const char *canonical = "ACDEFGHIKLMNPQRSTVWY";
+    for (int i = 0; i < AA_NS; ++i)
+        if ((uint8_t)canonical[i] == c) return (uint8_t)i;
+    switch (c) {
+    case 'B': return AA_CODE_B;
+    case 'Z': return AA_CODE_Z;
+    case 'J': return AA_CODE_J;
+    case 'X': return AA_CODE_X;
+    case '-': return AA_CODE_GAP;
+    default: return CODE_INVALID;
+    }
+}
+__host__ __device__ inline uint8_t aa_decode_code(uint8_t code)
+{
+    const char *all = "ACDEFGHIKLMNPQRSTVWYBZJX-";
+    return code <= AA_CODE_GAP ? (uint8_t)all[code] : (uint8_t)'?';
+}
+// The two states of a two-state ambiguity code, exactly as the reference writes them (alphabet.rs:91-112): B sets
+// indices 3 and 11, Z 4 and 14, J 8 and 9 -- the reference's comments name D|N, E|Q, I|L, but its CANONICAL order puts
+// those letters elsewhere; parity is with the indices the code uses (and its own test asserts: integration_test.rs:90-102).
+__host__ __device__ inline void aa_pair_states(uint32_t code, int &a, int &b)
+{
+    a = code == AA_CODE_B ? 3 : code == AA_CODE_Z ? 4 : 8;
+    b = code == AA_CODE_B ? 11 : code == AA_CODE_Z ? 14 : 9;
+}
+
+// Model in global memory (4.4 KB: beyond what is comfortable as a by-value kernel parameter).
+struct AaModelDev {
+    double lambda[AA_NS];
+    double V[AA_NS * AA_NS]; // column-major: V[i + 20 k] = component i of eigenvector k
+    double pi[AA_NS];
+    double sqrt_pi[AA_NS];
+    double inv_sqrt_pi[AA_NS];
+    double rates[MAX_CAT];
+    double weights[MAX_CAT];
+    double ln_weights[MAX_CAT];
+    int n_cat;
+    int pad;
+};
+
+// The up pass uses kernels.cuh's any-arity GenOp / GenChild tables (TreeSched::uops, grouped by level).
+// One node of one depth of the pre-order pass.
+struct AaDown {
+    int32_t node;        // dense id: row of the states / posteriors output
+    int32_t slot;        // CLV slot of the node (internal), -1 for a leaf
+    int32_t row;         // alignment row of a leaf, -1 otherwise
+    int32_t parent_slot; // CLV slot holding the parent's posterior, -1 for the root
+};
+
+// ---- P(t): diag(inv_sqrt_pi) V diag(exp(lambda r t)) V^T diag(sqrt_pi), exact identity at r t == 0 ------------------
+// One block per (edge, category).  Same operation order as RateMatrix::transition (rate_matrix.rs:119-133):
+// (V_ik e_k) V_jk summed over k ascending, then the two diagonal scalings.
+__global__ void __launch_bounds__(AA_THREADS)
+aa_transition_kernel(const double *__restrict__ blen, int n_edges, const AaModelDev *__restrict__ M, double *__restrict__ P)
+{
+    __shared__ double e[AA_NS];
+    const int n_cat = M->n_cat;
+    const int edge = blockIdx.x / n_cat, cat = blockIdx.x - edge * n_cat;
+    if (edge >= n_edges) return;
+    const double t = M->rates[cat] * blen[edge];
+    double *out = P + (size_t)blockIdx.x * (AA_NS * AA_NS);
+    if (t == 0.0) {
+        for (int idx = threadIdx.x; idx < AA_NS * AA_NS; idx += AA_THREADS) out[idx] = (idx / AA_NS == idx % AA_NS) ? 1.0 : 0.0;
+        return;
+    }
+    if (threadIdx.x < AA_NS) e[threadIdx.x] = exp(M->lambda[threadIdx.x] * t);
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < AA_NS * AA_NS; idx += AA_THREADS) {
+        const int i = idx / AA_NS, j = idx - i * AA_NS;
+        double acc = (M->V[i] * e[0]) * M->V[j];
+        for (int k = 1; k < AA_NS; ++k) acc += (M->V[i + AA_NS * k] * e[k]) * M->V[j + AA_NS * k];
+        out[idx] = M->inv_sqrt_pi[i] * acc * M->sqrt_pi[j];
+    }
+}
+
+// ---- leaves' log-scales: Profile::scale() of a leaf profile divides by its maximum (likelihood.rs:108, profile.rs:20-39):
+// 1 for a canonical letter, X and the gap (log-scale 0), 0.5 for B, Z, J (log-scale ln 0.5 each).
+__global__ void aa_tip_const_kernel(const int *__restrict__ leaf_rows, int n_leaves, const uint8_t *__restrict__ tips,
+                                    int64_t P_pad, int64_t P, double *__restrict__ leaf_ls)
+{
+    const int64_t site = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (site >= P) return;
+    int halves = 0;
+    for (int k = 0; k < n_leaves; ++k) {
+        const uint32_t c = tips[(int64_t)leaf_rows[k] * P_pad + site];
+        halves += (c >= AA_CODE_B && c <= AA_CODE_J) ? 1 : 0;
+    }
+    leaf_ls[site] = (double)halves * -0.69314718055994530942; // ln 0.5
+}
+
+// power-of-two normalisation of 20 states to a maximum in [1,2); returns the exponent taken out
+// (v_true = v_stored * 2^exponent).  Zero / negative maxima are left alone (Profile::scale's max_val <= 0 return).
+__device__ __forceinline__ int aa_normalize(double (&v)[AA_NS])
+{
+    int h = __double2hiint(v[0]);
+#pragma unroll
+    for (int i = 1; i < AA_NS; ++i) h = max(h, __double2hiint(v[i]));
+    if (h <= 0) return 0;
+    int s = 1023 - (h >> 20); // multiply by 2^s
+    if (s > 1000) s = 1000;   // subnormal maxima: as far as one exact factor goes
+    if (s < -1000) s = -1000;
+    const double f = __longlong_as_double((long long)(1023 + s) << 52);
+#pragma unroll
+    for (int i = 0; i < AA_NS; ++i) v[i] *= f;
+    return -s;
+}
+
+// the vector a tip contributes through P: sum_j P[i][j] profile[j] with the 0/1 profile Profile::scale() leaves
+// (zero terms of the reference's dense product are exact zeros, so the masked sums below are the same values)
+__device__ __forceinline__ double aa_tip_row(const double *Ps, int i, uint32_t code)
+{
+    const double *row = Ps + i * AA_NS;
+    if (code < (uint32_t)AA_NS) return row[code];
+    if (code <= AA_CODE_J) {
+        int a, b;
+        aa_pair_states(code, a, b);
+        return row[a] + row[b];
+    }
+    double s = row[0];
+#pragma unroll
+    for (int j = 1; j < AA_NS; ++j) s += row[j];
+    return s;
+}
+
+// ---- one level of prune_pattern_category (likelihood.rs:110-131), any arity ---------------------------------------
+// grid: x = pattern blocks of the tile, y = op of the level, z = category.  values = prod over children of
+// P_child * profile_child; the product is rescaled ONCE per node, like the reference's single Profile::scale() per
+// node, so a node with very many children leaves the f64 range where the reference does.
+__global__ void __launch_bounds__(AA_THREADS)
+aa_clv_kernel(const GenOp *__restrict__ ops, const GenChild *__restrict__ kids, int n_cat, const double *__restrict__ Pmat,
+              double *__restrict__ clv, int *__restrict__ exps, size_t slot_stride, size_t tile_pad, int tile_len,
+              const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off)
+{
+    __shared__ double Ps[AA_NS * AA_NS];
+    const GenOp op = ops[blockIdx.y];
+    const int cat = blockIdx.z;
+    const int64_t site = (int64_t)blockIdx.x * AA_THREADS + threadIdx.x;
+    const bool active = site < tile_len;
+    double acc[AA_NS];
+#pragma unroll
+    for (int i = 0; i < AA_NS; ++i) acc[i] = 1.0;
+    int ex = 0;
+    for (int k = op.child_begin; k < op.child_end; ++k) {
+        const GenChild ch = kids[k];
+        __syncthreads(); // the previous child's matrix is no longer read
+        const double *src = Pmat + ((size_t)ch.edge * n_cat + cat) * (AA_NS * AA_NS);
+        for (int idx = threadIdx.x; idx < AA_NS * AA_NS; idx += AA_THREADS) Ps[idx] = src[idx];
+        __syncthreads();
+        if (!active) continue;
+        if (ch.is_tip) {
+            const uint32_t code = tips[(int64_t)ch.src * P_pad + tile_off + site];
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) acc[i] *= aa_tip_row(Ps, i, code);
+        } else {
+            const double *x_src = clv + (size_t)ch.src * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
+            double x[AA_NS];
+#pragma unroll
+            for (int j = 0; j < AA_NS; ++j) x[j] = x_src[(size_t)j * tile_pad];
+            ex += exps[((size_t)ch.src * n_cat + cat) * tile_pad + site];
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) {
+                double y = Ps[i * AA_NS] * x[0];
+#pragma unroll
+                for (int j = 1; j < AA_NS; ++j) y += Ps[i * AA_NS + j] * x[j];
+                acc[i] *= y;
+            }
+        }
+    }
+    if (!active) return;
+    ex += aa_normalize(acc);
+    double *dst = clv + (size_t)op.out_slot * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
+#pragma unroll
+    for (int i = 0; i < AA_NS; ++i) dst[(size_t)i * tile_pad] = acc[i];
+    exps[((size_t)op.out_slot * n_cat + cat) * tile_pad + site] = ex;
+}
+
+// the root's vector for one (pattern, category): its CLV, or its tip profile when the tree is a single leaf
+__device__ __forceinline__ void aa_load_vec(const double *__restrict__ clv, size_t slot_stride, size_t tile_pad, int slot, int cat,
+                                            int64_t site, double (&x)[AA_NS])
+{
+    const double *src = clv + (size_t)slot * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
+#pragma unroll
+    for (int j = 0; j < AA_NS; ++j) x[j] = src[(size_t)j * tile_pad];
+}
+__device__ __forceinline__ void aa_tip_vec(uint32_t code, double (&x)[AA_NS])
+{
+    int a = -1, b = -1;
+    if (code >= AA_CODE_B && code <= AA_CODE_J) aa_pair_states(code, a, b);
+#pragma unroll
+    for (int j = 0; j < AA_NS; ++j) x[j] = (code >= AA_CODE_X || (int)code == j || j == a || j == b) ? 1.0 : 0.0;
+}
+
+// ---- root: cat_ll_c = ln w_c + ln(sum_i pi_i v_i) + log-scale (likelihood.rs:135-140); site_ll = log_sum_exp over the
+// categories (:61-68: a non-finite maximum is returned as it is); per-block sum of multiplicity * site_ll (:205-206).
+// cat_ll_out[c][pattern of the tile] (without the leaves' log-scale, which is common to the categories) feeds the
+// mixture weights of the down pass.
+__global__ void __launch_bounds__(AA_THREADS)
+aa_root_kernel(int root_slot, int root_row, const AaModelDev *__restrict__ M, const double *__restrict__ clv,
+               const int *__restrict__ exps, size_t slot_stride, size_t tile_pad, int tile_len, const uint8_t *__restrict__ tips,
+               int64_t P_pad, int64_t tile_off, const double *__restrict__ leaf_ls, const double *__restrict__ mult,
+               double *__restrict__ per_pattern, double *__restrict__ cat_ll_out, double *__restrict__ partials)
+{
+    __shared__ double red[AA_THREADS];
+    const int64_t site = (int64_t)blockIdx.x * AA_THREADS + threadIdx.x;
+    const int n_cat = M->n_cat;
+    double weighted = 0.0;
+    if (site < tile_len) {
+        double mx = -INFINITY;
+        for (int c = 0; c < n_cat; ++c) {
+            double x[AA_NS];
+            int ex = 0;
+            if (root_slot >= 0) {
+                aa_load_vec(clv, slot_stride, tile_pad, root_slot, c, site, x);
+                ex = exps[((size_t)root_slot * n_cat + c) * tile_pad + site];
+            } else
+                aa_tip_vec(tips[(int64_t)root_row * P_pad + tile_off + site], x);
+            double mass = M->pi[0] * x[0];
+#pragma unroll
+            for (int i = 1; i < AA_NS; ++i) mass += M->pi[i] * x[i];
+            const double ll = M->ln_weights[c] + log(mass) + (double)ex * 0.69314718055994530942;
+            cat_ll_out[(size_t)c * tile_pad + site] = ll;
+            mx = fmax(mx, ll);
+        }
+        double lse = mx;
+        if (isfinite(mx)) {
+            double sum = 0.0;
+            for (int c = 0; c < n_cat; ++c) sum += exp(cat_ll_out[(size_t)c * tile_pad + site] - mx);
+            lse = mx + log(sum);
+        }
+        cat_ll_out[(size_t)n_cat * tile_pad + site] = lse; // row n_cat: the log_sum_exp itself
+        const double site_ll = lse + leaf_ls[tile_off + site];
+        per_pattern[tile_off + site] = site_ll;
+        weighted = mult[tile_off + site] * site_ll;
+    }
+    red[threadIdx.x] = weighted;
+    __syncthreads();
+    for (int s = AA_THREADS / 2; s > 0; s >>= 1) {
+        if ((int)threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) partials[blockIdx.x] = red[0];
+}
+
+// ---- one depth of the marginal pre-order pass (likelihood.rs:303-390) -------------------------------------------------
+// grid: x = pattern blocks of the tile, y = node of the depth.  A thread owns one pattern and loops over the categories:
+//   root:   post = pi (.) up                                                        (:304-316)
+//   else:   msg = P^T post_parent,  post = up (.) msg                               (:318-341)
+//   post /= its sum when the sum is > 0; mixed += mix_c post, mix_c = exp(cat_ll_c - site_ll), uniform when site_ll is
+//   not finite (:351-362); mixed /= its sum when > 0; state = LAST maximal index (Iterator::max_by, :385-390).
+// The posterior of an internal node overwrites its up-pass CLV in place (its children read it one depth further down;
+// nobody reads the up-pass values again); a leaf's goes nowhere but into the mixture.
+__global__ void __launch_bounds__(AA_THREADS)
+aa_down_kernel(const AaDown *__restrict__ nodes, const AaModelDev *__restrict__ M, const double *__restrict__ Pmat,
+               double *__restrict__ clv, size_t slot_stride, size_t tile_pad, int tile_len, const uint8_t *__restrict__ tips,
+               int64_t P_pad, int64_t tile_off, const double *__restrict__ cat_ll, uint8_t *__restrict__ states,
+               double *__restrict__ post_out)
+{
+    __shared__ double Ps[AA_NS * AA_NS];
+    const AaDown nd = nodes[blockIdx.y];
+    const int n_cat = M->n_cat;
+    const int64_t site = (int64_t)blockIdx.x * AA_THREADS + threadIdx.x;
+    const bool active = site < tile_len;
+    double mixed[AA_NS];
+#pragma unroll
+    for (int i = 0; i < AA_NS; ++i) mixed[i] = 0.0;
+    const double lse = active ? cat_ll[(size_t)n_cat * tile_pad + site] : 0.0;
+    const uint32_t code = (active && nd.slot < 0) ? tips[(int64_t)nd.row * P_pad + tile_off + site] : 0u;
+    for (int c = 0; c < n_cat; ++c) {
+        if (nd.parent_slot >= 0) {
+            __syncthreads();
+            const double *src = Pmat + ((size_t)nd.node * n_cat + c) * (AA_NS * AA_NS);
+            for (int idx = threadIdx.x; idx < AA_NS * AA_NS; idx += AA_THREADS) Ps[idx] = src[idx];
+            __syncthreads();
+        }
+        if (!active) continue;
+        double post[AA_NS];
+        if (nd.parent_slot < 0) {
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) post[i] = M->pi[i];
+        } else {
+            const double *pp = clv + (size_t)nd.parent_slot * slot_stride + (size_t)c * AA_NS * tile_pad + site;
+            const double p0 = pp[0];
+#pragma unroll
+            for (int j = 0; j < AA_NS; ++j) post[j] = Ps[j] * p0;
+#pragma unroll
+            for (int i = 1; i < AA_NS; ++i) {
+                const double pi_ = pp[(size_t)i * tile_pad];
+#pragma unroll
+                for (int j = 0; j < AA_NS; ++j) post[j] += Ps[i * AA_NS + j] * pi_;
+            }
+        }
+        double *own = nd.slot >= 0 ? clv + (size_t)nd.slot * slot_stride + (size_t)c * AA_NS * tile_pad + site : nullptr;
+        if (own) {
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) post[i] = nd.parent_slot < 0 ? post[i] * own[(size_t)i * tile_pad] : own[(size_t)i * tile_pad] * post[i];
+        } else {
+            double up[AA_NS];
+            aa_tip_vec(code, up);
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) post[i] = nd.parent_slot < 0 ? post[i] * up[i] : up[i] * post[i];
+        }
+        double sum = 0.0;
+#pragma unroll
+        for (int i = 0; i < AA_NS; ++i) sum += post[i];
+        if (sum > 0.0) {
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) post[i] /= sum;
+        }
+        if (own) {
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) own[(size_t)i * tile_pad] = post[i];
+        }
+        const double mix = isfinite(lse) ? exp(cat_ll[(size_t)c * tile_pad + site] - lse) : 1.0 / (double)n_cat;
+#pragma unroll
+        for (int i = 0; i < AA_NS; ++i) mixed[i] += mix * post[i];
+    }
+    if (!active) return;
+    double sum = 0.0;
+#pragma unroll
+    for (int i = 0; i < AA_NS; ++i) sum += mixed[i];
+    if (sum > 0.0) {
+#pragma unroll
+        for (int i = 0; i < AA_NS; ++i) mixed[i] /= sum;
+    }
+    int best = 0;
+    double best_v = mixed[0];
+#pragma unroll
+    for (int i = 1; i < AA_NS; ++i)
+        if (mixed[i] >= best_v) {
+            best_v = mixed[i];
+            best = i;
+        }
+    states[(size_t)nd.node * tile_pad + site] = (uint8_t)best;
+    if (post_out) {
+        double *o = post_out + ((size_t)nd.node * tile_len + site) * AA_NS;
+#pragma unroll
+        for (int i = 0; i < AA_NS; ++i) o[i] = mixed[i];
+    }
+}
+
+} // namespace phb

@@ -1,0 +1,254 @@
+// aa_engine.cuh — host side of the 20-state (AminoAcid) engines of a context created with PHB_FLAG_AMINO_ACID.
+// Included by phylo_b200.cu after phb_ctx, DevBuf, TreeSched and the CU / CHECK_LAUNCH macros; kernels: aa.cuh.
+// One device (the context's first); site patterns are tiled so that the CLVs of a tile fit the CLV budget.
+#pragma once
+
+namespace {
+
+inline AaState &aa_of(phb_ctx *ctx) { return ctx->aa; }
+
+int aa_set_alignment(phb_ctx *ctx, int32_t n_rows, int64_t P, const uint8_t *bytes, int32_t layout, const uint64_t *multiplicity)
+{
+    AaState &A = aa_of(ctx);
+    Device &d = ctx->devs[0];
+    CU(cudaSetDevice(d.ordinal));
+    ctx->have_aln = false;
+    ctx->n_rows = n_rows;
+    ctx->n_patterns = P;
+    A.P_pad = round_up(std::max<int64_t>(P, 1), AA_THREADS);
+    ctx->row_invalid_host.assign(std::max(n_rows, 1), 0);
+    ctx->row_first_invalid.assign(std::max(n_rows, 1), 0);
+    // ASCII -> tip codes, transposed to [row][P_pad] on the host (the padding is the gap code)
+    std::vector<uint8_t> codes((size_t)std::max(n_rows, 1) * (size_t)A.P_pad, AA_CODE_GAP);
+    uint8_t table[256];
+    for (int c = 0; c < 256; ++c) table[c] = aa_encode_byte((uint8_t)c);
+    for (int r = 0; r < n_rows; ++r) {
+        uint8_t *dst = codes.data() + (size_t)r * A.P_pad;
+        int bad = 0;
+        for (int64_t p = 0; p < P; ++p) {
+            const uint8_t b = layout == PHB_LAYOUT_PATTERN_MAJOR ? bytes[(size_t)p * n_rows + r] : bytes[(size_t)r * P + p];
+            const uint8_t c = table[b];
+            dst[p] = c;
+            bad |= c == CODE_INVALID;
+        }
+        ctx->row_invalid_host[r] = bad;
+        ctx->row_first_invalid[r] = P > 0 && dst[0] == CODE_INVALID;
+    }
+    CU(A.tips.ensure(codes.size()));
+    CU(cudaMemcpyAsync(A.tips.p, codes.data(), codes.size(), cudaMemcpyHostToDevice, d.stream));
+    std::vector<double> mult((size_t)A.P_pad, 0.0);
+    for (int64_t p = 0; p < P; ++p) mult[p] = multiplicity ? (double)multiplicity[p] : 1.0;
+    CU(A.mult.ensure(sizeof(double) * mult.size()));
+    CU(cudaMemcpyAsync(A.mult.p, mult.data(), sizeof(double) * mult.size(), cudaMemcpyHostToDevice, d.stream));
+    CU(cudaStreamSynchronize(d.stream)); // the host vectors go out of scope
+    A.tip_const_valid = false;
+    ctx->have_aln = true;
+    return PHB_OK;
+}
+
+int aa_set_model(phb_ctx *ctx, const double *lambda, const double *V, const double *pi, const double *sqrt_pi,
+                 const double *inv_sqrt_pi, int32_t n_cat, const double *rates, const double *weights)
+{
+    AaState &A = aa_of(ctx);
+    Device &d = ctx->devs[0];
+    CU(cudaSetDevice(d.ordinal));
+    AaModelDev &M = A.M;
+    memset(&M, 0, sizeof M);
+    memcpy(M.lambda, lambda, sizeof M.lambda);
+    memcpy(M.V, V, sizeof M.V);
+    memcpy(M.pi, pi, sizeof M.pi);
+    memcpy(M.sqrt_pi, sqrt_pi, sizeof M.sqrt_pi);
+    memcpy(M.inv_sqrt_pi, inv_sqrt_pi, sizeof M.inv_sqrt_pi);
+    for (int c = 0; c < n_cat; ++c) {
+        M.rates[c] = rates[c];
+        M.weights[c] = weights[c];
+        M.ln_weights[c] = std::log(weights[c]);
+    }
+    M.n_cat = n_cat;
+    CU(A.model.ensure(sizeof M));
+    CU(cudaMemcpyAsync(A.model.p, &M, sizeof M, cudaMemcpyHostToDevice, d.stream));
+    CU(cudaStreamSynchronize(d.stream));
+    ctx->have_model = true;
+    return PHB_OK;
+}
+
+// device tables of the tree: any-arity ops by level (TreeSched::uops), pre-order nodes by depth, branch lengths
+int aa_upload_tree(phb_ctx *ctx)
+{
+    AaState &A = aa_of(ctx);
+    const TreeSched &T = ctx->tree;
+    Device &d = ctx->devs[0];
+    CU(cudaSetDevice(d.ordinal));
+    std::vector<std::vector<int>> by_depth(T.max_depth + 1);
+    for (int v = 0; v < T.n; ++v) by_depth[T.depth[v]].push_back(v);
+    A.down_nodes.clear();
+    A.down_off.assign(1, 0);
+    for (int dep = 0; dep <= T.max_depth; ++dep) {
+        for (int v : by_depth[dep]) {
+            AaDown nd;
+            nd.node = v;
+            nd.slot = T.slot[v];
+            nd.row = T.slot[v] < 0 ? T.leaf_row[v] : -1;
+            nd.parent_slot = v == T.root ? -1 : T.slot[T.parent[v]];
+            A.down_nodes.push_back(nd);
+        }
+        A.down_off.push_back((int)A.down_nodes.size());
+    }
+    auto up = [&](DevBuf &b, const void *src, size_t bytes) -> cudaError_t {
+        cudaError_t e = b.ensure(bytes);
+        if (e != cudaSuccess) return e;
+        if (bytes) return cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, d.stream);
+        return cudaSuccess;
+    };
+    CU(up(A.blen, T.blen.data(), sizeof(double) * T.n));
+    CU(up(A.uops, T.uops.data(), sizeof(GenOp) * T.uops.size()));
+    CU(up(A.ukids, T.ukids.data(), sizeof(GenChild) * T.ukids.size()));
+    CU(up(A.down, A.down_nodes.data(), sizeof(AaDown) * A.down_nodes.size()));
+    CU(up(A.leaf_rows, T.leaf_rows.data(), sizeof(int) * T.leaf_rows.size()));
+    CU(cudaStreamSynchronize(d.stream));
+    A.tip_const_valid = false;
+    ctx->tree_uploaded = true;
+    return PHB_OK;
+}
+
+// compute_log_likelihood (likelihood.rs:156-209) / compute_marginal_asr (:224-408) at 20 states
+int aa_evaluate(phb_ctx *ctx, bool asr, uint8_t *states_out, double *post_out, double *total)
+{
+    AaState &A = aa_of(ctx);
+    const TreeSched &T = ctx->tree;
+    Device &d = ctx->devs[0];
+    if (!ctx->have_aln || !ctx->have_model || !T.valid)
+        return ctx->fail(PHB_ERR_STATE, "set_alignment, set_model and set_tree must precede the evaluation");
+    int rc = check_leaves(ctx);
+    if (rc) return rc;
+    CU(cudaSetDevice(d.ordinal));
+    const int64_t P = ctx->n_patterns;
+    const int K = A.M.n_cat;
+    const int n_int = std::max(T.n_internal, 1);
+    // tile of patterns: CLVs (160 K bytes per node and pattern) + exponents, states and posteriors when asked for
+    size_t free_b = 0, total_b = 0;
+    CU(cudaMemGetInfo(&free_b, &total_b));
+    size_t budget = ctx->clv_budget ? (size_t)ctx->clv_budget : (free_b + A.clv.cap + A.exps.cap + A.states.cap + A.post.cap) / 10 * 7;
+    size_t per_pattern_bytes = (size_t)n_int * K * (AA_NS * sizeof(double) + sizeof(int));
+    if (asr) per_pattern_bytes += (size_t)T.n * (1 + (post_out ? AA_NS * sizeof(double) : 0));
+    int64_t tile_pad = (int64_t)(budget / per_pattern_bytes) / AA_THREADS * AA_THREADS;
+    tile_pad = std::max<int64_t>(AA_THREADS, std::min<int64_t>(tile_pad, A.P_pad));
+    const size_t slot_stride = (size_t)K * AA_NS * (size_t)tile_pad;
+    CU(A.clv.ensure(sizeof(double) * slot_stride * n_int));
+    CU(A.exps.ensure(sizeof(int) * (size_t)n_int * K * tile_pad));
+    CU(A.cat_ll.ensure(sizeof(double) * (size_t)(K + 1) * tile_pad));
+    CU(A.per_pattern.ensure(sizeof(double) * (size_t)A.P_pad));
+    CU(A.leaf_ls.ensure(sizeof(double) * (size_t)A.P_pad));
+    CU(A.Pmat.ensure(sizeof(double) * AA_NS * AA_NS * (size_t)T.n * K));
+    const int max_blocks = (int)(tile_pad / AA_THREADS);
+    CU(A.partials.ensure(sizeof(double) * max_blocks));
+    if (asr) {
+        CU(A.states.ensure((size_t)T.n * tile_pad));
+        if (post_out) CU(A.post.ensure(sizeof(double) * AA_NS * (size_t)T.n * tile_pad));
+    }
+    const AaModelDev *Md = A.model.as<AaModelDev>();
+    PHB_LAUNCH(aa_transition_kernel, dim3((unsigned)(T.n * K)), dim3(AA_THREADS), d.stream, A.blen.as<double>(), T.n, Md, A.Pmat.as<double>());
+    CHECK_LAUNCH();
+    if (!A.tip_const_valid && P > 0) {
+        PHB_LAUNCH(aa_tip_const_kernel, dim3((unsigned)((P + 255) / 256)), dim3(256), d.stream, A.leaf_rows.as<int>(),
+                   (int)T.leaf_rows.size(), A.tips.as<uint8_t>(), A.P_pad, P, A.leaf_ls.as<double>());
+        CHECK_LAUNCH();
+        A.tip_const_valid = true;
+    }
+    const int root_slot = T.slot[T.root];
+    const int root_row = root_slot < 0 ? T.leaf_row[T.root] : -1;
+    std::vector<double> h_part;
+    double sum = 0.0;
+    ctx->stats.n_tiles = 0;
+    for (int64_t off = 0; off < P; off += tile_pad) {
+        const int tile_len = (int)std::min<int64_t>(tile_pad, P - off);
+        const unsigned bx = (unsigned)((tile_len + AA_THREADS - 1) / AA_THREADS);
+        for (int l = 1; l <= T.n_levels; ++l) {
+            const int b = T.ulevel_off[l - 1], n_ops = T.ulevel_off[l] - b;
+            for (int o = 0; o < n_ops; o += 65535) { // grid.y limit
+                const int cnt = std::min(65535, n_ops - o);
+                PHB_LAUNCH(aa_clv_kernel, dim3(bx, (unsigned)cnt, (unsigned)K), dim3(AA_THREADS), d.stream, A.uops.as<GenOp>() + b + o,
+                           A.ukids.as<GenChild>(), K, A.Pmat.as<double>(), A.clv.as<double>(), A.exps.as<int>(), slot_stride,
+                           (size_t)tile_pad, tile_len, A.tips.as<uint8_t>(), A.P_pad, off);
+                CHECK_LAUNCH();
+            }
+        }
+        PHB_LAUNCH(aa_root_kernel, dim3(bx), dim3(AA_THREADS), d.stream, root_slot, root_row, Md, A.clv.as<double>(), A.exps.as<int>(),
+                   slot_stride, (size_t)tile_pad, tile_len, A.tips.as<uint8_t>(), A.P_pad, off, A.leaf_ls.as<double>(),
+                   A.mult.as<double>(), A.per_pattern.as<double>(), A.cat_ll.as<double>(), A.partials.as<double>());
+        CHECK_LAUNCH();
+        if (asr) {
+            for (int dep = 0; dep <= T.max_depth; ++dep) {
+                const int b = A.down_off[dep], n_nd = A.down_off[dep + 1] - b;
+                for (int o = 0; o < n_nd; o += 65535) {
+                    const int cnt = std::min(65535, n_nd - o);
+                    PHB_LAUNCH(aa_down_kernel, dim3(bx, (unsigned)cnt), dim3(AA_THREADS), d.stream, A.down.as<AaDown>() + b + o, Md,
+                               A.Pmat.as<double>(), A.clv.as<double>(), slot_stride, (size_t)tile_pad, tile_len, A.tips.as<uint8_t>(),
+                               A.P_pad, off, A.cat_ll.as<double>(), A.states.as<uint8_t>(), post_out ? A.post.as<double>() : (double *)nullptr);
+                    CHECK_LAUNCH();
+                }
+            }
+            if (states_out)
+                CU(cudaMemcpy2DAsync(states_out + off, (size_t)P, A.states.p, (size_t)tile_pad, (size_t)tile_len, (size_t)T.n,
+                                     cudaMemcpyDeviceToHost, d.stream));
+            if (post_out)
+                CU(cudaMemcpy2DAsync(post_out + (size_t)off * AA_NS, (size_t)P * AA_NS * sizeof(double), A.post.p,
+                                     (size_t)tile_len * AA_NS * sizeof(double), (size_t)tile_len * AA_NS * sizeof(double), (size_t)T.n,
+                                     cudaMemcpyDeviceToHost, d.stream));
+        }
+        h_part.resize(bx);
+        CU(cudaMemcpyAsync(h_part.data(), A.partials.p, sizeof(double) * bx, cudaMemcpyDeviceToHost, d.stream));
+        CU(cudaStreamSynchronize(d.stream));
+        for (unsigned i = 0; i < bx; ++i) sum += h_part[i]; // fixed order: deterministic
+        ctx->stats.n_tiles++;
+    }
+    CU(cudaStreamSynchronize(d.stream));
+    ctx->stats.n_patterns = P;
+    ctx->stats.tile_patterns = tile_pad;
+    ctx->stats.n_levels = T.n_levels;
+    ctx->stats.n_internal = T.n_internal;
+    ctx->stats.n_clv_categories = K;
+    ctx->stats.kernel_launches = ctx->launches;
+    if (total) *total = sum;
+    return PHB_OK;
+}
+
+int aa_get_per_pattern(phb_ctx *ctx, double *per_pattern)
+{
+    AaState &A = aa_of(ctx);
+    Device &d = ctx->devs[0];
+    CU(cudaSetDevice(d.ordinal));
+    if (A.per_pattern.cap < sizeof(double) * (size_t)std::max<int64_t>(ctx->n_patterns, 1))
+        return ctx->fail(PHB_ERR_STATE, "no evaluation has run yet");
+    if (ctx->n_patterns > 0)
+        CU(cudaMemcpyAsync(per_pattern, A.per_pattern.p, sizeof(double) * (size_t)ctx->n_patterns, cudaMemcpyDeviceToHost, d.stream));
+    CU(cudaStreamSynchronize(d.stream));
+    return PHB_OK;
+}
+
+int aa_transition_matrices(phb_ctx *ctx, int32_t n_t, const double *t, double *out)
+{
+    AaState &A = aa_of(ctx);
+    Device &d = ctx->devs[0];
+    CU(cudaSetDevice(d.ordinal));
+    const size_t n_out = (size_t)n_t * A.M.n_cat * AA_NS * AA_NS;
+    CU(d.scratch.ensure(sizeof(double) * ((size_t)n_t + n_out)));
+    double *d_t = d.scratch.as<double>(), *d_P = d_t + n_t;
+    CU(cudaMemcpyAsync(d_t, t, sizeof(double) * n_t, cudaMemcpyHostToDevice, d.stream));
+    PHB_LAUNCH(aa_transition_kernel, dim3((unsigned)(n_t * A.M.n_cat)), dim3(AA_THREADS), d.stream, d_t, (int)n_t,
+               A.model.as<AaModelDev>(), d_P);
+    CHECK_LAUNCH();
+    CU(cudaMemcpyAsync(out, d_P, sizeof(double) * n_out, cudaMemcpyDeviceToHost, d.stream));
+    CU(cudaStreamSynchronize(d.stream));
+    return PHB_OK;
+}
+
+void aa_release(phb_ctx *ctx)
+{
+    AaState &A = aa_of(ctx);
+    for (DevBuf *b : {&A.model, &A.tips, &A.mult, &A.leaf_ls, &A.per_pattern, &A.Pmat, &A.blen, &A.clv, &A.exps, &A.cat_ll, &A.partials,
+                      &A.uops, &A.ukids, &A.down, &A.leaf_rows, &A.states, &A.post})
+        b->release();
+}
+
+} // namespace

@@ -13,6 +13,7 @@
 #include "compress.cuh"
 #include "sweep_sched.h"
 #include "down_sweep.cuh"
+#include "aa.cuh"
 #include "../../include/phylo_b200.h"
 
 #include <algorithm>
@@ -264,6 +265,16 @@ struct Device {
     std::vector<std::pair<int, size_t>> ev_log; // (phase, pool index)
 };
 
+// 20-state (AminoAcid) engines of a PHB_FLAG_AMINO_ACID context: aa.cuh, aa_engine.cuh
+struct AaState {
+    AaModelDev M;
+    DevBuf model, tips, mult, leaf_ls, per_pattern, Pmat, blen, clv, exps, cat_ll, partials, uops, ukids, down, leaf_rows, states, post;
+    std::vector<AaDown> down_nodes;
+    std::vector<int> down_off; // by depth, max_depth + 2 entries
+    int64_t P_pad = 0;
+    bool tip_const_valid = false;
+};
+
 enum Phase { PH_TRANSITION = 0, PH_CLV = 1, PH_ROOT = 2, PH_DOWN = 3, PH_UPPER = 4 };
 
 } // namespace
@@ -296,6 +307,9 @@ struct phb_ctx {
     // stats
     phb_stats stats;
     int64_t launches = 0;
+    // 20 states (PHB_FLAG_AMINO_ACID)
+    bool is_aa = false;
+    AaState aa;
 
     int fail(int code, const char *fmt, ...)
     {
@@ -1466,6 +1480,8 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
 
 } // namespace
 
+#include "aa_engine.cuh"
+
 // =================================================================================================
 // C ABI
 // =================================================================================================
@@ -1486,6 +1502,11 @@ int32_t phb_ctx_create(const int32_t *devices, int32_t n_dev, uint64_t flags, ph
     else ords.assign(devices, devices + n_dev);
     phb_ctx *ctx = new phb_ctx();
     ctx->flags = flags;
+    ctx->is_aa = (flags & PHB_FLAG_AMINO_ACID) != 0;
+    if (ctx->is_aa && ords.size() != 1) { // the 20-state engines drive one device
+        delete ctx;
+        return PHB_ERR_INVALID_ARGUMENT;
+    }
     memset(&ctx->stats, 0, sizeof ctx->stats);
     memset(&ctx->model, 0, sizeof ctx->model);
     for (int o : ords) {
@@ -1537,6 +1558,7 @@ void phb_ctx_destroy(phb_ctx *ctx)
                           &d.sw_stream, &d.sw_gstack, &d.sw_err, &d.sw_opoff, &d.dn_ops, &d.dn_descs, &d.dn_blocks, &d.dn_stream, &d.dn_opoff, &d.dn_gstack, &d.sw_ops, &d.uops, &d.ukids, &d.lnP, &d.jbest,
                           &d.nni_upper, &d.nni_uexps, &d.nni_jobs, &d.nni_rows, &d.nni_exps, &d.nni_partials, &d.nni_totals, &d.nni_moves, &d.nni_steps, &d.nni_need};
         for (DevBuf *b : bufs) b->release();
+        if (ctx->is_aa) aa_release(ctx);
         for (auto &ep : d.ev_pool) {
             cudaEventDestroy(ep.a);
             cudaEventDestroy(ep.b);
@@ -1709,6 +1731,7 @@ int32_t phb_set_alignment(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns, cons
     if (n_rows < 0 || n_patterns < 0 || (layout != PHB_LAYOUT_PATTERN_MAJOR && layout != PHB_LAYOUT_ROW_MAJOR) ||
         (!bytes && n_rows > 0 && n_patterns > 0))
         return ctx->fail(PHB_ERR_INVALID_ARGUMENT, "set_alignment: bad arguments");
+    if (ctx->is_aa) return aa_set_alignment(ctx, n_rows, n_patterns, bytes, layout, multiplicity);
     ctx->have_aln = false;
     int rc = shard_and_alloc(ctx, n_rows, n_patterns);
     if (rc) return rc;
@@ -1755,6 +1778,7 @@ static int32_t compress_impl(phb_ctx *ctx, int32_t n_rows, int64_t width, const 
                              int64_t *n_patterns, uint64_t *site_to_pattern, uint64_t *multiplicity)
 {
     if (!ctx || !n_patterns) return PHB_ERR_INVALID_ARGUMENT;
+    if (ctx->is_aa) return ctx->fail(PHB_ERR_STATE, "compress_columns: not available in a 20-state (PHB_FLAG_AMINO_ACID) context");
     if (n_rows < 0 || width < 0 || width > 0x7fffffff || (!bytes && !row_ptrs && n_rows > 0 && width > 0))
         return ctx->fail(PHB_ERR_INVALID_ARGUMENT, "compress_columns: bad arguments");
     if (!bytes && row_ptrs)
@@ -1973,6 +1997,7 @@ int32_t phb_set_model(phb_ctx *ctx, const double *lambda, const double *V, const
         return ctx->fail(PHB_ERR_INVALID_ARGUMENT, "set_model: null pointer");
     if (n_cat < 1 || n_cat > MAX_CAT)
         return ctx->fail(PHB_ERR_INVALID_MODEL_PARAMETER, "set_model: n_cat must be in [1, %d]", MAX_CAT);
+    if (ctx->is_aa) return aa_set_model(ctx, lambda, V, pi, sqrt_pi, inv_sqrt_pi, n_cat, rates, weights);
     ModelDev M;
     memset(&M, 0, sizeof M);
     memcpy(M.lambda, lambda, sizeof M.lambda);
@@ -2041,13 +2066,14 @@ int32_t phb_set_tree(phb_ctx *ctx, int32_t n_nodes, const int32_t *postorder, co
             seen[v] = 1;
         }
     }
+    if (ctx->is_aa) return aa_upload_tree(ctx);
     return upload_tree(ctx);
 }
 
 int32_t phb_log_likelihood(phb_ctx *ctx, double *total, double *per_pattern)
 {
     if (!ctx || !total) return PHB_ERR_INVALID_ARGUMENT;
-    int rc = evaluate(ctx, false, false, total);
+    int rc = ctx->is_aa ? aa_evaluate(ctx, false, nullptr, nullptr, total) : evaluate(ctx, false, false, total);
     if (rc) return rc;
     if (per_pattern) return phb_get_per_pattern(ctx, per_pattern);
     return PHB_OK;
@@ -2057,6 +2083,7 @@ int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns
                                 const uint64_t *multiplicity, double *total, double *per_pattern)
 {
     if (!ctx || !total) return PHB_ERR_INVALID_ARGUMENT;
+    if (ctx->is_aa) return ctx->fail(PHB_ERR_STATE, "log_likelihood_host: not available in a 20-state (PHB_FLAG_AMINO_ACID) context");
     if (n_rows < 0 || n_patterns < 0 || (layout != PHB_LAYOUT_PATTERN_MAJOR && layout != PHB_LAYOUT_ROW_MAJOR) ||
         (!bytes && n_rows > 0 && n_patterns > 0))
         return ctx->fail(PHB_ERR_INVALID_ARGUMENT, "log_likelihood_host: bad arguments");
@@ -2208,6 +2235,7 @@ int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns
 int32_t phb_get_per_pattern(phb_ctx *ctx, double *per_pattern)
 {
     if (!ctx || !per_pattern) return PHB_ERR_INVALID_ARGUMENT;
+    if (ctx->is_aa) return aa_get_per_pattern(ctx, per_pattern);
     for (Device &d : ctx->devs) {
         if (d.P == 0) continue;
         CU(cudaSetDevice(d.ordinal));
@@ -2223,6 +2251,7 @@ int32_t phb_get_per_pattern(phb_ctx *ctx, double *per_pattern)
 int32_t phb_marginal_asr(phb_ctx *ctx, uint8_t *states, double *posteriors, double *total)
 {
     if (!ctx || !total || !states) return PHB_ERR_INVALID_ARGUMENT;
+    if (ctx->is_aa) return aa_evaluate(ctx, true, states, posteriors, total);
     // the outputs leave tile by tile on the copy stream while the next tile is computed (pinned host
     // buffers get the full PCIe rate; pageable ones work, staged by the driver)
     ctx->asr_states_out = states;
@@ -2236,6 +2265,7 @@ int32_t phb_marginal_asr(phb_ctx *ctx, uint8_t *states, double *posteriors, doub
 int32_t phb_joint_asr(phb_ctx *ctx, uint8_t *states, double *total)
 {
     if (!ctx || !total || !states) return PHB_ERR_INVALID_ARGUMENT;
+    if (ctx->is_aa) return ctx->fail(PHB_ERR_STATE, "joint_asr: not available in a 20-state (PHB_FLAG_AMINO_ACID) context");
     ctx->asr_states_out = states;
     ctx->asr_post_out = nullptr;
     int rc = evaluate(ctx, true, false, total, true);
@@ -2246,6 +2276,7 @@ int32_t phb_joint_asr(phb_ctx *ctx, uint8_t *states, double *total)
 int32_t phb_score_nni(phb_ctx *ctx, int32_t n_moves, const int32_t *node_id, const uint8_t *left_ch, double *totals)
 {
     if (!ctx || n_moves < 0 || (n_moves > 0 && (!node_id || !left_ch || !totals))) return PHB_ERR_INVALID_ARGUMENT;
+    if (ctx->is_aa) return ctx->fail(PHB_ERR_STATE, "score_nni: not available in a 20-state (PHB_FLAG_AMINO_ACID) context");
     if (!ctx->tree.valid) return ctx->fail(PHB_ERR_STATE, "score_nni: set_tree first");
     if (!ctx->have_aln || !ctx->have_model)
         return ctx->fail(PHB_ERR_STATE, "score_nni: set_alignment and set_model first");
@@ -2313,6 +2344,7 @@ int32_t phb_score_nni(phb_ctx *ctx, int32_t n_moves, const int32_t *node_id, con
 int32_t phb_score_trees(phb_ctx *ctx, int32_t n_trees, const phb_tree_desc *trees, double *totals)
 {
     if (!ctx || n_trees < 0 || (n_trees > 0 && (!trees || !totals))) return PHB_ERR_INVALID_ARGUMENT;
+    if (ctx->is_aa) return ctx->fail(PHB_ERR_STATE, "score_trees: not available in a 20-state (PHB_FLAG_AMINO_ACID) context");
     if (!ctx->have_aln || !ctx->have_model) return ctx->fail(PHB_ERR_STATE, "score_trees: set_alignment and set_model first");
     const bool had_tree = ctx->tree.valid;
     for (Device &d : ctx->devs) {
@@ -2342,6 +2374,7 @@ int32_t phb_score_trees(phb_ctx *ctx, int32_t n_trees, const phb_tree_desc *tree
 int32_t phb_simulate_alignment(phb_ctx *ctx, int64_t n_patterns, int64_t global_offset, uint64_t seed)
 {
     if (!ctx || n_patterns < 0) return PHB_ERR_INVALID_ARGUMENT;
+    if (ctx->is_aa) return ctx->fail(PHB_ERR_STATE, "simulate_alignment: not available in a 20-state (PHB_FLAG_AMINO_ACID) context");
     if (!ctx->have_model || !ctx->tree.valid) return ctx->fail(PHB_ERR_STATE, "simulate: set_model and set_tree first");
     TreeSched &T = ctx->tree;
     const int n_leaves = (int)T.leaf_nodes.size();
@@ -2417,6 +2450,7 @@ int32_t phb_simulate_alignment(phb_ctx *ctx, int64_t n_patterns, int64_t global_
 int32_t phb_get_alignment(phb_ctx *ctx, uint8_t *bytes, int32_t layout, int64_t first_pattern, int64_t n_patterns)
 {
     if (!ctx || !bytes || first_pattern < 0 || n_patterns < 0) return PHB_ERR_INVALID_ARGUMENT;
+    if (ctx->is_aa) return ctx->fail(PHB_ERR_STATE, "get_alignment: not available in a 20-state (PHB_FLAG_AMINO_ACID) context");
     if (!ctx->have_aln) return ctx->fail(PHB_ERR_STATE, "get_alignment: no alignment set");
     if (first_pattern + n_patterns > ctx->n_patterns || (layout != 0 && layout != 1))
         return ctx->fail(PHB_ERR_INVALID_ARGUMENT, "get_alignment: range or layout out of bounds");
@@ -2491,6 +2525,7 @@ int32_t phb_transition_matrices(phb_ctx *ctx, int32_t n_t, const double *t, doub
     if (!ctx || n_t < 0 || (n_t > 0 && (!t || !out))) return ctx ? ctx->fail(PHB_ERR_INVALID_ARGUMENT, "transition_matrices: null/negative argument") : PHB_ERR_INVALID_ARGUMENT;
     if (!ctx->have_model) return ctx->fail(PHB_ERR_STATE, "set_model must precede transition_matrices");
     if (n_t == 0) return PHB_OK;
+    if (ctx->is_aa) return aa_transition_matrices(ctx, n_t, t, out);
     Device &d = ctx->devs[0];
     const ModelDev &M = ctx->model_lit;
     CU(cudaSetDevice(d.ordinal));
@@ -2536,6 +2571,7 @@ int32_t phb_transition_matrices_noalloc(phb_ctx *ctx, int32_t n_t, const double 
 {
     if (!ctx || n_t < 0 || (n_t > 0 && (!t || !out)))
         return ctx ? ctx->fail(PHB_ERR_INVALID_ARGUMENT, "transition_matrices_noalloc: null/negative argument") : PHB_ERR_INVALID_ARGUMENT;
+    if (ctx->is_aa) return ctx->fail(PHB_ERR_STATE, "transition_matrices_noalloc: not available in a 20-state (PHB_FLAG_AMINO_ACID) context");
     if (!ctx->have_model) return ctx->fail(PHB_ERR_STATE, "set_model must precede transition_matrices_noalloc");
     if (n_t == 0) return PHB_OK;
     Device &d = ctx->devs[0];

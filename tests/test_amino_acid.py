@@ -1,0 +1,219 @@
+"""the 20-state AminoAcid instance of the engines (PHB_FLAG_AMINO_ACID contexts, csrc/aa.cuh).
+
+CPU part: the oracle's 20-state build (oracle/libphylo_oracle_aa.so: the same C restatement with -DNS=20) is pinned on
+the reference's own AminoAcid fixtures (src/tree/likelihood/integration_test.rs:75-109, 612-615), on brute-force
+enumeration and on an independent numpy pruning + scipy expm; the product sources run on the emulation build.
+GPU part (`-m gpu`): the real sm_100a library through its C ABI against that oracle, at BASELINE.json's bars
+(total lnL 1e-9 relative, per-pattern 1e-8 absolute, ASR states bit-exact, posteriors 1e-9)."""
+import numpy as np
+import pytest
+
+import oracle
+from oracle import AaModel, amino_acid_profile, workloads
+from phylo_rs_b200 import capi
+
+import _cases
+
+AA = capi.FLAG_AMINO_ACID
+CANONICAL = b"ACDEFGHIKLMNPQRSTVWY"
+
+
+# ---- oracle, pinned on the reference's fixtures ------------------------------------------------------------------
+def test_oracle_canonical_and_n_states():
+    """integration_test.rs:75-83 (char_of / index_of round trip over CANONICAL), :612-615 (N_STATES == 20)."""
+    assert oracle.lib_aa().orc_n_states() == 20 and len(CANONICAL) == 20
+    for i, c in enumerate(CANONICAL):
+        p = amino_acid_profile(c)
+        assert p[i] == 1.0 and p.sum() == 1.0
+
+
+def test_oracle_ambiguity_profiles():
+    """integration_test.rs:86-109: B -> 0.5 at indices 3 and 11, Z -> 4 and 14, J -> 8 and 9, X all ones; alphabet.rs:113-114:
+    the gap as X, anything else None."""
+    for c, (a, b) in ((ord("B"), (3, 11)), (ord("Z"), (4, 14)), (ord("J"), (8, 9))):
+        p = amino_acid_profile(c)
+        assert abs(p[a] - 0.5) < 1e-10 and abs(p[b] - 0.5) < 1e-10 and np.count_nonzero(p) == 2
+    assert np.all(amino_acid_profile(ord("X")) == 1.0) and np.all(amino_acid_profile(ord("-")) == 1.0)
+    for c in b"OU*acgt?.":
+        assert amino_acid_profile(c) is None
+
+
+def test_oracle_rate_matrix_and_transition():
+    scipy_linalg = pytest.importorskip("scipy.linalg")
+    m = workloads.make_aa_model("aa")
+    pi = m.pi
+    assert abs(pi.sum() - 1) < 1e-14 and np.all(m.eigenvalues <= 1e-12) and np.sum(np.abs(m.eigenvalues) < 1e-10) == 1
+    V = m.eigenvectors
+    assert np.max(np.abs(V.T @ V - np.eye(20))) < 1e-12
+    # rebuild Q the way RateMatrix::new does (rate_matrix.rs:34-97) and compare P(t) with expm(Q t)
+    rng = np.random.default_rng(0xAA20)
+    pi0 = rng.dirichlet(np.full(20, 8.0))
+    w = rng.gamma(1.5, 1.0, (20, 20)) + 0.05
+    w = (w + w.T) / 2
+    np.fill_diagonal(w, 0.0)
+    q = w * pi0[None, :]
+    np.fill_diagonal(q, -q.sum(axis=1))
+    q /= -(pi0 * np.diag(q)).sum()
+    for t in (0.0, 1e-6, 0.05, 0.7, 5.0):
+        P = m.transition(t)
+        assert np.max(np.abs(P - scipy_linalg.expm(q * t))) < 1e-12
+        assert np.max(np.abs(P.sum(axis=1) - 1)) < 1e-12
+    assert np.array_equal(m.transition(0.0), np.eye(20))  # rate_matrix.rs:115-117
+    with pytest.raises(oracle.OracleError):
+        AaModel([0.25] * 4, np.ones((4, 4)))  # AlphabetMismatch, gtr.rs:39-41
+
+
+def _numpy_site_lnl(ft, m, pat, rate=1.0):
+    clv = [None] * ft["n_nodes"]
+    for v in ft["postorder"]:
+        ks = ft["children"][ft["child_off"][v]:ft["child_off"][v + 1]]
+        if len(ks) == 0:
+            clv[v] = amino_acid_profile(pat[ft["leaf_row"][v]])
+        else:
+            x = np.ones(20)
+            for k in ks:
+                x = x * (m.transition(rate * ft["blen"][k]) @ clv[k])
+            clv[v] = x
+    with np.errstate(divide="ignore"):
+        return np.log(m.pi @ clv[ft["root"]])
+
+
+def test_oracle_lnl_against_bruteforce_and_numpy():
+    c = workloads.make_case(5, 12, model="aa", seed=4, ambiguity=0.25)
+    tot, per = oracle.log_likelihood_flat(c.ft, c.model, c.patterns, c.mult)
+    for i in range(len(per)):
+        bf = oracle.bruteforce_site_likelihood(c.ft, c.model, c.patterns[i])  # 20^4 internal-state assignments
+        assert abs(per[i] - np.log(bf)) < 1e-11
+        assert abs(per[i] - _numpy_site_lnl(c.ft, c.model, c.patterns[i])) < 1e-11
+    assert abs(tot - per.sum()) < 1e-10
+    c = workloads.make_case(40, 30, model="aa_i_g4", seed=9, ambiguity=0.1)
+    tot, per = oracle.log_likelihood_flat(c.ft, c.model, c.patterns, c.mult)
+    m = c.model
+    for i in range(0, 30, 7):
+        cats = [np.log(w) + _numpy_site_lnl(c.ft, m, c.patterns[i], r) for r, w in zip(m.rates, m.weights)]
+        assert abs(per[i] - np.logaddexp.reduce(cats)) < 1e-10
+
+
+def test_oracle_marginal_posteriors_sum_to_one():
+    c = workloads.make_case(12, 60, model="aa_g4", seed=2, ambiguity=0.1)
+    tot, per, st, post = oracle.marginal_asr_flat(c.ft, c.model, c.patterns, c.mult, want_posteriors=True)
+    assert np.allclose(post.sum(axis=2), 1.0, atol=1e-12) and st.max() < 20
+    assert np.array_equal(post.shape, (c.ft["n_nodes"], 60, 20))
+    # a leaf with a canonical letter is reconstructed as that letter
+    for v in range(c.ft["n_nodes"]):
+        r = c.ft["leaf_row"][v]
+        if r >= 0 and c.ft["child_off"][v + 1] == c.ft["child_off"][v]:
+            for p in range(60):
+                b = c.patterns[p, r]
+                if b in CANONICAL:
+                    assert st[v, p] == CANONICAL.index(b)
+
+
+# ---- product sources: emulation build (CPU) and the real library (GPU) -----------------------------------------------
+def _parity(lib, n_taxa, n_sites, model, seed, ambiguity=0.05, budget=None, want_post=True):
+    case = workloads.make_case(n_taxa, n_sites, model=model, seed=seed, ambiguity=ambiguity)
+    _cases.check_lnl(lib, case, flags=AA, budget=budget)
+    assert _cases.check_asr(lib, case, want_post=want_post, flags=AA, budget=budget) == 0
+    return case
+
+
+def _star_and_polytomy(lib):
+    """any arity (likelihood.rs:113 iterates all children): a root with 5 children, each a 30-leaf caterpillar, and a
+    unifurcation chain"""
+    from oracle import parse_newick
+
+    rng = np.random.default_rng(5)
+    names, parts = [], []
+    for j in range(5):
+        s = f"(a{j}_0:0.3,a{j}_1:0.2)"
+        names += [f"a{j}_0", f"a{j}_1"]
+        for i in range(2, 30):
+            names.append(f"a{j}_{i}")
+            s = f"({s}:0.4,a{j}_{i}:0.25)"
+        parts.append(f"(({s}:0.1):0.05):0.2")  # two unifurcations above each caterpillar
+    tree = parse_newick("(" + ",".join(parts) + ");")
+    ft = workloads.flatten_fast(tree, names)
+    pats = np.frombuffer(workloads.AA_LETTERS + b"BZJX-", np.uint8)[rng.integers(25, size=(64, len(names)))]
+    case = workloads.Case(tree, ft, workloads.make_aa_model("aa_g4"), "aa_g4", np.ascontiguousarray(pats), np.ones(64, np.uint64), names)
+    _cases.check_lnl(lib, case, flags=AA)
+    assert _cases.check_asr(lib, case, want_post=True, flags=AA) == 0
+
+
+def _abi_behaviour(lib):
+    case = workloads.make_case(6, 20, model="aa_g4", seed=3, ambiguity=0.2)
+    m, ft = case.model, case.ft
+    with capi.Context(flags=AA, library=lib) as ctx:
+        with pytest.raises(capi.PhbError) as ei:
+            ctx.log_likelihood()
+        assert ei.value.variant == "State"
+        with pytest.raises(ValueError):
+            ctx.set_model(np.zeros(4), np.eye(4), [0.25] * 4, [0.5] * 4, [2.0] * 4, [1.0], [1.0])
+        workloads.load_into(ctx, case)
+        tot = ctx.log_likelihood()
+        # multiplicities weight the per-pattern values; row-major input is the same alignment
+        mult = np.arange(1, 21, dtype=np.uint64)
+        ctx.set_alignment(np.ascontiguousarray(case.patterns.T), multiplicity=mult, layout=capi.LAYOUT_ROW_MAJOR)
+        tot_m, per = ctx.log_likelihood(per_pattern=True)
+        assert abs(tot_m - float((per * mult).sum())) <= 1e-12 * abs(tot_m)
+        ctx.set_alignment(case.patterns)
+        assert ctx.log_likelihood() == tot
+        # P(t) at 20 states, exact identity at t == 0
+        Pm = ctx.transition_matrices(np.array([0.0, 0.3]), len(m.rates))
+        assert np.array_equal(Pm[0, 0], np.eye(20)) and Pm.shape == (2, len(m.rates), 20, 20)
+        for c in range(len(m.rates)):
+            assert np.max(np.abs(Pm[1, c] - m.category_transition(c, 0.3))) <= 1e-13
+        # entry points without a 20-state instance say so
+        for call in (lambda: ctx.joint_asr(), lambda: ctx.score_nni([0], [0]), lambda: ctx.transition_matrices_noalloc([0.1], 4)):
+            with pytest.raises(capi.PhbError) as ei:
+                call()
+            assert ei.value.variant == "State" and "20-state" in str(ei.value)
+        # a nucleotide-only byte in a LEAF row: AlphabetMismatch at evaluation (likelihood.rs:105-107)
+        bad = case.patterns.copy()
+        bad[7, 2] = ord("O")
+        ctx.set_alignment(bad)
+        with pytest.raises(capi.PhbError) as ei:
+            ctx.log_likelihood()
+        assert ei.value.variant == "AlphabetMismatch"
+        # a leaf without a row: InvalidAlignment (likelihood.rs:99-103)
+        ctx.set_alignment(case.patterns)
+        lr = ft["leaf_row"].copy()
+        lr[np.where(lr >= 0)[0][0]] = -1
+        ctx.set_tree(ft["postorder"], ft["child_off"], ft["children"], ft["blen"], lr, ft["root"])
+        with pytest.raises(capi.PhbError) as ei:
+            ctx.marginal_asr()
+        assert ei.value.variant == "InvalidAlignment"
+    with pytest.raises(capi.PhbError):
+        capi.Context(devices=[0, 0], flags=AA, library=lib)  # one device per 20-state context
+
+
+@pytest.mark.parametrize("model", workloads.AA_MODELS)
+def test_emu_lnl_and_asr(emu_lib, model):
+    _parity(emu_lib, 14, 150, model, seed=11)
+
+
+def test_emu_tiling_polytomy_abi(emu_lib):
+    _parity(emu_lib, 9, 700, "aa_g4", seed=12, budget=9 * 4 * 164 * 256)  # 3 tiles of 256 patterns
+    _star_and_polytomy(emu_lib)
+    _abi_behaviour(emu_lib)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("model", workloads.AA_MODELS)
+def test_gpu_lnl_and_asr(gpu_lib, model):
+    _parity(gpu_lib, 48, 1200, model, seed=21)
+
+
+@pytest.mark.gpu
+def test_gpu_tiling_polytomy_abi(gpu_lib):
+    _parity(gpu_lib, 9, 700, "aa_g4", seed=12, budget=9 * 4 * 164 * 256)
+    _star_and_polytomy(gpu_lib)
+    _abi_behaviour(gpu_lib)
+
+
+@pytest.mark.gpu
+def test_gpu_deep_tree_scaling(gpu_lib):
+    """600 taxa: per-site |lnL| in the thousands, CLVs leave the f64 range without the power-of-two rescaling."""
+    case = workloads.make_case(600, 96, model="aa_i_g4", seed=23, ambiguity=0.02)
+    tot, per, _ = _cases.check_lnl(gpu_lib, case, flags=AA)
+    assert per.min() < -800  # exp(-800) is below the smallest f64
+    assert _cases.check_asr(gpu_lib, case, flags=AA) == 0
