@@ -32,6 +32,8 @@ pub const PHB_FLAG_TIMING: u64 = 1 << 1;
 pub const PHB_FLAG_LEVEL_KERNELS: u64 = 1 << 2;
 pub const PHB_FLAG_NNI_FULL: u64 = 1 << 3;
 pub const PHB_FLAG_NNI_WALK: u64 = 1 << 4;
+/// 20-state context: the AminoAcid alphabet (`src/alphabet.rs:66-116`) instead of Nucleotide.
+pub const PHB_FLAG_AMINO_ACID: u64 = 1 << 5;
 
 // ---- alignment layouts ----
 pub const PHB_LAYOUT_PATTERN_MAJOR: i32 = 0;
