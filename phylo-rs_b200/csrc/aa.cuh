@@ -152,9 +152,17 @@ __device__ __forceinline__ double aa_tip_row(const double *Ps, int i, uint32_t c
 }
 
 // ---- one level of prune_pattern_category (likelihood.rs:110-131), any arity ---------------------------------------
-// grid: x = pattern blocks of the tile, y = op of the level, z = category.  values = prod over children of
-// P_child * profile_child; the product is rescaled ONCE per node, like the reference's single Profile::scale() per
-// node, so a node with very many children leaves the f64 range where the reference does.
+// grid: x = blocks of AA_R * AA_THREADS patterns of the tile, y = op of the level, z = category.  values = prod over
+// children of P_child * profile_child; the product is rescaled ONCE per node, like the reference's single
+// Profile::scale() per node, so a node with very many children leaves the f64 range where the reference does
+// (DESIGN.md §2.1).  A thread owns AA_R = 2 patterns (one block-width apart, so that both streams stay coalesced): every
+// P(t) entry read from shared memory feeds two DFMA instead of one -- with one pattern per thread the mat-vec issues one
+// broadcast LDS.128 per two DFMA and the shared-memory pipe, not the FP64 pipe, bounds the kernel (tools/ubench.cu:
+// 2.0 clocks per broadcast LDS.128 per SM against 2.2 clocks per DFMA per SM sub-partition).
+#ifndef PHB_AA_R
+#define PHB_AA_R 1
+#endif
+constexpr int AA_R = PHB_AA_R;
 __global__ void __launch_bounds__(AA_THREADS)
 aa_clv_kernel(const GenOp *__restrict__ ops, const GenChild *__restrict__ kids, int n_cat, const double *__restrict__ Pmat,
               double *__restrict__ clv, int *__restrict__ exps, size_t slot_stride, size_t tile_pad, int tile_len,
@@ -163,44 +171,69 @@ aa_clv_kernel(const GenOp *__restrict__ ops, const GenChild *__restrict__ kids, 
     __shared__ double Ps[AA_NS * AA_NS];
     const GenOp op = ops[blockIdx.y];
     const int cat = blockIdx.z;
-    const int64_t site = (int64_t)blockIdx.x * AA_THREADS + threadIdx.x;
-    const bool active = site < tile_len;
-    double acc[AA_NS];
+    int64_t site[AA_R];
+    bool active[AA_R];
 #pragma unroll
-    for (int i = 0; i < AA_NS; ++i) acc[i] = 1.0;
-    int ex = 0;
+    for (int r = 0; r < AA_R; ++r) {
+        site[r] = ((int64_t)blockIdx.x * AA_R + r) * AA_THREADS + threadIdx.x;
+        active[r] = site[r] < tile_len;
+        if (!active[r]) site[r] = 0; // reads stay in range; nothing is written for it
+    }
+    double acc[AA_R][AA_NS];
+#pragma unroll
+    for (int r = 0; r < AA_R; ++r)
+#pragma unroll
+        for (int i = 0; i < AA_NS; ++i) acc[r][i] = 1.0;
+    int ex[AA_R];
+#pragma unroll
+    for (int r = 0; r < AA_R; ++r) ex[r] = 0;
     for (int k = op.child_begin; k < op.child_end; ++k) {
         const GenChild ch = kids[k];
         __syncthreads(); // the previous child's matrix is no longer read
         const double *src = Pmat + ((size_t)ch.edge * n_cat + cat) * (AA_NS * AA_NS);
         for (int idx = threadIdx.x; idx < AA_NS * AA_NS; idx += AA_THREADS) Ps[idx] = src[idx];
         __syncthreads();
-        if (!active) continue;
         if (ch.is_tip) {
-            const uint32_t code = tips[(int64_t)ch.src * P_pad + tile_off + site];
 #pragma unroll
-            for (int i = 0; i < AA_NS; ++i) acc[i] *= aa_tip_row(Ps, i, code);
+            for (int r = 0; r < AA_R; ++r) {
+                const uint32_t code = tips[(int64_t)ch.src * P_pad + tile_off + site[r]];
+#pragma unroll
+                for (int i = 0; i < AA_NS; ++i) acc[r][i] *= aa_tip_row(Ps, i, code);
+            }
         } else {
-            const double *x_src = clv + (size_t)ch.src * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
-            double x[AA_NS];
+            const double *x_src = clv + (size_t)ch.src * slot_stride + (size_t)cat * AA_NS * tile_pad;
+            double x[AA_R][AA_NS];
 #pragma unroll
-            for (int j = 0; j < AA_NS; ++j) x[j] = x_src[(size_t)j * tile_pad];
-            ex += exps[((size_t)ch.src * n_cat + cat) * tile_pad + site];
+            for (int r = 0; r < AA_R; ++r) {
+#pragma unroll
+                for (int j = 0; j < AA_NS; ++j) x[r][j] = x_src[(size_t)j * tile_pad + site[r]];
+                ex[r] += exps[((size_t)ch.src * n_cat + cat) * tile_pad + site[r]];
+            }
 #pragma unroll
             for (int i = 0; i < AA_NS; ++i) {
-                double y = Ps[i * AA_NS] * x[0];
+                double y[AA_R];
 #pragma unroll
-                for (int j = 1; j < AA_NS; ++j) y += Ps[i * AA_NS + j] * x[j];
-                acc[i] *= y;
+                for (int r = 0; r < AA_R; ++r) y[r] = Ps[i * AA_NS] * x[r][0];
+#pragma unroll
+                for (int j = 1; j < AA_NS; ++j) {
+                    const double pij = Ps[i * AA_NS + j];
+#pragma unroll
+                    for (int r = 0; r < AA_R; ++r) y[r] += pij * x[r][j];
+                }
+#pragma unroll
+                for (int r = 0; r < AA_R; ++r) acc[r][i] *= y[r];
             }
         }
     }
-    if (!active) return;
-    ex += aa_normalize(acc);
-    double *dst = clv + (size_t)op.out_slot * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
 #pragma unroll
-    for (int i = 0; i < AA_NS; ++i) dst[(size_t)i * tile_pad] = acc[i];
-    exps[((size_t)op.out_slot * n_cat + cat) * tile_pad + site] = ex;
+    for (int r = 0; r < AA_R; ++r) {
+        if (!active[r]) continue;
+        ex[r] += aa_normalize(acc[r]);
+        double *dst = clv + (size_t)op.out_slot * slot_stride + (size_t)cat * AA_NS * tile_pad + site[r];
+#pragma unroll
+        for (int i = 0; i < AA_NS; ++i) dst[(size_t)i * tile_pad] = acc[r][i];
+        exps[((size_t)op.out_slot * n_cat + cat) * tile_pad + site[r]] = ex[r];
+    }
 }
 
 // the root's vector for one (pattern, category): its CLV, or its tip profile when the tree is a single leaf
@@ -278,6 +311,9 @@ aa_root_kernel(int root_slot, int root_row, const AaModelDev *__restrict__ M, co
 //   not finite (:351-362); mixed /= its sum when > 0; state = LAST maximal index (Iterator::max_by, :385-390).
 // The posterior of an internal node overwrites its up-pass CLV in place (its children read it one depth further down;
 // nobody reads the up-pass values again); a leaf's goes nowhere but into the mixture.
+// A thread owns AA_R patterns, as in the up pass.  A leaf showing a canonical letter has a one-hot up vector, so its
+// posterior is that letter whenever the parent's message gives it any mass: only msg[letter] is computed (20 DFMA
+// instead of 400) -- identical values, since the other 19 products are exact zeros in the reference too.
 __global__ void __launch_bounds__(AA_THREADS)
 aa_down_kernel(const AaDown *__restrict__ nodes, const AaModelDev *__restrict__ M, const double *__restrict__ Pmat,
                double *__restrict__ clv, size_t slot_stride, size_t tile_pad, int tile_len, const uint8_t *__restrict__ tips,
@@ -287,13 +323,21 @@ aa_down_kernel(const AaDown *__restrict__ nodes, const AaModelDev *__restrict__ 
     __shared__ double Ps[AA_NS * AA_NS];
     const AaDown nd = nodes[blockIdx.y];
     const int n_cat = M->n_cat;
-    const int64_t site = (int64_t)blockIdx.x * AA_THREADS + threadIdx.x;
-    const bool active = site < tile_len;
-    double mixed[AA_NS];
+    int64_t site[AA_R];
+    bool active[AA_R];
+    double lse[AA_R];
+    uint32_t code[AA_R];
+    double mixed[AA_R][AA_NS];
 #pragma unroll
-    for (int i = 0; i < AA_NS; ++i) mixed[i] = 0.0;
-    const double lse = active ? cat_ll[(size_t)n_cat * tile_pad + site] : 0.0;
-    const uint32_t code = (active && nd.slot < 0) ? tips[(int64_t)nd.row * P_pad + tile_off + site] : 0u;
+    for (int r = 0; r < AA_R; ++r) {
+        site[r] = ((int64_t)blockIdx.x * AA_R + r) * AA_THREADS + threadIdx.x;
+        active[r] = site[r] < tile_len;
+        if (!active[r]) site[r] = 0;
+        lse[r] = cat_ll[(size_t)n_cat * tile_pad + site[r]];
+        code[r] = nd.slot < 0 ? tips[(int64_t)nd.row * P_pad + tile_off + site[r]] : 0u;
+#pragma unroll
+        for (int i = 0; i < AA_NS; ++i) mixed[r][i] = 0.0;
+    }
     for (int c = 0; c < n_cat; ++c) {
         if (nd.parent_slot >= 0) {
             __syncthreads();
@@ -301,69 +345,104 @@ aa_down_kernel(const AaDown *__restrict__ nodes, const AaModelDev *__restrict__ 
             for (int idx = threadIdx.x; idx < AA_NS * AA_NS; idx += AA_THREADS) Ps[idx] = src[idx];
             __syncthreads();
         }
-        if (!active) continue;
-        double post[AA_NS];
+        double mix[AA_R];
+#pragma unroll
+        for (int r = 0; r < AA_R; ++r)
+            mix[r] = isfinite(lse[r]) ? exp(cat_ll[(size_t)c * tile_pad + site[r]] - lse[r]) : 1.0 / (double)n_cat;
+        const double *pp = nd.parent_slot >= 0 ? clv + (size_t)nd.parent_slot * slot_stride + (size_t)c * AA_NS * tile_pad : nullptr;
+        if (nd.slot < 0 && nd.parent_slot >= 0 && code[0] < (uint32_t)AA_NS && (AA_R == 1 || code[AA_R - 1] < (uint32_t)AA_NS)) {
+            // canonical leaf (all of the thread's patterns): post = one-hot when msg[letter] > 0, all zeros otherwise
+#pragma unroll
+            for (int r = 0; r < AA_R; ++r) {
+                double m = Ps[code[r]] * pp[site[r]];
+#pragma unroll
+                for (int i = 1; i < AA_NS; ++i) m += Ps[i * AA_NS + code[r]] * pp[(size_t)i * tile_pad + site[r]];
+                const double v = 1.0 * m; // up (.) msg, then / sum: m / m
+                const double one = v > 0.0 ? v / v : v;
+#pragma unroll
+                for (int i = 0; i < AA_NS; ++i) mixed[r][i] += (i == (int)code[r]) ? mix[r] * one : mix[r] * 0.0;
+            }
+        } else {
+        double post[AA_R][AA_NS];
         if (nd.parent_slot < 0) {
 #pragma unroll
-            for (int i = 0; i < AA_NS; ++i) post[i] = M->pi[i];
-        } else {
-            const double *pp = clv + (size_t)nd.parent_slot * slot_stride + (size_t)c * AA_NS * tile_pad + site;
-            const double p0 = pp[0];
+            for (int r = 0; r < AA_R; ++r)
 #pragma unroll
-            for (int j = 0; j < AA_NS; ++j) post[j] = Ps[j] * p0;
+                for (int i = 0; i < AA_NS; ++i) post[r][i] = M->pi[i];
+        } else {
+            double p_i[AA_R];
+#pragma unroll
+            for (int r = 0; r < AA_R; ++r) p_i[r] = pp[site[r]];
+#pragma unroll
+            for (int j = 0; j < AA_NS; ++j) {
+                const double pij = Ps[j];
+#pragma unroll
+                for (int r = 0; r < AA_R; ++r) post[r][j] = pij * p_i[r];
+            }
 #pragma unroll
             for (int i = 1; i < AA_NS; ++i) {
-                const double pi_ = pp[(size_t)i * tile_pad];
 #pragma unroll
-                for (int j = 0; j < AA_NS; ++j) post[j] += Ps[i * AA_NS + j] * pi_;
+                for (int r = 0; r < AA_R; ++r) p_i[r] = pp[(size_t)i * tile_pad + site[r]];
+#pragma unroll
+                for (int j = 0; j < AA_NS; ++j) {
+                    const double pij = Ps[i * AA_NS + j];
+#pragma unroll
+                    for (int r = 0; r < AA_R; ++r) post[r][j] += pij * p_i[r];
+                }
             }
         }
-        double *own = nd.slot >= 0 ? clv + (size_t)nd.slot * slot_stride + (size_t)c * AA_NS * tile_pad + site : nullptr;
-        if (own) {
 #pragma unroll
-            for (int i = 0; i < AA_NS; ++i) post[i] = nd.parent_slot < 0 ? post[i] * own[(size_t)i * tile_pad] : own[(size_t)i * tile_pad] * post[i];
-        } else {
-            double up[AA_NS];
-            aa_tip_vec(code, up);
+        for (int r = 0; r < AA_R; ++r) {
+            double *own = nd.slot >= 0 ? clv + (size_t)nd.slot * slot_stride + (size_t)c * AA_NS * tile_pad + site[r] : nullptr;
+            if (own) {
 #pragma unroll
-            for (int i = 0; i < AA_NS; ++i) post[i] = nd.parent_slot < 0 ? post[i] * up[i] : up[i] * post[i];
+                for (int i = 0; i < AA_NS; ++i) post[r][i] *= own[(size_t)i * tile_pad];
+            } else {
+                double up[AA_NS];
+                aa_tip_vec(code[r], up);
+#pragma unroll
+                for (int i = 0; i < AA_NS; ++i) post[r][i] *= up[i];
+            }
+            double sum = 0.0;
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) sum += post[r][i];
+            if (sum > 0.0) {
+#pragma unroll
+                for (int i = 0; i < AA_NS; ++i) post[r][i] /= sum;
+            }
+            if (own && active[r]) {
+#pragma unroll
+                for (int i = 0; i < AA_NS; ++i) own[(size_t)i * tile_pad] = post[r][i];
+            }
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) mixed[r][i] += mix[r] * post[r][i];
         }
+        } // general path
+    }
+#pragma unroll
+    for (int r = 0; r < AA_R; ++r) {
+        if (!active[r]) continue;
         double sum = 0.0;
 #pragma unroll
-        for (int i = 0; i < AA_NS; ++i) sum += post[i];
+        for (int i = 0; i < AA_NS; ++i) sum += mixed[r][i];
         if (sum > 0.0) {
 #pragma unroll
-            for (int i = 0; i < AA_NS; ++i) post[i] /= sum;
+            for (int i = 0; i < AA_NS; ++i) mixed[r][i] /= sum;
         }
-        if (own) {
+        int best = 0;
+        double best_v = mixed[r][0];
 #pragma unroll
-            for (int i = 0; i < AA_NS; ++i) own[(size_t)i * tile_pad] = post[i];
+        for (int i = 1; i < AA_NS; ++i)
+            if (mixed[r][i] >= best_v) {
+                best_v = mixed[r][i];
+                best = i;
+            }
+        states[(size_t)nd.node * tile_pad + site[r]] = (uint8_t)best;
+        if (post_out) {
+            double *o = post_out + ((size_t)nd.node * tile_len + site[r]) * AA_NS;
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) o[i] = mixed[r][i];
         }
-        const double mix = isfinite(lse) ? exp(cat_ll[(size_t)c * tile_pad + site] - lse) : 1.0 / (double)n_cat;
-#pragma unroll
-        for (int i = 0; i < AA_NS; ++i) mixed[i] += mix * post[i];
-    }
-    if (!active) return;
-    double sum = 0.0;
-#pragma unroll
-    for (int i = 0; i < AA_NS; ++i) sum += mixed[i];
-    if (sum > 0.0) {
-#pragma unroll
-        for (int i = 0; i < AA_NS; ++i) mixed[i] /= sum;
-    }
-    int best = 0;
-    double best_v = mixed[0];
-#pragma unroll
-    for (int i = 1; i < AA_NS; ++i)
-        if (mixed[i] >= best_v) {
-            best_v = mixed[i];
-            best = i;
-        }
-    states[(size_t)nd.node * tile_pad + site] = (uint8_t)best;
-    if (post_out) {
-        double *o = post_out + ((size_t)nd.node * tile_len + site) * AA_NS;
-#pragma unroll
-        for (int i = 0; i < AA_NS; ++i) o[i] = mixed[i];
     }
 }
 
