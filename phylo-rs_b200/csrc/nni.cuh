@@ -357,14 +357,16 @@ nni_reduce_kernel(const NniMove *__restrict__ moves, const double *__restrict__ 
 
 // Pre-order pass, one launch per depth.  One block = (parent, category, 512 patterns); a thread = a
 // pattern pair; both children of the (binary) parent are served from one read of the parent's upper.
-// upper / uexps are indexed by CLV slot like clv / exps.  DownOp::pad = the parent's dense node id.
+// clv / exps are indexed by the ROW the host gave a node's lower partial (DownChild::src; only the partials some
+// scored edge or some upper partial reads have one), upper / uexps by the row of its upper partial: DownChild::pad =
+// that row + 1, 0 = nobody reads the child's upper partial (a tip, a cherry, a node off every path from a scored
+// edge to the root); DownOp::parent_slot = the parent's upper row, DownOp::pad = the parent's dense node id.
 template <int MINB>
 __global__ void __launch_bounds__(CLV_THREADS, MINB)
 upper_level_kernel(const DownOp *__restrict__ ops, int n_ops, const DownChild *__restrict__ kids, int root_node, ModelDev M,
                    const double *__restrict__ Pmat, const double *__restrict__ clv, double *__restrict__ upper,
                    size_t slot_stride, size_t tile_pad, int tile_len, int blocks_per_row, const int *__restrict__ exps,
-                   int *__restrict__ uexps, const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off,
-                   const uint8_t *__restrict__ need /* per dense node: on the path from a scored edge to the root; null = all */)
+                   int *__restrict__ uexps, const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off)
 {
     const int sb = blockIdx.x % blocks_per_row;
     const int rest = blockIdx.x / blocks_per_row;
@@ -376,9 +378,7 @@ upper_level_kernel(const DownOp *__restrict__ ops, int n_ops, const DownChild *_
     const DownOp op = ops[opi];
     if (op.child_end - op.child_begin != 2) return; // binary trees only (the host checks)
     const DownChild c0 = kids[op.child_begin], c1 = kids[op.child_begin + 1];
-    // upper_v is read by the edges v -> (internal child) and by v's own children's partials: a child without an
-    // internal child of its own (a tip, a cherry) needs none
-    const bool want0 = c0.pad && (!need || need[c0.node]), want1 = c1.pad && (!need || need[c1.node]);
+    const bool want0 = c0.pad != 0, want1 = c1.pad != 0;
     if (!want0 && !want1) return;
     const int cat_model = M.cat_of_clv[cat];
     const size_t stride2 = tile_pad / 2;
@@ -425,10 +425,23 @@ upper_level_kernel(const DownOp *__restrict__ ops, int n_ops, const DownChild *_
         }
         e.x += rescale_site_local(ox[0], ox[1], ox[2], ox[3]);
         e.y += rescale_site_local(oy[0], oy[1], oy[2], oy[3]);
-        double2 *dst = reinterpret_cast<double2 *>(upper + (size_t)me.src * slot_stride + cat_off);
+        double2 *dst = reinterpret_cast<double2 *>(upper + (size_t)(me.pad - 1) * slot_stride + cat_off);
 #pragma unroll
         for (int j = 0; j < 4; ++j) dst[j * stride2] = make_double2(ox[j], oy[j]);
-        *reinterpret_cast<int2 *>(uexps + (size_t)me.src * exp_stride + exp_off) = e;
+        *reinterpret_cast<int2 *>(uexps + (size_t)(me.pad - 1) * exp_stride + exp_off) = e;
+    }
+}
+
+// Subtree exponents from the running counts the storing sweep leaves (sweep.cuh, SweepParams::exp_out):
+// exps[row] = cnt[row] - cnt[pred[row]], pred = the row holding the count before the subtree's first op (-1: zero).
+__global__ void nni_exp_rows_kernel(const int *__restrict__ cnt, const int *__restrict__ pred, int n_rows, size_t row_elems /* n_clv * tile_pad */,
+                                    int *__restrict__ exps)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= row_elems) return;
+    for (int r = 0; r < n_rows; ++r) {
+        const int pr = pred[r];
+        exps[(size_t)r * row_elems + i] = cnt[(size_t)r * row_elems + i] - (pr >= 0 ? cnt[(size_t)pr * row_elems + i] : 0);
     }
 }
 
@@ -438,7 +451,7 @@ struct NniEdgeJob {
     int32_t k1_src, k1_edge, k1_is_tip;
     int32_t s_src, s_edge, s_is_tip;
     int32_t v_edge;       // dense id of v (its edge to p)
-    int32_t p_upper_slot; // CLV slot of p, -1 = p is the root (W = pi)
+    int32_t p_upper_slot; // row of p's upper partial, -1 = p is the root (W = pi)
     int32_t out0, out1;
     int32_t pad[3];
 };

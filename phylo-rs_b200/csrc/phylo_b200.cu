@@ -244,7 +244,7 @@ struct Device {
     DevBuf tips, mult, leaf_ls, inv_mask, per_pattern, row_invalid, Pmat, blen, clv, scale, cat_ll,
         partials, total, ops, gops, gkids, dops, dkids, leaf_rows, states, posteriors, staging,
         sim_pre, sim_parent, sim_depth, sim_leafrow, sim_stack, scratch, sw_descs, sw_opoff, sw_blocks, sw_stream, sw_gstack,
-        sw_err, sw_ops, dn_ops, dn_descs, dn_blocks, dn_stream, dn_opoff, dn_gstack, uops, ukids, lnP, jbest, nni_upper, nni_uexps, nni_jobs, nni_rows, nni_exps, nni_partials, nni_totals, nni_moves, nni_steps, nni_need;
+        sw_err, sw_ops, dn_ops, dn_descs, dn_blocks, dn_stream, dn_opoff, dn_gstack, uops, ukids, lnP, jbest, nni_upper, nni_uexps, nni_jobs, nni_rows, nni_exps, nni_partials, nni_totals, nni_moves, nni_steps, nni_need, nni_cnt, nni_pred, nni_dops, nni_dkids;
     bool sweep_uploaded = false;
     bool sweep_ops_stale = false; // the guard flags of the op table changed since the last upload
     bool down_uploaded = false;   // pre-order sweep schedule (down_sweep.cuh)
@@ -300,6 +300,11 @@ struct phb_ctx {
     SweepSched sweep;      // fused-sweep op stream for (tree, n_clv)
     SweepGeom sweep_geom;
     bool sweep_guards_valid = false; // guard flags planned for the current branch lengths and rates
+    // the NNI cache pass runs a storing sweep with its own schedule (only the partials some scored edge reads are
+    // written); it is swapped into `sweep` for the duration of the pass (score_nni_paths)
+    SweepSched nni_sweep;
+    SweepGeom nni_geom;
+    bool nni_guards_valid = false;
     DownSched down;        // pre-order sweep schedule of the marginal-ASR down pass for (tree, n_clv)
     // marginal ASR: caller's output buffers, so that a finished tile's states go home while the next tile runs
     uint8_t *asr_states_out = nullptr;
@@ -412,6 +417,8 @@ int upload_tree(phb_ctx *ctx)
     }
     ctx->tree_uploaded = true;
     if (!ctx->sweep.same_topology(T.root, T.child_off, T.children, T.leaf_row, T.slot)) ctx->sweep.valid = false;
+    if (!ctx->nni_sweep.same_topology(T.root, T.child_off, T.children, T.leaf_row, T.slot)) ctx->nni_sweep.valid = false;
+    ctx->nni_guards_valid = false;
     ctx->sweep_guards_valid = false; // branch lengths may have changed: re-plan the guards (and re-check the folded cherries)
     return PHB_OK;
 }
@@ -646,7 +653,8 @@ int run_tile_joint(phb_ctx *ctx, Device &d, const ModelDev &M, int64_t tile_off,
 
 // ---- fused sweep (sweep.cuh) ---------------------------------------------------------------------
 // (Re)builds the op stream for the current tree and category count and uploads it to every device.
-int ensure_sweep(phb_ctx *ctx, const ModelDev &M, bool store)
+// keep: nodes whose own CLV the caller wants written (NNI cache pass): their cherries are not folded away
+int ensure_sweep(phb_ctx *ctx, const ModelDev &M, bool store, const std::vector<char> *keep = nullptr)
 {
     const auto t_begin = std::chrono::steady_clock::now();
     struct Trace {
@@ -668,10 +676,14 @@ int ensure_sweep(phb_ctx *ctx, const ModelDev &M, bool store)
     const bool collapse = !store && !getenv("PHB_SWEEP_NO_COLLAPSE");
     std::vector<double> gb, gbd;
     std::vector<char> no_collapse;
-    const bool replan = !S.valid || S.n_clv != M.n_clv || S.collapsed_build != collapse || !ctx->sweep_guards_valid;
+    const bool replan = keep || !S.valid || S.n_clv != M.n_clv || S.collapsed_build != collapse || !ctx->sweep_guards_valid;
     if (replan) { // per-edge shrink bounds: which cherries may be folded, where the underflow guard runs
         sweep_guard_bounds(M, T.blen, gb, gbd);
         if (collapse) sweep_no_collapse(T.child_off, T.children, gb, gbd, no_collapse);
+        if (collapse && keep) {
+            no_collapse.resize(T.n, 0);
+            for (int v = 0; v < T.n; ++v) no_collapse[v] = no_collapse[v] || (*keep)[v];
+        }
     }
     if (!S.valid || S.n_clv != M.n_clv || S.collapsed_build != collapse || (replan && collapse && no_collapse != S.built_no_collapse)) {
         for (Device &d : ctx->devs) { // the old host image may still be in flight
@@ -752,7 +764,7 @@ int launch_sweep_transition(phb_ctx *ctx, Device &d, const ModelDev &M)
 // clv_out[slot][cat][state][site - p0] with row stride tile_pad, per-category log-likelihoods to cat_ll_out.
 int launch_sweep_range(phb_ctx *ctx, Device &d, const ModelDev &M, const SweepGeom &G, int64_t p0, int64_t np,
                        size_t part_off, double *clv_out = nullptr, double *cat_ll_out = nullptr, size_t tile_pad = 0,
-                       bool blocked = false)
+                       bool blocked = false, int *exp_out = nullptr, uint32_t n_store = 0xffffffffu)
 {
     const SweepSched &S = ctx->sweep;
     const int sites_per_block = 4 * G.Q;
@@ -789,6 +801,8 @@ int launch_sweep_range(phb_ctx *ctx, Device &d, const ModelDev &M, const SweepGe
     sp.tile_pad = tile_pad;
     sp.slot_stride = blocked ? (size_t)n_blocks * M.n_clv * 4 * sites_per_block : (size_t)M.n_clv * 4 * tile_pad;
     sp.blocked = blocked ? 1 : 0;
+    sp.exp_out = exp_out;
+    sp.n_store = n_store;
     ScopedTimer tm(ctx, &d, PH_CLV);
 #ifndef PHB_HOST_EMU
     static bool attr_set[64] = {false};
@@ -1247,11 +1261,11 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
                 const int sn = other_child(p, v);
                 NniEdgeJob jb;
                 memset(&jb, 0, sizeof jb);
-                jb.k0_src = src_of(k0); jb.k0_edge = k0; jb.k0_is_tip = T.slot[k0] < 0;
-                jb.k1_src = src_of(k1); jb.k1_edge = k1; jb.k1_is_tip = T.slot[k1] < 0;
-                jb.s_src = src_of(sn); jb.s_edge = sn; jb.s_is_tip = T.slot[sn] < 0;
+                jb.k0_edge = k0; jb.k0_is_tip = T.slot[k0] < 0; // the *_src rows are filled in once the rows are known
+                jb.k1_edge = k1; jb.k1_is_tip = T.slot[k1] < 0;
+                jb.s_edge = sn; jb.s_is_tip = T.slot[sn] < 0;
                 jb.v_edge = v;
-                jb.p_upper_slot = p == T.root ? -1 : T.slot[p];
+                jb.p_upper_slot = p == T.root ? -1 : p; // dense id for now
                 jb.out0 = jb.out1 = -1;
                 job_of[v] = (int)jobs.size();
                 jobs.push_back(jb);
@@ -1273,11 +1287,101 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
     if (use_upper)
         for (int m : order)
             for (int g = T.parent[node_id[m]]; g != T.root && g >= 0 && !need_upper[g]; g = T.parent[g]) need_upper[g] = 1;
-    bool need_all = true; // every node that could carry upper partials is wanted: the kernel skips the lookup
-    for (int v = 0; v < T.n && use_upper; ++v) {
-        if (v == T.root || T.slot[v] < 0 || need_upper[v]) continue;
-        for (int k = T.child_off[v]; k < T.child_off[v + 1]; ++k)
-            if (T.slot[T.children[k]] >= 0) need_all = false;
+    // Rows.  lrow[v]: row of v's lower partial in the cache (only the partials some scored edge or some upper partial
+    // reads get one when the cache is written by the storing sweep; every internal node when the level kernels write
+    // it); urow[v]: row of v's upper partial (an internal node with an internal child, on a path from a scored edge to
+    // the root).
+    std::vector<int> lrow(T.n, -1), urow(T.n, -1);
+    int n_store = 0, n_upper = 0;
+    static const bool level_cache_env = getenv("PHB_NNI_LEVEL_CACHE") != nullptr;
+    const bool sweep_cache = use_upper && !level_cache_env && sweep_q_max(M.n_clv) >= sweep_q_step(M.n_clv) && T.n_internal < 0x7fff0000;
+    std::vector<DownOp> ndops;
+    std::vector<DownChild> ndkids;
+    if (!sweep_cache) {
+        for (int v = 0; v < T.n; ++v) lrow[v] = T.slot[v];
+        n_store = T.n_internal;
+    }
+    if (use_upper) {
+        auto want_lower = [&](int c) {
+            if (T.slot[c] >= 0 && lrow[c] < 0) lrow[c] = n_store++;
+        };
+        for (const NniEdgeJob &jb : jobs) {
+            want_lower(jb.k0_edge);
+            want_lower(jb.k1_edge);
+            want_lower(jb.s_edge);
+        }
+        for (const DownChild &dc : T.dkids)
+            if (dc.pad && need_upper[dc.node]) urow[dc.node] = n_upper++;
+        for (const DownOp &o : T.dops) { // the sibling of a child whose upper partial is wanted is read through P
+            if (o.child_end - o.child_begin != 2) continue;
+            const DownChild &c0 = T.dkids[o.child_begin], &c1 = T.dkids[o.child_begin + 1];
+            if (urow[c0.node] >= 0) want_lower(c1.node);
+            if (urow[c1.node] >= 0) want_lower(c0.node);
+        }
+        ndops = T.dops;
+        ndkids = T.dkids;
+        for (DownChild &dc : ndkids) {
+            dc.src = dc.is_tip ? dc.src : lrow[dc.node];
+            dc.pad = urow[dc.node] + 1;
+        }
+        for (DownOp &o : ndops) o.parent_slot = o.pad == T.root ? -1 : urow[o.pad];
+        for (NniEdgeJob &jb : jobs) {
+            jb.k0_src = jb.k0_is_tip ? T.leaf_row[jb.k0_edge] : lrow[jb.k0_edge];
+            jb.k1_src = jb.k1_is_tip ? T.leaf_row[jb.k1_edge] : lrow[jb.k1_edge];
+            jb.s_src = jb.s_is_tip ? T.leaf_row[jb.s_edge] : lrow[jb.s_edge];
+            if (jb.p_upper_slot >= 0) jb.p_upper_slot = urow[jb.p_upper_slot];
+        }
+    }
+    // The storing sweep as the cache pass: its own schedule (cherries whose CLV is wanted stay explicit), swapped into
+    // ctx->sweep while the pass runs so that ensure_sweep / launch_sweep_* work on it.
+    struct SweepSwap {
+        phb_ctx *c;
+        bool on;
+        void flip()
+        {
+            std::swap(c->sweep, c->nni_sweep);
+            std::swap(c->sweep_geom, c->nni_geom);
+            std::swap(c->sweep_guards_valid, c->nni_guards_valid);
+            for (Device &d : c->devs) d.sweep_uploaded = false; // the device tables belong to the other schedule now
+        }
+        ~SweepSwap()
+        {
+            if (on) flip();
+        }
+    } swap_guard{ctx, false};
+    std::vector<int> pred_row; // per cache row: the row holding the running exponent count before its subtree began
+    int n_rows = n_store;
+    if (sweep_cache) {
+        std::vector<char> keep(T.n, 0);
+        for (int v = 0; v < T.n; ++v) keep[v] = lrow[v] >= 0;
+        swap_guard.flip();
+        swap_guard.on = true;
+        rc = ensure_sweep(ctx, M, false, &keep);
+        if (rc) return rc;
+        SweepSched &S = ctx->sweep;
+        std::vector<int> row_of(T.n, -1);
+        for (int v = 0; v < T.n; ++v) row_of[v] = lrow[v];
+        pred_row.assign(n_store, -1);
+        for (int v = 0; v < T.n; ++v) {
+            if (lrow[v] < 0) continue;
+            const int fo = S.first_op[v];
+            if (fo < 0 || S.done_op[v] < 0) return ctx->fail(PHB_ERR_NUMERICAL_INSTABILITY, "NNI cache: node %d has no op of its own", v);
+            if (fo == 0) continue;
+            const int y = S.op_node[fo - 1];
+            if (y < 0) return ctx->fail(PHB_ERR_NUMERICAL_INSTABILITY, "NNI cache: op %d completes no node", fo - 1);
+            if (row_of[y] < 0) row_of[y] = n_rows++;
+            pred_row[lrow[v]] = row_of[y];
+        }
+        for (Device &d : ctx->devs) { // the op table is about to change under a copy that may still be in flight
+            cudaSetDevice(d.ordinal);
+            cudaStreamSynchronize(d.stream);
+        }
+        for (size_t k = 0; k < S.op_node.size(); ++k) S.ops[k].w2 = S.op_node[k] >= 0 && row_of[S.op_node[k]] >= 0 ? (uint32_t)row_of[S.op_node[k]] : SW_NO_ROW;
+        for (Device &d : ctx->devs) {
+            if (d.P == 0) continue;
+            CU(cudaSetDevice(d.ordinal));
+            CU(cudaMemcpyAsync(d.sw_ops.p, S.ops.data(), sizeof(SweepOp) * S.ops.size(), cudaMemcpyHostToDevice, d.stream));
+        }
     }
     phb_stats &S = ctx->stats;
     S.nni_path_moves = (int)moves.size();
@@ -1304,12 +1408,14 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
         CU(cudaMemcpyAsync(d.nni_steps.p, steps.data(), sizeof(NniStep) * steps.size(), cudaMemcpyHostToDevice, d.stream));
         CU(cudaMemsetAsync(d.nni_totals.p, 0, sizeof(double) * (size_t)n_moves, d.stream));
         // tile the pattern axis so that one tile's CLVs + subtree exponents fit the budget
-        const size_t per_site = (size_t)T.n_internal * M.n_clv * (4 * sizeof(double) + sizeof(int)) * (use_upper ? 2 : 1);
+        const size_t row_bytes = (size_t)M.n_clv * (4 * sizeof(double) + sizeof(int));
+        const size_t per_site = ((size_t)n_store + (size_t)n_upper) * row_bytes + (size_t)(sweep_cache ? n_rows : 0) * M.n_clv * sizeof(int);
         size_t budget = ctx->clv_budget;
-        if (!budget) {
+        if (!budget) { // a third of the card at most: the cache is scratch, the tiles cost no time
             size_t free_b = 0, total_b = 0;
             CU(cudaMemGetInfo(&free_b, &total_b));
-            budget = (size_t)((double)(free_b + d.clv.cap + d.nni_exps.cap + d.nni_upper.cap + d.nni_uexps.cap) * 0.85);
+            const size_t avail = free_b + d.clv.cap + d.nni_exps.cap + d.nni_upper.cap + d.nni_uexps.cap + d.nni_cnt.cap;
+            budget = std::min((size_t)((double)avail * 0.85), total_b / 3);
         }
         int64_t tile = d.P_pad;
         if (per_site * (size_t)d.P_pad > budget) {
@@ -1321,17 +1427,32 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
         const int n_tiles = (int)((d.P + tile - 1) / tile);
         const size_t tile_pad = (size_t)tile;
         const size_t slot_stride = (size_t)M.n_clv * 4 * tile_pad;
-        CU(d.clv.ensure(sizeof(double) * slot_stride * (size_t)T.n_internal));
-        CU(d.nni_exps.ensure(sizeof(int) * (size_t)M.n_clv * tile_pad * (size_t)T.n_internal));
+        CU(d.clv.ensure(sizeof(double) * slot_stride * (size_t)std::max(n_store, 1)));
+        CU(d.nni_exps.ensure(sizeof(int) * (size_t)M.n_clv * tile_pad * (size_t)std::max(n_store, 1)));
+        SweepGeom tile_geom;
         if (use_upper) {
-            CU(d.nni_upper.ensure(sizeof(double) * slot_stride * (size_t)T.n_internal));
-            CU(d.nni_uexps.ensure(sizeof(int) * (size_t)M.n_clv * tile_pad * (size_t)T.n_internal));
+            CU(d.nni_upper.ensure(sizeof(double) * slot_stride * (size_t)std::max(n_upper, 1)));
+            CU(d.nni_uexps.ensure(sizeof(int) * (size_t)M.n_clv * tile_pad * (size_t)std::max(n_upper, 1)));
             CU(d.nni_jobs.ensure(sizeof(NniEdgeJob) * jobs.size()));
             CU(d.nni_rows.ensure(sizeof(int32_t) * job_rows.size()));
-            CU(d.nni_need.ensure(need_upper.size()));
-            CU(cudaMemcpyAsync(d.nni_need.p, need_upper.data(), need_upper.size(), cudaMemcpyHostToDevice, d.stream));
+            CU(d.nni_dops.ensure(sizeof(DownOp) * std::max<size_t>(ndops.size(), 1)));
+            CU(d.nni_dkids.ensure(sizeof(DownChild) * std::max<size_t>(ndkids.size(), 1)));
+            CU(cudaMemcpyAsync(d.nni_dops.p, ndops.data(), sizeof(DownOp) * ndops.size(), cudaMemcpyHostToDevice, d.stream));
+            CU(cudaMemcpyAsync(d.nni_dkids.p, ndkids.data(), sizeof(DownChild) * ndkids.size(), cudaMemcpyHostToDevice, d.stream));
             CU(cudaMemcpyAsync(d.nni_jobs.p, jobs.data(), sizeof(NniEdgeJob) * jobs.size(), cudaMemcpyHostToDevice, d.stream));
             CU(cudaMemcpyAsync(d.nni_rows.p, job_rows.data(), sizeof(int32_t) * job_rows.size(), cudaMemcpyHostToDevice, d.stream));
+        }
+        if (sweep_cache) {
+            CU(d.nni_cnt.ensure(sizeof(int) * (size_t)M.n_clv * tile_pad * (size_t)n_rows));
+            CU(d.nni_pred.ensure(sizeof(int) * (size_t)std::max(n_store, 1)));
+            CU(cudaMemcpyAsync(d.nni_pred.p, pred_row.data(), sizeof(int) * pred_row.size(), cudaMemcpyHostToDevice, d.stream));
+            if (!tile_geom.plan(ctx->sweep, d.smem_optin, std::min<int64_t>(tile, d.P), std::max(d.sm_count, 1)))
+                return ctx->fail(PHB_ERR_INVALID_MODEL_PARAMETER, "sweep: %d CLV categories do not fit one CTA", M.n_clv);
+            const int64_t bs = 4 * tile_geom.Q;
+            CU(d.partials.ensure(sizeof(double) * (size_t)((tile + bs - 1) / bs + 1)));
+            CU(d.per_pattern.ensure(sizeof(double) * (size_t)d.P_pad));
+            CU(d.cat_ll.ensure(sizeof(double) * (size_t)M.n_cat * tile_pad));
+            CU(d.total.ensure(2 * sizeof(double)));
         }
         if (&d == &ctx->devs[0]) {
             d.ev_used = 0;
@@ -1351,6 +1472,10 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
                        d.Pmat.as<double>());
             CHECK_LAUNCH();
         }
+        if (sweep_cache) {
+            rc = launch_sweep_transition(ctx, d, M);
+            if (rc) return rc;
+        }
         if (!d.tip_constants_valid) {
             int64_t groups = d.P_pad / 4;
             PHB_LAUNCH(tip_constants_kernel, dim3((unsigned)((groups * 4 + TIPC_SITES - 1) / TIPC_SITES)), dim3(TIPC_THREADS), d.stream,
@@ -1364,7 +1489,19 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
             const int64_t off = (int64_t)t * tile;
             const int len = (int)std::min<int64_t>(tile, d.P - off);
             const int bpr = (len + SITES_PER_BLOCK - 1) / SITES_PER_BLOCK;
-            for (int l = 1; l <= T.n_levels; ++l) { // cache the base tree's CLVs of this tile
+            if (sweep_cache) { // the base tree's partials of this tile: one storing sweep + the exponent differences
+                rc = launch_sweep_range(ctx, d, M, tile_geom, off, len, 0, d.clv.as<double>(), d.cat_ll.as<double>(), tile_pad, false,
+                                        d.nni_cnt.as<int>(), (uint32_t)n_store);
+                if (rc) return rc;
+                if (n_store > 0) {
+                    ScopedTimer tm(ctx, &d, PH_CLV);
+                    const size_t row_elems = (size_t)M.n_clv * tile_pad;
+                    PHB_LAUNCH(nni_exp_rows_kernel, dim3((unsigned)((row_elems + 255) / 256)), dim3(256), d.stream, d.nni_cnt.as<int>(),
+                               d.nni_pred.as<int>(), n_store, row_elems, d.nni_exps.as<int>());
+                    CHECK_LAUNCH();
+                }
+            }
+            for (int l = 1; l <= T.n_levels && !sweep_cache; ++l) { // ... or level by level, every node
                 const int nb = T.level_off[l] - T.level_off[l - 1];
                 if (nb <= 0) continue;
                 ScopedTimer tm(ctx, &d, PH_CLV);
@@ -1381,9 +1518,9 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
                     ScopedTimer tm(ctx, &d, PH_UPPER);
 #define PHB_UPPER_LAUNCH(MINB)                                                                                         \
     PHB_LAUNCH(upper_level_kernel<MINB>, dim3((unsigned)((int64_t)nb * M.n_clv * bpr)), dim3(CLV_THREADS), d.stream,   \
-               d.dops.as<DownOp>() + T.dlevel_off[dl], nb, d.dkids.as<DownChild>(), T.root, M, d.Pmat.as<double>(),    \
+               d.nni_dops.as<DownOp>() + T.dlevel_off[dl], nb, d.nni_dkids.as<DownChild>(), T.root, M, d.Pmat.as<double>(), \
                d.clv.as<double>(), d.nni_upper.as<double>(), slot_stride, tile_pad, len, bpr, d.nni_exps.as<int>(),    \
-               d.nni_uexps.as<int>(), d.tips.as<uint8_t>(), d.P_pad, off, need_all ? (const uint8_t *)nullptr : d.nni_need.as<uint8_t>())
+               d.nni_uexps.as<int>(), d.tips.as<uint8_t>(), d.P_pad, off)
                     if (upper_minb == 2) PHB_UPPER_LAUNCH(2);
                     else if (upper_minb == 4) PHB_UPPER_LAUNCH(4);
                     else PHB_UPPER_LAUNCH(3);
@@ -1556,7 +1693,7 @@ void phb_ctx_destroy(phb_ctx *ctx)
                           &d.dkids, &d.leaf_rows, &d.states, &d.posteriors, &d.staging, &d.sim_pre, &d.sim_parent,
                           &d.sim_depth, &d.sim_leafrow, &d.sim_stack, &d.scratch, &d.sw_descs, &d.sw_blocks,
                           &d.sw_stream, &d.sw_gstack, &d.sw_err, &d.sw_opoff, &d.dn_ops, &d.dn_descs, &d.dn_blocks, &d.dn_stream, &d.dn_opoff, &d.dn_gstack, &d.sw_ops, &d.uops, &d.ukids, &d.lnP, &d.jbest,
-                          &d.nni_upper, &d.nni_uexps, &d.nni_jobs, &d.nni_rows, &d.nni_exps, &d.nni_partials, &d.nni_totals, &d.nni_moves, &d.nni_steps, &d.nni_need};
+                          &d.nni_upper, &d.nni_uexps, &d.nni_jobs, &d.nni_rows, &d.nni_exps, &d.nni_partials, &d.nni_totals, &d.nni_moves, &d.nni_steps, &d.nni_need, &d.nni_cnt, &d.nni_pred, &d.nni_dops, &d.nni_dkids};
         for (DevBuf *b : bufs) b->release();
         if (ctx->is_aa) aa_release(ctx);
         for (auto &ep : d.ev_pool) {
@@ -2021,6 +2158,7 @@ int32_t phb_set_model(phb_ctx *ctx, const double *lambda, const double *V, const
     build_model_dev(M, true, ctx->model_lit);
     ctx->have_model = true;
     ctx->sweep_guards_valid = false; // the guard plan depends on the rates
+    ctx->nni_guards_valid = false;
     return PHB_OK;
 }
 

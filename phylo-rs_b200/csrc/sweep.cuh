@@ -56,6 +56,8 @@ constexpr int SW_FLAG_NORMOUT = 64; // after the op: rescale every site to max i
 constexpr int SW_FLAG_FIRST = 128; // first op of a ring stage: wait for the stage's data before touching it
 constexpr int SW_FLAG_LAST = 256;  // last op of a ring stage: hand the stage back to the producer afterwards
 
+constexpr uint32_t SW_NO_ROW = 0xffffffffu; // header w2 of a completing op whose node the storing variant does not write
+
 constexpr int SW_P_BYTES = 128;    // 4x4 f64 row-major
 // Tables are PLANAR with a 16-byte row stride: states 0,1 of all rows, then states 2,3.  The rows that carry almost
 // every site (A,C,G,T; the pairs a == b) then fall in different bank groups of a quarter-warp's LDS.128.
@@ -356,6 +358,12 @@ struct SweepParams {
     size_t slot_stride; // n_clv * 4 * tile_pad; blocked layout: n_blocks * n_clv * 4 * (4 Q)
     size_t tile_pad;
     int blocked;        // clv_out is [slot][site block][cat][state][4 Q]: one node's block is contiguous (down_sweep.cuh)
+    // NNI cache pass (phylo_b200.cu score_nni_paths): exp_out != null -- a completed node with row w2 is first brought
+    // to a maximum in [1,2) and the RUNNING exponent count of its (site, category) goes to exp_out[row][cat][site]; the
+    // exponent of the node's own subtree is the difference to the count before the subtree's first op (a row of its
+    // own: the ops of a subtree are consecutive).  Only rows < n_store get their CLV written.
+    int *exp_out;
+    uint32_t n_store;
 };
 
 __device__ __forceinline__ void sw_matvec(const double (&p)[16], const double (&x)[4], double (&y)[4])
@@ -829,9 +837,23 @@ sweep_kernel(SweepParams p, ModelDev M)
                 if (flags & SW_FLAG_U) guard(u);
                 else guard(v);
             }
-            if (STORE && (flags & SW_FLAG_DONE)) {
+            if (STORE && (flags & SW_FLAG_DONE) && h.z != SW_NO_ROW) {
                 const bool use_u = flags & SW_FLAG_U;
-                if (p.blocked) { // whole blocks: the buffer covers n_blocks * 4 Q patterns
+                if (p.exp_out) {
+#pragma unroll
+                    for (int r = 0; r < SW_R; ++r) {
+                        if (use_u) sw_rescale<true>(u[r], sc[r]);
+                        else sw_rescale<true>(v[r], sc[r]);
+                    }
+                    const int64_t rel = b * sites_per_block + 4 * q;
+                    int *e = p.exp_out + ((size_t)h.z * M.n_clv + cc) * p.tile_pad + (size_t)rel;
+#pragma unroll
+                    for (int r = 0; r < SW_R; ++r)
+                        if (rel + r < p.P) e[r] = sc[r];
+                }
+                if (h.z >= p.n_store) {
+                    // a counter-only row
+                } else if (p.blocked) { // whole blocks: the buffer covers n_blocks * 4 Q patterns
                     double *dst = p.clv_out + (size_t)h.z * p.slot_stride + ((size_t)b * M.n_clv + cc) * (size_t)(4 * sites_per_block) + 4 * q;
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {

@@ -42,6 +42,9 @@ struct SweepSched {
     // guard planning (plan_guards): the op that completes each node, the flags the schedule itself needs, and the
     // tree in post-order
     std::vector<int> done_op;           // node -> index of the op that completes it (-1: leaf)
+    std::vector<int> first_op;          // node -> index of the first op of its subtree (the ops of a subtree are
+                                        // consecutive: first_op[v] .. done_op[v]); -1: leaf / folded cherry
+    std::vector<int> op_node;           // op -> node it completes (-1: not a completing op)
     std::vector<uint32_t> base_w0;      // per op: w0 without SW_FLAG_GUARD / SW_FLAG_NORMOUT
     std::vector<int> post_order;        // children before parents
     std::vector<int> kid_off, kids;     // copy of the child lists
@@ -207,6 +210,8 @@ struct SweepSched {
         struct Frame { int v, j; bool ret; };
         std::vector<Frame> st;
         st.push_back({root, 0, false});
+        first_op.assign(n, -1);
+        first_op[root] = 0;
         while (!st.empty()) {
             Frame &f = st.back();
             const int v = f.v;
@@ -233,6 +238,7 @@ struct SweepSched {
                 }
                 f.ret = true;
                 int c = iv[f.j++];
+                first_op[c] = (int)recs.size(); // the next op emitted opens c's subtree
                 st.push_back({c, 0, false});
                 continue;
             }
@@ -363,6 +369,7 @@ struct SweepSched {
         ops.assign(recs.size() + 2, SweepOp{0, 0, 0, 0}); // + two padding entries
         base_w0.assign(recs.size(), 0);
         done_op.assign(n, -1);
+        op_node.assign(recs.size(), -1);
         for (size_t k = 0; k < recs.size(); ++k) {
             const Hdr &h = recs[k].h;
             const uint32_t code = (uint32_t)sw_code(h.kind, (h.flags & (SW_FLAG_U | SW_FLAG_XU)) != 0);
@@ -371,7 +378,9 @@ struct SweepSched {
             ops[k].w1 = (uint32_t)(h.szA + h.szB) | ((uint32_t)h.szA << 16);
             const int nd = (h.flags & SW_FLAG_DONE) ? recs[k].node : -1;
             if (nd >= 0) done_op[nd] = (int)k;
-            ops[k].w2 = (nd >= 0 && (size_t)nd < slot.size() && slot[nd] >= 0) ? (uint32_t)slot[nd] : 0u;
+            op_node[k] = nd;
+            // the storing variant skips a node whose row is SW_NO_ROW (a node nobody asked for)
+            ops[k].w2 = (nd >= 0 && (size_t)nd < slot.size() && slot[nd] >= 0) ? (uint32_t)slot[nd] : SW_NO_ROW;
             ops[k].w3 = op_w3[k];
         }
         plan_guards(std::vector<double>(), std::vector<double>()); // until bounds are known: guard after every node
