@@ -182,7 +182,8 @@ def run_nni(tag, n_taxa, n_sites, model, seed, n_moves, reps, flags=0):
                       else "edge-local scoring with upper partials"),
                 nni_path_moves=st["nni_path_moves"], nni_path_steps=st["nni_path_steps"], nni_tiles=st["nni_tiles"],
                 nni_cache_GB=st["nni_cache_bytes"] / 1e9, nni_read_GB=st["nni_read_bytes"] / 1e9,
-                walk_read_GBps=st["nni_read_bytes"] / (dev_ms * 1e-3) / 1e9)
+                walk_read_GBps=st["nni_read_bytes"] / (dev_ms * 1e-3) / 1e9,
+                phases_ms=dict(cache_pass=st["ms_nni_cache"], upper_pass=st["ms_nni_upper"], edge_kernel=st["ms_nni_edge"]))
 
 
 CASES = {
