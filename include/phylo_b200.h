@@ -263,7 +263,7 @@ typedef struct phb_stats {
     int32_t nni_path_moves;    /* last phb_score_nni: neighbours scored by the path-only kernel     */
     int32_t nni_tiles;         /* ... CLV-cache tiles per device                                    */
     int64_t nni_path_steps;    /* ... walk steps summed over those neighbours                       */
-    double nni_cache_bytes;    /* ... bytes of cached CLVs + subtree exponents per device (all tiles)*/
+    double nni_cache_bytes;    /* ... bytes of cached partials (lower rows, upper rows, exponents) RESIDENT on device 0: one tile at a time */
     double nni_read_bytes;     /* ... algorithmic bytes the walks read (sibling CLVs, exponents, tips)*/
     int32_t sweep_guards;      /* fused sweep: nodes followed by the lazy underflow check (2^-256 threshold) */
     int32_t sweep_normouts;    /* ... nodes normalised to max in [1,2) on completion (extreme branch x rate)  */

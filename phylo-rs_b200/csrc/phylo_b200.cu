@@ -1297,6 +1297,7 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
     const bool sweep_cache = use_upper && !level_cache_env && sweep_q_max(M.n_clv) >= sweep_q_step(M.n_clv) && T.n_internal < 0x7fff0000;
     std::vector<DownOp> ndops;
     std::vector<DownChild> ndkids;
+    std::vector<int> ndlevel_off;
     if (!sweep_cache) {
         for (int v = 0; v < T.n; ++v) lrow[v] = T.slot[v];
         n_store = T.n_internal;
@@ -1318,13 +1319,24 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
             if (urow[c0.node] >= 0) want_lower(c1.node);
             if (urow[c1.node] >= 0) want_lower(c0.node);
         }
-        ndops = T.dops;
         ndkids = T.dkids;
         for (DownChild &dc : ndkids) {
             dc.src = dc.is_tip ? dc.src : lrow[dc.node];
             dc.pad = urow[dc.node] + 1;
         }
-        for (DownOp &o : ndops) o.parent_slot = o.pad == T.root ? -1 : urow[o.pad];
+        // per depth, only the parents with a child whose upper partial is wanted: the launch holds no idle blocks
+        ndlevel_off.assign(1, 0);
+        for (int dl = 0; dl <= T.max_depth; ++dl) {
+            for (int k = T.dlevel_off[dl]; k < T.dlevel_off[dl + 1]; ++k) {
+                DownOp o = T.dops[k];
+                bool wanted = false;
+                for (int c = o.child_begin; c < o.child_end; ++c) wanted = wanted || ndkids[c].pad != 0;
+                if (!wanted) continue;
+                o.parent_slot = o.pad == T.root ? -1 : urow[o.pad];
+                ndops.push_back(o);
+            }
+            ndlevel_off.push_back((int)ndops.size());
+        }
         for (NniEdgeJob &jb : jobs) {
             jb.k0_src = jb.k0_is_tip ? T.leaf_row[jb.k0_edge] : lrow[jb.k0_edge];
             jb.k1_src = jb.k1_is_tip ? T.leaf_row[jb.k1_edge] : lrow[jb.k1_edge];
@@ -1411,11 +1423,11 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
         const size_t row_bytes = (size_t)M.n_clv * (4 * sizeof(double) + sizeof(int));
         const size_t per_site = ((size_t)n_store + (size_t)n_upper) * row_bytes + (size_t)(sweep_cache ? n_rows : 0) * M.n_clv * sizeof(int);
         size_t budget = ctx->clv_budget;
-        if (!budget) { // a third of the card at most: the cache is scratch, the tiles cost no time
+        if (!budget) { // 30 % of the card at most: the cache is scratch, and tiles cost no time
             size_t free_b = 0, total_b = 0;
             CU(cudaMemGetInfo(&free_b, &total_b));
             const size_t avail = free_b + d.clv.cap + d.nni_exps.cap + d.nni_upper.cap + d.nni_uexps.cap + d.nni_cnt.cap;
-            budget = std::min((size_t)((double)avail * 0.85), total_b / 3);
+            budget = std::min((size_t)((double)avail * 0.85), total_b / 10 * 3);
         }
         int64_t tile = d.P_pad;
         if (per_site * (size_t)d.P_pad > budget) {
@@ -1463,7 +1475,7 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
         CU(d.nni_partials.ensure(sizeof(double) * (size_t)std::max<size_t>(nm, 2 * jobs.size()) * (size_t)max_sb));
         if (&d == &ctx->devs[0]) {
             S.nni_tiles = n_tiles;
-            S.nni_cache_bytes = (double)per_site * (double)d.P;
+            S.nni_cache_bytes = (double)per_site * (double)std::min<int64_t>(tile, d.P); // resident: one tile at a time
         }
         {
             ScopedTimer tm(ctx, &d, PH_TRANSITION);
@@ -1513,12 +1525,12 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
             const int n_sb = (len + nni_bs - 1) / nni_bs;
             if (use_upper) {
                 for (int dl = 0; dl <= T.max_depth; ++dl) { // upper partials, root downwards
-                    const int nb = T.dlevel_off[dl + 1] - T.dlevel_off[dl];
+                    const int nb = ndlevel_off[dl + 1] - ndlevel_off[dl];
                     if (nb <= 0) continue;
                     ScopedTimer tm(ctx, &d, PH_UPPER);
 #define PHB_UPPER_LAUNCH(MINB)                                                                                         \
     PHB_LAUNCH(upper_level_kernel<MINB>, dim3((unsigned)((int64_t)nb * M.n_clv * bpr)), dim3(CLV_THREADS), d.stream,   \
-               d.nni_dops.as<DownOp>() + T.dlevel_off[dl], nb, d.nni_dkids.as<DownChild>(), T.root, M, d.Pmat.as<double>(), \
+               d.nni_dops.as<DownOp>() + ndlevel_off[dl], nb, d.nni_dkids.as<DownChild>(), T.root, M, d.Pmat.as<double>(), \
                d.clv.as<double>(), d.nni_upper.as<double>(), slot_stride, tile_pad, len, bpr, d.nni_exps.as<int>(),    \
                d.nni_uexps.as<int>(), d.tips.as<uint8_t>(), d.P_pad, off)
                     if (upper_minb == 2) PHB_UPPER_LAUNCH(2);
