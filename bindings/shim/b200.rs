@@ -38,14 +38,26 @@ impl Drop for Ctx {
 }
 
 thread_local! {
-    static CTX: RefCell<Ctx> = RefCell::new(Ctx(ptr::null_mut()));
+    static CTX: RefCell<Ctx> = RefCell::new(Ctx(ptr::null_mut()));      // Nucleotide (4 states)
+    static CTX_AA: RefCell<Ctx> = RefCell::new(Ctx(ptr::null_mut()));   // AminoAcid (20 states)
 }
 
-fn ctx() -> Result<*mut sys::phb_ctx, AsrError> {
-    CTX.with(|c| {
+/// The library has one instance of the engines per alphabet of the crate: 4 states, and 20 behind
+/// `PHB_FLAG_AMINO_ACID`.
+fn ctx<A: Alphabet>() -> Result<*mut sys::phb_ctx, AsrError> {
+    let (key, flags) = match A::N_STATES {
+        4 => (&CTX, 0u64),
+        20 => (&CTX_AA, sys::PHB_FLAG_AMINO_ACID),
+        n => {
+            return Err(AsrError::AlphabetMismatch(format!(
+                "the B200 backend has no {n}-state instance"
+            )))
+        }
+    };
+    key.with(|c| {
         let mut c = c.borrow_mut();
         if c.0.is_null() {
-            let rc = unsafe { sys::phb_ctx_create(ptr::null(), 0, 0, &mut c.0) };
+            let rc = unsafe { sys::phb_ctx_create(ptr::null(), 0, flags, &mut c.0) };
             if rc != sys::PHB_OK {
                 // no usable sm_100 device / CUDA failure: there is no host fallback behind this feature
                 return Err(AsrError::NumericalInstability);
@@ -153,7 +165,7 @@ fn flatten(tree: &PhyloTree, leaf_order: &[String]) -> Result<Flat, AsrError> {
 }
 
 fn set_model<A: Alphabet>(c: *mut sys::phb_ctx, model: &GtrModel<A>) -> Result<(), AsrError> {
-    debug_assert_eq!(A::N_STATES, 4, "the B200 backend implements the 4-state Nucleotide alphabet");
+    debug_assert_eq!(model.rate_matrix().eigenvalues().len(), A::N_STATES);
     let rm = model.rate_matrix();
     let cats = model.categories();
     let rates: Vec<f64> = cats.iter().map(|c| c.rate).collect();
@@ -197,7 +209,7 @@ fn load<A: Alphabet>(
     model: &GtrModel<A>,
     aln: &Alignment,
 ) -> Result<(*mut sys::phb_ctx, Flat, CompressedColumns), AsrError> {
-    let c = ctx()?;
+    let c = ctx::<A>()?;
     let comp = aln.compress_columns();
     let f = flatten(tree, &comp.leaf_order)?;
     let rows = comp.leaf_order.len();
@@ -220,13 +232,19 @@ fn load<A: Alphabet>(
 }
 
 /// The faster load: the sequences go across as they lie in `Alignment::seqs` and the device performs
-/// `compress_columns` (patterns numbered by first appearance, as on the host).
+/// `compress_columns` (patterns numbered by first appearance, as on the host).  The 20-state instance has no
+/// device compressor: it takes the host-side `load`.
 fn load_dev<A: Alphabet>(
     tree: &PhyloTree,
     model: &GtrModel<A>,
     aln: &Alignment,
 ) -> Result<(*mut sys::phb_ctx, Flat, Vec<u64>, usize), AsrError> {
-    let c = ctx()?;
+    if A::N_STATES != 4 {
+        let (c, f, comp) = load(tree, model, aln)?;
+        let s2p: Vec<u64> = comp.site_to_pattern.iter().map(|&s| s as u64).collect();
+        return Ok((c, f, s2p, comp.patterns.len()));
+    }
+    let c = ctx::<A>()?;
     let leaf_order: Vec<String> = aln.seqs.keys().cloned().collect();
     let f = flatten(tree, &leaf_order)?; // errors before the device is touched
     let rows: Vec<*const u8> = leaf_order.iter().map(|n| aln.seqs[n].as_ptr()).collect();
@@ -280,7 +298,7 @@ fn expand<A: Alphabet>(
     for id in tree.get_node_ids() {
         sequences.insert(id, vec![0; width]);
         if let Some(map) = posteriors.as_mut() {
-            map.insert(id, vec![vec![0.0; 4]; width]);
+            map.insert(id, vec![vec![0.0; A::N_STATES]; width]);
         }
     }
     for (k, &id) in f.ids.iter().enumerate() {
@@ -292,7 +310,10 @@ fn expand<A: Alphabet>(
         if let (Some(map), Some(p)) = (posteriors.as_mut(), post) {
             let rows: Vec<Vec<f64>> = site_to_pattern
                 .iter()
-                .map(|&s| p[(k * n_patterns + s) * 4..(k * n_patterns + s) * 4 + 4].to_vec())
+                .map(|&s| {
+                    let at = (k * n_patterns + s) * A::N_STATES;
+                    p[at..at + A::N_STATES].to_vec()
+                })
                 .collect();
             map.insert(id, rows);
         }
@@ -316,7 +337,7 @@ pub fn marginal_asr<A: Alphabet>(
     let (n, p) = (f.ids.len(), comp.patterns.len());
     let mut states = vec![0u8; n * p.max(1)];
     let mut post = if want_posteriors {
-        vec![0f64; n * p.max(1) * 4]
+        vec![0f64; n * p.max(1) * A::N_STATES]
     } else {
         Vec::new()
     };

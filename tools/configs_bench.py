@@ -240,7 +240,7 @@ def _oracle_tree(tree):
     return ft
 
 
-def driver_configs(hbm_gbs, reps=3, which=("cfg2", "cfg4", "joint", "cfg5", "compress")):
+def driver_configs(hbm_gbs, reps=3, which=("cfg2", "cfg4", "joint", "cfg5", "compress", "amino_acid")):
     import oracle
 
     oracle.build()
@@ -394,7 +394,37 @@ def driver_configs(hbm_gbs, reps=3, which=("cfg2", "cfg4", "joint", "cfg5", "com
                     wall_ms=wall_ms, device_ms=dev_ms, input_GB=n * W / 1e9, end_to_end_GBps=n * W / (wall_ms * 1e-3) / 1e9,
                     parity=dict(n_patterns=int(Pn), expected_patterns=W - 1000, site_to_pattern_exact=ok_s2p, multiplicity_exact=ok_mult))
 
+    def amino_acid():
+        """the 20-state engines (PHB_FLAG_AMINO_ACID) on a seeded general GTR20+G4; the oracle's NS=20 build
+        checks 32 patterns of the same alignment."""
+        from oracle import workloads
+
+        n, P = 1000, 20_000
+        case = workloads.make_case(n, 32, model="aa_g4", seed=0x5EED00AA, ambiguity=0.02)
+        m, ft = case.model, case.ft
+        rng = np.random.default_rng(7)
+        pats = case.patterns[rng.integers(32, size=P)].copy()
+        flip = rng.random(pats.shape) < 0.3  # decorrelate the resampled columns
+        pats[flip] = np.frombuffer(workloads.AA_LETTERS, np.uint8)[rng.integers(20, size=int(flip.sum()))]
+        pats[:32] = case.patterns
+        with capi.Context(flags=capi.FLAG_AMINO_ACID) as ctx:
+            ctx.set_alignment(pats)
+            ctx.set_model(m.eigenvalues, m.eigenvectors, m.pi, m.sqrt_pi, m.inv_sqrt_pi, m.rates, m.weights)
+            ctx.set_tree(ft["postorder"], ft["child_off"], ft["children"], ft["blen"], ft["leaf_row"], ft["root"])
+            _, dev_ms, wall_ms = timed(ctx, ctx.log_likelihood, reps)
+            tot, per = ctx.log_likelihood(per_pattern=True)
+            (_t, states, _p), asr_ms, _w = timed(ctx, ctx.marginal_asr, max(1, reps - 1))
+        _rt, ref_per, ref_states, _rp = oracle.marginal_asr_flat(ft, m, case.patterns, n_threads=8)
+        K = len(m.rates)
+        flops = P * K * (820.0 * (n - 2) + 20.0 * n)
+        return dict(workload="AminoAcid GTR20+G4 log-likelihood and marginal ASR, 1000 taxa x 20k patterns", device_ms=dev_ms,
+                    wall_ms=wall_ms, asr_device_ms=asr_ms, updates_per_s=(n - 1) * P / (dev_ms * 1e-3),
+                    fp64_tflops=flops / (dev_ms * 1e-3) / 1e12, frac_of_hbm=P * K * 164.0 * (2 * n - 3) / (dev_ms * 1e-3) / 1e9 / hbm_gbs,
+                    parity=dict(sample_patterns=32, max_abs_per_pattern_lnl=float(np.max(np.abs(per[:32] - ref_per))),
+                                asr_state_mismatches=int((states[:, :32] != ref_states).sum())))
+
     guard("cfg2", cfg2)
+    guard("amino_acid", amino_acid)
     guard("cfg4", cfg4)
     guard("joint", joint)
     guard("cfg5", cfg5)
