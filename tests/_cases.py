@@ -143,3 +143,36 @@ def check_compress(lib, rows, devices=None):
         valid = np.isin(canon, np.frombuffer(b"ACGTRYSWKMBDHVN-", np.uint8))
         assert np.array_equal(back[valid], canon[valid]) and np.all(back[~valid] == ord("?"))
     return n
+
+
+NONBINARY_NEWICKS = [
+    # polytomies of arity 3..6, unifurcations, a polytomy under a polytomy (the oracle itself is checked on these by
+    # brute-force enumeration: tests/test_oracle_kat.py)
+    "((a:0.1,b:0.2,c:0.3):0.2,(d:0.1,e:0.4,f:0.1,g:0.2):0.3,h:0.5);",
+    "(((a:0.2,b:0.1):0.1):0.3,((c:0.3):0.2,d:0.1,e:0.2,f:0.3,g:0.1,h:0.2):0.2,(i:0.1,j:0.3):0.4);",
+    "((a:0.05,b:0.4,c:0.1,d:0.3,e:0.2):0.6,(f:0.2,(g:0.1,h:0.1,i:0.3):0.2,j:0.2):0.1,k:0.7,l:0.02);",
+    "(a:0.3,b:0.1,c:0.2,d:0.4,e:0.5,f:0.6);",
+]
+
+
+def nonbinary_case(nwk, model, n_sites=300):
+    import re
+
+    from oracle import parse_newick
+
+    tree = parse_newick(nwk)
+    names = re.findall(r"[(,]([a-z])", nwk)
+    ft = workloads.flatten_fast(tree, names)
+    rng = np.random.default_rng(len(nwk))
+    pats = np.frombuffer(b"ACGTACGTACGTRYN-", np.uint8)[rng.integers(16, size=(n_sites, len(names)))]
+    return workloads.Case(tree, ft, workloads.make_model(model), model, np.ascontiguousarray(pats), np.ones(n_sites, np.uint64), names)
+
+
+def check_nonbinary(lib):
+    for nwk in NONBINARY_NEWICKS:
+        for model in ("gtr", "gtr_i_g4"):
+            case = nonbinary_case(nwk, model)
+            check_lnl(lib, case)
+            check_lnl(lib, case, flags=capi.FLAG_LEVEL_KERNELS)
+            check_asr(lib, case, want_post=True)
+            check_joint(lib, case)

@@ -486,3 +486,8 @@ def test_fused_host_call(gpu_lib):
         with pytest.raises(capi.PhbError) as e:
             ctx.log_likelihood_host(bad)
         assert e.value.variant == "AlphabetMismatch"
+
+
+def test_nonbinary_trees_all_engines(gpu_lib):
+    """polytomies of arity 3..6, unifurcations, nested polytomies: lnL (sweep and level kernels), marginal and joint ASR"""
+    _cases.check_nonbinary(gpu_lib)

@@ -134,6 +134,38 @@ def test_bruteforce_enumeration(seed):
         assert per[p] == pytest.approx(math.log(bf), abs=1e-11), (p, ls)
 
 
+NONBINARY = [
+    # polytomies of arity 3..6, unifurcations, a polytomy under a polytomy; <= 9 internal nodes (4^9 assignments)
+    "((a:0.1,b:0.2,c:0.3):0.2,(d:0.1,e:0.4,f:0.1,g:0.2):0.3,h:0.5);",
+    "(((a:0.2,b:0.1):0.1):0.3,((c:0.3):0.2,d:0.1,e:0.2,f:0.3,g:0.1,h:0.2):0.2,(i:0.1,j:0.3):0.4);",
+    "((a:0.05,b:0.4,c:0.1,d:0.3,e:0.2):0.6,(f:0.2,(g:0.1,h:0.1,i:0.3):0.2,j:0.2):0.1,k:0.7,l:0.02);",
+    "(a:0.3,b:0.1,c:0.2,d:0.4,e:0.5,f:0.6);",
+]
+
+
+@pytest.mark.parametrize("nwk", NONBINARY)
+@pytest.mark.parametrize("model", ["gtr", "gtr_i_g4"])
+def test_bruteforce_enumeration_nonbinary(nwk, model):
+    """An independent checker for arbitrary arity (likelihood.rs:113 iterates over any number of children): the sum over
+    all internal-state assignments, per rate category, against the pruning restatement."""
+    import re
+
+    from oracle import parse_newick, workloads
+
+    tree = parse_newick(nwk)
+    names = re.findall(r"[(,]([a-z])", nwk)
+    ft = workloads.flatten_fast(tree, names)
+    m = workloads.make_model(model)
+    rng = np.random.default_rng(len(nwk))
+    pats = np.frombuffer(b"ACGTACGTACGTRYN-", np.uint8)[rng.integers(16, size=(10, len(names)))]
+    _tot, per = oracle.log_likelihood_flat(ft, m, np.ascontiguousarray(pats))
+    for p in range(len(pats)):
+        with np.errstate(divide="ignore"):
+            cats = [math.log(w) + np.log(oracle.bruteforce_site_likelihood(ft, m, pats[p], rate=float(r)))
+                    for r, w in zip(m.rates, m.weights)]
+        assert per[p] == pytest.approx(float(np.logaddexp.reduce(cats)), abs=1e-11)
+
+
 def test_modes_agree():
     from oracle import workloads
 

@@ -525,3 +525,8 @@ def test_fused_host_call_matches_two_call_path(emu_lib):
                 ctx.log_likelihood_host(case.patterns[:, :-1].copy())
             assert e.value.variant == "InvalidAlignment"
             assert ctx.log_likelihood_host(case.patterns, multiplicity=mult) == tot
+
+
+def test_nonbinary_trees_all_engines(emu_lib):
+    """polytomies of arity 3..6, unifurcations, nested polytomies: lnL (sweep and level kernels), marginal and joint ASR"""
+    _cases.check_nonbinary(emu_lib)
