@@ -152,88 +152,96 @@ __device__ __forceinline__ double aa_tip_row(const double *Ps, int i, uint32_t c
 }
 
 // ---- one level of prune_pattern_category (likelihood.rs:110-131), any arity ---------------------------------------
-// grid: x = blocks of AA_R * AA_THREADS patterns of the tile, y = op of the level, z = category.  values = prod over
-// children of P_child * profile_child; the product is rescaled ONCE per node, like the reference's single
-// Profile::scale() per node, so a node with very many children leaves the f64 range where the reference does
-// (DESIGN.md §2.1).  A thread owns AA_R = 2 patterns (one block-width apart, so that both streams stay coalesced): every
-// P(t) entry read from shared memory feeds two DFMA instead of one -- with one pattern per thread the mat-vec issues one
-// broadcast LDS.128 per two DFMA and the shared-memory pipe, not the FP64 pipe, bounds the kernel (tools/ubench.cu:
-// 2.0 clocks per broadcast LDS.128 per SM against 2.2 clocks per DFMA per SM sub-partition).
+// grid: x = blocks of AA_THREADS patterns of the tile, y = op of the level, z = category.  values = prod over children
+// of P_child * profile_child; the product is rescaled ONCE per node, like the reference's single Profile::scale() per
+// node, so a node with very many children leaves the f64 range where the reference does.
+// The child's P(t) is staged TRANSPOSED (Pt[j][i] = P[i][j]) and the mat-vec runs column by column,
+//     y[0..19] += Pt[j][0..19] * x_j     for j = 0..19  (the reference's gemv order: likelihood.rs:121, column j ascending),
+// so that a thread holds the 20 sums and the running product but never the child's whole vector (x_j streams in from
+// HBM): 100 registers instead of 148, five blocks per SM instead of three -- the kernel waits on HBM latency, and the
+// resident warps are what hides it (9.9 -> 13.5 ms at 1,000 x 20k when a rewrite cost a block per SM).  A tip child
+// reads ONE column of P = one contiguous row of Pt.
 #ifndef PHB_AA_R
 #define PHB_AA_R 1
 #endif
-constexpr int AA_R = PHB_AA_R;
-__global__ void __launch_bounds__(AA_THREADS)
+constexpr int AA_R = PHB_AA_R; // patterns per thread in the pre-order kernel
+constexpr int AA_STAGE = 2;    // children whose P(t) the up-pass kernel stages at once
+__device__ __forceinline__ void aa_tip_col(const double *Pt, uint32_t code, double (&y)[AA_NS])
+{
+    if (code < (uint32_t)AA_NS) {
+#pragma unroll
+        for (int i = 0; i < AA_NS; ++i) y[i] = Pt[code * AA_NS + i];
+    } else if (code <= AA_CODE_J) {
+        int a, b;
+        aa_pair_states(code, a, b);
+#pragma unroll
+        for (int i = 0; i < AA_NS; ++i) y[i] = Pt[a * AA_NS + i] + Pt[b * AA_NS + i];
+    } else {
+#pragma unroll
+        for (int i = 0; i < AA_NS; ++i) y[i] = Pt[i];
+        for (int j = 1; j < AA_NS; ++j) {
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) y[i] += Pt[j * AA_NS + i];
+        }
+    }
+}
+#ifndef PHB_AA_MINB
+#define PHB_AA_MINB 4
+#endif
+__global__ void __launch_bounds__(AA_THREADS, PHB_AA_MINB)
 aa_clv_kernel(const GenOp *__restrict__ ops, const GenChild *__restrict__ kids, int n_cat, const double *__restrict__ Pmat,
               double *__restrict__ clv, int *__restrict__ exps, size_t slot_stride, size_t tile_pad, int tile_len,
               const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off)
 {
-    __shared__ double Ps[AA_NS * AA_NS];
+    __shared__ __align__(16) double Pt[AA_STAGE][AA_NS * AA_NS];
     const GenOp op = ops[blockIdx.y];
     const int cat = blockIdx.z;
-    int64_t site[AA_R];
-    bool active[AA_R];
+    int64_t site = (int64_t)blockIdx.x * AA_THREADS + threadIdx.x;
+    const bool active = site < tile_len;
+    if (!active) site = 0; // reads stay in range; nothing is written
+    double acc[AA_NS];
 #pragma unroll
-    for (int r = 0; r < AA_R; ++r) {
-        site[r] = ((int64_t)blockIdx.x * AA_R + r) * AA_THREADS + threadIdx.x;
-        active[r] = site[r] < tile_len;
-        if (!active[r]) site[r] = 0; // reads stay in range; nothing is written for it
-    }
-    double acc[AA_R][AA_NS];
-#pragma unroll
-    for (int r = 0; r < AA_R; ++r)
-#pragma unroll
-        for (int i = 0; i < AA_NS; ++i) acc[r][i] = 1.0;
-    int ex[AA_R];
-#pragma unroll
-    for (int r = 0; r < AA_R; ++r) ex[r] = 0;
-    for (int k = op.child_begin; k < op.child_end; ++k) {
-        const GenChild ch = kids[k];
-        __syncthreads(); // the previous child's matrix is no longer read
-        const double *src = Pmat + ((size_t)ch.edge * n_cat + cat) * (AA_NS * AA_NS);
-        for (int idx = threadIdx.x; idx < AA_NS * AA_NS; idx += AA_THREADS) Ps[idx] = src[idx];
+    for (int i = 0; i < AA_NS; ++i) acc[i] = 1.0;
+    int ex = 0;
+    for (int k0 = op.child_begin; k0 < op.child_end; k0 += AA_STAGE) {
+        // the matrices of up to AA_STAGE children (both of a binary node) are staged together: one barrier pair and one
+        // round of dependent loads per node instead of one per child
+        const int nb = min(AA_STAGE, op.child_end - k0);
+        __syncthreads(); // the previous batch is no longer read
+        for (int idx = threadIdx.x; idx < nb * AA_NS * AA_NS; idx += AA_THREADS) {
+            const int c = idx / (AA_NS * AA_NS), e = idx - c * (AA_NS * AA_NS);
+            Pt[c][(e % AA_NS) * AA_NS + e / AA_NS] = Pmat[((size_t)kids[k0 + c].edge * n_cat + cat) * (AA_NS * AA_NS) + e];
+        }
         __syncthreads();
-        if (ch.is_tip) {
+        for (int c = 0; c < nb; ++c) {
+            const GenChild ch = kids[k0 + c];
+            const double *P_t = Pt[c];
+            double y[AA_NS];
+            if (ch.is_tip) {
+                aa_tip_col(P_t, tips[(int64_t)ch.src * P_pad + tile_off + site], y);
+            } else {
+                const double *x_src = clv + (size_t)ch.src * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
+                ex += exps[((size_t)ch.src * n_cat + cat) * tile_pad + site];
+                const double x0 = x_src[0];
 #pragma unroll
-            for (int r = 0; r < AA_R; ++r) {
-                const uint32_t code = tips[(int64_t)ch.src * P_pad + tile_off + site[r]];
-#pragma unroll
-                for (int i = 0; i < AA_NS; ++i) acc[r][i] *= aa_tip_row(Ps, i, code);
-            }
-        } else {
-            const double *x_src = clv + (size_t)ch.src * slot_stride + (size_t)cat * AA_NS * tile_pad;
-            double x[AA_R][AA_NS];
-#pragma unroll
-            for (int r = 0; r < AA_R; ++r) {
-#pragma unroll
-                for (int j = 0; j < AA_NS; ++j) x[r][j] = x_src[(size_t)j * tile_pad + site[r]];
-                ex[r] += exps[((size_t)ch.src * n_cat + cat) * tile_pad + site[r]];
-            }
-#pragma unroll
-            for (int i = 0; i < AA_NS; ++i) {
-                double y[AA_R];
-#pragma unroll
-                for (int r = 0; r < AA_R; ++r) y[r] = Ps[i * AA_NS] * x[r][0];
+                for (int i = 0; i < AA_NS; ++i) y[i] = P_t[i] * x0;
 #pragma unroll
                 for (int j = 1; j < AA_NS; ++j) {
-                    const double pij = Ps[i * AA_NS + j];
+                    const double xj = x_src[(size_t)j * tile_pad];
 #pragma unroll
-                    for (int r = 0; r < AA_R; ++r) y[r] += pij * x[r][j];
+                    for (int i = 0; i < AA_NS; ++i) y[i] += P_t[j * AA_NS + i] * xj;
                 }
-#pragma unroll
-                for (int r = 0; r < AA_R; ++r) acc[r][i] *= y[r];
             }
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) acc[i] *= y[i];
         }
     }
+    if (!active) return;
+    ex += aa_normalize(acc);
+    double *dst = clv + (size_t)op.out_slot * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
 #pragma unroll
-    for (int r = 0; r < AA_R; ++r) {
-        if (!active[r]) continue;
-        ex[r] += aa_normalize(acc[r]);
-        double *dst = clv + (size_t)op.out_slot * slot_stride + (size_t)cat * AA_NS * tile_pad + site[r];
-#pragma unroll
-        for (int i = 0; i < AA_NS; ++i) dst[(size_t)i * tile_pad] = acc[r][i];
-        exps[((size_t)op.out_slot * n_cat + cat) * tile_pad + site[r]] = ex[r];
-    }
+    for (int i = 0; i < AA_NS; ++i) dst[(size_t)i * tile_pad] = acc[i];
+    exps[((size_t)op.out_slot * n_cat + cat) * tile_pad + site] = ex;
 }
 
 // the root's vector for one (pattern, category): its CLV, or its tip profile when the tree is a single leaf
@@ -314,7 +322,7 @@ aa_root_kernel(int root_slot, int root_row, const AaModelDev *__restrict__ M, co
 // A thread owns AA_R patterns, as in the up pass.  A leaf showing a canonical letter has a one-hot up vector, so its
 // posterior is that letter whenever the parent's message gives it any mass: only msg[letter] is computed (20 DFMA
 // instead of 400) -- identical values, since the other 19 products are exact zeros in the reference too.
-__global__ void __launch_bounds__(AA_THREADS)
+__global__ void __launch_bounds__(AA_THREADS, AA_R == 1 ? 3 : 1)
 aa_down_kernel(const AaDown *__restrict__ nodes, const AaModelDev *__restrict__ M, const double *__restrict__ Pmat,
                double *__restrict__ clv, size_t slot_stride, size_t tile_pad, int tile_len, const uint8_t *__restrict__ tips,
                int64_t P_pad, int64_t tile_off, const double *__restrict__ cat_ll, uint8_t *__restrict__ states,
