@@ -1293,7 +1293,7 @@ int score_nni_paths(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uin
     // the root).
     std::vector<int> lrow(T.n, -1), urow(T.n, -1);
     int n_store = 0, n_upper = 0;
-    static const bool level_cache_env = getenv("PHB_NNI_LEVEL_CACHE") != nullptr;
+    const bool level_cache_env = getenv("PHB_NNI_LEVEL_CACHE") != nullptr; // cross-check: every node, level kernels
     const bool sweep_cache = use_upper && !level_cache_env && sweep_q_max(M.n_clv) >= sweep_q_step(M.n_clv) && T.n_internal < 0x7fff0000;
     std::vector<DownOp> ndops;
     std::vector<DownChild> ndkids;

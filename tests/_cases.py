@@ -176,3 +176,38 @@ def check_nonbinary(lib):
             check_lnl(lib, case, flags=capi.FLAG_LEVEL_KERNELS)
             check_asr(lib, case, want_post=True)
             check_joint(lib, case)
+
+
+def check_nni_cache_variants(lib, case):
+    """phb_score_nni on ONE context, several move sets in a row (the rows of the cache and the sweep schedule are re-planned
+    per call), each once with the storing-sweep cache and once with the level-kernel cache (PHB_NNI_LEVEL_CACHE): the two
+    must agree to round-off, and both with full rescoring of a few neighbours."""
+    import os
+
+    ft = case.ft
+    co = ft["child_off"]
+    internal = [v for v in range(ft["n_nodes"]) if co[v + 1] - co[v] == 2 and v != ft["root"]]
+    cherries = [v for v in internal if all(co[c + 1] == co[c] for c in ft["children"][co[v]:co[v] + 2])]
+    sets = [[(v, lc) for v in internal[:7] for lc in (0, 1)], [(v, 1) for v in cherries[:5]],
+            [(v, lc) for v in internal[::3] for lc in (1, 0)], [(internal[-1], 0)]]
+    with capi.Context(library=lib) as ctx:
+        workloads.load_into(ctx, case)
+        base = ctx.log_likelihood()
+        for moves in sets:
+            ids, left = [m[0] for m in moves], [m[1] for m in moves]
+            a = ctx.score_nni(ids, left)
+            os.environ["PHB_NNI_LEVEL_CACHE"] = "1"
+            try:
+                b = ctx.score_nni(ids, left)
+            finally:
+                del os.environ["PHB_NNI_LEVEL_CACHE"]
+            assert np.all(np.abs(a - b) <= 1e-11 * np.abs(b)), (moves, a, b)
+            assert ctx.log_likelihood() == base
+    with capi.Context(flags=capi.FLAG_NNI_FULL, library=lib) as ctx:
+        workloads.load_into(ctx, case)
+        moves = sets[2][:6]
+        full = ctx.score_nni([m[0] for m in moves], [m[1] for m in moves])
+    with capi.Context(library=lib) as ctx:
+        workloads.load_into(ctx, case)
+        got = ctx.score_nni([m[0] for m in moves], [m[1] for m in moves])
+    assert np.all(np.abs(got - full) <= REL_TOL * np.abs(full))

@@ -491,3 +491,8 @@ def test_fused_host_call(gpu_lib):
 def test_nonbinary_trees_all_engines(gpu_lib):
     """polytomies of arity 3..6, unifurcations, nested polytomies: lnL (sweep and level kernels), marginal and joint ASR"""
     _cases.check_nonbinary(gpu_lib)
+
+
+def test_score_nni_cache_variants_and_repeated_calls(gpu_lib):
+    case = workloads.make_case(300, 3000, model="gtr_i_g4", seed=77, ambiguity=0.03)
+    _cases.check_nni_cache_variants(gpu_lib, case)

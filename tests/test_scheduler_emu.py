@@ -530,3 +530,8 @@ def test_fused_host_call_matches_two_call_path(emu_lib):
 def test_nonbinary_trees_all_engines(emu_lib):
     """polytomies of arity 3..6, unifurcations, nested polytomies: lnL (sweep and level kernels), marginal and joint ASR"""
     _cases.check_nonbinary(emu_lib)
+
+
+def test_score_nni_cache_variants_and_repeated_calls(emu_lib):
+    case = workloads.make_case(40, 300, model="gtr_i_g4", seed=77, ambiguity=0.03)
+    _cases.check_nni_cache_variants(emu_lib, case)
