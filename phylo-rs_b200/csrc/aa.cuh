@@ -188,60 +188,84 @@ __device__ __forceinline__ void aa_tip_col(const double *Pt, uint32_t code, doub
 #ifndef PHB_AA_MINB
 #define PHB_AA_MINB 4
 #endif
+constexpr int AA_CSTAGE = 4; // categories a block works through (grid.z = ceil(n_cat / AA_CSTAGE))
+constexpr int AA_DCATS = 8;  // categories whose P(t) the pre-order kernel stages at once
+// A block = one node x 128 patterns x up to AA_CSTAGE categories.  For a node with at most AA_STAGE children (every node
+// of a binary tree) all categories' matrices are staged up front behind ONE barrier pair; a polytomy stages per category
+// and child batch.  (Measured at 1,000 x 20k: 9.8 -> 9.0 ms against one category per block.  Staging the children's CLV
+// tiles in shared memory with TMA bulk copies, double-buffered over the categories, was tried and was slower -- 10.7 ms:
+// at 107 KB of shared memory only two blocks fit an SM, and the resident blocks are what hides the HBM latency here.)
 __global__ void __launch_bounds__(AA_THREADS, PHB_AA_MINB)
 aa_clv_kernel(const GenOp *__restrict__ ops, const GenChild *__restrict__ kids, int n_cat, const double *__restrict__ Pmat,
               double *__restrict__ clv, int *__restrict__ exps, size_t slot_stride, size_t tile_pad, int tile_len,
               const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off)
 {
-    __shared__ __align__(16) double Pt[AA_STAGE][AA_NS * AA_NS];
+    __shared__ __align__(16) double Pt[AA_CSTAGE * AA_STAGE][AA_NS * AA_NS];
     const GenOp op = ops[blockIdx.y];
-    const int cat = blockIdx.z;
+    const int cat0 = blockIdx.z * AA_CSTAGE;
+    const int ncat = min(AA_CSTAGE, n_cat - cat0);
+    const int nch = op.child_end - op.child_begin;
+    const bool upfront = nch <= AA_STAGE;
     int64_t site = (int64_t)blockIdx.x * AA_THREADS + threadIdx.x;
     const bool active = site < tile_len;
     if (!active) site = 0; // reads stay in range; nothing is written
-    double acc[AA_NS];
-#pragma unroll
-    for (int i = 0; i < AA_NS; ++i) acc[i] = 1.0;
-    int ex = 0;
-    for (int k0 = op.child_begin; k0 < op.child_end; k0 += AA_STAGE) {
-        // the matrices of up to AA_STAGE children (both of a binary node) are staged together: one barrier pair and one
-        // round of dependent loads per node instead of one per child
-        const int nb = min(AA_STAGE, op.child_end - k0);
-        __syncthreads(); // the previous batch is no longer read
-        for (int idx = threadIdx.x; idx < nb * AA_NS * AA_NS; idx += AA_THREADS) {
-            const int c = idx / (AA_NS * AA_NS), e = idx - c * (AA_NS * AA_NS);
-            Pt[c][(e % AA_NS) * AA_NS + e / AA_NS] = Pmat[((size_t)kids[k0 + c].edge * n_cat + cat) * (AA_NS * AA_NS) + e];
+    if (upfront) {
+        for (int idx = threadIdx.x; idx < ncat * nch * AA_NS * AA_NS; idx += AA_THREADS) {
+            const int m = idx / (AA_NS * AA_NS), e = idx - m * (AA_NS * AA_NS); // m = c * nch + child
+            const int c = m / nch, k = m - c * nch;
+            Pt[c * AA_STAGE + k][(e % AA_NS) * AA_NS + e / AA_NS] =
+                Pmat[((size_t)kids[op.child_begin + k].edge * n_cat + cat0 + c) * (AA_NS * AA_NS) + e];
         }
         __syncthreads();
-        for (int c = 0; c < nb; ++c) {
-            const GenChild ch = kids[k0 + c];
-            const double *P_t = Pt[c];
-            double y[AA_NS];
-            if (ch.is_tip) {
-                aa_tip_col(P_t, tips[(int64_t)ch.src * P_pad + tile_off + site], y);
-            } else {
-                const double *x_src = clv + (size_t)ch.src * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
-                ex += exps[((size_t)ch.src * n_cat + cat) * tile_pad + site];
-                const double x0 = x_src[0];
+    }
+    for (int c = 0; c < ncat; ++c) {
+        const int cat = cat0 + c;
+        double acc[AA_NS];
 #pragma unroll
-                for (int i = 0; i < AA_NS; ++i) y[i] = P_t[i] * x0;
-#pragma unroll
-                for (int j = 1; j < AA_NS; ++j) {
-                    const double xj = x_src[(size_t)j * tile_pad];
-#pragma unroll
-                    for (int i = 0; i < AA_NS; ++i) y[i] += P_t[j * AA_NS + i] * xj;
+        for (int i = 0; i < AA_NS; ++i) acc[i] = 1.0;
+        int ex = 0;
+        for (int k0 = 0; k0 < nch; k0 += AA_STAGE) {
+            const int nb = min(AA_STAGE, nch - k0);
+            if (!upfront) {
+                __syncthreads(); // the previous batch is no longer read
+                for (int idx = threadIdx.x; idx < nb * AA_NS * AA_NS; idx += AA_THREADS) {
+                    const int k = idx / (AA_NS * AA_NS), e = idx - k * (AA_NS * AA_NS);
+                    Pt[k][(e % AA_NS) * AA_NS + e / AA_NS] =
+                        Pmat[((size_t)kids[op.child_begin + k0 + k].edge * n_cat + cat) * (AA_NS * AA_NS) + e];
                 }
+                __syncthreads();
             }
+            for (int k = 0; k < nb; ++k) {
+                const GenChild ch = kids[op.child_begin + k0 + k];
+                const double *P_t = upfront ? Pt[c * AA_STAGE + k] : Pt[k];
+                double y[AA_NS];
+                if (ch.is_tip) {
+                    aa_tip_col(P_t, tips[(int64_t)ch.src * P_pad + tile_off + site], y);
+                } else {
+                    const double *x_src = clv + (size_t)ch.src * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
+                    ex += exps[((size_t)ch.src * n_cat + cat) * tile_pad + site];
+                    const double x0 = x_src[0];
 #pragma unroll
-            for (int i = 0; i < AA_NS; ++i) acc[i] *= y[i];
+                    for (int i = 0; i < AA_NS; ++i) y[i] = P_t[i] * x0;
+#pragma unroll
+                    for (int j = 1; j < AA_NS; ++j) {
+                        const double xj = x_src[(size_t)j * tile_pad];
+#pragma unroll
+                        for (int i = 0; i < AA_NS; ++i) y[i] += P_t[j * AA_NS + i] * xj;
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < AA_NS; ++i) acc[i] *= y[i];
+            }
+        }
+        if (active) {
+            ex += aa_normalize(acc);
+            double *dst = clv + (size_t)op.out_slot * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) dst[(size_t)i * tile_pad] = acc[i];
+            exps[((size_t)op.out_slot * n_cat + cat) * tile_pad + site] = ex;
         }
     }
-    if (!active) return;
-    ex += aa_normalize(acc);
-    double *dst = clv + (size_t)op.out_slot * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
-#pragma unroll
-    for (int i = 0; i < AA_NS; ++i) dst[(size_t)i * tile_pad] = acc[i];
-    exps[((size_t)op.out_slot * n_cat + cat) * tile_pad + site] = ex;
 }
 
 // the root's vector for one (pattern, category): its CLV, or its tip profile when the tree is a single leaf
@@ -328,9 +352,17 @@ aa_down_kernel(const AaDown *__restrict__ nodes, const AaModelDev *__restrict__ 
                int64_t P_pad, int64_t tile_off, const double *__restrict__ cat_ll, uint8_t *__restrict__ states,
                double *__restrict__ post_out)
 {
-    __shared__ double Ps[AA_NS * AA_NS];
+    __shared__ double Pall[AA_DCATS][AA_NS * AA_NS];
     const AaDown nd = nodes[blockIdx.y];
     const int n_cat = M->n_cat;
+    // the node's P(t) of every category staged at once behind one barrier (up to AA_DCATS categories; beyond that the
+    // staging goes category by category)
+    const bool upfront = n_cat <= AA_DCATS;
+    if (upfront && nd.parent_slot >= 0) {
+        const double *src = Pmat + (size_t)nd.node * n_cat * (AA_NS * AA_NS);
+        for (int idx = threadIdx.x; idx < n_cat * AA_NS * AA_NS; idx += AA_THREADS) Pall[idx / (AA_NS * AA_NS)][idx % (AA_NS * AA_NS)] = src[idx];
+        __syncthreads();
+    }
     int64_t site[AA_R];
     bool active[AA_R];
     double lse[AA_R];
@@ -347,12 +379,13 @@ aa_down_kernel(const AaDown *__restrict__ nodes, const AaModelDev *__restrict__ 
         for (int i = 0; i < AA_NS; ++i) mixed[r][i] = 0.0;
     }
     for (int c = 0; c < n_cat; ++c) {
-        if (nd.parent_slot >= 0) {
+        if (!upfront && nd.parent_slot >= 0) {
             __syncthreads();
             const double *src = Pmat + ((size_t)nd.node * n_cat + c) * (AA_NS * AA_NS);
-            for (int idx = threadIdx.x; idx < AA_NS * AA_NS; idx += AA_THREADS) Ps[idx] = src[idx];
+            for (int idx = threadIdx.x; idx < AA_NS * AA_NS; idx += AA_THREADS) Pall[0][idx] = src[idx];
             __syncthreads();
         }
+        const double *Ps = upfront ? Pall[c] : Pall[0];
         double mix[AA_R];
 #pragma unroll
         for (int r = 0; r < AA_R; ++r)

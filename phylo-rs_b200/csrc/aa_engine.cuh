@@ -167,7 +167,7 @@ int aa_evaluate(phb_ctx *ctx, bool asr, uint8_t *states_out, double *post_out, d
             const int b = T.ulevel_off[l - 1], n_ops = T.ulevel_off[l] - b;
             for (int o = 0; o < n_ops; o += 65535) { // grid.y limit
                 const int cnt = std::min(65535, n_ops - o);
-                PHB_LAUNCH(aa_clv_kernel, dim3(bx, (unsigned)cnt, (unsigned)K), dim3(AA_THREADS), d.stream, A.uops.as<GenOp>() + b + o,
+                PHB_LAUNCH(aa_clv_kernel, dim3(bx, (unsigned)cnt, (unsigned)((K + AA_CSTAGE - 1) / AA_CSTAGE)), dim3(AA_THREADS), d.stream, A.uops.as<GenOp>() + b + o,
                            A.ukids.as<GenChild>(), K, A.Pmat.as<double>(), A.clv.as<double>(), A.exps.as<int>(), slot_stride,
                            (size_t)tile_pad, tile_len, A.tips.as<uint8_t>(), A.P_pad, off);
                 CHECK_LAUNCH();
