@@ -211,3 +211,82 @@ def check_nni_cache_variants(lib, case):
         workloads.load_into(ctx, case)
         got = ctx.score_nni([m[0] for m in moves], [m[1] for m in moves])
     assert np.all(np.abs(got - full) <= REL_TOL * np.abs(full))
+
+
+def random_tree_case(seed, n_leaves_max=40, n_sites=96):
+    """A random rooted tree of any shape: arities 1..5 mixed, branch lengths from exactly 0 over 1e-8 to 4 (+ a missing
+    one, which the reference reads as 0: likelihood.rs:115-118), a random model of the family and 0-20 % ambiguity codes."""
+    from oracle import parse_newick
+
+    rng = np.random.default_rng(seed)
+    n_leaves = int(rng.integers(2, n_leaves_max + 1))
+    names = [f"t{i}" for i in range(n_leaves)]
+
+    def blen():
+        r = rng.random()
+        if r < 0.06:
+            return ":0"
+        if r < 0.10:
+            return ""  # no branch length
+        if r < 0.18:
+            return f":{10.0 ** rng.uniform(-8, -4):.3e}"
+        if r < 0.24:
+            return f":{rng.uniform(2.0, 4.0):.4f}"
+        return f":{rng.exponential(0.15) + 1e-4:.5f}"
+
+    nodes = [n + blen() for n in names]
+    while len(nodes) > 1:
+        k = int(min(len(nodes), rng.choice([1, 2, 2, 2, 2, 3, 3, 4, 5])))
+        if k == 1 and len(nodes) == 1:
+            break
+        idx = sorted(rng.choice(len(nodes), size=k, replace=False).tolist(), reverse=True)
+        kids = [nodes.pop(i) for i in idx]
+        last = len(nodes) == 0
+        nodes.append("(" + ",".join(kids) + ")" + ("" if last else blen()))
+        if last:
+            break
+    nwk = nodes[0] + ";"
+    tree = parse_newick(nwk)
+    ft = workloads.flatten_fast(tree, names)
+    model = workloads.MODELS[int(rng.integers(len(workloads.MODELS)))]
+    m = workloads.make_model(model)
+    pats = workloads.simulate_patterns(ft, m, n_sites, rng)
+    amb = float(rng.choice([0.0, 0.05, 0.2]))
+    if amb > 0:
+        mask = rng.random(pats.shape) < amb
+        codes = np.frombuffer(workloads.AMBIG, np.uint8)
+        pats[mask] = codes[rng.integers(len(codes), size=int(mask.sum()))]
+    mult = rng.integers(1, 5, size=n_sites).astype(np.uint64)
+    return workloads.Case(tree, ft, m, model, np.ascontiguousarray(pats), mult, names), nwk
+
+
+def check_random_trees(lib, seeds):
+    for seed in seeds:
+        case, nwk = random_tree_case(seed)
+        try:
+            check_lnl(lib, case)
+            check_lnl(lib, case, flags=capi.FLAG_LEVEL_KERNELS)
+            check_asr(lib, case, want_post=True)
+            check_joint(lib, case)
+        except AssertionError as e:
+            raise AssertionError(f"seed {seed}, model {case.model_name}, tree {nwk}: {e}") from e
+
+
+def check_random_trees_amino_acid(lib, seeds):
+    """the same random shapes through the 20-state engines"""
+    for seed in seeds:
+        case, nwk = random_tree_case(seed, n_leaves_max=25, n_sites=40)
+        rng = np.random.default_rng(seed + 10_000)
+        model = workloads.AA_MODELS[int(rng.integers(3))]
+        m = workloads.make_aa_model(model, seed=0xAA20 + seed % 5)
+        pats = workloads.simulate_patterns(case.ft, m, 40, rng)
+        if seed % 2:
+            mask = rng.random(pats.shape) < 0.15
+            codes = np.frombuffer(workloads.AA_AMBIG, np.uint8)
+            pats[mask] = codes[rng.integers(len(codes), size=int(mask.sum()))]
+        c2 = workloads.Case(case.tree, case.ft, m, model, np.ascontiguousarray(pats), case.mult[:40], case.leaf_order)
+        try:
+            check_lnl(lib, c2, flags=capi.FLAG_AMINO_ACID)
+            assert check_asr(lib, c2, want_post=True, flags=capi.FLAG_AMINO_ACID) == 0
+        except AssertionError as e:
+            raise AssertionError(f"seed {seed}, model {model}, tree {nwk}: {e}") from e

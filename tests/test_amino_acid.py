@@ -217,3 +217,12 @@ def test_gpu_deep_tree_scaling(gpu_lib):
     tot, per, _ = _cases.check_lnl(gpu_lib, case, flags=AA)
     assert per.min() < -800  # exp(-800) is below the smallest f64
     assert _cases.check_asr(gpu_lib, case, flags=AA) == 0
+
+
+def test_emu_random_trees(emu_lib):
+    _cases.check_random_trees_amino_acid(emu_lib, range(200, 210))
+
+
+@pytest.mark.gpu
+def test_gpu_random_trees(gpu_lib):
+    _cases.check_random_trees_amino_acid(gpu_lib, range(200, 240))

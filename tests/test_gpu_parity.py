@@ -496,3 +496,8 @@ def test_nonbinary_trees_all_engines(gpu_lib):
 def test_score_nni_cache_variants_and_repeated_calls(gpu_lib):
     case = workloads.make_case(300, 3000, model="gtr_i_g4", seed=77, ambiguity=0.03)
     _cases.check_nni_cache_variants(gpu_lib, case)
+
+
+def test_random_trees_all_engines(gpu_lib):
+    """random shapes (arities 1..5), zero / missing / tiny / long branches, random models, ambiguity, multiplicities"""
+    _cases.check_random_trees(gpu_lib, range(100, 160))

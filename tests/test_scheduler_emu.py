@@ -535,3 +535,8 @@ def test_nonbinary_trees_all_engines(emu_lib):
 def test_score_nni_cache_variants_and_repeated_calls(emu_lib):
     case = workloads.make_case(40, 300, model="gtr_i_g4", seed=77, ambiguity=0.03)
     _cases.check_nni_cache_variants(emu_lib, case)
+
+
+def test_random_trees_all_engines(emu_lib):
+    """random shapes (arities 1..5), zero / missing / tiny / long branches, random models, ambiguity, multiplicities"""
+    _cases.check_random_trees(emu_lib, range(100, 112))
