@@ -96,8 +96,8 @@ aa_transition_kernel(const double *__restrict__ blen, int n_edges, const AaModel
     __syncthreads();
     for (int idx = threadIdx.x; idx < AA_NS * AA_NS; idx += AA_THREADS) {
         const int i = idx / AA_NS, j = idx - i * AA_NS;
-        double acc = (M->V[i] * e[0]) * M->V[j];
-        for (int k = 1; k < AA_NS; ++k) acc += (M->V[i + AA_NS * k] * e[k]) * M->V[j + AA_NS * k];
+        double acc = __dmul_rn(__dmul_rn(M->V[i], e[0]), M->V[j]);
+        for (int k = 1; k < AA_NS; ++k) acc = __dadd_rn(acc, __dmul_rn(__dmul_rn(M->V[i + AA_NS * k], e[k]), M->V[j + AA_NS * k])); // no FMA (kernels.cuh transition_kernel)
         out[idx] = M->inv_sqrt_pi[i] * acc * M->sqrt_pi[j];
     }
 }

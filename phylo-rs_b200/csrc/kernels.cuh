@@ -206,6 +206,11 @@ __global__ void unpack_kernel(const uint8_t *__restrict__ tips, int n_rows, int 
 // P = diag(1/sqrt(pi)) * (V * diag(exp(lambda * r * t))) * V^T * diag(sqrt(pi));
 // exact identity when r * t == 0.0.  Follows GtrModel::category_transition (src/models/gtr.rs:61-64)
 // and RateMatrix::transition (src/models/rate_matrix.rs:113-135).
+// The products and sums are rounded one by one (__dmul_rn / __dadd_rn: the compiler must not contract them into FMAs),
+// as the reference's are: for a branch of ~1e-8 the off-diagonal entries (~1e-10) are what is left of O(1) terms that
+// cancel, one ulp of those terms is 3e-7 of the entry, and a pattern that needs a substitution on such a branch carries
+// that straight into its log-likelihood (2e-8 measured against the oracle with contracted FMAs; found by the random-tree
+// tests).  With the reference's own rounding sequence the entries agree bit for bit wherever exp() does.
 // ---------------------------------------------------------------------------------------------
 __global__ void transition_kernel(const double *__restrict__ blen, int n_nodes, ModelDev M,
                                   double *__restrict__ P)
@@ -227,9 +232,9 @@ __global__ void transition_kernel(const double *__restrict__ blen, int n_nodes, 
     for (int i = 0; i < 4; ++i) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            double acc = (M.V[i + 0] * e[0]) * M.V[j + 0];
+            double acc = __dmul_rn(__dmul_rn(M.V[i + 0], e[0]), M.V[j + 0]);
 #pragma unroll
-            for (int k = 1; k < 4; ++k) acc += (M.V[i + 4 * k] * e[k]) * M.V[j + 4 * k];
+            for (int k = 1; k < 4; ++k) acc = __dadd_rn(acc, __dmul_rn(__dmul_rn(M.V[i + 4 * k], e[k]), M.V[j + 4 * k])); // no FMA: see transition_kernel
             out[i * 4 + j] = M.inv_sqrt_pi[i] * acc * M.sqrt_pi[j];
         }
     }

@@ -957,12 +957,35 @@ int run_sweep(phb_ctx *ctx, Device &d, const ModelDev &M)
 {
     const SweepGeom &G = ctx->sweep_geom;
     const int64_t n_blocks = (d.P + 4 * G.Q - 1) / (4 * G.Q);
-    CU(d.partials.ensure(sizeof(double) * (size_t)std::max<int64_t>(n_blocks, 1)));
+    const int n_sm = std::max(d.sm_count, 1);
+    // A pass of the persistent grid over the op list costs about the same for 9-11 consumer warps, 14 % less for 5-7
+    // and 31 % less for <= 3 (one, two or three warps per scheduler: profiles/r2_pass_time_vs_width.txt), so the
+    // patterns left over after the last FULL pass go out as a launch of their own, just wide enough to take them in one
+    // pass (10k x 1M: the 20th pass holds 10,144 of the 1M patterns; a 125k shard's third pass 20,808).
+    int64_t main_blocks = n_blocks / n_sm * n_sm;
+    SweepGeom tail;
+    int64_t tail_P = 0, tail_blocks = 0;
+    static const bool no_tail = getenv("PHB_SWEEP_NO_TAIL") != nullptr;
+    if (!no_tail && main_blocks > 0 && main_blocks < n_blocks) {
+        tail_P = d.P - main_blocks * 4 * G.Q;
+        const int step = sweep_q_step(M.n_clv);
+        int q_tail = (int)((tail_P + (int64_t)4 * n_sm - 1) / ((int64_t)4 * n_sm));
+        q_tail = (q_tail + step - 1) / step * step;
+        auto warps_per_scheduler = [&](int q) { return (q * M.n_clv / 32 + 1 + 3) / 4; };
+        if (q_tail < G.Q && warps_per_scheduler(q_tail) < warps_per_scheduler(G.Q) && tail.plan(ctx->sweep, d.smem_optin, tail_P, n_sm, q_tail))
+            tail_blocks = (tail_P + 4 * tail.Q - 1) / (4 * tail.Q);
+    }
+    if (tail_blocks == 0) main_blocks = n_blocks;
+    CU(d.partials.ensure(sizeof(double) * (size_t)std::max<int64_t>(main_blocks + tail_blocks, 1)));
     int rc = launch_sweep_transition(ctx, d, M);
     if (rc) return rc;
-    rc = launch_sweep_range(ctx, d, M, G, 0, d.P, 0);
+    rc = launch_sweep_range(ctx, d, M, G, 0, tail_blocks ? main_blocks * 4 * G.Q : d.P, 0);
     if (rc) return rc;
-    return launch_sweep_reduce(ctx, d, (size_t)n_blocks);
+    if (tail_blocks) {
+        rc = launch_sweep_range(ctx, d, M, tail, main_blocks * 4 * G.Q, tail_P, (size_t)main_blocks);
+        if (rc) return rc;
+    }
+    return launch_sweep_reduce(ctx, d, (size_t)(main_blocks + tail_blocks));
 }
 
 // One full evaluation on every device.  asr=false: compute_log_likelihood; asr=true: + down pass.

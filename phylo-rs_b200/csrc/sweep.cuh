@@ -113,9 +113,9 @@ __device__ __forceinline__ void sw_transition(const ModelDev &M, double t, doubl
         for (int i = 0; i < 4; ++i)
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                double acc = (M.V[i + 0] * e[0]) * M.V[j + 0];
+                double acc = __dmul_rn(__dmul_rn(M.V[i + 0], e[0]), M.V[j + 0]);
 #pragma unroll
-                for (int k = 1; k < 4; ++k) acc += (M.V[i + 4 * k] * e[k]) * M.V[j + 4 * k];
+                for (int k = 1; k < 4; ++k) acc = __dadd_rn(acc, __dmul_rn(__dmul_rn(M.V[i + 4 * k], e[k]), M.V[j + 4 * k])); // no FMA: see transition_kernel
                 p[i * 4 + j] = M.inv_sqrt_pi[i] * acc * M.sqrt_pi[j];
             }
     }

@@ -65,6 +65,9 @@ static inline int __double2hiint(double d) { long long v; memcpy(&v, &d, 8); ret
 static inline double __shfl_down_sync(unsigned, double v, unsigned delta) { return emu::shfl_down(v, delta); }
 template <typename T> static inline T __ldg(const T *p) { return *p; }
 static inline int __popc(unsigned v) { return __builtin_popcount(v); }
+// round-to-nearest product / sum that the device compiler may not contract (the harness is built with -ffp-contract=off)
+static inline double __dmul_rn(double a, double b) { return a * b; }
+static inline double __dadd_rn(double a, double b) { return a + b; }
 static inline double __longlong_as_double(long long v) { double d; memcpy(&d, &v, 8); return d; }
 static inline int atomicAdd(int *p, int v) { int o = *p; *p += v; return o; }
 static inline unsigned atomicOr(unsigned *p, unsigned v) { unsigned o = *p; *p |= v; return o; }
