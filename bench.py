@@ -344,7 +344,8 @@ def run_gpu(args, rank, world, local_rank):
             src = os.path.join(ROOT, "phylo-rs_b200", "csrc", tj.get("source_file", "sweep.cuh"))
             sha = hashlib.sha256(open(src, "rb").read()).hexdigest()
             if tj.get("patterns") and tj.get("source_sha256") == sha:
-                traffic = tj["dram_bytes_per_launch"] * (cnt / tj["patterns"]) * (N_TAXA / tj["taxa"])
+                per_eval = tj.get("dram_bytes_per_evaluation", tj["dram_bytes_per_launch"])  # all launches of one evaluation
+                traffic = per_eval * (cnt / tj["patterns"]) * (N_TAXA / tj["taxa"]) / max(st["clv_launches"], 1)
                 traffic_note = f"ncu capture {tj.get('capture')} of {tj.get('source_file')} at {sha[:12]}"
             else:
                 traffic_note = "no ncu capture on file for the current kernel source (profiles/traffic.json is for another revision)"

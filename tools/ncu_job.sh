@@ -5,7 +5,8 @@
 set -x
 T=${1:-r2f}
 export PHB_BENCH_KERNEL_ONLY=1
-python bench.py --steps 1 --warmup 3 --no-cpu > gpurun_out/plain1.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:sweep_kernel -s 3 -c 1 -o gpurun_out/${T}_sweep python bench.py --steps 1 --warmup 3 --no-cpu > gpurun_out/ncu1.log 2>&1
+# (an evaluation = two sweep launches, the full passes and the narrower rest: launches 2 and 3 are the second evaluation)
+python bench.py --steps 1 --warmup 3 --no-cpu > gpurun_out/plain1.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:sweep_kernel -s 2 -c 2 -o gpurun_out/${T}_sweep python bench.py --steps 1 --warmup 3 --no-cpu > gpurun_out/ncu1.log 2>&1
 unset PHB_BENCH_KERNEL_ONLY
 python bench.py --steps 2 --warmup 3 --no-cpu --no-configs > gpurun_out/plain2.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${T}_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu --no-configs > gpurun_out/ncu2.log 2>&1
 python tools/configs_bench.py --cases cfg4_small --reps 1 > gpurun_out/plain3.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:asr_down_sweep -s 1 -c 1 -o gpurun_out/${T}_down python tools/configs_bench.py --cases cfg4_small --reps 1 > gpurun_out/ncu3.log 2>&1

@@ -17,24 +17,40 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("report")
+    ap.add_argument("report", nargs="+", help="one or more reports; launches whose DRAM counters ncu left as NaN are skipped")
     ap.add_argument("--kernel", default="sweep_kernel")
     ap.add_argument("--source", default="sweep.cuh")
     ap.add_argument("--taxa", type=int, default=10_000)
     ap.add_argument("--patterns", type=int, default=1_000_000)
     args = ap.parse_args()
-    out = subprocess.run(["ncu", "-i", args.report, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
-    rows = list(csv.reader(out.splitlines()))
-    hdr, units, data = rows[0], rows[1], rows[2]
-    col = {h: i for i, h in enumerate(hdr)}
+    import math
 
-    def val(name):
-        v = float(data[col[name]].replace(",", ""))
-        u = units[col[name]].lower()
-        return v * {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9, "tbyte": 1e12,
-                    "ns": 1e-6, "nsecond": 1e-6, "us": 1e-3, "usecond": 1e-3, "ms": 1, "msecond": 1, "s": 1e3, "second": 1e3}.get(u, 1)
+    scale = {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9, "tbyte": 1e12,
+             "ns": 1e-6, "nsecond": 1e-6, "us": 1e-3, "usecond": 1e-3, "ms": 1, "msecond": 1, "s": 1e3, "second": 1e3}
+    launches = []  # (read bytes, written bytes, ms, grid) of every launch with valid DRAM counters
+    for rep in args.report:
+        out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+        rows = list(csv.reader(out.splitlines()))
+        hdr, units = rows[0], rows[1]
+        col = {h: i for i, h in enumerate(hdr)}
 
-    rd, wr = val("dram__bytes_read.sum"), val("dram__bytes_write.sum")
+        def val(name, data):
+            return float(data[col[name]].replace(",", "")) * scale.get(units[col[name]].lower(), 1)
+
+        for r in rows[2:]:
+            if len(r) <= col["dram__bytes_read.sum"]:
+                continue
+            try:
+                rd_ = val("dram__bytes_read.sum", r)
+            except ValueError:
+                continue
+            if math.isnan(rd_):
+                continue  # ncu left the counters of this launch empty
+            launches.append((rd_, val("dram__bytes_write.sum", r), val("gpu__time_duration.sum", r), r[col["Grid Size"]]))
+    # one evaluation = every captured launch (the sweep goes out as the full passes + a narrower launch for the rest)
+    rd = sum(l[0] for l in launches)
+    wr = sum(l[1] for l in launches)
+    dur = sum(l[2] for l in launches)
     src = os.path.join(ROOT, "phylo-rs_b200", "csrc", args.source)
     path = os.path.join(ROOT, "profiles", "traffic.json")
     try:
@@ -42,9 +58,10 @@ def main():
     except Exception:
         tj = {}
     tj[args.kernel] = {
-        "dram_bytes_per_launch": rd + wr, "dram_read": rd, "dram_write": wr, "patterns": args.patterns, "taxa": args.taxa,
-        "duration_ms_under_ncu": val("gpu__time_duration.sum") if "gpu__time_duration.sum" in col else None,
-        "capture": os.path.basename(args.report), "source_file": args.source,
+        "dram_bytes_per_evaluation": rd + wr, "launches_per_evaluation": len(launches),
+        "dram_bytes_per_launch": (rd + wr) / max(len(launches), 1), "dram_read": rd, "dram_write": wr,
+        "patterns": args.patterns, "taxa": args.taxa, "duration_ms_under_ncu": dur,
+        "capture": " + ".join(os.path.basename(r) for r in args.report), "grids": [l[3] for l in launches], "source_file": args.source,
         "source_sha256": hashlib.sha256(open(src, "rb").read()).hexdigest(),
     }
     json.dump(tj, open(path, "w"), indent=1)
