@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """One-off parity hunt on the GPU (not part of the test suite): random trees through every engine against the oracle,
-random NNI move sets, random 20-state cases.  Prints one line per failing seed.
+random NNI move sets, random 20-state cases, deep trees, compression and the host-streaming call.  Prints one line per failing seed.
 
   python tools/fuzz_gpu.py [--seeds 0:600] [--aa 0:200] [--nni 0:100]"""
 import argparse
@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--aa", default="0:200")
     ap.add_argument("--nni", default="0:100")
     ap.add_argument("--deep", default="0:0")
+    ap.add_argument("--misc", default="0:0")
     args = ap.parse_args()
     lib = capi.default_library()
     bad = 0
@@ -89,6 +90,55 @@ def main():
         except Exception as e:
             bad += 1
             print("FAIL deep", seed, n, mean, model, shape, str(e)[:300], flush=True)
+    # column compression on random alignments (any byte values, repeated columns, both entry points) against the
+    # first-appearance numbering; the host-streaming call against the resident one and the oracle, over random sizes,
+    # virtual ranks and CLV budgets
+    import oracle
+
+    for seed in rng_of(args.misc):
+        rng = np.random.default_rng(seed)
+        try:
+            # ---- compression: random alignment with repeated columns, any byte values
+            n_rows = int(rng.integers(1, 40)); width = int(rng.integers(0, 3000)); distinct = int(rng.integers(1, max(2, width // 3 + 2)))
+            alphabet = np.frombuffer(b"ACGT-NRYKM?xz", np.uint8) if seed % 3 else np.arange(256, dtype=np.uint8)
+            cols = alphabet[rng.integers(len(alphabet), size=(distinct, n_rows))]
+            pick = rng.integers(distinct, size=width)
+            mat = np.ascontiguousarray(cols[pick].T) if width else np.zeros((n_rows, 0), np.uint8)
+            # reference numbering: first appearance
+            idx, s2p_ref, mult_ref, pats_ref = {}, [], [], []
+            for i in range(width):
+                key = mat[:, i].tobytes()
+                j = idx.setdefault(key, len(idx))
+                if j == len(pats_ref):
+                    pats_ref.append(mat[:, i]); mult_ref.append(0)
+                mult_ref[j] += 1; s2p_ref.append(j)
+            with capi.Context(library=lib) as ctx:
+                if seed % 2:
+                    n, s2p, mult = ctx.compress_columns(mat)
+                else:
+                    n, s2p, mult = ctx.compress_rows([mat[r].tobytes() for r in range(n_rows)])
+                assert n == len(pats_ref), ("n_patterns", n, len(pats_ref))
+                assert np.array_equal(s2p.astype(np.int64), np.asarray(s2p_ref, np.int64)), "s2p"
+                assert np.array_equal(mult.astype(np.int64), np.asarray(mult_ref, np.int64)), "mult"
+            # ---- host-streaming lnL == resident lnL == oracle, random sizes, virtual ranks, budgets
+            case = workloads.make_case(int(rng.integers(3, 50)), int(rng.integers(1, 2500)), model=workloads.MODELS[int(rng.integers(6))], seed=seed, ambiguity=float(rng.choice([0, 0.1])))
+            ref_tot, ref_per = oracle.log_likelihood_flat(case.ft, case.model, case.patterns, case.mult, mode=2, n_threads=8)
+            devs = [0] * int(rng.integers(1, 4))
+            with capi.Context(devices=devs, library=lib) as ctx:
+                if seed % 4 == 0:
+                    ctx.set_clv_budget(int(rng.integers(8, 64)) * 1_000_000)
+                m, ft = case.model, case.ft
+                ctx.set_model(m.eigenvalues, m.eigenvectors, m.pi, m.sqrt_pi, m.inv_sqrt_pi, m.rates, m.weights)
+                ctx.set_tree(ft["postorder"], ft["child_off"], ft["children"], ft["blen"], ft["leaf_row"], ft["root"])
+                tot_h, per_h = ctx.log_likelihood_host(case.patterns, multiplicity=case.mult, per_pattern=True)
+                _cases.assert_lnl_close(tot_h, per_h, ref_tot, ref_per)
+                tot_r, per_r = ctx.log_likelihood(per_pattern=True)
+                assert np.array_equal(per_r, per_h), "resident vs streamed per-pattern"
+                tot_a, st, _ = ctx.marginal_asr()
+                assert abs(tot_a - ref_tot) <= 1e-9 * abs(ref_tot)
+        except Exception as e:
+            bad += 1
+            print("FAIL misc", seed, type(e).__name__, str(e)[:300], flush=True)
     print("fuzz done, failures:", bad)
 
 
