@@ -11,8 +11,6 @@ unset PHB_BENCH_KERNEL_ONLY
 python bench.py --steps 2 --warmup 3 --no-cpu --no-configs > gpurun_out/plain2.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${T}_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu --no-configs > gpurun_out/ncu2.log 2>&1
 python tools/configs_bench.py --cases cfg4_small --reps 1 > gpurun_out/plain3.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:asr_down_sweep -s 1 -c 1 -o gpurun_out/${T}_down python tools/configs_bench.py --cases cfg4_small --reps 1 > gpurun_out/ncu3.log 2>&1
 python tools/configs_bench.py --cases cfg5 --reps 1 > gpurun_out/plain4.log 2>&1 && ncu --set full --clock-control none -k regex:nni_edge_kernel -s 1 -c 1 -o gpurun_out/${T}_nni_edge python tools/configs_bench.py --cases cfg5 --reps 1 > gpurun_out/ncu4.log 2>&1
-# the NNI cache pass: the storing sweep of config 5 (third launch: after the warm-up calls)
-ncu --set full --clock-control none -k regex:sweep_kernel -s 6 -c 1 -o gpurun_out/${T}_nni_cache_sweep python tools/configs_bench.py --cases cfg5 --reps 1 > gpurun_out/ncu5.log 2>&1
 # 20-state CLV kernel: the launches of one evaluation (a launch per tree level), time only, then the longest in full
 python tools/aa_bench.py --taxa 1000 --patterns 20000 --reps 1 > gpurun_out/plain6.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -k regex:aa_ -c 200 --csv --log-file gpurun_out/${T}_aa_launches.csv python tools/aa_bench.py --taxa 1000 --patterns 20000 --reps 1 > gpurun_out/ncu6.log 2>&1
-for f in gpurun_out/ncu1.log gpurun_out/ncu3.log gpurun_out/ncu4.log gpurun_out/ncu5.log gpurun_out/ncu6.log; do tail -n 2 $f | cut -c1-300; done
+for f in gpurun_out/ncu1.log gpurun_out/ncu3.log gpurun_out/ncu4.log gpurun_out/ncu6.log; do tail -n 2 $f | cut -c1-300; done
