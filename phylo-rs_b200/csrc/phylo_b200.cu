@@ -21,7 +21,11 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <condition_variable>
+#include <functional>
+#include <memory>
 #include <mutex>
+#include <thread>
 #include <string>
 #include <chrono>
 #include <vector>
@@ -237,6 +241,102 @@ struct EventPair {
     cudaEvent_t a = nullptr, b = nullptr;
 };
 
+// bytes per pinned bounce buffer (two per device); PHB_BOUNCE_BYTES shrinks it so that tests walk through many slices
+inline size_t bounce_bytes()
+{
+    static const size_t v = [] {
+        const char *e = getenv("PHB_BOUNCE_BYTES");
+        const long long n = e ? atoll(e) : 0;
+        return n >= 4096 ? (size_t)n / 4096 * 4096 : (size_t)32 << 20;
+    }();
+    return v;
+}
+
+// Host threads that copy slices of a caller's PAGEABLE buffer into pinned bounce buffers (h2d_from_host): the driver's own
+// path for pageable memory stages through one thread at about 11 GB/s, a fifth of what the link takes from pinned memory.
+struct CopyPool {
+    std::vector<std::thread> workers;
+    std::mutex m;
+    std::condition_variable cv, done_cv;
+    struct Task { const uint8_t *src; uint8_t *dst; size_t n; };
+    std::vector<Task> tasks;
+    size_t pending = 0;
+    bool stop = false;
+    explicit CopyPool(int n)
+    {
+        for (int i = 0; i < n; ++i)
+            workers.emplace_back([this] {
+                for (;;) {
+                    Task t;
+                    {
+                        std::unique_lock<std::mutex> lk(m);
+                        cv.wait(lk, [this] { return stop || !tasks.empty(); });
+                        if (tasks.empty()) return; // stop
+                        t = tasks.back();
+                        tasks.pop_back();
+                    }
+                    memcpy(t.dst, t.src, t.n);
+                    {
+                        std::lock_guard<std::mutex> lk(m);
+                        if (--pending == 0) done_cv.notify_all();
+                    }
+                }
+            });
+    }
+    ~CopyPool()
+    {
+        {
+            std::lock_guard<std::mutex> lk(m);
+            stop = true;
+        }
+        cv.notify_all();
+        for (std::thread &t : workers) t.join();
+    }
+    // every task of `list`, the last ones by the calling thread while it waits
+    void run(std::vector<Task> &list)
+    {
+        if (workers.empty() || list.size() < 2) {
+            for (const Task &t : list) memcpy(t.dst, t.src, t.n);
+            return;
+        }
+        Task own = list.back();
+        list.pop_back();
+        {
+            std::lock_guard<std::mutex> lk(m);
+            for (const Task &t : list) {
+                tasks.push_back(t);
+                ++pending;
+            }
+        }
+        cv.notify_all();
+        memcpy(own.dst, own.src, own.n);
+        std::unique_lock<std::mutex> lk(m);
+        done_cv.wait(lk, [this] { return pending == 0; });
+    }
+    // dst[0..n) = src[0..n), split over the workers and the calling thread
+    void copy(uint8_t *dst, const uint8_t *src, size_t n)
+    {
+        const size_t parts = workers.size() + 1;
+        const size_t slice = (n / parts + 4095) / 4096 * 4096;
+        if (workers.empty() || n < std::min<size_t>((size_t)1 << 20, bounce_bytes() / 2) || slice == 0) {
+            memcpy(dst, src, n);
+            return;
+        }
+        size_t own = std::min(slice, n);
+        {
+            std::lock_guard<std::mutex> lk(m);
+            for (size_t off = own; off < n; off += slice) {
+                tasks.push_back({src + off, dst + off, std::min(slice, n - off)});
+                ++pending;
+            }
+        }
+        cv.notify_all();
+        memcpy(dst, src, own);
+        std::unique_lock<std::mutex> lk(m);
+        done_cv.wait(lk, [this] { return pending == 0; });
+    }
+};
+
 struct Device {
     int ordinal = 0;
     cudaStream_t stream = nullptr;
@@ -254,6 +354,9 @@ struct Device {
     DevBuf staging2;                             // second staging buffer (double buffering)
     cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
     double *h_total = nullptr; // pinned
+    uint8_t *bounce[2] = {nullptr, nullptr};           // pinned, bounce_bytes() each: pageable host input goes through them
+    cudaEvent_t ev_bounce[2] = {nullptr, nullptr};     // the DMA out of bounce[i] has finished
+    uint64_t bounce_uses = 0;                          // slices sent so far: slice k uses bounce[k & 1]
     cudaEvent_t tm_a = nullptr, tm_b = nullptr; // phb_timer_start / phb_timer_stop
     int64_t tile_pad = 0;
     int n_tiles = 0;
@@ -312,6 +415,7 @@ struct phb_ctx {
     // stats
     phb_stats stats;
     int64_t launches = 0;
+    std::unique_ptr<CopyPool> copy_pool; // created by the first call that is handed pageable memory
     // 20 states (PHB_FLAG_AMINO_ACID)
     bool is_aa = false;
     AaState aa;
@@ -1736,6 +1840,10 @@ void phb_ctx_destroy(phb_ctx *ctx)
             cudaEventDestroy(ep.b);
         }
         if (d.h_total) cudaFreeHost(d.h_total);
+        for (int i = 0; i < 2; ++i) {
+            if (d.bounce[i]) cudaFreeHost(d.bounce[i]);
+            if (d.ev_bounce[i]) cudaEventDestroy(d.ev_bounce[i]);
+        }
         if (d.tm_a) cudaEventDestroy(d.tm_a);
         if (d.tm_b) cudaEventDestroy(d.tm_b);
         d.staging2.release();
@@ -1790,9 +1898,90 @@ namespace {
 // interior bound a multiple of 64.
 // `begin` puts the copies of the first two chunks on the wire and returns how many it issued, so that a
 // caller can do its host-side preparation (schedules, uploads) under them; the main loop then skips those.
+// Is this host pointer plain (unregistered, pageable) memory?  A Rust caller's Vec<u8> is.
+bool host_is_pageable(const void *p)
+{
+    if (const char *e = getenv("PHB_FORCE_BOUNCE")) return atoi(e) != 0; // tests: take the bounce path (1) / never (0)
+#ifdef PHB_HOST_EMU
+    (void)p;
+    return false;
+#else
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeUnregistered;
+#endif
+}
+
+// dst (device) <- src (host), `bytes`, in order on `stream`.  Pinned source: one asynchronous copy.  Pageable source:
+// slices are copied by the pool's threads into two pinned bounce buffers and leave from there, the host copy of slice
+// k + 1 overlapping the DMA of slice k; the call returns when the last slice has been handed to the stream.
+int h2d_from_host(phb_ctx *ctx, Device &d, uint8_t *dst, const uint8_t *src, size_t bytes, cudaStream_t stream, bool pageable)
+{
+    if (!pageable) {
+        if (bytes) CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, stream));
+        return PHB_OK;
+    }
+    if (!ctx->copy_pool) {
+        int n = 7;
+        if (const char *e = getenv("PHB_COPY_THREADS")) n = std::max(0, atoi(e) - 1);
+        n = std::min<int>(n, std::max(0, (int)std::thread::hardware_concurrency() - 1));
+        ctx->copy_pool.reset(new CopyPool(n));
+    }
+    for (int i = 0; i < 2; ++i)
+        if (!d.bounce[i]) {
+            CU(cudaHostAlloc((void **)&d.bounce[i], bounce_bytes(), cudaHostAllocDefault));
+            CU(cudaEventCreate(&d.ev_bounce[i]));
+        }
+    for (size_t off = 0; off < bytes; off += bounce_bytes()) {
+        const size_t n = std::min(bounce_bytes(), bytes - off);
+        const int b = (int)(d.bounce_uses & 1);
+        if (d.bounce_uses >= 2) CU(cudaEventSynchronize(d.ev_bounce[b])); // the DMA that last read this bounce buffer
+        ctx->copy_pool->copy(d.bounce[b], src + off, n);
+        CU(cudaMemcpyAsync(dst + off, d.bounce[b], n, cudaMemcpyHostToDevice, stream));
+        CU(cudaEventRecord(d.ev_bounce[b], stream));
+        ++d.bounce_uses;
+    }
+    return PHB_OK;
+}
+
+// The same for `nr` separate host rows of `W` bytes each (row r at rows(r)) going to dst + r * pitch: as many rows as fit
+// are gathered into a bounce buffer, one memcpy task per row, and leave as one (2-D) copy.
+template <class RowPtr>
+int h2d_rows_from_host(phb_ctx *ctx, Device &d, uint8_t *dst, size_t pitch, RowPtr rows, size_t W, int nr, cudaStream_t stream,
+                       bool pageable)
+{
+    if (!pageable || W == 0 || W > bounce_bytes()) {
+        for (int r = 0; r < nr; ++r) {
+            int rc = h2d_from_host(ctx, d, dst + (size_t)r * pitch, rows(r), W, stream, pageable);
+            if (rc) return rc;
+        }
+        return PHB_OK;
+    }
+    int rc = h2d_from_host(ctx, d, dst, rows(0), 0, stream, true); // pool and bounce buffers exist from here on
+    if (rc) return rc;
+    const int per_slice = (int)std::max<size_t>(1, bounce_bytes() / W);
+    std::vector<CopyPool::Task> list;
+    for (int r0 = 0; r0 < nr; r0 += per_slice) {
+        const int m = std::min(per_slice, nr - r0);
+        const int b = (int)(d.bounce_uses & 1);
+        if (d.bounce_uses >= 2) CU(cudaEventSynchronize(d.ev_bounce[b]));
+        list.clear();
+        for (int r = 0; r < m; ++r) list.push_back({rows(r0 + r), d.bounce[b] + (size_t)r * W, W});
+        ctx->copy_pool->run(list);
+        CU(cudaMemcpy2DAsync(dst + (size_t)r0 * pitch, pitch, d.bounce[b], W, W, (size_t)m, cudaMemcpyHostToDevice, stream));
+        CU(cudaEventRecord(d.ev_bounce[b], stream));
+        ++d.bounce_uses;
+    }
+    return PHB_OK;
+}
+
 int stream_pattern_major_begin(phb_ctx *ctx, Device &d, const uint8_t *bytes, int n_rows, const std::vector<int64_t> &bounds,
                                int *issued)
 {
+    const bool pageable = host_is_pageable(bytes);
     size_t max_bytes = 0;
     for (size_t c = 0; c + 1 < bounds.size(); ++c) max_bytes = std::max(max_bytes, (size_t)(bounds[c + 1] - bounds[c]) * n_rows);
     CU(d.staging.ensure(max_bytes));
@@ -1806,8 +1995,8 @@ int stream_pattern_major_begin(phb_ctx *ctx, Device &d, const uint8_t *bytes, in
         const int64_t c0 = bounds[c], np = bounds[c + 1] - c0;
         if (np > 0) {
             uint8_t *st = (buf ? d.staging2 : d.staging).as<uint8_t>();
-            CU(cudaMemcpyAsync(st, bytes + (size_t)(d.p_begin + c0) * n_rows, (size_t)np * n_rows, cudaMemcpyHostToDevice,
-                               d.copy_stream));
+            int rc = h2d_from_host(ctx, d, st, bytes + (size_t)(d.p_begin + c0) * n_rows, (size_t)np * n_rows, d.copy_stream, pageable);
+            if (rc) return rc;
             CU(cudaEventRecord(d.ev_copied[buf], d.copy_stream));
         }
         *issued = (int)c + 1;
@@ -1823,6 +2012,7 @@ int stream_pattern_major(phb_ctx *ctx, Device &d, const uint8_t *bytes, int n_ro
         int rc0 = stream_pattern_major_begin(ctx, d, bytes, n_rows, bounds, &issued);
         if (rc0) return rc0;
     }
+    const bool pageable = host_is_pageable(bytes);
     for (size_t c = 0; c + 1 < bounds.size(); ++c) {
         const int buf = (int)(c & 1);
         const int64_t c0 = bounds[c], np = bounds[c + 1] - c0;
@@ -1830,8 +2020,8 @@ int stream_pattern_major(phb_ctx *ctx, Device &d, const uint8_t *bytes, int n_ro
         uint8_t *st = (buf ? d.staging2 : d.staging).as<uint8_t>();
         if ((int)c >= issued) {
             if (c >= 2) CU(cudaStreamWaitEvent(d.copy_stream, d.ev_free[buf], 0));
-            CU(cudaMemcpyAsync(st, bytes + (size_t)(d.p_begin + c0) * n_rows, (size_t)np * n_rows, cudaMemcpyHostToDevice,
-                               d.copy_stream));
+            int rc1 = h2d_from_host(ctx, d, st, bytes + (size_t)(d.p_begin + c0) * n_rows, (size_t)np * n_rows, d.copy_stream, pageable);
+            if (rc1) return rc1;
             CU(cudaEventRecord(d.ev_copied[buf], d.copy_stream));
         }
         CU(cudaStreamWaitEvent(d.stream, d.ev_copied[buf], 0));
@@ -1992,6 +2182,8 @@ static int32_t compress_impl(phb_ctx *ctx, int32_t n_rows, int64_t width, const 
         ~Cleanup() { for (size_t i = 0; i < n; ++i) b[i]->release(); }
     } cleanup{all, sizeof all / sizeof all[0]};
     const size_t W = (size_t)width;
+    // a caller's Vec<u8> rows are pageable memory: they go through the pinned bounce buffers (h2d_rows_from_host)
+    const bool pageable = width > 0 && n_rows > 0 && host_is_pageable(bytes ? (const void *)bytes : (const void *)row_ptrs[0]);
     CU(raw.ensure((size_t)rows_alloc * (size_t)pitch));
     CU(hash.ensure(sizeof(uint64_t) * W));
     CU(keys.ensure(sizeof(uint64_t) * W));
@@ -2029,13 +2221,15 @@ static int32_t compress_impl(phb_ctx *ctx, int32_t n_rows, int64_t width, const 
         for (int r0 = 0, ci = 0; r0 < std::max(n_rows, 1); r0 += rows_per_chunk, ++ci) {
             const int nr = std::min(rows_per_chunk, n_rows - r0);
             if (attempt == 0 && nr > 0) {
-                if (bytes)
+                if (bytes && !pageable)
                     CU(cudaMemcpy2DAsync(raw.as<uint8_t>() + (size_t)r0 * pitch, (size_t)pitch, bytes + (size_t)r0 * W, W, W,
                                          (size_t)nr, cudaMemcpyHostToDevice, d0.copy_stream));
-                else
-                    for (int r = r0; r < r0 + nr; ++r)
-                        CU(cudaMemcpyAsync(raw.as<uint8_t>() + (size_t)r * pitch, row_ptrs[r], W, cudaMemcpyHostToDevice,
-                                           d0.copy_stream));
+                else {
+                    int rcc = h2d_rows_from_host(ctx, d0, raw.as<uint8_t>() + (size_t)r0 * pitch, (size_t)pitch,
+                                                 [&](int r) { return bytes ? bytes + (size_t)(r0 + r) * W : row_ptrs[r0 + r]; }, W, nr,
+                                                 d0.copy_stream, pageable);
+                    if (rcc) return rcc;
+                }
                 cudaEvent_t e;
                 CU(cudaEventCreate(&e));
                 chunk_events.push_back(e);

@@ -111,6 +111,7 @@ cudaError_t cudaEventCreate(cudaEvent_t *e);
 cudaError_t cudaEventDestroy(cudaEvent_t e);
 cudaError_t cudaEventRecord(cudaEvent_t e, cudaStream_t s);
 cudaError_t cudaStreamWaitEvent(cudaStream_t s, cudaEvent_t e, unsigned flags = 0);
+inline cudaError_t cudaEventSynchronize(cudaEvent_t) { return cudaSuccess; } // the emulation executes in issue order
 cudaError_t cudaEventElapsedTime(float *ms, cudaEvent_t a, cudaEvent_t b);
 cudaError_t cudaGetLastError();
 const char *cudaGetErrorString(cudaError_t e);

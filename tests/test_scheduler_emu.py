@@ -540,3 +540,40 @@ def test_score_nni_cache_variants_and_repeated_calls(emu_lib):
 def test_random_trees_all_engines(emu_lib):
     """random shapes (arities 1..5), zero / missing / tiny / long branches, random models, ambiguity, multiplicities"""
     _cases.check_random_trees(emu_lib, range(100, 112))
+
+
+def test_host_call_from_pageable_memory_bounce_path():
+    """phb_log_likelihood_host / phb_set_alignment handed pageable memory: slices go through two pinned bounce buffers filled
+    by the copy pool.  A fresh process with tiny bounce buffers (many slices per chunk) and three copy threads must give the
+    resident path's per-pattern values."""
+    import os
+    import subprocess
+    import sys
+    import textwrap
+
+    ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = textwrap.dedent("""
+        import sys, numpy as np
+        sys.path.insert(0, %r); sys.path.insert(0, %r)
+        import __graft_entry__ as g
+        from oracle import workloads
+        from phylo_rs_b200 import capi
+        lib = capi.Library(g.build_emu())
+        case = workloads.make_case(23, 5000, model="gtr_i_g4", seed=3, ambiguity=0.05)
+        m, ft = case.model, case.ft
+        with capi.Context(devices=[0, 0], library=lib) as ctx:
+            ctx.set_model(m.eigenvalues, m.eigenvectors, m.pi, m.sqrt_pi, m.inv_sqrt_pi, m.rates, m.weights)
+            ctx.set_tree(ft["postorder"], ft["child_off"], ft["children"], ft["blen"], ft["leaf_row"], ft["root"])
+            tot_h, per_h = ctx.log_likelihood_host(case.patterns, multiplicity=case.mult, per_pattern=True)
+            ctx.set_alignment(case.patterns, multiplicity=case.mult)
+            tot_r, per_r = ctx.log_likelihood(per_pattern=True)
+            back = ctx.get_alignment()
+        assert np.array_equal(per_h, per_r) and abs(tot_h - tot_r) <= 1e-12 * abs(tot_r)
+        canon = case.patterns.copy()
+        canon[canon == ord("U")] = ord("T")  # get_alignment returns the canonical letter of a code
+        assert np.array_equal(back, canon)
+        print("bounce ok")
+    """) % (ROOT, os.path.join(ROOT, "tests"))
+    env = dict(os.environ, PHB_FORCE_BOUNCE="1", PHB_BOUNCE_BYTES="8192", PHB_COPY_THREADS="3")
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "bounce ok" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
