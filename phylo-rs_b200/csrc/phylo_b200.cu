@@ -2116,8 +2116,15 @@ int32_t phb_set_alignment(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns, cons
                 CU(d.staging.ensure((size_t)rr * d.P));
                 for (int64_t r0 = 0; r0 < n_rows; r0 += rr) {
                     int64_t nr = std::min<int64_t>(rr, n_rows - r0);
-                    CU(cudaMemcpy2DAsync(d.staging.p, (size_t)d.P, bytes + (size_t)r0 * n_patterns + d.p_begin,
-                                         (size_t)n_patterns, (size_t)d.P, (size_t)nr, cudaMemcpyHostToDevice, d.stream));
+                    if (!host_is_pageable(bytes))
+                        CU(cudaMemcpy2DAsync(d.staging.p, (size_t)d.P, bytes + (size_t)r0 * n_patterns + d.p_begin,
+                                             (size_t)n_patterns, (size_t)d.P, (size_t)nr, cudaMemcpyHostToDevice, d.stream));
+                    else {
+                        rc = h2d_rows_from_host(ctx, d, d.staging.as<uint8_t>(), (size_t)d.P,
+                                                [&](int r) { return bytes + (size_t)(r0 + r) * n_patterns + d.p_begin; }, (size_t)d.P,
+                                                (int)nr, d.stream, true);
+                        if (rc) return rc;
+                    }
                     dim3 grid((unsigned)std::min<int64_t>((d.P + 255) / 256, 4096), (unsigned)nr);
                     PHB_LAUNCH(pack_row_major_kernel, grid, dim3(256), d.stream, d.staging.as<uint8_t>(), (int)nr, d.P,
                                d.P, (int64_t)0, d.tips.as<uint8_t>() + (size_t)r0 * d.P_pad, d.P_pad, (int64_t)0,
