@@ -252,6 +252,9 @@ inline size_t bounce_bytes()
     return v;
 }
 
+// pageable copies below this size take the driver's path (0 in the tests' tiny-buffer mode)
+inline size_t bounce_min_bytes() { return getenv("PHB_BOUNCE_BYTES") ? 0 : (size_t)16 << 20; }
+
 // Host threads that copy slices of a caller's PAGEABLE buffer into pinned bounce buffers (h2d_from_host): the driver's own
 // path for pageable memory stages through one thread at about 11 GB/s, a fifth of what the link takes from pinned memory.
 struct CopyPool {
@@ -1920,7 +1923,8 @@ bool host_is_pageable(const void *p)
 // k + 1 overlapping the DMA of slice k; the call returns when the last slice has been handed to the stream.
 int h2d_from_host(phb_ctx *ctx, Device &d, uint8_t *dst, const uint8_t *src, size_t bytes, cudaStream_t stream, bool pageable)
 {
-    if (!pageable) {
+    // small inputs are not worth the pool and the 64 MB of pinned memory: the driver's own staging is fine for them
+    if (!pageable || (bytes && bytes < bounce_min_bytes() && !d.bounce[0])) {
         if (bytes) CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, stream));
         return PHB_OK;
     }
@@ -1953,7 +1957,7 @@ template <class RowPtr>
 int h2d_rows_from_host(phb_ctx *ctx, Device &d, uint8_t *dst, size_t pitch, RowPtr rows, size_t W, int nr, cudaStream_t stream,
                        bool pageable)
 {
-    if (!pageable || W == 0 || W > bounce_bytes()) {
+    if (!pageable || W == 0 || W > bounce_bytes() || (W * (size_t)nr < bounce_min_bytes() && !d.bounce[0])) {
         for (int r = 0; r < nr; ++r) {
             int rc = h2d_from_host(ctx, d, dst + (size_t)r * pitch, rows(r), W, stream, pageable);
             if (rc) return rc;
