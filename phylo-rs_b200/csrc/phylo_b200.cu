@@ -1095,6 +1095,10 @@ int run_sweep(phb_ctx *ctx, Device &d, const ModelDev &M)
     return launch_sweep_reduce(ctx, d, (size_t)(main_blocks + tail_blocks));
 }
 
+bool host_is_pageable(const void *p);
+int d2h_rows_to_pageable(phb_ctx *ctx, Device &d, uint8_t *dst, size_t dst_pitch, const uint8_t *src, size_t src_pitch, size_t width,
+                         int height, cudaStream_t stream);
+
 // One full evaluation on every device.  asr=false: compute_log_likelihood; asr=true: + down pass.
 int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint = false)
 {
@@ -1198,6 +1202,20 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
                 if (rc) return rc;
             }
         }
+        const int64_t Ptot_out = ctx->n_patterns;
+        const bool out_pageable = asr && ctx->asr_states_out && (size_t)T.n * (size_t)d.P >= bounce_min_bytes() &&
+                                  host_is_pageable(ctx->asr_states_out);
+        int64_t prev_off = 0;
+        int prev_len = 0;
+        auto ship_pageable = [&](int64_t off, int len) -> int {
+            int r = d2h_rows_to_pageable(ctx, d, ctx->asr_states_out + d.p_begin + off, (size_t)Ptot_out, d.states.as<uint8_t>() + off,
+                                         (size_t)d.P_pad, (size_t)len, T.n, d.copy_stream);
+            if (r || !(ctx->asr_post_out && want_post)) return r;
+            return d2h_rows_to_pageable(ctx, d, reinterpret_cast<uint8_t *>(ctx->asr_post_out + (d.p_begin + off) * 4),
+                                        (size_t)Ptot_out * 4 * sizeof(double),
+                                        reinterpret_cast<const uint8_t *>(d.posteriors.as<double>() + off * 4),
+                                        (size_t)d.P_pad * 4 * sizeof(double), (size_t)len * 4 * sizeof(double), T.n, d.copy_stream);
+        };
         for (int t = 0; t < d.n_tiles; ++t) {
             int64_t off = (int64_t)t * d.tile_pad;
             int len = (int)std::min<int64_t>(d.tile_pad, d.P - off);
@@ -1211,7 +1229,19 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
                 rc = joint ? PHB_OK : asr_blocked ? launch_down_sweep(ctx, d, M, 4 * tile_geom.Q, off, len, want_post)
                                                   : run_tile_down(ctx, d, M, off, len, want_post);
                 if (rc) return rc;
-                if (ctx->asr_states_out) { // ship this tile's states (and posteriors) on the copy stream
+                if (ctx->asr_states_out && out_pageable) {
+                    // a pageable destination (a caller's Vec): the tile before this one goes home through the bounce buffers
+                    // while the GPU works on this one; this tile's turn comes in the next iteration
+                    if (prev_len > 0) {
+                        rc = ship_pageable(prev_off, prev_len);
+                        if (rc) return rc;
+                    }
+                    const int buf = t & 1;
+                    CU(cudaEventRecord(d.ev_free[buf], d.stream));
+                    CU(cudaStreamWaitEvent(d.copy_stream, d.ev_free[buf], 0));
+                    prev_off = off;
+                    prev_len = len;
+                } else if (ctx->asr_states_out) { // ship this tile's states (and posteriors) on the copy stream
                     const int buf = t & 1;
                     CU(cudaEventRecord(d.ev_free[buf], d.stream));
                     CU(cudaStreamWaitEvent(d.copy_stream, d.ev_free[buf], 0));
@@ -1227,6 +1257,10 @@ int evaluate(phb_ctx *ctx, bool asr, bool want_post, double *total, bool joint =
             }
             if (asr_sweep) part_off += (size_t)((len + 4 * tile_geom.Q - 1) / (4 * tile_geom.Q));
             else part_off += (size_t)((len + ROOT_THREADS - 1) / ROOT_THREADS);
+        }
+        if (prev_len > 0) { // the last tile's outputs
+            rc = ship_pageable(prev_off, prev_len);
+            if (rc) return rc;
         }
         {
             ScopedTimer tm(ctx, &d, PH_ROOT);
@@ -1979,6 +2013,44 @@ int h2d_rows_from_host(phb_ctx *ctx, Device &d, uint8_t *dst, size_t pitch, RowP
         CU(cudaEventRecord(d.ev_bounce[b], stream));
         ++d.bounce_uses;
     }
+    return PHB_OK;
+}
+
+// The way back: `height` device rows of `width` bytes (row r at src + r * src_pitch) into a caller's PAGEABLE buffer (row r
+// at dst + r * dst_pitch).  Groups of rows arrive in the pinned bounce buffers by DMA and are scattered to the caller's
+// memory by the pool, the DMA of group g + 1 overlapping the host copy of group g.  Blocks until everything is home.
+int d2h_rows_to_pageable(phb_ctx *ctx, Device &d, uint8_t *dst, size_t dst_pitch, const uint8_t *src, size_t src_pitch, size_t width,
+                         int height, cudaStream_t stream)
+{
+    if (width == 0 || height <= 0) return PHB_OK;
+    if (width > bounce_bytes()) { // a row does not fit a bounce buffer: the driver's staged copy
+        CU(cudaMemcpy2DAsync(dst, dst_pitch, src, src_pitch, width, (size_t)height, cudaMemcpyDeviceToHost, stream));
+        CU(cudaStreamSynchronize(stream));
+        return PHB_OK;
+    }
+    int rc = h2d_from_host(ctx, d, nullptr, nullptr, 0, stream, true); // pool and bounce buffers exist from here on
+    if (rc) return rc;
+    for (int b = 0; b < 2 && d.bounce_uses >= 2; ++b) CU(cudaEventSynchronize(d.ev_bounce[b])); // earlier traffic through them
+    const int per = (int)std::max<size_t>(1, bounce_bytes() / width);
+    const int n_groups = (height + per - 1) / per;
+    auto issue = [&](int g) -> cudaError_t {
+        const int r0 = g * per, m = std::min(per, height - r0), b = g & 1;
+        cudaError_t e = cudaMemcpy2DAsync(d.bounce[b], width, src + (size_t)r0 * src_pitch, src_pitch, width, (size_t)m,
+                                          cudaMemcpyDeviceToHost, stream);
+        if (e != cudaSuccess) return e;
+        return cudaEventRecord(d.ev_bounce[b], stream);
+    };
+    CU(issue(0));
+    std::vector<CopyPool::Task> list;
+    for (int g = 0; g < n_groups; ++g) {
+        if (g + 1 < n_groups) CU(issue(g + 1)); // its bounce buffer was emptied by the host in iteration g - 1
+        const int r0 = g * per, m = std::min(per, height - r0), b = g & 1;
+        CU(cudaEventSynchronize(d.ev_bounce[b]));
+        list.clear();
+        for (int r = 0; r < m; ++r) list.push_back({d.bounce[b] + (size_t)r * width, dst + (size_t)(r0 + r) * dst_pitch, width});
+        ctx->copy_pool->run(list);
+    }
+    d.bounce_uses += 2; // both events have been recorded (and waited for)
     return PHB_OK;
 }
 

@@ -21,6 +21,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--taxa", type=int, default=10_000)
     ap.add_argument("--sites", type=int, default=1_000_000)
+    ap.add_argument("--asr", action="store_true", help="also time marginal ASR (states: taxa x sites bytes of pageable memory)")
     args = ap.parse_args()
     n, W = args.taxa, args.sites
     tree = synthetic.yule_flat(n, 0x5EED0003)
@@ -31,7 +32,11 @@ def main():
         per_row = [np.ascontiguousarray(block[:, r]) for r in range(n)]  # one buffer per sequence, as Alignment::seqs holds them
         out = {"taxa": n, "sites": W, "bounce": os.environ.get("PHB_FORCE_BOUNCE", "auto"), "copy_threads": os.environ.get("PHB_COPY_THREADS", "8")}
         for name, fn in (("compress_rows_ms", lambda: ctx.compress_rows(per_row)),
-                         ("log_likelihood_host_ms", lambda: ctx.log_likelihood_host(block))):
+                         ("log_likelihood_host_ms", lambda: ctx.log_likelihood_host(block)),
+                         # marginal ASR with its states written to a pageable numpy array (capi allocates one per call)
+                         ("marginal_asr_pageable_states_ms", (lambda: ctx.marginal_asr()) if args.asr else None)):
+            if fn is None:
+                continue
             fn()
             best = 1e30
             for _ in range(2):
