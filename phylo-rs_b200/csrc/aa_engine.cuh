@@ -188,10 +188,21 @@ int aa_evaluate(phb_ctx *ctx, bool asr, uint8_t *states_out, double *post_out, d
                     CHECK_LAUNCH();
                 }
             }
-            if (states_out)
+            // pageable destinations of some size go through the pinned bounce buffers (phylo_b200.cu d2h_rows_to_pageable)
+            const bool bounce = states_out && (size_t)T.n * (size_t)P >= bounce_min_bytes() && host_is_pageable(states_out);
+            if (states_out && bounce) {
+                rc = d2h_rows_to_pageable(ctx, d, states_out + off, (size_t)P, A.states.as<uint8_t>(), (size_t)tile_pad, (size_t)tile_len,
+                                          T.n, d.stream);
+                if (rc) return rc;
+            } else if (states_out)
                 CU(cudaMemcpy2DAsync(states_out + off, (size_t)P, A.states.p, (size_t)tile_pad, (size_t)tile_len, (size_t)T.n,
                                      cudaMemcpyDeviceToHost, d.stream));
-            if (post_out)
+            if (post_out && bounce) {
+                rc = d2h_rows_to_pageable(ctx, d, reinterpret_cast<uint8_t *>(post_out + (size_t)off * AA_NS), (size_t)P * AA_NS * sizeof(double),
+                                          A.post.as<uint8_t>(), (size_t)tile_len * AA_NS * sizeof(double),
+                                          (size_t)tile_len * AA_NS * sizeof(double), T.n, d.stream);
+                if (rc) return rc;
+            } else if (post_out)
                 CU(cudaMemcpy2DAsync(post_out + (size_t)off * AA_NS, (size_t)P * AA_NS * sizeof(double), A.post.p,
                                      (size_t)tile_len * AA_NS * sizeof(double), (size_t)tile_len * AA_NS * sizeof(double), (size_t)T.n,
                                      cudaMemcpyDeviceToHost, d.stream));
