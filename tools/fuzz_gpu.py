@@ -29,6 +29,7 @@ def main():
     ap.add_argument("--nni", default="0:100")
     ap.add_argument("--deep", default="0:0")
     ap.add_argument("--misc", default="0:0")
+    ap.add_argument("--spr", default="0:0")
     args = ap.parse_args()
     lib = capi.default_library()
     bad = 0
@@ -139,6 +140,42 @@ def main():
         except Exception as e:
             bad += 1
             print("FAIL misc", seed, type(e).__name__, str(e)[:300], flush=True)
+    # phb_score_trees on random SPR candidates (prune + graft with the reference's semantics: src/tree/ops.rs:34-41)
+    from oracle.refhost import Node
+
+    for seed in rng_of(args.spr):
+        rng = np.random.default_rng(seed)
+        model = workloads.MODELS[int(rng.integers(len(workloads.MODELS)))]
+        case = workloads.make_case(int(rng.integers(5, 60)), int(rng.integers(10, 400)), model=model, seed=seed, ambiguity=float(rng.choice([0, 0.1])))
+        base = case.tree
+        ids = list(base.get_node_ids())
+        cands, refs = [], []
+        for _ in range(200):
+            if len(cands) == 6:
+                break
+            t = base.clone()
+            x, y = int(rng.choice(ids)), int(rng.choice(ids))
+            px, py = t.nodes[x].parent, t.nodes[y].parent
+            if px is None or py is None or y in set(t.preord_ids(x)):
+                continue
+            t.delete_edge(px, x)
+            new = Node(t.next_id())
+            t.split_edge((py, y), new)
+            t.set_child(new.id, x)
+            ft = workloads.flatten_fast(t, case.leaf_order)
+            cands.append((ft["postorder"], ft["child_off"], ft["children"], ft["blen"], ft["leaf_row"], ft["root"]))
+            refs.append(oracle.log_likelihood_flat(ft, case.model, case.patterns, case.mult, mode=0, n_threads=8)[0])
+        try:
+            with capi.Context(library=lib) as ctx:
+                workloads.load_into(ctx, case)
+                before = ctx.log_likelihood()
+                got = ctx.score_trees(cands)
+                assert ctx.log_likelihood() == before
+            for g, r in zip(got, refs):
+                assert (abs(g - r) <= 1e-9 * abs(r)) if np.isfinite(r) else (g == r), (g, r)
+        except Exception as e:
+            bad += 1
+            print("FAIL spr", seed, model, str(e)[:300], flush=True)
     print("fuzz done, failures:", bad)
 
 
