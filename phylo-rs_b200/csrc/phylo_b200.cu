@@ -810,7 +810,7 @@ int ensure_sweep(phb_ctx *ctx, const ModelDev &M, bool store, const std::vector<
                     S.n_levels, S.stream_bytes, S.rec_cap, S.max_rows);
     }
     if (ctx->sweep_geom.planned_P != shard_P) {
-        if (!ctx->sweep_geom.plan(S, smem_max, shard_P, std::max(ctx->devs[0].sm_count, 1)))
+        if (!ctx->sweep_geom.plan(S, smem_max, shard_P, std::max(ctx->devs[0].sm_count, 1), 0, true)) // run_sweep splits the tail off
             return ctx->fail(PHB_ERR_INVALID_MODEL_PARAMETER, "sweep: %d CLV categories do not fit one CTA", M.n_clv);
     }
     if (!ctx->sweep_guards_valid) { // branch lengths or rates changed: re-plan where the underflow guard runs

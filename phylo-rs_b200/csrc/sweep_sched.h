@@ -546,12 +546,20 @@ struct SweepGeom {
     int Q = 0, n_consumers = 0, threads = 0, n_stages = 0, stage_bytes = 0, smem_levels = 0, g_levels = 0;
     size_t level_bytes = 0, smem_bytes = 0;
     int64_t planned_P = -1;
-    // Picks the site quads per CTA pass (Q) for a shard of P patterns on n_sm SMs.  A pass over the op list
-    // costs about t(n) = 304 + 2.67 n clocks per op for n consumer threads (measured on B200 at n = 256 and
-    // 320), and the persistent grid needs ceil(blocks / n_sm) passes, so a slightly narrower or wider CTA
-    // can save a whole pass when the block count lands just above a multiple of the SM count (the strong-
-    // scaling shards of 125k-500k patterns).  PHB_SWEEP_Q overrides the choice (experiments).
-    bool plan(const SweepSched &S, size_t smem_max, int64_t P = 0, int n_sm = 148, int force_q = 0)
+    // Picks the site quads per CTA pass (Q) for a shard of P patterns on n_sm SMs.  A pass of the persistent grid over
+    // the op list is latency-bound: its time depends on the resident warps per scheduler, hardly on the width within
+    // such a class (B200, 10k-taxon tree, ms per pass at Q = 16 / 24 | 40 / 56 | 72 / 88: 2.79 / 2.87 | 3.53 / 3.59 |
+    // 4.10 / 4.14, profiles/r2_pass_time_vs_width.txt), and the grid needs ceil(blocks / n_sm) passes -- so the widest
+    // CTA wins unless a narrower one saves a pass.  tail_split: the caller sends the blocks left over after the last full
+    // pass as a launch of their own, just wide enough for one pass (run_sweep); the cost model then charges that pass at
+    // its own, cheaper class.  PHB_SWEEP_Q overrides the choice (experiments).
+    static int warps_per_scheduler(int q, int n_clv) { return (q * n_clv / 32 + 1 + 3) / 4; }
+    static double pass_cost(int q, int n_clv)
+    {
+        const int c = warps_per_scheduler(q, n_clv);
+        return (c <= 1 ? 0.69 : c == 2 ? 0.86 : 1.0) * (1.0 + 0.0006 * q);
+    }
+    bool plan(const SweepSched &S, size_t smem_max, int64_t P = 0, int n_sm = 148, int force_q = 0, bool tail_split = false)
     {
         const int step = sweep_q_step(S.n_clv), q_max = sweep_q_max(S.n_clv);
         if (q_max < step) return false;
@@ -561,8 +569,15 @@ struct SweepGeom {
             double best = 1e300;
             for (int q = q_max; q >= step && q >= q_max / 2; q -= step) {
                 const int64_t blocks = (P + 4 * q - 1) / (4 * q);
-                const int64_t passes = (blocks + n_sm - 1) / n_sm;
-                const double cost = (double)passes * (304.0 + 2.67 * q * S.n_clv);
+                const int64_t full = blocks / n_sm, rem = blocks - full * n_sm;
+                double cost;
+                if (tail_split && full > 0 && rem > 0) {
+                    const int64_t tail_P = P - full * n_sm * 4 * q;
+                    int qt = (int)((tail_P + (int64_t)4 * n_sm - 1) / ((int64_t)4 * n_sm));
+                    qt = std::min(q, (qt + step - 1) / step * step);
+                    cost = (double)full * pass_cost(q, S.n_clv) + pass_cost(qt, S.n_clv);
+                } else
+                    cost = (double)(full + (rem > 0 ? 1 : 0)) * pass_cost(q, S.n_clv);
                 if (cost < best - 1e-9) {
                     best = cost;
                     Q = q;

@@ -56,7 +56,8 @@ def test_sweep_many_blocks_per_cta(emu_lib):
     case = workloads.make_case(7, 2600, model="gtr_g4", seed=14)  # <= 320-site blocks -> >= 9 blocks on 3 CTAs
     st = _cases.check_lnl(emu_lib, case)[2]
     assert 160 <= st["sweep_block_sites"] <= 352 and st["sweep_block_sites"] % 16 == 0
-    assert 3 <= st["sweep_ops"] < 6 and st["clv_launches"] == 1  # 6 internal nodes, the cherries folded into their parents' ops
+    # 6 internal nodes, the cherries folded into their parents' ops; one launch for the full passes + one, narrower, for the rest
+    assert 3 <= st["sweep_ops"] < 6 and st["clv_launches"] in (1, 2)
 
 
 def test_sweep_global_stack_levels(emu_lib, monkeypatch):
