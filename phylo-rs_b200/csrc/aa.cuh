@@ -76,6 +76,55 @@ struct AaDown {
     int32_t parent_slot; // CLV slot holding the parent's posterior, -1 for the root
 };
 
+// ---- alignment bytes -> tip codes, transposed to [row][P_pad] -----------------------------------------------------
+// raw: a chunk of the caller's bytes as they came ([pattern][row] when pattern_major, else [row][pattern]), np patterns
+// starting at pattern p0 (pattern-major) or all P patterns of rows r0.. (row-major: rows_in_chunk rows).  32 x 32 tiles
+// through shared memory so that both the reads and the writes are coalesced.  row_flags[r] |= 1 when the row holds a byte
+// AminoAcid::profile rejects, |= 2 when that byte is the row's first pattern (error precedence, check_leaves).
+__global__ void aa_pack_kernel(const uint8_t *__restrict__ raw, int pattern_major, int n_rows, int64_t np, int64_t p0, int r0,
+                               int rows_in_chunk, uint8_t *__restrict__ tips, int64_t P_pad, int *__restrict__ row_flags)
+{
+    __shared__ uint8_t tile[32][33];
+    const int64_t pb = (int64_t)blockIdx.x * 32; // pattern offset inside the chunk
+    const int rb = blockIdx.y * 32;              // row offset inside the chunk
+    const int tx = threadIdx.x, ty = threadIdx.y; // 32 x 8
+    const int nr = pattern_major ? n_rows : rows_in_chunk;
+    if (pattern_major) { // consecutive bytes = consecutive rows of one pattern
+        for (int k = ty; k < 32; k += 8) {
+            const int64_t p = pb + k;
+            const int r = rb + tx;
+            tile[k][tx] = (p < np && r < nr) ? raw[(size_t)p * n_rows + r] : (uint8_t)'-';
+        }
+        __syncthreads();
+        for (int k = ty; k < 32; k += 8) {
+            const int r = rb + k;
+            const int64_t p = pb + tx;
+            if (r < nr && p < np) {
+                const uint8_t c = aa_encode_byte(tile[tx][k]);
+                tips[(size_t)r * P_pad + p0 + p] = c;
+                if (c == CODE_INVALID) atomicOr(reinterpret_cast<unsigned *>(row_flags + r), (p0 + p == 0) ? 3u : 1u);
+            }
+        }
+    } else { // consecutive bytes = consecutive patterns of one row: no transposition
+        for (int k = ty; k < 32; k += 8) {
+            const int r = rb + k;
+            const int64_t p = pb + tx;
+            if (r < nr && p < np) {
+                const uint8_t c = aa_encode_byte(raw[(size_t)r * np + p]);
+                tips[(size_t)(r0 + r) * P_pad + p] = c;
+                if (c == CODE_INVALID) atomicOr(reinterpret_cast<unsigned *>(row_flags + r0 + r), p == 0 ? 3u : 1u);
+            }
+        }
+    }
+}
+__global__ void aa_fill_pad_kernel(uint8_t *__restrict__ tips, int n_rows, int64_t P, int64_t P_pad)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t w = P_pad - P;
+    if (w <= 0 || i >= (int64_t)n_rows * w) return;
+    tips[(size_t)(i / w) * P_pad + P + i % w] = AA_CODE_GAP;
+}
+
 // ---- P(t): diag(inv_sqrt_pi) V diag(exp(lambda r t)) V^T diag(sqrt_pi), exact identity at r t == 0 ------------------
 // One block per (edge, category).  Same operation order as RateMatrix::transition (rate_matrix.rs:119-133):
 // (V_ik e_k) V_jk summed over k ascending, then the two diagonal scalings.

@@ -18,24 +18,53 @@ int aa_set_alignment(phb_ctx *ctx, int32_t n_rows, int64_t P, const uint8_t *byt
     A.P_pad = round_up(std::max<int64_t>(P, 1), AA_THREADS);
     ctx->row_invalid_host.assign(std::max(n_rows, 1), 0);
     ctx->row_first_invalid.assign(std::max(n_rows, 1), 0);
-    // ASCII -> tip codes, transposed to [row][P_pad] on the host (the padding is the gap code)
-    std::vector<uint8_t> codes((size_t)std::max(n_rows, 1) * (size_t)A.P_pad, AA_CODE_GAP);
-    uint8_t table[256];
-    for (int c = 0; c < 256; ++c) table[c] = aa_encode_byte((uint8_t)c);
-    for (int r = 0; r < n_rows; ++r) {
-        uint8_t *dst = codes.data() + (size_t)r * A.P_pad;
-        int bad = 0;
-        for (int64_t p = 0; p < P; ++p) {
-            const uint8_t b = layout == PHB_LAYOUT_PATTERN_MAJOR ? bytes[(size_t)p * n_rows + r] : bytes[(size_t)r * P + p];
-            const uint8_t c = table[b];
-            dst[p] = c;
-            bad |= c == CODE_INVALID;
-        }
-        ctx->row_invalid_host[r] = bad;
-        ctx->row_first_invalid[r] = P > 0 && dst[0] == CODE_INVALID;
+    // ASCII -> tip codes on the device, chunk by chunk (the caller's bytes travel as they are; pageable memory through the
+    // bounce buffers): aa_pack_kernel
+    const int nr1 = std::max(n_rows, 1);
+    CU(A.tips.ensure((size_t)nr1 * (size_t)A.P_pad));
+    CU(A.row_flags.ensure(sizeof(int) * (size_t)nr1));
+    CU(cudaMemsetAsync(A.row_flags.p, 0, sizeof(int) * (size_t)nr1, d.stream));
+    if (n_rows > 0 && A.P_pad > P) {
+        const int64_t cells = (int64_t)n_rows * (A.P_pad - P);
+        PHB_LAUNCH(aa_fill_pad_kernel, dim3((unsigned)((cells + 255) / 256)), dim3(256), d.stream, A.tips.as<uint8_t>(), n_rows, P, A.P_pad);
+        CHECK_LAUNCH();
     }
-    CU(A.tips.ensure(codes.size()));
-    CU(cudaMemcpyAsync(A.tips.p, codes.data(), codes.size(), cudaMemcpyHostToDevice, d.stream));
+    if (n_rows > 0 && P > 0) {
+        const bool pageable = host_is_pageable(bytes);
+        const size_t CHUNK = (size_t)128 << 20;
+        if (layout == PHB_LAYOUT_PATTERN_MAJOR) {
+            const int64_t pp = std::max<int64_t>(32, (int64_t)(CHUNK / (size_t)n_rows) / 32 * 32);
+            CU(d.staging.ensure((size_t)std::min<int64_t>(pp, P) * n_rows));
+            for (int64_t p0 = 0; p0 < P; p0 += pp) {
+                const int64_t np = std::min<int64_t>(pp, P - p0);
+                int rc = h2d_from_host(ctx, d, d.staging.as<uint8_t>(), bytes + (size_t)p0 * n_rows, (size_t)np * n_rows, d.stream, pageable);
+                if (rc) return rc;
+                PHB_LAUNCH(aa_pack_kernel, dim3((unsigned)((np + 31) / 32), (unsigned)((n_rows + 31) / 32)), dim3(32, 8), d.stream,
+                           d.staging.as<uint8_t>(), 1, n_rows, np, p0, 0, n_rows, A.tips.as<uint8_t>(), A.P_pad, A.row_flags.as<int>());
+                CHECK_LAUNCH();
+            }
+        } else {
+            const int rr = (int)std::max<int64_t>(1, std::min<int64_t>(n_rows, (int64_t)(CHUNK / (size_t)P)));
+            CU(d.staging.ensure((size_t)rr * (size_t)P));
+            for (int r0 = 0; r0 < n_rows; r0 += rr) {
+                const int nr = std::min(rr, n_rows - r0);
+                int rc = h2d_from_host(ctx, d, d.staging.as<uint8_t>(), bytes + (size_t)r0 * P, (size_t)nr * P, d.stream, pageable);
+                if (rc) return rc;
+                PHB_LAUNCH(aa_pack_kernel, dim3((unsigned)((P + 31) / 32), (unsigned)((nr + 31) / 32)), dim3(32, 8), d.stream,
+                           d.staging.as<uint8_t>(), 0, n_rows, P, (int64_t)0, r0, nr, A.tips.as<uint8_t>(), A.P_pad, A.row_flags.as<int>());
+                CHECK_LAUNCH();
+            }
+        }
+    }
+    {
+        std::vector<int> flags((size_t)nr1, 0);
+        CU(cudaMemcpyAsync(flags.data(), A.row_flags.p, sizeof(int) * (size_t)nr1, cudaMemcpyDeviceToHost, d.stream));
+        CU(cudaStreamSynchronize(d.stream));
+        for (int r = 0; r < n_rows; ++r) {
+            ctx->row_invalid_host[r] = (flags[r] & 1) != 0;
+            ctx->row_first_invalid[r] = (flags[r] & 2) != 0;
+        }
+    }
     std::vector<double> mult((size_t)A.P_pad, 0.0);
     for (int64_t p = 0; p < P; ++p) mult[p] = multiplicity ? (double)multiplicity[p] : 1.0;
     CU(A.mult.ensure(sizeof(double) * mult.size()));
@@ -258,7 +287,7 @@ void aa_release(phb_ctx *ctx)
 {
     AaState &A = aa_of(ctx);
     for (DevBuf *b : {&A.model, &A.tips, &A.mult, &A.leaf_ls, &A.per_pattern, &A.Pmat, &A.blen, &A.clv, &A.exps, &A.cat_ll, &A.partials,
-                      &A.uops, &A.ukids, &A.down, &A.leaf_rows, &A.states, &A.post})
+                      &A.uops, &A.ukids, &A.down, &A.leaf_rows, &A.states, &A.post, &A.row_flags})
         b->release();
 }
 

@@ -374,7 +374,7 @@ struct Device {
 // 20-state (AminoAcid) engines of a PHB_FLAG_AMINO_ACID context: aa.cuh, aa_engine.cuh
 struct AaState {
     AaModelDev M;
-    DevBuf model, tips, mult, leaf_ls, per_pattern, Pmat, blen, clv, exps, cat_ll, partials, uops, ukids, down, leaf_rows, states, post;
+    DevBuf model, tips, mult, leaf_ls, per_pattern, Pmat, blen, clv, exps, cat_ll, partials, uops, ukids, down, leaf_rows, states, post, row_flags;
     std::vector<AaDown> down_nodes;
     std::vector<int> down_off; // by depth, max_depth + 2 entries
     int64_t P_pad = 0;
@@ -1096,6 +1096,7 @@ int run_sweep(phb_ctx *ctx, Device &d, const ModelDev &M)
 }
 
 bool host_is_pageable(const void *p);
+int h2d_from_host(phb_ctx *ctx, Device &d, uint8_t *dst, const uint8_t *src, size_t bytes, cudaStream_t stream, bool pageable);
 int d2h_rows_to_pageable(phb_ctx *ctx, Device &d, uint8_t *dst, size_t dst_pitch, const uint8_t *src, size_t src_pitch, size_t width,
                          int height, cudaStream_t stream);
 
