@@ -69,6 +69,7 @@ extern "C" {
  *   phb_set_model            takes lambda[20], V[400] (V[i + 20*k]), pi / sqrt_pi / inv_sqrt_pi[20];
  *   phb_set_tree, phb_log_likelihood, phb_get_per_pattern, phb_set_clv_budget   as documented below;
  *   phb_marginal_asr         states are indices 0..19 into CANONICAL, posteriors [n_nodes][n_patterns][20];
+ *   phb_joint_asr            as documented below, states 0..19;
  *   phb_transition_matrices  out[(k * n_cat + c) * 400 + 20 * i + j];
  * rate-0 categories are evaluated literally (identity P).  One device per context.  Every other entry point returns
  * PHB_ERR_STATE. */

@@ -423,12 +423,14 @@ def joint_assignment_value(ft, model, pattern, states):
             for v in range(n):
                 for k in range(co[v], co[v + 1]):
                     c = int(ch[k])
-                    P = np.zeros(16)
-                    lib().orc_transition(C.byref(model.rm), float(r * blen[c]), _dp(P))
-                    val += np.log(P[4 * int(states[v]) + int(states[c])])
+                    ns = model.NS
+                    P = np.zeros(ns * ns)
+                    model._lib().orc_transition(C.byref(model.rm), float(r * blen[c]), _dp(P))
+                    val += np.log(P[ns * int(states[v]) + int(states[c])])
                 if co[v + 1] == co[v]:
-                    prof = np.zeros(4)
-                    lib().orc_nucleotide_profile(int(pattern[leaf_row[v]]), _dp(prof))
+                    prof = np.zeros(model.NS)
+                    L = model._lib()
+                    (L.orc_nucleotide_profile if model.NS == 4 else L.orc_amino_acid_profile)(int(pattern[leaf_row[v]]), _dp(prof))
                     val += np.log(prof[int(states[v])])
             if val > best:
                 best = val

@@ -536,4 +536,174 @@ aa_down_kernel(const AaDown *__restrict__ nodes, const AaModelDev *__restrict__ 
     }
 }
 
+// =====================================================================================================================
+// Joint (Viterbi) reconstruction at 20 states: compute_joint_asr (likelihood.rs:421-560), as joint.cuh does it for 4 --
+// log space, max-plus, no back-pointer table (the traceback re-evaluates the one row it needs from the child's C values).
+//   leaf      C_v[i] = ln profile_v[i]  (the profile as AminoAcid::profile gives it: ln 1, ln 0.5, -inf)      :477-480
+//   internal  C_v[i] = sum_children max_j ( ln P_c[i][j] + C_c[j] )                                            :483-509
+//   root      per category the FIRST maximal i of ln pi_i + C_root[i]; the category with the strictly greatest
+//             ln w + max wins                                                                                   :512-527
+//   traceback state_c = FIRST maximal j of ln P_c[state_parent][j] + C_c[j]                                     :531-538
+// `val > best` comparisons throughout: a NaN never wins, as in the reference.
+// =====================================================================================================================
+constexpr uint8_t AA_NO_CATEGORY = 0xFF;
+
+// ln profile[j] of a tip code
+__device__ __forceinline__ double aa_joint_tip_value(uint32_t code, int j)
+{
+    if (code < (uint32_t)AA_NS) return (int)code == j ? 0.0 : -INFINITY;
+    if (code <= AA_CODE_J) {
+        int a, b;
+        aa_pair_states(code, a, b);
+        return (j == a || j == b) ? -0.69314718055994530942 : -INFINITY;
+    }
+    return 0.0; // X, gap: all ones
+}
+
+// Up pass, one level.  Same grid and staging as aa_clv_kernel (ln P transposed, all of the block's categories behind one
+// barrier for nodes with at most AA_STAGE children); the buffer holds C values instead of CLVs, no exponents.
+__global__ void __launch_bounds__(AA_THREADS, PHB_AA_MINB)
+aa_joint_up_kernel(const GenOp *__restrict__ ops, const GenChild *__restrict__ kids, int n_cat, const double *__restrict__ lnP,
+                   double *__restrict__ cbuf, size_t slot_stride, size_t tile_pad, int tile_len, const uint8_t *__restrict__ tips,
+                   int64_t P_pad, int64_t tile_off)
+{
+    __shared__ __align__(16) double Lt[AA_CSTAGE * AA_STAGE][AA_NS * AA_NS];
+    const GenOp op = ops[blockIdx.y];
+    const int cat0 = blockIdx.z * AA_CSTAGE;
+    const int ncat = min(AA_CSTAGE, n_cat - cat0);
+    const int nch = op.child_end - op.child_begin;
+    const bool upfront = nch <= AA_STAGE;
+    int64_t site = (int64_t)blockIdx.x * AA_THREADS + threadIdx.x;
+    const bool active = site < tile_len;
+    if (!active) site = 0;
+    if (upfront) {
+        for (int idx = threadIdx.x; idx < ncat * nch * AA_NS * AA_NS; idx += AA_THREADS) {
+            const int m = idx / (AA_NS * AA_NS), e = idx - m * (AA_NS * AA_NS);
+            const int c = m / nch, k = m - c * nch;
+            Lt[c * AA_STAGE + k][(e % AA_NS) * AA_NS + e / AA_NS] =
+                lnP[((size_t)kids[op.child_begin + k].edge * n_cat + cat0 + c) * (AA_NS * AA_NS) + e];
+        }
+        __syncthreads();
+    }
+    for (int c = 0; c < ncat; ++c) {
+        const int cat = cat0 + c;
+        double acc[AA_NS];
+#pragma unroll
+        for (int i = 0; i < AA_NS; ++i) acc[i] = 0.0;
+        for (int k0 = 0; k0 < nch; k0 += AA_STAGE) {
+            const int nb = min(AA_STAGE, nch - k0);
+            if (!upfront) {
+                __syncthreads();
+                for (int idx = threadIdx.x; idx < nb * AA_NS * AA_NS; idx += AA_THREADS) {
+                    const int k = idx / (AA_NS * AA_NS), e = idx - k * (AA_NS * AA_NS);
+                    Lt[k][(e % AA_NS) * AA_NS + e / AA_NS] = lnP[((size_t)kids[op.child_begin + k0 + k].edge * n_cat + cat) * (AA_NS * AA_NS) + e];
+                }
+                __syncthreads();
+            }
+            for (int k = 0; k < nb; ++k) {
+                const GenChild ch = kids[op.child_begin + k0 + k];
+                const double *L_t = upfront ? Lt[c * AA_STAGE + k] : Lt[k];
+                double y[AA_NS];
+#pragma unroll
+                for (int i = 0; i < AA_NS; ++i) y[i] = -INFINITY;
+                const uint32_t code = ch.is_tip ? tips[(int64_t)ch.src * P_pad + tile_off + site] : 0u;
+                const double *x_src = ch.is_tip ? nullptr : cbuf + (size_t)ch.src * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
+                for (int j = 0; j < AA_NS; ++j) { // j ascending with `>`: the reference's sequential maximum
+                    const double cj = ch.is_tip ? aa_joint_tip_value(code, j) : x_src[(size_t)j * tile_pad];
+#pragma unroll
+                    for (int i = 0; i < AA_NS; ++i) {
+                        const double val = L_t[j * AA_NS + i] + cj;
+                        if (val > y[i]) y[i] = val;
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < AA_NS; ++i) acc[i] += y[i];
+            }
+        }
+        if (active) {
+            double *dst = cbuf + (size_t)op.out_slot * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) dst[(size_t)i * tile_pad] = acc[i];
+        }
+    }
+}
+
+// Root: winning category, root state, per-pattern value, block sums of multiplicity * value.
+__global__ void __launch_bounds__(AA_THREADS)
+aa_joint_root_kernel(int root_slot, int root_row, int root_node, const AaModelDev *__restrict__ M, const double *__restrict__ cbuf,
+                     size_t slot_stride, size_t tile_pad, int tile_len, const uint8_t *__restrict__ tips, int64_t P_pad,
+                     int64_t tile_off, const double *__restrict__ mult, double *__restrict__ per_pattern,
+                     uint8_t *__restrict__ best_cat, uint8_t *__restrict__ states, double *__restrict__ partials)
+{
+    __shared__ double red[AA_THREADS];
+    const int64_t site = (int64_t)blockIdx.x * AA_THREADS + threadIdx.x;
+    const int n_cat = M->n_cat;
+    double contrib = 0.0;
+    if (site < tile_len) {
+        double best = -INFINITY;
+        int bcat = AA_NO_CATEGORY, bstate = 0;
+        const uint32_t code = root_slot < 0 ? tips[(int64_t)root_row * P_pad + tile_off + site] : 0u;
+        for (int c = 0; c < n_cat; ++c) {
+            double root_max = -INFINITY;
+            int root_best = 0;
+            for (int i = 0; i < AA_NS; ++i) {
+                const double cv = root_slot < 0 ? aa_joint_tip_value(code, i)
+                                                : cbuf[(size_t)root_slot * slot_stride + ((size_t)c * AA_NS + i) * tile_pad + site];
+                const double ll = log(M->pi[i]) + cv;
+                if (ll > root_max) {
+                    root_max = ll;
+                    root_best = i;
+                }
+            }
+            const double cat_ll = M->ln_weights[c] + root_max;
+            if (cat_ll > best) {
+                best = cat_ll;
+                bcat = c;
+                bstate = root_best;
+            }
+        }
+        per_pattern[tile_off + site] = best;
+        best_cat[site] = (uint8_t)bcat;
+        states[(size_t)root_node * tile_pad + site] = (uint8_t)bstate;
+        contrib = mult[tile_off + site] * best;
+    }
+    red[threadIdx.x] = contrib;
+    __syncthreads();
+    for (int s = AA_THREADS / 2; s > 0; s >>= 1) {
+        if ((int)threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) partials[blockIdx.x] = red[0];
+}
+
+// Traceback, one depth (the root's own depth is done by the root kernel).  grid: x = pattern blocks, y = node of the depth.
+__global__ void __launch_bounds__(AA_THREADS)
+aa_joint_down_kernel(const AaDown *__restrict__ nodes, const int *__restrict__ parent_node, int n_cat, const double *__restrict__ lnP,
+                     const double *__restrict__ cbuf, size_t slot_stride, size_t tile_pad, int tile_len,
+                     const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off, const uint8_t *__restrict__ best_cat,
+                     uint8_t *__restrict__ states)
+{
+    const AaDown nd = nodes[blockIdx.y];
+    if (nd.parent_slot < 0) return; // the root
+    const int64_t site = (int64_t)blockIdx.x * AA_THREADS + threadIdx.x;
+    if (site >= tile_len) return;
+    const int cat = best_cat[site];
+    int st = 0;
+    if (cat != AA_NO_CATEGORY) {
+        const int s_p = states[(size_t)parent_node[nd.node] * tile_pad + site];
+        const double *row = lnP + ((size_t)nd.node * n_cat + cat) * (AA_NS * AA_NS) + (size_t)s_p * AA_NS;
+        const uint32_t code = nd.slot < 0 ? tips[(int64_t)nd.row * P_pad + tile_off + site] : 0u;
+        const double *c_src = nd.slot < 0 ? nullptr : cbuf + (size_t)nd.slot * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
+        double best = -INFINITY;
+        for (int j = 0; j < AA_NS; ++j) {
+            const double val = row[j] + (nd.slot < 0 ? aa_joint_tip_value(code, j) : c_src[(size_t)j * tile_pad]);
+            if (val > best) {
+                best = val;
+                st = j;
+            }
+        }
+    }
+    states[(size_t)nd.node * tile_pad + site] = (uint8_t)st;
+}
+
 } // namespace phb

@@ -253,6 +253,95 @@ int aa_evaluate(phb_ctx *ctx, bool asr, uint8_t *states_out, double *post_out, d
     return PHB_OK;
 }
 
+// compute_joint_asr (likelihood.rs:421-560) at 20 states: states [n_nodes][n_patterns], *total = sum multiplicity * best
+int aa_joint(phb_ctx *ctx, uint8_t *states_out, double *total)
+{
+    AaState &A = aa_of(ctx);
+    const TreeSched &T = ctx->tree;
+    Device &d = ctx->devs[0];
+    if (!ctx->have_aln || !ctx->have_model || !T.valid)
+        return ctx->fail(PHB_ERR_STATE, "set_alignment, set_model and set_tree must precede the evaluation");
+    int rc = check_leaves(ctx);
+    if (rc) return rc;
+    CU(cudaSetDevice(d.ordinal));
+    const int64_t P = ctx->n_patterns;
+    const int K = A.M.n_cat;
+    const int n_int = std::max(T.n_internal, 1);
+    size_t free_b = 0, total_b = 0;
+    CU(cudaMemGetInfo(&free_b, &total_b));
+    size_t budget = ctx->clv_budget ? (size_t)ctx->clv_budget : (free_b + A.clv.cap + A.states.cap) / 10 * 7;
+    const size_t per_pattern_bytes = (size_t)n_int * K * AA_NS * sizeof(double) + (size_t)T.n + 1;
+    int64_t tile_pad = (int64_t)(budget / per_pattern_bytes) / AA_THREADS * AA_THREADS;
+    tile_pad = std::max<int64_t>(AA_THREADS, std::min<int64_t>(tile_pad, A.P_pad));
+    const size_t slot_stride = (size_t)K * AA_NS * (size_t)tile_pad;
+    const size_t n_ent = (size_t)AA_NS * AA_NS * (size_t)T.n * K;
+    CU(A.clv.ensure(sizeof(double) * slot_stride * n_int));
+    CU(A.per_pattern.ensure(sizeof(double) * (size_t)A.P_pad));
+    CU(A.Pmat.ensure(sizeof(double) * n_ent));
+    CU(A.lnP.ensure(sizeof(double) * n_ent));
+    CU(A.jbest.ensure((size_t)tile_pad));
+    CU(A.states.ensure((size_t)T.n * tile_pad));
+    CU(A.partials.ensure(sizeof(double) * (size_t)(tile_pad / AA_THREADS)));
+    CU(A.parent.ensure(sizeof(int) * (size_t)T.n));
+    CU(cudaMemcpyAsync(A.parent.p, T.parent.data(), sizeof(int) * (size_t)T.n, cudaMemcpyHostToDevice, d.stream));
+    const AaModelDev *Md = A.model.as<AaModelDev>();
+    PHB_LAUNCH(aa_transition_kernel, dim3((unsigned)(T.n * K)), dim3(AA_THREADS), d.stream, A.blen.as<double>(), T.n, Md, A.Pmat.as<double>());
+    CHECK_LAUNCH();
+    PHB_LAUNCH(log_transition_kernel, dim3((unsigned)((n_ent + 255) / 256)), dim3(256), d.stream, A.Pmat.as<double>(), n_ent, A.lnP.as<double>());
+    CHECK_LAUNCH();
+    const int root_slot = T.slot[T.root];
+    const int root_row = root_slot < 0 ? T.leaf_row[T.root] : -1;
+    const bool bounce = states_out && (size_t)T.n * (size_t)P >= bounce_min_bytes() && host_is_pageable(states_out);
+    std::vector<double> h_part;
+    double sum = 0.0;
+    ctx->stats.n_tiles = 0;
+    for (int64_t off = 0; off < P; off += tile_pad) {
+        const int tile_len = (int)std::min<int64_t>(tile_pad, P - off);
+        const unsigned bx = (unsigned)((tile_len + AA_THREADS - 1) / AA_THREADS);
+        for (int l = 1; l <= T.n_levels; ++l) {
+            const int b = T.ulevel_off[l - 1], n_ops = T.ulevel_off[l] - b;
+            for (int o = 0; o < n_ops; o += 65535) {
+                const int cnt = std::min(65535, n_ops - o);
+                PHB_LAUNCH(aa_joint_up_kernel, dim3(bx, (unsigned)cnt, (unsigned)((K + AA_CSTAGE - 1) / AA_CSTAGE)), dim3(AA_THREADS), d.stream,
+                           A.uops.as<GenOp>() + b + o, A.ukids.as<GenChild>(), K, A.lnP.as<double>(), A.clv.as<double>(), slot_stride,
+                           (size_t)tile_pad, tile_len, A.tips.as<uint8_t>(), A.P_pad, off);
+                CHECK_LAUNCH();
+            }
+        }
+        PHB_LAUNCH(aa_joint_root_kernel, dim3(bx), dim3(AA_THREADS), d.stream, root_slot, root_row, T.root, Md, A.clv.as<double>(), slot_stride,
+                   (size_t)tile_pad, tile_len, A.tips.as<uint8_t>(), A.P_pad, off, A.mult.as<double>(), A.per_pattern.as<double>(),
+                   A.jbest.as<uint8_t>(), A.states.as<uint8_t>(), A.partials.as<double>());
+        CHECK_LAUNCH();
+        for (int dep = 1; dep <= T.max_depth; ++dep) {
+            const int b = A.down_off[dep], n_nd = A.down_off[dep + 1] - b;
+            for (int o = 0; o < n_nd; o += 65535) {
+                const int cnt = std::min(65535, n_nd - o);
+                PHB_LAUNCH(aa_joint_down_kernel, dim3(bx, (unsigned)cnt), dim3(AA_THREADS), d.stream, A.down.as<AaDown>() + b + o,
+                           A.parent.as<int>(), K, A.lnP.as<double>(), A.clv.as<double>(), slot_stride, (size_t)tile_pad, tile_len,
+                           A.tips.as<uint8_t>(), A.P_pad, off, A.jbest.as<uint8_t>(), A.states.as<uint8_t>());
+                CHECK_LAUNCH();
+            }
+        }
+        if (states_out && bounce) {
+            rc = d2h_rows_to_pageable(ctx, d, states_out + off, (size_t)P, A.states.as<uint8_t>(), (size_t)tile_pad, (size_t)tile_len, T.n, d.stream);
+            if (rc) return rc;
+        } else if (states_out)
+            CU(cudaMemcpy2DAsync(states_out + off, (size_t)P, A.states.p, (size_t)tile_pad, (size_t)tile_len, (size_t)T.n,
+                                 cudaMemcpyDeviceToHost, d.stream));
+        h_part.resize(bx);
+        CU(cudaMemcpyAsync(h_part.data(), A.partials.p, sizeof(double) * bx, cudaMemcpyDeviceToHost, d.stream));
+        CU(cudaStreamSynchronize(d.stream));
+        for (unsigned i = 0; i < bx; ++i) sum += h_part[i];
+        ctx->stats.n_tiles++;
+    }
+    CU(cudaStreamSynchronize(d.stream));
+    ctx->stats.n_patterns = P;
+    ctx->stats.tile_patterns = tile_pad;
+    ctx->stats.kernel_launches = ctx->launches;
+    if (total) *total = sum;
+    return PHB_OK;
+}
+
 int aa_get_per_pattern(phb_ctx *ctx, double *per_pattern)
 {
     AaState &A = aa_of(ctx);
@@ -287,7 +376,7 @@ void aa_release(phb_ctx *ctx)
 {
     AaState &A = aa_of(ctx);
     for (DevBuf *b : {&A.model, &A.tips, &A.mult, &A.leaf_ls, &A.per_pattern, &A.Pmat, &A.blen, &A.clv, &A.exps, &A.cat_ll, &A.partials,
-                      &A.uops, &A.ukids, &A.down, &A.leaf_rows, &A.states, &A.post, &A.row_flags})
+                      &A.uops, &A.ukids, &A.down, &A.leaf_rows, &A.states, &A.post, &A.row_flags, &A.lnP, &A.jbest, &A.parent})
         b->release();
 }
 

@@ -374,7 +374,7 @@ struct Device {
 // 20-state (AminoAcid) engines of a PHB_FLAG_AMINO_ACID context: aa.cuh, aa_engine.cuh
 struct AaState {
     AaModelDev M;
-    DevBuf model, tips, mult, leaf_ls, per_pattern, Pmat, blen, clv, exps, cat_ll, partials, uops, ukids, down, leaf_rows, states, post, row_flags;
+    DevBuf model, tips, mult, leaf_ls, per_pattern, Pmat, blen, clv, exps, cat_ll, partials, uops, ukids, down, leaf_rows, states, post, row_flags, lnP, jbest, parent;
     std::vector<AaDown> down_nodes;
     std::vector<int> down_off; // by depth, max_depth + 2 entries
     int64_t P_pad = 0;
@@ -2716,7 +2716,7 @@ int32_t phb_marginal_asr(phb_ctx *ctx, uint8_t *states, double *posteriors, doub
 int32_t phb_joint_asr(phb_ctx *ctx, uint8_t *states, double *total)
 {
     if (!ctx || !total || !states) return PHB_ERR_INVALID_ARGUMENT;
-    if (ctx->is_aa) return ctx->fail(PHB_ERR_STATE, "joint_asr: not available in a 20-state (PHB_FLAG_AMINO_ACID) context");
+    if (ctx->is_aa) return aa_joint(ctx, states, total);
     ctx->asr_states_out = states;
     ctx->asr_post_out = nullptr;
     int rc = evaluate(ctx, true, false, total, true);

@@ -100,12 +100,12 @@ def check_nni(lib, case, moves=None, flags=0, budget=None, devices=None, expect_
     return got, st
 
 
-def check_joint(lib, case, devices=None, budget=None):
+def check_joint(lib, case, devices=None, budget=None, flags=0):
     """phb_joint_asr against the oracle's compute_joint_asr restatement.  Per-pattern Viterbi values within
     1e-8 absolute, total within 1e-9 relative, states bit-exact except at audited numerical ties: a differing
     pattern is accepted only if the GPU's state assignment reaches the oracle's best value to 1e-9 under the
     oracle's own arithmetic (two assignments of equal joint probability)."""
-    with capi.Context(devices=devices, library=lib) as ctx:
+    with capi.Context(devices=devices, flags=flags, library=lib) as ctx:
         if budget:
             ctx.set_clv_budget(budget)
         workloads.load_into(ctx, case)
@@ -288,5 +288,6 @@ def check_random_trees_amino_acid(lib, seeds):
         try:
             check_lnl(lib, c2, flags=capi.FLAG_AMINO_ACID)
             assert check_asr(lib, c2, want_post=True, flags=capi.FLAG_AMINO_ACID) == 0
+            check_joint(lib, c2, flags=capi.FLAG_AMINO_ACID)
         except AssertionError as e:
             raise AssertionError(f"seed {seed}, model {model}, tree {nwk}: {e}") from e

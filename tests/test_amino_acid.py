@@ -114,6 +114,7 @@ def _parity(lib, n_taxa, n_sites, model, seed, ambiguity=0.05, budget=None, want
     case = workloads.make_case(n_taxa, n_sites, model=model, seed=seed, ambiguity=ambiguity)
     _cases.check_lnl(lib, case, flags=AA, budget=budget)
     assert _cases.check_asr(lib, case, want_post=want_post, flags=AA, budget=budget) == 0
+    _cases.check_joint(lib, case, flags=AA, budget=budget)
     return case
 
 
@@ -137,6 +138,7 @@ def _star_and_polytomy(lib):
     case = workloads.Case(tree, ft, workloads.make_aa_model("aa_g4"), "aa_g4", np.ascontiguousarray(pats), np.ones(64, np.uint64), names)
     _cases.check_lnl(lib, case, flags=AA)
     assert _cases.check_asr(lib, case, want_post=True, flags=AA) == 0
+    _cases.check_joint(lib, case, flags=AA)
 
 
 def _abi_behaviour(lib):
@@ -163,7 +165,7 @@ def _abi_behaviour(lib):
         for c in range(len(m.rates)):
             assert np.max(np.abs(Pm[1, c] - m.category_transition(c, 0.3))) <= 1e-13
         # entry points without a 20-state instance say so
-        for call in (lambda: ctx.joint_asr(), lambda: ctx.score_nni([0], [0]), lambda: ctx.transition_matrices_noalloc([0.1], 4)):
+        for call in (lambda: ctx.score_nni([0], [0]), lambda: ctx.transition_matrices_noalloc([0.1], 4)):
             with pytest.raises(capi.PhbError) as ei:
                 call()
             assert ei.value.variant == "State" and "20-state" in str(ei.value)
