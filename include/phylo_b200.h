@@ -71,6 +71,9 @@ extern "C" {
  *   phb_marginal_asr         states are indices 0..19 into CANONICAL, posteriors [n_nodes][n_patterns][20];
  *   phb_joint_asr            as documented below, states 0..19;
  *   phb_transition_matrices  out[(k * n_cat + c) * 400 + 20 * i + j];
+ *   phb_score_nni, phb_score_trees   every neighbour / candidate is re-scheduled and scored in full against the
+ *                            resident alignment and model (the reference's caller loop; the cached-partials walk of
+ *                            phb_score_nni is a 4-state kernel set, nni_path_moves stays 0);
  * rate-0 categories are evaluated literally (identity P).  One device per context.  Every other entry point returns
  * PHB_ERR_STATE. */
 #define PHB_FLAG_AMINO_ACID (1ull << 5)

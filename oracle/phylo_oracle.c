@@ -778,7 +778,9 @@ static void *lnl_opt_worker(void *arg)
                     goto done;
                 }
                 for (int b = 0; b < OB; ++b) {
-                    double pv[NS] = {1, 1, 1, 1}, l = 0.0;
+                    double pv[NS], l = 0.0;
+                    for (int i = 0; i < NS; ++i)
+                        pv[i] = 1.0;
                     if (b < nb) {
                         if (!alphabet_profile(J->patterns[(size_t)(p0 + b) * J->n_rows + row], pv)) {
                             J->status = ORC_ERR_ALPHABET_MISMATCH;
@@ -808,17 +810,17 @@ static void *lnl_opt_worker(void *arg)
                         for (int i = 0; i < NS; ++i)
                             for (int b = 0; b < OB; ++b) {
                                 double acc = P[i * NS + 0] * in[0 * OB + b];
-                                acc += P[i * NS + 1] * in[1 * OB + b];
-                                acc += P[i * NS + 2] * in[2 * OB + b];
-                                acc += P[i * NS + 3] * in[3 * OB + b];
+                                for (int j = 1; j < NS; ++j)
+                                    acc += P[i * NS + j] * in[j * OB + b];
                                 out[i * OB + b] *= acc;
                             }
                         for (int b = 0; b < OB; ++b)
                             lo[b] += li[b];
                     }
                     for (int b = 0; b < OB; ++b) {
-                        double mx = fmax(fmax(out[0 * OB + b], out[1 * OB + b]),
-                                         fmax(out[2 * OB + b], out[3 * OB + b]));
+                        double mx = out[b];
+                        for (int i = 1; i < NS; ++i)
+                            mx = fmax(mx, out[i * OB + b]);
                         if (mx > 0.0) {
                             for (int i = 0; i < NS; ++i)
                                 out[i * OB + b] /= mx;

@@ -150,6 +150,7 @@ int aa_evaluate(phb_ctx *ctx, bool asr, uint8_t *states_out, double *post_out, d
         return ctx->fail(PHB_ERR_STATE, "set_alignment, set_model and set_tree must precede the evaluation");
     int rc = check_leaves(ctx);
     if (rc) return rc;
+    if (!ctx->tree_uploaded && (rc = aa_upload_tree(ctx))) return rc; // after phb_score_nni / phb_score_trees
     CU(cudaSetDevice(d.ordinal));
     const int64_t P = ctx->n_patterns;
     const int K = A.M.n_cat;
@@ -263,6 +264,7 @@ int aa_joint(phb_ctx *ctx, uint8_t *states_out, double *total)
         return ctx->fail(PHB_ERR_STATE, "set_alignment, set_model and set_tree must precede the evaluation");
     int rc = check_leaves(ctx);
     if (rc) return rc;
+    if (!ctx->tree_uploaded && (rc = aa_upload_tree(ctx))) return rc; // after phb_score_nni / phb_score_trees
     CU(cudaSetDevice(d.ordinal));
     const int64_t P = ctx->n_patterns;
     const int K = A.M.n_cat;

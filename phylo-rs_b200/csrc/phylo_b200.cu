@@ -2727,7 +2727,6 @@ int32_t phb_joint_asr(phb_ctx *ctx, uint8_t *states, double *total)
 int32_t phb_score_nni(phb_ctx *ctx, int32_t n_moves, const int32_t *node_id, const uint8_t *left_ch, double *totals)
 {
     if (!ctx || n_moves < 0 || (n_moves > 0 && (!node_id || !left_ch || !totals))) return PHB_ERR_INVALID_ARGUMENT;
-    if (ctx->is_aa) return ctx->fail(PHB_ERR_STATE, "score_nni: not available in a 20-state (PHB_FLAG_AMINO_ACID) context");
     if (!ctx->tree.valid) return ctx->fail(PHB_ERR_STATE, "score_nni: set_tree first");
     if (!ctx->have_aln || !ctx->have_model)
         return ctx->fail(PHB_ERR_STATE, "score_nni: set_alignment and set_model first");
@@ -2735,8 +2734,9 @@ int32_t phb_score_nni(phb_ctx *ctx, int32_t n_moves, const int32_t *node_id, con
     ctx->stats.nni_path_steps = 0;
     ctx->stats.nni_tiles = 0;
     ctx->stats.nni_cache_bytes = ctx->stats.nni_read_bytes = 0;
-    // Binary trees: walk v -> root against the cached CLVs of the base tree (nni.cuh).
-    if (nni_path_eligible(ctx)) return score_nni_paths(ctx, n_moves, node_id, left_ch, totals);
+    // Binary trees: walk v -> root against the cached CLVs of the base tree (nni.cuh).  20-state contexts take the
+    // full re-scoring below (aa_evaluate per neighbour).
+    if (!ctx->is_aa && nni_path_eligible(ctx)) return score_nni_paths(ctx, n_moves, node_id, left_ch, totals);
     // Otherwise (polytomies / unifurcations, PHB_FLAG_NNI_FULL): each neighbour is re-scheduled and scored
     // from scratch, which is what the reference's caller loop does.
     TreeSched base = ctx->tree;
@@ -2776,7 +2776,7 @@ int32_t phb_score_nni(phb_ctx *ctx, int32_t n_moves, const int32_t *node_id, con
         rc = T.build(ctx->err);
         if (rc) break;
         ctx->tree_uploaded = false;
-        rc = evaluate(ctx, false, false, &totals[m]);
+        rc = ctx->is_aa ? aa_evaluate(ctx, false, nullptr, nullptr, &totals[m]) : evaluate(ctx, false, false, &totals[m]);
     }
     for (Device &d : ctx->devs) {
         cudaSetDevice(d.ordinal);
@@ -2795,7 +2795,6 @@ int32_t phb_score_nni(phb_ctx *ctx, int32_t n_moves, const int32_t *node_id, con
 int32_t phb_score_trees(phb_ctx *ctx, int32_t n_trees, const phb_tree_desc *trees, double *totals)
 {
     if (!ctx || n_trees < 0 || (n_trees > 0 && (!trees || !totals))) return PHB_ERR_INVALID_ARGUMENT;
-    if (ctx->is_aa) return ctx->fail(PHB_ERR_STATE, "score_trees: not available in a 20-state (PHB_FLAG_AMINO_ACID) context");
     if (!ctx->have_aln || !ctx->have_model) return ctx->fail(PHB_ERR_STATE, "score_trees: set_alignment and set_model first");
     const bool had_tree = ctx->tree.valid;
     for (Device &d : ctx->devs) {
@@ -2808,7 +2807,7 @@ int32_t phb_score_trees(phb_ctx *ctx, int32_t n_trees, const phb_tree_desc *tree
         const phb_tree_desc &t = trees[i];
         totals[i] = NAN;
         int r2 = phb_set_tree(ctx, t.n_nodes, t.postorder, t.child_offsets, t.children, t.branch_len, t.leaf_row, t.root);
-        if (r2 == PHB_OK) r2 = evaluate(ctx, false, false, &totals[i]);
+        if (r2 == PHB_OK) r2 = ctx->is_aa ? aa_evaluate(ctx, false, nullptr, nullptr, &totals[i]) : evaluate(ctx, false, false, &totals[i]);
         if (r2 == PHB_ERR_CUDA || r2 == PHB_ERR_OOM) rc = r2; // device trouble ends the batch; a bad candidate does not
         else if (r2 != PHB_OK) totals[i] = NAN;
     }

@@ -100,6 +100,45 @@ def check_nni(lib, case, moves=None, flags=0, budget=None, devices=None, expect_
     return got, st
 
 
+def check_score_trees(lib, case, flags=0, seed=72):
+    """phb_score_trees: the caller loop `t = base.clone(); t.spr(e1, e2); t.log_likelihood(..)` (src/tree/ops.rs:34-41,
+    src/tree.rs:1161-1204) as one call.  The candidates are built by the oracle's tree with the reference's prune /
+    graft semantics (the pruned node's parent stays behind as a unifurcation, a new node splits the target edge)."""
+    from oracle.refhost import Node
+
+    base = case.tree
+    ids = [i for i in base.get_node_ids()]
+    rng = np.random.default_rng(seed)
+    cands, refs = [], []
+    for _ in range(400):
+        if len(cands) == 5:
+            break
+        t = base.clone()
+        x, y = int(rng.choice(ids)), int(rng.choice(ids))
+        px, py = t.nodes[x].parent, t.nodes[y].parent
+        if px is None or py is None or y in set(t.preord_ids(x)):
+            continue
+        t.delete_edge(px, x)                # SPR::prune: the subtree leaves its parent, which stays behind
+        new = Node(t.next_id())             # SPR::graft: a new node splits the target edge (no weight: length 0) ...
+        t.split_edge((py, y), new)
+        t.set_child(new.id, x)              # ... and takes the pruned subtree as its second child
+        ft = workloads.flatten_fast(t, case.leaf_order)
+        cands.append((ft["postorder"], ft["child_off"], ft["children"], ft["blen"], ft["leaf_row"], ft["root"]))
+        refs.append(oracle.log_likelihood_flat(ft, case.model, case.patterns, case.mult, mode=0, n_threads=4)[0])
+    assert len(cands) >= 3
+    with capi.Context(flags=flags, library=lib) as ctx:
+        workloads.load_into(ctx, case)
+        before = ctx.log_likelihood()
+        bad = list(cands[0])
+        bad[4] = np.full_like(np.asarray(bad[4]), -1)  # no leaf has a row: unschedulable, scores NaN
+        got = ctx.score_trees(cands + [tuple(bad)])
+        assert ctx.log_likelihood() == before  # the context's own tree is untouched
+    assert np.isnan(got[-1])
+    for g, r in zip(got[:-1], refs):
+        assert abs(g - r) <= 1e-9 * abs(r)
+    assert len({round(float(x), 6) for x in got[:-1]}) > 1
+
+
 def check_joint(lib, case, devices=None, budget=None, flags=0):
     """phb_joint_asr against the oracle's compute_joint_asr restatement.  Per-pattern Viterbi values within
     1e-8 absolute, total within 1e-9 relative, states bit-exact except at audited numerical ties: a differing

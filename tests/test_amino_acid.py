@@ -141,6 +141,16 @@ def _star_and_polytomy(lib):
     _cases.check_joint(lib, case, flags=AA)
 
 
+def _rearrangements(lib):
+    """phb_score_nni / phb_score_trees in a 20-state context: every neighbour / candidate is re-scheduled and scored in
+    full (the reference's caller loop: clone, NNI::nni src/tree.rs:1213-1242 or SPR::spr src/tree/ops.rs:34-41,
+    log_likelihood), against the oracle on each rebuilt tree"""
+    case = workloads.make_case(9, 40, model="aa_i_g4", seed=17, ambiguity=0.1)
+    _, st = _cases.check_nni(lib, case, flags=AA, expect_path=False)
+    assert st["nni_path_moves"] == 0
+    _cases.check_score_trees(lib, workloads.make_case(11, 30, model="aa_g4", seed=19, ambiguity=0.05), flags=AA)
+
+
 def _abi_behaviour(lib):
     case = workloads.make_case(6, 20, model="aa_g4", seed=3, ambiguity=0.2)
     m, ft = case.model, case.ft
@@ -165,10 +175,9 @@ def _abi_behaviour(lib):
         for c in range(len(m.rates)):
             assert np.max(np.abs(Pm[1, c] - m.category_transition(c, 0.3))) <= 1e-13
         # entry points without a 20-state instance say so
-        for call in (lambda: ctx.score_nni([0], [0]), lambda: ctx.transition_matrices_noalloc([0.1], 4)):
-            with pytest.raises(capi.PhbError) as ei:
-                call()
-            assert ei.value.variant == "State" and "20-state" in str(ei.value)
+        with pytest.raises(capi.PhbError) as ei:
+            ctx.transition_matrices_noalloc([0.1], 4)
+        assert ei.value.variant == "State" and "20-state" in str(ei.value)
         # a nucleotide-only byte in a LEAF row: AlphabetMismatch at evaluation (likelihood.rs:105-107)
         bad = case.patterns.copy()
         bad[7, 2] = ord("O")
@@ -191,6 +200,15 @@ def _abi_behaviour(lib):
 @pytest.mark.parametrize("model", workloads.AA_MODELS)
 def test_emu_lnl_and_asr(emu_lib, model):
     _parity(emu_lib, 14, 150, model, seed=11)
+
+
+def test_emu_rearrangements(emu_lib):
+    _rearrangements(emu_lib)
+
+
+@pytest.mark.gpu
+def test_gpu_rearrangements(gpu_lib):
+    _rearrangements(gpu_lib)
 
 
 def test_emu_tiling_polytomy_abi(emu_lib):
