@@ -209,7 +209,8 @@ int32_t phb_get_per_pattern(phb_ctx *ctx, double *per_pattern);
 /* Batch scoring of NNI neighbours of the tree set by phb_set_tree (config 5; caller loop
  * `t.nni(node, left_ch); t.log_likelihood(..)`, NNI::nni src/tree.rs:1213-1242).  For each i the
  * tree is the base tree with nni(node_id[i], left_ch[i]) applied (dense ids); totals[i] receives
- * its log-likelihood.  Invalid moves (leaf/root) yield NaN in totals[i]. */
+ * its log-likelihood.  Invalid moves yield NaN in totals[i]: an unknown node, a leaf or the root (the reference's
+ * Err), and the two moves its indexing panics on (the second child of a unifurcation, a node without a sibling). */
 int32_t phb_score_nni(phb_ctx *ctx, int32_t n_moves, const int32_t *node_id, const uint8_t *left_ch,
                       double *totals);
 

@@ -2744,7 +2744,9 @@ int32_t phb_score_nni(phb_ctx *ctx, int32_t n_moves, const int32_t *node_id, con
     for (int m = 0; m < n_moves && rc == PHB_OK; ++m) {
         int v = node_id[m];
         totals[m] = NAN;
-        if (v < 0 || v >= base.n || v == base.root || base.child_off[v + 1] - base.child_off[v] < 2) continue;
+        // NaN: unknown node, leaf or root (the reference's Err), and the two cases its indexing panics on -- the second
+        // child of a unifurcation, a node without a sibling.  A unifurcation's ONLY child (left_ch == false) does move.
+        if (v < 0 || v >= base.n || v == base.root || base.child_off[v + 1] - base.child_off[v] <= (left_ch[m] ? 1 : 0)) continue;
         // NNI::nni, src/tree.rs:1213-1242 on dense child lists
         std::vector<std::vector<int>> ch(base.n);
         for (int u = 0; u < base.n; ++u)
