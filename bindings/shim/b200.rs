@@ -232,18 +232,12 @@ fn load<A: Alphabet>(
 }
 
 /// The faster load: the sequences go across as they lie in `Alignment::seqs` and the device performs
-/// `compress_columns` (patterns numbered by first appearance, as on the host).  The 20-state instance has no
-/// device compressor: it takes the host-side `load`.
+/// `compress_columns` (patterns numbered by first appearance, as on the host), for either alphabet.
 fn load_dev<A: Alphabet>(
     tree: &PhyloTree,
     model: &GtrModel<A>,
     aln: &Alignment,
 ) -> Result<(*mut sys::phb_ctx, Flat, Vec<u64>, usize), AsrError> {
-    if A::N_STATES != 4 {
-        let (c, f, comp) = load(tree, model, aln)?;
-        let s2p: Vec<u64> = comp.site_to_pattern.iter().map(|&s| s as u64).collect();
-        return Ok((c, f, s2p, comp.patterns.len()));
-    }
     let c = ctx::<A>()?;
     let leaf_order: Vec<String> = aln.seqs.keys().cloned().collect();
     let f = flatten(tree, &leaf_order)?; // errors before the device is touched

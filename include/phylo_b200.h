@@ -71,6 +71,9 @@ extern "C" {
  *   phb_marginal_asr         states are indices 0..19 into CANONICAL, posteriors [n_nodes][n_patterns][20];
  *   phb_joint_asr            as documented below, states 0..19;
  *   phb_transition_matrices  out[(k * n_cat + c) * 400 + 20 * i + j];
+ *   phb_compress_columns, phb_compress_rows   as documented below (the compressor compares bytes and does not look at
+ *                            the alphabet, as Alignment::compress_columns does not); the unique columns are encoded to
+ *                            20-state tip codes on the device;
  *   phb_score_nni, phb_score_trees   every neighbour / candidate is re-scheduled and scored in full against the
  *                            resident alignment and model (the reference's caller loop; the cached-partials walk of
  *                            phb_score_nni is a 4-state kernel set, nni_path_moves stays 0);

@@ -117,6 +117,19 @@ __global__ void aa_pack_kernel(const uint8_t *__restrict__ raw, int pattern_majo
         }
     }
 }
+// The unique columns of a compressed alignment (compress.cuh: raw[row][site] at `pitch`, replist[p] = first site of
+// pattern p) -> tip codes [row][P_pad].  blockIdx.y = row; consecutive threads = consecutive patterns (first-appearance
+// order, so replist ascends and the reads of one row stay near each other).
+__global__ void aa_gather_patterns_kernel(const uint8_t *__restrict__ raw, int64_t pitch, const uint32_t *__restrict__ replist,
+                                          int64_t P, int r0, uint8_t *__restrict__ tips, int64_t P_pad, int *__restrict__ row_flags)
+{
+    const int r = r0 + blockIdx.y;
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P; p += (int64_t)gridDim.x * blockDim.x) {
+        const uint8_t c = aa_encode_byte(raw[(size_t)r * pitch + replist[p]]);
+        tips[(size_t)r * P_pad + p] = c;
+        if (c == CODE_INVALID) atomicOr(reinterpret_cast<unsigned *>(row_flags + r), p == 0 ? 3u : 1u);
+    }
+}
 __global__ void aa_fill_pad_kernel(uint8_t *__restrict__ tips, int n_rows, int64_t P, int64_t P_pad)
 {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -75,6 +75,54 @@ int aa_set_alignment(phb_ctx *ctx, int32_t n_rows, int64_t P, const uint8_t *byt
     return PHB_OK;
 }
 
+// phb_compress_columns / phb_compress_rows in a 20-state context: the unique columns found on the device (compress_impl,
+// alphabet-agnostic as Alignment::compress_columns is, alignment.rs:95-139) become the context's alignment without a
+// trip through the host.  raw / replist / mult_u64 are compress_impl's device buffers; the work is queued on d.stream.
+int aa_adopt_compressed(phb_ctx *ctx, int32_t n_rows, int64_t P, const uint8_t *raw, int64_t pitch, const uint32_t *replist,
+                        const uint64_t *mult_u64)
+{
+    AaState &A = aa_of(ctx);
+    Device &d = ctx->devs[0];
+    CU(cudaSetDevice(d.ordinal));
+    ctx->n_rows = n_rows;
+    ctx->n_patterns = P;
+    A.P_pad = round_up(std::max<int64_t>(P, 1), AA_THREADS);
+    const int nr1 = std::max(n_rows, 1);
+    ctx->row_invalid_host.assign(nr1, 0);
+    ctx->row_first_invalid.assign(nr1, 0);
+    CU(A.tips.ensure((size_t)nr1 * (size_t)A.P_pad));
+    CU(A.row_flags.ensure(sizeof(int) * (size_t)nr1));
+    CU(A.mult.ensure(sizeof(double) * (size_t)A.P_pad));
+    CU(cudaMemsetAsync(A.row_flags.p, 0, sizeof(int) * (size_t)nr1, d.stream));
+    if (n_rows > 0 && A.P_pad > P) {
+        const int64_t cells = (int64_t)n_rows * (A.P_pad - P);
+        PHB_LAUNCH(aa_fill_pad_kernel, dim3((unsigned)((cells + 255) / 256)), dim3(256), d.stream, A.tips.as<uint8_t>(), n_rows, P, A.P_pad);
+        CHECK_LAUNCH();
+    }
+    for (int r0 = 0; r0 < n_rows && P > 0; r0 += 32768) {
+        dim3 grid((unsigned)std::min<int64_t>((P + 255) / 256, 1024), (unsigned)std::min(32768, n_rows - r0));
+        PHB_LAUNCH(aa_gather_patterns_kernel, grid, dim3(256), d.stream, raw, pitch, replist, P, r0, A.tips.as<uint8_t>(), A.P_pad,
+                   A.row_flags.as<int>());
+        CHECK_LAUNCH();
+    }
+    if (P > 0) {
+        PHB_LAUNCH(mult_u64_to_double_kernel, dim3((unsigned)std::min<int64_t>((A.P_pad + 255) / 256, 4096)), dim3(256), d.stream,
+                   mult_u64, (int64_t)0, P, A.P_pad, A.mult.as<double>());
+        CHECK_LAUNCH();
+    } else
+        CU(cudaMemsetAsync(A.mult.p, 0, sizeof(double) * (size_t)A.P_pad, d.stream));
+    std::vector<int> flags((size_t)nr1, 0);
+    CU(cudaMemcpyAsync(flags.data(), A.row_flags.p, sizeof(int) * (size_t)nr1, cudaMemcpyDeviceToHost, d.stream));
+    CU(cudaStreamSynchronize(d.stream));
+    for (int r = 0; r < n_rows; ++r) {
+        ctx->row_invalid_host[r] = (flags[r] & 1) != 0;
+        ctx->row_first_invalid[r] = (flags[r] & 2) != 0;
+    }
+    A.tip_const_valid = false;
+    ctx->have_aln = true;
+    return PHB_OK;
+}
+
 int aa_set_model(phb_ctx *ctx, const double *lambda, const double *V, const double *pi, const double *sqrt_pi,
                  const double *inv_sqrt_pi, int32_t n_cat, const double *rates, const double *weights)
 {

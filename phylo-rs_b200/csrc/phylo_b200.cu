@@ -2224,7 +2224,6 @@ static int32_t compress_impl(phb_ctx *ctx, int32_t n_rows, int64_t width, const 
                              int64_t *n_patterns, uint64_t *site_to_pattern, uint64_t *multiplicity)
 {
     if (!ctx || !n_patterns) return PHB_ERR_INVALID_ARGUMENT;
-    if (ctx->is_aa) return ctx->fail(PHB_ERR_STATE, "compress_columns: not available in a 20-state (PHB_FLAG_AMINO_ACID) context");
     if (n_rows < 0 || width < 0 || width > 0x7fffffff || (!bytes && !row_ptrs && n_rows > 0 && width > 0))
         return ctx->fail(PHB_ERR_INVALID_ARGUMENT, "compress_columns: bad arguments");
     if (!bytes && row_ptrs)
@@ -2232,6 +2231,7 @@ static int32_t compress_impl(phb_ctx *ctx, int32_t n_rows, int64_t width, const 
             if (!row_ptrs[r]) return ctx->fail(PHB_ERR_INVALID_ARGUMENT, "compress_rows: row %d is null", r);
     ctx->have_aln = false;
     *n_patterns = 0;
+    if (width == 0 && ctx->is_aa) return aa_adopt_compressed(ctx, n_rows, 0, nullptr, 0, nullptr, nullptr);
     if (width == 0) { // no sites: no patterns (alignment.rs:102 never iterates)
         int rc0 = shard_and_alloc(ctx, n_rows, 0);
         if (rc0) return rc0;
@@ -2375,6 +2375,13 @@ static int32_t compress_impl(phb_ctx *ctx, int32_t n_rows, int64_t width, const 
     CU(cudaStreamSynchronize(d0.stream));
     lap("pattern ids + results to host");
     // 5. the unique columns become the context's alignment: tip codes [row][pattern] per device shard
+    if (ctx->is_aa) { // 20-state codes, one device (aa_engine.cuh)
+        int rca = aa_adopt_compressed(ctx, n_rows, P, raw.as<uint8_t>(), pitch, replist.as<uint32_t>(), mult.as<uint64_t>());
+        if (rca) return rca;
+        lap("gather to 20-state tip codes");
+        *n_patterns = P;
+        return PHB_OK;
+    }
     int rc = shard_and_alloc(ctx, n_rows, P);
     if (rc) return rc;
     ctx->row_invalid_host.assign(std::max(n_rows, 1), 0);

@@ -151,6 +151,47 @@ def _rearrangements(lib):
     _cases.check_score_trees(lib, workloads.make_case(11, 30, model="aa_g4", seed=19, ambiguity=0.05), flags=AA)
 
 
+def _compression(lib):
+    """phb_compress_columns / phb_compress_rows in a 20-state context (Alignment::compress_columns, alignment.rs:93-139, is
+    alphabet-agnostic): pattern numbering bit-exact against the oracle's restatement, and the evaluation of the adopted
+    patterns equals the oracle on the host-compressed alignment"""
+    from oracle import RefAlignment
+
+    case = workloads.make_case(12, 90, model="aa_g4", seed=23, ambiguity=0.1)
+    rng = np.random.default_rng(24)
+    pick = rng.integers(90, size=700)
+    rows = np.ascontiguousarray(case.patterns[pick].T)  # [row][site], 700 sites over <= 90 distinct columns
+    n_rows, width = rows.shape
+    pats, s2p, mult, _ = RefAlignment({f"r{i:02d}": bytes(rows[i]) for i in range(n_rows)}, width).compress_columns()
+    ref_tot, ref_per = oracle.log_likelihood_flat(case.ft, case.model, pats, mult, mode=0, n_threads=4)
+    m, ft = case.model, case.ft
+    for by_rows in (False, True):
+        with capi.Context(flags=AA, library=lib) as ctx:
+            if by_rows:
+                n, got_s2p, got_mult = ctx.compress_rows([rows[r].tobytes() for r in range(n_rows)])
+            else:
+                n, got_s2p, got_mult = ctx.compress_columns(rows)
+            assert n == len(pats)
+            assert np.array_equal(got_s2p.astype(np.int64), s2p) and np.array_equal(got_mult, mult)
+            ctx.set_model(m.eigenvalues, m.eigenvectors, m.pi, m.sqrt_pi, m.inv_sqrt_pi, m.rates, m.weights)
+            ctx.set_tree(ft["postorder"], ft["child_off"], ft["children"], ft["blen"], ft["leaf_row"], ft["root"])
+            tot, per = ctx.log_likelihood(per_pattern=True)
+            _cases.assert_lnl_close(tot, per, ref_tot, ref_per)
+            tot_a, states, _ = ctx.marginal_asr()
+            assert abs(tot_a - ref_tot) <= 1e-9 * abs(ref_tot) and states.shape == (ft["n_nodes"], n)
+            # a byte AminoAcid::profile rejects, in a leaf row: AlphabetMismatch at evaluation, not at compression
+            bad = rows.copy()
+            bad[3, 5] = ord("O")
+            ctx.compress_columns(bad)
+            with pytest.raises(capi.PhbError) as ei:
+                ctx.log_likelihood()
+            assert ei.value.variant == "AlphabetMismatch"
+            # no sites: no patterns
+            n0, s0, m0 = ctx.compress_columns(np.zeros((n_rows, 0), np.uint8))
+            assert n0 == 0 and len(s0) == 0 and len(m0) == 0
+            assert ctx.log_likelihood() == 0.0
+
+
 def _abi_behaviour(lib):
     case = workloads.make_case(6, 20, model="aa_g4", seed=3, ambiguity=0.2)
     m, ft = case.model, case.ft
@@ -200,6 +241,15 @@ def _abi_behaviour(lib):
 @pytest.mark.parametrize("model", workloads.AA_MODELS)
 def test_emu_lnl_and_asr(emu_lib, model):
     _parity(emu_lib, 14, 150, model, seed=11)
+
+
+def test_emu_compression(emu_lib):
+    _compression(emu_lib)
+
+
+@pytest.mark.gpu
+def test_gpu_compression(gpu_lib):
+    _compression(gpu_lib)
 
 
 def test_emu_rearrangements(emu_lib):
