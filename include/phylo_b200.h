@@ -74,6 +74,7 @@ extern "C" {
  *   phb_compress_columns, phb_compress_rows   as documented below (the compressor compares bytes and does not look at
  *                            the alphabet, as Alignment::compress_columns does not); the unique columns are encoded to
  *                            20-state tip codes on the device;
+ *   phb_get_alignment        the 25 accepted bytes read back as themselves, any other byte as '?';
  *   phb_score_nni, phb_score_trees   every neighbour / candidate is re-scheduled and scored in full against the
  *                            resident alignment and model (the reference's caller loop; the cached-partials walk of
  *                            phb_score_nni is a 4-state kernel set, nni_path_moves stays 0);

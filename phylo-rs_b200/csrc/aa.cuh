@@ -130,6 +130,17 @@ __global__ void aa_gather_patterns_kernel(const uint8_t *__restrict__ raw, int64
         if (c == CODE_INVALID) atomicOr(reinterpret_cast<unsigned *>(row_flags + r), p == 0 ? 3u : 1u);
     }
 }
+// tip codes -> the canonical byte of each code ('?' for a byte the alphabet rejects), either layout (phb_get_alignment)
+__global__ void aa_unpack_kernel(const uint8_t *__restrict__ tips, int n_rows, int row0, int64_t P_pad, int64_t first, int64_t n,
+                                 int layout, uint8_t *__restrict__ out)
+{
+    const int r = row0 + blockIdx.y;
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (int64_t)gridDim.x * blockDim.x) {
+        const uint8_t ch = aa_decode_code(tips[(size_t)r * P_pad + first + p]);
+        if (layout == 0) out[p * n_rows + r] = ch;
+        else out[(int64_t)r * n + p] = ch;
+    }
+}
 __global__ void aa_fill_pad_kernel(uint8_t *__restrict__ tips, int n_rows, int64_t P, int64_t P_pad)
 {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -123,6 +123,25 @@ int aa_adopt_compressed(phb_ctx *ctx, int32_t n_rows, int64_t P, const uint8_t *
     return PHB_OK;
 }
 
+int aa_get_alignment(phb_ctx *ctx, uint8_t *bytes, int32_t layout, int64_t first, int64_t cnt)
+{
+    AaState &A = aa_of(ctx);
+    Device &d = ctx->devs[0];
+    const int n_rows = ctx->n_rows;
+    if (cnt == 0 || n_rows == 0) return PHB_OK;
+    CU(cudaSetDevice(d.ordinal));
+    CU(d.staging.ensure((size_t)cnt * n_rows));
+    for (int r0 = 0; r0 < n_rows; r0 += 32768) {
+        dim3 grid((unsigned)std::min<int64_t>((cnt + 255) / 256, 4096), (unsigned)std::min(32768, n_rows - r0));
+        PHB_LAUNCH(aa_unpack_kernel, grid, dim3(256), d.stream, A.tips.as<uint8_t>(), n_rows, r0, A.P_pad, first, cnt, (int)layout,
+                   d.staging.as<uint8_t>());
+        CHECK_LAUNCH();
+    }
+    CU(cudaMemcpyAsync(bytes, d.staging.p, (size_t)cnt * n_rows, cudaMemcpyDeviceToHost, d.stream));
+    CU(cudaStreamSynchronize(d.stream));
+    return PHB_OK;
+}
+
 int aa_set_model(phb_ctx *ctx, const double *lambda, const double *V, const double *pi, const double *sqrt_pi,
                  const double *inv_sqrt_pi, int32_t n_cat, const double *rates, const double *weights)
 {

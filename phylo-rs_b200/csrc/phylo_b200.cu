@@ -2909,10 +2909,10 @@ int32_t phb_simulate_alignment(phb_ctx *ctx, int64_t n_patterns, int64_t global_
 int32_t phb_get_alignment(phb_ctx *ctx, uint8_t *bytes, int32_t layout, int64_t first_pattern, int64_t n_patterns)
 {
     if (!ctx || !bytes || first_pattern < 0 || n_patterns < 0) return PHB_ERR_INVALID_ARGUMENT;
-    if (ctx->is_aa) return ctx->fail(PHB_ERR_STATE, "get_alignment: not available in a 20-state (PHB_FLAG_AMINO_ACID) context");
     if (!ctx->have_aln) return ctx->fail(PHB_ERR_STATE, "get_alignment: no alignment set");
     if (first_pattern + n_patterns > ctx->n_patterns || (layout != 0 && layout != 1))
         return ctx->fail(PHB_ERR_INVALID_ARGUMENT, "get_alignment: range or layout out of bounds");
+    if (ctx->is_aa) return aa_get_alignment(ctx, bytes, layout, first_pattern, n_patterns);
     const int n_rows = ctx->n_rows;
     for (Device &d : ctx->devs) {
         int64_t lo = std::max(first_pattern, d.p_begin), hi = std::min(first_pattern + n_patterns, d.p_begin + d.P);

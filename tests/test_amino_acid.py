@@ -173,6 +173,9 @@ def _compression(lib):
                 n, got_s2p, got_mult = ctx.compress_columns(rows)
             assert n == len(pats)
             assert np.array_equal(got_s2p.astype(np.int64), s2p) and np.array_equal(got_mult, mult)
+            # the adopted patterns, read back in both layouts (all 25 accepted bytes are their own canonical byte)
+            assert np.array_equal(ctx.get_alignment(), pats)
+            assert np.array_equal(ctx.get_alignment(first=3, count=11, layout=capi.LAYOUT_ROW_MAJOR), pats[3:14].T)
             ctx.set_model(m.eigenvalues, m.eigenvectors, m.pi, m.sqrt_pi, m.inv_sqrt_pi, m.rates, m.weights)
             ctx.set_tree(ft["postorder"], ft["child_off"], ft["children"], ft["blen"], ft["leaf_row"], ft["root"])
             tot, per = ctx.log_likelihood(per_pattern=True)
@@ -183,6 +186,7 @@ def _compression(lib):
             bad = rows.copy()
             bad[3, 5] = ord("O")
             ctx.compress_columns(bad)
+            assert int((ctx.get_alignment() == ord("?")).sum()) == 1  # the rejected byte, and nothing else
             with pytest.raises(capi.PhbError) as ei:
                 ctx.log_likelihood()
             assert ei.value.variant == "AlphabetMismatch"
@@ -210,6 +214,7 @@ def _abi_behaviour(lib):
         assert abs(tot_m - float((per * mult).sum())) <= 1e-12 * abs(tot_m)
         ctx.set_alignment(case.patterns)
         assert ctx.log_likelihood() == tot
+        assert np.array_equal(ctx.get_alignment(), case.patterns)
         # P(t) at 20 states, exact identity at t == 0
         Pm = ctx.transition_matrices(np.array([0.0, 0.3]), len(m.rates))
         assert np.array_equal(Pm[0, 0], np.eye(20)) and Pm.shape == (2, len(m.rates), 20, 20)
