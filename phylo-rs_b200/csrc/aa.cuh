@@ -408,6 +408,48 @@ aa_root_kernel(int root_slot, int root_row, const AaModelDev *__restrict__ M, co
     if (threadIdx.x == 0) partials[blockIdx.x] = red[0];
 }
 
+// ---- NNI neighbours (aa_engine.cuh aa_score_nni): the root of neighbour blockIdx.y lies in slot root_slots[blockIdx.y];
+// the same arithmetic as aa_root_kernel (the category values are formed twice instead of being parked in HBM), the
+// per-block sums of multiplicity * site_ll go to partials[neighbour][block].
+__global__ void __launch_bounds__(AA_THREADS)
+aa_nni_root_kernel(const int *__restrict__ root_slots, const AaModelDev *__restrict__ M, const double *__restrict__ clv,
+                   const int *__restrict__ exps, size_t slot_stride, size_t tile_pad, int tile_len, int64_t tile_off,
+                   const double *__restrict__ leaf_ls, const double *__restrict__ mult, double *__restrict__ partials)
+{
+    __shared__ double red[AA_THREADS];
+    const int64_t site = (int64_t)blockIdx.x * AA_THREADS + threadIdx.x;
+    const int n_cat = M->n_cat;
+    const int root_slot = root_slots[blockIdx.y];
+    double weighted = 0.0;
+    if (site < tile_len) {
+        auto cat_value = [&](int c) {
+            double x[AA_NS];
+            aa_load_vec(clv, slot_stride, tile_pad, root_slot, c, site, x);
+            const int ex = exps[((size_t)root_slot * n_cat + c) * tile_pad + site];
+            double mass = M->pi[0] * x[0];
+#pragma unroll
+            for (int i = 1; i < AA_NS; ++i) mass += M->pi[i] * x[i];
+            return M->ln_weights[c] + log(mass) + (double)ex * 0.69314718055994530942;
+        };
+        double mx = -INFINITY;
+        for (int c = 0; c < n_cat; ++c) mx = fmax(mx, cat_value(c));
+        double lse = mx;
+        if (isfinite(mx)) {
+            double sum = 0.0;
+            for (int c = 0; c < n_cat; ++c) sum += exp(cat_value(c) - mx);
+            lse = mx + log(sum);
+        }
+        weighted = mult[tile_off + site] * (lse + leaf_ls[tile_off + site]);
+    }
+    red[threadIdx.x] = weighted;
+    __syncthreads();
+    for (int s = AA_THREADS / 2; s > 0; s >>= 1) {
+        if ((int)threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) partials[(size_t)blockIdx.y * gridDim.x + blockIdx.x] = red[0];
+}
+
 // ---- one depth of the marginal pre-order pass (likelihood.rs:303-390) -------------------------------------------------
 // grid: x = pattern blocks of the tile, y = node of the depth.  A thread owns one pattern and loops over the categories:
 //   root:   post = pi (.) up                                                        (:304-316)

@@ -321,6 +321,181 @@ int aa_evaluate(phb_ctx *ctx, bool asr, uint8_t *states_out, double *post_out, d
     return PHB_OK;
 }
 
+// phb_score_nni at 20 states (caller loop: clone, NNI::nni src/tree.rs:1213-1242, log_likelihood).  An NNI at v changes the
+// partials of v, of its parent and of their ancestors only, and no branch length: with the base tree's CLVs of a pattern tile
+// resident, a neighbour costs depth(v) + 1 node updates instead of a whole sweep.  The updates of a BATCH of neighbours run
+// side by side -- step j of every neighbour's path in one aa_clv_kernel launch (any arity, the child lists in the order
+// the re-linked tree has them: the moved child / sibling appended last) -- into two scratch slots per neighbour used in
+// turn; aa_nni_root_kernel then reads each neighbour's root.  Same kernels, same child order, same P(t): the totals are
+// those of a full re-scoring of the rebuilt tree (PHB_FLAG_NNI_FULL), bit for bit.
+constexpr int AA_NNI_BATCH = 256;
+int aa_score_nni(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uint8_t *left_ch, double *totals)
+{
+    AaState &A = aa_of(ctx);
+    const TreeSched &T = ctx->tree;
+    Device &d = ctx->devs[0];
+    int rc = check_leaves(ctx);
+    if (rc) return rc;
+    if (!ctx->tree_uploaded && (rc = aa_upload_tree(ctx))) return rc;
+    CU(cudaSetDevice(d.ordinal));
+    const int64_t P = ctx->n_patterns;
+    const int K = A.M.n_cat;
+    const int n_int = std::max(T.n_internal, 1);
+    auto base_child = [&](int c) {
+        GenChild g;
+        g.is_tip = T.slot[c] < 0;
+        g.src = g.is_tip ? T.leaf_row[c] : T.slot[c];
+        g.edge = c;
+        g.pad = 0;
+        return g;
+    };
+    // ---- the valid moves and, batch by batch, their ops grouped by step
+    std::vector<int> valid;
+    for (int m = 0; m < n_moves; ++m) {
+        totals[m] = NAN;
+        const int v = node_id[m];
+        if (v < 0 || v >= T.n || v == T.root || T.child_off[v + 1] - T.child_off[v] <= (left_ch[m] ? 1 : 0)) continue;
+        const int p = T.parent[v];
+        bool has_sib = false;
+        for (int k = T.child_off[p]; k < T.child_off[p + 1]; ++k) has_sib |= T.children[k] != v;
+        if (has_sib) valid.push_back(m);
+    }
+    ctx->stats.nni_path_moves = (int64_t)valid.size();
+    if (valid.empty() || P == 0) {
+        for (int m : valid) totals[m] = 0.0;
+        return PHB_OK;
+    }
+    const int B = (int)std::min<size_t>(valid.size(), AA_NNI_BATCH);
+    struct Batch {
+        int first, count;           // range in `valid`
+        std::vector<int> step_off;  // ops of step j: [step_off[j], step_off[j+1]) (absolute op indices)
+    };
+    std::vector<Batch> batches;
+    std::vector<GenOp> ops;
+    std::vector<GenChild> kids;
+    std::vector<int> root_slots(valid.size());
+    for (int b0 = 0; b0 < (int)valid.size(); b0 += B) {
+        Batch bt;
+        bt.first = b0;
+        bt.count = std::min(B, (int)valid.size() - b0);
+        int max_len = 0;
+        std::vector<std::vector<int>> path(bt.count); // v, its parent, ..., the root
+        for (int i = 0; i < bt.count; ++i) {
+            for (int a = node_id[valid[b0 + i]]; a >= 0; a = a == T.root ? -1 : T.parent[a]) path[i].push_back(a);
+            max_len = std::max(max_len, (int)path[i].size());
+        }
+        for (int j = 0; j < max_len; ++j) {
+            bt.step_off.push_back((int)ops.size());
+            for (int i = 0; i < bt.count; ++i) {
+                const int m = valid[b0 + i];
+                const int v = node_id[m];
+                if ((int)path[i].size() <= j) continue;
+                const int p = T.parent[v];
+                const int c1 = T.children[T.child_off[v] + (left_ch[m] ? 1 : 0)];
+                int sib = -1;
+                for (int k = T.child_off[p]; k < T.child_off[p + 1] && sib < 0; ++k)
+                    if (T.children[k] != v) sib = T.children[k];
+                const int scratch[2] = {n_int + 2 * i, n_int + 2 * i + 1};
+                GenOp op;
+                op.out_slot = scratch[j & 1];
+                op.child_begin = (int)kids.size();
+                op.pad = 0;
+                if (j == 0) { // v: its children without c1, then the former sibling
+                    for (int k = T.child_off[v]; k < T.child_off[v + 1]; ++k)
+                        if (T.children[k] != c1) kids.push_back(base_child(T.children[k]));
+                    kids.push_back(base_child(sib));
+                } else {
+                    const int a = path[i][j], below = path[i][j - 1];
+                    for (int k = T.child_off[a]; k < T.child_off[a + 1]; ++k) {
+                        const int c = T.children[k];
+                        if (j == 1 && c == sib) continue; // the sibling went below v
+                        GenChild g = base_child(c);
+                        if (c == below) {
+                            g.is_tip = 0;
+                            g.src = scratch[(j - 1) & 1];
+                        }
+                        kids.push_back(g);
+                    }
+                    if (j == 1) kids.push_back(base_child(c1)); // ... and c1 came up
+                }
+                op.child_end = (int)kids.size();
+                ops.push_back(op);
+                if (j + 1 == (int)path[i].size()) root_slots[b0 + i] = op.out_slot;
+            }
+        }
+        bt.step_off.push_back((int)ops.size());
+        batches.push_back(std::move(bt));
+    }
+    ctx->stats.nni_path_steps = (int64_t)ops.size();
+    // ---- buffers: the base tree's CLVs of a pattern tile + two scratch slots per neighbour of a batch
+    const int n_slots = n_int + 2 * B;
+    size_t free_b = 0, total_b = 0;
+    CU(cudaMemGetInfo(&free_b, &total_b));
+    size_t budget = ctx->clv_budget ? (size_t)ctx->clv_budget : (free_b + A.clv.cap + A.exps.cap) / 10 * 7;
+    const size_t per_pattern_bytes = (size_t)n_slots * K * (AA_NS * sizeof(double) + sizeof(int));
+    int64_t tile_pad = (int64_t)(budget / per_pattern_bytes) / AA_THREADS * AA_THREADS;
+    tile_pad = std::max<int64_t>(AA_THREADS, std::min<int64_t>(tile_pad, A.P_pad));
+    const size_t slot_stride = (size_t)K * AA_NS * (size_t)tile_pad;
+    const int max_blocks = (int)(tile_pad / AA_THREADS);
+    CU(A.clv.ensure(sizeof(double) * slot_stride * n_slots));
+    CU(A.exps.ensure(sizeof(int) * (size_t)n_slots * K * tile_pad));
+    CU(A.leaf_ls.ensure(sizeof(double) * (size_t)A.P_pad));
+    CU(A.Pmat.ensure(sizeof(double) * AA_NS * AA_NS * (size_t)T.n * K));
+    CU(A.partials.ensure(sizeof(double) * (size_t)max_blocks * B));
+    CU(A.nni_ops.ensure(sizeof(GenOp) * ops.size()));
+    CU(A.nni_kids.ensure(sizeof(GenChild) * kids.size()));
+    CU(A.nni_roots.ensure(sizeof(int) * root_slots.size()));
+    CU(cudaMemcpyAsync(A.nni_ops.p, ops.data(), sizeof(GenOp) * ops.size(), cudaMemcpyHostToDevice, d.stream));
+    CU(cudaMemcpyAsync(A.nni_kids.p, kids.data(), sizeof(GenChild) * kids.size(), cudaMemcpyHostToDevice, d.stream));
+    CU(cudaMemcpyAsync(A.nni_roots.p, root_slots.data(), sizeof(int) * root_slots.size(), cudaMemcpyHostToDevice, d.stream));
+    const AaModelDev *Md = A.model.as<AaModelDev>();
+    PHB_LAUNCH(aa_transition_kernel, dim3((unsigned)(T.n * K)), dim3(AA_THREADS), d.stream, A.blen.as<double>(), T.n, Md, A.Pmat.as<double>());
+    CHECK_LAUNCH();
+    if (!A.tip_const_valid) {
+        PHB_LAUNCH(aa_tip_const_kernel, dim3((unsigned)((P + 255) / 256)), dim3(256), d.stream, A.leaf_rows.as<int>(),
+                   (int)T.leaf_rows.size(), A.tips.as<uint8_t>(), A.P_pad, P, A.leaf_ls.as<double>());
+        CHECK_LAUNCH();
+        A.tip_const_valid = true;
+    }
+    const unsigned kz = (unsigned)((K + AA_CSTAGE - 1) / AA_CSTAGE);
+    std::vector<double> sums(valid.size(), 0.0), h_part;
+    ctx->stats.nni_tiles = 0;
+    ctx->stats.nni_cache_bytes = (int64_t)(sizeof(double) * slot_stride * n_slots + sizeof(int) * (size_t)n_slots * K * tile_pad);
+    for (int64_t off = 0; off < P; off += tile_pad) {
+        const int tile_len = (int)std::min<int64_t>(tile_pad, P - off);
+        const unsigned bx = (unsigned)((tile_len + AA_THREADS - 1) / AA_THREADS);
+        auto clv_launch = [&](const GenOp *o, const GenChild *k, int cnt) -> int {
+            PHB_LAUNCH(aa_clv_kernel, dim3(bx, (unsigned)cnt, kz), dim3(AA_THREADS), d.stream, o, k, K, A.Pmat.as<double>(), A.clv.as<double>(),
+                       A.exps.as<int>(), slot_stride, (size_t)tile_pad, tile_len, A.tips.as<uint8_t>(), A.P_pad, off);
+            CHECK_LAUNCH();
+            return PHB_OK;
+        };
+        for (int l = 1; l <= T.n_levels; ++l) { // the base tree, as aa_evaluate does
+            const int b = T.ulevel_off[l - 1], n_ops = T.ulevel_off[l] - b;
+            for (int o = 0; o < n_ops; o += 65535)
+                if ((rc = clv_launch(A.uops.as<GenOp>() + b + o, A.ukids.as<GenChild>(), std::min(65535, n_ops - o)))) return rc;
+        }
+        for (const Batch &bt : batches) {
+            for (size_t j = 0; j + 1 < bt.step_off.size(); ++j)
+                if ((rc = clv_launch(A.nni_ops.as<GenOp>() + bt.step_off[j], A.nni_kids.as<GenChild>(), bt.step_off[j + 1] - bt.step_off[j])))
+                    return rc;
+            PHB_LAUNCH(aa_nni_root_kernel, dim3(bx, (unsigned)bt.count), dim3(AA_THREADS), d.stream, A.nni_roots.as<int>() + bt.first, Md,
+                       A.clv.as<double>(), A.exps.as<int>(), slot_stride, (size_t)tile_pad, tile_len, off, A.leaf_ls.as<double>(),
+                       A.mult.as<double>(), A.partials.as<double>());
+            CHECK_LAUNCH();
+            h_part.resize((size_t)bx * bt.count);
+            CU(cudaMemcpyAsync(h_part.data(), A.partials.p, sizeof(double) * h_part.size(), cudaMemcpyDeviceToHost, d.stream));
+            CU(cudaStreamSynchronize(d.stream));
+            for (int i = 0; i < bt.count; ++i)
+                for (unsigned x = 0; x < bx; ++x) sums[bt.first + i] += h_part[(size_t)i * bx + x]; // fixed order: deterministic
+        }
+        ctx->stats.nni_tiles++;
+    }
+    for (size_t i = 0; i < valid.size(); ++i) totals[valid[i]] = sums[i];
+    ctx->stats.kernel_launches = ctx->launches;
+    return PHB_OK;
+}
+
 // compute_joint_asr (likelihood.rs:421-560) at 20 states: states [n_nodes][n_patterns], *total = sum multiplicity * best
 int aa_joint(phb_ctx *ctx, uint8_t *states_out, double *total)
 {
@@ -445,7 +620,8 @@ void aa_release(phb_ctx *ctx)
 {
     AaState &A = aa_of(ctx);
     for (DevBuf *b : {&A.model, &A.tips, &A.mult, &A.leaf_ls, &A.per_pattern, &A.Pmat, &A.blen, &A.clv, &A.exps, &A.cat_ll, &A.partials,
-                      &A.uops, &A.ukids, &A.down, &A.leaf_rows, &A.states, &A.post, &A.row_flags, &A.lnP, &A.jbest, &A.parent})
+                      &A.uops, &A.ukids, &A.down, &A.leaf_rows, &A.states, &A.post, &A.row_flags, &A.lnP, &A.jbest, &A.parent, &A.nni_ops,
+                      &A.nni_kids, &A.nni_roots})
         b->release();
 }
 

@@ -374,7 +374,7 @@ struct Device {
 // 20-state (AminoAcid) engines of a PHB_FLAG_AMINO_ACID context: aa.cuh, aa_engine.cuh
 struct AaState {
     AaModelDev M;
-    DevBuf model, tips, mult, leaf_ls, per_pattern, Pmat, blen, clv, exps, cat_ll, partials, uops, ukids, down, leaf_rows, states, post, row_flags, lnP, jbest, parent;
+    DevBuf model, tips, mult, leaf_ls, per_pattern, Pmat, blen, clv, exps, cat_ll, partials, uops, ukids, down, leaf_rows, states, post, row_flags, lnP, jbest, parent, nni_ops, nni_kids, nni_roots;
     std::vector<AaDown> down_nodes;
     std::vector<int> down_off; // by depth, max_depth + 2 entries
     int64_t P_pad = 0;
@@ -2741,8 +2741,9 @@ int32_t phb_score_nni(phb_ctx *ctx, int32_t n_moves, const int32_t *node_id, con
     ctx->stats.nni_path_steps = 0;
     ctx->stats.nni_tiles = 0;
     ctx->stats.nni_cache_bytes = ctx->stats.nni_read_bytes = 0;
-    // Binary trees: walk v -> root against the cached CLVs of the base tree (nni.cuh).  20-state contexts take the
-    // full re-scoring below (aa_evaluate per neighbour).
+    // Binary trees: walk v -> root against the cached CLVs of the base tree (nni.cuh).  20-state contexts re-evaluate
+    // the path v -> root of every neighbour against the base tree's CLVs, any arity (aa_engine.cuh).
+    if (ctx->is_aa && !(ctx->flags & PHB_FLAG_NNI_FULL)) return aa_score_nni(ctx, n_moves, node_id, left_ch, totals);
     if (!ctx->is_aa && nni_path_eligible(ctx)) return score_nni_paths(ctx, n_moves, node_id, left_ch, totals);
     // Otherwise (polytomies / unifurcations, PHB_FLAG_NNI_FULL): each neighbour is re-scheduled and scored
     // from scratch, which is what the reference's caller loop does.

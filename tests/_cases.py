@@ -344,6 +344,8 @@ def check_random_trees_amino_acid(lib, seeds):
             if seed % 3 == 0:  # a few NNI neighbours of the random shape, each re-scored in full
                 n = c2.ft["n_nodes"]
                 moves = [(int(v), int(lc)) for v, lc in zip(rng.integers(n, size=6), rng.integers(2, size=6))]
-                check_nni(lib, c2, moves=moves, flags=capi.FLAG_AMINO_ACID, expect_path=False)
+                a, _ = check_nni(lib, c2, moves=moves, flags=capi.FLAG_AMINO_ACID)
+                b, _ = check_nni(lib, c2, moves=moves, flags=capi.FLAG_AMINO_ACID | capi.FLAG_NNI_FULL, expect_path=False)
+                assert np.array_equal(a, b, equal_nan=True), (a, b)
         except AssertionError as e:
             raise AssertionError(f"seed {seed}, model {model}, tree {nwk}: {e}") from e

@@ -142,12 +142,36 @@ def _star_and_polytomy(lib):
 
 
 def _rearrangements(lib):
-    """phb_score_nni / phb_score_trees in a 20-state context: every neighbour / candidate is re-scheduled and scored in
-    full (the reference's caller loop: clone, NNI::nni src/tree.rs:1213-1242 or SPR::spr src/tree/ops.rs:34-41,
-    log_likelihood), against the oracle on each rebuilt tree"""
+    """phb_score_nni / phb_score_trees in a 20-state context (the reference's caller loop: clone, NNI::nni
+    src/tree.rs:1213-1242 or SPR::spr src/tree/ops.rs:34-41, log_likelihood) against the oracle on each rebuilt tree.
+    NNI neighbours re-evaluate the path v -> root against the base tree's CLVs (aa_score_nni, any arity): the same values,
+    bit for bit, as re-scoring every rebuilt tree in full (PHB_FLAG_NNI_FULL), also when the patterns are tiled and when
+    the neighbours outnumber a batch."""
     case = workloads.make_case(9, 40, model="aa_i_g4", seed=17, ambiguity=0.1)
-    _, st = _cases.check_nni(lib, case, flags=AA, expect_path=False)
-    assert st["nni_path_moves"] == 0
+    got, st = _cases.check_nni(lib, case, flags=AA)
+    full, st_full = _cases.check_nni(lib, case, flags=AA | capi.FLAG_NNI_FULL, expect_path=False)
+    assert np.array_equal(got, full, equal_nan=True) and st["nni_path_steps"] > 0 and st_full["nni_path_moves"] == 0
+    # 3 tiles of 256 patterns (CLVs of 29 internal nodes + 2 x 58 scratch slots), every move listed ten times: 3 batches
+    case = workloads.make_case(30, 600, model="aa_g4", seed=18, ambiguity=0.05)
+    n = case.ft["n_nodes"]
+    moves = [(v, lc) for v in range(n) for lc in (0, 1)]
+    got, st = _cases.check_nni(lib, case, moves=moves, flags=AA, budget=(29 + 2 * 56) * 4 * 164 * 256)  # 56 valid moves
+    assert st["nni_tiles"] == 3
+    with capi.Context(flags=AA, library=lib) as ctx:
+        workloads.load_into(ctx, case)
+        many = ctx.score_nni([m[0] for m in moves] * 10, [m[1] for m in moves] * 10)
+        assert ctx.stats()["nni_path_moves"] == 10 * int(np.isfinite(got).sum()) > 256
+    assert np.array_equal(many, np.tile(got, 10), equal_nan=True)
+    # polytomies and unifurcations: the moved child / sibling is appended last, as set_child does
+    for nwk in _cases.NONBINARY_NEWICKS[:3]:
+        c4 = _cases.nonbinary_case(nwk, "gtr", n_sites=8)
+        rng = np.random.default_rng(len(nwk))
+        pats = np.frombuffer(workloads.AA_LETTERS + b"BZJX-", np.uint8)[rng.integers(25, size=(50, len(c4.leaf_order)))]
+        c20 = workloads.Case(c4.tree, c4.ft, workloads.make_aa_model("aa_g4"), "aa_g4", np.ascontiguousarray(pats), np.ones(50, np.uint64),
+                             c4.leaf_order)
+        a, _ = _cases.check_nni(lib, c20, flags=AA)
+        b, _ = _cases.check_nni(lib, c20, flags=AA | capi.FLAG_NNI_FULL, expect_path=False)
+        assert np.array_equal(a, b, equal_nan=True) and np.isfinite(a).sum() >= 4
     _cases.check_score_trees(lib, workloads.make_case(11, 30, model="aa_g4", seed=19, ambiguity=0.05), flags=AA)
 
 

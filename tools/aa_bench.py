@@ -21,6 +21,7 @@ def main():
     ap.add_argument("--taxa", type=int, default=1000)
     ap.add_argument("--patterns", type=int, default=20000)
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--moves", type=int, default=1024)
     args = ap.parse_args()
     from phylo_rs_b200 import capi, synthetic
 
@@ -64,6 +65,25 @@ def main():
             tot3, _jstates = ctx.joint_asr()
             best["joint"] = min(best.get("joint", 1e30), ctx.timer_stop())
         st = ctx.stats()
+        # NNI neighbourhood (config 5's shape at 20 states): 1,024 (node, left_ch) moves, each the re-evaluation of the path
+        # v -> root against the base tree's CLVs; a handful re-scored in full beside it (PHB_FLAG_NNI_FULL's loop)
+        co = tree["child_off"]
+        internal = [v for v in range(tree["n_nodes"]) if co[v + 1] > co[v] and v != tree["root"]]
+        moves = [(v, left) for v in internal for left in (0, 1)][:args.moves]
+        ids, left = [m[0] for m in moves], [m[1] for m in moves]
+        ctx.score_nni(ids, left)
+        for _ in range(args.reps):
+            ctx.timer_start()
+            nni = ctx.score_nni(ids, left)
+            best["nni"] = min(best.get("nni", 1e30), ctx.timer_stop())
+        st_nni = ctx.stats()
+    with capi.Context(flags=capi.FLAG_AMINO_ACID | capi.FLAG_NNI_FULL) as ctx:
+        ctx.set_alignment(pats)
+        ctx.set_model(lam, vec, pi, sp, isp, rates, np.full(K, 1.0 / K))
+        ctx.set_tree(tree["postorder"], tree["child_off"], tree["children"], tree["blen"], tree["leaf_row"], tree["root"])
+        ctx.timer_start()
+        nni_full = ctx.score_nni(ids[:8], left[:8])
+        full_ms = ctx.timer_stop() / 8
     n_int = args.taxa - 1
     updates = n_int * args.patterns
     # per update (internal node x pattern), K categories: internal children read 160 B each + 4 B exponent, the result
@@ -76,7 +96,10 @@ def main():
         "case": f"AminoAcid GTR20+G4 {args.taxa} x {args.patterns}", "lnl": tot, "asr_lnl": tot2,
         "lnl_ms": best["lnl"], "asr_ms": best["asr"], "joint_ms": best["joint"], "joint_value": tot3, "asr_wall_ms": wall, "tiles": st["n_tiles"],
         "updates_per_s": updates / (best["lnl"] * 1e-3), "algorithmic_GBps": bytes_lnl / (best["lnl"] * 1e-3) / 1e9,
-        "fp64_TFLOPs": flops_lnl / (best["lnl"] * 1e-3) / 1e12, "states_hist_head": np.bincount(states.ravel(), minlength=20)[:5].tolist()}))
+        "fp64_TFLOPs": flops_lnl / (best["lnl"] * 1e-3) / 1e12, "states_hist_head": np.bincount(states.ravel(), minlength=20)[:5].tolist(),
+        "nni_moves": len(moves), "nni_ms": best["nni"], "nni_trees_per_s": len(moves) / (best["nni"] * 1e-3), "nni_path_steps": st_nni["nni_path_steps"],
+        "nni_cache_GB": st_nni["nni_cache_bytes"] / 1e9, "nni_tiles": st_nni["nni_tiles"], "nni_full_ms_per_tree": full_ms,
+        "nni_equals_full_rescoring": bool(np.array_equal(nni[:8], nni_full)), "nni_best_delta": float(np.nanmax(nni) - tot)}))
 
 
 if __name__ == "__main__":
