@@ -408,27 +408,114 @@ aa_root_kernel(int root_slot, int root_row, const AaModelDev *__restrict__ M, co
     if (threadIdx.x == 0) partials[blockIdx.x] = red[0];
 }
 
-// ---- NNI neighbours (aa_engine.cuh aa_score_nni): the root of neighbour blockIdx.y lies in slot root_slots[blockIdx.y];
-// the same arithmetic as aa_root_kernel (the category values are formed twice instead of being parked in HBM), the
-// per-block sums of multiplicity * site_ll go to partials[neighbour][block].
+// ---- NNI neighbours (aa_engine.cuh aa_score_nni) --------------------------------------------------------------------
+// Upper partials.  up(x)[i] = the likelihood of everything OUTSIDE the subtree of x given state i at x:
+//     out[k]   = up(parent)[k] * prod over the siblings s of x of (P_s L_s)[k]        (up(root) = pi)
+//     up(x)[i] = sum_k out[k] P_x[k][i]
+// so that sum_i up(x)[i] L(x)[i] is the site likelihood for ANY x.  An op lists the parent's upper vector as a DIRECT
+// child (GenChild.pad == 1: multiplied in as it is, no P) and the siblings as ordinary children; GenOp.pad = x + 1 names
+// the edge of the closing transposed product.  grid: x = pattern blocks, y = op, z = category.  Stored like a CLV
+// (maximum in [1,2), exponent beside it).  One matrix staged at a time: the pass runs once per call.
+__global__ void __launch_bounds__(AA_THREADS, 3)
+aa_upper_kernel(const GenOp *__restrict__ ops, const GenChild *__restrict__ kids, int n_cat, const double *__restrict__ Pmat,
+                double *__restrict__ clv, int *__restrict__ exps, size_t slot_stride, size_t tile_pad, int tile_len,
+                const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off)
+{
+    __shared__ __align__(16) double Ps[AA_NS * AA_NS];
+    const GenOp op = ops[blockIdx.y];
+    const int cat = blockIdx.z;
+    int64_t site = (int64_t)blockIdx.x * AA_THREADS + threadIdx.x;
+    const bool active = site < tile_len;
+    if (!active) site = 0;
+    double acc[AA_NS];
+#pragma unroll
+    for (int i = 0; i < AA_NS; ++i) acc[i] = 1.0;
+    int ex = 0;
+    for (int k = op.child_begin; k < op.child_end; ++k) {
+        const GenChild ch = kids[k];
+        if (ch.pad == 1) { // the parent's upper vector
+            const double *x_src = clv + (size_t)ch.src * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
+            ex += exps[((size_t)ch.src * n_cat + cat) * tile_pad + site];
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) acc[i] *= x_src[(size_t)i * tile_pad];
+            continue;
+        }
+        __syncthreads(); // the previous matrix is no longer read
+        for (int e = threadIdx.x; e < AA_NS * AA_NS; e += AA_THREADS)
+            Ps[(e % AA_NS) * AA_NS + e / AA_NS] = Pmat[((size_t)ch.edge * n_cat + cat) * (AA_NS * AA_NS) + e]; // transposed
+        __syncthreads();
+        double y[AA_NS];
+        if (ch.is_tip) {
+            aa_tip_col(Ps, tips[(int64_t)ch.src * P_pad + tile_off + site], y);
+        } else {
+            const double *x_src = clv + (size_t)ch.src * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
+            ex += exps[((size_t)ch.src * n_cat + cat) * tile_pad + site];
+            const double x0 = x_src[0];
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) y[i] = Ps[i] * x0;
+#pragma unroll
+            for (int j = 1; j < AA_NS; ++j) {
+                const double xj = x_src[(size_t)j * tile_pad];
+#pragma unroll
+                for (int i = 0; i < AA_NS; ++i) y[i] += Ps[j * AA_NS + i] * xj;
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < AA_NS; ++i) acc[i] *= y[i];
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < AA_NS * AA_NS; e += AA_THREADS)
+        Ps[e] = Pmat[((size_t)(op.pad - 1) * n_cat + cat) * (AA_NS * AA_NS) + e]; // row k = P[k][.]
+    __syncthreads();
+    double up[AA_NS];
+#pragma unroll
+    for (int i = 0; i < AA_NS; ++i) up[i] = Ps[i] * acc[0];
+#pragma unroll
+    for (int k = 1; k < AA_NS; ++k) {
+#pragma unroll
+        for (int i = 0; i < AA_NS; ++i) up[i] += Ps[k * AA_NS + i] * acc[k];
+    }
+    if (active) {
+        ex += aa_normalize(up);
+        double *dst = clv + (size_t)op.out_slot * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
+#pragma unroll
+        for (int i = 0; i < AA_NS; ++i) dst[(size_t)i * tile_pad] = up[i];
+        exps[((size_t)op.out_slot * n_cat + cat) * tile_pad + site] = ex;
+    }
+}
+// up(root): pi for every pattern and category, exponent 0
+__global__ void aa_fill_pi_kernel(const AaModelDev *__restrict__ M, double *__restrict__ clv, int *__restrict__ exps, int slot,
+                                  size_t slot_stride, size_t tile_pad)
+{
+    const int n_cat = M->n_cat;
+    const size_t n = (size_t)n_cat * AA_NS * tile_pad;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        clv[(size_t)slot * slot_stride + i] = M->pi[(i / tile_pad) % AA_NS];
+        if (i < (size_t)n_cat * tile_pad) exps[(size_t)slot * n_cat * tile_pad + i] = 0;
+    }
+}
+// The value of neighbour blockIdx.y: sum_i up[i] L[i] with L in slot low_slots[y] and up in slot up_slots[y] (the pi slot
+// when the re-linked parent is the root: then this is aa_root_kernel's arithmetic, bit for bit); the category values are
+// formed twice instead of being parked in HBM; per-block sums of multiplicity * site_ll go to partials[neighbour][block].
 __global__ void __launch_bounds__(AA_THREADS)
-aa_nni_root_kernel(const int *__restrict__ root_slots, const AaModelDev *__restrict__ M, const double *__restrict__ clv,
-                   const int *__restrict__ exps, size_t slot_stride, size_t tile_pad, int tile_len, int64_t tile_off,
-                   const double *__restrict__ leaf_ls, const double *__restrict__ mult, double *__restrict__ partials)
+aa_nni_root_kernel(const int *__restrict__ low_slots, const int *__restrict__ up_slots, const AaModelDev *__restrict__ M,
+                   const double *__restrict__ clv, const int *__restrict__ exps, size_t slot_stride, size_t tile_pad, int tile_len,
+                   int64_t tile_off, const double *__restrict__ leaf_ls, const double *__restrict__ mult, double *__restrict__ partials)
 {
     __shared__ double red[AA_THREADS];
     const int64_t site = (int64_t)blockIdx.x * AA_THREADS + threadIdx.x;
     const int n_cat = M->n_cat;
-    const int root_slot = root_slots[blockIdx.y];
+    const int low = low_slots[blockIdx.y], upper = up_slots[blockIdx.y];
     double weighted = 0.0;
     if (site < tile_len) {
         auto cat_value = [&](int c) {
-            double x[AA_NS];
-            aa_load_vec(clv, slot_stride, tile_pad, root_slot, c, site, x);
-            const int ex = exps[((size_t)root_slot * n_cat + c) * tile_pad + site];
-            double mass = M->pi[0] * x[0];
+            double x[AA_NS], u[AA_NS];
+            aa_load_vec(clv, slot_stride, tile_pad, low, c, site, x);
+            aa_load_vec(clv, slot_stride, tile_pad, upper, c, site, u);
+            const int ex = exps[((size_t)low * n_cat + c) * tile_pad + site] + exps[((size_t)upper * n_cat + c) * tile_pad + site];
+            double mass = u[0] * x[0];
 #pragma unroll
-            for (int i = 1; i < AA_NS; ++i) mass += M->pi[i] * x[i];
+            for (int i = 1; i < AA_NS; ++i) mass += u[i] * x[i];
             return M->ln_weights[c] + log(mass) + (double)ex * 0.69314718055994530942;
         };
         double mx = -INFINITY;

@@ -321,13 +321,16 @@ int aa_evaluate(phb_ctx *ctx, bool asr, uint8_t *states_out, double *post_out, d
     return PHB_OK;
 }
 
-// phb_score_nni at 20 states (caller loop: clone, NNI::nni src/tree.rs:1213-1242, log_likelihood).  An NNI at v changes the
-// partials of v, of its parent and of their ancestors only, and no branch length: with the base tree's CLVs of a pattern tile
-// resident, a neighbour costs depth(v) + 1 node updates instead of a whole sweep.  The updates of a BATCH of neighbours run
-// side by side -- step j of every neighbour's path in one aa_clv_kernel launch (any arity, the child lists in the order
-// the re-linked tree has them: the moved child / sibling appended last) -- into two scratch slots per neighbour used in
-// turn; aa_nni_root_kernel then reads each neighbour's root.  Same kernels, same child order, same P(t): the totals are
-// those of a full re-scoring of the rebuilt tree (PHB_FLAG_NNI_FULL), bit for bit.
+// phb_score_nni at 20 states (caller loop: clone, NNI::nni src/tree.rs:1213-1242, log_likelihood).  An NNI at v re-links
+// v and its parent p and changes no branch length.  With the base tree's CLVs of a pattern tile resident and the UPPER
+// partial of every parent (aa_upper_kernel: one pre-order pass), a neighbour costs two node updates -- v without the
+// moved child but with its former sibling, p without that sibling but with the moved child -- and one dot product of
+// the new p with up(p).  The updates of a BATCH of neighbours run side by side through aa_clv_kernel (any arity, the
+// child lists in the order the re-linked tree has them: the moved child / sibling appended last) into two scratch slots
+// per neighbour; aa_nni_root_kernel forms each neighbour's value.
+// PHB_AA_NNI_PATH=1 (cross-check): no upper partials, every neighbour re-evaluates its whole path v -> root instead --
+// the same kernels on the same operands in the same order as a full re-scoring of the rebuilt tree (PHB_FLAG_NNI_FULL),
+// bit-identical to it.
 constexpr int AA_NNI_BATCH = 256;
 int aa_score_nni(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uint8_t *left_ch, double *totals)
 {
@@ -341,6 +344,8 @@ int aa_score_nni(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uint8_
     const int64_t P = ctx->n_patterns;
     const int K = A.M.n_cat;
     const int n_int = std::max(T.n_internal, 1);
+    const char *path_env = getenv("PHB_AA_NNI_PATH");
+    const bool use_upper = !(path_env && path_env[0] == '1');
     auto base_child = [&](int c) {
         GenChild g;
         g.is_tip = T.slot[c] < 0;
@@ -349,7 +354,7 @@ int aa_score_nni(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uint8_
         g.pad = 0;
         return g;
     };
-    // ---- the valid moves and, batch by batch, their ops grouped by step
+    // ---- the valid moves
     std::vector<int> valid;
     for (int m = 0; m < n_moves; ++m) {
         totals[m] = NAN;
@@ -366,22 +371,61 @@ int aa_score_nni(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uint8_
         return PHB_OK;
     }
     const int B = (int)std::min<size_t>(valid.size(), AA_NNI_BATCH);
+    // slots: [0, n_int) the base tree's CLVs | pi | the upper partials by the node's slot | two per neighbour of a batch
+    const int pi_slot = n_int, upper_base = n_int + 1, scratch_base = upper_base + (use_upper ? n_int : 0);
+    const int n_slots = scratch_base + 2 * B;
+    // ---- upper ops by depth, for the parents the moves name and their ancestors
+    std::vector<GenOp> ops;
+    std::vector<GenChild> kids;
+    std::vector<int> upper_off(1, 0);
+    if (use_upper) {
+        std::vector<char> need(T.n, 0);
+        for (int m : valid)
+            for (int a = T.parent[node_id[m]]; a != T.root && !need[a]; a = T.parent[a]) need[a] = 1;
+        std::vector<std::vector<int>> by_depth(T.max_depth + 1);
+        for (int x = 0; x < T.n; ++x)
+            if (need[x]) by_depth[T.depth[x]].push_back(x);
+        for (int dep = 1; dep <= T.max_depth; ++dep) {
+            for (int x : by_depth[dep]) {
+                const int g = T.parent[x];
+                GenOp op;
+                op.out_slot = upper_base + T.slot[x];
+                op.child_begin = (int)kids.size();
+                op.pad = x + 1;
+                GenChild up;
+                up.src = g == T.root ? pi_slot : upper_base + T.slot[g];
+                up.edge = 0;
+                up.is_tip = 0;
+                up.pad = 1;
+                kids.push_back(up);
+                for (int k = T.child_off[g]; k < T.child_off[g + 1]; ++k)
+                    if (T.children[k] != x) kids.push_back(base_child(T.children[k]));
+                op.child_end = (int)kids.size();
+                ops.push_back(op);
+            }
+            if ((int)ops.size() > upper_off.back()) upper_off.push_back((int)ops.size());
+        }
+    }
+    // ---- batch by batch, the neighbours' ops grouped by step
     struct Batch {
         int first, count;           // range in `valid`
         std::vector<int> step_off;  // ops of step j: [step_off[j], step_off[j+1]) (absolute op indices)
     };
     std::vector<Batch> batches;
-    std::vector<GenOp> ops;
-    std::vector<GenChild> kids;
-    std::vector<int> root_slots(valid.size());
+    std::vector<int> low_slots(valid.size()), up_slots(valid.size());
+    const size_t n_upper_ops = ops.size();
     for (int b0 = 0; b0 < (int)valid.size(); b0 += B) {
         Batch bt;
         bt.first = b0;
         bt.count = std::min(B, (int)valid.size() - b0);
         int max_len = 0;
-        std::vector<std::vector<int>> path(bt.count); // v, its parent, ..., the root
+        std::vector<std::vector<int>> path(bt.count); // v, its parent (, ..., the root)
         for (int i = 0; i < bt.count; ++i) {
-            for (int a = node_id[valid[b0 + i]]; a >= 0; a = a == T.root ? -1 : T.parent[a]) path[i].push_back(a);
+            const int v = node_id[valid[b0 + i]];
+            if (use_upper)
+                path[i] = {v, T.parent[v]};
+            else
+                for (int a = v; a >= 0; a = a == T.root ? -1 : T.parent[a]) path[i].push_back(a);
             max_len = std::max(max_len, (int)path[i].size());
         }
         for (int j = 0; j < max_len; ++j) {
@@ -395,7 +439,7 @@ int aa_score_nni(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uint8_
                 int sib = -1;
                 for (int k = T.child_off[p]; k < T.child_off[p + 1] && sib < 0; ++k)
                     if (T.children[k] != v) sib = T.children[k];
-                const int scratch[2] = {n_int + 2 * i, n_int + 2 * i + 1};
+                const int scratch[2] = {scratch_base + 2 * i, scratch_base + 2 * i + 1};
                 GenOp op;
                 op.out_slot = scratch[j & 1];
                 op.child_begin = (int)kids.size();
@@ -420,15 +464,17 @@ int aa_score_nni(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uint8_
                 }
                 op.child_end = (int)kids.size();
                 ops.push_back(op);
-                if (j + 1 == (int)path[i].size()) root_slots[b0 + i] = op.out_slot;
+                if (j + 1 == (int)path[i].size()) {
+                    low_slots[b0 + i] = op.out_slot;
+                    up_slots[b0 + i] = (use_upper && p != T.root) ? upper_base + T.slot[p] : pi_slot;
+                }
             }
         }
         bt.step_off.push_back((int)ops.size());
         batches.push_back(std::move(bt));
     }
-    ctx->stats.nni_path_steps = (int64_t)ops.size();
+    ctx->stats.nni_path_steps = (int64_t)(ops.size() - n_upper_ops);
     // ---- buffers: the base tree's CLVs of a pattern tile + two scratch slots per neighbour of a batch
-    const int n_slots = n_int + 2 * B;
     size_t free_b = 0, total_b = 0;
     CU(cudaMemGetInfo(&free_b, &total_b));
     size_t budget = ctx->clv_budget ? (size_t)ctx->clv_budget : (free_b + A.clv.cap + A.exps.cap) / 10 * 7;
@@ -444,10 +490,11 @@ int aa_score_nni(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uint8_
     CU(A.partials.ensure(sizeof(double) * (size_t)max_blocks * B));
     CU(A.nni_ops.ensure(sizeof(GenOp) * ops.size()));
     CU(A.nni_kids.ensure(sizeof(GenChild) * kids.size()));
-    CU(A.nni_roots.ensure(sizeof(int) * root_slots.size()));
+    CU(A.nni_roots.ensure(sizeof(int) * 2 * valid.size()));
     CU(cudaMemcpyAsync(A.nni_ops.p, ops.data(), sizeof(GenOp) * ops.size(), cudaMemcpyHostToDevice, d.stream));
     CU(cudaMemcpyAsync(A.nni_kids.p, kids.data(), sizeof(GenChild) * kids.size(), cudaMemcpyHostToDevice, d.stream));
-    CU(cudaMemcpyAsync(A.nni_roots.p, root_slots.data(), sizeof(int) * root_slots.size(), cudaMemcpyHostToDevice, d.stream));
+    CU(cudaMemcpyAsync(A.nni_roots.p, low_slots.data(), sizeof(int) * valid.size(), cudaMemcpyHostToDevice, d.stream));
+    CU(cudaMemcpyAsync(A.nni_roots.as<int>() + valid.size(), up_slots.data(), sizeof(int) * valid.size(), cudaMemcpyHostToDevice, d.stream));
     const AaModelDev *Md = A.model.as<AaModelDev>();
     PHB_LAUNCH(aa_transition_kernel, dim3((unsigned)(T.n * K)), dim3(AA_THREADS), d.stream, A.blen.as<double>(), T.n, Md, A.Pmat.as<double>());
     CHECK_LAUNCH();
@@ -475,11 +522,22 @@ int aa_score_nni(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uint8_
             for (int o = 0; o < n_ops; o += 65535)
                 if ((rc = clv_launch(A.uops.as<GenOp>() + b + o, A.ukids.as<GenChild>(), std::min(65535, n_ops - o)))) return rc;
         }
+        PHB_LAUNCH(aa_fill_pi_kernel, dim3((unsigned)std::min<size_t>(((size_t)K * AA_NS * tile_pad + 255) / 256, 2048)), dim3(256), d.stream, Md,
+                   A.clv.as<double>(), A.exps.as<int>(), pi_slot, slot_stride, (size_t)tile_pad);
+        CHECK_LAUNCH();
+        for (size_t l = 0; l + 1 < upper_off.size(); ++l) // the upper partials, parents before children
+            for (int o = upper_off[l]; o < upper_off[l + 1]; o += 65535) {
+                PHB_LAUNCH(aa_upper_kernel, dim3(bx, (unsigned)std::min(65535, upper_off[l + 1] - o), (unsigned)K), dim3(AA_THREADS), d.stream,
+                           A.nni_ops.as<GenOp>() + o, A.nni_kids.as<GenChild>(), K, A.Pmat.as<double>(), A.clv.as<double>(), A.exps.as<int>(),
+                           slot_stride, (size_t)tile_pad, tile_len, A.tips.as<uint8_t>(), A.P_pad, off);
+                CHECK_LAUNCH();
+            }
         for (const Batch &bt : batches) {
             for (size_t j = 0; j + 1 < bt.step_off.size(); ++j)
                 if ((rc = clv_launch(A.nni_ops.as<GenOp>() + bt.step_off[j], A.nni_kids.as<GenChild>(), bt.step_off[j + 1] - bt.step_off[j])))
                     return rc;
-            PHB_LAUNCH(aa_nni_root_kernel, dim3(bx, (unsigned)bt.count), dim3(AA_THREADS), d.stream, A.nni_roots.as<int>() + bt.first, Md,
+            PHB_LAUNCH(aa_nni_root_kernel, dim3(bx, (unsigned)bt.count), dim3(AA_THREADS), d.stream, A.nni_roots.as<int>() + bt.first,
+                       A.nni_roots.as<int>() + valid.size() + bt.first, Md,
                        A.clv.as<double>(), A.exps.as<int>(), slot_stride, (size_t)tile_pad, tile_len, off, A.leaf_ls.as<double>(),
                        A.mult.as<double>(), A.partials.as<double>());
             CHECK_LAUNCH();

@@ -344,8 +344,18 @@ def check_random_trees_amino_acid(lib, seeds):
             if seed % 3 == 0:  # a few NNI neighbours of the random shape, each re-scored in full
                 n = c2.ft["n_nodes"]
                 moves = [(int(v), int(lc)) for v, lc in zip(rng.integers(n, size=6), rng.integers(2, size=6))]
+                import os
+
                 a, _ = check_nni(lib, c2, moves=moves, flags=capi.FLAG_AMINO_ACID)
+                os.environ["PHB_AA_NNI_PATH"] = "1"  # without upper partials: bit-identical to full re-scoring
+                try:
+                    w, _ = check_nni(lib, c2, moves=moves, flags=capi.FLAG_AMINO_ACID)
+                finally:
+                    del os.environ["PHB_AA_NNI_PATH"]
                 b, _ = check_nni(lib, c2, moves=moves, flags=capi.FLAG_AMINO_ACID | capi.FLAG_NNI_FULL, expect_path=False)
-                assert np.array_equal(a, b, equal_nan=True), (a, b)
+                assert np.array_equal(w, b, equal_nan=True), (w, b)
+                fin = np.isfinite(b)
+                assert np.array_equal(np.isnan(a), np.isnan(b)) and np.allclose(a[fin], b[fin], rtol=1e-11, atol=0), (a, b)
+                assert np.array_equal(a[~fin], b[~fin], equal_nan=True)
         except AssertionError as e:
             raise AssertionError(f"seed {seed}, model {model}, tree {nwk}: {e}") from e

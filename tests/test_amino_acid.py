@@ -5,6 +5,8 @@ the reference's own AminoAcid fixtures (src/tree/likelihood/integration_test.rs:
 enumeration and on an independent numpy pruning + scipy expm; the product sources run on the emulation build.
 GPU part (`-m gpu`): the real sm_100a library through its C ABI against that oracle, at BASELINE.json's bars
 (total lnL 1e-9 relative, per-pattern 1e-8 absolute, ASR states bit-exact, posteriors 1e-9)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -141,21 +143,34 @@ def _star_and_polytomy(lib):
     _cases.check_joint(lib, case, flags=AA)
 
 
+class _path_mode:
+    """PHB_AA_NNI_PATH=1: aa_score_nni without upper partials (every neighbour re-evaluates its whole path v -> root)"""
+
+    def __enter__(self):
+        os.environ["PHB_AA_NNI_PATH"] = "1"
+
+    def __exit__(self, *exc):
+        del os.environ["PHB_AA_NNI_PATH"]
+
+
 def _rearrangements(lib):
     """phb_score_nni / phb_score_trees in a 20-state context (the reference's caller loop: clone, NNI::nni
     src/tree.rs:1213-1242 or SPR::spr src/tree/ops.rs:34-41, log_likelihood) against the oracle on each rebuilt tree.
-    NNI neighbours re-evaluate the path v -> root against the base tree's CLVs (aa_score_nni, any arity): the same values,
-    bit for bit, as re-scoring every rebuilt tree in full (PHB_FLAG_NNI_FULL), also when the patterns are tiled and when
-    the neighbours outnumber a batch."""
+    NNI neighbours are scored against the base tree's resident CLVs and upper partials (aa_score_nni, any arity); its
+    cross-check mode without upper partials gives the same values, bit for bit, as re-scoring every rebuilt tree in full
+    (PHB_FLAG_NNI_FULL).  Also with tiled patterns and more neighbours than a batch holds."""
     case = workloads.make_case(9, 40, model="aa_i_g4", seed=17, ambiguity=0.1)
     got, st = _cases.check_nni(lib, case, flags=AA)
+    with _path_mode():
+        walked, st_w = _cases.check_nni(lib, case, flags=AA)
     full, st_full = _cases.check_nni(lib, case, flags=AA | capi.FLAG_NNI_FULL, expect_path=False)
-    assert np.array_equal(got, full, equal_nan=True) and st["nni_path_steps"] > 0 and st_full["nni_path_moves"] == 0
-    # 3 tiles of 256 patterns (CLVs of 29 internal nodes + 2 x 58 scratch slots), every move listed ten times: 3 batches
+    assert np.array_equal(walked, full, equal_nan=True) and st_full["nni_path_moves"] == 0
+    assert np.allclose(got, full, rtol=1e-12, atol=0, equal_nan=True) and 0 < st["nni_path_steps"] < st_w["nni_path_steps"]
+    # 3 tiles of 256 patterns (29 CLVs + pi + 29 upper partials + 2 x 56 scratch slots), every move ten times: 3 batches
     case = workloads.make_case(30, 600, model="aa_g4", seed=18, ambiguity=0.05)
     n = case.ft["n_nodes"]
     moves = [(v, lc) for v in range(n) for lc in (0, 1)]
-    got, st = _cases.check_nni(lib, case, moves=moves, flags=AA, budget=(29 + 2 * 56) * 4 * 164 * 256)  # 56 valid moves
+    got, st = _cases.check_nni(lib, case, moves=moves, flags=AA, budget=(59 + 2 * 56) * 4 * 164 * 256)  # 56 valid moves
     assert st["nni_tiles"] == 3
     with capi.Context(flags=AA, library=lib) as ctx:
         workloads.load_into(ctx, case)
@@ -170,8 +185,11 @@ def _rearrangements(lib):
         c20 = workloads.Case(c4.tree, c4.ft, workloads.make_aa_model("aa_g4"), "aa_g4", np.ascontiguousarray(pats), np.ones(50, np.uint64),
                              c4.leaf_order)
         a, _ = _cases.check_nni(lib, c20, flags=AA)
+        with _path_mode():
+            w, _ = _cases.check_nni(lib, c20, flags=AA)
         b, _ = _cases.check_nni(lib, c20, flags=AA | capi.FLAG_NNI_FULL, expect_path=False)
-        assert np.array_equal(a, b, equal_nan=True) and np.isfinite(a).sum() >= 4
+        assert np.array_equal(w, b, equal_nan=True) and np.isfinite(a).sum() >= 4
+        assert np.allclose(a, b, rtol=1e-12, atol=0, equal_nan=True)
     _cases.check_score_trees(lib, workloads.make_case(11, 30, model="aa_g4", seed=19, ambiguity=0.05), flags=AA)
 
 

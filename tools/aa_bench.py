@@ -77,6 +77,11 @@ def main():
             nni = ctx.score_nni(ids, left)
             best["nni"] = min(best.get("nni", 1e30), ctx.timer_stop())
         st_nni = ctx.stats()
+        os.environ["PHB_AA_NNI_PATH"] = "1"  # cross-check mode: whole paths v -> root, no upper partials
+        ctx.timer_start()
+        nni_walk = ctx.score_nni(ids, left)
+        walk_ms = ctx.timer_stop()
+        del os.environ["PHB_AA_NNI_PATH"]
     with capi.Context(flags=capi.FLAG_AMINO_ACID | capi.FLAG_NNI_FULL) as ctx:
         ctx.set_alignment(pats)
         ctx.set_model(lam, vec, pi, sp, isp, rates, np.full(K, 1.0 / K))
@@ -99,7 +104,8 @@ def main():
         "fp64_TFLOPs": flops_lnl / (best["lnl"] * 1e-3) / 1e12, "states_hist_head": np.bincount(states.ravel(), minlength=20)[:5].tolist(),
         "nni_moves": len(moves), "nni_ms": best["nni"], "nni_trees_per_s": len(moves) / (best["nni"] * 1e-3), "nni_path_steps": st_nni["nni_path_steps"],
         "nni_cache_GB": st_nni["nni_cache_bytes"] / 1e9, "nni_tiles": st_nni["nni_tiles"], "nni_full_ms_per_tree": full_ms,
-        "nni_equals_full_rescoring": bool(np.array_equal(nni[:8], nni_full)), "nni_best_delta": float(np.nanmax(nni) - tot)}))
+        "nni_path_mode_ms": walk_ms, "nni_path_mode_equals_full_rescoring": bool(np.array_equal(nni_walk[:8], nni_full)),
+        "nni_max_rel_diff_to_path_mode": float(np.nanmax(np.abs(nni - nni_walk) / np.abs(nni_walk))), "nni_best_delta": float(np.nanmax(nni) - tot)}))
 
 
 if __name__ == "__main__":
