@@ -75,8 +75,8 @@ extern "C" {
  *                            the alphabet, as Alignment::compress_columns does not); the unique columns are encoded to
  *                            20-state tip codes on the device;
  *   phb_get_alignment        the 25 accepted bytes read back as themselves, any other byte as '?';
- *   phb_score_nni            every neighbour re-evaluates the path node -> root against the base tree's resident
- *                            partials (any arity); the totals equal a full re-scoring of the rebuilt tree bit for bit;
+ *   phb_score_nni            every neighbour is two node updates and a dot product against the base tree's resident
+ *                            partials and upper partials (any arity);
  *   phb_score_trees          every candidate is re-scheduled and scored in full against the resident alignment;
  * rate-0 categories are evaluated literally (identity P).  One device per context.  Every other entry point returns
  * PHB_ERR_STATE. */
