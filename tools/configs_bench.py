@@ -414,14 +414,32 @@ def driver_configs(hbm_gbs, reps=3, which=("cfg2", "cfg4", "joint", "cfg5", "com
             _, dev_ms, wall_ms = timed(ctx, ctx.log_likelihood, reps)
             tot, per = ctx.log_likelihood(per_pattern=True)
             (_t, states, _p), asr_ms, _w = timed(ctx, ctx.marginal_asr, max(1, reps - 1))
+            # 1,024 NNI neighbours at 20 states (two node updates + a dot product each against resident CLVs / upper partials)
+            co = ft["child_off"]
+            internal = [v for v in range(ft["n_nodes"]) if co[v + 1] > co[v] and v != ft["root"]]
+            moves = [(v, lc) for v in internal for lc in (0, 1)][:1024]
+            ids, left = [x[0] for x in moves], [x[1] for x in moves]
+            _nn, nni_ms, _w2 = timed(ctx, lambda: ctx.score_nni(ids, left), max(1, reps - 1))
+            # ... and eight of them on the 32 sample patterns against the oracle on each rebuilt tree
+            ctx.set_alignment(case.patterns)
+            sample = moves[::128]
+            got_nni = ctx.score_nni([x[0] for x in sample], [x[1] for x in sample])
+        nni_rel = 0.0
+        for (v, lc), val in zip(sample, got_nni):
+            t = case.tree.clone()
+            assert not t.nni(int(ft["ids"][v]), bool(lc))
+            ref, _ = oracle.log_likelihood_flat(workloads.flatten_fast(t, case.leaf_order), m, case.patterns, mode=2, n_threads=8)
+            nni_rel = max(nni_rel, abs(val - ref) / abs(ref))
         _rt, ref_per, ref_states, _rp = oracle.marginal_asr_flat(ft, m, case.patterns, n_threads=8)
         K = len(m.rates)
         flops = P * K * (820.0 * (n - 2) + 20.0 * n)
-        return dict(workload="AminoAcid GTR20+G4 log-likelihood and marginal ASR, 1000 taxa x 20k patterns", device_ms=dev_ms,
+        return dict(workload="AminoAcid GTR20+G4 log-likelihood, marginal ASR and 1,024 NNI neighbours, 1000 taxa x 20k patterns", device_ms=dev_ms,
                     wall_ms=wall_ms, asr_device_ms=asr_ms, updates_per_s=(n - 1) * P / (dev_ms * 1e-3),
                     fp64_tflops=flops / (dev_ms * 1e-3) / 1e12, frac_of_hbm=P * K * 164.0 * (2 * n - 3) / (dev_ms * 1e-3) / 1e9 / hbm_gbs,
+                    nni_1024_device_ms=nni_ms, nni_trees_per_s=len(moves) / (nni_ms * 1e-3),
                     parity=dict(sample_patterns=32, max_abs_per_pattern_lnl=float(np.max(np.abs(per[:32] - ref_per))),
-                                asr_state_mismatches=int((states[:, :32] != ref_states).sum())))
+                                asr_state_mismatches=int((states[:, :32] != ref_states).sum()), nni_neighbours_checked=len(sample),
+                                nni_max_rel_total=float(nni_rel)))
 
     guard("cfg2", cfg2)
     guard("amino_acid", amino_acid)
