@@ -495,8 +495,8 @@ __global__ void aa_fill_pi_kernel(const AaModelDev *__restrict__ M, double *__re
     }
 }
 // The value of neighbour blockIdx.y: sum_i up[i] L[i] with L in slot low_slots[y] and up in slot up_slots[y] (the pi slot
-// when the re-linked parent is the root: then this is aa_root_kernel's arithmetic, bit for bit); the category values are
-// formed twice instead of being parked in HBM; per-block sums of multiplicity * site_ll go to partials[neighbour][block].
+// when the re-linked parent is the root: then this is aa_root_kernel's arithmetic, bit for bit); the category values stay
+// in registers instead of being parked in HBM; per-block sums of multiplicity * site_ll go to partials[neighbour][block].
 __global__ void __launch_bounds__(AA_THREADS)
 aa_nni_root_kernel(const int *__restrict__ low_slots, const int *__restrict__ up_slots, const AaModelDev *__restrict__ M,
                    const double *__restrict__ clv, const int *__restrict__ exps, size_t slot_stride, size_t tile_pad, int tile_len,
@@ -518,12 +518,21 @@ aa_nni_root_kernel(const int *__restrict__ low_slots, const int *__restrict__ up
             for (int i = 1; i < AA_NS; ++i) mass += u[i] * x[i];
             return M->ln_weights[c] + log(mass) + (double)ex * 0.69314718055994530942;
         };
+        constexpr int KEEP = 8; // category values kept in registers; beyond that they are formed a second time
+        double kept[KEEP];
         double mx = -INFINITY;
-        for (int c = 0; c < n_cat; ++c) mx = fmax(mx, cat_value(c));
+        for (int c = 0; c < n_cat; ++c) {
+            const double ll = cat_value(c);
+            if (c < KEEP) kept[c] = ll;
+            mx = fmax(mx, ll);
+        }
         double lse = mx;
         if (isfinite(mx)) {
             double sum = 0.0;
-            for (int c = 0; c < n_cat; ++c) sum += exp(cat_value(c) - mx);
+#pragma unroll
+            for (int c = 0; c < KEEP; ++c)
+                if (c < n_cat) sum += exp(kept[c] - mx);
+            for (int c = KEEP; c < n_cat; ++c) sum += exp(cat_value(c) - mx);
             lse = mx + log(sum);
         }
         weighted = mult[tile_off + site] * (lse + leaf_ls[tile_off + site]);
