@@ -268,12 +268,19 @@ constexpr int AA_DCATS = 8;  // categories whose P(t) the pre-order kernel stage
 // and child batch.  (Measured at 1,000 x 20k: 9.8 -> 9.0 ms against one category per block.  Staging the children's CLV
 // tiles in shared memory with TMA bulk copies, double-buffered over the categories, was tried and was slower -- 10.7 ms:
 // at 107 KB of shared memory only two blocks fit an SM, and the resident blocks are what hides the HBM latency here.)
+// DOT = true (aa_score_nni, the re-linked parent p' of an NNI neighbour; needs n_cat <= AA_CSTAGE, grid.z == 1): the node's
+// vector is not stored but multiplied with the upper partial in slot op.pad - 1 straight away -- sum_i up[i] L[i], the
+// category values, their log_sum_exp and the block's sum of multiplicity * site_ll into partials[blockIdx.y][blockIdx.x]:
+// aa_nni_root_kernel's arithmetic on the values this kernel would have written, without the 12.8 MB round trip.
+template <bool DOT>
 __global__ void __launch_bounds__(AA_THREADS, PHB_AA_MINB)
 aa_clv_kernel(const GenOp *__restrict__ ops, const GenChild *__restrict__ kids, int n_cat, const double *__restrict__ Pmat,
               double *__restrict__ clv, int *__restrict__ exps, size_t slot_stride, size_t tile_pad, int tile_len,
-              const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off)
+              const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off, const AaModelDev *__restrict__ M,
+              const double *__restrict__ leaf_ls, const double *__restrict__ mult, double *__restrict__ partials)
 {
     __shared__ __align__(16) double Pt[AA_CSTAGE * AA_STAGE][AA_NS * AA_NS];
+    double kept[DOT ? AA_CSTAGE : 1]; // the category values of this thread's pattern (DOT)
     const GenOp op = ops[blockIdx.y];
     const int cat0 = blockIdx.z * AA_CSTAGE;
     const int ncat = min(AA_CSTAGE, n_cat - cat0);
@@ -331,13 +338,48 @@ aa_clv_kernel(const GenOp *__restrict__ ops, const GenChild *__restrict__ kids, 
                 for (int i = 0; i < AA_NS; ++i) acc[i] *= y[i];
             }
         }
-        if (active) {
+        if (DOT) {
+            ex += aa_normalize(acc);
+            const int up = op.pad - 1;
+            const double *u = clv + (size_t)up * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
+            ex += exps[((size_t)up * n_cat + cat) * tile_pad + site];
+            double mass = u[0] * acc[0];
+#pragma unroll
+            for (int i = 1; i < AA_NS; ++i) mass += u[(size_t)i * tile_pad] * acc[i];
+            kept[c] = M->ln_weights[cat] + log(mass) + (double)ex * 0.69314718055994530942;
+        } else if (active) {
             ex += aa_normalize(acc);
             double *dst = clv + (size_t)op.out_slot * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
 #pragma unroll
             for (int i = 0; i < AA_NS; ++i) dst[(size_t)i * tile_pad] = acc[i];
             exps[((size_t)op.out_slot * n_cat + cat) * tile_pad + site] = ex;
         }
+    }
+    if (DOT) {
+        __shared__ double red[AA_THREADS];
+        double weighted = 0.0;
+        if (active) {
+            double mx = -INFINITY;
+#pragma unroll
+            for (int c = 0; c < AA_CSTAGE; ++c)
+                if (c < ncat) mx = fmax(mx, kept[c]);
+            double lse = mx;
+            if (isfinite(mx)) {
+                double sum = 0.0;
+#pragma unroll
+                for (int c = 0; c < AA_CSTAGE; ++c)
+                    if (c < ncat) sum += exp(kept[c] - mx);
+                lse = mx + log(sum);
+            }
+            weighted = mult[tile_off + site] * (lse + leaf_ls[tile_off + site]);
+        }
+        red[threadIdx.x] = weighted;
+        __syncthreads();
+        for (int s = AA_THREADS / 2; s > 0; s >>= 1) {
+            if ((int)threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s];
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) partials[(size_t)blockIdx.y * gridDim.x + blockIdx.x] = red[0];
     }
 }
 

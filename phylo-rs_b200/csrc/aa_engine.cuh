@@ -264,9 +264,10 @@ int aa_evaluate(phb_ctx *ctx, bool asr, uint8_t *states_out, double *post_out, d
             const int b = T.ulevel_off[l - 1], n_ops = T.ulevel_off[l] - b;
             for (int o = 0; o < n_ops; o += 65535) { // grid.y limit
                 const int cnt = std::min(65535, n_ops - o);
-                PHB_LAUNCH(aa_clv_kernel, dim3(bx, (unsigned)cnt, (unsigned)((K + AA_CSTAGE - 1) / AA_CSTAGE)), dim3(AA_THREADS), d.stream, A.uops.as<GenOp>() + b + o,
+                PHB_LAUNCH(aa_clv_kernel<false>, dim3(bx, (unsigned)cnt, (unsigned)((K + AA_CSTAGE - 1) / AA_CSTAGE)), dim3(AA_THREADS), d.stream, A.uops.as<GenOp>() + b + o,
                            A.ukids.as<GenChild>(), K, A.Pmat.as<double>(), A.clv.as<double>(), A.exps.as<int>(), slot_stride,
-                           (size_t)tile_pad, tile_len, A.tips.as<uint8_t>(), A.P_pad, off);
+                           (size_t)tile_pad, tile_len, A.tips.as<uint8_t>(), A.P_pad, off, (const AaModelDev *)nullptr, (const double *)nullptr,
+                           (const double *)nullptr, (double *)nullptr);
                 CHECK_LAUNCH();
             }
         }
@@ -467,6 +468,7 @@ int aa_score_nni(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uint8_
                 if (j + 1 == (int)path[i].size()) {
                     low_slots[b0 + i] = op.out_slot;
                     up_slots[b0 + i] = (use_upper && p != T.root) ? upper_base + T.slot[p] : pi_slot;
+                    ops.back().pad = up_slots[b0 + i] + 1; // read by aa_clv_kernel<true>
                 }
             }
         }
@@ -511,9 +513,15 @@ int aa_score_nni(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uint8_
     for (int64_t off = 0; off < P; off += tile_pad) {
         const int tile_len = (int)std::min<int64_t>(tile_pad, P - off);
         const unsigned bx = (unsigned)((tile_len + AA_THREADS - 1) / AA_THREADS);
-        auto clv_launch = [&](const GenOp *o, const GenChild *k, int cnt) -> int {
-            PHB_LAUNCH(aa_clv_kernel, dim3(bx, (unsigned)cnt, kz), dim3(AA_THREADS), d.stream, o, k, K, A.Pmat.as<double>(), A.clv.as<double>(),
-                       A.exps.as<int>(), slot_stride, (size_t)tile_pad, tile_len, A.tips.as<uint8_t>(), A.P_pad, off);
+        auto clv_launch = [&](const GenOp *o, const GenChild *k, int cnt, bool dot = false) -> int {
+            if (dot)
+                PHB_LAUNCH(aa_clv_kernel<true>, dim3(bx, (unsigned)cnt, 1), dim3(AA_THREADS), d.stream, o, k, K, A.Pmat.as<double>(), A.clv.as<double>(),
+                           A.exps.as<int>(), slot_stride, (size_t)tile_pad, tile_len, A.tips.as<uint8_t>(), A.P_pad, off, Md,
+                           (const double *)A.leaf_ls.as<double>(), (const double *)A.mult.as<double>(), A.partials.as<double>());
+            else
+                PHB_LAUNCH(aa_clv_kernel<false>, dim3(bx, (unsigned)cnt, kz), dim3(AA_THREADS), d.stream, o, k, K, A.Pmat.as<double>(), A.clv.as<double>(),
+                           A.exps.as<int>(), slot_stride, (size_t)tile_pad, tile_len, A.tips.as<uint8_t>(), A.P_pad, off, (const AaModelDev *)nullptr,
+                           (const double *)nullptr, (const double *)nullptr, (double *)nullptr);
             CHECK_LAUNCH();
             return PHB_OK;
         };
@@ -533,10 +541,14 @@ int aa_score_nni(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uint8_
                 CHECK_LAUNCH();
             }
         for (const Batch &bt : batches) {
+            // with upper partials every neighbour has exactly two steps; the second one (p') is fused with the dot product
+            const bool fuse = use_upper && K <= AA_CSTAGE;
             for (size_t j = 0; j + 1 < bt.step_off.size(); ++j)
-                if ((rc = clv_launch(A.nni_ops.as<GenOp>() + bt.step_off[j], A.nni_kids.as<GenChild>(), bt.step_off[j + 1] - bt.step_off[j])))
+                if ((rc = clv_launch(A.nni_ops.as<GenOp>() + bt.step_off[j], A.nni_kids.as<GenChild>(), bt.step_off[j + 1] - bt.step_off[j],
+                                     fuse && j == 1)))
                     return rc;
-            PHB_LAUNCH(aa_nni_root_kernel, dim3(bx, (unsigned)bt.count), dim3(AA_THREADS), d.stream, A.nni_roots.as<int>() + bt.first,
+            if (!fuse)
+                PHB_LAUNCH(aa_nni_root_kernel, dim3(bx, (unsigned)bt.count), dim3(AA_THREADS), d.stream, A.nni_roots.as<int>() + bt.first,
                        A.nni_roots.as<int>() + valid.size() + bt.first, Md,
                        A.clv.as<double>(), A.exps.as<int>(), slot_stride, (size_t)tile_pad, tile_len, off, A.leaf_ls.as<double>(),
                        A.mult.as<double>(), A.partials.as<double>());
