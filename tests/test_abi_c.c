@@ -1,7 +1,7 @@
 /* The C ABI exercised from plain C, in exactly the order the Rust shim (bindings/shim/b200.rs) calls it:
  *   ctx -> set_model -> set_tree -> compress_rows -> log_likelihood          (TreeLikelihood::log_likelihood)
  *   ctx -> set_alignment -> set_model -> set_tree -> marginal_asr            (MarginalAsr::marginal_asr)
- *   joint_asr, score_nni, score_trees on the same context.
+ *   joint_asr, score_nni, score_trees on the same context; then the same order in a 20-state context.
  * No Python in between.  The fixture is the reference's own (src/tree/likelihood/integration_test.rs:14-17):
  * tree ((A:0.601,B:0.301)C:0.100,D:0.200)E:0.001 under JC69; the expected values are the known answers of
  * tests/golden/kat.json (brute-force enumeration, checked against the oracle).
@@ -33,6 +33,95 @@ static int failures = 0;
             ++failures;                                                                   \
         }                                                                                 \
     } while (0)
+
+/* The same call order in a 20-state context (PHB_FLAG_AMINO_ACID) under the equal-rates (Poisson) model: pi = 1/20,
+ * Q normalised to mean rate 1 has eigenvalues 0 and -20/19 (x19) and ANY orthonormal basis with a constant first column
+ * as eigenvectors (a Helmert basis here), so P_ii(t) = 1/20 + 19/20 e^(-20t/19), P_ij(t) = 1/20 - 1/20 e^(-20t/19) in
+ * closed form: the expected log-likelihood is a brute-force sum over the 400 states of the two internal nodes. */
+static double poisson_p(int i, int j, double t)
+{
+    const double e = exp(-20.0 * t / 19.0);
+    return i == j ? 0.05 + 0.95 * e : 0.05 - 0.05 * e;
+}
+static double amino_acid_section(const int32_t *post, const int32_t *off, const int32_t *kids, const double *blen,
+                                 const int32_t *leaf_row, const int32_t *post2, const int32_t *kids2)
+{
+    phb_ctx *ctx = NULL;
+    OK(phb_ctx_create(NULL, 0, PHB_FLAG_AMINO_ACID, &ctx));
+    if (!ctx) return NAN;
+    double lambda[20], V[400], pi[20], sp[20], isp[20];
+    for (int i = 0; i < 20; ++i) {
+        lambda[i] = i ? -20.0 / 19.0 : 0.0;
+        pi[i] = 0.05;
+        sp[i] = sqrt(0.05);
+        isp[i] = 1.0 / sqrt(0.05);
+        V[i] = 1.0 / sqrt(20.0); /* column 0; V[i + 20 * k] */
+    }
+    for (int k = 1; k < 20; ++k)
+        for (int i = 0; i < 20; ++i) V[i + 20 * k] = i < k ? 1.0 / sqrt((double)k * (k + 1)) : i == k ? -k / sqrt((double)k * (k + 1)) : 0.0;
+    const double rates[1] = {1.0}, weights[1] = {1.0};
+    const char *canon = "ACDEFGHIKLMNPQRSTVWY";
+    /* rows A, B, D; 8 sites, 4 distinct columns twice; X (any state) in the last one */
+    const char *A = "MKVLMKVL", *B = "MRVXMRVX", *D = "MKWLMKWL";
+    const uint8_t *rows[3] = {(const uint8_t *)A, (const uint8_t *)B, (const uint8_t *)D};
+    OK(phb_set_model(ctx, lambda, V, pi, sp, isp, 1, rates, weights));
+    OK(phb_set_tree(ctx, 5, post, off, kids, blen, leaf_row, 0));
+    int64_t n_pat = 0;
+    uint64_t s2p[8], mult[8];
+    OK(phb_compress_rows(ctx, 3, 8, rows, &n_pat, s2p, mult));
+    CHECK(n_pat == 4, "20 states: 4 distinct columns expected, got %lld", (long long)n_pat);
+    for (int i = 0; i < 8; ++i) CHECK(s2p[i] == (uint64_t)(i & 3), "20 states: site_to_pattern[%d] = %llu", i, (unsigned long long)s2p[i]);
+    uint8_t back[12];
+    OK(phb_get_alignment(ctx, back, PHB_LAYOUT_ROW_MAJOR, 0, 4));
+    CHECK(!memcmp(back, "MKVL", 4) && !memcmp(back + 4, "MRVX", 4) && !memcmp(back + 8, "MKWL", 4), "20 states: patterns read back");
+    double total = 0, per[4];
+    OK(phb_log_likelihood(ctx, &total, per));
+    /* brute force: root E (state e) -> C (state c, 0.100) -> A (0.601), B (0.301); E -> D (0.200) */
+    double expect = 0;
+    for (int p = 0; p < 4; ++p) {
+        const int a = (int)(strchr(canon, A[p]) - canon), d = (int)(strchr(canon, D[p]) - canon);
+        const int b = B[p] == 'X' ? -1 : (int)(strchr(canon, B[p]) - canon);
+        double site = 0;
+        for (int e = 0; e < 20; ++e)
+            for (int c = 0; c < 20; ++c) {
+                double pb = 0;
+                for (int x = 0; x < 20; ++x)
+                    if (b < 0 || b == x) pb += poisson_p(c, x, blen[4]);
+                site += 0.05 * poisson_p(e, c, blen[1]) * poisson_p(c, a, blen[3]) * pb * poisson_p(e, d, blen[2]);
+            }
+        CHECK(fabs(per[p] - log(site)) <= 1e-12, "20 states: pattern %d lnL %.17g, closed form %.17g", p, per[p], log(site));
+        expect += 2.0 * log(site);
+    }
+    CHECK(fabs(total - expect) <= 1e-12 * fabs(expect), "20 states: total %.17g, closed form %.17g", total, expect);
+    /* P(t) itself */
+    double Pm[400];
+    const double t1[1] = {0.301};
+    OK(phb_transition_matrices(ctx, 1, t1, Pm));
+    CHECK(fabs(Pm[0] - poisson_p(0, 0, 0.301)) <= 1e-14 && fabs(Pm[7 * 20 + 3] - poisson_p(7, 3, 0.301)) <= 1e-14, "20 states: P(0.301)");
+    /* marginal and joint ASR: leaves reproduce their letters */
+    uint8_t states[5 * 4], jstates[5 * 4];
+    double t_asr = 0, t_joint = 0;
+    OK(phb_marginal_asr(ctx, states, NULL, &t_asr));
+    OK(phb_joint_asr(ctx, jstates, &t_joint));
+    CHECK(fabs(t_asr - total) <= 1e-12 * fabs(total) && t_joint <= total + 1e-9, "20 states: ASR totals %.17g / %.17g", t_asr, t_joint);
+    for (int p = 0; p < 4; ++p) {
+        CHECK(canon[states[3 * 4 + p]] == A[p] && canon[jstates[3 * 4 + p]] == A[p], "20 states: leaf A pattern %d", p);
+        CHECK(canon[states[2 * 4 + p]] == D[p] && canon[jstates[2 * 4 + p]] == D[p], "20 states: leaf D pattern %d", p);
+    }
+    /* NNI around C against the hand-built neighbour through score_trees */
+    const int32_t nid[3] = {1, 1, 3};
+    const uint8_t left[3] = {0, 1, 0};
+    double nni[3], sc[2];
+    OK(phb_score_nni(ctx, 3, nid, left, nni));
+    CHECK(isfinite(nni[0]) && isfinite(nni[1]) && isnan(nni[2]), "20 states: NNI values");
+    phb_tree_desc cand[2] = {{5, post, off, kids, blen, leaf_row, 0}, {5, post2, off, kids2, blen, leaf_row, 0}};
+    OK(phb_score_trees(ctx, 2, cand, sc));
+    CHECK(fabs(sc[0] - total) <= 1e-12 * fabs(total), "20 states: score_trees(base) %.17g vs %.17g", sc[0], total);
+    CHECK(fabs(sc[1] - nni[0]) <= 1e-10 * fabs(sc[1]) || fabs(sc[1] - nni[1]) <= 1e-10 * fabs(sc[1]),
+          "20 states: the hand-built neighbour %.17g must equal one of phb_score_nni's %.17g / %.17g", sc[1], nni[0], nni[1]);
+    phb_ctx_destroy(ctx);
+    return total;
+}
 
 int main(void)
 {
@@ -140,6 +229,8 @@ int main(void)
     CHECK(rc == PHB_ERR_ALPHABET_MISMATCH, "unaccepted byte in a leaf row -> AlphabetMismatch, got %d", rc);
 
     phb_ctx_destroy(ctx);
+    const double lnl20 = amino_acid_section(post, off, kids, blen, leaf_row, post2, kids2);
+    printf("20-state lnL %.12f\n", lnl20);
     printf("lnL %.12f  joint %.12f  nni %.12f %.12f  -> %s\n", total, jtotal, nni[0], nni[1], failures ? "FAILED" : "ok");
     return failures ? 1 : 0;
 }
