@@ -383,6 +383,137 @@ aa_clv_kernel(const GenOp *__restrict__ ops, const GenChild *__restrict__ kids, 
     }
 }
 
+// ---- one NNI neighbour in ONE pass (aa_score_nni with upper partials, n_cat <= AA_CSTAGE): the update of v (op ops_v[y]),
+// the update of its re-linked parent p (op ops_p[y], one of whose children is v's scratch slot) and the dot product with
+// up(p) (slot ops_p[y].pad - 1), per category; v's new vector stays in registers -- neither it nor p's is written.
+// In p's product the factor coming from v is taken first (the others follow in list order), so that v's vector is dead
+// before the next child's is formed: 128 registers as in aa_clv_kernel.  The matrices of a child batch are staged per
+// category.  partials[y][block] = sum over the block's patterns of multiplicity * site_ll.
+__global__ void __launch_bounds__(AA_THREADS, PHB_AA_MINB)
+aa_nni_pair_kernel(const GenOp *__restrict__ ops_v, const GenOp *__restrict__ ops_p, const GenChild *__restrict__ kids, int n_cat,
+                   const double *__restrict__ Pmat, const double *__restrict__ clv, const int *__restrict__ exps, size_t slot_stride,
+                   size_t tile_pad, int tile_len, const uint8_t *__restrict__ tips, int64_t P_pad, int64_t tile_off,
+                   const AaModelDev *__restrict__ M, const double *__restrict__ leaf_ls, const double *__restrict__ mult,
+                   double *__restrict__ partials)
+{
+    __shared__ __align__(16) double Pt[AA_STAGE][AA_NS * AA_NS];
+    __shared__ double red[AA_THREADS];
+    const GenOp opv = ops_v[blockIdx.y], opp = ops_p[blockIdx.y];
+    int64_t site = (int64_t)blockIdx.x * AA_THREADS + threadIdx.x;
+    const bool active = site < tile_len;
+    if (!active) site = 0;
+    int inline_kid = opp.child_begin; // p's child that is v
+    for (int k = opp.child_begin; k < opp.child_end; ++k)
+        if (!kids[k].is_tip && kids[k].src == opv.out_slot) inline_kid = k;
+    const int edge_v = kids[inline_kid].edge;
+    double kept[AA_CSTAGE];
+    // stage the transposed P(t) of up to AA_STAGE children (edges given by `edge_of`) for category `cat`
+    auto stage = [&](int n, auto edge_of, int cat) {
+        __syncthreads(); // the previous matrices are no longer read
+        for (int idx = threadIdx.x; idx < n * AA_NS * AA_NS; idx += AA_THREADS) {
+            const int k = idx / (AA_NS * AA_NS), e = idx - k * (AA_NS * AA_NS);
+            Pt[k][(e % AA_NS) * AA_NS + e / AA_NS] = Pmat[((size_t)edge_of(k) * n_cat + cat) * (AA_NS * AA_NS) + e];
+        }
+        __syncthreads();
+    };
+    // y = P_child (child's vector); adds the child's exponent
+    auto child_vec = [&](const double *P_t, const GenChild &ch, int cat, double (&y)[AA_NS], int &ex) {
+        if (ch.is_tip) {
+            aa_tip_col(P_t, tips[(int64_t)ch.src * P_pad + tile_off + site], y);
+        } else {
+            const double *x_src = clv + (size_t)ch.src * slot_stride + (size_t)cat * AA_NS * tile_pad + site;
+            ex += exps[((size_t)ch.src * n_cat + cat) * tile_pad + site];
+            const double x0 = x_src[0];
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) y[i] = P_t[i] * x0;
+#pragma unroll
+            for (int j = 1; j < AA_NS; ++j) {
+                const double xj = x_src[(size_t)j * tile_pad];
+#pragma unroll
+                for (int i = 0; i < AA_NS; ++i) y[i] += P_t[j * AA_NS + i] * xj;
+            }
+        }
+    };
+#pragma unroll 1
+    for (int c = 0; c < n_cat && c < AA_CSTAGE; ++c) {
+        double acc[AA_NS];
+#pragma unroll
+        for (int i = 0; i < AA_NS; ++i) acc[i] = 1.0;
+        int ex = 0;
+        for (int k0 = opv.child_begin; k0 < opv.child_end; k0 += AA_STAGE) { // v without the moved child, with its former sibling
+            const int nb = min(AA_STAGE, opv.child_end - k0);
+            stage(nb, [&](int k) { return kids[k0 + k].edge; }, c);
+            for (int k = 0; k < nb; ++k) {
+                double y[AA_NS];
+                child_vec(Pt[k], kids[k0 + k], c, y, ex);
+#pragma unroll
+                for (int i = 0; i < AA_NS; ++i) acc[i] *= y[i];
+            }
+        }
+        ex += aa_normalize(acc);
+        // p: the factor through v first ...
+        stage(1, [&](int) { return edge_v; }, c);
+        {
+            double y[AA_NS];
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) y[i] = Pt[0][i] * acc[0];
+#pragma unroll
+            for (int j = 1; j < AA_NS; ++j) {
+#pragma unroll
+                for (int i = 0; i < AA_NS; ++i) y[i] += Pt[0][j * AA_NS + i] * acc[j];
+            }
+#pragma unroll
+            for (int i = 0; i < AA_NS; ++i) acc[i] = y[i];
+        }
+        // ... then its other children in list order, the inline one skipped
+        for (int k0 = opp.child_begin; k0 < opp.child_end; k0 += AA_STAGE) {
+            const int nb = min(AA_STAGE, opp.child_end - k0);
+            bool any = false;
+            for (int k = 0; k < nb; ++k) any |= (k0 + k != inline_kid);
+            if (!any) continue;
+            stage(nb, [&](int k) { return kids[k0 + k].edge; }, c);
+            for (int k = 0; k < nb; ++k) {
+                if (k0 + k == inline_kid) continue;
+                double y[AA_NS];
+                child_vec(Pt[k], kids[k0 + k], c, y, ex);
+#pragma unroll
+                for (int i = 0; i < AA_NS; ++i) acc[i] *= y[i];
+            }
+        }
+        ex += aa_normalize(acc);
+        const int up = opp.pad - 1;
+        const double *u = clv + (size_t)up * slot_stride + (size_t)c * AA_NS * tile_pad + site;
+        ex += exps[((size_t)up * n_cat + c) * tile_pad + site];
+        double mass = u[0] * acc[0];
+#pragma unroll
+        for (int i = 1; i < AA_NS; ++i) mass += u[(size_t)i * tile_pad] * acc[i];
+        kept[c] = M->ln_weights[c] + log(mass) + (double)ex * 0.69314718055994530942;
+    }
+    double weighted = 0.0;
+    if (active) {
+        double mx = -INFINITY;
+#pragma unroll
+        for (int c = 0; c < AA_CSTAGE; ++c)
+            if (c < n_cat) mx = fmax(mx, kept[c]);
+        double lse = mx;
+        if (isfinite(mx)) {
+            double sum = 0.0;
+#pragma unroll
+            for (int c = 0; c < AA_CSTAGE; ++c)
+                if (c < n_cat) sum += exp(kept[c] - mx);
+            lse = mx + log(sum);
+        }
+        weighted = mult[tile_off + site] * (lse + leaf_ls[tile_off + site]);
+    }
+    red[threadIdx.x] = weighted;
+    __syncthreads();
+    for (int s = AA_THREADS / 2; s > 0; s >>= 1) {
+        if ((int)threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) partials[(size_t)blockIdx.y * gridDim.x + blockIdx.x] = red[0];
+}
+
 // the root's vector for one (pattern, category): its CLV, or its tip profile when the tree is a single leaf
 __device__ __forceinline__ void aa_load_vec(const double *__restrict__ clv, size_t slot_stride, size_t tile_pad, int slot, int cat,
                                             int64_t site, double (&x)[AA_NS])

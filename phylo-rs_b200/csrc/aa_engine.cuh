@@ -374,7 +374,13 @@ int aa_score_nni(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uint8_
     const int B = (int)std::min<size_t>(valid.size(), AA_NNI_BATCH);
     // slots: [0, n_int) the base tree's CLVs | pi | the upper partials by the node's slot | two per neighbour of a batch
     const int pi_slot = n_int, upper_base = n_int + 1, scratch_base = upper_base + (use_upper ? n_int : 0);
-    const int n_slots = scratch_base + 2 * B;
+    // With upper partials and all categories in one block, v, p and the dot product are ONE launch per batch
+    // (aa_nni_pair_kernel) and nothing of a neighbour is written: no scratch slots.  PHB_AA_NNI_NO_PAIR=1 (cross-check)
+    // keeps v in a scratch slot and fuses only p with the dot product (aa_clv_kernel<true>).
+    const char *nopair_env = getenv("PHB_AA_NNI_NO_PAIR");
+    const bool fuse = use_upper && K <= AA_CSTAGE;
+    const bool pair = fuse && !(nopair_env && nopair_env[0] == '1');
+    const int n_slots = scratch_base + (pair ? 0 : 2 * B);
     // ---- upper ops by depth, for the parents the moves name and their ancestors
     std::vector<GenOp> ops;
     std::vector<GenChild> kids;
@@ -542,8 +548,14 @@ int aa_score_nni(phb_ctx *ctx, int n_moves, const int32_t *node_id, const uint8_
             }
         for (const Batch &bt : batches) {
             // with upper partials every neighbour has exactly two steps; the second one (p') is fused with the dot product
-            const bool fuse = use_upper && K <= AA_CSTAGE;
-            for (size_t j = 0; j + 1 < bt.step_off.size(); ++j)
+            if (pair) {
+                PHB_LAUNCH(aa_nni_pair_kernel, dim3(bx, (unsigned)bt.count), dim3(AA_THREADS), d.stream, A.nni_ops.as<GenOp>() + bt.step_off[0],
+                           A.nni_ops.as<GenOp>() + bt.step_off[1], A.nni_kids.as<GenChild>(), K, A.Pmat.as<double>(), A.clv.as<double>(),
+                           A.exps.as<int>(), slot_stride, (size_t)tile_pad, tile_len, A.tips.as<uint8_t>(), A.P_pad, off, Md,
+                           A.leaf_ls.as<double>(), A.mult.as<double>(), A.partials.as<double>());
+                CHECK_LAUNCH();
+            }
+            for (size_t j = 0; !pair && j + 1 < bt.step_off.size(); ++j)
                 if ((rc = clv_launch(A.nni_ops.as<GenOp>() + bt.step_off[j], A.nni_kids.as<GenChild>(), bt.step_off[j + 1] - bt.step_off[j],
                                      fuse && j == 1)))
                     return rc;

@@ -144,13 +144,17 @@ def _star_and_polytomy(lib):
 
 
 class _path_mode:
-    """PHB_AA_NNI_PATH=1: aa_score_nni without upper partials (every neighbour re-evaluates its whole path v -> root)"""
+    """PHB_AA_NNI_PATH=1: aa_score_nni without upper partials (every neighbour re-evaluates its whole path v -> root);
+    PHB_AA_NNI_NO_PAIR=1: upper partials, but v goes through a scratch slot instead of staying in registers"""
+
+    def __init__(self, var="PHB_AA_NNI_PATH"):
+        self.var = var
 
     def __enter__(self):
-        os.environ["PHB_AA_NNI_PATH"] = "1"
+        os.environ[self.var] = "1"
 
     def __exit__(self, *exc):
-        del os.environ["PHB_AA_NNI_PATH"]
+        del os.environ[self.var]
 
 
 def _rearrangements(lib):
@@ -166,11 +170,17 @@ def _rearrangements(lib):
     full, st_full = _cases.check_nni(lib, case, flags=AA | capi.FLAG_NNI_FULL, expect_path=False)
     assert np.array_equal(walked, full, equal_nan=True) and st_full["nni_path_moves"] == 0
     assert np.allclose(got, full, rtol=1e-12, atol=0, equal_nan=True) and 0 < st["nni_path_steps"] < st_w["nni_path_steps"]
-    # 3 tiles of 256 patterns (29 CLVs + pi + 29 upper partials + 2 x 56 scratch slots), every move ten times: 3 batches
+    case4 = workloads.make_case(13, 70, model="aa_g4", seed=16, ambiguity=0.1)  # 4 categories: one launch per batch
+    got4, _ = _cases.check_nni(lib, case4, flags=AA)
+    with _path_mode("PHB_AA_NNI_NO_PAIR"):
+        two4, _ = _cases.check_nni(lib, case4, flags=AA)
+    full4, _ = _cases.check_nni(lib, case4, flags=AA | capi.FLAG_NNI_FULL, expect_path=False)
+    assert np.allclose(got4, full4, rtol=1e-12, atol=0, equal_nan=True) and np.allclose(two4, full4, rtol=1e-12, atol=0, equal_nan=True)
+    # 3 tiles of 256 patterns (29 CLVs + pi + 29 upper partials), every move ten times: 3 batches
     case = workloads.make_case(30, 600, model="aa_g4", seed=18, ambiguity=0.05)
     n = case.ft["n_nodes"]
     moves = [(v, lc) for v in range(n) for lc in (0, 1)]
-    got, st = _cases.check_nni(lib, case, moves=moves, flags=AA, budget=(59 + 2 * 56) * 4 * 164 * 256)  # 56 valid moves
+    got, st = _cases.check_nni(lib, case, moves=moves, flags=AA, budget=59 * 4 * 164 * 256)
     assert st["nni_tiles"] == 3
     with capi.Context(flags=AA, library=lib) as ctx:
         workloads.load_into(ctx, case)
@@ -187,6 +197,9 @@ def _rearrangements(lib):
         a, _ = _cases.check_nni(lib, c20, flags=AA)
         with _path_mode():
             w, _ = _cases.check_nni(lib, c20, flags=AA)
+        with _path_mode("PHB_AA_NNI_NO_PAIR"):
+            t2, _ = _cases.check_nni(lib, c20, flags=AA)
+        assert np.allclose(a, t2, rtol=1e-12, atol=0, equal_nan=True)
         b, _ = _cases.check_nni(lib, c20, flags=AA | capi.FLAG_NNI_FULL, expect_path=False)
         assert np.array_equal(w, b, equal_nan=True) and np.isfinite(a).sum() >= 4
         assert np.allclose(a, b, rtol=1e-12, atol=0, equal_nan=True)
