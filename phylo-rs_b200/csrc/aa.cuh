@@ -8,6 +8,10 @@
 //   aa_clv_kernel          one level of prune_pattern_category            likelihood.rs:110-131
 //   aa_root_kernel         root mass, ln weights, log_sum_exp, weighting  likelihood.rs:135-140, 61-68, 205-206
 //   aa_down_kernel         one depth of the marginal pre-order pass       likelihood.rs:303-390
+//   aa_joint_*_kernel      joint (Viterbi) reconstruction                 likelihood.rs:421-560
+//   aa_pack / aa_gather_patterns / aa_unpack_kernel   bytes <-> tip codes (set_alignment, compress_*, get_alignment)
+//   aa_upper / aa_nni_pair / aa_nni_root_kernel, aa_clv_kernel<true>   NNI neighbours against resident CLVs and upper
+//                          partials (caller loop: NNI::nni tree.rs:1213-1242 + log_likelihood)
 // Work split: one thread = one site pattern of one rate category (all categories in the down pass, where the mixture
 // over categories is thread-local); a block works on ONE (node, category), so every P(t) it touches is block-uniform
 // and is staged once in shared memory and read by broadcast.  Per internal child that is a 20x20 mat-vec per thread
