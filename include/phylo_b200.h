@@ -75,6 +75,7 @@ extern "C" {
  *                            the alphabet, as Alignment::compress_columns does not); the unique columns are encoded to
  *                            20-state tip codes on the device;
  *   phb_get_alignment        the 25 accepted bytes read back as themselves, any other byte as '?';
+ *   phb_log_likelihood_host  phb_set_alignment + phb_log_likelihood in one call (not overlapped);
  *   phb_score_nni            every neighbour is two node updates and a dot product against the base tree's resident
  *                            partials and upper partials (any arity);
  *   phb_score_trees          every candidate is re-scheduled and scored in full against the resident alignment;

@@ -2541,7 +2541,6 @@ int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns
                                 const uint64_t *multiplicity, double *total, double *per_pattern)
 {
     if (!ctx || !total) return PHB_ERR_INVALID_ARGUMENT;
-    if (ctx->is_aa) return ctx->fail(PHB_ERR_STATE, "log_likelihood_host: not available in a 20-state (PHB_FLAG_AMINO_ACID) context");
     if (n_rows < 0 || n_patterns < 0 || (layout != PHB_LAYOUT_PATTERN_MAJOR && layout != PHB_LAYOUT_ROW_MAJOR) ||
         (!bytes && n_rows > 0 && n_patterns > 0))
         return ctx->fail(PHB_ERR_INVALID_ARGUMENT, "log_likelihood_host: bad arguments");
@@ -2549,7 +2548,8 @@ int32_t phb_log_likelihood_host(phb_ctx *ctx, int32_t n_rows, int64_t n_patterns
         return ctx->fail(PHB_ERR_STATE, "set_model and set_tree must precede log_likelihood_host");
     const TreeSched &T = ctx->tree;
     const ModelDev &M = ctx->model;
-    const bool fused = layout == PHB_LAYOUT_PATTERN_MAJOR && !(ctx->flags & PHB_FLAG_LEVEL_KERNELS) && T.n_internal > 0 &&
+    // (a 20-state context takes the two-call path: its packing kernel already runs chunk by chunk behind the copies)
+    const bool fused = !ctx->is_aa && layout == PHB_LAYOUT_PATTERN_MAJOR && !(ctx->flags & PHB_FLAG_LEVEL_KERNELS) && T.n_internal > 0 &&
                        M.n_clv > 0 && M.n_cat <= 4 * M.n_clv && n_patterns > 0 && n_rows > 0;
     if (!fused) { // the general two-call path
         int rc = phb_set_alignment(ctx, n_rows, n_patterns, bytes, layout, multiplicity);

@@ -270,6 +270,9 @@ def _abi_behaviour(lib):
         ctx.set_alignment(case.patterns)
         assert ctx.log_likelihood() == tot
         assert np.array_equal(ctx.get_alignment(), case.patterns)
+        # host bytes in, lnL out: the same values as the two calls
+        tot_h, per_h = ctx.log_likelihood_host(case.patterns, per_pattern=True)
+        assert tot_h == tot and np.array_equal(per_h, ctx.log_likelihood(per_pattern=True)[1])
         # P(t) at 20 states, exact identity at t == 0
         Pm = ctx.transition_matrices(np.array([0.0, 0.3]), len(m.rates))
         assert np.array_equal(Pm[0, 0], np.eye(20)) and Pm.shape == (2, len(m.rates), 20, 20)
