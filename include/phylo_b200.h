@@ -79,8 +79,8 @@ extern "C" {
  *   phb_score_nni            every neighbour is two node updates and a dot product against the base tree's resident
  *                            partials and upper partials (any arity);
  *   phb_score_trees          every candidate is re-scheduled and scored in full against the resident alignment;
- * rate-0 categories are evaluated literally (identity P).  One device per context.  Every other entry point returns
- * PHB_ERR_STATE. */
+ * rate-0 categories are evaluated literally (identity P).  One device per context.  phb_simulate_alignment and
+ * phb_transition_matrices_noalloc have no 20-state form and return PHB_ERR_STATE. */
 #define PHB_FLAG_AMINO_ACID (1ull << 5)
 
 /* ---- alignment layouts --------------------------------------------------------------------- */
